@@ -1,0 +1,401 @@
+/*
+ * tafl.h — C ABI of libtafl_b200.so, the B200-native lockstep Hnefatafl engine.
+ *
+ * Every entry point is the batched equivalent of one public item of the reference
+ * `hnefatafl` crate (paths relative to the reference tree) or of `src/mcts.py`; the item each
+ * one replaces is cited beside it.  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions
+ *  - every call returns TAFL_OK (0) or a negative tafl_err; no exceptions cross the ABI.
+ *  - buffers named `h_*` are HOST pointers (copied inside the call), `d_*` are DEVICE pointers
+ *    on the engine's device (no copy).  The caller owns every buffer.
+ *  - an engine is thread-compatible: one caller at a time per handle.  All work is enqueued on
+ *    the engine's own CUDA stream; blocking calls return after the stream is synchronised,
+ *    `_async` variants return after enqueue.
+ *  - there is no CPU fallback: if no CUDA device is usable, tafl_engine_create fails with
+ *    TAFL_ERR_CUDA and nothing else can be called.
+ */
+#ifndef TAFL_B200_H
+#define TAFL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * Enumerations (values follow the reference's declaration order)
+ * ---------------------------------------------------------------------------------------- */
+
+/* pieces.rs:13-17  `enum Side { Attacker = 0, Defender = 8 }` */
+enum { TAFL_ATTACKER = 0, TAFL_DEFENDER = 8 };
+
+/* pieces.rs:31-38  `enum PieceType` bit flags; PieceSet (pieces.rs:157) = type << side */
+enum { TAFL_KING = 1, TAFL_SOLDIER = 2, TAFL_KNIGHT = 4, TAFL_COMMANDER = 8, TAFL_GUARD = 16,
+       TAFL_MERCENARY = 32 };
+#define TAFL_PIECESET_NONE 0x0000u
+#define TAFL_PIECESET_ALL  0xFFFFu
+#define TAFL_PIECESET_TYPE(t) ((uint16_t)((t) | ((t) << 8)))     /* PieceSet::from_piece_type */
+#define TAFL_PIECESET_SIDE(s) ((uint16_t)(0x00FFu << (s)))       /* PieceSet::from(Side)      */
+#define TAFL_PIECESET_PIECE(t, s) ((uint16_t)((t) << (s)))       /* PieceSet::from_piece      */
+
+/* tiles.rs:167-170  `enum Axis { Vertical = 0, Horizontal = 0x80 }` */
+enum { TAFL_VERTICAL = 0, TAFL_HORIZONTAL = 0x80 };
+
+/* rules.rs:6-17 */
+enum { TAFL_THRONE_NOTHRONE = 0, TAFL_THRONE_NOPASS = 1, TAFL_THRONE_KINGPASS = 2,
+       TAFL_THRONE_NOENTRY = 3, TAFL_THRONE_KINGENTRY = 4 };
+/* rules.rs:22-30 */
+enum { TAFL_KING_STRONG = 0, TAFL_KING_STRONG_BY_THRONE = 1, TAFL_KING_WEAK = 2 };
+/* rules.rs:34-42 */
+enum { TAFL_KING_ARMED = 0, TAFL_KING_ANVIL = 1, TAFL_KING_HAMMER = 2 };
+/* rules.rs:64-69; 0 = Option::None */
+enum { TAFL_ENCL_NONE = 0, TAFL_ENCL_WITH_EDGE_ACCESS = 1, TAFL_ENCL_WITHOUT_EDGE_ACCESS = 2 };
+
+/* error.rs:50-71  `enum PlayInvalid`, declaration order, 0 = Ok */
+enum { TAFL_PLAY_OK = 0, TAFL_WRONG_PLAYER = 1, TAFL_NO_PIECE = 2, TAFL_OUT_OF_BOUNDS = 3,
+       TAFL_NO_COMMON_AXIS = 4, TAFL_BLOCKED_BY_PIECE = 5, TAFL_MOVE_THROUGH_BLOCKED_TILE = 6,
+       TAFL_MOVE_ONTO_BLOCKED_TILE = 7, TAFL_TOO_FAR = 8, TAFL_GAME_OVER = 9 };
+
+/* game/mod.rs:17-33  `enum WinReason`, declaration order */
+enum { TAFL_WIN_KING_ESCAPED = 0, TAFL_WIN_EXIT_FORT = 1, TAFL_WIN_KING_CAPTURED = 2,
+       TAFL_WIN_ALL_CAPTURED = 3, TAFL_WIN_ENCLOSED = 4, TAFL_WIN_NO_PLAYS = 5,
+       TAFL_WIN_REPETITION = 6 };
+/* game/mod.rs:37-42  `enum DrawReason` */
+enum { TAFL_DRAW_REPETITION = 0, TAFL_DRAW_NO_PLAYS = 1 };
+
+/* GameStatus (game/mod.rs:64-70) packed in one byte:
+ *   0                      Ongoing
+ *   0x80 | reason<<1 | w   Over(Win(reason, side)),  w = 1 iff side == Defender
+ *   0xC0 | reason<<1       Over(Draw(reason))                                              */
+#define TAFL_STATUS_ONGOING 0u
+#define TAFL_STATUS_WIN(reason, winner_is_defender) \
+    ((uint8_t)(0x80u | ((reason) << 1) | ((winner_is_defender) ? 1u : 0u)))
+#define TAFL_STATUS_DRAW(reason) ((uint8_t)(0xC0u | ((reason) << 1)))
+#define TAFL_STATUS_IS_OVER(s) (((s) & 0x80u) != 0)
+#define TAFL_STATUS_IS_DRAW(s) (((s) & 0xC0u) == 0xC0u)
+#define TAFL_STATUS_REASON(s) (((s) >> 1) & 7u)
+#define TAFL_STATUS_WINNER_IS_DEFENDER(s) (((s) & 1u) != 0)
+
+/* library error codes */
+typedef enum {
+    TAFL_OK = 0,
+    TAFL_ERR_INVALID_ARG = -1,
+    TAFL_ERR_CUDA = -2,          /* no device / CUDA runtime failure: message in tafl_last_error */
+    TAFL_ERR_PARSE_BAD_LINE_LEN = -3,   /* error.rs:11  ParseError::BadLineLen */
+    TAFL_ERR_PARSE_BAD_CHAR = -4,       /* error.rs:13  ParseError::BadChar    */
+    TAFL_ERR_PARSE_EMPTY = -5,          /* error.rs:15  ParseError::EmptyString */
+    TAFL_ERR_PARSE_BAD_INT = -6,        /* error.rs:18  ParseError::BadInt     */
+    TAFL_ERR_PARSE_BAD_PLAY = -7,       /* error.rs:20  ParseError::BadPlay(DisjointTiles) */
+    TAFL_ERR_PARSE_BAD_STRING = -8,     /* error.rs:22  ParseError::BadString  */
+    TAFL_ERR_UNSUPPORTED = -9,   /* board does not fit u64 (<=7) / u128 (<=11) bitfields */
+    TAFL_ERR_CAPACITY = -10,     /* MCTS node/edge pool exhausted                       */
+    TAFL_ERR_NO_PIECE = -11      /* error.rs:44  BoardError::NoPiece                    */
+} tafl_err;
+
+/* ------------------------------------------------------------------------------------------
+ * POD mirrors of the reference types
+ * ---------------------------------------------------------------------------------------- */
+
+/* play.rs:23-27  `struct Play { from: Tile, movement: AxisOffset }` */
+typedef struct {
+    uint8_t from_row, from_col;
+    uint8_t axis;   /* TAFL_VERTICAL | TAFL_HORIZONTAL */
+    int8_t  disp;   /* signed displacement along the axis */
+} tafl_play;
+
+/* rules.rs:83-117  `struct Ruleset` (+ HostilityRules :46-50, ShieldwallRules :54-59,
+ * RepetitionRule :73-79).  Option<..> fields carry an `_enabled` flag / 0 value. */
+typedef struct {
+    uint8_t  edge_escape;
+    uint8_t  king_strength;          /* TAFL_KING_STRONG ..           */
+    uint8_t  king_attack;            /* TAFL_KING_ARMED ..            */
+    uint8_t  shieldwall_enabled;     /* Option<ShieldwallRules>       */
+    uint8_t  sw_corners_may_close;
+    uint8_t  exit_fort;
+    uint8_t  throne_movement;        /* TAFL_THRONE_*                 */
+    uint8_t  starting_side;          /* TAFL_ATTACKER | TAFL_DEFENDER */
+    uint16_t sw_captures;            /* PieceSet                      */
+    uint16_t may_enter_corners;      /* PieceSet                      */
+    uint16_t hostility_throne;       /* PieceSet                      */
+    uint16_t hostility_corners;      /* PieceSet                      */
+    uint16_t hostility_edge;         /* PieceSet                      */
+    uint16_t slow_pieces;            /* PieceSet                      */
+    uint8_t  enclosure_win;          /* TAFL_ENCL_*                   */
+    uint8_t  repetition_enabled;     /* Option<RepetitionRule>        */
+    uint8_t  repetition_is_loss;
+    uint8_t  draw_on_no_plays;
+    uint8_t  linnaean_capture;
+    uint8_t  _pad[3];
+    uint32_t n_repetitions;
+} tafl_rules;
+
+/* One game: `GameState<BitfieldBoardState<T>>` (game/state.rs:120-133) packed to 64 bytes.
+ * This is also the HBM-resident form inside the engine.
+ *
+ * att/def are the two bitfield words of BitfieldBoardState (board/state.rs:117-121) in the
+ * REFERENCE bit layout: bit (row*ROW_WIDTH + col), ROW_WIDTH = 7 for u64 boards and 11 for u128
+ * boards (bitfield.rs:178-179); the king's row lives in the top nibble of `def`, its column in
+ * the top nibble of `att` (board/state.rs:127-147).  For u128 boards [0] is the low 64 bits and
+ * the nibble is bits 60..63 of [1]; for u64 boards only [0] is used (nibble = bits 60..63 of
+ * [0]) and [1] must be 0. */
+typedef struct {
+    uint64_t att[2];
+    uint64_t def[2];
+    /* RepetitionTracker.recent_plays (game/state.rs:49, utils.rs:30-81): ring of 4 records.
+     * byte0 from_row, byte1 from_col, byte2 disp (int8), byte3 flags:
+     *   bit0 Some(..), bit1 captures, bit2 side==Defender, bit3 axis==Horizontal */
+    uint32_t recent[4];
+    uint8_t  att_reps, def_reps;     /* RepetitionTracker.{attacker,defender}_reps (saturating) */
+    uint8_t  flags;                  /* bit0 attacker_mid_pair, bit1 defender_mid_pair,
+                                        bit2 side_to_play == Defender                        */
+    uint8_t  status;                 /* packed GameStatus, see TAFL_STATUS_*                 */
+    uint32_t turn;                   /* GameState.turn                                       */
+    uint32_t plays_since_capture;    /* GameState.plays_since_capture (write-only upstream)  */
+    uint8_t  ring_head;              /* FixedSizeQueue.first_i                               */
+    uint8_t  side_len;               /* BitfieldBoardState.side_len                          */
+    uint8_t  _pad[2];
+} tafl_state;
+
+#define TAFL_FLAG_ATT_MID 1u
+#define TAFL_FLAG_DEF_MID 2u
+#define TAFL_FLAG_DEF_TO_PLAY 4u
+
+#define TAFL_REC_SOME 1u
+#define TAFL_REC_CAPTURES 2u
+#define TAFL_REC_DEFENDER 4u
+#define TAFL_REC_HORIZONTAL 8u
+
+/* Effects of one play: `PlayRecord.effects` (play.rs:106-113, game/mod.rs:56-61).  The capture
+ * set is a tile bitboard in the board's own bit layout (no nibbles). */
+typedef struct {
+    uint64_t captures[2];
+    uint8_t  status;        /* game outcome after the play, packed GameStatus */
+    uint8_t  err;           /* PlayInvalid code, 0 if the play was applied     */
+    uint8_t  n_captures;
+    uint8_t  _pad[5];
+} tafl_play_effects;
+
+/* `Enclosure` (logic.rs:25-32) as three tile bitboards; found == 0 mirrors Option::None. */
+typedef struct {
+    uint64_t occupied[2];
+    uint64_t unoccupied[2];
+    uint64_t boundary[2];
+    uint8_t  found;
+    uint8_t  _pad[7];
+} tafl_enclosure;
+
+/* Compact move: from_bit | to_bit << 7, bit indices in the board's own layout.
+ * TAFL_MAX_MOVES bounds a legal-move list (<= pieces * 2(N-1); 512 is safe for 11x11). */
+typedef uint16_t tafl_move;
+#define TAFL_MOVE_FROM(m) ((m) & 127u)
+#define TAFL_MOVE_TO(m) (((m) >> 7) & 127u)
+#define TAFL_MAX_MOVES 512
+
+/* presets (preset.rs) */
+enum { TAFL_PRESET_COPENHAGEN = 0, TAFL_PRESET_BRANDUBH = 1, TAFL_PRESET_MAGPIE = 2,
+       TAFL_PRESET_TABLUT = 3, TAFL_PRESET_KOCH = 4 };
+
+/* ------------------------------------------------------------------------------------------
+ * Host-only helpers (no device needed)
+ * ---------------------------------------------------------------------------------------- */
+
+/* preset::rules::{COPENHAGEN,BRANDUBH,MAGPIE,TABLUT,KOCH}  (preset.rs:12-124) */
+int tafl_preset_rules(int preset_id, tafl_rules* out);
+/* preset::boards::{COPENHAGEN,BRANDUBH,MAGPIE,TABLUT} (preset.rs:127-134); KOCH has no board of
+ * its own upstream — the demo pairs it with the Brandubh board (game/main.rs:137-140). */
+int tafl_preset_board_fen(int preset_id, const char** out_fen);
+
+/* BoardState::from_fen (board/state.rs:225-250) + GameState::new (game/state.rs:136-145).
+ * width_bits = 64 or 128 selects BitfieldBoardState<u64|u128>. */
+int tafl_state_from_fen(const char* fen, int width_bits, int side_to_play, tafl_state* out);
+/* BoardState::to_fen (board/state.rs:271-295); buf must hold >= 256 bytes. */
+int tafl_state_to_fen(const tafl_state* st, int width_bits, char* buf, size_t buf_len);
+/* Play::from_tiles (play.rs:36-49) / Play::to (play.rs:59-62) */
+int tafl_play_from_tiles(uint8_t from_row, uint8_t from_col, uint8_t to_row, uint8_t to_col,
+                         tafl_play* out);
+/* Play: FromStr / Display (play.rs:70-92, tiles.rs:131-157), e.g. "d6-f6" */
+int tafl_play_from_str(const char* s, tafl_play* out);
+int tafl_play_to_str(const tafl_play* p, char* buf, size_t buf_len);
+/* compact move <-> Play for a given bitfield width */
+int tafl_move_to_play(tafl_move m, int width_bits, tafl_play* out);
+
+const char* tafl_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Engine: `GameLogic` (logic.rs:61-72) + n_games resident `GameState`s on one GPU
+ * ---------------------------------------------------------------------------------------- */
+typedef struct tafl_engine tafl_engine;
+
+/* Game::new(rules, starting_board) (game/mod.rs:86-91) x n_games, on CUDA device `device`.
+ * width_bits: 64 | 128 | 0 (= smallest that fits the FEN's side length). */
+int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width_bits,
+                       uint32_t n_games, int device, tafl_engine** out);
+int tafl_engine_destroy(tafl_engine* e);
+const char* tafl_last_error(const tafl_engine* e);   /* e may be NULL: last create() error */
+int tafl_engine_info(const tafl_engine* e, uint32_t* n_games, int* width_bits, int* side_len,
+                     int* device, int* sm_count);
+/* cudaStream_t of the engine (for callers that want to order their own work / events) */
+void* tafl_engine_stream(const tafl_engine* e);
+int tafl_engine_sync(tafl_engine* e);
+
+/* reset games to the start position (ids == NULL: all games) */
+int tafl_reset(tafl_engine* e, const uint32_t* h_game_ids, uint32_t n);
+/* copy resident states in/out (reference layout) */
+int tafl_set_states(tafl_engine* e, const tafl_state* h_states, uint32_t first, uint32_t n);
+int tafl_get_states(tafl_engine* e, tafl_state* h_states, uint32_t first, uint32_t n);
+/* device pointer to the resident [n_games] tafl_state array */
+tafl_state* tafl_states_device(tafl_engine* e);
+
+/* get_all_possible_moves (game/main.rs:33-43): every legal play of the side to move of every
+ * resident game, canonical order = pieces ascending bit index x (V+,V-,H+,H-) x distance
+ * ascending (play.rs:157,166-183,189-225).  d_moves is [n_games][TAFL_MAX_MOVES] tafl_move,
+ * d_counts [n_games]; both DEVICE buffers (NULL = engine-owned, see tafl_moves_device). */
+int tafl_legal_moves(tafl_engine* e, tafl_move* d_moves, uint32_t* d_counts);
+int tafl_moves_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_counts);
+/* same, results copied to HOST buffers */
+int tafl_legal_moves_host(tafl_engine* e, tafl_move* h_moves, uint32_t* h_counts,
+                          uint32_t first, uint32_t n);
+
+/* Game::do_play (game/mod.rs:95-101) for every resident game: one tafl_play per game (HOST).
+ * h_effects[i].err != 0 leaves game i unchanged (logic.rs:827-834). h_effects may be NULL. */
+int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_effects);
+/* do_valid_play (logic.rs:782-820) on DEVICE-resident compact moves, no validation, no copy. */
+int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_status);
+
+/* Random playouts (BASELINE.json configs 1-2): n_steps lockstep plies for every
+ * resident game, move index = mulhi64(splitmix64(seed ^ game_id*0x9E3779B97F4A7C15 ^
+ * ply*0xBF58476D1CE4E5B9), n_legal) into the canonical list; `ply` is the engine-wide step
+ * counter (tafl_random_ply) and game_id = first_game_id + resident index.  With auto_reset a
+ * game that is Over at the start of a step is first reset to the start position.  Games that
+ * are Over (and not reset) do not step.  steps_per_launch <= 0 picks the default (1 = state
+ * round-trips HBM every ply). */
+int tafl_step_random(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset,
+                     int steps_per_launch);
+int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset,
+                           int steps_per_launch);
+int tafl_set_game_id_base(tafl_engine* e, uint64_t first_game_id);
+int tafl_set_random_ply(tafl_engine* e, uint64_t ply);
+uint64_t tafl_random_ply(const tafl_engine* e);
+
+/* counters accumulated on device by tafl_step_random since the last tafl_stats_reset */
+typedef struct {
+    uint64_t steps;              /* do_play's applied                                   */
+    uint64_t legal_moves;        /* sum of legal-move counts over stepped positions     */
+    uint64_t captures;           /* pieces captured                                     */
+    uint64_t games_finished;     /* games that reached Over                             */
+    uint64_t finished_plies;     /* sum of GameState.turn over finished games           */
+    uint64_t win_reason[2][8];   /* [winner: 0 att, 1 def][WinReason]                   */
+    uint64_t draw_reason[2];     /* [DrawReason]                                        */
+    uint64_t state_checksum;     /* filled by tafl_stats_get: xor-fold of all states    */
+} tafl_stats;
+int tafl_stats_reset(tafl_engine* e);
+int tafl_stats_get(tafl_engine* e, tafl_stats* out);
+
+/* ------------------------------------------------------------------------------------------
+ * Functional (by-value) batch API: GameLogic methods on caller-supplied states (HOST buffers)
+ * ---------------------------------------------------------------------------------------- */
+
+/* GameLogic::validate_play (logic.rs:219-222): out_err[i] = PlayInvalid code or 0 */
+int tafl_validate_plays(tafl_engine* e, const tafl_state* h_states, const tafl_play* h_plays,
+                        uint32_t n, uint8_t* h_out_err);
+/* GameLogic::do_play (logic.rs:827-834): h_out_states[i] = new state (or the input state when
+ * the play is invalid), h_out_effects[i] = captures + outcome + err */
+int tafl_do_plays(tafl_engine* e, const tafl_state* h_states, const tafl_play* h_plays,
+                  uint32_t n, tafl_state* h_out_states, tafl_play_effects* h_out_effects);
+/* get_all_possible_moves (game/main.rs:33-43) for arbitrary states */
+int tafl_legal_moves_of(tafl_engine* e, const tafl_state* h_states, uint32_t n,
+                        tafl_move* h_moves /* [n][TAFL_MAX_MOVES] */, uint32_t* h_counts);
+/* GameLogic::iter_plays(tile) (logic.rs:850-856, play.rs:139-226): plays of the piece on one
+ * tile (either side); h_counts[i] = -1 mirrors Err(BoardError::NoPiece) */
+int tafl_piece_plays(tafl_engine* e, const tafl_state* h_states, const uint8_t* h_tiles_rc,
+                     uint32_t n, tafl_move* h_moves /* [n][32] */, int32_t* h_counts);
+/* GameLogic::get_captures (logic.rs:604-699): the piece at play.from is moved on a copy of the
+ * board first, exactly as do_valid_play does (logic.rs:789-791) */
+int tafl_get_captures(tafl_engine* e, const tafl_state* h_states, const tafl_play* h_plays,
+                      uint32_t n, tafl_play_effects* h_out);
+/* GameLogic::detect_shieldwall (logic.rs:535-569) on the board AS GIVEN (no piece is moved);
+ * h_out[i].n_captures = 0xFF mirrors None */
+int tafl_detect_shieldwall(tafl_engine* e, const tafl_state* h_states, const tafl_play* h_plays,
+                           uint32_t n, tafl_play_effects* h_out);
+/* GameLogic::find_enclosure (logic.rs:309-401) */
+typedef struct {
+    uint8_t  row, col;
+    uint8_t  abort_on_edge, abort_on_corner;
+    uint16_t enclosed_pieces, enclosing_pieces;   /* PieceSet */
+    uint8_t  inside_safe, outside_safe;           /* used by tafl_enclosure_secure */
+    uint8_t  _pad[6];
+} tafl_enclosure_query;
+int tafl_find_enclosure(tafl_engine* e, const tafl_state* h_states,
+                        const tafl_enclosure_query* h_q, uint32_t n, tafl_enclosure* h_out);
+/* find_enclosure + GameLogic::enclosure_secure (logic.rs:408-463):
+ * h_out[i] = 0xFF if no enclosure, else 0/1 */
+int tafl_enclosure_secure(tafl_engine* e, const tafl_state* h_states,
+                          const tafl_enclosure_query* h_q, uint32_t n, uint8_t* h_out);
+/* GameLogic::detect_exit_fort (logic.rs:572-601) */
+int tafl_detect_exit_fort(tafl_engine* e, const tafl_state* h_states, uint32_t n,
+                          uint8_t* h_out);
+/* GameLogic::side_can_play (logic.rs:837-846) */
+int tafl_side_can_play(tafl_engine* e, const tafl_state* h_states, const uint8_t* h_sides,
+                       uint32_t n, uint8_t* h_out);
+
+/* ------------------------------------------------------------------------------------------
+ * MCTS: `class MCTS` (src/mcts.py:11-136) with the stub evaluator (uniform priors over the
+ * legal moves, value 0), one search tree per resident game, f64 PUCT, first-max tie-break.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct {
+    uint32_t num_sims;          /* args.numMCTSSims (mcts.py:37)                          */
+    double   cpuct;             /* args.cpuct (mcts.py:112)                               */
+    double   draw_value;        /* getGameEnded value of a draw (non-zero; 1e-4 default)  */
+    uint32_t edge_capacity;     /* per-tree edge pool, 0 = default (num_sims+1)*160       */
+    uint32_t _pad;
+} tafl_mcts_config;
+
+/* allocate node/edge pools for every resident game (idempotent for an equal config) */
+int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg);
+/* MCTS.getActionProb (mcts.py:28-53) for every resident game from a FRESH tree rooted at the
+ * game's current state: runs cfg.num_sims x MCTS.search (mcts.py:55-136).  Outputs are DEVICE
+ * buffers owned by the engine (tafl_mcts_results_device), layout [n_games][TAFL_MAX_MOVES]:
+ * root moves (canonical order), visit counts Nsa, Q values Qsa; d_counts = number of root
+ * edges; d_best = index of the first-max visit count (temp = 0 without the random tie choice). */
+int tafl_mcts_search(tafl_engine* e);
+int tafl_mcts_search_async(tafl_engine* e);
+int tafl_mcts_results_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_visits,
+                             double** d_q, uint32_t** d_counts, uint32_t** d_best);
+int tafl_mcts_results_host(tafl_engine* e, uint32_t first, uint32_t n, tafl_move* h_moves,
+                           uint32_t* h_visits, double* h_q, uint32_t* h_counts,
+                           uint32_t* h_best);
+/* play the chosen move (d_best) in every resident game that is Ongoing: do_valid_play */
+int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status /* may be NULL */);
+/* totals since configure: simulations run, nodes expanded, sum of path depths, sum of edges */
+typedef struct {
+    uint64_t sims, nodes, depth_sum, edges, terminal_hits, max_edges_used;
+} tafl_mcts_stats;
+int tafl_mcts_stats_get(tafl_engine* e, tafl_mcts_stats* out);
+
+/* ------------------------------------------------------------------------------------------
+ * Self-play records (replay-buffer rows; nearest upstream analogue: write_to_file,
+ * game/main.rs:86-132, with board_to_matrix :55-83 as the position encoding)
+ * ---------------------------------------------------------------------------------------- */
+typedef struct {
+    uint64_t game_id;
+    uint32_t ply;
+    uint16_t n_moves;
+    uint8_t  side_to_play;      /* TAFL_ATTACKER | TAFL_DEFENDER */
+    uint8_t  status;            /* status AFTER the chosen move   */
+    uint64_t att[2], def[2];    /* position the search was run on */
+    uint16_t best;              /* index of the move played       */
+    uint16_t _pad[3];
+} tafl_record_header;           /* 56 bytes */
+/* pack one record per resident game into a DEVICE buffer:
+ * header + moves[TAFL_REC_MOVES] u16 + visits[TAFL_REC_MOVES] u32, fixed stride */
+#define TAFL_REC_MOVES 256
+#define TAFL_REC_STRIDE (56 + 2 * TAFL_REC_MOVES + 4 * TAFL_REC_MOVES)
+int tafl_pack_records(tafl_engine* e, void* d_out /* [n_games][TAFL_REC_STRIDE] */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TAFL_B200_H */
