@@ -1,0 +1,641 @@
+// tafl_core.cuh — the rules engine as branch-light bitboard code, one game per thread.
+//
+// Everything here is __host__ __device__: the CUDA kernels (tafl_kernels.cu) inline it, and
+// tests/hostsim compiles the very same functions with g++ so the kernel math can be checked
+// against the CPU oracle on millions of positions without a GPU.  (The host build is a test
+// harness only; the product library has no CPU path.)
+//
+// Reference behaviour reproduced (paths relative to the reference tree, `game/`):
+//   board/state.rs   bit layout, king nibbles, get/set/move/clear, count_pieces
+//   game/logic.rs    validate_play_for_side, hostility, get_captures, detect_shieldwall,
+//                    find_enclosure, enclosure_secure, detect_exit_fort, get_game_outcome,
+//                    do_valid_play, side_can_play
+//   play.rs          ValidPlayIterator (ray order V+,V-,H+,H-, distance ascending)
+//   game/state.rs    RepetitionTracker
+//   game/main.rs     get_all_possible_moves (canonical move order)
+#pragma once
+#include "../../include/tafl.h"
+#include "tafl_bb.cuh"
+
+namespace tafl {
+
+enum { KIND_AS = 0, KIND_DS = 1, KIND_K = 2, KIND_NONE = 3 };
+enum { DIR_VP = 0, DIR_VM = 1, DIR_HP = 2, DIR_HM = 3 };  // play.rs:157,166-183
+
+// ---------------------------------------------------------------------------------------------
+// Ctx: `GameLogic` (logic.rs:61-72) = rules + board geometry, pre-digested into masks on the
+// host (tafl_ctx.hpp) and handed to every kernel as a __grid_constant__ parameter.
+// ---------------------------------------------------------------------------------------------
+template <class BB>
+struct Ctx {
+    BB board;        // every in-bounds tile
+    BB edge;         // geometry.rs:111-116
+    BB corners;      // geometry.rs:13-24
+    BB throne;       // centre tile
+    BB throne_adj;   // in-bounds neighbours of the throne
+    BB not_col0, not_colL;   // board minus first / last column (guards for +-1 shifts)
+    BB row0, rowL, col0, colL;
+    BB sh[3];          // special_tile_hostile (logic.rs:76-82), in-bounds part, per victim kind
+    BB dest_block[3];  // tiles a piece of this kind can never stop on / occupy
+                       //   (logic.rs:190-193,201-206 == coords_occupiable logic.rs:250-266)
+    int32_t N, mid;
+    uint8_t edge_hostile[3];   // hostility.edge contains kind
+    uint8_t pass_block[3];     // ray may not continue past the throne (NoPass / KingPass&&!king)
+    uint8_t noentry[3];        // may not stop on the throne but passes it (NoEntry / KingEntry&&!king)
+    uint8_t may_corner[3];
+    uint8_t slow[3];
+    uint8_t sw_caps[3];        // shieldwall.captures contains kind
+    uint8_t king_hostile;      // king_attack in {Armed, Anvil}   (logic.rs:89-93)
+    uint8_t king_captures;     // king_attack in {Armed, Hammer}  (logic.rs:609-611)
+    uint8_t sbt_special;       // StrongByThrone && throne rule in {NoEntry, KingEntry} (logic.rs:621-625)
+    uint8_t _pad[5];
+    tafl_rules rules;
+};
+
+template <class BB>
+struct Pos {
+    BB att, def;   // occupancy without the king nibbles
+    int kr, kc;    // raw king nibbles (board/state.rs:127-131); survive the king's capture
+    BB kbit;       // bit of the nibble tile when it is in bounds (else empty) — NOT occupancy
+    TAFL_HD BB occ() const { return att | def; }
+    TAFL_HD BB king() const { return def & kbit; }     // get_piece == King (board/state.rs:173-180)
+    TAFL_HD BB dsold() const { return def & ~kbit; }
+    TAFL_HD BB kind(int k) const { return k == KIND_AS ? att : (k == KIND_DS ? dsold() : king()); }
+    TAFL_HD BB side(int def_side) const { return def_side ? def : att; }
+};
+
+template <class BB> TAFL_HD int idx_of(int r, int c) { return r * BB::STRIDE + c; }
+
+template <class BB>
+TAFL_HD BB king_bit(const Ctx<BB>& cx, int kr, int kc) {
+    return (kr < cx.N && kc < cx.N) ? BB::bit(idx_of<BB>(kr, kc)) : BB::zero();
+}
+
+template <class BB> struct Nib;
+template <> struct Nib<BB64> {
+    TAFL_HD static void load(const tafl_state& s, Pos<BB64>& p) {
+        p.att = BB64{s.att[0] & 0x0FFFFFFFFFFFFFFFull};
+        p.def = BB64{s.def[0] & 0x0FFFFFFFFFFFFFFFull};
+        p.kr = (int)(s.def[0] >> 60);
+        p.kc = (int)(s.att[0] >> 60);
+    }
+    TAFL_HD static void store(const Pos<BB64>& p, tafl_state& s) {
+        s.att[0] = p.att.v | ((uint64_t)p.kc << 60);
+        s.def[0] = p.def.v | ((uint64_t)p.kr << 60);
+        s.att[1] = 0;
+        s.def[1] = 0;
+    }
+    // raw get_piece bits incl. nibble region (validate_play probes `from` before the bounds check)
+    TAFL_HD static bool raw_att(const tafl_state& s, int i) { return i < 64 && ((s.att[0] >> i) & 1); }
+    TAFL_HD static bool raw_def(const tafl_state& s, int i) { return i < 64 && ((s.def[0] >> i) & 1); }
+};
+template <> struct Nib<BB128> {
+    TAFL_HD static void load(const tafl_state& s, Pos<BB128>& p) {
+        p.att = BB128{s.att[0], s.att[1] & 0x0FFFFFFFFFFFFFFFull};
+        p.def = BB128{s.def[0], s.def[1] & 0x0FFFFFFFFFFFFFFFull};
+        p.kr = (int)(s.def[1] >> 60);
+        p.kc = (int)(s.att[1] >> 60);
+    }
+    TAFL_HD static void store(const Pos<BB128>& p, tafl_state& s) {
+        s.att[0] = p.att.lo;
+        s.att[1] = p.att.hi | ((uint64_t)p.kc << 60);
+        s.def[0] = p.def.lo;
+        s.def[1] = p.def.hi | ((uint64_t)p.kr << 60);
+    }
+    TAFL_HD static bool raw_att(const tafl_state& s, int i) {
+        return i < 128 && (((i < 64 ? s.att[0] >> i : s.att[1] >> (i - 64))) & 1);
+    }
+    TAFL_HD static bool raw_def(const tafl_state& s, int i) {
+        return i < 128 && (((i < 64 ? s.def[0] >> i : s.def[1] >> (i - 64))) & 1);
+    }
+};
+
+template <class BB>
+TAFL_HD Pos<BB> load_pos(const Ctx<BB>& cx, const tafl_state& s) {
+    Pos<BB> p;
+    Nib<BB>::load(s, p);
+    p.kbit = king_bit(cx, p.kr, p.kc);
+    return p;
+}
+template <class BB>
+TAFL_HD void store_pos(const Pos<BB>& p, tafl_state& s) { Nib<BB>::store(p, s); }
+
+// one-tile steps of a tile set, results clipped to the board
+template <class BB> TAFL_HD BB step_up(const Ctx<BB>&, BB x) { return x.template shr<BB::STRIDE>(); }              // row-1
+template <class BB> TAFL_HD BB step_down(const Ctx<BB>& cx, BB x) { return x.template shl<BB::STRIDE>() & cx.board; }  // row+1
+template <class BB> TAFL_HD BB step_left(const Ctx<BB>& cx, BB x) { return x.template shr<1>() & cx.not_colL; }     // col-1
+template <class BB> TAFL_HD BB step_right(const Ctx<BB>& cx, BB x) { return x.template shl<1>() & cx.not_col0; }    // col+1
+template <class BB> TAFL_HD BB dilate4(const Ctx<BB>& cx, BB x) {
+    return step_up(cx, x) | step_down(cx, x) | step_left(cx, x) | step_right(cx, x);
+}
+template <class BB> TAFL_HD BB step_dir(const Ctx<BB>& cx, BB x, int dir) {
+    switch (dir) {
+        case DIR_VP: return step_down(cx, x);
+        case DIR_VM: return step_up(cx, x);
+        case DIR_HP: return step_right(cx, x);
+        default: return step_left(cx, x);
+    }
+}
+
+// kind of the piece on tile bit `b` (board/state.rs:173-187)
+template <class BB>
+TAFL_HD int kind_at(const Pos<BB>& p, BB b) {
+    if ((p.def & b).any()) return (b == p.kbit) ? KIND_K : KIND_DS;
+    if ((p.att & b).any()) return KIND_AS;
+    return KIND_NONE;
+}
+
+// tile_hostile (logic.rs:85-99) as a tile set, for a victim of kind vk
+template <class BB>
+TAFL_HD BB hostile_set(const Ctx<BB>& cx, const Pos<BB>& p, int vk) {
+    BB empty = cx.board & ~p.occ();
+    BB pieces = (vk == KIND_AS) ? (cx.king_hostile ? p.def : p.dsold()) : p.att;
+    return pieces | (empty & cx.sh[vk]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Rays of one piece, in "line space" (bit i of a line word = i-th tile of the row / column).
+// ---------------------------------------------------------------------------------------------
+template <class BB>
+TAFL_HD uint32_t extract_row(const Ctx<BB>& cx, BB x, int row) {
+    return x.extract32(row * BB::STRIDE) & ((1u << cx.N) - 1u);
+}
+template <class BB>
+TAFL_HD uint32_t extract_col(const Ctx<BB>& cx, BB x, int col) {
+    BB t = x.shrv(col);
+    uint32_t out = 0;
+#pragma unroll
+    for (int i = 0; i < 11; ++i) {
+        if (i < cx.N) out |= (uint32_t)t.test(i * BB::STRIDE) << i;
+    }
+    return out;
+}
+
+struct Rays {
+    uint32_t m[4];  // destination positions along the line per direction (DIR_*), bit = row (V) / col (H)
+    int cnt[4];
+};
+
+// ValidPlayIterator (play.rs:189-225) + validate_play_for_side (logic.rs:159-214) for the piece
+// of kind `k` on (row, col): the set of tiles it may move to, per direction.
+template <class BB>
+TAFL_HD Rays piece_rays(const Ctx<BB>& cx, BB occ, int k, int row, int col) {
+    Rays r;
+    const int N = cx.N, mid = cx.mid;
+    const uint32_t full = (1u << N) - 1u;
+#pragma unroll
+    for (int ax = 0; ax < 2; ++ax) {
+        // ax 0: vertical (line = column `col`, position = row); ax 1: horizontal
+        const int line = ax == 0 ? col : row, p = ax == 0 ? row : col;
+        uint32_t lw = ax == 0 ? extract_col(cx, occ, col) : extract_row(cx, occ, row);
+        // plus direction: free run above p
+        uint32_t x = (lw >> (p + 1)) | (1u << (N - 1 - p));
+        int lenp = ctz32(x);
+        uint32_t mp = (((1u << lenp) - 1u) << (p + 1)) & full;
+        // minus direction
+        uint32_t y = lw & ((1u << p) - 1u);
+        int top = 32 - clz32(y);
+        uint32_t mm = ((1u << p) - 1u) & ~((1u << top) - 1u);
+        const bool has_throne = (line == mid);
+        if (has_throne && cx.pass_block[k]) {  // logic.rs:194-200: may reach, not cross, the throne
+            if (p < mid) mp &= (2u << mid) - 1u;
+            if (p > mid) mm &= ~((1u << mid) - 1u);
+        }
+        uint32_t blocked = 0;
+        if (has_throne && cx.noentry[k]) blocked |= 1u << mid;                                   // logic.rs:201-206
+        if ((line == 0 || line == N - 1) && !cx.may_corner[k]) blocked |= 1u | (1u << (N - 1));   // logic.rs:190-193
+        mp &= ~blocked;
+        mm &= ~blocked;
+        if (cx.slow[k]) {  // logic.rs:207-210 (a skipped throne does not extend a slow piece's reach)
+            mp &= 1u << (p + 1);
+            mm &= (p > 0) ? (1u << (p - 1)) : 0u;
+        }
+        r.m[ax * 2 + 0] = mp;
+        r.m[ax * 2 + 1] = mm;
+        r.cnt[ax * 2 + 0] = popc32(mp);
+        r.cnt[ax * 2 + 1] = popc32(mm);
+    }
+    return r;
+}
+
+// j-th destination (distance ascending) of direction `dir` -> position along the line
+TAFL_HD int ray_nth(uint32_t m, int dir, int j) {
+    if ((dir & 1) == 0) {  // plus: ascending bit order
+        for (int i = 0; i < j; ++i) m &= m - 1;
+        return ctz32(m);
+    }
+    for (int i = 0; i < j; ++i) m &= ~(0x80000000u >> clz32(m));
+    return 31 - clz32(m);
+}
+
+// Full legal-move list of the side to move, canonical order (game/main.rs:33-43).
+// Simple per-piece generator; the kernels use it for list materialisation.
+template <class BB>
+TAFL_HD int gen_moves_side(const Ctx<BB>& cx, const Pos<BB>& p, int def_side, tafl_move* out, int cap) {
+    BB own = p.side(def_side);
+    BB occ = p.occ();
+    int n = 0;
+    while (own.any()) {
+        int s = own.ctz();
+        own = own & ~BB::bit(s);
+        int row = s / BB::STRIDE, col = s - row * BB::STRIDE;
+        int k = def_side ? ((BB::bit(s) == p.kbit) ? KIND_K : KIND_DS) : KIND_AS;
+        Rays r = piece_rays(cx, occ, k, row, col);
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            uint32_t m = r.m[d];
+            while (m) {
+                int pos;
+                if ((d & 1) == 0) { pos = ctz32(m); m &= m - 1; }
+                else { pos = 31 - clz32(m); m &= ~(1u << pos); }
+                int to = (d < 2) ? idx_of<BB>(pos, col) : idx_of<BB>(row, pos);
+                if (n < cap) out[n] = (tafl_move)(s | (to << 7));
+                ++n;
+            }
+        }
+    }
+    return n;
+}
+template <class BB>
+TAFL_HD int gen_moves(const Ctx<BB>& cx, const tafl_state& st, tafl_move* out, int cap) {
+    if (st.status != TAFL_STATUS_ONGOING) return 0;  // logic.rs:165-167
+    Pos<BB> p = load_pos(cx, st);
+    return gen_moves_side(cx, p, (st.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, out, cap);
+}
+
+// side_can_play (logic.rs:837-846): does any piece of the side have a legal play?
+template <class BB>
+TAFL_HD bool side_can_play(const Ctx<BB>& cx, const Pos<BB>& p, int def_side) {
+    BB empty = cx.board & ~p.occ();
+    bool any = false;
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk) {
+        int k = def_side ? (kk == 0 ? KIND_DS : KIND_K) : KIND_AS;
+        if (!def_side && kk == 1) break;
+        BB src = p.kind(k);
+        BB ok = ~cx.dest_block[k];
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            BB s1 = step_dir(cx, src, d) & empty;
+            any |= (s1 & ok).any();
+            if (cx.noentry[k] && !cx.slow[k]) {  // hop over the empty throne (play.rs:208-211)
+                BB s2 = step_dir(cx, s1 & cx.throne, d) & empty & ok;
+                any |= s2.any();
+            }
+        }
+    }
+    return any;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Captures
+// ---------------------------------------------------------------------------------------------
+// detect_shieldwall (logic.rs:535-569) + dir_sw_search (logic.rs:471-530).
+// `mover_def` is state.side_to_play.  Returns true for Some(..) and the captured tiles in *caps.
+template <class BB>
+TAFL_HD bool detect_shieldwall(const Ctx<BB>& cx, const Pos<BB>& p, int mover_def, int to_r, int to_c, BB* caps) {
+    *caps = BB::zero();
+    if (!cx.rules.shieldwall_enabled) return false;
+    const int N = cx.N;
+    if (to_r < 0 || to_c < 0 || to_r >= N || to_c >= N) return false;
+    int horizontal, away;  // away: +1 / -1 along the other axis
+    if (to_r == 0) { horizontal = 1; away = 1; }
+    else if (to_r == N - 1) { horizontal = 1; away = -1; }
+    else if (to_c == 0) { horizontal = 0; away = 1; }
+    else if (to_c == N - 1) { horizontal = 0; away = -1; }
+    else return false;
+    const BB own = p.side(mover_def), opp = p.side(!mover_def), occ = p.occ();
+    const bool cmc = cx.rules.sw_corners_may_close != 0;
+    BB wall = BB::zero();
+    bool found = false;
+    for (int dd = 0; dd < 2 && !found; ++dd) {
+        const int dir = dd == 0 ? -1 : 1;
+        wall = BB::zero();
+        int cnt = 0, r = to_r, c = to_c;
+        for (int it = 0; it < 12; ++it) {
+            if (horizontal) c += dir; else r += dir;
+            if (r < 0 || c < 0 || r >= N || c >= N) break;  // ran off the board: None
+            BB tb = BB::bit(idx_of<BB>(r, c));
+            bool is_occ = (occ & tb).any(), is_corner = (cx.corners & tb).any();
+            if (!(is_occ || (cmc && is_corner))) break;
+            if (!is_occ) { found = cnt >= 2; break; }  // empty closing corner
+            if ((opp & tb).any()) {
+                int pr = horizontal ? r + away : r, pc = horizontal ? c : c + away;
+                BB pin = BB::bit(idx_of<BB>(pr, pc));
+                if ((own & pin).any()) { wall = wall | tb; ++cnt; }
+                else break;  // not pinned by a piece of the mover
+            }
+            if ((own & tb).any() || (is_corner && cmc)) { found = cnt >= 2; break; }
+        }
+    }
+    if (!found) return false;
+    BB keep = BB::zero();
+    const int osk = mover_def ? KIND_AS : KIND_DS;
+    if (cx.sw_caps[osk]) keep = keep | ~p.kbit;
+    if (cx.sw_caps[KIND_K]) keep = keep | p.kbit;
+    *caps = wall & keep;
+    return true;
+}
+
+// get_captures (logic.rs:604-699) on the post-move board.  piece_def / piece_kind describe the
+// moving piece, mover_def is state.side_to_play (used by shield wall and Linnaean capture).
+template <class BB>
+TAFL_HD BB get_captures(const Ctx<BB>& cx, const Pos<BB>& p, int piece_def, int piece_kind, int mover_def,
+                        int to_r, int to_c) {
+    BB caps = BB::zero();
+    const int N = cx.N;
+    const bool to_in = to_r >= 0 && to_c >= 0 && to_r < N && to_c < N;
+    if (to_in && (piece_kind != KIND_K || cx.king_captures)) {
+        const BB tob = BB::bit(idx_of<BB>(to_r, to_c));
+        const BB opp = p.side(!piece_def);
+        const BB kingb = p.king();
+        // king strength (logic.rs:225-245), from the nibble tile
+        const bool beside = (p.kbit & cx.throne_adj).any();
+        const bool strong = cx.rules.king_strength == TAFL_KING_STRONG ||
+                            (cx.rules.king_strength == TAFL_KING_STRONG_BY_THRONE &&
+                             (beside || (p.kbit & cx.throne).any()));
+        const BB hostK = hostile_set(cx, p, KIND_K);
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            BB n = step_dir(cx, tob, d);
+            if (!(n & opp).any()) continue;
+            const bool vking = (n & kingb).any();
+            const int vk = vking ? KIND_K : (piece_def ? KIND_AS : KIND_DS);
+            if (vking && beside && cx.sbt_special) {  // logic.rs:621-632
+                BB nb = dilate4(cx, n);
+                if (!(nb & ~cx.throne & ~hostK).any()) { caps = caps | n; continue; }
+            }
+            BB far = step_dir(cx, n, d);
+            const BB host = vking ? hostK : hostile_set(cx, p, vk);
+            const bool far_h = far.any() ? (far & host).any() : (cx.edge_hostile[vk] != 0);  // logic.rs:103-114
+            if (far_h) {
+                if (vking && strong) {  // logic.rs:647-674
+                    BB q1 = step_dir(cx, n, d < 2 ? DIR_HP : DIR_VP), q2 = step_dir(cx, n, d < 2 ? DIR_HM : DIR_VM);
+                    bool h1 = q1.any() ? (q1 & host).any() : (cx.edge_hostile[KIND_K] != 0);
+                    bool h2 = q2.any() ? (q2 & host).any() : (cx.edge_hostile[KIND_K] != 0);
+                    if (!(h1 && h2)) continue;
+                }
+                caps = caps | n;
+            } else if (cx.rules.linnaean_capture && !mover_def) {  // logic.rs:676-685, 859-879
+                if (far.any() && far == cx.throne && p.kbit == cx.throne &&
+                    (cx.throne_adj & hostK).popc() == 3)
+                    caps = caps | n;
+            }
+        }
+    }
+    BB walled;
+    if (detect_shieldwall(cx, p, mover_def, to_r, to_c, &walled)) caps = caps | walled;  // logic.rs:691-696
+    return caps;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Enclosures
+// ---------------------------------------------------------------------------------------------
+template <class BB>
+struct Encl {
+    BB region;    // occupied | unoccupied (logic.rs:25-38)
+    BB boundary;
+    bool found;
+};
+TAFL_HD bool pieceset_has(uint16_t set, int kind) {
+    uint16_t m = kind == KIND_AS ? TAFL_PIECESET_PIECE(TAFL_SOLDIER, TAFL_ATTACKER)
+               : kind == KIND_DS ? TAFL_PIECESET_PIECE(TAFL_SOLDIER, TAFL_DEFENDER)
+                                 : TAFL_PIECESET_PIECE(TAFL_KING, TAFL_DEFENDER);
+    return (set & m) != 0;
+}
+template <class BB>
+TAFL_HD BB pieceset_bb(const Pos<BB>& p, uint16_t set) {
+    BB r = BB::zero();
+    if (pieceset_has(set, KIND_AS)) r = r | p.att;
+    if (pieceset_has(set, KIND_DS)) r = r | p.dsold();
+    if (pieceset_has(set, KIND_K)) r = r | p.king();
+    return r;
+}
+// find_enclosure (logic.rs:309-401).  The reference's span fill visits exactly the 4-connected
+// component of fillable tiles (empty or `enclosed` pieces) around the start and probes exactly
+// that component's 4-neighbourhood, so the result is computed by mask dilation.
+template <class BB>
+TAFL_HD Encl<BB> find_enclosure(const Ctx<BB>& cx, const Pos<BB>& p, int r, int c, BB enclosed, BB enclosing,
+                                bool abort_on_edge, bool abort_on_corner) {
+    Encl<BB> e;
+    e.region = BB::zero();
+    e.boundary = BB::zero();
+    e.found = false;
+    if (r < 0 || c < 0 || r >= cx.N || c >= cx.N) return e;
+    const BB occ = p.occ();
+    const BB fillable = (cx.board & ~occ) | enclosed;
+    const BB neither = occ & ~enclosed & ~enclosing;
+    const BB stop = (abort_on_edge ? cx.edge : BB::zero()) | (abort_on_corner ? cx.corners : BB::zero());
+    BB reg = BB::bit(idx_of<BB>(r, c)) & fillable;
+    if (!reg.any()) return e;
+    for (int it = 0; it < 128; ++it) {
+        if ((reg & stop).any()) return e;
+        BB grown = reg | (dilate4(cx, reg) & fillable);
+        if (grown == reg) break;
+        reg = grown;
+    }
+    if ((reg & stop).any()) return e;
+    BB nb = dilate4(cx, reg) & ~reg;
+    if ((nb & neither).any()) return e;
+    e.region = reg;
+    e.boundary = nb & enclosing;
+    e.found = true;
+    return e;
+}
+// enclosure_secure (logic.rs:408-463)
+template <class BB>
+TAFL_HD bool enclosure_secure(const Ctx<BB>& cx, const Pos<BB>& p, const Encl<BB>& e, bool inside_safe,
+                              bool outside_safe) {
+    if (inside_safe && outside_safe) return true;
+    const BB occ = p.occ();
+    const BB empty = cx.board & ~occ;
+    const BB safe_zone = (inside_safe ? e.region : BB::zero()) | (outside_safe ? (cx.board & ~e.region) : BB::zero());
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        BB bk = e.boundary & p.kind(k);
+        if (!bk.any()) continue;
+        const int ek = (k == KIND_AS) ? KIND_DS : KIND_AS;  // hostile soldier (logic.rs:426)
+        const BB hostile = hostile_set(cx, p, k);
+        const BB prot = (safe_zone & ~cx.sh[k]) | (cx.board & ~hostile & (occ | cx.dest_block[ek]));
+        const bool oob_ok = !cx.edge_hostile[k];
+        // value of `prot` at the four neighbours, aligned to the boundary tile
+        BB up = prot.template shl<BB::STRIDE>() | (oob_ok ? cx.row0 : BB::zero());           // neighbour row-1
+        BB down = prot.template shr<BB::STRIDE>() | (oob_ok ? cx.rowL : BB::zero());         // neighbour row+1
+        BB left = (prot.template shl<1>() & cx.not_col0) | (oob_ok ? cx.col0 : BB::zero());  // neighbour col-1
+        BB right = (prot.template shr<1>() & cx.not_colL) | (oob_ok ? cx.colL : BB::zero()); // neighbour col+1
+        (void)empty;
+        if ((bk & ~((up | down) & (left | right))).any()) ok = false;
+    }
+    return ok;
+}
+// detect_exit_fort (logic.rs:572-601)
+template <class BB>
+TAFL_HD bool detect_exit_fort(const Ctx<BB>& cx, const Pos<BB>& p) {
+    const int N = cx.N;
+    if (!(p.kr == 0 || p.kr == N - 1 || p.kc == 0 || p.kc == N - 1)) return false;
+    if (!p.kbit.any()) return false;
+    // enclosed = PieceSet::from(King), enclosing = PieceSet::from(Defender); attackers are "neither"
+    Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.king(), p.dsold(), false, true);
+    if (!e.found) return false;
+    if (!(dilate4(cx, p.kbit) & ~p.occ()).any()) return false;
+    return enclosure_secure(cx, p, e, true, false);
+}
+
+// ---------------------------------------------------------------------------------------------
+// RepetitionTracker::track_play (game/state.rs:71-113) on the packed state
+// ---------------------------------------------------------------------------------------------
+TAFL_HD uint32_t pack_rec(int from_r, int from_c, int horizontal, int disp, int def_side, bool captures) {
+    uint32_t fl = TAFL_REC_SOME | (captures ? TAFL_REC_CAPTURES : 0u) | (def_side ? TAFL_REC_DEFENDER : 0u) |
+                  (horizontal ? TAFL_REC_HORIZONTAL : 0u);
+    return (uint32_t)(from_r & 0xFF) | ((uint32_t)(from_c & 0xFF) << 8) | ((uint32_t)(disp & 0xFF) << 16) | (fl << 24);
+}
+TAFL_HD void track_play(tafl_state& s, uint32_t rec, int def_side, bool captures) {
+    const uint32_t head = s.ring_head & 3u;
+    uint32_t first = s.recent[0];
+    first = head == 1 ? s.recent[1] : first;
+    first = head == 2 ? s.recent[2] : first;
+    first = head == 3 ? s.recent[3] : first;
+    const uint8_t mid_bit = def_side ? TAFL_FLAG_DEF_MID : TAFL_FLAG_ATT_MID;
+    uint8_t reps = def_side ? s.def_reps : s.att_reps;
+    if (!captures && first == rec) {
+        bool is_rep = !(s.flags & mid_bit);
+        s.flags ^= mid_bit;
+        if (is_rep && reps < 255) ++reps;
+    } else {
+        reps = 0;
+        s.flags &= (uint8_t)~mid_bit;
+    }
+    if (def_side) s.def_reps = reps; else s.att_reps = reps;
+    if (head == 0) s.recent[0] = rec;
+    if (head == 1) s.recent[1] = rec;
+    if (head == 2) s.recent[2] = rec;
+    if (head == 3) s.recent[3] = rec;
+    s.ring_head = (uint8_t)((head + 1u) & 3u);
+}
+
+// ---------------------------------------------------------------------------------------------
+// get_game_outcome (logic.rs:702-771) — returns the packed status (0 = still Ongoing)
+// ---------------------------------------------------------------------------------------------
+template <class BB>
+TAFL_HD uint8_t game_outcome(const Ctx<BB>& cx, const Pos<BB>& p, const tafl_state& s, int mover_def, int piece_kind,
+                             int to_r, int to_c, BB caps) {
+    if (!p.side(!mover_def).any()) return TAFL_STATUS_WIN(TAFL_WIN_ALL_CAPTURED, mover_def);
+    const int N = cx.N;
+    if (!mover_def) {
+        if ((caps & p.kbit).any()) return TAFL_STATUS_WIN(TAFL_WIN_KING_CAPTURED, 0);
+        if (cx.rules.enclosure_win != TAFL_ENCL_NONE) {
+            Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.def, p.att,
+                                        cx.rules.enclosure_win == TAFL_ENCL_WITHOUT_EDGE_ACCESS, true);
+            if (e.found && (e.region & p.occ()).popc() == p.def.popc() && enclosure_secure(cx, p, e, false, true))
+                return TAFL_STATUS_WIN(TAFL_WIN_ENCLOSED, 0);
+        }
+    } else {
+        if (piece_kind == KIND_K) {
+            const bool at_edge = to_r == 0 || to_r == N - 1 || to_c == 0 || to_c == N - 1;
+            const bool at_corner = (to_r == 0 || to_r == N - 1) && (to_c == 0 || to_c == N - 1);
+            if (cx.rules.edge_escape ? at_edge : at_corner) return TAFL_STATUS_WIN(TAFL_WIN_KING_ESCAPED, 1);
+        }
+        if (cx.rules.exit_fort && detect_exit_fort(cx, p)) return TAFL_STATUS_WIN(TAFL_WIN_EXIT_FORT, 1);
+    }
+    if (cx.rules.repetition_enabled) {
+        uint32_t reps = mover_def ? s.def_reps : s.att_reps;
+        if (reps >= cx.rules.n_repetitions)
+            return cx.rules.repetition_is_loss ? TAFL_STATUS_WIN(TAFL_WIN_REPETITION, !mover_def)
+                                               : TAFL_STATUS_DRAW(TAFL_DRAW_REPETITION);
+    }
+    if (!side_can_play(cx, p, !mover_def))
+        return cx.rules.draw_on_no_plays ? TAFL_STATUS_DRAW(TAFL_DRAW_NO_PLAYS)
+                                         : TAFL_STATUS_WIN(TAFL_WIN_NO_PLAYS, mover_def);
+    return TAFL_STATUS_ONGOING;
+}
+
+// ---------------------------------------------------------------------------------------------
+// do_valid_play (logic.rs:782-820).  (from, axis, disp) is the Play; the caller guarantees a
+// piece on `from` and an in-bounds destination.  Returns the captured tiles.
+// ---------------------------------------------------------------------------------------------
+template <class BB>
+TAFL_HD BB do_valid_play(const Ctx<BB>& cx, tafl_state& s, int from_r, int from_c, int horizontal, int disp) {
+    Pos<BB> p = load_pos(cx, s);
+    const int mover_def = (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
+    const int to_r = horizontal ? from_r : from_r + disp, to_c = horizontal ? from_c + disp : from_c;
+    const BB fb = BB::bit(idx_of<BB>(from_r, from_c)), tb = BB::bit(idx_of<BB>(to_r, to_c));
+    // move_piece (board/state.rs:218-223)
+    const int pk = kind_at(p, fb);
+    const int piece_def = pk != KIND_AS;
+    if (piece_def) { p.def = p.def | tb; p.att = p.att & ~tb; }
+    else { p.att = p.att | tb; p.def = p.def & ~tb; }
+    if (pk == KIND_K) { p.kr = to_r; p.kc = to_c; p.kbit = tb; }
+    p.att = p.att & ~fb;
+    p.def = p.def & ~fb;
+    const BB caps = get_captures(cx, p, piece_def, pk, mover_def, to_r, to_c);
+    p.att = p.att & ~caps;
+    p.def = p.def & ~caps;
+    const bool captured = caps.any();
+    track_play(s, pack_rec(from_r, from_c, horizontal, disp, mover_def, captured), mover_def, captured);
+    if (!captured) s.plays_since_capture += 1;
+    const uint8_t status = game_outcome(cx, p, s, mover_def, pk, to_r, to_c, caps);
+    s.turn += 1;
+    s.flags ^= TAFL_FLAG_DEF_TO_PLAY;
+    s.status = status;
+    store_pos(p, s);
+    return caps;
+}
+template <class BB>
+TAFL_HD BB do_valid_move(const Ctx<BB>& cx, tafl_state& s, tafl_move m) {
+    const int f = TAFL_MOVE_FROM(m), t = TAFL_MOVE_TO(m);
+    const int fr = f / BB::STRIDE, fc = f - fr * BB::STRIDE, tr = t / BB::STRIDE, tc = t - tr * BB::STRIDE;
+    const int horizontal = fr == tr;  // Play::from_tiles (play.rs:36-49)
+    return do_valid_play(cx, s, fr, fc, horizontal, horizontal ? tc - fc : tr - fr);
+}
+
+// validate_play_for_side (logic.rs:159-214)
+template <class BB>
+TAFL_HD int validate_play(const Ctx<BB>& cx, const tafl_state& s, const tafl_play& pl, int side_def) {
+    if (s.status != TAFL_STATUS_ONGOING) return TAFL_GAME_OVER;
+    const int N = cx.N;
+    const int fr = pl.from_row, fc = pl.from_col;
+    const int horizontal = pl.axis == TAFL_HORIZONTAL;
+    // Coords arithmetic in i8, destination cast to u8 (play.rs:59-67)
+    const int tr = horizontal ? fr : (int)(uint8_t)(int8_t)((int8_t)fr + pl.disp);
+    const int tc = horizontal ? (int)(uint8_t)(int8_t)((int8_t)fc + pl.disp) : fc;
+    const int fi = fr * BB::STRIDE + fc;
+    int pk;
+    {
+        Pos<BB> q = load_pos(cx, s);
+        if (Nib<BB>::raw_def(s, fi)) pk = (fr == q.kr && fc == q.kc) ? KIND_K : KIND_DS;
+        else if (Nib<BB>::raw_att(s, fi)) pk = KIND_AS;
+        else return TAFL_NO_PIECE;
+    }
+    if ((pk != KIND_AS) != (side_def != 0)) return TAFL_WRONG_PLAYER;
+    if (!(fr < N && fc < N && tr < N && tc < N)) return TAFL_OUT_OF_BOUNDS;
+    if (fr != tr && fc != tc) return TAFL_NO_COMMON_AXIS;
+    Pos<BB> p = load_pos(cx, s);
+    const BB occ = p.occ();
+    const BB tb = BB::bit(idx_of<BB>(tr, tc));
+    if ((occ & tb).any()) return TAFL_BLOCKED_BY_PIECE;
+    BB between = BB::zero();  // geometry.rs:85-108
+    if (fr == tr) { int lo = fc < tc ? fc : tc, hi = fc < tc ? tc : fc; for (int c = lo + 1; c < hi; ++c) between = between | BB::bit(idx_of<BB>(fr, c)); }
+    else { int lo = fr < tr ? fr : tr, hi = fr < tr ? tr : fr; for (int r = lo + 1; r < hi; ++r) between = between | BB::bit(idx_of<BB>(r, fc)); }
+    if ((between & occ).any()) return TAFL_BLOCKED_BY_PIECE;
+    if (!cx.may_corner[pk] && (cx.corners & tb).any()) return TAFL_MOVE_ONTO_BLOCKED_TILE;
+    if (cx.pass_block[pk] && (between & cx.throne).any()) return TAFL_MOVE_THROUGH_BLOCKED_TILE;
+    if (cx.noentry[pk] && tb == cx.throne) return TAFL_MOVE_ONTO_BLOCKED_TILE;
+    int dist = pl.disp < 0 ? -(int)pl.disp : (int)pl.disp;
+    if (cx.slow[pk] && dist > 1) return TAFL_TOO_FAR;
+    return TAFL_PLAY_OK;
+}
+
+// Counter-based RNG of the random-playout workload, identical to the oracle's.
+TAFL_HD uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+TAFL_HD uint32_t pick_index(uint64_t seed, uint64_t game_id, uint64_t ply, uint32_t n) {
+    uint64_t x = splitmix64(seed ^ (game_id * 0x9E3779B97F4A7C15ull) ^ (ply * 0xBF58476D1CE4E5B9ull));
+    return (uint32_t)mulhi64(x, (uint64_t)n);
+}
+
+}  // namespace tafl

@@ -1,0 +1,652 @@
+// tafl_engine.cu — engine handle, lockstep kernels (one game per thread) and the C ABI
+// (include/tafl.h) except the MCTS entry points (tafl_mcts.cu) and host text helpers
+// (tafl_host.cpp).  sm_100a only; no CPU path.
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "tafl_engine.hpp"
+#include "tafl_select.cuh"
+
+using namespace tafl;
+
+// ---------------------------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int STEP_BLOCK = 64;   // threads per CTA for the per-game kernels
+
+__global__ void k_fill_states(tafl_state* __restrict__ states, uint32_t n, const __grid_constant__ tafl_state start) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g < n) store_state(states + g, start);
+}
+__global__ void k_reset_ids(tafl_state* __restrict__ states, const uint32_t* __restrict__ ids, uint32_t n,
+                            uint32_t n_games, const __grid_constant__ tafl_state start) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && ids[i] < n_games) store_state(states + ids[i], start);
+}
+
+// get_all_possible_moves (game/main.rs:33-43), one game per thread
+template <class BB>
+__global__ void __launch_bounds__(STEP_BLOCK)
+k_legal_moves(const __grid_constant__ Ctx<BB> cx, const tafl_state* __restrict__ states, uint32_t n,
+              tafl_move* __restrict__ moves, uint32_t* __restrict__ counts) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    tafl_state s = load_state(states + g);
+    counts[g] = (uint32_t)gen_moves(cx, s, moves + (size_t)g * TAFL_MAX_MOVES, TAFL_MAX_MOVES);
+}
+
+// Game::do_play (game/mod.rs:95-101) with validation
+template <class BB>
+__global__ void __launch_bounds__(STEP_BLOCK)
+k_step_plays(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
+             const tafl_play* __restrict__ plays, tafl_play_effects* __restrict__ fx_out) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    tafl_state s = load_state(states + g);
+    const tafl_play pl = plays[g];
+    tafl_play_effects fx;
+    fx.captures[0] = fx.captures[1] = 0;
+    fx.n_captures = 0;
+    for (int i = 0; i < 5; ++i) fx._pad[i] = 0;
+    const int err = validate_play(cx, s, pl, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
+    fx.err = (uint8_t)err;
+    if (!err) {
+        BB caps = do_valid_play(cx, s, pl.from_row, pl.from_col, pl.axis == TAFL_HORIZONTAL, pl.disp);
+        put_bb(fx.captures, caps);
+        fx.n_captures = (uint8_t)caps.popc();
+        store_state(states + g, s);
+    }
+    fx.status = s.status;
+    if (fx_out) fx_out[g] = fx;
+}
+
+// do_valid_play (logic.rs:782-820) on one compact move per game
+template <class BB>
+__global__ void __launch_bounds__(STEP_BLOCK)
+k_step_moves(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
+             const tafl_move* __restrict__ mv, uint32_t mv_stride, const uint32_t* __restrict__ pick,
+             uint8_t* __restrict__ status_out) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    tafl_state s = load_state(states + g);
+    if (s.status == TAFL_STATUS_ONGOING) {
+        const tafl_move m = mv[(size_t)g * mv_stride + (pick ? pick[g] : 0u)];
+        do_valid_move(cx, s, m);
+        store_state(states + g, s);
+    }
+    if (status_out) status_out[g] = s.status;
+}
+
+// The fused random-playout step (K4): count -> pick -> select -> apply -> outcome, `steps`
+// plies per launch with the state held in registers in between.
+template <class BB>
+__global__ void __launch_bounds__(STEP_BLOCK)
+k_step_random(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
+              const __grid_constant__ tafl_state start, uint64_t seed, uint64_t gid_base, uint64_t ply0,
+              uint32_t steps, int auto_reset, DevStats* __restrict__ stats) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t c_steps = 0, c_legal = 0, c_caps = 0;
+    if (g < n) {
+        tafl_state s = load_state(states + g);
+        for (uint32_t i = 0; i < steps; ++i) {
+            StepEvt ev = random_step(cx, s, start, seed, gid_base + g, ply0 + i, auto_reset != 0);
+            c_steps += ev.stepped;
+            c_legal += ev.legal;
+            c_caps += ev.caps;
+            if (ev.status) {  // rare: a game ended
+                atomicAdd(&stats->finished, 1ull);
+                atomicAdd(&stats->plies, (unsigned long long)ev.turn);
+                if (TAFL_STATUS_IS_DRAW(ev.status)) atomicAdd(&stats->draw[TAFL_STATUS_REASON(ev.status) & 1], 1ull);
+                else atomicAdd(&stats->win[ev.status & 1][TAFL_STATUS_REASON(ev.status)], 1ull);
+            }
+        }
+        store_state(states + g, s);
+    }
+    // warp-level reduction of the dense counters, one atomic per warp
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        c_steps += __shfl_down_sync(0xFFFFFFFFu, c_steps, o);
+        c_legal += __shfl_down_sync(0xFFFFFFFFu, c_legal, o);
+        c_caps += __shfl_down_sync(0xFFFFFFFFu, c_caps, o);
+    }
+    if ((threadIdx.x & 31) == 0 && c_steps) {
+        atomicAdd(&stats->steps, (unsigned long long)c_steps);
+        atomicAdd(&stats->legal, (unsigned long long)c_legal);
+        atomicAdd(&stats->caps, (unsigned long long)c_caps);
+    }
+}
+
+__global__ void k_checksum(const tafl_state* __restrict__ states, uint32_t n, unsigned long long* out) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long acc = 0;
+    if (g < n) {
+        const unsigned long long* w = reinterpret_cast<const unsigned long long*>(states + g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc ^= splitmix64(w[j] ^ (((unsigned long long)g * 8ull + j) * 0x9E3779B97F4A7C15ull));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc ^= __shfl_down_sync(0xFFFFFFFFu, acc, o);
+    if ((threadIdx.x & 31) == 0) atomicXor(out, acc);
+}
+
+// ---- by-value batch kernels -------------------------------------------------------------------
+template <class BB>
+__global__ void k_bv_validate(const __grid_constant__ Ctx<BB> cx, const tafl_state* st, const tafl_play* pl, uint32_t n,
+                              uint8_t* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    tafl_state s = st[i];
+    out[i] = (uint8_t)validate_play(cx, s, pl[i], (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
+}
+template <class BB>
+__global__ void k_bv_do_plays(const __grid_constant__ Ctx<BB> cx, const tafl_state* st, const tafl_play* pl, uint32_t n,
+                              tafl_state* out_st, tafl_play_effects* out_fx) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    tafl_state s = st[i];
+    const tafl_play p = pl[i];
+    tafl_play_effects fx;
+    fx.captures[0] = fx.captures[1] = 0;
+    fx.n_captures = 0;
+    for (int k = 0; k < 5; ++k) fx._pad[k] = 0;
+    const int err = validate_play(cx, s, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
+    fx.err = (uint8_t)err;
+    if (!err) {
+        BB caps = do_valid_play(cx, s, p.from_row, p.from_col, p.axis == TAFL_HORIZONTAL, p.disp);
+        put_bb(fx.captures, caps);
+        fx.n_captures = (uint8_t)caps.popc();
+    }
+    fx.status = s.status;
+    out_st[i] = s;
+    out_fx[i] = fx;
+}
+template <class BB>
+__global__ void k_bv_piece_plays(const __grid_constant__ Ctx<BB> cx, const tafl_state* st, const uint8_t* rc, uint32_t n,
+                                 tafl_move* moves, int32_t* counts) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    tafl_state s = st[i];
+    counts[i] = piece_plays(cx, s, rc[2 * i], rc[2 * i + 1], moves + (size_t)i * 32);
+}
+template <class BB>
+__global__ void k_bv_captures(const __grid_constant__ Ctx<BB> cx, const tafl_state* st, const tafl_play* pl, uint32_t n,
+                              tafl_play_effects* out, int shieldwall_only) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    tafl_state s = st[i];
+    out[i] = shieldwall_only ? query_shieldwall(cx, s, pl[i]) : query_captures(cx, s, pl[i]);
+}
+template <class BB>
+__global__ void k_bv_enclosure(const __grid_constant__ Ctx<BB> cx, const tafl_state* st, const tafl_enclosure_query* q,
+                               uint32_t n, tafl_enclosure* out, uint8_t* secure) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    tafl_state s = st[i];
+    uint8_t sec;
+    tafl_enclosure e = query_enclosure(cx, s, q[i], &sec);
+    if (out) out[i] = e;
+    if (secure) secure[i] = sec;
+}
+template <class BB>
+__global__ void k_bv_exit_fort(const __grid_constant__ Ctx<BB> cx, const tafl_state* st, uint32_t n, uint8_t* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    tafl_state s = st[i];
+    out[i] = detect_exit_fort(cx, load_pos(cx, s)) ? 1 : 0;
+}
+template <class BB>
+__global__ void k_bv_can_play(const __grid_constant__ Ctx<BB> cx, const tafl_state* st, const uint8_t* sides, uint32_t n,
+                              uint8_t* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    tafl_state s = st[i];
+    out[i] = query_can_play(cx, s, sides[i] != 0);
+}
+
+std::string g_create_error;
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// internal helpers
+// ---------------------------------------------------------------------------------------------
+namespace tafl {
+
+int set_cuda_error(tafl_engine* e, cudaError_t ce, const char* what) {
+    std::string msg = std::string("CUDA error: ") + cudaGetErrorString(ce) + " in " + what;
+    if (e) e->err = msg; else g_create_error = msg;
+    return TAFL_ERR_CUDA;
+}
+int scratch(tafl_engine* e, int slot, size_t bytes, void** out) {
+    if (bytes == 0) bytes = 16;
+    if (e->scratch_bytes[slot] < bytes) {
+        if (e->d_scratch[slot]) cudaFree(e->d_scratch[slot]);
+        e->d_scratch[slot] = nullptr;
+        e->scratch_bytes[slot] = 0;
+        size_t cap = bytes + bytes / 2;
+        TAFL_CUDA_TRY(e, cudaMalloc(&e->d_scratch[slot], cap));
+        e->scratch_bytes[slot] = cap;
+    }
+    *out = e->d_scratch[slot];
+    return TAFL_OK;
+}
+
+}  // namespace tafl
+
+#define TAFL_CHECK_E(e) \
+    if (!(e)) return TAFL_ERR_INVALID_ARG
+// run `body` with BB / cx bound to the engine's bitfield width
+#define TAFL_WIDTH_DISPATCH(e, body)                                     \
+    do {                                                                 \
+        if ((e)->width == 64) { using BB = BB64; const Ctx<BB64>& cx = (e)->cx64; body; }       \
+        else { using BB = BB128; const Ctx<BB128>& cx = (e)->cx128; body; }                     \
+    } while (0)
+#define TAFL_LAUNCHED(e)                                                 \
+    do {                                                                 \
+        (e)->launches += 1;                                              \
+        TAFL_CUDA_TRY((e), cudaGetLastError());                          \
+    } while (0)
+
+static int sync_engine(tafl_engine* e) {
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return TAFL_OK;
+}
+static int check_side_len(tafl_engine* e, const tafl_state* st, uint32_t n) {
+    for (uint32_t i = 0; i < n; ++i)
+        if (st[i].side_len != e->N) {
+            e->err = "state side_len does not match the engine's board";
+            return TAFL_ERR_INVALID_ARG;
+        }
+    return TAFL_OK;
+}
+template <class T>
+static int upload(tafl_engine* e, int slot, const T* h, size_t n, T** d) {
+    void* p;
+    int rc = scratch(e, slot, n * sizeof(T), &p);
+    if (rc) return rc;
+    if (n) TAFL_CUDA_TRY(e, cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, e->stream));
+    *d = (T*)p;
+    return TAFL_OK;
+}
+template <class T>
+static int device_out(tafl_engine* e, int slot, size_t n, T** d) {
+    void* p;
+    int rc = scratch(e, slot, n * sizeof(T), &p);
+    if (rc) return rc;
+    *d = (T*)p;
+    return TAFL_OK;
+}
+template <class T>
+static int download(tafl_engine* e, T* h, const T* d, size_t n) {
+    if (n) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h, d, n * sizeof(T), cudaMemcpyDeviceToHost, e->stream));
+    return TAFL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* tafl_last_error(const tafl_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
+
+int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width_bits, uint32_t n_games, int device,
+                       tafl_engine** out) {
+    if (!rules || !start_fen || !out || n_games == 0) { g_create_error = "invalid argument"; return TAFL_ERR_INVALID_ARG; }
+    *out = nullptr;
+    // parse once at 128 bits to learn the side length, then at the chosen width
+    tafl_state probe;
+    int rc = tafl_state_from_fen(start_fen, 128, rules->starting_side, &probe);
+    if (rc) { g_create_error = "could not parse the starting FEN"; return rc; }
+    const int N = probe.side_len;
+    if (width_bits == 0) width_bits = N <= 7 ? 64 : 128;
+    if ((width_bits != 64 && width_bits != 128) || N < 1 || N > (width_bits == 64 ? 7 : 11)) {
+        g_create_error = "board does not fit the requested bitfield width (u64: <=7, u128: <=11)";
+        return TAFL_ERR_UNSUPPORTED;
+    }
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no usable CUDA device (") + cudaGetErrorString(ce) +
+                         "); libtafl_b200 has no CPU fallback";
+        return TAFL_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return TAFL_ERR_INVALID_ARG; }
+    tafl_engine* e = new tafl_engine();
+    e->device = device; e->width = width_bits; e->N = N; e->n_games = n_games; e->rules = *rules;
+    rc = tafl_state_from_fen(start_fen, width_bits, rules->starting_side, &e->start);
+    if (rc) { delete e; g_create_error = "could not parse the starting FEN"; return rc; }
+    e->cx64 = make_ctx<BB64>(*rules, N <= 7 ? N : 7);
+    e->cx128 = make_ctx<BB128>(*rules, N);
+#define TAFL_CREATE_TRY(call)                                                                \
+    do {                                                                                     \
+        cudaError_t _ce = (call);                                                            \
+        if (_ce != cudaSuccess) {                                                            \
+            g_create_error = std::string("CUDA error: ") + cudaGetErrorString(_ce) + " in " #call; \
+            tafl_engine_destroy(e);                                                          \
+            return TAFL_ERR_CUDA;                                                            \
+        }                                                                                    \
+    } while (0)
+    TAFL_CREATE_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    TAFL_CREATE_TRY(cudaGetDeviceProperties(&prop, device));
+    e->sm_count = prop.multiProcessorCount;
+    TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    TAFL_CREATE_TRY(cudaMalloc(&e->d_states, (size_t)n_games * sizeof(tafl_state)));
+    TAFL_CREATE_TRY(cudaMalloc(&e->d_counts, (size_t)n_games * sizeof(uint32_t)));
+    TAFL_CREATE_TRY(cudaMalloc(&e->d_status, (size_t)n_games));
+    TAFL_CREATE_TRY(cudaMalloc(&e->d_stats, sizeof(DevStats)));
+    TAFL_CREATE_TRY(cudaMalloc(&e->d_checksum, sizeof(unsigned long long)));
+    TAFL_CREATE_TRY(cudaMemsetAsync(e->d_stats, 0, sizeof(DevStats), e->stream));
+    k_fill_states<<<grid_for(n_games, 256), 256, 0, e->stream>>>(e->d_states, n_games, e->start);
+    e->launches += 1;
+    TAFL_CREATE_TRY(cudaGetLastError());
+    TAFL_CREATE_TRY(cudaStreamSynchronize(e->stream));
+#undef TAFL_CREATE_TRY
+    *out = e;
+    return TAFL_OK;
+}
+
+int tafl_engine_destroy(tafl_engine* e) {
+    if (!e) return TAFL_OK;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    mcts_free(e);
+    cudaFree(e->d_states); cudaFree(e->d_moves); cudaFree(e->d_counts); cudaFree(e->d_status);
+    cudaFree(e->d_stats); cudaFree(e->d_checksum);
+    for (auto& p : e->d_scratch) cudaFree(p);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+    return TAFL_OK;
+}
+
+int tafl_engine_info(const tafl_engine* e, uint32_t* n_games, int* width_bits, int* side_len, int* device, int* sm_count) {
+    TAFL_CHECK_E(e);
+    if (n_games) *n_games = e->n_games;
+    if (width_bits) *width_bits = e->width;
+    if (side_len) *side_len = e->N;
+    if (device) *device = e->device;
+    if (sm_count) *sm_count = e->sm_count;
+    return TAFL_OK;
+}
+void* tafl_engine_stream(const tafl_engine* e) { return e ? (void*)e->stream : nullptr; }
+int tafl_engine_sync(tafl_engine* e) { TAFL_CHECK_E(e); cudaSetDevice(e->device); return sync_engine(e); }
+uint64_t tafl_launch_count(const tafl_engine* e) { return e ? e->launches : 0; }
+tafl_state* tafl_states_device(tafl_engine* e) { return e ? e->d_states : nullptr; }
+
+int tafl_reset(tafl_engine* e, const uint32_t* h_ids, uint32_t n) {
+    TAFL_CHECK_E(e);
+    cudaSetDevice(e->device);
+    if (!h_ids) {
+        k_fill_states<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, e->start);
+        TAFL_LAUNCHED(e);
+    } else if (n) {
+        uint32_t* d_ids;
+        int rc = upload(e, 0, h_ids, n, &d_ids);
+        if (rc) return rc;
+        k_reset_ids<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_states, d_ids, n, e->n_games, e->start);
+        TAFL_LAUNCHED(e);
+    }
+    return sync_engine(e);
+}
+int tafl_set_states(tafl_engine* e, const tafl_state* h, uint32_t first, uint32_t n) {
+    TAFL_CHECK_E(e);
+    if (!h || (uint64_t)first + n > e->n_games) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    int rc = check_side_len(e, h, n);
+    if (rc) return rc;
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_states + first, h, (size_t)n * sizeof(tafl_state), cudaMemcpyHostToDevice, e->stream));
+    return sync_engine(e);
+}
+int tafl_get_states(tafl_engine* e, tafl_state* h, uint32_t first, uint32_t n) {
+    TAFL_CHECK_E(e);
+    if (!h || (uint64_t)first + n > e->n_games) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h, e->d_states + first, (size_t)n * sizeof(tafl_state), cudaMemcpyDeviceToHost, e->stream));
+    return sync_engine(e);
+}
+
+static int ensure_moves(tafl_engine* e) {
+    if (!e->d_moves) TAFL_CUDA_TRY(e, cudaMalloc(&e->d_moves, (size_t)e->n_games * TAFL_MAX_MOVES * sizeof(tafl_move)));
+    return TAFL_OK;
+}
+int tafl_moves_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_counts) {
+    TAFL_CHECK_E(e);
+    cudaSetDevice(e->device);
+    int rc = ensure_moves(e);
+    if (rc) return rc;
+    if (d_moves) *d_moves = e->d_moves;
+    if (d_counts) *d_counts = e->d_counts;
+    return TAFL_OK;
+}
+static int legal_moves_enqueue(tafl_engine* e, const tafl_state* d_states, uint32_t n, tafl_move* d_moves, uint32_t* d_counts) {
+    TAFL_WIDTH_DISPATCH(e, (k_legal_moves<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, d_states, n, d_moves, d_counts)));
+    TAFL_LAUNCHED(e);
+    return TAFL_OK;
+}
+int tafl_legal_moves(tafl_engine* e, tafl_move* d_moves, uint32_t* d_counts) {
+    TAFL_CHECK_E(e);
+    cudaSetDevice(e->device);
+    if (!d_moves || !d_counts) {
+        int rc = ensure_moves(e);
+        if (rc) return rc;
+        if (!d_moves) d_moves = e->d_moves;
+        if (!d_counts) d_counts = e->d_counts;
+    }
+    int rc = legal_moves_enqueue(e, e->d_states, e->n_games, d_moves, d_counts);
+    if (rc) return rc;
+    return sync_engine(e);
+}
+int tafl_legal_moves_host(tafl_engine* e, tafl_move* h_moves, uint32_t* h_counts, uint32_t first, uint32_t n) {
+    TAFL_CHECK_E(e);
+    if (!h_moves || !h_counts || (uint64_t)first + n > e->n_games) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    int rc = ensure_moves(e);
+    if (rc) return rc;
+    rc = legal_moves_enqueue(e, e->d_states, e->n_games, e->d_moves, e->d_counts);
+    if (rc) return rc;
+    rc = download(e, h_moves, e->d_moves + (size_t)first * TAFL_MAX_MOVES, (size_t)n * TAFL_MAX_MOVES);
+    if (rc) return rc;
+    rc = download(e, h_counts, e->d_counts + first, n);
+    if (rc) return rc;
+    return sync_engine(e);
+}
+
+int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_fx) {
+    TAFL_CHECK_E(e);
+    if (!h_plays) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    tafl_play* d_pl;
+    tafl_play_effects* d_fx;
+    int rc = upload(e, 0, h_plays, n, &d_pl);
+    if (rc) return rc;
+    rc = device_out(e, 1, n, &d_fx);
+    if (rc) return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_step_plays<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx)));
+    TAFL_LAUNCHED(e);
+    if (h_fx) { rc = download(e, h_fx, d_fx, n); if (rc) return rc; }
+    return sync_engine(e);
+}
+int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_status) {
+    TAFL_CHECK_E(e);
+    if (!d_moves) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    TAFL_WIDTH_DISPATCH(e, (k_step_moves<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_moves, 1u, nullptr, d_status)));
+    TAFL_LAUNCHED(e);
+    return sync_engine(e);
+}
+
+int tafl_set_game_id_base(tafl_engine* e, uint64_t v) { TAFL_CHECK_E(e); e->game_id_base = v; return TAFL_OK; }
+int tafl_set_random_ply(tafl_engine* e, uint64_t v) { TAFL_CHECK_E(e); e->ply = v; return TAFL_OK; }
+uint64_t tafl_random_ply(const tafl_engine* e) { return e ? e->ply : 0; }
+
+int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset, int spl) {
+    TAFL_CHECK_E(e);
+    cudaSetDevice(e->device);
+    if (spl <= 0) spl = 1;
+    const uint32_t n = e->n_games;
+    uint32_t done = 0;
+    while (done < n_steps) {
+        const uint32_t chunk = (n_steps - done) < (uint32_t)spl ? (n_steps - done) : (uint32_t)spl;
+        TAFL_WIDTH_DISPATCH(e, (k_step_random<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(
+                                   cx, e->d_states, n, e->start, seed, e->game_id_base, e->ply, chunk, auto_reset, e->d_stats)));
+        TAFL_LAUNCHED(e);
+        e->ply += chunk;
+        done += chunk;
+    }
+    return TAFL_OK;
+}
+int tafl_step_random(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset, int spl) {
+    int rc = tafl_step_random_async(e, seed, n_steps, auto_reset, spl);
+    if (rc) return rc;
+    return sync_engine(e);
+}
+
+int tafl_stats_reset(tafl_engine* e) {
+    TAFL_CHECK_E(e);
+    cudaSetDevice(e->device);
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(e->d_stats, 0, sizeof(DevStats), e->stream));
+    return sync_engine(e);
+}
+int tafl_stats_get(tafl_engine* e, tafl_stats* out) {
+    TAFL_CHECK_E(e);
+    if (!out) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(e->d_checksum, 0, sizeof(unsigned long long), e->stream));
+    k_checksum<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, e->d_checksum);
+    TAFL_LAUNCHED(e);
+    DevStats ds;
+    unsigned long long cs;
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(&ds, e->d_stats, sizeof(ds), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(&cs, e->d_checksum, sizeof(cs), cudaMemcpyDeviceToHost, e->stream));
+    int rc = sync_engine(e);
+    if (rc) return rc;
+    std::memset(out, 0, sizeof(*out));
+    out->steps = ds.steps; out->legal_moves = ds.legal; out->captures = ds.caps;
+    out->games_finished = ds.finished; out->finished_plies = ds.plies;
+    for (int i = 0; i < 2; ++i) for (int j = 0; j < 8; ++j) out->win_reason[i][j] = ds.win[i][j];
+    for (int j = 0; j < 2; ++j) out->draw_reason[j] = ds.draw[j];
+    out->state_checksum = cs;
+    return TAFL_OK;
+}
+
+// ---- functional batch API -----------------------------------------------------------------------
+#define TAFL_BV_PROLOGUE(e, st, n)                        \
+    TAFL_CHECK_E(e);                                      \
+    if (!(st) && (n)) return TAFL_ERR_INVALID_ARG;        \
+    cudaSetDevice((e)->device);                           \
+    {                                                     \
+        int _rc = check_side_len((e), (st), (n));         \
+        if (_rc) return _rc;                              \
+    }
+
+int tafl_validate_plays(tafl_engine* e, const tafl_state* h_st, const tafl_play* h_pl, uint32_t n, uint8_t* h_out) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state* d_st; tafl_play* d_pl; uint8_t* d_out;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = upload(e, 1, h_pl, n, &d_pl)) || (rc = device_out(e, 2, n, &d_out))) return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_bv_validate<BB><<<grid_for(n, 128), 128, 0, e->stream>>>(cx, d_st, d_pl, n, d_out)));
+    TAFL_LAUNCHED(e);
+    if ((rc = download(e, h_out, d_out, n))) return rc;
+    return sync_engine(e);
+}
+int tafl_do_plays(tafl_engine* e, const tafl_state* h_st, const tafl_play* h_pl, uint32_t n, tafl_state* h_out_st,
+                  tafl_play_effects* h_out_fx) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state *d_st, *d_ost; tafl_play* d_pl; tafl_play_effects* d_fx;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = upload(e, 1, h_pl, n, &d_pl)) || (rc = device_out(e, 2, n, &d_ost)) ||
+        (rc = device_out(e, 3, n, &d_fx)))
+        return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_bv_do_plays<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, d_st, d_pl, n, d_ost, d_fx)));
+    TAFL_LAUNCHED(e);
+    if (h_out_st && (rc = download(e, h_out_st, d_ost, n))) return rc;
+    if (h_out_fx && (rc = download(e, h_out_fx, d_fx, n))) return rc;
+    return sync_engine(e);
+}
+int tafl_legal_moves_of(tafl_engine* e, const tafl_state* h_st, uint32_t n, tafl_move* h_moves, uint32_t* h_counts) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state* d_st; tafl_move* d_mv; uint32_t* d_cnt;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = device_out(e, 1, (size_t)n * TAFL_MAX_MOVES, &d_mv)) ||
+        (rc = device_out(e, 2, n, &d_cnt)))
+        return rc;
+    if ((rc = legal_moves_enqueue(e, d_st, n, d_mv, d_cnt))) return rc;
+    if ((rc = download(e, h_moves, d_mv, (size_t)n * TAFL_MAX_MOVES)) || (rc = download(e, h_counts, d_cnt, n))) return rc;
+    return sync_engine(e);
+}
+int tafl_piece_plays(tafl_engine* e, const tafl_state* h_st, const uint8_t* h_rc, uint32_t n, tafl_move* h_moves, int32_t* h_counts) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state* d_st; uint8_t* d_rc; tafl_move* d_mv; int32_t* d_cnt;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = upload(e, 1, h_rc, (size_t)2 * n, &d_rc)) ||
+        (rc = device_out(e, 2, (size_t)n * 32, &d_mv)) || (rc = device_out(e, 3, n, &d_cnt)))
+        return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_bv_piece_plays<BB><<<grid_for(n, 128), 128, 0, e->stream>>>(cx, d_st, d_rc, n, d_mv, d_cnt)));
+    TAFL_LAUNCHED(e);
+    if ((rc = download(e, h_moves, d_mv, (size_t)n * 32)) || (rc = download(e, h_counts, d_cnt, n))) return rc;
+    return sync_engine(e);
+}
+static int captures_common(tafl_engine* e, const tafl_state* h_st, const tafl_play* h_pl, uint32_t n, tafl_play_effects* h_out, int sw) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state* d_st; tafl_play* d_pl; tafl_play_effects* d_fx;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = upload(e, 1, h_pl, n, &d_pl)) || (rc = device_out(e, 2, n, &d_fx))) return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_bv_captures<BB><<<grid_for(n, 128), 128, 0, e->stream>>>(cx, d_st, d_pl, n, d_fx, sw)));
+    TAFL_LAUNCHED(e);
+    if ((rc = download(e, h_out, d_fx, n))) return rc;
+    return sync_engine(e);
+}
+int tafl_get_captures(tafl_engine* e, const tafl_state* s, const tafl_play* p, uint32_t n, tafl_play_effects* o) { return captures_common(e, s, p, n, o, 0); }
+int tafl_detect_shieldwall(tafl_engine* e, const tafl_state* s, const tafl_play* p, uint32_t n, tafl_play_effects* o) { return captures_common(e, s, p, n, o, 1); }
+
+static int enclosure_common(tafl_engine* e, const tafl_state* h_st, const tafl_enclosure_query* h_q, uint32_t n, tafl_enclosure* h_enc, uint8_t* h_sec) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state* d_st; tafl_enclosure_query* d_q; tafl_enclosure* d_enc; uint8_t* d_sec;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = upload(e, 1, h_q, n, &d_q)) || (rc = device_out(e, 2, n, &d_enc)) ||
+        (rc = device_out(e, 3, n, &d_sec)))
+        return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_bv_enclosure<BB><<<grid_for(n, 128), 128, 0, e->stream>>>(cx, d_st, d_q, n, d_enc, d_sec)));
+    TAFL_LAUNCHED(e);
+    if (h_enc && (rc = download(e, h_enc, d_enc, n))) return rc;
+    if (h_sec && (rc = download(e, h_sec, d_sec, n))) return rc;
+    return sync_engine(e);
+}
+int tafl_find_enclosure(tafl_engine* e, const tafl_state* s, const tafl_enclosure_query* q, uint32_t n, tafl_enclosure* o) { return enclosure_common(e, s, q, n, o, nullptr); }
+int tafl_enclosure_secure(tafl_engine* e, const tafl_state* s, const tafl_enclosure_query* q, uint32_t n, uint8_t* o) { return enclosure_common(e, s, q, n, nullptr, o); }
+
+int tafl_detect_exit_fort(tafl_engine* e, const tafl_state* h_st, uint32_t n, uint8_t* h_out) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state* d_st; uint8_t* d_out;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = device_out(e, 1, n, &d_out))) return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_bv_exit_fort<BB><<<grid_for(n, 128), 128, 0, e->stream>>>(cx, d_st, n, d_out)));
+    TAFL_LAUNCHED(e);
+    if ((rc = download(e, h_out, d_out, n))) return rc;
+    return sync_engine(e);
+}
+int tafl_side_can_play(tafl_engine* e, const tafl_state* h_st, const uint8_t* h_sides, uint32_t n, uint8_t* h_out) {
+    TAFL_BV_PROLOGUE(e, h_st, n);
+    if (!n) return TAFL_OK;
+    tafl_state* d_st; uint8_t *d_sides, *d_out;
+    int rc;
+    if ((rc = upload(e, 0, h_st, n, &d_st)) || (rc = upload(e, 1, h_sides, n, &d_sides)) || (rc = device_out(e, 2, n, &d_out))) return rc;
+    TAFL_WIDTH_DISPATCH(e, (k_bv_can_play<BB><<<grid_for(n, 128), 128, 0, e->stream>>>(cx, d_st, d_sides, n, d_out)));
+    TAFL_LAUNCHED(e);
+    if ((rc = download(e, h_out, d_out, n))) return rc;
+    return sync_engine(e);
+}
+
+}  // extern "C"

@@ -1,0 +1,306 @@
+// tafl_select.cuh — branch-free legal-move COUNT and k-th-move SELECT for one game per thread,
+// plus the fused random-playout step and the by-value query helpers.
+//
+// The random-play step never materialises the move list.  Instead (all 128-bit bit-parallel):
+//   1. for each of the 4 ray directions and each distance d, E_d = set of own soldiers that can
+//      legally move exactly d tiles that way (source-aligned ray fill; play.rs:189-225 semantics);
+//   2. the <= 40 E_d boards are summed per source tile with a carry-save-adder tree into 5
+//      bit-sliced planes (plane b = bit b of "number of legal plays of the piece on this tile");
+//      the king's count (different throne/corner rights) is computed in line space and OR-ed in;
+//   3. total L = sum_b 2^b popc(plane_b); the k-th play in canonical order (pieces ascending
+//      bit index, game/main.rs:33-43) is found by a word-level then 5-level binary search on
+//      masked plane popcounts, and resolved to (direction, distance) with piece_rays().
+#pragma once
+#include "tafl_core.cuh"
+
+namespace tafl {
+
+template <class BB>
+struct MoveSel {
+    BB plane[5];
+    int total;
+    int def_side;
+};
+
+template <class BB>
+struct CsaAcc {
+    BB ones, twos, fours, eights, sixteens, p1, p2, p4;
+    TAFL_HD void init() { ones = twos = fours = eights = sixteens = p1 = p2 = p4 = BB::zero(); }
+    TAFL_HD static void csa(BB& h, BB& l, BB a, BB b, BB c) {
+        BB u = a ^ b;
+        h = (a & b) | (u & c);
+        l = u ^ c;
+    }
+    // i = 0,1,2,... must be a compile-time constant after unrolling
+    TAFL_HD void add(BB x, int i) {
+        if ((i & 1) == 0) { p1 = x; return; }
+        BB t, f, e;
+        csa(t, ones, ones, p1, x);
+        if ((i & 2) == 0) { p2 = t; return; }
+        csa(f, twos, twos, p2, t);
+        if ((i & 4) == 0) { p4 = f; return; }
+        csa(e, fours, fours, p4, f);
+        BB carry = eights & e;
+        eights = eights ^ e;
+        sixteens = sixteens ^ carry;
+    }
+};
+
+template <class BB> struct MaxD;
+template <> struct MaxD<BB64> { static constexpr int v = 6; };
+template <> struct MaxD<BB128> { static constexpr int v = 10; };
+
+// count legal plays of `def_side`'s pieces on position p (status must be Ongoing)
+template <class BB>
+TAFL_HD MoveSel<BB> count_moves(const Ctx<BB>& cx, const Pos<BB>& p, int def_side) {
+    constexpr int S = BB::STRIDE;
+    constexpr int MD = MaxD<BB>::v;
+    MoveSel<BB> ms;
+    ms.def_side = def_side;
+    const int k = def_side ? KIND_DS : KIND_AS;
+    const BB occ = p.occ();
+    // a blocked corner always ends a ray, so it can be treated as not walkable (logic.rs:190-193)
+    const BB walk = cx.board & ~occ & ~(cx.may_corner[k] ? BB::zero() : cx.corners);
+    const BB src = p.kind(k);
+    const BB thr = cx.throne;
+    const bool noentry = cx.noentry[k] != 0, passblk = cx.pass_block[k] != 0, slow = cx.slow[k] != 0;
+    CsaAcc<BB> acc;
+    acc.init();
+    int n = 0;
+#pragma unroll
+    for (int dir = 0; dir < 4; ++dir) {
+        BB X = walk, E = src, T = thr, Tprev = BB::zero();
+#pragma unroll
+        for (int d = 1; d <= MD; ++d) {
+            // X(s) = walkable(s + d*step); T(s) = [s + d*step == throne]
+            if (dir == DIR_VP) { X = X.template shr<S>(); T = T.template shr<S>(); }
+            else if (dir == DIR_VM) { X = X.template shl<S>(); T = T.template shl<S>(); }
+            else if (dir == DIR_HP) { X = X.template shr<1>() & cx.not_colL; T = T.template shr<1>(); }
+            else { X = X.template shl<1>() & cx.not_col0; T = T.template shl<1>(); }
+            E = E & X;
+            if (passblk) E = E & ~Tprev;                  // logic.rs:194-200
+            BB emit = noentry ? (E & ~T) : E;             // logic.rs:201-206 + play.rs:208-211
+            if (slow && d > 1) emit = BB::zero();         // logic.rs:207-210
+            acc.add(emit, n);
+            ++n;
+            Tprev = T;
+        }
+    }
+    // flush pending partial sums when the number of inputs is not a multiple of 8 (BB64: 24 = 3*8 ok)
+    ms.plane[0] = acc.ones; ms.plane[1] = acc.twos; ms.plane[2] = acc.fours; ms.plane[3] = acc.eights;
+    ms.plane[4] = acc.sixteens;
+    if (def_side && (p.def & p.kbit).any()) {
+        Rays r = piece_rays(cx, occ, KIND_K, p.kr, p.kc);
+        int ck = r.cnt[0] + r.cnt[1] + r.cnt[2] + r.cnt[3];
+#pragma unroll
+        for (int b = 0; b < 5; ++b)
+            if ((ck >> b) & 1) ms.plane[b] = ms.plane[b] | p.kbit;
+    }
+    int total = 0;
+#pragma unroll
+    for (int b = 0; b < 5; ++b) total += ms.plane[b].popc() << b;
+    ms.total = total;
+    return ms;
+}
+
+// k-th legal play (0 <= k < ms.total) in canonical order
+template <class BB>
+TAFL_HD tafl_move select_move(const Ctx<BB>& cx, const Pos<BB>& p, const MoveSel<BB>& ms, uint32_t k) {
+    // word-level prefix
+    uint32_t pw[5] = {0, 0, 0, 0, 0};
+    int wsel = 0;
+    bool done = false;
+#pragma unroll
+    for (int j = 0; j < BB::WORDS; ++j) {
+        uint32_t w = 0;
+#pragma unroll
+        for (int b = 0; b < 5; ++b) w += (uint32_t)popc32(ms.plane[b].word(j)) << b;
+        const bool here = !done && k < w;
+        if (here) {
+            wsel = j;
+#pragma unroll
+            for (int b = 0; b < 5; ++b) pw[b] = ms.plane[b].word(j);
+            done = true;
+        }
+        if (!done) k -= w;
+    }
+    // binary search for the source bit inside the word
+    int lo = 0;
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const uint32_t m = ((1u << half) - 1u) << lo;
+        uint32_t w = 0;
+#pragma unroll
+        for (int b = 0; b < 5; ++b) w += (uint32_t)popc32(pw[b] & m) << b;
+        if (k >= w) { k -= w; lo += half; }
+    }
+    const int s = wsel * 32 + lo;
+    const int row = s / BB::STRIDE, col = s - row * BB::STRIDE;
+    const int kind = ms.def_side ? ((BB::bit(s) == p.kbit) ? KIND_K : KIND_DS) : KIND_AS;
+    Rays r = piece_rays(cx, p.occ(), kind, row, col);
+    int dir = 0;
+    uint32_t kk = k;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        if (dir == d && kk >= (uint32_t)r.cnt[d]) { kk -= r.cnt[d]; dir = d + 1; }
+    }
+    const uint32_t m = dir == 0 ? r.m[0] : dir == 1 ? r.m[1] : dir == 2 ? r.m[2] : r.m[3];
+    const int pos = ray_nth(m, dir, (int)kk);
+    const int to = dir < 2 ? idx_of<BB>(pos, col) : idx_of<BB>(row, pos);
+    return (tafl_move)(s | (to << 7));
+}
+
+// ---------------------------------------------------------------------------------------------
+// fused random-playout step (BASELINE.json configs 1-2)
+// ---------------------------------------------------------------------------------------------
+struct StepEvt {
+    uint32_t stepped, legal, caps;
+    uint8_t status;   // != 0: the game ended on this step
+    uint32_t turn;
+};
+template <class BB>
+TAFL_HD StepEvt random_step(const Ctx<BB>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
+                            uint64_t ply, bool auto_reset) {
+    StepEvt ev;
+    ev.stepped = ev.legal = ev.caps = ev.turn = 0;
+    ev.status = 0;
+    if (s.status != TAFL_STATUS_ONGOING) {
+        if (!auto_reset) return ev;
+        s = start;
+    }
+    const Pos<BB> p = load_pos(cx, s);
+    const MoveSel<BB> ms = count_moves(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
+    if (ms.total == 0) return ev;
+    const uint32_t k = pick_index(seed, gid, ply, (uint32_t)ms.total);
+    const tafl_move m = select_move(cx, p, ms, k);
+    const BB caps = do_valid_move(cx, s, m);
+    ev.stepped = 1;
+    ev.legal = (uint32_t)ms.total;
+    ev.caps = (uint32_t)caps.popc();
+    ev.status = s.status;
+    ev.turn = s.turn;
+    return ev;
+}
+
+struct StepStats {
+    uint64_t steps, legal, caps, finished, plies, win[2][8], draw[2];
+};
+TAFL_HD void add_evt(StepStats& a, const StepEvt& e) {
+    a.steps += e.stepped;
+    a.legal += e.legal;
+    a.caps += e.caps;
+    if (e.status) {
+        a.finished += 1;
+        a.plies += e.turn;
+        if (TAFL_STATUS_IS_DRAW(e.status)) a.draw[TAFL_STATUS_REASON(e.status) & 1] += 1;
+        else a.win[e.status & 1][TAFL_STATUS_REASON(e.status)] += 1;
+    }
+}
+template <class BB>
+TAFL_HD void random_step(const Ctx<BB>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
+                         uint64_t ply, bool auto_reset, StepStats& acc) {
+    add_evt(acc, random_step(cx, s, start, seed, gid, ply, auto_reset));
+}
+inline void fold_stats(const StepStats& a, tafl_stats* o) {
+    o->steps += a.steps; o->legal_moves += a.legal; o->captures += a.caps;
+    o->games_finished += a.finished; o->finished_plies += a.plies;
+    for (int i = 0; i < 2; ++i) for (int j = 0; j < 8; ++j) o->win_reason[i][j] += a.win[i][j];
+    for (int j = 0; j < 2; ++j) o->draw_reason[j] += a.draw[j];
+}
+
+// ---------------------------------------------------------------------------------------------
+// by-value query helpers (one item each; used by the functional batch kernels)
+// ---------------------------------------------------------------------------------------------
+template <class BB> TAFL_HD void put_bb(uint64_t o[2], BB b) { o[0] = b.lo64(); o[1] = b.hi64(); }
+
+// GameLogic::iter_plays(tile) (logic.rs:850-856): -1 == Err(NoPiece)
+template <class BB>
+TAFL_HD int piece_plays(const Ctx<BB>& cx, const tafl_state& st, int row, int col, tafl_move* out) {
+    Pos<BB> p = load_pos(cx, st);
+    const int s = idx_of<BB>(row, col);
+    int kind;
+    if (Nib<BB>::raw_def(st, s)) kind = (row == p.kr && col == p.kc) ? KIND_K : KIND_DS;
+    else if (Nib<BB>::raw_att(st, s)) kind = KIND_AS;
+    else return -1;
+    if (st.status != TAFL_STATUS_ONGOING) return 0;
+    if (row >= cx.N || col >= cx.N) return 0;
+    Rays r = piece_rays(cx, p.occ(), kind, row, col);
+    int n = 0;
+    for (int d = 0; d < 4; ++d)
+        for (int j = 0; j < r.cnt[d]; ++j) {
+            int pos = ray_nth(r.m[d], d, j);
+            int to = d < 2 ? idx_of<BB>(pos, col) : idx_of<BB>(row, pos);
+            if (n < 32) out[n] = (tafl_move)(s | (to << 7));
+            ++n;
+        }
+    return n;
+}
+// GameLogic::get_captures (logic.rs:604-699) after moving the piece as do_valid_play does
+template <class BB>
+TAFL_HD tafl_play_effects query_captures(const Ctx<BB>& cx, const tafl_state& st, const tafl_play& pl) {
+    tafl_play_effects fx;
+    fx.captures[0] = fx.captures[1] = 0;
+    fx.status = st.status; fx.err = 0; fx.n_captures = 0;
+    for (int i = 0; i < 5; ++i) fx._pad[i] = 0;
+    Pos<BB> p = load_pos(cx, st);
+    const int fr = pl.from_row, fc = pl.from_col, hz = pl.axis == TAFL_HORIZONTAL;
+    const int tr = hz ? fr : fr + pl.disp, tc = hz ? fc + pl.disp : fc;
+    const BB fb = (fr < cx.N && fc < cx.N) ? BB::bit(idx_of<BB>(fr, fc)) : BB::zero();
+    const int pk = kind_at(p, fb);
+    if (pk == KIND_NONE || tr < 0 || tc < 0 || tr >= cx.N || tc >= cx.N) { fx.err = TAFL_NO_PIECE; return fx; }
+    const BB tb = BB::bit(idx_of<BB>(tr, tc));
+    const int piece_def = pk != KIND_AS;
+    if (piece_def) { p.def = p.def | tb; p.att = p.att & ~tb; } else { p.att = p.att | tb; p.def = p.def & ~tb; }
+    if (pk == KIND_K) { p.kr = tr; p.kc = tc; p.kbit = tb; }
+    p.att = p.att & ~fb; p.def = p.def & ~fb;
+    BB caps = get_captures(cx, p, piece_def, pk, (st.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, tr, tc);
+    put_bb(fx.captures, caps);
+    fx.n_captures = (uint8_t)caps.popc();
+    return fx;
+}
+// GameLogic::detect_shieldwall (logic.rs:535-569) on the board as given
+template <class BB>
+TAFL_HD tafl_play_effects query_shieldwall(const Ctx<BB>& cx, const tafl_state& st, const tafl_play& pl) {
+    tafl_play_effects fx;
+    fx.captures[0] = fx.captures[1] = 0;
+    fx.status = st.status; fx.err = 0; fx.n_captures = 0xFF;
+    for (int i = 0; i < 5; ++i) fx._pad[i] = 0;
+    Pos<BB> p = load_pos(cx, st);
+    const int fr = pl.from_row, fc = pl.from_col, hz = pl.axis == TAFL_HORIZONTAL;
+    const int tr = hz ? fr : fr + pl.disp, tc = hz ? fc + pl.disp : fc;
+    BB caps;
+    if (detect_shieldwall(cx, p, (st.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, tr, tc, &caps)) {
+        put_bb(fx.captures, caps);
+        fx.n_captures = (uint8_t)caps.popc();
+    }
+    return fx;
+}
+// GameLogic::find_enclosure (logic.rs:309-401) [+ enclosure_secure logic.rs:408-463 -> *secure]
+template <class BB>
+TAFL_HD tafl_enclosure query_enclosure(const Ctx<BB>& cx, const tafl_state& st, const tafl_enclosure_query& q,
+                                       uint8_t* secure) {
+    tafl_enclosure o;
+    o.occupied[0] = o.occupied[1] = o.unoccupied[0] = o.unoccupied[1] = o.boundary[0] = o.boundary[1] = 0;
+    o.found = 0;
+    for (int i = 0; i < 7; ++i) o._pad[i] = 0;
+    Pos<BB> p = load_pos(cx, st);
+    BB enclosed = pieceset_bb(p, q.enclosed_pieces);
+    BB enclosing = pieceset_bb(p, q.enclosing_pieces) & ~enclosed;
+    Encl<BB> e = find_enclosure(cx, p, q.row, q.col, enclosed, enclosing, q.abort_on_edge != 0, q.abort_on_corner != 0);
+    *secure = 0xFF;
+    if (!e.found) return o;
+    o.found = 1;
+    put_bb(o.occupied, e.region & p.occ());
+    put_bb(o.unoccupied, e.region & ~p.occ());
+    put_bb(o.boundary, e.boundary);
+    *secure = enclosure_secure(cx, p, e, q.inside_safe != 0, q.outside_safe != 0) ? 1 : 0;
+    return o;
+}
+// GameLogic::side_can_play (logic.rs:837-846)
+template <class BB>
+TAFL_HD uint8_t query_can_play(const Ctx<BB>& cx, const tafl_state& st, int def_side) {
+    if (st.status != TAFL_STATUS_ONGOING) return 0;  // every play validates as GameOver (logic.rs:165-167)
+    return side_can_play(cx, load_pos(cx, st), def_side) ? 1 : 0;
+}
+
+}  // namespace tafl

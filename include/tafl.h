@@ -222,6 +222,37 @@ int tafl_play_to_str(const tafl_play* p, char* buf, size_t buf_len);
 /* compact move <-> Play for a given bitfield width */
 int tafl_move_to_play(tafl_move m, int width_bits, tafl_play* out);
 
+/* BoardState::from_display_str / to_display_str (board/state.rs:252-269, 297-311) */
+int tafl_state_from_display_str(const char* s, int width_bits, int side_to_play, tafl_state* out);
+int tafl_state_to_display_str(const tafl_state* st, int width_bits, char* buf, size_t buf_len);
+
+/* `trait BoardState` accessors (board/state.rs:13-81) on one packed state */
+int tafl_board_get_king(const tafl_state* st, int width_bits, uint8_t* row, uint8_t* col);   /* :17,127 */
+int tafl_board_set_king(tafl_state* st, int width_bits, uint8_t row, uint8_t col);           /* :20,136 */
+int tafl_board_is_king(const tafl_state* st, int width_bits, uint8_t row, uint8_t col);      /* :23     */
+int tafl_board_set_piece(tafl_state* st, int width_bits, uint8_t row, uint8_t col,
+                         int piece_type, int side);                                           /* :28,149 */
+int tafl_board_clear_tile(tafl_state* st, int width_bits, uint8_t row, uint8_t col);         /* :31,167 */
+/* returns 0 and *piece_type = 0 for an empty tile (Option::None) */
+int tafl_board_get_piece(const tafl_state* st, int width_bits, uint8_t row, uint8_t col,
+                         int* piece_type, int* side);                                         /* :34,173 */
+int tafl_board_tile_occupied(const tafl_state* st, int width_bits, uint8_t row, uint8_t col);/* :37,189 */
+int tafl_board_count_pieces(const tafl_state* st, int width_bits, int side);                 /* :41,195 */
+/* tiles in ascending bit order; out_rc = [row, col] pairs (>= 2*128 bytes); returns the count */
+int tafl_board_iter_occupied(const tafl_state* st, int width_bits, int side, uint8_t* out_rc);/* :45,202 */
+/* TAFL_ERR_NO_PIECE mirrors the `expect("No piece to move.")` panic (board/state.rs:219) */
+int tafl_board_move_piece(tafl_state* st, int width_bits, uint8_t from_row, uint8_t from_col,
+                          uint8_t to_row, uint8_t to_col);                                    /* :50,218 */
+int tafl_board_swap_pieces(tafl_state* st, int width_bits, uint8_t r1, uint8_t c1, uint8_t r2,
+                           uint8_t c2);                                                       /* :69     */
+/* Tile: FromStr / Display (tiles.rs:131-157), e.g. "a8" <-> (7, 0) */
+int tafl_tile_from_str(const char* s, uint8_t* row, uint8_t* col);
+int tafl_tile_to_str(uint8_t row, uint8_t col, char* buf, size_t buf_len);
+/* RepetitionTracker::track_play (game/state.rs:92-113) on one packed state */
+int tafl_track_play(tafl_state* st, int side, const tafl_play* play, int captures);
+/* board_to_matrix (game/main.rs:55-83): side_len*side_len bytes, row-major */
+int tafl_board_to_matrix(const tafl_state* st, int width_bits, uint8_t* out, size_t out_len);
+
 const char* tafl_version(void);
 
 /* ------------------------------------------------------------------------------------------
@@ -240,6 +271,8 @@ int tafl_engine_info(const tafl_engine* e, uint32_t* n_games, int* width_bits, i
 /* cudaStream_t of the engine (for callers that want to order their own work / events) */
 void* tafl_engine_stream(const tafl_engine* e);
 int tafl_engine_sync(tafl_engine* e);
+/* number of kernels this engine has launched so far (bench.py's gpu_launches) */
+uint64_t tafl_launch_count(const tafl_engine* e);
 
 /* reset games to the start position (ids == NULL: all games) */
 int tafl_reset(tafl_engine* e, const uint32_t* h_game_ids, uint32_t n);

@@ -1,0 +1,277 @@
+"""Test-only loaders for the CPU oracle (oracle/liboracle.so) and for the host build of the
+kernel math (tests/hostsim/libhostsim.so).  Nothing in the product package imports this file."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from alphazeroforhnefatafl_b200 import _abi as A
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+HOSTSIM_DIR = os.path.join(ROOT, "tests", "hostsim")
+CSRC = os.path.join(ROOT, "alphazeroforhnefatafl_b200", "csrc")
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build_oracle():
+    so = os.path.join(ORACLE_DIR, "liboracle.so")
+    deps = [os.path.join(ORACLE_DIR, f) for f in ("oracle_capi.cpp", "tafl_oracle.hpp", "mcts_oracle.hpp")]
+    deps.append(os.path.join(ROOT, "include", "tafl.h"))
+    if _newer(so, deps) or _newer(os.path.join(ORACLE_DIR, "oracle_kat"), deps + [os.path.join(ORACLE_DIR, "kat_main.cpp")]):
+        subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "all"])
+    return so
+
+
+def build_hostsim():
+    so = os.path.join(HOSTSIM_DIR, "libhostsim.so")
+    deps = [os.path.join(HOSTSIM_DIR, "hostsim.cpp"), os.path.join(ROOT, "include", "tafl.h")]
+    deps += [os.path.join(CSRC, f) for f in ("tafl_bb.cuh", "tafl_core.cuh", "tafl_select.cuh", "tafl_ctx.hpp")]
+    if _newer(so, deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
+                               "-Wno-unknown-pragmas", "-o", so, os.path.join(HOSTSIM_DIR, "hostsim.cpp")])
+    return so
+
+
+class ByValueImpl:
+    """The functional (by-value) batch API, identical for oracle (orc_) and hostsim (sim_)."""
+
+    def __init__(self, lib, prefix, rules, width):
+        self.lib, self.prefix, self.rules, self.width = lib, prefix, rules, width
+
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    def validate_plays(self, states, plays):
+        n = len(states)
+        out = np.zeros(n, np.uint8)
+        rc = self._f("validate_plays")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(plays), n, A.ptr(out))
+        assert rc == 0, rc
+        return out
+
+    def do_plays(self, states, plays):
+        n = len(states)
+        out = np.zeros(n, A.STATE_DTYPE)
+        fx = np.zeros(n, A.EFFECTS_DTYPE)
+        rc = self._f("do_plays")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(plays), n, A.ptr(out), A.ptr(fx))
+        assert rc == 0, rc
+        return out, fx
+
+    def legal_moves_of(self, states):
+        n = len(states)
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        counts = np.zeros(n, np.uint32)
+        rc = self._f("legal_moves_of")(C.byref(self.rules), self.width, A.ptr(states), n, A.ptr(moves), A.ptr(counts))
+        assert rc == 0, rc
+        return moves, counts
+
+    def piece_plays(self, states, tiles_rc):
+        n = len(states)
+        tiles_rc = np.ascontiguousarray(tiles_rc, np.uint8)
+        moves = np.zeros((n, 32), np.uint16)
+        counts = np.zeros(n, np.int32)
+        rc = self._f("piece_plays")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(tiles_rc), n, A.ptr(moves),
+                                    A.ptr(counts))
+        assert rc == 0, rc
+        return moves, counts
+
+    def get_captures(self, states, plays):
+        n = len(states)
+        fx = np.zeros(n, A.EFFECTS_DTYPE)
+        rc = self._f("get_captures")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(plays), n, A.ptr(fx))
+        assert rc == 0, rc
+        return fx
+
+    def detect_shieldwall(self, states, plays):
+        n = len(states)
+        fx = np.zeros(n, A.EFFECTS_DTYPE)
+        rc = self._f("detect_shieldwall")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(plays), n, A.ptr(fx))
+        assert rc == 0, rc
+        return fx
+
+    def find_enclosure(self, states, queries):
+        n = len(states)
+        out = np.zeros(n, A.ENCLOSURE_DTYPE)
+        rc = self._f("find_enclosure")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(queries), n, A.ptr(out))
+        assert rc == 0, rc
+        return out
+
+    def enclosure_secure(self, states, queries):
+        n = len(states)
+        out = np.zeros(n, np.uint8)
+        rc = self._f("enclosure_secure")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(queries), n, A.ptr(out))
+        assert rc == 0, rc
+        return out
+
+    def detect_exit_fort(self, states):
+        n = len(states)
+        out = np.zeros(n, np.uint8)
+        rc = self._f("detect_exit_fort")(C.byref(self.rules), self.width, A.ptr(states), n, A.ptr(out))
+        assert rc == 0, rc
+        return out
+
+    def side_can_play(self, states, sides):
+        n = len(states)
+        sides = np.ascontiguousarray(sides, np.uint8)
+        out = np.zeros(n, np.uint8)
+        rc = self._f("side_can_play")(C.byref(self.rules), self.width, A.ptr(states), A.ptr(sides), n, A.ptr(out))
+        assert rc == 0, rc
+        return out
+
+
+class Oracle:
+    """ctypes face of oracle/liboracle.so."""
+
+    def __init__(self):
+        self.lib = C.CDLL(build_oracle())
+        L = self.lib
+        L.orc_preset_board_fen.restype = C.c_char_p
+        for name in ("orc_random_playout", "orc_mcts_search"):
+            getattr(L, name).restype = C.c_int
+        L.orc_random_playout.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_uint64, C.c_uint64, C.c_uint32,
+                                         C.c_uint64, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_mcts_search.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_double, C.c_double,
+                                      C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+
+    def preset_rules(self, preset):
+        r = A.Rules()
+        assert self.lib.orc_preset_rules(preset, C.byref(r)) == 0
+        return r
+
+    def preset_board(self, preset):
+        return self.lib.orc_preset_board_fen(preset).decode()
+
+    def state_from_fen(self, fen, width, side=A.ATTACKER):
+        st = np.zeros(1, A.STATE_DTYPE)
+        rc = self.lib.orc_state_from_fen(fen.encode(), width, 1 if side == A.DEFENDER else 0, A.ptr(st))
+        return rc, st
+
+    def state_from_display_str(self, s, width, side=A.ATTACKER):
+        st = np.zeros(1, A.STATE_DTYPE)
+        rc = self.lib.orc_state_from_display_str(s.encode(), width, 1 if side == A.DEFENDER else 0, A.ptr(st))
+        return rc, st
+
+    def state_to_fen(self, st, width):
+        buf = C.create_string_buffer(512)
+        assert self.lib.orc_state_to_fen(A.ptr(st), width, buf, C.c_size_t(512)) == 0
+        return buf.value.decode()
+
+    def board_op(self, st, width, op, row=0, col=0, a=0, b=0):
+        out = (C.c_int * 2)()
+        rc = self.lib.orc_board_op(A.ptr(st), width, op, row, col, a, b, out)
+        return rc, (out[0], out[1])
+
+    def iter_occupied(self, st, width, side):
+        buf = np.zeros(2 * 128, np.uint8)
+        n = self.lib.orc_iter_occupied(A.ptr(st), width, 1 if side == A.DEFENDER else 0, A.ptr(buf))
+        return [(int(buf[2 * i]), int(buf[2 * i + 1])) for i in range(n)]
+
+    def play_from_str(self, s):
+        p = A.Play()
+        rc = self.lib.orc_play_from_str(s.encode(), C.byref(p))
+        return rc, p
+
+    def play_to_str(self, p):
+        buf = C.create_string_buffer(64)
+        assert self.lib.orc_play_to_str(C.byref(p), buf, C.c_size_t(64)) == 0
+        return buf.value.decode()
+
+    def tile_from_str(self, s):
+        r, c = C.c_uint8(), C.c_uint8()
+        rc = self.lib.orc_tile_from_str(s.encode(), C.byref(r), C.byref(c))
+        return rc, (r.value, c.value)
+
+    def track_play(self, st, width, side, play, captures):
+        assert self.lib.orc_track_play(A.ptr(st), width, 1 if side == A.DEFENDER else 0, C.byref(play), int(captures)) == 0
+
+    def by_value(self, rules, width):
+        return ByValueImpl(self.lib, "orc_", rules, width)
+
+    def random_playout(self, rules, fen, width, seed, n_games, n_steps, auto_reset=True, game_id_base=0, ply0=0,
+                       n_threads=1, states=None):
+        if states is None:
+            rc, st0 = self.state_from_fen(fen, width, A.DEFENDER if rules.starting_side else A.ATTACKER)
+            assert rc == 0
+            states = np.repeat(st0, n_games)
+        states = np.ascontiguousarray(states)
+        stats = A.Stats()
+        rc = self.lib.orc_random_playout(C.addressof(rules), fen.encode(), width, seed, game_id_base, n_games, ply0,
+                                         n_steps, int(auto_reset), n_threads, states.ctypes.data, C.addressof(stats))
+        assert rc == 0, rc
+        return states, stats
+
+    def mcts_search(self, rules, width, roots, num_sims, cpuct=1.0, draw_value=1e-4, n_threads=1):
+        roots = np.ascontiguousarray(roots)
+        n = len(roots)
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        visits = np.zeros((n, A.MAX_MOVES), np.uint32)
+        q = np.zeros((n, A.MAX_MOVES), np.float64)
+        counts = np.zeros(n, np.uint32)
+        best = np.zeros(n, np.uint32)
+        stats = A.MctsStats()
+        rc = self.lib.orc_mcts_search(C.addressof(rules), width, roots.ctypes.data, n, num_sims, cpuct, draw_value,
+                                      n_threads, moves.ctypes.data, visits.ctypes.data, q.ctypes.data,
+                                      counts.ctypes.data, best.ctypes.data, C.addressof(stats))
+        assert rc == 0, rc
+        return dict(moves=moves, visits=visits, q=q, counts=counts, best=best, stats=stats)
+
+    def hw_threads(self):
+        return self.lib.orc_hw_threads()
+
+
+class HostSim:
+    """ctypes face of tests/hostsim/libhostsim.so (the kernels' math compiled for the CPU)."""
+
+    def __init__(self):
+        self.lib = C.CDLL(build_hostsim())
+        self.lib.sim_random_playout.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_uint32,
+                                                C.c_uint64, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+
+    def by_value(self, rules, width):
+        return ByValueImpl(self.lib, "sim_", rules, width)
+
+    def random_playout(self, rules, start_state, width, seed, n_games, n_steps, auto_reset=True, game_id_base=0, ply0=0,
+                       states=None):
+        if states is None:
+            states = np.repeat(start_state, n_games)
+        states = np.ascontiguousarray(states)
+        start_state = np.ascontiguousarray(start_state)
+        stats = A.Stats()
+        rc = self.lib.sim_random_playout(C.addressof(rules), start_state.ctypes.data, width, seed, game_id_base, n_games,
+                                         ply0, n_steps, int(auto_reset), states.ctypes.data, C.addressof(stats))
+        assert rc == 0, rc
+        return states, stats
+
+    def select_moves(self, rules, width, states, ks):
+        n = len(states)
+        ks = np.ascontiguousarray(ks, np.uint32)
+        moves = np.zeros(n, np.uint16)
+        counts = np.zeros(n, np.uint32)
+        rc = self.lib.sim_select_moves(C.byref(rules), width, A.ptr(states), A.ptr(ks), n, A.ptr(moves), A.ptr(counts))
+        assert rc == 0, rc
+        return moves, counts
+
+
+_ORACLE = None
+_HOSTSIM = None
+
+
+def oracle():
+    global _ORACLE
+    if _ORACLE is None:
+        _ORACLE = Oracle()
+    return _ORACLE
+
+
+def hostsim():
+    global _HOSTSIM
+    if _HOSTSIM is None:
+        _HOSTSIM = HostSim()
+    return _HOSTSIM
