@@ -240,7 +240,7 @@ template <class BB>
 TAFL_HD tafl_play_effects query_captures(const Ctx<BB>& cx, const tafl_state& st, const tafl_play& pl) {
     tafl_play_effects fx;
     fx.captures[0] = fx.captures[1] = 0;
-    fx.status = st.status; fx.err = 0; fx.n_captures = 0;
+    fx.status = 0; fx.err = 0; fx.n_captures = 0;   // status is not part of a capture query
     for (int i = 0; i < 5; ++i) fx._pad[i] = 0;
     Pos<BB> p = load_pos(cx, st);
     const int fr = pl.from_row, fc = pl.from_col, hz = pl.axis == TAFL_HORIZONTAL;
@@ -263,7 +263,7 @@ template <class BB>
 TAFL_HD tafl_play_effects query_shieldwall(const Ctx<BB>& cx, const tafl_state& st, const tafl_play& pl) {
     tafl_play_effects fx;
     fx.captures[0] = fx.captures[1] = 0;
-    fx.status = st.status; fx.err = 0; fx.n_captures = 0xFF;
+    fx.status = 0; fx.err = 0; fx.n_captures = 0xFF;
     for (int i = 0; i < 5; ++i) fx._pad[i] = 0;
     Pos<BB> p = load_pos(cx, st);
     const int fr = pl.from_row, fc = pl.from_col, hz = pl.axis == TAFL_HORIZONTAL;

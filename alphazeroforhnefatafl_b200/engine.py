@@ -1,0 +1,335 @@
+"""Host-side mirror of the reference's game API over the C ABI (``include/tafl.h``).
+
+Names follow the reference crate (paths relative to the reference tree, ``game/``):
+
+* ``preset.rules.COPENHAGEN`` ... / ``preset.boards.COPENHAGEN`` ...   — preset.rs:12-134
+* ``Play``                                                             — play.rs:23-92
+* ``GameLogic`` (by-value batch methods: validate_play, do_play, iter_plays, side_can_play,
+  get_captures, detect_shieldwall, find_enclosure, enclosure_secure, detect_exit_fort)
+                                                                       — game/logic.rs:61-880
+* ``LockstepGames``: ``n_games`` resident ``Game``s advanced together  — game/mod.rs:76-116
+
+Every array argument is a batch: the GPU advances tens of thousands of games per launch.  All
+compute happens in libtafl_b200.so on the device; nothing here re-implements rules on the CPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as A
+from ._lib import TaflError, lib
+
+
+def _check(rc, eng=None):
+    if rc != 0:
+        msg = lib().tafl_last_error(eng).decode() if rc == A.ERR_CUDA or eng else ""
+        raise TaflError(rc, msg)
+
+
+def preset_rules(preset_id):
+    r = A.Rules()
+    _check(lib().tafl_preset_rules(preset_id, C.byref(r)))
+    return r
+
+
+def preset_board(preset_id):
+    p = C.c_char_p()
+    _check(lib().tafl_preset_board_fen(preset_id, C.byref(p)))
+    return p.value.decode()
+
+
+class _Namespace:
+    def __init__(self, fn, names):
+        self._fn, self._names = fn, names
+
+    def __getattr__(self, name):
+        if name in self._names:
+            return self._fn(self._names[name])
+        raise AttributeError(name)
+
+
+class preset:  # noqa: N801  (mirrors the reference module name `preset`)
+    rules = _Namespace(preset_rules, dict(COPENHAGEN=A.PRESET_COPENHAGEN, BRANDUBH=A.PRESET_BRANDUBH,
+                                          MAGPIE=A.PRESET_MAGPIE, TABLUT=A.PRESET_TABLUT, KOCH=A.PRESET_KOCH))
+    boards = _Namespace(preset_board, dict(COPENHAGEN=A.PRESET_COPENHAGEN, BRANDUBH=A.PRESET_BRANDUBH,
+                                           MAGPIE=A.PRESET_MAGPIE, TABLUT=A.PRESET_TABLUT))
+
+
+def state_from_fen(fen, width=0, side=A.ATTACKER):
+    """``GameState::new(fen, side)`` (game/state.rs:136-145) -> 1-element STATE_DTYPE array."""
+    if width == 0:
+        width = A.width_for(_fen_width(fen))
+    st = np.zeros(1, A.STATE_DTYPE)
+    _check(lib().tafl_state_from_fen(fen.encode(), width, side, A.ptr(st)))
+    return st
+
+
+def _fen_width(fen):
+    n, num = 0, ""
+    for ch in fen.split("/")[0]:
+        if ch.isdigit():
+            num += ch
+        else:
+            n += int(num) if num else 0
+            num = ""
+            n += 1
+    return n + (int(num) if num else 0)
+
+
+def state_to_fen(st, width):
+    buf = C.create_string_buffer(512)
+    _check(lib().tafl_state_to_fen(A.ptr(np.ascontiguousarray(st)), width, buf, 512))
+    return buf.value.decode()
+
+
+def play_from_str(s):
+    p = A.Play()
+    _check(lib().tafl_play_from_str(s.encode(), C.byref(p)))
+    return p
+
+
+def play_to_str(p):
+    buf = C.create_string_buffer(64)
+    _check(lib().tafl_play_to_str(C.byref(p), buf, 64))
+    return buf.value.decode()
+
+
+def plays_array(plays):
+    """list of A.Play / (from_row, from_col, axis, disp) tuples -> PLAY_DTYPE array"""
+    out = np.zeros(len(plays), A.PLAY_DTYPE)
+    for i, p in enumerate(plays):
+        if isinstance(p, A.Play):
+            out[i] = (p.from_row, p.from_col, p.axis, p.disp)
+        else:
+            out[i] = tuple(p)
+    return out
+
+
+def moves_to_plays(moves, width):
+    """compact tafl_move array -> PLAY_DTYPE array (Play::from_tiles, play.rs:36-49)"""
+    moves = np.asarray(moves, np.uint16)
+    s = A.stride_for(width)
+    f, t = (moves & 127).astype(np.int32), ((moves >> 7) & 127).astype(np.int32)
+    fr, fc, tr, tc = f // s, f % s, t // s, t % s
+    out = np.zeros(moves.shape, A.PLAY_DTYPE)
+    hz = fr == tr
+    out["from_row"], out["from_col"] = fr, fc
+    out["axis"] = np.where(hz, A.HORIZONTAL, A.VERTICAL)
+    out["disp"] = np.where(hz, tc - fc, tr - fr)
+    return out
+
+
+class LockstepGames:
+    """``n_games`` resident games on one GPU, advanced in lockstep (Game, game/mod.rs:76-116)."""
+
+    def __init__(self, rules, start_fen, n_games, device=0, width=0):
+        self._h = C.c_void_p()
+        self.rules = rules
+        rc = lib().tafl_engine_create(C.byref(rules), start_fen.encode(), width, n_games, device, C.byref(self._h))
+        if rc != 0:
+            raise TaflError(rc, lib().tafl_last_error(None).decode())
+        n, w, sl, dev, sm = C.c_uint32(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _check(lib().tafl_engine_info(self._h, C.byref(n), C.byref(w), C.byref(sl), C.byref(dev), C.byref(sm)))
+        self.n_games, self.width, self.side_len, self.device, self.sm_count = n.value, w.value, sl.value, dev.value, sm.value
+        self.start_fen = start_fen
+
+    # -- lifetime -------------------------------------------------------------------------------
+    def close(self):
+        if self._h:
+            lib().tafl_engine_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        _check(rc, self._h)
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def stream(self):
+        return lib().tafl_engine_stream(self._h)
+
+    @property
+    def launches(self):
+        return int(lib().tafl_launch_count(self._h))
+
+    def sync(self):
+        self._ck(lib().tafl_engine_sync(self._h))
+
+    # -- resident state -------------------------------------------------------------------------
+    def reset(self, game_ids=None):
+        if game_ids is None:
+            self._ck(lib().tafl_reset(self._h, None, 0))
+        else:
+            ids = np.ascontiguousarray(game_ids, np.uint32)
+            self._ck(lib().tafl_reset(self._h, A.ptr(ids), len(ids)))
+
+    def get_states(self, first=0, n=None):
+        n = self.n_games - first if n is None else n
+        out = np.zeros(n, A.STATE_DTYPE)
+        self._ck(lib().tafl_get_states(self._h, A.ptr(out), first, n))
+        return out
+
+    def set_states(self, states, first=0):
+        states = np.ascontiguousarray(states, A.STATE_DTYPE)
+        self._ck(lib().tafl_set_states(self._h, A.ptr(states), first, len(states)))
+
+    def states_device_ptr(self):
+        return lib().tafl_states_device(self._h)
+
+    # -- legal moves (get_all_possible_moves, game/main.rs:33-43) ---------------------------------
+    def legal_moves(self, first=0, n=None):
+        n = self.n_games - first if n is None else n
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        counts = np.zeros(n, np.uint32)
+        self._ck(lib().tafl_legal_moves_host(self._h, A.ptr(moves), A.ptr(counts), first, n))
+        return moves, counts
+
+    def legal_moves_device(self):
+        """enqueue movegen into the engine-owned device buffers; returns (d_moves, d_counts) pointers"""
+        self._ck(lib().tafl_legal_moves(self._h, None, None))
+        dm, dc = C.c_void_p(), C.c_void_p()
+        self._ck(lib().tafl_moves_device(self._h, C.byref(dm), C.byref(dc)))
+        return dm.value, dc.value
+
+    # -- stepping -------------------------------------------------------------------------------
+    def step(self, plays, want_effects=True):
+        """Game::do_play for every resident game; plays is a PLAY_DTYPE array [n_games]."""
+        plays = np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        assert len(plays) == self.n_games
+        fx = np.zeros(self.n_games, A.EFFECTS_DTYPE) if want_effects else None
+        self._ck(lib().tafl_step(self._h, A.ptr(plays), A.ptr(fx) if want_effects else None))
+        return fx
+
+    def step_random(self, seed, n_steps, auto_reset=True, steps_per_launch=1, sync=True):
+        fn = lib().tafl_step_random if sync else lib().tafl_step_random_async
+        self._ck(fn(self._h, seed, n_steps, int(auto_reset), steps_per_launch))
+
+    def set_game_id_base(self, v):
+        self._ck(lib().tafl_set_game_id_base(self._h, v))
+
+    def set_random_ply(self, v):
+        self._ck(lib().tafl_set_random_ply(self._h, v))
+
+    @property
+    def random_ply(self):
+        return int(lib().tafl_random_ply(self._h))
+
+    def stats_reset(self):
+        self._ck(lib().tafl_stats_reset(self._h))
+
+    def stats(self):
+        s = A.Stats()
+        self._ck(lib().tafl_stats_get(self._h, C.byref(s)))
+        return s
+
+    # -- MCTS (src/mcts.py) -----------------------------------------------------------------------
+    def mcts_configure(self, num_sims, cpuct=1.0, draw_value=1e-4, edge_capacity=0):
+        cfg = A.MctsConfig(num_sims=num_sims, cpuct=cpuct, draw_value=draw_value, edge_capacity=edge_capacity)
+        self._ck(lib().tafl_mcts_configure(self._h, C.byref(cfg)))
+
+    def mcts_search(self, sync=True):
+        self._ck((lib().tafl_mcts_search if sync else lib().tafl_mcts_search_async)(self._h))
+
+    def mcts_results(self, first=0, n=None):
+        n = self.n_games - first if n is None else n
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        visits = np.zeros((n, A.MAX_MOVES), np.uint32)
+        q = np.zeros((n, A.MAX_MOVES), np.float64)
+        counts = np.zeros(n, np.uint32)
+        best = np.zeros(n, np.uint32)
+        self._ck(lib().tafl_mcts_results_host(self._h, first, n, A.ptr(moves), A.ptr(visits), A.ptr(q), A.ptr(counts),
+                                              A.ptr(best)))
+        return dict(moves=moves, visits=visits, q=q, counts=counts, best=best)
+
+    def mcts_play_best(self, want_status=True):
+        st = np.zeros(self.n_games, np.uint8) if want_status else None
+        self._ck(lib().tafl_mcts_play_best(self._h, A.ptr(st) if want_status else None))
+        return st
+
+    def mcts_stats(self):
+        s = A.MctsStats()
+        self._ck(lib().tafl_mcts_stats_get(self._h, C.byref(s)))
+        return s
+
+    def pack_records(self, d_out):
+        self._ck(lib().tafl_pack_records(self._h, d_out))
+
+    # -- GameLogic by-value batch API (logic.rs) --------------------------------------------------
+    def validate_play(self, states, plays):
+        states, plays = np.ascontiguousarray(states, A.STATE_DTYPE), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_validate_plays(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(out)))
+        return out
+
+    def do_play(self, states, plays):
+        states, plays = np.ascontiguousarray(states, A.STATE_DTYPE), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        out = np.zeros(len(states), A.STATE_DTYPE)
+        fx = np.zeros(len(states), A.EFFECTS_DTYPE)
+        self._ck(lib().tafl_do_plays(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(out), A.ptr(fx)))
+        return out, fx
+
+    def legal_moves_of(self, states):
+        states = np.ascontiguousarray(states, A.STATE_DTYPE)
+        moves = np.zeros((len(states), A.MAX_MOVES), np.uint16)
+        counts = np.zeros(len(states), np.uint32)
+        self._ck(lib().tafl_legal_moves_of(self._h, A.ptr(states), len(states), A.ptr(moves), A.ptr(counts)))
+        return moves, counts
+
+    def iter_plays(self, states, tiles_rc):
+        states = np.ascontiguousarray(states, A.STATE_DTYPE)
+        tiles_rc = np.ascontiguousarray(tiles_rc, np.uint8)
+        moves = np.zeros((len(states), 32), np.uint16)
+        counts = np.zeros(len(states), np.int32)
+        self._ck(lib().tafl_piece_plays(self._h, A.ptr(states), A.ptr(tiles_rc), len(states), A.ptr(moves), A.ptr(counts)))
+        return moves, counts
+
+    def get_captures(self, states, plays):
+        states, plays = np.ascontiguousarray(states, A.STATE_DTYPE), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        fx = np.zeros(len(states), A.EFFECTS_DTYPE)
+        self._ck(lib().tafl_get_captures(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(fx)))
+        return fx
+
+    def detect_shieldwall(self, states, plays):
+        states, plays = np.ascontiguousarray(states, A.STATE_DTYPE), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        fx = np.zeros(len(states), A.EFFECTS_DTYPE)
+        self._ck(lib().tafl_detect_shieldwall(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(fx)))
+        return fx
+
+    def find_enclosure(self, states, queries):
+        states, queries = np.ascontiguousarray(states, A.STATE_DTYPE), np.ascontiguousarray(queries, A.ENCL_QUERY_DTYPE)
+        out = np.zeros(len(states), A.ENCLOSURE_DTYPE)
+        self._ck(lib().tafl_find_enclosure(self._h, A.ptr(states), A.ptr(queries), len(states), A.ptr(out)))
+        return out
+
+    def enclosure_secure(self, states, queries):
+        states, queries = np.ascontiguousarray(states, A.STATE_DTYPE), np.ascontiguousarray(queries, A.ENCL_QUERY_DTYPE)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_enclosure_secure(self._h, A.ptr(states), A.ptr(queries), len(states), A.ptr(out)))
+        return out
+
+    def detect_exit_fort(self, states):
+        states = np.ascontiguousarray(states, A.STATE_DTYPE)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_detect_exit_fort(self._h, A.ptr(states), len(states), A.ptr(out)))
+        return out
+
+    def side_can_play(self, states, sides):
+        states = np.ascontiguousarray(states, A.STATE_DTYPE)
+        sides = np.ascontiguousarray(sides, np.uint8)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_side_can_play(self._h, A.ptr(states), A.ptr(sides), len(states), A.ptr(out)))
+        return out

@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py — Copenhagen 11x11 env steps/s (BASELINE.json configs[1]: 65 536 lockstep games of
+random legal play on one B200) plus MCTS simulations/s, through libtafl_b200.so.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One bench "step" = `--plies` lockstep plies of all resident games (default 64 launches of the
+fused step kernel, the state round-trips HBM after every ply); the L2 is flushed between timed
+steps.  Prints ONE JSON line (see DESIGN.md §measurement for every field).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ENV_BYTES_PER_STEP = 136          # 64 B state read + 64 B state write + 4 B action + 4 B status
+METRIC, UNIT = "copenhagen_11x11_env_steps_per_s", "env steps/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--games", type=int, default=65536)
+    ap.add_argument("--plies", type=int, default=64, help="lockstep plies per bench step")
+    ap.add_argument("--seed", type=int, default=20261104)
+    ap.add_argument("--no-mcts", action="store_true")
+    ap.add_argument("--mcts-games", type=int, default=4096)
+    ap.add_argument("--mcts-sims", type=int, default=800)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", d
+    return 6650.0, "fallback (B200_PROFILING.md)", {}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (C++ restatement of the reference crate; the Rust crate itself cannot be
+# built in this image) on the host cores, one game per thread.
+# ------------------------------------------------------------------------------------------------
+def oracle_handle():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_ffi
+    return oracle_ffi.oracle()
+
+
+def cpu_playout_rate(orc, seconds, seed, plies):
+    """steps/s of the oracle random-playout loop with every host thread busy, on a bounded sample."""
+    from alphazeroforhnefatafl_b200 import _abi as A
+    cores = max(1, orc.hw_threads())
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    games = cores * 8
+    st, _ = orc.random_playout(rules, fen, 128, seed, games, 16, n_threads=cores)   # warm
+    steps = 0
+    t0 = time.perf_counter()
+    ply = 16
+    while True:
+        st, stats = orc.random_playout(rules, fen, 128, seed, games, plies, ply0=ply, n_threads=cores, states=st)
+        steps += stats.steps
+        ply += plies
+        el = time.perf_counter() - t0
+        if el >= seconds:
+            break
+    return steps / el, cores, "%d games x %d plies (auto-reset), %d threads, %.1f s" % (games, ply - 16, cores, el)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from alphazeroforhnefatafl_b200 import _abi as A
+    orc = oracle_handle()
+    cores = max(1, orc.hw_threads())
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    # each step is a bounded sample of the 65 536-game workload: `games` games x `plies` plies
+    games = cores * 4
+    budget = 150.0 / max(1, args.steps + args.warmup)
+    st, _ = orc.random_playout(rules, fen, 128, args.seed, games, 8, n_threads=cores)
+    t0 = time.perf_counter()
+    st, s0 = orc.random_playout(rules, fen, 128, args.seed, games, 32, ply0=8, n_threads=cores, states=st)
+    rate = s0.steps / (time.perf_counter() - t0)
+    plies = int(max(1, min(args.plies, rate * min(budget, 0.5) / games)))
+    ply = 40
+    for _ in range(args.warmup):
+        st, _ = orc.random_playout(rules, fen, 128, args.seed, games, plies, ply0=ply, n_threads=cores, states=st)
+        ply += plies
+    total = 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        st, s = orc.random_playout(rules, fen, 128, args.seed, games, plies, ply0=ply, n_threads=cores, states=st)
+        total += s.steps
+        ply += plies
+    el = time.perf_counter() - t0
+    v = total / el
+    sample = "%d games x %d plies per step (sample of the 65536-game workload), %d threads" % (games, plies, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * el / max(1, args.steps), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u128 bitboards (2 x u64)", "data": "synthetic",
+        "config": {"workload": "Copenhagen 11x11 random-play env stepping (BASELINE configs[1]), CPU oracle port of "
+                               "the reference crate (Rust toolchain unavailable)", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (NVML): SM clock + throttle reasons during the timed region
+# ------------------------------------------------------------------------------------------------
+class Clocks(threading.Thread):
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake", 0x2: "applications_clocks_setting", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+        self.power = []
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        while not self.stop_flag:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                self.power.append(self.nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                r = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "power_w_max": max(self.power) if self.power else None, "samples": len(s)}
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from alphazeroforhnefatafl_b200 import _abi as A
+    from alphazeroforhnefatafl_b200 import engine as E
+    from alphazeroforhnefatafl_b200._lib import lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — libtafl_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    hbm_peak, peak_src, _ = peaks()
+    n, P = args.games, args.plies
+    rules, fen = E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN
+    g = E.LockstepGames(rules, fen, n, local, 128)
+    g.set_game_id_base(rank * n)           # games shard by id range; no data-path collective
+    stream = torch.cuda.ExternalStream(g.stream, device=local)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")    # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step():
+        g.step_random(args.seed, P, auto_reset=True, steps_per_launch=1, sync=False)
+
+    with torch.cuda.stream(stream):
+        for _ in range(max(3, args.warmup)):
+            flush.zero_()
+            one_step()
+        barrier()
+        g.stats_reset()
+        clk = Clocks(local)
+        clk.start()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        l0 = g.launches
+        barrier()
+        t_wall0 = time.perf_counter()
+        for a, b in evs:
+            flush.zero_()                  # L2 flush between timed iterations (not inside the events)
+            a.record(stream)
+            one_step()
+            b.record(stream)
+        barrier()
+        t_wall = time.perf_counter() - t_wall0
+        launches = g.launches - l0
+        clk.stop_flag = True
+        clk.join()
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    stats = g.stats()
+    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+    steps_done = torch.tensor([stats.steps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(steps_done, op=dist.ReduceOp.SUM)
+    dev_ms_max, total_steps = float(t.item()), float(steps_done.item())
+    value = total_steps / (dev_ms_max * 1e-3)
+    kernel_us = 1e3 * dev_ms / max(1, args.steps * P)          # average launch duration (this rank)
+    achieved = ENV_BYTES_PER_STEP * n / (kernel_us * 1e-6) / 1e9
+    mean_legal = stats.legal_moves / max(1, stats.steps)
+
+    # ---- e2e: GameLogic::do_play-style by-value stepping through the C ABI with HOST buffers ----
+    # every step: H2D of the 64-byte states from pinned memory, one fused ply on the device, D2H of
+    # the successor states (which carry the status byte).
+    h_in = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
+    g.sync()
+    h_in.numpy()[:] = np.frombuffer(g.get_states().tobytes(), np.uint8)
+    L = lib()
+    e2e_steps = max(10, min(args.steps, 200))
+
+    def e2e_step():
+        L.tafl_set_states(g.handle, h_in.data_ptr(), 0, n)
+        L.tafl_step_random(g.handle, args.seed, 1, 1, 1)
+        L.tafl_get_states(g.handle, h_out.data_ptr(), 0, n)
+
+    for _ in range(3):
+        e2e_step()
+    g.stats_reset()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+        h_in, h_out = h_out, h_in
+    barrier()
+    e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    e2e_n = torch.tensor([float(g.stats().steps)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e2e_n, op=dist.ReduceOp.SUM)
+    e2e_value = float(e2e_n.item()) / float(e2e_t.item())
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_ms_max / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u128 bitboards (2 x u64)", "data": "synthetic",
+        "config": {"workload": "Copenhagen 11x11 random-play env stepping, %d lockstep games per GPU (BASELINE configs[1])" % n,
+                   "games_per_gpu": n, "plies_per_step": P, "steps_per_launch": 1, "auto_reset": True,
+                   "l2": "flushed between timed iterations (256 MiB memset, outside the events)",
+                   "sharding": "game-id ranges, no data-path collective", "mean_legal_moves": mean_legal},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                     "traffic": ncu_traffic(), "peak_source": peak_src, "kernel": "k_step_random<BB128>",
+                     "kernel_us": kernel_us, "bytes_per_env_step": ENV_BYTES_PER_STEP,
+                     "note": "integer-issue bound, not HBM bound: see profiles/ for issue-slot utilisation"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 64, "d2h_bytes_per_step": n * 64,
+                "api": "tafl_set_states + tafl_step_random(1 ply) + tafl_get_states, pinned host buffers",
+                "steps": e2e_steps},
+        "gpu_launches": int(launches),
+        "clocks": clk.summary(),
+        "wall_s_timed_region": t_wall,
+    }
+    if not args.no_mcts:
+        try:
+            out["mcts"] = bench_mcts(args, E, rank, world, local, barrier, dist if world > 1 else None, torch)
+        except Exception as ex:  # the env-step line must survive an MCTS failure, loudly
+            out["mcts"] = {"error": repr(ex)}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, cores, sample = cpu_playout_rate(oracle_handle(), args.cpu_seconds, args.seed, 64)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+    g.close()
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def ncu_traffic():
+    p = os.path.join(ROOT, "profiles", "ncu_summary.json")
+    if os.path.exists(p):
+        try:
+            with open(p) as f:
+                return json.load(f).get("k_step_random", {}).get("dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
+    """Copenhagen MCTS, 800 sims/move, stub evaluator, 4096 trees per GPU (BASELINE configs[2])."""
+    n = args.mcts_games
+    g = E.LockstepGames(E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN, n, local, 128)
+    g.set_game_id_base(rank * n)
+    g.step_random(args.seed, 20, auto_reset=True)          # start the trees from 20-ply positions
+    g.mcts_configure(args.mcts_sims, 1.0)
+    stream = torch.cuda.ExternalStream(g.stream, device=local)
+    moves = 3
+    with torch.cuda.stream(stream):
+        g.mcts_search()                                    # warm-up move
+        g.mcts_play_best(False)
+        s0 = g.mcts_stats().as_dict()
+        l0 = g.launches
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a.record(stream)
+        for _ in range(moves):
+            g.mcts_search(sync=False)
+            g.mcts_play_best(False)
+        b.record(stream)
+        barrier()
+    ms = a.elapsed_time(b)
+    s1 = g.mcts_stats().as_dict()
+    sims = s1["sims"] - s0["sims"]
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    c = torch.tensor([float(sims)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    nodes, depth, edges = s1["nodes"] - s0["nodes"], s1["depth_sum"] - s0["depth_sum"], s1["edges"] - s0["edges"]
+    d_bar, l_bar = depth / max(1, sims), edges / max(1, nodes)
+    b_sim = d_bar * (16 + 12 * l_bar) + (144 + 18 * l_bar) + 32 * d_bar
+    v = float(c.item()) / (float(t.item()) * 1e-3)
+    hbm_peak, _, _ = peaks()
+    res = {"metric": "copenhagen_11x11_mcts_sims_per_s", "value": v, "unit": "sims/s", "trees_per_gpu": n,
+           "sims_per_move": args.mcts_sims, "moves_timed": moves, "ms_per_move": float(t.item()) / moves,
+           "mean_depth": d_bar, "mean_edges_per_node": l_bar, "bytes_per_sim_model": b_sim,
+           "roofline": {"bound": "hbm", "achieved": v / world * b_sim / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": v / world * b_sim / 1e9 / hbm_peak},
+           "gpu_launches": int(g.launches - l0)}
+    g.close()
+    return res
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -275,3 +275,26 @@ def hostsim():
     if _HOSTSIM is None:
         _HOSTSIM = HostSim()
     return _HOSTSIM
+
+
+class OracleHost:
+    """Text/board helpers for tests/kat_runner.py, served by the oracle."""
+
+    def __init__(self):
+        self.o = oracle()
+
+    def preset_rules(self, pid):
+        return self.o.preset_rules(pid)
+
+    def preset_board(self, pid):
+        return self.o.preset_board(pid)
+
+    def state_from_fen(self, fen, width, side):
+        return self.o.state_from_fen(fen, width, side)
+
+    def move_piece(self, st, width, frm, to):
+        rc, _ = self.o.board_op(st, width, 6, frm[0], frm[1], to[0], to[1])
+        assert rc == 0, rc
+
+    def play_from_str(self, s):
+        return self.o.play_from_str(s)

@@ -1,0 +1,164 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against the
+CPU oracle on the same seeded inputs, against the committed golden vectors, and — at the
+BASELINE.json sizes — through size-independent properties.  Bit-exact: this is integer work."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import kat_runner
+from alphazeroforhnefatafl_b200 import _abi as A
+from alphazeroforhnefatafl_b200 import engine as E
+from parity_cases import PRESET_CONFIGS, board_for, compare_by_value, random_boards, sample_positions
+from product_host import GpuImplFactory, ProductHost
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def gpu(built_lib):
+    f = GpuImplFactory(0)
+    yield f
+    f.close()
+
+
+def test_gpu_reference_kats(gpu):
+    """The reference's own unit tests (golden/reference_kats.json) through the CUDA path."""
+    n = kat_runner.run_all(ProductHost(), gpu)
+    assert n >= 150
+
+
+def test_gpu_golden_playouts(built_lib):
+    """Committed oracle playout vectors: end states (sha256) and statistics."""
+    with open(os.path.join(GOLDEN, "playout_vectors.json")) as f:
+        vectors = json.load(f)["vectors"]
+    for v in vectors:
+        rules = E.preset_rules(v["preset"])
+        fen = E.preset_board(A.PRESET_BRANDUBH if v["preset"] == A.PRESET_KOCH else v["preset"])
+        with E.LockstepGames(rules, fen, v["n_games"], 0, v["width"]) as g:
+            g.set_game_id_base(v["game_id_base"])
+            g.step_random(v["seed"], v["n_steps"], auto_reset=v["auto_reset"], steps_per_launch=1)
+            st = g.get_states()
+            assert hashlib.sha256(st.tobytes()).hexdigest() == v["states_sha256"], v["name"]
+            assert [st[i].tobytes().hex() for i in range(2)] == v["first_states_hex"]
+            assert g.stats().as_dict() == v["stats"], v["name"]
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS)
+def test_gpu_random_playouts_vs_oracle(orc, built_lib, name, preset, width):
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    for seed, n_games, n_steps, auto_reset, spl in ((41, 300, 500, True, 1), (42, 257, 333, False, 7), (43, 64, 900, True, 64)):
+        so, so_stats = orc.random_playout(rules, fen, width, seed, n_games, n_steps, auto_reset=auto_reset,
+                                          game_id_base=1000, n_threads=8)
+        with E.LockstepGames(rules, fen, n_games, 0, width) as g:
+            g.set_game_id_base(1000)
+            g.step_random(seed, n_steps, auto_reset=auto_reset, steps_per_launch=spl)
+            assert g.get_states().tobytes() == so.tobytes(), (name, seed)
+            assert g.stats().as_dict() == so_stats.as_dict(), (name, seed)
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS)
+def test_gpu_by_value_vs_oracle(orc, gpu, name, preset, width):
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    N = len(fen.split("/"))
+    rng = np.random.default_rng(1234)
+    states = np.concatenate([sample_positions(orc, rules, fen, width, 128, seed=51),
+                             random_boards(orc, rng, N, width, 800)])
+    compare_by_value(orc.by_value(rules, width), gpu(rules, width, N), states, width, rng)
+
+
+def test_gpu_rule_variants_vs_oracle(orc, gpu):
+    rng = np.random.default_rng(321)
+    base = orc.preset_rules(A.PRESET_COPENHAGEN)
+    sets = [0, 0xFFFF, A.pieceset_type(A.KING), A.pieceset_type(A.SOLDIER), A.pieceset_side(A.ATTACKER),
+            A.pieceset_side(A.DEFENDER)]
+    for trial in range(12):
+        r = base.copy(
+            throne_movement=int(rng.integers(0, 5)), king_strength=int(rng.integers(0, 3)),
+            king_attack=int(rng.integers(0, 3)), edge_escape=int(rng.integers(0, 2)),
+            shieldwall_enabled=int(rng.integers(0, 2)), sw_corners_may_close=int(rng.integers(0, 2)),
+            sw_captures=int(rng.choice(sets)), exit_fort=int(rng.integers(0, 2)),
+            may_enter_corners=int(rng.choice(sets)), hostility_throne=int(rng.choice(sets)),
+            hostility_corners=int(rng.choice(sets)), hostility_edge=int(rng.choice(sets)),
+            slow_pieces=int(rng.choice([0, 0, A.pieceset_type(A.KING), 0xFFFF])),
+            enclosure_win=int(rng.integers(0, 3)), repetition_enabled=int(rng.integers(0, 2)),
+            repetition_is_loss=int(rng.integers(0, 2)), draw_on_no_plays=int(rng.integers(0, 2)),
+            linnaean_capture=int(rng.integers(0, 2)), n_repetitions=int(rng.integers(1, 4)))
+        N, width = [(7, 64), (9, 128), (11, 128), (7, 128)][trial % 4]
+        states = random_boards(orc, rng, N, width, 200)
+        compare_by_value(orc.by_value(r, width), gpu(r, width, N), states, width, rng)
+
+
+def test_gpu_resident_legal_moves_and_step(orc, built_lib):
+    """tafl_legal_moves_host + tafl_step (Game::do_play with validation) on resident games, driven
+    move by move from the host, against the oracle's do_play."""
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    n = 96
+    rng = np.random.default_rng(8)
+    ref = orc.by_value(rules, 128)
+    with E.LockstepGames(rules, fen, n, 0, 128) as g:
+        states = g.get_states()
+        for ply in range(40):
+            moves, counts = g.legal_moves()
+            mr, cr = ref.legal_moves_of(states)
+            assert np.array_equal(counts, cr)
+            pick = (rng.integers(0, 1 << 30, n) % np.maximum(counts, 1)).astype(np.int64)
+            chosen = moves[np.arange(n), pick]
+            plays = E.moves_to_plays(chosen, 128)
+            if ply % 5 == 4:   # inject an illegal play: the game must stay unchanged
+                plays[0] = (0, 0, A.VERTICAL, 1)
+            fx = g.step(plays)
+            exp_states, exp_fx = ref.do_plays(states, plays)
+            assert fx.tobytes() == exp_fx.tobytes()
+            states = g.get_states()
+            assert states.tobytes() == exp_states.tobytes()
+
+
+def test_gpu_reset_and_set_states(orc, built_lib):
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
+    with E.LockstepGames(rules, fen, 50, 0, 64) as g:
+        start = g.get_states()
+        g.step_random(1, 30)
+        moved = g.get_states()
+        assert moved.tobytes() != start.tobytes()
+        g.reset([3, 7])
+        st = g.get_states()
+        assert st[3].tobytes() == start[3].tobytes() and st[7].tobytes() == start[7].tobytes()
+        assert st[4].tobytes() == moved[4].tobytes()
+        g.set_states(moved[10:20], first=0)
+        assert g.get_states(0, 10).tobytes() == moved[10:20].tobytes()
+        g.reset()
+        assert g.get_states().tobytes() == start.tobytes()
+
+
+def test_gpu_full_size_properties(orc, built_lib):
+    """BASELINE config 2 size (65 536 Copenhagen games): size-independent properties.
+    (1) sharding: game ids [0, n) on one engine == two engines over disjoint id ranges;
+    (2) steps_per_launch does not change results; (3) the first 64 games equal the oracle;
+    (4) conservation: steps == n_games * n_steps under auto-reset; checksum is reproducible."""
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    n, steps, seed = 65536, 200, 2024
+    with E.LockstepGames(rules, fen, n, 0, 128) as g:
+        g.step_random(seed, steps, steps_per_launch=1)
+        full = g.get_states()
+        s_full = g.stats()
+        assert s_full.steps == n * steps
+        g.reset(); g.stats_reset(); g.set_random_ply(0)
+        g.step_random(seed, steps, steps_per_launch=8)
+        assert g.get_states().tobytes() == full.tobytes()
+        assert g.stats().state_checksum == s_full.state_checksum
+    half = n // 2
+    parts = []
+    for base in (0, half):
+        with E.LockstepGames(rules, fen, half, 0, 128) as g:
+            g.set_game_id_base(base)
+            g.step_random(seed, steps, steps_per_launch=4)
+            parts.append(g.get_states())
+    assert np.concatenate(parts).tobytes() == full.tobytes()
+    so, _ = orc.random_playout(rules, fen, 128, seed, 64, steps, n_threads=8)
+    assert so.tobytes() == full[:64].tobytes()
+    so, _ = orc.random_playout(rules, fen, 128, seed, 32, steps, game_id_base=n - 32, n_threads=8)
+    assert so.tobytes() == full[n - 32:].tobytes()

@@ -1,0 +1,93 @@
+"""CPU differential tests: the kernels' __host__ __device__ game logic (csrc/tafl_core.cuh,
+tafl_select.cuh) compiled with g++ (tests/hostsim) against the oracle.  This is how the device
+math is checked on a machine without a GPU; the GPU tests repeat the same comparisons through
+the C ABI."""
+import numpy as np
+import pytest
+
+import kat_runner
+import oracle_ffi as F
+from alphazeroforhnefatafl_b200 import _abi as A
+from parity_cases import PRESET_CONFIGS, board_for, compare_by_value, random_boards, sample_positions
+
+
+def test_hostsim_reference_kats(orc, sim):
+    n = kat_runner.run_all(F.OracleHost(), lambda rules, width, side_len: sim.by_value(rules, width))
+    assert n >= 150
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS)
+def test_hostsim_random_playouts(orc, sim, name, preset, width):
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    rc, st0 = orc.state_from_fen(fen, width, A.ATTACKER)
+    for seed, n_games, n_steps, auto_reset in ((11, 96, 700, True), (12, 64, 500, False)):
+        so, so_stats = orc.random_playout(rules, fen, width, seed, n_games, n_steps, auto_reset=auto_reset, n_threads=8)
+        sh, sh_stats = sim.random_playout(rules, st0, width, seed, n_games, n_steps, auto_reset=auto_reset)
+        assert so.tobytes() == sh.tobytes()
+        assert so_stats.as_dict() == sh_stats.as_dict()
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS)
+def test_hostsim_by_value_on_played_positions(orc, sim, name, preset, width):
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    states = sample_positions(orc, rules, fen, width, 160, seed=21)
+    rng = np.random.default_rng(5)
+    assert compare_by_value(orc.by_value(rules, width), sim.by_value(rules, width), states, width, rng) > 0
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS)
+def test_hostsim_by_value_on_synthetic_boards(orc, sim, name, preset, width):
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    N = len(fen.split("/"))
+    rng = np.random.default_rng(77)
+    states = random_boards(orc, rng, N, width, 600)
+    compare_by_value(orc.by_value(rules, width), sim.by_value(rules, width), states, width, rng)
+
+
+def test_hostsim_rule_variants_on_synthetic_boards(orc, sim):
+    """Non-preset Ruleset combinations: throne rules, king strength/attack, hostile
+    edges, slow pieces, enclosure/edge-escape/shield-wall variants."""
+    rng = np.random.default_rng(123)
+    base = orc.preset_rules(A.PRESET_COPENHAGEN)
+    sets = [0, 0xFFFF, A.pieceset_type(A.KING), A.pieceset_type(A.SOLDIER), A.pieceset_side(A.ATTACKER),
+            A.pieceset_side(A.DEFENDER)]
+    for trial in range(24):
+        r = base.copy(
+            throne_movement=int(rng.integers(0, 5)), king_strength=int(rng.integers(0, 3)),
+            king_attack=int(rng.integers(0, 3)), edge_escape=int(rng.integers(0, 2)),
+            shieldwall_enabled=int(rng.integers(0, 2)), sw_corners_may_close=int(rng.integers(0, 2)),
+            sw_captures=int(rng.choice(sets)), exit_fort=int(rng.integers(0, 2)),
+            may_enter_corners=int(rng.choice(sets)), hostility_throne=int(rng.choice(sets)),
+            hostility_corners=int(rng.choice(sets)), hostility_edge=int(rng.choice(sets)),
+            slow_pieces=int(rng.choice([0, 0, A.pieceset_type(A.KING), 0xFFFF])),
+            enclosure_win=int(rng.integers(0, 3)), repetition_enabled=int(rng.integers(0, 2)),
+            repetition_is_loss=int(rng.integers(0, 2)), draw_on_no_plays=int(rng.integers(0, 2)),
+            linnaean_capture=int(rng.integers(0, 2)), n_repetitions=int(rng.integers(1, 4)))
+        N, width = [(7, 64), (9, 128), (11, 128), (7, 128)][trial % 4]
+        states = random_boards(orc, rng, N, width, 120)
+        compare_by_value(orc.by_value(r, width), sim.by_value(r, width), states, width, rng)
+        # and whole random games under these rules
+        fen = orc.preset_board({7: A.PRESET_BRANDUBH, 9: A.PRESET_TABLUT, 11: A.PRESET_COPENHAGEN}[N])
+        rc, st0 = orc.state_from_fen(fen, width, A.DEFENDER if r.starting_side else A.ATTACKER)
+        so, so_stats = orc.random_playout(r, fen, width, trial, 24, 300, n_threads=8)
+        sh, sh_stats = sim.random_playout(r, st0, width, trial, 24, 300)
+        assert so.tobytes() == sh.tobytes(), trial
+        assert so_stats.as_dict() == sh_stats.as_dict()
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS[:3])
+def test_hostsim_select_kth_move(orc, sim, name, preset, width):
+    """The bit-sliced count/select (tafl_select.cuh) returns exactly the k-th entry of the
+    canonical move list (game/main.rs:33-43 order)."""
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    states = sample_positions(orc, rules, fen, width, 200, seed=31)
+    states = states[states["status"] == 0]
+    moves, counts = orc.by_value(rules, width).legal_moves_of(states)
+    rng = np.random.default_rng(9)
+    for rep in range(6):
+        ks = rng.integers(0, 1 << 30, len(states)).astype(np.uint32)
+        got, got_counts = sim.select_moves(rules, width, states, ks)
+        assert np.array_equal(got_counts, counts)
+        nz = counts > 0
+        exp = moves[np.arange(len(states))[nz], (ks[nz] % counts[nz])]
+        assert np.array_equal(got[nz], exp)
