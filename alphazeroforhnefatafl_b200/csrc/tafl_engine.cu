@@ -17,14 +17,23 @@ namespace {
 
 constexpr int STEP_BLOCK = 64;   // threads per CTA for the per-game kernels
 
-__global__ void k_fill_states(tafl_state* __restrict__ states, uint32_t n, const __grid_constant__ tafl_state start) {
+// NOTE: the start position travels as StateWords (plain uint4 words) and is rebuilt with
+// unpack_state: assigning a tafl_state kernel parameter to a local that is modified afterwards
+// (`s = start` on auto-reset) made nvcc 12.9 reload att[0] from the parameter at the final store.
+__global__ void k_fill_states(tafl_state* __restrict__ states, uint32_t n, const __grid_constant__ StateWords start) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g < n) store_state(states + g, start);
+    if (g < n) {
+        uint4* q = reinterpret_cast<uint4*>(states + g);
+        q[0] = start.v[0]; q[1] = start.v[1]; q[2] = start.v[2]; q[3] = start.v[3];
+    }
 }
 __global__ void k_reset_ids(tafl_state* __restrict__ states, const uint32_t* __restrict__ ids, uint32_t n,
-                            uint32_t n_games, const __grid_constant__ tafl_state start) {
+                            uint32_t n_games, const __grid_constant__ StateWords start) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n && ids[i] < n_games) store_state(states + ids[i], start);
+    if (i < n && ids[i] < n_games) {
+        uint4* q = reinterpret_cast<uint4*>(states + ids[i]);
+        q[0] = start.v[0]; q[1] = start.v[1]; q[2] = start.v[2]; q[3] = start.v[3];
+    }
 }
 
 // get_all_possible_moves (game/main.rs:33-43), one game per thread
@@ -85,11 +94,12 @@ k_step_moves(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states
 template <class BB>
 __global__ void __launch_bounds__(STEP_BLOCK)
 k_step_random(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
-              const __grid_constant__ tafl_state start, uint64_t seed, uint64_t gid_base, uint64_t ply0,
+              const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
               uint32_t steps, int auto_reset, DevStats* __restrict__ stats) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t c_steps = 0, c_legal = 0, c_caps = 0;
     if (g < n) {
+        const tafl_state start = unpack_state(start_w.v[0], start_w.v[1], start_w.v[2], start_w.v[3]);
         tafl_state s = load_state(states + g);
         for (uint32_t i = 0; i < steps; ++i) {
             StepEvt ev = random_step(cx, s, start, seed, gid_base + g, ply0 + i, auto_reset != 0);
@@ -340,7 +350,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     TAFL_CREATE_TRY(cudaMalloc(&e->d_stats, sizeof(DevStats)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_checksum, sizeof(unsigned long long)));
     TAFL_CREATE_TRY(cudaMemsetAsync(e->d_stats, 0, sizeof(DevStats), e->stream));
-    k_fill_states<<<grid_for(n_games, 256), 256, 0, e->stream>>>(e->d_states, n_games, e->start);
+    k_fill_states<<<grid_for(n_games, 256), 256, 0, e->stream>>>(e->d_states, n_games, state_words(e->start));
     e->launches += 1;
     TAFL_CREATE_TRY(cudaGetLastError());
     TAFL_CREATE_TRY(cudaStreamSynchronize(e->stream));
@@ -380,13 +390,13 @@ int tafl_reset(tafl_engine* e, const uint32_t* h_ids, uint32_t n) {
     TAFL_CHECK_E(e);
     cudaSetDevice(e->device);
     if (!h_ids) {
-        k_fill_states<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, e->start);
+        k_fill_states<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, state_words(e->start));
         TAFL_LAUNCHED(e);
     } else if (n) {
         uint32_t* d_ids;
         int rc = upload(e, 0, h_ids, n, &d_ids);
         if (rc) return rc;
-        k_reset_ids<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_states, d_ids, n, e->n_games, e->start);
+        k_reset_ids<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_states, d_ids, n, e->n_games, state_words(e->start));
         TAFL_LAUNCHED(e);
     }
     return sync_engine(e);
@@ -493,7 +503,7 @@ int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int 
     while (done < n_steps) {
         const uint32_t chunk = (n_steps - done) < (uint32_t)spl ? (n_steps - done) : (uint32_t)spl;
         TAFL_WIDTH_DISPATCH(e, (k_step_random<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(
-                                   cx, e->d_states, n, e->start, seed, e->game_id_base, e->ply, chunk, auto_reset, e->d_stats)));
+                                   cx, e->d_states, n, state_words(e->start), seed, e->game_id_base, e->ply, chunk, auto_reset, e->d_stats)));
         TAFL_LAUNCHED(e);
         e->ply += chunk;
         done += chunk;

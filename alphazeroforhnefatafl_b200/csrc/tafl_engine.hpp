@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstring>
 #include <string>
 
 #include "tafl_ctx.hpp"
@@ -55,18 +56,47 @@ void mcts_free(tafl_engine* e);
 
 inline unsigned grid_for(uint32_t n, unsigned block) { return (n + block - 1) / block; }
 
-// 64-byte state <-> registers as four 16-byte vectors
+// 64-byte state <-> registers as four 16-byte vector accesses.  Fields are packed/unpacked
+// explicitly (no union type punning: nvcc kept a stale att[0] through a punned store).
+// start position passed to kernels as plain words (see unpack_state)
+struct StateWords { uint4 v[4]; };
+inline StateWords state_words(const tafl_state& s) {
+    StateWords w;
+    static_assert(sizeof(StateWords) == sizeof(tafl_state), "64-byte state");
+    std::memcpy(&w, &s, sizeof(w));
+    return w;
+}
+__device__ __forceinline__ tafl_state unpack_state(const uint4 a, const uint4 d, const uint4 r, const uint4 m) {
+    tafl_state s;
+    s.att[0] = (uint64_t)a.x | ((uint64_t)a.y << 32);
+    s.att[1] = (uint64_t)a.z | ((uint64_t)a.w << 32);
+    s.def[0] = (uint64_t)d.x | ((uint64_t)d.y << 32);
+    s.def[1] = (uint64_t)d.z | ((uint64_t)d.w << 32);
+    s.recent[0] = r.x; s.recent[1] = r.y; s.recent[2] = r.z; s.recent[3] = r.w;
+    s.att_reps = (uint8_t)(m.x & 0xFF);
+    s.def_reps = (uint8_t)((m.x >> 8) & 0xFF);
+    s.flags = (uint8_t)((m.x >> 16) & 0xFF);
+    s.status = (uint8_t)(m.x >> 24);
+    s.turn = m.y;
+    s.plays_since_capture = m.z;
+    s.ring_head = (uint8_t)(m.w & 0xFF);
+    s.side_len = (uint8_t)((m.w >> 8) & 0xFF);
+    s._pad[0] = (uint8_t)((m.w >> 16) & 0xFF);
+    s._pad[1] = (uint8_t)(m.w >> 24);
+    return s;
+}
 __device__ __forceinline__ tafl_state load_state(const tafl_state* p) {
-    union { tafl_state s; uint4 v[4]; } u;
     const uint4* q = reinterpret_cast<const uint4*>(p);
-    u.v[0] = q[0]; u.v[1] = q[1]; u.v[2] = q[2]; u.v[3] = q[3];
-    return u.s;
+    return unpack_state(q[0], q[1], q[2], q[3]);
 }
 __device__ __forceinline__ void store_state(tafl_state* p, const tafl_state& s) {
-    union { tafl_state s; uint4 v[4]; } u;
-    u.s = s;
     uint4* q = reinterpret_cast<uint4*>(p);
-    q[0] = u.v[0]; q[1] = u.v[1]; q[2] = u.v[2]; q[3] = u.v[3];
+    q[0] = make_uint4((uint32_t)s.att[0], (uint32_t)(s.att[0] >> 32), (uint32_t)s.att[1], (uint32_t)(s.att[1] >> 32));
+    q[1] = make_uint4((uint32_t)s.def[0], (uint32_t)(s.def[0] >> 32), (uint32_t)s.def[1], (uint32_t)(s.def[1] >> 32));
+    q[2] = make_uint4(s.recent[0], s.recent[1], s.recent[2], s.recent[3]);
+    q[3] = make_uint4((uint32_t)s.att_reps | ((uint32_t)s.def_reps << 8) | ((uint32_t)s.flags << 16) | ((uint32_t)s.status << 24),
+                      s.turn, s.plays_since_capture,
+                      (uint32_t)s.ring_head | ((uint32_t)s.side_len << 8) | ((uint32_t)s._pad[0] << 16) | ((uint32_t)s._pad[1] << 24));
 }
 
 }  // namespace tafl
