@@ -1,13 +1,452 @@
-// tafl_mcts.cu — placeholder until the MCTS kernels land (next commit).
+// tafl_mcts.cu — batched MCTS kernels (K5 select, K6 expand, K7 backup, K8 root policy / play,
+// K9 pack_records) and their C ABI (include/tafl.h, "MCTS" and "Self-play records" sections).
+// Reference: src/mcts.py:11-136 (`class MCTS`), restated for the CPU in oracle/mcts_oracle.hpp.
+#include <cstdio>
+#include <cstring>
+
 #include "tafl_engine.hpp"
-namespace tafl { void mcts_free(tafl_engine*) {} }
-extern "C" {
-int tafl_mcts_configure(tafl_engine*, const tafl_mcts_config*) { return TAFL_ERR_UNSUPPORTED; }
-int tafl_mcts_search(tafl_engine*) { return TAFL_ERR_UNSUPPORTED; }
-int tafl_mcts_search_async(tafl_engine*) { return TAFL_ERR_UNSUPPORTED; }
-int tafl_mcts_results_device(tafl_engine*, tafl_move**, uint32_t**, double**, uint32_t**, uint32_t**) { return TAFL_ERR_UNSUPPORTED; }
-int tafl_mcts_results_host(tafl_engine*, uint32_t, uint32_t, tafl_move*, uint32_t*, double*, uint32_t*, uint32_t*) { return TAFL_ERR_UNSUPPORTED; }
-int tafl_mcts_play_best(tafl_engine*, uint8_t*) { return TAFL_ERR_UNSUPPORTED; }
-int tafl_mcts_stats_get(tafl_engine*, tafl_mcts_stats*) { return TAFL_ERR_UNSUPPORTED; }
-int tafl_pack_records(tafl_engine*, void*) { return TAFL_ERR_UNSUPPORTED; }
+#include "tafl_mcts.cuh"
+#include "tafl_select.cuh"
+
+using namespace tafl;
+
+namespace tafl {
+
+struct MctsPools {
+    tafl_mcts_config cfg{};
+    MctsView v{};
+    // root results, [n_games][TAFL_MAX_MOVES] (+ [n_games] for counts / best)
+    tafl_move* r_moves = nullptr;
+    uint32_t* r_visits = nullptr;
+    double* r_q = nullptr;
+    uint32_t* r_counts = nullptr;
+    uint32_t* r_best = nullptr;
+    uint32_t* d_any_overflow = nullptr;
+    bool searched = false;
+};
+
+}  // namespace tafl
+
+namespace {
+
+constexpr int MCTS_WARPS = 4;                 // trees per CTA
+constexpr double MCTS_EPS = 1e-8;             // mcts.py:6
+enum { ST_SIMS = 0, ST_NODES, ST_DEPTH, ST_EDGES, ST_TERMINAL, ST_MAXEDGES, ST_COUNT };
+
+// fresh tree per game, rooted at the game's current state (MCTS.__init__ + first getActionProb)
+__global__ void k_mcts_init(const tafl_state* __restrict__ states, uint32_t n, MctsView mv) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const tafl_state s = load_state(states + g);
+    store_state(mv.n_state + (size_t)g * mv.node_cap, s);
+    mv.n_hdr[(size_t)g * mv.node_cap] = make_uint4(0u, 0u, MCTS_NO_PARENT, hdr_pack(0, 0, 0, es_code(s)));
+    mv.t_nodes[g] = 1;
+    mv.t_edges[g] = 0;
+    mv.t_overflow[g] = 0;
+    atomicAdd(&mv.stats[ST_NODES], 1ull);   // the root (oracle: Mcts::reset -> new_node)
 }
+
+// `sims` x MCTS.search (mcts.py:55-136) for every tree; warp w of the grid owns tree w.
+template <class BB>
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_mcts_sims(const __grid_constant__ Ctx<BB> cx, MctsView mv, uint32_t n_trees, uint32_t sims, double cpuct, double draw_value,
+            uint32_t* __restrict__ any_overflow) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (tree >= n_trees) return;
+    tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    uint32_t* const e_N = mv.e_N + (size_t)tree * mv.edge_cap;
+    double* const e_Q = mv.e_Q + (size_t)tree * mv.edge_cap;
+    uint32_t* const e_child = mv.e_child + (size_t)tree * mv.edge_cap;
+    tafl_move* const e_move = mv.e_move + (size_t)tree * mv.edge_cap;
+    uint32_t n_nodes = mv.t_nodes[tree], n_edges_used = mv.t_edges[tree];
+    bool overflow = mv.t_overflow[tree] != 0;
+    unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_edges = 0, c_term = 0;
+
+    for (uint32_t sim = 0; sim < sims && !overflow; ++sim) {
+        uint32_t node = 0, depth = 0;
+        double v;   // value returned by search(node) to its caller
+        // ---- descend ---------------------------------------------------------------------------
+        while (true) {
+            uint4 h = n_hdr[node];
+            const uint32_t es = hdr_es(h.w);
+            if (es != ES_ONGOING) {   // mcts.py:77-81  terminal: return -Es[s]
+                const double Es = es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value);
+                v = -Es;
+                c_term += 1;
+                c_depth += depth;
+                break;
+            }
+            if (!hdr_expanded(h.w)) {   // mcts.py:83-102  leaf: expand, Ns = 0, return -v with v = 0
+                const tafl_state s = load_state(n_state + node);
+                const Pos<BB> p = load_pos(cx, s);
+                const uint32_t room = mv.edge_cap - n_edges_used;
+                const int L = warp_gen_moves(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, e_move + n_edges_used, (int)room, lane);
+                if ((uint32_t)L > room) { overflow = true; break; }
+                for (int a = lane; a < L; a += 32) e_N[n_edges_used + a] = 0u;   // Nsa absent == 0
+                if (lane == 0) n_hdr[node] = make_uint4(n_edges_used, 0u, h.z, hdr_pack((uint32_t)L, hdr_pedge(h.w), 1u, es));
+                n_edges_used += (uint32_t)L;
+                c_edges += (unsigned long long)L;
+                c_depth += depth;
+                __syncwarp();
+                v = -0.0;
+                break;
+            }
+            // ---- select (mcts.py:104-119) --------------------------------------------------------
+            const uint32_t L = hdr_n_edges(h.w), base = h.x, Ns = h.y;
+            if (L == 0) { v = 0.0; break; }   // Ongoing node without plays: oracle returns 0.0 unnegated
+            const double P = 1.0 / (double)L;                    // uniform prior over the valid moves
+            const double c = cpuct * P;
+            const double t_vis = c * sqrt((double)Ns);           // numerator for visited edges
+            const double u_new = c * sqrt((double)Ns + MCTS_EPS);
+            double best_u = -INFINITY;
+            uint32_t best_a = 0xFFFFFFFFu;
+            for (uint32_t a = lane; a < L; a += 32) {
+                const uint32_t N = e_N[base + a];
+                double u;
+                if (N > 0) u = e_Q[base + a] + t_vis / (double)(1u + N);
+                else u = u_new;
+                if (u > best_u) { best_u = u; best_a = a; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const double ou = __shfl_xor_sync(0xFFFFFFFFu, best_u, o);
+                const uint32_t oa = __shfl_xor_sync(0xFFFFFFFFu, best_a, o);
+                if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; }
+            }
+            const uint32_t a = best_a;
+            uint32_t child;
+            if (e_N[base + a] == 0) {   // first traversal: getNextState (mcts.py:122-123)
+                tafl_state s = load_state(n_state + node);
+                do_valid_move(cx, s, e_move[base + a]);
+                child = n_nodes++;
+                c_nodes += 1;
+                if (lane == 0) {
+                    store_state(n_state + child, s);
+                    n_hdr[child] = make_uint4(0u, 0u, node, hdr_pack(0, a, 0, es_code(s)));
+                    e_child[base + a] = child;
+                }
+                __syncwarp();
+            } else {
+                child = e_child[base + a];
+            }
+            node = child;
+            depth += 1;
+        }
+        if (overflow) break;
+        // ---- backup (mcts.py:125-136) ----------------------------------------------------------------
+        while (true) {
+            const uint4 h = n_hdr[node];
+            if (h.z == MCTS_NO_PARENT) break;
+            const uint32_t parent = h.z, a = hdr_pedge(h.w);
+            uint4 ph = n_hdr[parent];
+            const uint32_t e = ph.x + a;
+            const uint32_t N = e_N[e];
+            double q;
+            if (N > 0) q = ((double)N * e_Q[e] + v) / (double)(N + 1u);
+            else q = v;
+            __syncwarp();
+            if (lane == 0) {
+                e_Q[e] = q;
+                e_N[e] = N + 1u;
+                ph.y += 1u;   // Ns[s] += 1
+                n_hdr[parent] = ph;
+            }
+            __syncwarp();
+            v = -v;
+            node = parent;
+        }
+        c_sims += 1;
+    }
+    if (lane == 0) {
+        mv.t_nodes[tree] = n_nodes;
+        mv.t_edges[tree] = n_edges_used;
+        if (overflow) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+        atomicAdd(&mv.stats[ST_SIMS], c_sims);
+        atomicAdd(&mv.stats[ST_NODES], c_nodes);
+        atomicAdd(&mv.stats[ST_DEPTH], c_depth);
+        atomicAdd(&mv.stats[ST_EDGES], c_edges);
+        atomicAdd(&mv.stats[ST_TERMINAL], c_term);
+        atomicMax(&mv.stats[ST_MAXEDGES], (unsigned long long)n_edges_used);
+    }
+}
+
+// MCTS.getActionProb (mcts.py:40-47), temp = 0 with first-max: root visit counts, Q, moves, argmax
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_mcts_results(MctsView mv, uint32_t n_trees, tafl_move* __restrict__ r_moves, uint32_t* __restrict__ r_visits,
+               double* __restrict__ r_q, uint32_t* __restrict__ r_counts, uint32_t* __restrict__ r_best) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (tree >= n_trees) return;
+    const uint4 h = mv.n_hdr[(size_t)tree * mv.node_cap];
+    const uint32_t L = hdr_expanded(h.w) ? hdr_n_edges(h.w) : 0u, base = h.x;
+    const size_t eo = (size_t)tree * mv.edge_cap + base, ro = (size_t)tree * TAFL_MAX_MOVES;
+    uint32_t best_n = 0, best_a = 0xFFFFFFFFu;
+    for (uint32_t a = lane; a < TAFL_MAX_MOVES; a += 32) {
+        uint32_t N = 0;
+        double q = 0.0;
+        tafl_move m = 0;
+        if (a < L) {
+            N = mv.e_N[eo + a];
+            m = mv.e_move[eo + a];
+            if (N > 0) q = mv.e_Q[eo + a];
+        }
+        r_moves[ro + a] = m;
+        r_visits[ro + a] = N;
+        r_q[ro + a] = q;
+        if (N > best_n) { best_n = N; best_a = a; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint32_t on = __shfl_xor_sync(0xFFFFFFFFu, best_n, o), oa = __shfl_xor_sync(0xFFFFFFFFu, best_a, o);
+        if (on > best_n || (on == best_n && oa < best_a)) { best_n = on; best_a = oa; }
+    }
+    if (lane == 0) {
+        r_counts[tree] = L;
+        r_best[tree] = best_n > 0 ? best_a : 0u;
+    }
+}
+
+// play the chosen root move in every Ongoing game (do_valid_play, logic.rs:782-820)
+template <class BB>
+__global__ void __launch_bounds__(64)
+k_mcts_play_best(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
+                 const tafl_move* __restrict__ r_moves, const uint32_t* __restrict__ r_counts,
+                 const uint32_t* __restrict__ r_best, uint8_t* __restrict__ status_out) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    tafl_state s = load_state(states + g);
+    if (s.status == TAFL_STATUS_ONGOING && r_counts[g] > 0) {
+        do_valid_move(cx, s, r_moves[(size_t)g * TAFL_MAX_MOVES + r_best[g]]);
+        store_state(states + g, s);
+    }
+    if (status_out) status_out[g] = s.status;
+}
+
+// one replay-buffer row per game: header (root position, side, chosen move, status after it) +
+// root moves + visit counts, fixed stride (include/tafl.h TAFL_REC_STRIDE); one warp per game
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_pack_records(MctsView mv, const tafl_state* __restrict__ states, uint32_t n, uint64_t gid_base,
+               const tafl_move* __restrict__ r_moves, const uint32_t* __restrict__ r_visits,
+               const uint32_t* __restrict__ r_counts, const uint32_t* __restrict__ r_best, uint8_t* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t g = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (g >= n) return;
+    uint8_t* rec = out + (size_t)g * TAFL_REC_STRIDE;
+    const uint32_t cnt = r_counts[g];
+    if (lane == 0) {
+        const tafl_state root = load_state(mv.n_state + (size_t)g * mv.node_cap);
+        const tafl_state cur = load_state(states + g);
+        tafl_record_header h;
+        h.game_id = gid_base + g;
+        h.ply = root.turn;
+        h.n_moves = (uint16_t)cnt;
+        h.side_to_play = (root.flags & TAFL_FLAG_DEF_TO_PLAY) ? TAFL_DEFENDER : TAFL_ATTACKER;
+        h.status = cur.status;
+        h.att[0] = root.att[0]; h.att[1] = root.att[1]; h.def[0] = root.def[0]; h.def[1] = root.def[1];
+        h.best = (uint16_t)r_best[g];
+        h._pad[0] = h._pad[1] = h._pad[2] = 0;
+        *reinterpret_cast<tafl_record_header*>(rec) = h;
+    }
+    uint16_t* mo = reinterpret_cast<uint16_t*>(rec + sizeof(tafl_record_header));
+    uint32_t* vo = reinterpret_cast<uint32_t*>(rec + sizeof(tafl_record_header) + 2 * TAFL_REC_MOVES);
+    for (uint32_t a = lane; a < TAFL_REC_MOVES; a += 32) {
+        mo[a] = a < cnt ? r_moves[(size_t)g * TAFL_MAX_MOVES + a] : (uint16_t)0;
+        vo[a] = a < cnt ? r_visits[(size_t)g * TAFL_MAX_MOVES + a] : 0u;
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+namespace tafl {
+
+void mcts_free(tafl_engine* e) {
+    MctsPools* m = e->mcts;
+    if (!m) return;
+    cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.e_N); cudaFree(m->v.e_Q); cudaFree(m->v.e_child);
+    cudaFree(m->v.e_move); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
+    cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best);
+    cudaFree(m->d_any_overflow);
+    delete m;
+    e->mcts = nullptr;
+}
+
+}  // namespace tafl
+
+#define MCTS_WIDTH_DISPATCH(e, body)                                                        \
+    do {                                                                                    \
+        if ((e)->width == 64) { using BB = BB64; const Ctx<BB64>& cx = (e)->cx64; body; }   \
+        else { using BB = BB128; const Ctx<BB128>& cx = (e)->cx128; body; }                 \
+    } while (0)
+#define MCTS_LAUNCHED(e)                         \
+    do {                                         \
+        (e)->launches += 1;                      \
+        TAFL_CUDA_TRY((e), cudaGetLastError());  \
+    } while (0)
+
+static int need_mcts(tafl_engine* e) {
+    if (!e) return TAFL_ERR_INVALID_ARG;
+    if (!e->mcts) { e->err = "tafl_mcts_configure has not been called"; return TAFL_ERR_INVALID_ARG; }
+    return TAFL_OK;
+}
+
+extern "C" {
+
+int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg) {
+    if (!e || !cfg || cfg->num_sims == 0 || !(cfg->draw_value != 0.0)) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    tafl_mcts_config c = *cfg;
+    if (c.edge_capacity == 0) c.edge_capacity = (c.num_sims + 1) * 160u;
+    if (e->mcts && e->mcts->cfg.num_sims == c.num_sims && e->mcts->cfg.edge_capacity == c.edge_capacity) {
+        e->mcts->cfg = c;   // same pools, possibly new cpuct / draw value
+        return TAFL_OK;
+    }
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    mcts_free(e);
+    MctsPools* m = new MctsPools();
+    m->cfg = c;
+    e->mcts = m;
+    const size_t n = e->n_games, nc = (size_t)c.num_sims + 1, ec = c.edge_capacity;
+    m->v.node_cap = (uint32_t)nc;
+    m->v.edge_cap = (uint32_t)ec;
+#define MCTS_ALLOC(ptr, bytes)                                          \
+    do {                                                                \
+        cudaError_t _ce = cudaMalloc((void**)&(ptr), (bytes));          \
+        if (_ce != cudaSuccess) {                                       \
+            int _rc = set_cuda_error(e, _ce, "cudaMalloc(" #ptr ")");   \
+            mcts_free(e);                                               \
+            return _rc;                                                 \
+        }                                                               \
+    } while (0)
+    MCTS_ALLOC(m->v.n_state, n * nc * sizeof(tafl_state));
+    MCTS_ALLOC(m->v.n_hdr, n * nc * sizeof(uint4));
+    MCTS_ALLOC(m->v.e_N, n * ec * sizeof(uint32_t));
+    MCTS_ALLOC(m->v.e_Q, n * ec * sizeof(double));
+    MCTS_ALLOC(m->v.e_child, n * ec * sizeof(uint32_t));
+    MCTS_ALLOC(m->v.e_move, n * ec * sizeof(tafl_move));
+    MCTS_ALLOC(m->v.t_nodes, n * sizeof(uint32_t));
+    MCTS_ALLOC(m->v.t_edges, n * sizeof(uint32_t));
+    MCTS_ALLOC(m->v.t_overflow, n * sizeof(uint32_t));
+    MCTS_ALLOC(m->v.stats, ST_COUNT * sizeof(unsigned long long));
+    MCTS_ALLOC(m->r_moves, n * TAFL_MAX_MOVES * sizeof(tafl_move));
+    MCTS_ALLOC(m->r_visits, n * TAFL_MAX_MOVES * sizeof(uint32_t));
+    MCTS_ALLOC(m->r_q, n * TAFL_MAX_MOVES * sizeof(double));
+    MCTS_ALLOC(m->r_counts, n * sizeof(uint32_t));
+    MCTS_ALLOC(m->r_best, n * sizeof(uint32_t));
+    MCTS_ALLOC(m->d_any_overflow, sizeof(uint32_t));
+#undef MCTS_ALLOC
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->v.stats, 0, ST_COUNT * sizeof(unsigned long long), e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->d_any_overflow, 0, sizeof(uint32_t), e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return TAFL_OK;
+}
+
+int tafl_mcts_search_async(tafl_engine* e) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    cudaSetDevice(e->device);
+    MctsPools* m = e->mcts;
+    const uint32_t n = e->n_games;
+    k_mcts_init<<<grid_for(n, 128), 128, 0, e->stream>>>(e->d_states, n, m->v);
+    MCTS_LAUNCHED(e);
+    const unsigned grid = grid_for(n, MCTS_WARPS);
+    MCTS_WIDTH_DISPATCH(e, (k_mcts_sims<BB><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->cfg.num_sims, m->cfg.cpuct,
+                                                                                    m->cfg.draw_value, m->d_any_overflow)));
+    MCTS_LAUNCHED(e);
+    k_mcts_results<<<grid, MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->r_moves, m->r_visits, m->r_q, m->r_counts, m->r_best);
+    MCTS_LAUNCHED(e);
+    m->searched = true;
+    return TAFL_OK;
+}
+
+int tafl_mcts_search(tafl_engine* e) {
+    int rc = tafl_mcts_search_async(e);
+    if (rc) return rc;
+    uint32_t of = 0;
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(&of, e->mcts->d_any_overflow, sizeof(of), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    if (of) {
+        e->err = "MCTS edge pool exhausted for at least one tree: raise tafl_mcts_config.edge_capacity";
+        return TAFL_ERR_CAPACITY;
+    }
+    return TAFL_OK;
+}
+
+int tafl_mcts_results_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_visits, double** d_q, uint32_t** d_counts,
+                             uint32_t** d_best) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (d_moves) *d_moves = m->r_moves;
+    if (d_visits) *d_visits = m->r_visits;
+    if (d_q) *d_q = m->r_q;
+    if (d_counts) *d_counts = m->r_counts;
+    if (d_best) *d_best = m->r_best;
+    return TAFL_OK;
+}
+
+int tafl_mcts_results_host(tafl_engine* e, uint32_t first, uint32_t n, tafl_move* h_moves, uint32_t* h_visits, double* h_q,
+                           uint32_t* h_counts, uint32_t* h_best) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    if ((uint64_t)first + n > e->n_games) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    MctsPools* m = e->mcts;
+    const size_t o = (size_t)first * TAFL_MAX_MOVES, k = (size_t)n * TAFL_MAX_MOVES;
+    if (h_moves) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_moves, m->r_moves + o, k * sizeof(tafl_move), cudaMemcpyDeviceToHost, e->stream));
+    if (h_visits) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_visits, m->r_visits + o, k * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    if (h_q) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_q, m->r_q + o, k * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    if (h_counts) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_counts, m->r_counts + first, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    if (h_best) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_best, m->r_best + first, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return TAFL_OK;
+}
+
+int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    if (!e->mcts->searched) { e->err = "tafl_mcts_search has not been run"; return TAFL_ERR_INVALID_ARG; }
+    cudaSetDevice(e->device);
+    MctsPools* m = e->mcts;
+    const uint32_t n = e->n_games;
+    MCTS_WIDTH_DISPATCH(e, (k_mcts_play_best<BB><<<grid_for(n, 64), 64, 0, e->stream>>>(cx, e->d_states, n, m->r_moves, m->r_counts,
+                                                                                       m->r_best, e->d_status)));
+    MCTS_LAUNCHED(e);
+    if (h_status) {
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_status, e->d_status, n, cudaMemcpyDeviceToHost, e->stream));
+        TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    }
+    return TAFL_OK;
+}
+
+int tafl_mcts_stats_get(tafl_engine* e, tafl_mcts_stats* out) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    if (!out) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    unsigned long long h[ST_COUNT];
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h, e->mcts->v.stats, sizeof(h), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    out->sims = h[ST_SIMS]; out->nodes = h[ST_NODES]; out->depth_sum = h[ST_DEPTH]; out->edges = h[ST_EDGES];
+    out->terminal_hits = h[ST_TERMINAL]; out->max_edges_used = h[ST_MAXEDGES];
+    return TAFL_OK;
+}
+
+int tafl_pack_records(tafl_engine* e, void* d_out) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    if (!d_out || !e->mcts->searched) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    MctsPools* m = e->mcts;
+    const uint32_t n = e->n_games;
+    k_pack_records<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, e->d_states, n, e->game_id_base, m->r_moves,
+                                                                              m->r_visits, m->r_counts, m->r_best, (uint8_t*)d_out);
+    MCTS_LAUNCHED(e);
+    return TAFL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,114 @@
+"""GPU parity tests of the batched MCTS (tafl_mcts.cu) against the CPU MCTS oracle
+(oracle/mcts_oracle.hpp, a restatement of the reference's src/mcts.py with the stub evaluator).
+Visit counts, move lists, best move and search statistics are bit-exact; Q within 1e-6 relative
+(BASELINE.json north_star) — in practice also bit-exact because the f64 operation order is the
+oracle's and FMA contraction is disabled."""
+import numpy as np
+import pytest
+
+from alphazeroforhnefatafl_b200 import _abi as A
+from alphazeroforhnefatafl_b200 import engine as E
+from alphazeroforhnefatafl_b200._lib import TaflError
+from parity_cases import board_for, sample_positions
+
+pytestmark = pytest.mark.gpu
+Q_RTOL = 1e-6
+
+
+def check_search(orc, rules, fen, width, roots, sims, cpuct=1.0, draw_value=1e-4):
+    n = len(roots)
+    ref = orc.mcts_search(rules, width, roots, sims, cpuct=cpuct, draw_value=draw_value, n_threads=8)
+    with E.LockstepGames(rules, fen, n, 0, width) as g:
+        g.set_states(roots)
+        g.mcts_configure(sims, cpuct, draw_value)
+        g.mcts_search()
+        got = g.mcts_results()
+        stats = g.mcts_stats().as_dict()
+        assert np.array_equal(got["counts"], ref["counts"])
+        for i in range(n):
+            c = int(ref["counts"][i])
+            assert np.array_equal(got["moves"][i, :c], ref["moves"][i, :c]), i
+            assert np.array_equal(got["visits"][i, :c], ref["visits"][i, :c]), i
+            assert np.allclose(got["q"][i, :c], ref["q"][i, :c], rtol=Q_RTOL, atol=0.0), i
+            assert not got["visits"][i, c:].any()
+        assert np.array_equal(got["best"], ref["best"])
+        assert stats == ref["stats"].as_dict()
+        q_exact = all(np.array_equal(got["q"][i, :ref["counts"][i]], ref["q"][i, :ref["counts"][i]]) for i in range(n))
+        # play the chosen move: equals the oracle's do_play of moves[best]
+        status = g.mcts_play_best()
+        after = g.get_states()
+        ongoing = (roots["status"] == 0) & (ref["counts"] > 0)
+        plays = E.moves_to_plays(ref["moves"][np.arange(n), ref["best"]], width)
+        exp, fx = orc.by_value(rules, width).do_plays(roots[ongoing], plays[ongoing])
+        assert not fx["err"].any()
+        assert after[ongoing].tobytes() == exp.tobytes()
+        assert after[~ongoing].tobytes() == roots[~ongoing].tobytes()
+        assert np.array_equal(status, after["status"])
+    return ref, q_exact
+
+
+@pytest.mark.parametrize("name,preset,width,sims", [
+    ("copenhagen", A.PRESET_COPENHAGEN, 128, 800), ("tablut", A.PRESET_TABLUT, 128, 400),
+    ("brandubh", A.PRESET_BRANDUBH, 64, 800), ("brandubh_u128", A.PRESET_BRANDUBH, 128, 150),
+    ("koch", A.PRESET_KOCH, 64, 300), ("magpie", A.PRESET_MAGPIE, 64, 100)])
+def test_gpu_mcts_vs_oracle(orc, built_lib, name, preset, width, sims):
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    roots = sample_positions(orc, rules, fen, width, 96, seed=61, max_steps=240)
+    ref, q_exact = check_search(orc, rules, fen, width, roots, sims)
+    assert q_exact, "Q values differ in the last bits"
+    # mcts.py:83-102: a fresh Ongoing root spends its first simulation on expansion
+    og = (roots["status"] == 0) & (ref["counts"] > 0)
+    assert np.array_equal(ref["visits"][og].sum(1), np.full(og.sum(), sims - 1))
+
+
+def test_gpu_mcts_terminal_values(orc, built_lib):
+    """Small boards late in the game: terminal leaves give non-zero Q (wins, losses, draws)."""
+    rules, fen = orc.preset_rules(A.PRESET_TABLUT), orc.preset_board(A.PRESET_TABLUT)
+    roots = sample_positions(orc, rules, fen, 128, 128, seed=71, max_steps=400)
+    ref, q_exact = check_search(orc, rules, fen, 128, roots, 500, cpuct=1.7, draw_value=0.25)
+    assert q_exact
+    assert ref["stats"].terminal_hits > 0
+    assert np.abs(ref["q"]).max() > 0
+
+
+def test_gpu_mcts_capacity_error(orc, built_lib):
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    with E.LockstepGames(rules, fen, 8, 0, 128) as g:
+        g.mcts_configure(64, 1.0, 1e-4, edge_capacity=500)
+        with pytest.raises(TaflError) as ei:
+            g.mcts_search()
+        assert ei.value.code == A.ERR_CAPACITY
+
+
+def test_gpu_pack_records(orc, built_lib):
+    import torch
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
+    n = 40
+    roots = sample_positions(orc, rules, fen, 64, n, seed=81, max_steps=60)
+    with E.LockstepGames(rules, fen, n, 0, 64) as g:
+        g.set_states(roots)
+        g.set_game_id_base(5000)
+        g.mcts_configure(120)
+        g.mcts_search()
+        res = g.mcts_results()
+        g.mcts_play_best(False)
+        buf = torch.zeros(n * A.REC_STRIDE, dtype=torch.uint8, device="cuda")
+        g.pack_records(buf.data_ptr())
+        g.sync()
+        after = g.get_states()
+    raw = buf.cpu().numpy().reshape(n, A.REC_STRIDE)
+    hdr = np.dtype([("game_id", "<u8"), ("ply", "<u4"), ("n_moves", "<u2"), ("side", "u1"), ("status", "u1"),
+                    ("att", "<u8", (2,)), ("def", "<u8", (2,)), ("best", "<u2"), ("_pad", "<u2", (3,))])
+    assert hdr.itemsize == 56
+    for i in range(n):
+        h = raw[i, :56].view(hdr)[0]
+        assert h["game_id"] == 5000 + i and h["ply"] == roots[i]["turn"]
+        assert h["n_moves"] == res["counts"][i] and h["best"] == res["best"][i]
+        assert h["side"] == (A.DEFENDER if roots[i]["flags"] & A.FLAG_DEF_TO_PLAY else A.ATTACKER)
+        assert h["status"] == after[i]["status"]
+        assert np.array_equal(h["att"], roots[i]["att"]) and np.array_equal(h["def"], roots[i]["def"])
+        c = int(res["counts"][i])
+        mv = raw[i, 56:56 + 2 * A.REC_MOVES].view("<u2")
+        vs = raw[i, 56 + 2 * A.REC_MOVES:].view("<u4")
+        assert np.array_equal(mv[:c], res["moves"][i, :c]) and not mv[c:].any()
+        assert np.array_equal(vs[:c], res["visits"][i, :c]) and not vs[c:].any()
