@@ -1,0 +1,64 @@
+"""Host-side mirror of the reference's ``class MCTS`` (src/mcts.py:11-136) over the CUDA engine.
+
+The reference object is ``MCTS(game, nnet, args)`` with ``getActionProb(canonicalBoard, temp)``
+running ``args.numMCTSSims`` x ``search`` and returning the visit-count policy.  Here one object
+drives the search trees of ALL resident games of a ``LockstepGames`` engine at once (one tree per
+game on the GPU); names and argument meaning follow the reference:
+
+    args.numMCTSSims, args.cpuct      (mcts.py:37, 112)
+    getActionProb(temp=1)             (mcts.py:28-53)  -> moves, probs, counts  (batched)
+    search()                          (mcts.py:55-136) -> runs the batched simulations only
+
+Differences that the reference leaves undefined and this build defines (SURVEY.md §A.11,
+DESIGN.md): the evaluator is the fixed stub (uniform priors over the legal moves, value 0); action
+index = position in the canonical legal-move list of the position; tree (not transposition-merged)
+node identity; temp == 0 picks the FIRST maximum instead of a random one among ties.
+"""
+from types import SimpleNamespace
+
+import numpy as np
+
+EPS = 1e-8   # mcts.py:6
+
+
+class MCTS:
+    def __init__(self, games, args=None, nnet=None):
+        """games: engine.LockstepGames; args: object with numMCTSSims and cpuct (mcts.py:16-26).
+        nnet must be None: only the stub evaluator exists on this path."""
+        if nnet is not None:
+            raise NotImplementedError("only the uniform-prior / value-0 stub evaluator is built (BASELINE.json north_star)")
+        self.games = games
+        self.args = args or SimpleNamespace(numMCTSSims=800, cpuct=1.0)
+        self.draw_value = getattr(self.args, "drawValue", 1e-4)
+        games.mcts_configure(int(self.args.numMCTSSims), float(self.args.cpuct), float(self.draw_value),
+                             int(getattr(self.args, "edgeCapacity", 0)))
+
+    def search(self, sync=True):
+        """numMCTSSims simulations from a fresh tree rooted at every game's current state."""
+        self.games.mcts_search(sync=sync)
+
+    def getActionProb(self, temp=1):  # noqa: N802  (reference name)
+        """Returns (moves [n, MAX_MOVES] u16, probs [n, MAX_MOVES] f64, counts [n]): for game i the
+        first counts[i] entries are its legal moves in canonical order and their probabilities
+        (mcts.py:40-53).  Games that are over have counts == 0."""
+        self.search()
+        r = self.games.mcts_results()
+        visits = r["visits"].astype(np.float64)
+        n = len(visits)
+        probs = np.zeros_like(visits)
+        if temp == 0:   # mcts.py:43-48, first-max instead of np.random.choice among the ties
+            has = r["counts"] > 0
+            probs[np.arange(n)[has], r["best"][has]] = 1.0
+        else:           # mcts.py:50-53
+            c = visits ** (1.0 / temp)
+            s = c.sum(1, keepdims=True)
+            np.divide(c, s, out=probs, where=s > 0)
+        self.last = r
+        return r["moves"], probs, r["counts"]
+
+    def play_best(self):
+        """Apply the temp == 0 choice of the last search in every Ongoing game; returns statuses."""
+        return self.games.mcts_play_best(True)
+
+    def stats(self):
+        return self.games.mcts_stats().as_dict()

@@ -1,0 +1,137 @@
+"""Self-play generation over game-sharded GPUs (BASELINE.json configs 4-5).
+
+Games shard by id range across ranks (one process per GPU); searching and stepping need no
+communication.  The only exchange is the per-move gather of fixed-stride replay records
+(``tafl_pack_records``: root position, legal moves, visit counts, chosen move, status) to the
+replay-buffer rank with ``torch.distributed`` (NCCL over NVLink on GPUs, gloo in the CPU tests).
+
+Nearest reference analogue: ``write_to_file`` (game/main.rs:86-132), a rolling window of the
+newest ``max_entries`` positions -> :class:`ReplayBuffer`.
+"""
+import collections
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _abi as A
+
+REC_HEADER = np.dtype([("game_id", "<u8"), ("ply", "<u4"), ("n_moves", "<u2"), ("side", "u1"), ("status", "u1"),
+                       ("att", "<u8", (2,)), ("def", "<u8", (2,)), ("best", "<u2"), ("_pad", "<u2", (3,))])
+assert REC_HEADER.itemsize == 56
+REC_DTYPE = np.dtype([("h", REC_HEADER), ("moves", "<u2", (A.REC_MOVES,)), ("visits", "<u4", (A.REC_MOVES,))])
+assert REC_DTYPE.itemsize == A.REC_STRIDE
+
+
+def gather_records(local, dst=0, group=None):
+    """Gather [n_local, REC_STRIDE] uint8 record tensors of every rank to rank ``dst``.
+
+    Ranks may hold different numbers of rows: counts are all-gathered first, rows are padded to
+    the maximum for the fixed-size gather and trimmed on arrival.  Returns the concatenated
+    [sum n, REC_STRIDE] tensor on ``dst`` (rank order == game-id order), None elsewhere."""
+    assert local.dtype == torch.uint8 and local.dim() == 2
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return local
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n = torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device)
+    counts = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(counts, n, group=group)
+    counts = [int(c.item()) for c in counts]
+    m = max(counts)
+    if m == 0:
+        return local[:0] if rank == dst else None
+    send = local
+    if local.shape[0] < m:
+        send = torch.zeros((m, local.shape[1]), dtype=torch.uint8, device=local.device)
+        send[:local.shape[0]] = local
+    send = send.contiguous()
+    if rank == dst:
+        bufs = [torch.empty_like(send) for _ in range(world)]
+        dist.gather(send, bufs, dst=dst, group=group)
+        return torch.cat([b[:c] for b, c in zip(bufs, counts)], 0)
+    dist.gather(send, None, dst=dst, group=group)
+    return None
+
+
+def records_to_numpy(t):
+    """[n, REC_STRIDE] uint8 tensor -> structured REC_DTYPE array (host)."""
+    return np.ascontiguousarray(t.cpu().numpy()).view(REC_DTYPE).reshape(-1)
+
+
+def backfill_outcomes(recs, draw_value=0.0):
+    """z for every record: +1 if the side to move at the record's position went on to win its game,
+    -1 if it lost, draw_value for a draw, NaN while the game is still unfinished (mcts.py callers
+    assign the episode result to every position of the episode)."""
+    z = np.full(len(recs), np.nan)
+    h = recs["h"]
+    final = {}
+    for gid, st in zip(h["game_id"], h["status"]):
+        if st & 0x80:
+            final[int(gid)] = int(st)
+    for i in range(len(recs)):
+        st = final.get(int(h["game_id"][i]))
+        if st is None:
+            continue
+        if (st & 0xC0) == 0xC0:
+            z[i] = draw_value
+        else:
+            winner = A.DEFENDER if st & 1 else A.ATTACKER
+            z[i] = 1.0 if winner == int(h["side"][i]) else -1.0
+    return z
+
+
+class ReplayBuffer:
+    """Rolling window of the newest ``max_entries`` records (write_to_file, game/main.rs:98-106:
+    when the window is full the oldest entry is dropped)."""
+
+    def __init__(self, max_entries):
+        self.max_entries = max_entries
+        self.q = collections.deque()
+        self.n = 0
+
+    def extend(self, recs):
+        if len(recs) == 0:
+            return
+        self.q.append(recs)
+        self.n += len(recs)
+        while self.n > self.max_entries:
+            over = self.n - self.max_entries
+            if len(self.q[0]) <= over:
+                self.n -= len(self.q.popleft())
+            else:
+                self.q[0] = self.q[0][over:]
+                self.n -= over
+
+    def __len__(self):
+        return self.n
+
+    def as_array(self):
+        return np.concatenate(list(self.q)) if self.q else np.zeros(0, REC_DTYPE)
+
+
+class SelfPlay:
+    """MCTS self-play of this rank's shard of games; records of every move are gathered to
+    ``dst``.  ``games`` is an engine.LockstepGames whose game-id base is already the shard's."""
+
+    def __init__(self, games, num_sims=800, cpuct=1.0, draw_value=1e-4, dst=0, group=None, edge_capacity=0):
+        self.g, self.dst, self.group = games, dst, group
+        games.mcts_configure(num_sims, cpuct, draw_value, edge_capacity)
+        self.stream = torch.cuda.ExternalStream(games.stream, device=games.device)
+        with torch.cuda.device(games.device):
+            self.rec = torch.zeros((games.n_games, A.REC_STRIDE), dtype=torch.uint8, device="cuda")
+
+    def move(self, gather=True, only_ongoing=True):
+        """One self-play move for every Ongoing game: search, play the first-max move, pack the
+        records, gather them.  Returns the gathered uint8 tensor on ``dst`` (None elsewhere)."""
+        g = self.g
+        with torch.cuda.stream(self.stream):
+            g.mcts_search(sync=False)
+            g.mcts_play_best(False)
+            g.pack_records(self.rec.data_ptr())
+            out = self.rec
+            if only_ongoing:   # rows of games that were already over carry n_moves == 0
+                n_moves = self.rec[:, 12].to(torch.int32) | (self.rec[:, 13].to(torch.int32) << 8)
+                out = self.rec[n_moves > 0]
+            if gather:
+                out = gather_records(out, self.dst, self.group)
+        return out

@@ -309,22 +309,22 @@ def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
     g = E.LockstepGames(E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN, n, local, 128)
     g.set_game_id_base(rank * n)
     g.step_random(args.seed, 20, auto_reset=True)          # start the trees from 20-ply positions
-    g.mcts_configure(args.mcts_sims, 1.0)
-    stream = torch.cuda.ExternalStream(g.stream, device=local)
+    from alphazeroforhnefatafl_b200 import selfplay as SP
+    sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0)     # search + first-max move + pack + gather to rank 0
+    stream = sp.stream
     moves = 3
-    with torch.cuda.stream(stream):
-        g.mcts_search()                                    # warm-up move
-        g.mcts_play_best(False)
-        s0 = g.mcts_stats().as_dict()
-        l0 = g.launches
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        a.record(stream)
-        for _ in range(moves):
-            g.mcts_search(sync=False)
-            g.mcts_play_best(False)
-        b.record(stream)
-        barrier()
+    sp.move()                                              # warm-up move
+    s0 = g.mcts_stats().as_dict()
+    l0 = g.launches
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    a.record(stream)
+    n_rec = 0
+    for _ in range(moves):
+        out = sp.move()
+        n_rec += 0 if out is None else out.shape[0]
+    b.record(stream)
+    barrier()
     ms = a.elapsed_time(b)
     s1 = g.mcts_stats().as_dict()
     sims = s1["sims"] - s0["sims"]
@@ -343,6 +343,8 @@ def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
            "mean_depth": d_bar, "mean_edges_per_node": l_bar, "bytes_per_sim_model": b_sim,
            "roofline": {"bound": "hbm", "achieved": v / world * b_sim / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": v / world * b_sim / 1e9 / hbm_peak},
+           "records_gathered_on_rank0": int(n_rec), "record_bytes": 1592,
+           "includes": "k_mcts_init + k_mcts_sims + k_mcts_results + k_mcts_play_best + k_pack_records + torch record gather",
            "gpu_launches": int(g.launches - l0)}
     g.close()
     return res

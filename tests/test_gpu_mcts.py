@@ -112,3 +112,40 @@ def test_gpu_pack_records(orc, built_lib):
         vs = raw[i, 56 + 2 * A.REC_MOVES:].view("<u4")
         assert np.array_equal(mv[:c], res["moves"][i, :c]) and not mv[c:].any()
         assert np.array_equal(vs[:c], res["visits"][i, :c]) and not vs[c:].any()
+
+
+def test_gpu_selfplay_episode_vs_oracle(orc, built_lib):
+    """MCTS self-play (search -> first-max move -> pack -> gather) for several moves on Tablut
+    (BASELINE configs[3] rules): records and game states follow the oracle move for move."""
+    from alphazeroforhnefatafl_b200 import selfplay as SP
+    rules, fen = orc.preset_rules(A.PRESET_TABLUT), orc.preset_board(A.PRESET_TABLUT)
+    n, sims, moves = 48, 96, 10
+    ref_bv = orc.by_value(rules, 128)
+    with E.LockstepGames(rules, fen, n, 0, 128) as g:
+        g.set_game_id_base(777)
+        g.step_random(5, 30, auto_reset=False)       # diversify the starting positions
+        states = g.get_states()
+        sp = SP.SelfPlay(g, num_sims=sims)
+        all_recs = []
+        for mv in range(moves):
+            out = sp.move()
+            g.sync()
+            recs = SP.records_to_numpy(out)
+            ref = orc.mcts_search(rules, 128, states, sims, n_threads=8)
+            ongoing = (states["status"] == 0) & (ref["counts"] > 0)
+            assert len(recs) == int(ongoing.sum())
+            idx = np.nonzero(ongoing)[0]
+            plays = E.moves_to_plays(ref["moves"][np.arange(n), ref["best"]], 128)
+            nxt, fx = ref_bv.do_plays(states[ongoing], plays[ongoing])
+            for r, i, s2 in zip(recs, idx, nxt):
+                h = r["h"]
+                c = int(ref["counts"][i])
+                assert h["game_id"] == 777 + i and h["ply"] == states[i]["turn"] and h["n_moves"] == c
+                assert h["best"] == ref["best"][i] and h["status"] == s2["status"]
+                assert np.array_equal(r["moves"][:c], ref["moves"][i, :c])
+                assert np.array_equal(r["visits"][:c], ref["visits"][i, :c])
+            states[ongoing] = nxt
+            assert g.get_states().tobytes() == states.tobytes()
+            all_recs.append(recs)
+        z = SP.backfill_outcomes(np.concatenate(all_recs))
+        assert z.shape[0] == sum(len(r) for r in all_recs)
