@@ -2,6 +2,7 @@
 // (include/tafl.h) except the MCTS entry points (tafl_mcts.cu) and host text helpers
 // (tafl_host.cpp).  sm_100a only; no CPU path.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -91,8 +92,8 @@ k_step_moves(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states
 
 // The fused random-playout step (K4): count -> pick -> select -> apply -> outcome, `steps`
 // plies per launch with the state held in registers in between.
-template <class BB>
-__global__ void __launch_bounds__(STEP_BLOCK)
+template <class BB, int MINB>
+__global__ void __launch_bounds__(STEP_BLOCK, MINB)
 k_step_random(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
               uint32_t steps, int auto_reset, DevStats* __restrict__ stats) {
@@ -343,6 +344,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     cudaDeviceProp prop;
     TAFL_CREATE_TRY(cudaGetDeviceProperties(&prop, device));
     e->sm_count = prop.multiProcessorCount;
+    if (const char* v = std::getenv("TAFL_STEP_MINB")) e->step_minb = std::atoi(v);   // tuning knob (profiles/)
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_states, (size_t)n_games * sizeof(tafl_state)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_counts, (size_t)n_games * sizeof(uint32_t)));
@@ -502,8 +504,17 @@ int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int 
     uint32_t done = 0;
     while (done < n_steps) {
         const uint32_t chunk = (n_steps - done) < (uint32_t)spl ? (n_steps - done) : (uint32_t)spl;
-        TAFL_WIDTH_DISPATCH(e, (k_step_random<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(
-                                   cx, e->d_states, n, state_words(e->start), seed, e->game_id_base, e->ply, chunk, auto_reset, e->d_stats)));
+#define TAFL_STEP_LAUNCH(MINB)                                                                                   \
+    TAFL_WIDTH_DISPATCH(e, (k_step_random<BB, MINB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(            \
+                               cx, e->d_states, n, state_words(e->start), seed, e->game_id_base, e->ply, chunk, auto_reset, e->d_stats)))
+        switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
+            case 6: TAFL_STEP_LAUNCH(6); break;
+            case 8: TAFL_STEP_LAUNCH(8); break;
+            case 10: TAFL_STEP_LAUNCH(10); break;
+            case 12: TAFL_STEP_LAUNCH(12); break;
+            default: TAFL_STEP_LAUNCH(4); break;
+        }
+#undef TAFL_STEP_LAUNCH
         TAFL_LAUNCHED(e);
         e->ply += chunk;
         done += chunk;

@@ -35,6 +35,7 @@ struct tafl_engine {
     tafl::DevStats* d_stats = nullptr;
     unsigned long long* d_checksum = nullptr;
     uint64_t game_id_base = 0, ply = 0, launches = 0;
+    int step_minb = 4;                 // k_step_random variant: CTAs of 64 threads resident per SM
     // scratch for the by-value batch API (grown on demand)
     void* d_scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[6] = {0, 0, 0, 0, 0, 0};
