@@ -3,9 +3,13 @@
 //
 // TEST INFRASTRUCTURE ONLY (see the header of tafl_oracle.hpp).
 //
-// PARITY UNPINNED at this boundary: src/mcts.py has no tests and the Game/NNet adapter it
-// expects (action indexing, stringRepresentation, getGameEnded values, canonical form) does not
-// exist in the reference.  The build-defined choices are:
+// PARITY PIN: src/mcts.py has no tests of its own, but it is importable in the build container, so
+// tests/golden/make_mcts_reference_vectors.py runs the UNMODIFIED reference class over a Game/NNet
+// adapter served by the game oracle and freezes its visit counts / Q values / node counts in
+// tests/golden/mcts_reference_vectors.json; tests/test_mcts_reference_golden.py checks this
+// restatement against them bit for bit.  What the reference leaves undefined is the adapter
+// (action indexing, stringRepresentation, getGameEnded values, canonical form); the build-defined
+// choices, used identically by the adapter, are:
 //   * node identity = path from the root (tree, as in src/mcts.rs:9-32), not the transposition-
 //     merged dict of mcts.py:20-26 — a tafl state also carries side-to-move and repetition
 //     history, so "same board string" is not "same state";

@@ -1,0 +1,85 @@
+"""MCTS parity against outputs of the UNMODIFIED reference `src/mcts.py` (class MCTS), frozen in
+tests/golden/mcts_reference_vectors.json by tests/golden/make_mcts_reference_vectors.py (which
+imports the reference in the build container; the reference tree does not exist on the GPU box).
+
+* CPU: the C++ MCTS oracle (oracle/mcts_oracle.hpp) reproduces the reference's root visit counts
+  exactly and its Q values bit for bit  -> the oracle is pinned by reference outputs.
+* GPU: the CUDA search (tafl_mcts.cu through the C ABI) reproduces the same vectors: visit counts
+  bit-exact, Q within 1e-6 relative (BASELINE.json north_star) — asserted bit-exact as well.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from alphazeroforhnefatafl_b200 import _abi as A
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+with open(os.path.join(HERE, "golden", "mcts_reference_vectors.json")) as f:
+    GOLDEN = json.load(f)
+CASES = GOLDEN["cases"]
+IDS = ["%s-%d" % (c["name"], i) for i, c in enumerate(CASES)]
+Q_RTOL = 1e-6
+
+
+def root_of(case):
+    return np.frombuffer(bytes.fromhex(case["root_hex"]), A.STATE_DTYPE).copy()
+
+
+def expected(case):
+    return (np.array(case["visits"], np.uint32), np.array([float.fromhex(x) for x in case["q_hex"]], np.float64))
+
+
+def test_golden_file_shape():
+    assert len(CASES) >= 20
+    assert "UNMODIFIED reference" in GOLDEN["provenance"]
+    # the fixture exercises non-trivial arithmetic: some Q are non-zero and not +-1
+    mixed = sum(1 for c in CASES for x in c["q_hex"] if 0.0 < abs(float.fromhex(x)) < 1.0)
+    assert mixed > 100
+    for c in CASES:
+        assert sum(c["visits"]) == c["sims"] - 1          # mcts.py:83-102: first simulation expands the root
+
+
+@pytest.mark.parametrize("case", CASES, ids=IDS)
+def test_mcts_oracle_matches_reference_mcts_py(orc, case):
+    rules = orc.preset_rules(case["preset"])
+    got = orc.mcts_search(rules, case["width"], root_of(case), case["sims"], cpuct=case["cpuct"],
+                          draw_value=case["draw_value"])
+    n, q = expected(case)
+    c = case["count"]
+    assert int(got["counts"][0]) == c
+    assert np.array_equal(got["visits"][0, :c], n)
+    assert got["q"][0, :c].tobytes() == q.tobytes(), "Q differs from the reference in the last bits"
+    assert int(got["best"][0]) == int(np.argmax(n))       # first-max
+    # the oracle counts the root among the nodes; mcts.py's Es dict has one entry per node met
+    assert got["stats"].nodes == case["n_nodes"]
+
+
+@pytest.mark.gpu
+def test_gpu_mcts_matches_reference_mcts_py(orc, built_lib):
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for
+    groups = {}
+    for case in CASES:
+        key = (case["preset"], case["width"], case["sims"], case["cpuct"], case["draw_value"])
+        groups.setdefault(key, []).append(case)
+    checked = 0
+    for (preset, width, sims, cpuct, dv), cases in groups.items():
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        roots = np.concatenate([root_of(c) for c in cases])
+        with E.LockstepGames(rules, fen, len(cases), 0, width) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, cpuct, dv)
+            g.mcts_search()
+            got = g.mcts_results()
+        for i, case in enumerate(cases):
+            n, q = expected(case)
+            c = case["count"]
+            assert int(got["counts"][i]) == c
+            assert np.array_equal(got["visits"][i, :c], n), case["name"]
+            assert np.allclose(got["q"][i, :c], q, rtol=Q_RTOL, atol=0.0), case["name"]
+            assert got["q"][i, :c].tobytes() == q.tobytes(), case["name"]
+            assert int(got["best"][i]) == int(np.argmax(n))
+            checked += 1
+    assert checked == len(CASES)
