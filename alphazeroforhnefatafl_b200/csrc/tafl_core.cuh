@@ -218,14 +218,23 @@ TAFL_HD Rays piece_rays(const Ctx<BB>& cx, BB occ, int k, int row, int col) {
     return r;
 }
 
+// position of the j-th (0-based, ascending) set bit of m; caller guarantees j < popc(m).
+// Branch-free 5-level search on masked popcounts (no data-dependent loop: lanes stay converged).
+TAFL_HD int nth_bit32(uint32_t m, int j) {
+    int pos = 0;
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const int c = popc32((m >> pos) & ((1u << half) - 1u));
+        const bool up = j >= c;
+        j -= up ? c : 0;
+        pos += up ? half : 0;
+    }
+    return pos;
+}
 // j-th destination (distance ascending) of direction `dir` -> position along the line
 TAFL_HD int ray_nth(uint32_t m, int dir, int j) {
-    if ((dir & 1) == 0) {  // plus: ascending bit order
-        for (int i = 0; i < j; ++i) m &= m - 1;
-        return ctz32(m);
-    }
-    for (int i = 0; i < j; ++i) m &= ~(0x80000000u >> clz32(m));
-    return 31 - clz32(m);
+    // plus directions enumerate ascending positions, minus directions descending ones
+    return nth_bit32(m, (dir & 1) == 0 ? j : popc32(m) - 1 - j);
 }
 
 // Full legal-move list of the side to move, canonical order (game/main.rs:33-43).
@@ -267,14 +276,23 @@ TAFL_HD int gen_moves(const Ctx<BB>& cx, const tafl_state& st, tafl_move* out, i
 template <class BB>
 TAFL_HD bool side_can_play(const Ctx<BB>& cx, const Pos<BB>& p, int def_side) {
     BB empty = cx.board & ~p.occ();
+    // Fast path (almost always decides): some piece has an empty neighbour it may stop on.  The
+    // one-step test below does not depend on the direction, so the four directions fold into one
+    // dilation per piece class; only the hop over the empty throne needs the per-direction walk.
+    {
+        const int ks = def_side ? KIND_DS : KIND_AS;
+        const BB srcS = def_side ? p.dsold() : p.att;
+        if ((dilate4(cx, srcS) & empty & ~cx.dest_block[ks]).any()) return true;
+        if (def_side && (dilate4(cx, p.king()) & empty & ~cx.dest_block[KIND_K]).any()) return true;
+    }
     bool any = false;
-#pragma unroll
+#pragma unroll 1
     for (int kk = 0; kk < 2; ++kk) {
         int k = def_side ? (kk == 0 ? KIND_DS : KIND_K) : KIND_AS;
         if (!def_side && kk == 1) break;
         BB src = p.kind(k);
         BB ok = ~cx.dest_block[k];
-#pragma unroll
+#pragma unroll 1
         for (int d = 0; d < 4; ++d) {
             BB s1 = step_dir(cx, src, d) & empty;
             any |= (s1 & ok).any();
@@ -305,6 +323,12 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB>& cx, const Pos<BB>& p, int mover_de
     else if (to_c == N - 1) { horizontal = 0; away = -1; }
     else return false;
     const BB own = p.side(mover_def), opp = p.side(!mover_def), occ = p.occ();
+    {   // a wall starts with an enemy piece right beside `to` along the edge (logic.rs:485-522: any
+        // other first tile ends the search with cnt == 0), so most edge moves leave here
+        const BB tb0 = BB::bit(idx_of<BB>(to_r, to_c));
+        const BB along = horizontal ? (step_left(cx, tb0) | step_right(cx, tb0)) : (step_up(cx, tb0) | step_down(cx, tb0));
+        if (!(along & opp).any()) return false;
+    }
     const bool cmc = cx.rules.sw_corners_may_close != 0;
     BB wall = BB::zero();
     bool found = false;
@@ -349,38 +373,61 @@ TAFL_HD BB get_captures(const Ctx<BB>& cx, const Pos<BB>& p, int piece_def, int 
         const BB tob = BB::bit(idx_of<BB>(to_r, to_c));
         const BB opp = p.side(!piece_def);
         const BB kingb = p.king();
-        // king strength (logic.rs:225-245), from the nibble tile
-        const bool beside = (p.kbit & cx.throne_adj).any();
-        const bool strong = cx.rules.king_strength == TAFL_KING_STRONG ||
-                            (cx.rules.king_strength == TAFL_KING_STRONG_BY_THRONE &&
-                             (beside || (p.kbit & cx.throne).any()));
-        const BB hostK = hostile_set(cx, p, KIND_K);
-#pragma unroll
-        for (int d = 0; d < 4; ++d) {
-            BB n = step_dir(cx, tob, d);
-            if (!(n & opp).any()) continue;
-            const bool vking = (n & kingb).any();
-            const int vk = vking ? KIND_K : (piece_def ? KIND_AS : KIND_DS);
-            if (vking && beside && cx.sbt_special) {  // logic.rs:621-632
+        // the four neighbours of `to`, per direction (n = to + d)
+        const BB nVP = step_down(cx, tob), nVM = step_up(cx, tob), nHP = step_right(cx, tob), nHM = step_left(cx, tob);
+        // ---- soldier victims (logic.rs:634-646,675): custodial against the far tile, all four
+        // directions as masks.  X aligned to n: bit n is set iff the tile n + d is hostile to the
+        // victim; an off-board far tile is hostile iff hostility.edge says so (logic.rs:103-114).
+        {
+            const int vs = piece_def ? KIND_AS : KIND_DS;
+            const BB oppS = opp & ~kingb;
+            const BB host = hostile_set(cx, p, vs);
+            const bool eh = cx.edge_hostile[vs] != 0;
+            BB hit = (nVP & (step_up(cx, host) | (eh ? cx.rowL : BB::zero()))) |
+                     (nVM & (step_down(cx, host) | (eh ? cx.row0 : BB::zero()))) |
+                     (nHP & (step_left(cx, host) | (eh ? cx.colL : BB::zero()))) |
+                     (nHM & (step_right(cx, host) | (eh ? cx.col0 : BB::zero())));
+            caps = hit & oppS;
+        }
+        // ---- Linnaean capture (logic.rs:676-685, 859-879): the far tile is the throne holding the
+        // king and exactly 3 of the throne's neighbours are hostile to the king
+        if (cx.rules.linnaean_capture && !mover_def && p.kbit == cx.throne) {
+            const BB hostK = hostile_set(cx, p, KIND_K);
+            if ((cx.throne_adj & hostK).popc() == 3) {
+                const BB t = cx.throne;
+                caps = caps | (opp & ((nVP & step_up(cx, t)) | (nVM & step_down(cx, t)) | (nHP & step_left(cx, t)) |
+                                      (nHM & step_right(cx, t))));
+            }
+        }
+        // ---- king victim (rare: the king stands beside `to`)
+        if (((nVP | nVM | nHP | nHM) & kingb & opp).any()) {
+            // king strength (logic.rs:225-245), from the nibble tile
+            const bool beside = (p.kbit & cx.throne_adj).any();
+            const bool strong = cx.rules.king_strength == TAFL_KING_STRONG ||
+                                (cx.rules.king_strength == TAFL_KING_STRONG_BY_THRONE &&
+                                 (beside || (p.kbit & cx.throne).any()));
+            const BB hostK = hostile_set(cx, p, KIND_K);
+            const BB n = kingb;
+            const int d = (nVP & kingb).any() ? DIR_VP : (nVM & kingb).any() ? DIR_VM : (nHP & kingb).any() ? DIR_HP : DIR_HM;
+            bool taken = false;
+            if (beside && cx.sbt_special) {  // logic.rs:621-632
                 BB nb = dilate4(cx, n);
-                if (!(nb & ~cx.throne & ~hostK).any()) { caps = caps | n; continue; }
+                taken = !(nb & ~cx.throne & ~hostK).any();
             }
-            BB far = step_dir(cx, n, d);
-            const BB host = vking ? hostK : hostile_set(cx, p, vk);
-            const bool far_h = far.any() ? (far & host).any() : (cx.edge_hostile[vk] != 0);  // logic.rs:103-114
-            if (far_h) {
-                if (vking && strong) {  // logic.rs:647-674
-                    BB q1 = step_dir(cx, n, d < 2 ? DIR_HP : DIR_VP), q2 = step_dir(cx, n, d < 2 ? DIR_HM : DIR_VM);
-                    bool h1 = q1.any() ? (q1 & host).any() : (cx.edge_hostile[KIND_K] != 0);
-                    bool h2 = q2.any() ? (q2 & host).any() : (cx.edge_hostile[KIND_K] != 0);
-                    if (!(h1 && h2)) continue;
+            if (!taken) {
+                BB far = step_dir(cx, n, d);
+                const bool far_h = far.any() ? (far & hostK).any() : (cx.edge_hostile[KIND_K] != 0);  // logic.rs:103-114
+                if (far_h) {
+                    taken = true;
+                    if (strong) {  // logic.rs:647-674
+                        BB q1 = step_dir(cx, n, d < 2 ? DIR_HP : DIR_VP), q2 = step_dir(cx, n, d < 2 ? DIR_HM : DIR_VM);
+                        bool h1 = q1.any() ? (q1 & hostK).any() : (cx.edge_hostile[KIND_K] != 0);
+                        bool h2 = q2.any() ? (q2 & hostK).any() : (cx.edge_hostile[KIND_K] != 0);
+                        taken = h1 && h2;
+                    }
                 }
-                caps = caps | n;
-            } else if (cx.rules.linnaean_capture && !mover_def) {  // logic.rs:676-685, 859-879
-                if (far.any() && far == cx.throne && p.kbit == cx.throne &&
-                    (cx.throne_adj & hostK).popc() == 3)
-                    caps = caps | n;
             }
+            if (taken) caps = caps | n;
         }
     }
     BB walled;
@@ -441,6 +488,27 @@ TAFL_HD Encl<BB> find_enclosure(const Ctx<BB>& cx, const Pos<BB>& p, int r, int 
     e.boundary = nb & enclosing;
     e.found = true;
     return e;
+}
+// Exact pre-filter for the enclosure WIN test of get_game_outcome (logic.rs:720-734).  The win needs
+// the king's region (fillable = empty or defender) to hold EVERY defender and to avoid the abort
+// tiles (corners, and the edge under WithoutEdgeAccess).  If that holds, the region equals the union
+// of the components of all defenders — so when a fill started from all defenders at once reaches an
+// abort tile, either the king's region reaches it too (find_enclosure returns None) or some
+// defender lies outside it (the occupied count differs): no win either way.  The multi-source fill
+// escapes in a step or two in ordinary positions, where the single-source fill from the king needs
+// many; only a genuinely sealed position pays for the full test afterwards.
+template <class BB>
+TAFL_HD bool enclosure_win_possible(const Ctx<BB>& cx, const Pos<BB>& p, bool abort_on_edge) {
+    const BB fillable = (cx.board & ~p.occ()) | p.def;
+    const BB stop = (abort_on_edge ? cx.edge : BB::zero()) | cx.corners;
+    BB reg = p.def;
+    for (int it = 0; it < 128; ++it) {
+        if ((reg & stop).any()) return false;
+        BB grown = reg | (dilate4(cx, reg) & fillable);
+        if (grown == reg) break;
+        reg = grown;
+    }
+    return !(reg & stop).any();
 }
 // enclosure_secure (logic.rs:408-463)
 template <class BB>
@@ -524,7 +592,8 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB>& cx, const Pos<BB>& p, const tafl_sta
     const int N = cx.N;
     if (!mover_def) {
         if ((caps & p.kbit).any()) return TAFL_STATUS_WIN(TAFL_WIN_KING_CAPTURED, 0);
-        if (cx.rules.enclosure_win != TAFL_ENCL_NONE) {
+        if (cx.rules.enclosure_win != TAFL_ENCL_NONE &&
+            enclosure_win_possible(cx, p, cx.rules.enclosure_win == TAFL_ENCL_WITHOUT_EDGE_ACCESS)) {
             Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.def, p.att,
                                         cx.rules.enclosure_win == TAFL_ENCL_WITHOUT_EDGE_ACCESS, true);
             if (e.found && (e.region & p.occ()).popc() == p.def.popc() && enclosure_secure(cx, p, e, false, true))

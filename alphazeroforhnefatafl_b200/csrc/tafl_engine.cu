@@ -100,10 +100,13 @@ k_step_random(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ state
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t c_steps = 0, c_legal = 0, c_caps = 0;
     if (g < n) {
-        const tafl_state start = unpack_state(start_w.v[0], start_w.v[1], start_w.v[2], start_w.v[3]);
         tafl_state s = load_state(states + g);
         for (uint32_t i = 0; i < steps; ++i) {
-            StepEvt ev = random_step(cx, s, start, seed, gid_base + g, ply0 + i, auto_reset != 0);
+            if (s.status != TAFL_STATUS_ONGOING) {   // rare: only these lanes pay for the reset
+                if (!auto_reset) break;
+                s = unpack_state(start_w.v[0], start_w.v[1], start_w.v[2], start_w.v[3]);
+            }
+            StepEvt ev = random_step_ongoing(cx, s, seed, gid_base + g, ply0 + i);
             c_steps += ev.stepped;
             c_legal += ev.legal;
             c_caps += ev.caps;

@@ -158,16 +158,12 @@ struct StepEvt {
     uint8_t status;   // != 0: the game ended on this step
     uint32_t turn;
 };
+// one random ply of a game that is Ongoing (the caller has already reset a finished game)
 template <class BB>
-TAFL_HD StepEvt random_step(const Ctx<BB>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
-                            uint64_t ply, bool auto_reset) {
+TAFL_HD StepEvt random_step_ongoing(const Ctx<BB>& cx, tafl_state& s, uint64_t seed, uint64_t gid, uint64_t ply) {
     StepEvt ev;
     ev.stepped = ev.legal = ev.caps = ev.turn = 0;
     ev.status = 0;
-    if (s.status != TAFL_STATUS_ONGOING) {
-        if (!auto_reset) return ev;
-        s = start;
-    }
     const Pos<BB> p = load_pos(cx, s);
     const MoveSel<BB> ms = count_moves(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
     if (ms.total == 0) return ev;
@@ -180,6 +176,20 @@ TAFL_HD StepEvt random_step(const Ctx<BB>& cx, tafl_state& s, const tafl_state& 
     ev.status = s.status;
     ev.turn = s.turn;
     return ev;
+}
+template <class BB>
+TAFL_HD StepEvt random_step(const Ctx<BB>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
+                            uint64_t ply, bool auto_reset) {
+    if (s.status != TAFL_STATUS_ONGOING) {
+        if (!auto_reset) {
+            StepEvt ev;
+            ev.stepped = ev.legal = ev.caps = ev.turn = 0;
+            ev.status = 0;
+            return ev;
+        }
+        s = start;
+    }
+    return random_step_ongoing(cx, s, seed, gid, ply);
 }
 
 struct StepStats {
