@@ -66,6 +66,8 @@ def lib():
         "tafl_engine_stream": (vp, [vp]),
         "tafl_engine_sync": (C.c_int, [vp]),
         "tafl_launch_count": (C.c_uint64, [vp]),
+        "tafl_engine_spec": (C.c_int, [vp]),
+        "tafl_engine_force_generic": (C.c_int, [vp, C.c_int]),
         "tafl_reset": (C.c_int, [vp, vp, C.c_uint32]),
         "tafl_set_states": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32]),
         "tafl_get_states": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32]),

@@ -15,6 +15,8 @@
 //   game/main.rs     get_all_possible_moves (canonical move order)
 #pragma once
 #include "../../include/tafl.h"
+#include <string.h>
+
 #include "tafl_bb.cuh"
 
 namespace tafl {
@@ -26,7 +28,68 @@ enum { DIR_VP = 0, DIR_VM = 1, DIR_HP = 2, DIR_HM = 3 };  // play.rs:157,166-183
 // Ctx: `GameLogic` (logic.rs:61-72) = rules + board geometry, pre-digested into masks on the
 // host (tafl_ctx.hpp) and handed to every kernel as a __grid_constant__ parameter.
 // ---------------------------------------------------------------------------------------------
-template <class BB>
+// Kernel specialisations: for the reference's presets (preset.rs:12-134) every rule flag below is
+// a compile-time constant, so the rule branches fold and the hot kernels shrink.  SPEC_GENERIC
+// reads the same flags from the Ctx at run time and serves every other Ruleset / board size.  The
+// engine only picks a specialisation after spec_matches() has compared each constant with the
+// run-time Ctx built from the caller's Ruleset (tafl_ctx.hpp), so a table typo can cost speed but
+// never correctness.
+enum { SPEC_GENERIC = 0, SPEC_COPENHAGEN = 1, SPEC_TABLUT = 2, SPEC_BRANDUBH = 3, SPEC_COUNT = 4 };
+
+template <int SP> struct SpecTraits;
+// rules::COPENHAGEN + boards::COPENHAGEN (preset.rs:12-34,127-128)
+template <> struct SpecTraits<SPEC_COPENHAGEN> {
+    static constexpr int N = 11;
+    TAFL_HD static constexpr bool noentry(int k) { return k != KIND_K; }      // ThroneRule::KingEntry
+    TAFL_HD static constexpr bool pass_block(int) { return false; }
+    TAFL_HD static constexpr bool may_corner(int k) { return k == KIND_K; }   // may_enter_corners: King
+    TAFL_HD static constexpr bool slow(int) { return false; }
+    TAFL_HD static constexpr bool edge_hostile(int) { return false; }
+    TAFL_HD static constexpr bool sw_caps(int k) { return k != KIND_K; }      // shieldwall captures Soldier
+    static constexpr bool king_hostile = true, king_captures = true;          // KingAttack::Armed
+    static constexpr bool sbt_special = false;                                // KingStrength::Strong
+    static constexpr int king_strength = TAFL_KING_STRONG;
+    static constexpr bool shieldwall = true, sw_cmc = true, linnaean = false, exit_fort = true, edge_escape = false;
+    static constexpr int enclosure_win = TAFL_ENCL_WITHOUT_EDGE_ACCESS;
+    static constexpr bool rep_enabled = true, rep_is_loss = true, draw_no_plays = false;
+    static constexpr uint32_t n_reps = 3;
+};
+// rules::TABLUT (Linnaeus) + boards::TABLUT (preset.rs:80-100,134)
+template <> struct SpecTraits<SPEC_TABLUT> {
+    static constexpr int N = 9;
+    TAFL_HD static constexpr bool noentry(int) { return true; }               // ThroneRule::NoEntry
+    TAFL_HD static constexpr bool pass_block(int) { return false; }
+    TAFL_HD static constexpr bool may_corner(int) { return true; }
+    TAFL_HD static constexpr bool slow(int) { return false; }
+    TAFL_HD static constexpr bool edge_hostile(int) { return false; }
+    TAFL_HD static constexpr bool sw_caps(int) { return false; }
+    static constexpr bool king_hostile = true, king_captures = true;
+    static constexpr bool sbt_special = true;                                 // StrongByThrone + NoEntry
+    static constexpr int king_strength = TAFL_KING_STRONG_BY_THRONE;
+    static constexpr bool shieldwall = false, sw_cmc = false, linnaean = true, exit_fort = false, edge_escape = true;
+    static constexpr int enclosure_win = TAFL_ENCL_NONE;
+    static constexpr bool rep_enabled = true, rep_is_loss = false, draw_no_plays = true;
+    static constexpr uint32_t n_reps = 3;
+};
+// rules::BRANDUBH (Federation) + boards::BRANDUBH (preset.rs:36-56,130)
+template <> struct SpecTraits<SPEC_BRANDUBH> {
+    static constexpr int N = 7;
+    TAFL_HD static constexpr bool noentry(int k) { return k != KIND_K; }      // ThroneRule::KingEntry
+    TAFL_HD static constexpr bool pass_block(int) { return false; }
+    TAFL_HD static constexpr bool may_corner(int k) { return k == KIND_K; }
+    TAFL_HD static constexpr bool slow(int) { return false; }
+    TAFL_HD static constexpr bool edge_hostile(int) { return false; }
+    TAFL_HD static constexpr bool sw_caps(int) { return false; }
+    static constexpr bool king_hostile = true, king_captures = true;
+    static constexpr bool sbt_special = true;                                 // StrongByThrone + KingEntry
+    static constexpr int king_strength = TAFL_KING_STRONG_BY_THRONE;
+    static constexpr bool shieldwall = false, sw_cmc = false, linnaean = false, exit_fort = false, edge_escape = false;
+    static constexpr int enclosure_win = TAFL_ENCL_WITHOUT_EDGE_ACCESS;
+    static constexpr bool rep_enabled = true, rep_is_loss = true, draw_no_plays = false;
+    static constexpr uint32_t n_reps = 3;
+};
+
+template <class BB, int SP = SPEC_GENERIC>
 struct Ctx {
     BB board;        // every in-bounds tile
     BB edge;         // geometry.rs:111-116
@@ -50,7 +113,70 @@ struct Ctx {
     uint8_t sbt_special;       // StrongByThrone && throne rule in {NoEntry, KingEntry} (logic.rs:621-625)
     uint8_t _pad[5];
     tafl_rules rules;
+
+    // rule flags: run-time fields for SPEC_GENERIC, compile-time constants otherwise
+#define TAFL_FLAG_K(name)                                                   \
+    TAFL_HD bool f_##name(int k) const {                                    \
+        if constexpr (SP == SPEC_GENERIC) return name[k] != 0;              \
+        else return SpecTraits<SP>::name(k);                                \
+    }
+    TAFL_FLAG_K(noentry) TAFL_FLAG_K(pass_block) TAFL_FLAG_K(may_corner) TAFL_FLAG_K(slow) TAFL_FLAG_K(edge_hostile)
+    TAFL_FLAG_K(sw_caps)
+#undef TAFL_FLAG_K
+#define TAFL_FLAG_0(acc, field, trait)                                      \
+    TAFL_HD auto acc() const {                                              \
+        if constexpr (SP == SPEC_GENERIC) return field;                     \
+        else return SpecTraits<SP>::trait;                                  \
+    }
+    TAFL_FLAG_0(f_king_hostile, king_hostile != 0, king_hostile)
+    TAFL_FLAG_0(f_king_captures, king_captures != 0, king_captures)
+    TAFL_FLAG_0(f_sbt_special, sbt_special != 0, sbt_special)
+    TAFL_FLAG_0(r_king_strength, (int)rules.king_strength, king_strength)
+    TAFL_FLAG_0(r_shieldwall_enabled, rules.shieldwall_enabled != 0, shieldwall)
+    TAFL_FLAG_0(r_sw_corners_may_close, rules.sw_corners_may_close != 0, sw_cmc)
+    TAFL_FLAG_0(r_linnaean_capture, rules.linnaean_capture != 0, linnaean)
+    TAFL_FLAG_0(r_exit_fort, rules.exit_fort != 0, exit_fort)
+    TAFL_FLAG_0(r_edge_escape, rules.edge_escape != 0, edge_escape)
+    TAFL_FLAG_0(r_enclosure_win, (int)rules.enclosure_win, enclosure_win)
+    TAFL_FLAG_0(r_repetition_enabled, rules.repetition_enabled != 0, rep_enabled)
+    TAFL_FLAG_0(r_repetition_is_loss, rules.repetition_is_loss != 0, rep_is_loss)
+    TAFL_FLAG_0(r_draw_on_no_plays, rules.draw_on_no_plays != 0, draw_no_plays)
+    TAFL_FLAG_0(r_n_repetitions, (uint32_t)rules.n_repetitions, n_reps)
+    TAFL_FLAG_0(n, (int)N, N)
+#undef TAFL_FLAG_0
+    TAFL_HD int m() const { return n() / 2; }
 };
+
+// does the run-time Ctx (built from the caller's Ruleset and board size) equal the constants of SP?
+template <int SP, class BB>
+inline bool spec_matches(const Ctx<BB, SPEC_GENERIC>& c) {
+    using T = SpecTraits<SP>;
+    bool ok = c.N == T::N && c.mid == T::N / 2;
+    for (int k = 0; k < 3; ++k)
+        ok = ok && (c.noentry[k] != 0) == T::noentry(k) && (c.pass_block[k] != 0) == T::pass_block(k) &&
+             (c.may_corner[k] != 0) == T::may_corner(k) && (c.slow[k] != 0) == T::slow(k) &&
+             (c.edge_hostile[k] != 0) == T::edge_hostile(k) &&
+             // shieldwall.captures only matters when the rule is on
+             (!T::shieldwall || (c.sw_caps[k] != 0) == T::sw_caps(k));
+    const tafl_rules& r = c.rules;
+    ok = ok && (c.king_hostile != 0) == T::king_hostile && (c.king_captures != 0) == T::king_captures &&
+         (c.sbt_special != 0) == T::sbt_special && (int)r.king_strength == T::king_strength &&
+         (r.shieldwall_enabled != 0) == T::shieldwall && (!T::shieldwall || (r.sw_corners_may_close != 0) == T::sw_cmc) &&
+         (r.linnaean_capture != 0) == T::linnaean && (r.exit_fort != 0) == T::exit_fort &&
+         (r.edge_escape != 0) == T::edge_escape && (int)r.enclosure_win == T::enclosure_win &&
+         (r.repetition_enabled != 0) == T::rep_enabled &&
+         (!T::rep_enabled || ((r.repetition_is_loss != 0) == T::rep_is_loss && r.n_repetitions == T::n_reps)) &&
+         (r.draw_on_no_plays != 0) == T::draw_no_plays;
+    return ok;
+}
+// same bytes, different compile-time view
+template <int SP, class BB>
+inline Ctx<BB, SP> spec_cast(const Ctx<BB, SPEC_GENERIC>& c) {
+    static_assert(sizeof(Ctx<BB, SP>) == sizeof(Ctx<BB, SPEC_GENERIC>), "Ctx layout is independent of SP");
+    Ctx<BB, SP> out;
+    memcpy(&out, &c, sizeof(out));
+    return out;
+}
 
 template <class BB>
 struct Pos {
@@ -66,9 +192,9 @@ struct Pos {
 
 template <class BB> TAFL_HD int idx_of(int r, int c) { return r * BB::STRIDE + c; }
 
-template <class BB>
-TAFL_HD BB king_bit(const Ctx<BB>& cx, int kr, int kc) {
-    return (kr < cx.N && kc < cx.N) ? BB::bit(idx_of<BB>(kr, kc)) : BB::zero();
+template <class BB, int SP>
+TAFL_HD BB king_bit(const Ctx<BB, SP>& cx, int kr, int kc) {
+    return (kr < cx.n() && kc < cx.n()) ? BB::bit(idx_of<BB>(kr, kc)) : BB::zero();
 }
 
 template <class BB> struct Nib;
@@ -110,8 +236,8 @@ template <> struct Nib<BB128> {
     }
 };
 
-template <class BB>
-TAFL_HD Pos<BB> load_pos(const Ctx<BB>& cx, const tafl_state& s) {
+template <class BB, int SP>
+TAFL_HD Pos<BB> load_pos(const Ctx<BB, SP>& cx, const tafl_state& s) {
     Pos<BB> p;
     Nib<BB>::load(s, p);
     p.kbit = king_bit(cx, p.kr, p.kc);
@@ -121,14 +247,14 @@ template <class BB>
 TAFL_HD void store_pos(const Pos<BB>& p, tafl_state& s) { Nib<BB>::store(p, s); }
 
 // one-tile steps of a tile set, results clipped to the board
-template <class BB> TAFL_HD BB step_up(const Ctx<BB>&, BB x) { return x.template shr<BB::STRIDE>(); }              // row-1
-template <class BB> TAFL_HD BB step_down(const Ctx<BB>& cx, BB x) { return x.template shl<BB::STRIDE>() & cx.board; }  // row+1
-template <class BB> TAFL_HD BB step_left(const Ctx<BB>& cx, BB x) { return x.template shr<1>() & cx.not_colL; }     // col-1
-template <class BB> TAFL_HD BB step_right(const Ctx<BB>& cx, BB x) { return x.template shl<1>() & cx.not_col0; }    // col+1
-template <class BB> TAFL_HD BB dilate4(const Ctx<BB>& cx, BB x) {
+template <class BB, int SP> TAFL_HD BB step_up(const Ctx<BB, SP>&, BB x) { return x.template shr<BB::STRIDE>(); }              // row-1
+template <class BB, int SP> TAFL_HD BB step_down(const Ctx<BB, SP>& cx, BB x) { return x.template shl<BB::STRIDE>() & cx.board; }  // row+1
+template <class BB, int SP> TAFL_HD BB step_left(const Ctx<BB, SP>& cx, BB x) { return x.template shr<1>() & cx.not_colL; }     // col-1
+template <class BB, int SP> TAFL_HD BB step_right(const Ctx<BB, SP>& cx, BB x) { return x.template shl<1>() & cx.not_col0; }    // col+1
+template <class BB, int SP> TAFL_HD BB dilate4(const Ctx<BB, SP>& cx, BB x) {
     return step_up(cx, x) | step_down(cx, x) | step_left(cx, x) | step_right(cx, x);
 }
-template <class BB> TAFL_HD BB step_dir(const Ctx<BB>& cx, BB x, int dir) {
+template <class BB, int SP> TAFL_HD BB step_dir(const Ctx<BB, SP>& cx, BB x, int dir) {
     switch (dir) {
         case DIR_VP: return step_down(cx, x);
         case DIR_VM: return step_up(cx, x);
@@ -146,27 +272,27 @@ TAFL_HD int kind_at(const Pos<BB>& p, BB b) {
 }
 
 // tile_hostile (logic.rs:85-99) as a tile set, for a victim of kind vk
-template <class BB>
-TAFL_HD BB hostile_set(const Ctx<BB>& cx, const Pos<BB>& p, int vk) {
+template <class BB, int SP>
+TAFL_HD BB hostile_set(const Ctx<BB, SP>& cx, const Pos<BB>& p, int vk) {
     BB empty = cx.board & ~p.occ();
-    BB pieces = (vk == KIND_AS) ? (cx.king_hostile ? p.def : p.dsold()) : p.att;
+    BB pieces = (vk == KIND_AS) ? (cx.f_king_hostile() ? p.def : p.dsold()) : p.att;
     return pieces | (empty & cx.sh[vk]);
 }
 
 // ---------------------------------------------------------------------------------------------
 // Rays of one piece, in "line space" (bit i of a line word = i-th tile of the row / column).
 // ---------------------------------------------------------------------------------------------
-template <class BB>
-TAFL_HD uint32_t extract_row(const Ctx<BB>& cx, BB x, int row) {
-    return x.extract32(row * BB::STRIDE) & ((1u << cx.N) - 1u);
+template <class BB, int SP>
+TAFL_HD uint32_t extract_row(const Ctx<BB, SP>& cx, BB x, int row) {
+    return x.extract32(row * BB::STRIDE) & ((1u << cx.n()) - 1u);
 }
-template <class BB>
-TAFL_HD uint32_t extract_col(const Ctx<BB>& cx, BB x, int col) {
+template <class BB, int SP>
+TAFL_HD uint32_t extract_col(const Ctx<BB, SP>& cx, BB x, int col) {
     BB t = x.shrv(col);
     uint32_t out = 0;
 #pragma unroll
     for (int i = 0; i < 11; ++i) {
-        if (i < cx.N) out |= (uint32_t)t.test(i * BB::STRIDE) << i;
+        if (i < cx.n()) out |= (uint32_t)t.test(i * BB::STRIDE) << i;
     }
     return out;
 }
@@ -178,10 +304,10 @@ struct Rays {
 
 // ValidPlayIterator (play.rs:189-225) + validate_play_for_side (logic.rs:159-214) for the piece
 // of kind `k` on (row, col): the set of tiles it may move to, per direction.
-template <class BB>
-TAFL_HD Rays piece_rays(const Ctx<BB>& cx, BB occ, int k, int row, int col) {
+template <class BB, int SP>
+TAFL_HD Rays piece_rays(const Ctx<BB, SP>& cx, BB occ, int k, int row, int col) {
     Rays r;
-    const int N = cx.N, mid = cx.mid;
+    const int N = cx.n(), mid = cx.m();
     const uint32_t full = (1u << N) - 1u;
 #pragma unroll
     for (int ax = 0; ax < 2; ++ax) {
@@ -197,16 +323,16 @@ TAFL_HD Rays piece_rays(const Ctx<BB>& cx, BB occ, int k, int row, int col) {
         int top = 32 - clz32(y);
         uint32_t mm = ((1u << p) - 1u) & ~((1u << top) - 1u);
         const bool has_throne = (line == mid);
-        if (has_throne && cx.pass_block[k]) {  // logic.rs:194-200: may reach, not cross, the throne
+        if (has_throne && cx.f_pass_block(k)) {  // logic.rs:194-200: may reach, not cross, the throne
             if (p < mid) mp &= (2u << mid) - 1u;
             if (p > mid) mm &= ~((1u << mid) - 1u);
         }
         uint32_t blocked = 0;
-        if (has_throne && cx.noentry[k]) blocked |= 1u << mid;                                   // logic.rs:201-206
-        if ((line == 0 || line == N - 1) && !cx.may_corner[k]) blocked |= 1u | (1u << (N - 1));   // logic.rs:190-193
+        if (has_throne && cx.f_noentry(k)) blocked |= 1u << mid;                                   // logic.rs:201-206
+        if ((line == 0 || line == N - 1) && !cx.f_may_corner(k)) blocked |= 1u | (1u << (N - 1));   // logic.rs:190-193
         mp &= ~blocked;
         mm &= ~blocked;
-        if (cx.slow[k]) {  // logic.rs:207-210 (a skipped throne does not extend a slow piece's reach)
+        if (cx.f_slow(k)) {  // logic.rs:207-210 (a skipped throne does not extend a slow piece's reach)
             mp &= 1u << (p + 1);
             mm &= (p > 0) ? (1u << (p - 1)) : 0u;
         }
@@ -239,8 +365,8 @@ TAFL_HD int ray_nth(uint32_t m, int dir, int j) {
 
 // Full legal-move list of the side to move, canonical order (game/main.rs:33-43).
 // Simple per-piece generator; the kernels use it for list materialisation.
-template <class BB>
-TAFL_HD int gen_moves_side(const Ctx<BB>& cx, const Pos<BB>& p, int def_side, tafl_move* out, int cap) {
+template <class BB, int SP>
+TAFL_HD int gen_moves_side(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side, tafl_move* out, int cap) {
     BB own = p.side(def_side);
     BB occ = p.occ();
     int n = 0;
@@ -265,16 +391,16 @@ TAFL_HD int gen_moves_side(const Ctx<BB>& cx, const Pos<BB>& p, int def_side, ta
     }
     return n;
 }
-template <class BB>
-TAFL_HD int gen_moves(const Ctx<BB>& cx, const tafl_state& st, tafl_move* out, int cap) {
+template <class BB, int SP>
+TAFL_HD int gen_moves(const Ctx<BB, SP>& cx, const tafl_state& st, tafl_move* out, int cap) {
     if (st.status != TAFL_STATUS_ONGOING) return 0;  // logic.rs:165-167
     Pos<BB> p = load_pos(cx, st);
     return gen_moves_side(cx, p, (st.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, out, cap);
 }
 
 // side_can_play (logic.rs:837-846): does any piece of the side have a legal play?
-template <class BB>
-TAFL_HD bool side_can_play(const Ctx<BB>& cx, const Pos<BB>& p, int def_side) {
+template <class BB, int SP>
+TAFL_HD bool side_can_play(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side) {
     BB empty = cx.board & ~p.occ();
     // Fast path (almost always decides): some piece has an empty neighbour it may stop on.  The
     // one-step test below does not depend on the direction, so the four directions fold into one
@@ -296,7 +422,7 @@ TAFL_HD bool side_can_play(const Ctx<BB>& cx, const Pos<BB>& p, int def_side) {
         for (int d = 0; d < 4; ++d) {
             BB s1 = step_dir(cx, src, d) & empty;
             any |= (s1 & ok).any();
-            if (cx.noentry[k] && !cx.slow[k]) {  // hop over the empty throne (play.rs:208-211)
+            if (cx.f_noentry(k) && !cx.f_slow(k)) {  // hop over the empty throne (play.rs:208-211)
                 BB s2 = step_dir(cx, s1 & cx.throne, d) & empty & ok;
                 any |= s2.any();
             }
@@ -310,11 +436,11 @@ TAFL_HD bool side_can_play(const Ctx<BB>& cx, const Pos<BB>& p, int def_side) {
 // ---------------------------------------------------------------------------------------------
 // detect_shieldwall (logic.rs:535-569) + dir_sw_search (logic.rs:471-530).
 // `mover_def` is state.side_to_play.  Returns true for Some(..) and the captured tiles in *caps.
-template <class BB>
-TAFL_HD bool detect_shieldwall(const Ctx<BB>& cx, const Pos<BB>& p, int mover_def, int to_r, int to_c, BB* caps) {
+template <class BB, int SP>
+TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int mover_def, int to_r, int to_c, BB* caps) {
     *caps = BB::zero();
-    if (!cx.rules.shieldwall_enabled) return false;
-    const int N = cx.N;
+    if (!cx.r_shieldwall_enabled()) return false;
+    const int N = cx.n();
     if (to_r < 0 || to_c < 0 || to_r >= N || to_c >= N) return false;
     int horizontal, away;  // away: +1 / -1 along the other axis
     if (to_r == 0) { horizontal = 1; away = 1; }
@@ -329,7 +455,7 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB>& cx, const Pos<BB>& p, int mover_de
         const BB along = horizontal ? (step_left(cx, tb0) | step_right(cx, tb0)) : (step_up(cx, tb0) | step_down(cx, tb0));
         if (!(along & opp).any()) return false;
     }
-    const bool cmc = cx.rules.sw_corners_may_close != 0;
+    const bool cmc = cx.r_sw_corners_may_close() != 0;
     BB wall = BB::zero();
     bool found = false;
     for (int dd = 0; dd < 2 && !found; ++dd) {
@@ -355,21 +481,21 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB>& cx, const Pos<BB>& p, int mover_de
     if (!found) return false;
     BB keep = BB::zero();
     const int osk = mover_def ? KIND_AS : KIND_DS;
-    if (cx.sw_caps[osk]) keep = keep | ~p.kbit;
-    if (cx.sw_caps[KIND_K]) keep = keep | p.kbit;
+    if (cx.f_sw_caps(osk)) keep = keep | ~p.kbit;
+    if (cx.f_sw_caps(KIND_K)) keep = keep | p.kbit;
     *caps = wall & keep;
     return true;
 }
 
 // get_captures (logic.rs:604-699) on the post-move board.  piece_def / piece_kind describe the
 // moving piece, mover_def is state.side_to_play (used by shield wall and Linnaean capture).
-template <class BB>
-TAFL_HD BB get_captures(const Ctx<BB>& cx, const Pos<BB>& p, int piece_def, int piece_kind, int mover_def,
+template <class BB, int SP>
+TAFL_HD BB get_captures(const Ctx<BB, SP>& cx, const Pos<BB>& p, int piece_def, int piece_kind, int mover_def,
                         int to_r, int to_c) {
     BB caps = BB::zero();
-    const int N = cx.N;
+    const int N = cx.n();
     const bool to_in = to_r >= 0 && to_c >= 0 && to_r < N && to_c < N;
-    if (to_in && (piece_kind != KIND_K || cx.king_captures)) {
+    if (to_in && (piece_kind != KIND_K || cx.f_king_captures())) {
         const BB tob = BB::bit(idx_of<BB>(to_r, to_c));
         const BB opp = p.side(!piece_def);
         const BB kingb = p.king();
@@ -382,7 +508,7 @@ TAFL_HD BB get_captures(const Ctx<BB>& cx, const Pos<BB>& p, int piece_def, int 
             const int vs = piece_def ? KIND_AS : KIND_DS;
             const BB oppS = opp & ~kingb;
             const BB host = hostile_set(cx, p, vs);
-            const bool eh = cx.edge_hostile[vs] != 0;
+            const bool eh = cx.f_edge_hostile(vs) != 0;
             BB hit = (nVP & (step_up(cx, host) | (eh ? cx.rowL : BB::zero()))) |
                      (nVM & (step_down(cx, host) | (eh ? cx.row0 : BB::zero()))) |
                      (nHP & (step_left(cx, host) | (eh ? cx.colL : BB::zero()))) |
@@ -391,7 +517,7 @@ TAFL_HD BB get_captures(const Ctx<BB>& cx, const Pos<BB>& p, int piece_def, int 
         }
         // ---- Linnaean capture (logic.rs:676-685, 859-879): the far tile is the throne holding the
         // king and exactly 3 of the throne's neighbours are hostile to the king
-        if (cx.rules.linnaean_capture && !mover_def && p.kbit == cx.throne) {
+        if (cx.r_linnaean_capture() && !mover_def && p.kbit == cx.throne) {
             const BB hostK = hostile_set(cx, p, KIND_K);
             if ((cx.throne_adj & hostK).popc() == 3) {
                 const BB t = cx.throne;
@@ -403,26 +529,26 @@ TAFL_HD BB get_captures(const Ctx<BB>& cx, const Pos<BB>& p, int piece_def, int 
         if (((nVP | nVM | nHP | nHM) & kingb & opp).any()) {
             // king strength (logic.rs:225-245), from the nibble tile
             const bool beside = (p.kbit & cx.throne_adj).any();
-            const bool strong = cx.rules.king_strength == TAFL_KING_STRONG ||
-                                (cx.rules.king_strength == TAFL_KING_STRONG_BY_THRONE &&
+            const bool strong = cx.r_king_strength() == TAFL_KING_STRONG ||
+                                (cx.r_king_strength() == TAFL_KING_STRONG_BY_THRONE &&
                                  (beside || (p.kbit & cx.throne).any()));
             const BB hostK = hostile_set(cx, p, KIND_K);
             const BB n = kingb;
             const int d = (nVP & kingb).any() ? DIR_VP : (nVM & kingb).any() ? DIR_VM : (nHP & kingb).any() ? DIR_HP : DIR_HM;
             bool taken = false;
-            if (beside && cx.sbt_special) {  // logic.rs:621-632
+            if (beside && cx.f_sbt_special()) {  // logic.rs:621-632
                 BB nb = dilate4(cx, n);
                 taken = !(nb & ~cx.throne & ~hostK).any();
             }
             if (!taken) {
                 BB far = step_dir(cx, n, d);
-                const bool far_h = far.any() ? (far & hostK).any() : (cx.edge_hostile[KIND_K] != 0);  // logic.rs:103-114
+                const bool far_h = far.any() ? (far & hostK).any() : (cx.f_edge_hostile(KIND_K) != 0);  // logic.rs:103-114
                 if (far_h) {
                     taken = true;
                     if (strong) {  // logic.rs:647-674
                         BB q1 = step_dir(cx, n, d < 2 ? DIR_HP : DIR_VP), q2 = step_dir(cx, n, d < 2 ? DIR_HM : DIR_VM);
-                        bool h1 = q1.any() ? (q1 & hostK).any() : (cx.edge_hostile[KIND_K] != 0);
-                        bool h2 = q2.any() ? (q2 & hostK).any() : (cx.edge_hostile[KIND_K] != 0);
+                        bool h1 = q1.any() ? (q1 & hostK).any() : (cx.f_edge_hostile(KIND_K) != 0);
+                        bool h2 = q2.any() ? (q2 & hostK).any() : (cx.f_edge_hostile(KIND_K) != 0);
                         taken = h1 && h2;
                     }
                 }
@@ -461,14 +587,14 @@ TAFL_HD BB pieceset_bb(const Pos<BB>& p, uint16_t set) {
 // find_enclosure (logic.rs:309-401).  The reference's span fill visits exactly the 4-connected
 // component of fillable tiles (empty or `enclosed` pieces) around the start and probes exactly
 // that component's 4-neighbourhood, so the result is computed by mask dilation.
-template <class BB>
-TAFL_HD Encl<BB> find_enclosure(const Ctx<BB>& cx, const Pos<BB>& p, int r, int c, BB enclosed, BB enclosing,
+template <class BB, int SP>
+TAFL_HD Encl<BB> find_enclosure(const Ctx<BB, SP>& cx, const Pos<BB>& p, int r, int c, BB enclosed, BB enclosing,
                                 bool abort_on_edge, bool abort_on_corner) {
     Encl<BB> e;
     e.region = BB::zero();
     e.boundary = BB::zero();
     e.found = false;
-    if (r < 0 || c < 0 || r >= cx.N || c >= cx.N) return e;
+    if (r < 0 || c < 0 || r >= cx.n() || c >= cx.n()) return e;
     const BB occ = p.occ();
     const BB fillable = (cx.board & ~occ) | enclosed;
     const BB neither = occ & ~enclosed & ~enclosing;
@@ -497,8 +623,8 @@ TAFL_HD Encl<BB> find_enclosure(const Ctx<BB>& cx, const Pos<BB>& p, int r, int 
 // defender lies outside it (the occupied count differs): no win either way.  The multi-source fill
 // escapes in a step or two in ordinary positions, where the single-source fill from the king needs
 // many; only a genuinely sealed position pays for the full test afterwards.
-template <class BB>
-TAFL_HD bool enclosure_win_possible(const Ctx<BB>& cx, const Pos<BB>& p, bool abort_on_edge) {
+template <class BB, int SP>
+TAFL_HD bool enclosure_win_possible(const Ctx<BB, SP>& cx, const Pos<BB>& p, bool abort_on_edge) {
     const BB fillable = (cx.board & ~p.occ()) | p.def;
     const BB stop = (abort_on_edge ? cx.edge : BB::zero()) | cx.corners;
     BB reg = p.def;
@@ -511,8 +637,8 @@ TAFL_HD bool enclosure_win_possible(const Ctx<BB>& cx, const Pos<BB>& p, bool ab
     return !(reg & stop).any();
 }
 // enclosure_secure (logic.rs:408-463)
-template <class BB>
-TAFL_HD bool enclosure_secure(const Ctx<BB>& cx, const Pos<BB>& p, const Encl<BB>& e, bool inside_safe,
+template <class BB, int SP>
+TAFL_HD bool enclosure_secure(const Ctx<BB, SP>& cx, const Pos<BB>& p, const Encl<BB>& e, bool inside_safe,
                               bool outside_safe) {
     if (inside_safe && outside_safe) return true;
     const BB occ = p.occ();
@@ -526,7 +652,7 @@ TAFL_HD bool enclosure_secure(const Ctx<BB>& cx, const Pos<BB>& p, const Encl<BB
         const int ek = (k == KIND_AS) ? KIND_DS : KIND_AS;  // hostile soldier (logic.rs:426)
         const BB hostile = hostile_set(cx, p, k);
         const BB prot = (safe_zone & ~cx.sh[k]) | (cx.board & ~hostile & (occ | cx.dest_block[ek]));
-        const bool oob_ok = !cx.edge_hostile[k];
+        const bool oob_ok = !cx.f_edge_hostile(k);
         // value of `prot` at the four neighbours, aligned to the boundary tile
         BB up = prot.template shl<BB::STRIDE>() | (oob_ok ? cx.row0 : BB::zero());           // neighbour row-1
         BB down = prot.template shr<BB::STRIDE>() | (oob_ok ? cx.rowL : BB::zero());         // neighbour row+1
@@ -538,9 +664,9 @@ TAFL_HD bool enclosure_secure(const Ctx<BB>& cx, const Pos<BB>& p, const Encl<BB
     return ok;
 }
 // detect_exit_fort (logic.rs:572-601)
-template <class BB>
-TAFL_HD bool detect_exit_fort(const Ctx<BB>& cx, const Pos<BB>& p) {
-    const int N = cx.N;
+template <class BB, int SP>
+TAFL_HD bool detect_exit_fort(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
+    const int N = cx.n();
     if (!(p.kr == 0 || p.kr == N - 1 || p.kc == 0 || p.kc == N - 1)) return false;
     if (!p.kbit.any()) return false;
     // enclosed = PieceSet::from(King), enclosing = PieceSet::from(Defender); attackers are "neither"
@@ -585,17 +711,17 @@ TAFL_HD void track_play(tafl_state& s, uint32_t rec, int def_side, bool captures
 // ---------------------------------------------------------------------------------------------
 // get_game_outcome (logic.rs:702-771) — returns the packed status (0 = still Ongoing)
 // ---------------------------------------------------------------------------------------------
-template <class BB>
-TAFL_HD uint8_t game_outcome(const Ctx<BB>& cx, const Pos<BB>& p, const tafl_state& s, int mover_def, int piece_kind,
+template <class BB, int SP>
+TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const tafl_state& s, int mover_def, int piece_kind,
                              int to_r, int to_c, BB caps) {
     if (!p.side(!mover_def).any()) return TAFL_STATUS_WIN(TAFL_WIN_ALL_CAPTURED, mover_def);
-    const int N = cx.N;
+    const int N = cx.n();
     if (!mover_def) {
         if ((caps & p.kbit).any()) return TAFL_STATUS_WIN(TAFL_WIN_KING_CAPTURED, 0);
-        if (cx.rules.enclosure_win != TAFL_ENCL_NONE &&
-            enclosure_win_possible(cx, p, cx.rules.enclosure_win == TAFL_ENCL_WITHOUT_EDGE_ACCESS)) {
+        if (cx.r_enclosure_win() != TAFL_ENCL_NONE &&
+            enclosure_win_possible(cx, p, cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS)) {
             Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.def, p.att,
-                                        cx.rules.enclosure_win == TAFL_ENCL_WITHOUT_EDGE_ACCESS, true);
+                                        cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS, true);
             if (e.found && (e.region & p.occ()).popc() == p.def.popc() && enclosure_secure(cx, p, e, false, true))
                 return TAFL_STATUS_WIN(TAFL_WIN_ENCLOSED, 0);
         }
@@ -603,18 +729,18 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB>& cx, const Pos<BB>& p, const tafl_sta
         if (piece_kind == KIND_K) {
             const bool at_edge = to_r == 0 || to_r == N - 1 || to_c == 0 || to_c == N - 1;
             const bool at_corner = (to_r == 0 || to_r == N - 1) && (to_c == 0 || to_c == N - 1);
-            if (cx.rules.edge_escape ? at_edge : at_corner) return TAFL_STATUS_WIN(TAFL_WIN_KING_ESCAPED, 1);
+            if (cx.r_edge_escape() ? at_edge : at_corner) return TAFL_STATUS_WIN(TAFL_WIN_KING_ESCAPED, 1);
         }
-        if (cx.rules.exit_fort && detect_exit_fort(cx, p)) return TAFL_STATUS_WIN(TAFL_WIN_EXIT_FORT, 1);
+        if (cx.r_exit_fort() && detect_exit_fort(cx, p)) return TAFL_STATUS_WIN(TAFL_WIN_EXIT_FORT, 1);
     }
-    if (cx.rules.repetition_enabled) {
+    if (cx.r_repetition_enabled()) {
         uint32_t reps = mover_def ? s.def_reps : s.att_reps;
-        if (reps >= cx.rules.n_repetitions)
-            return cx.rules.repetition_is_loss ? TAFL_STATUS_WIN(TAFL_WIN_REPETITION, !mover_def)
+        if (reps >= cx.r_n_repetitions())
+            return cx.r_repetition_is_loss() ? TAFL_STATUS_WIN(TAFL_WIN_REPETITION, !mover_def)
                                                : TAFL_STATUS_DRAW(TAFL_DRAW_REPETITION);
     }
     if (!side_can_play(cx, p, !mover_def))
-        return cx.rules.draw_on_no_plays ? TAFL_STATUS_DRAW(TAFL_DRAW_NO_PLAYS)
+        return cx.r_draw_on_no_plays() ? TAFL_STATUS_DRAW(TAFL_DRAW_NO_PLAYS)
                                          : TAFL_STATUS_WIN(TAFL_WIN_NO_PLAYS, mover_def);
     return TAFL_STATUS_ONGOING;
 }
@@ -623,8 +749,8 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB>& cx, const Pos<BB>& p, const tafl_sta
 // do_valid_play (logic.rs:782-820).  (from, axis, disp) is the Play; the caller guarantees a
 // piece on `from` and an in-bounds destination.  Returns the captured tiles.
 // ---------------------------------------------------------------------------------------------
-template <class BB>
-TAFL_HD BB do_valid_play(const Ctx<BB>& cx, tafl_state& s, int from_r, int from_c, int horizontal, int disp) {
+template <class BB, int SP>
+TAFL_HD BB do_valid_play(const Ctx<BB, SP>& cx, tafl_state& s, int from_r, int from_c, int horizontal, int disp) {
     Pos<BB> p = load_pos(cx, s);
     const int mover_def = (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
     const int to_r = horizontal ? from_r : from_r + disp, to_c = horizontal ? from_c + disp : from_c;
@@ -650,8 +776,8 @@ TAFL_HD BB do_valid_play(const Ctx<BB>& cx, tafl_state& s, int from_r, int from_
     store_pos(p, s);
     return caps;
 }
-template <class BB>
-TAFL_HD BB do_valid_move(const Ctx<BB>& cx, tafl_state& s, tafl_move m) {
+template <class BB, int SP>
+TAFL_HD BB do_valid_move(const Ctx<BB, SP>& cx, tafl_state& s, tafl_move m) {
     const int f = TAFL_MOVE_FROM(m), t = TAFL_MOVE_TO(m);
     const int fr = f / BB::STRIDE, fc = f - fr * BB::STRIDE, tr = t / BB::STRIDE, tc = t - tr * BB::STRIDE;
     const int horizontal = fr == tr;  // Play::from_tiles (play.rs:36-49)
@@ -659,10 +785,10 @@ TAFL_HD BB do_valid_move(const Ctx<BB>& cx, tafl_state& s, tafl_move m) {
 }
 
 // validate_play_for_side (logic.rs:159-214)
-template <class BB>
-TAFL_HD int validate_play(const Ctx<BB>& cx, const tafl_state& s, const tafl_play& pl, int side_def) {
+template <class BB, int SP>
+TAFL_HD int validate_play(const Ctx<BB, SP>& cx, const tafl_state& s, const tafl_play& pl, int side_def) {
     if (s.status != TAFL_STATUS_ONGOING) return TAFL_GAME_OVER;
-    const int N = cx.N;
+    const int N = cx.n();
     const int fr = pl.from_row, fc = pl.from_col;
     const int horizontal = pl.axis == TAFL_HORIZONTAL;
     // Coords arithmetic in i8, destination cast to u8 (play.rs:59-67)
@@ -687,11 +813,11 @@ TAFL_HD int validate_play(const Ctx<BB>& cx, const tafl_state& s, const tafl_pla
     if (fr == tr) { int lo = fc < tc ? fc : tc, hi = fc < tc ? tc : fc; for (int c = lo + 1; c < hi; ++c) between = between | BB::bit(idx_of<BB>(fr, c)); }
     else { int lo = fr < tr ? fr : tr, hi = fr < tr ? tr : fr; for (int r = lo + 1; r < hi; ++r) between = between | BB::bit(idx_of<BB>(r, fc)); }
     if ((between & occ).any()) return TAFL_BLOCKED_BY_PIECE;
-    if (!cx.may_corner[pk] && (cx.corners & tb).any()) return TAFL_MOVE_ONTO_BLOCKED_TILE;
-    if (cx.pass_block[pk] && (between & cx.throne).any()) return TAFL_MOVE_THROUGH_BLOCKED_TILE;
-    if (cx.noentry[pk] && tb == cx.throne) return TAFL_MOVE_ONTO_BLOCKED_TILE;
+    if (!cx.f_may_corner(pk) && (cx.corners & tb).any()) return TAFL_MOVE_ONTO_BLOCKED_TILE;
+    if (cx.f_pass_block(pk) && (between & cx.throne).any()) return TAFL_MOVE_THROUGH_BLOCKED_TILE;
+    if (cx.f_noentry(pk) && tb == cx.throne) return TAFL_MOVE_ONTO_BLOCKED_TILE;
     int dist = pl.disp < 0 ? -(int)pl.disp : (int)pl.disp;
-    if (cx.slow[pk] && dist > 1) return TAFL_TOO_FAR;
+    if (cx.f_slow(pk) && dist > 1) return TAFL_TOO_FAR;
     return TAFL_PLAY_OK;
 }
 

@@ -74,9 +74,9 @@ k_step_plays(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states
 }
 
 // do_valid_play (logic.rs:782-820) on one compact move per game
-template <class BB>
+template <class BB, int SP>
 __global__ void __launch_bounds__(STEP_BLOCK)
-k_step_moves(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
+k_step_moves(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
              const tafl_move* __restrict__ mv, uint32_t mv_stride, const uint32_t* __restrict__ pick,
              uint8_t* __restrict__ status_out) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -92,9 +92,9 @@ k_step_moves(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states
 
 // The fused random-playout step (K4): count -> pick -> select -> apply -> outcome, `steps`
 // plies per launch with the state held in registers in between.
-template <class BB, int MINB>
+template <class BB, int SP, int MINB>
 __global__ void __launch_bounds__(STEP_BLOCK, MINB)
-k_step_random(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
+k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
               uint32_t steps, int auto_reset, DevStats* __restrict__ stats) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -334,6 +334,13 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     if (rc) { delete e; g_create_error = "could not parse the starting FEN"; return rc; }
     e->cx64 = make_ctx<BB64>(*rules, N <= 7 ? N : 7);
     e->cx128 = make_ctx<BB128>(*rules, N);
+    if (width_bits == 64) {
+        if (spec_matches<SPEC_BRANDUBH>(e->cx64)) e->spec_detected = SPEC_BRANDUBH;
+    } else {
+        if (spec_matches<SPEC_COPENHAGEN>(e->cx128)) e->spec_detected = SPEC_COPENHAGEN;
+        else if (spec_matches<SPEC_TABLUT>(e->cx128)) e->spec_detected = SPEC_TABLUT;
+    }
+    e->spec = e->spec_detected;
 #define TAFL_CREATE_TRY(call)                                                                \
     do {                                                                                     \
         cudaError_t _ce = (call);                                                            \
@@ -389,6 +396,12 @@ int tafl_engine_info(const tafl_engine* e, uint32_t* n_games, int* width_bits, i
 void* tafl_engine_stream(const tafl_engine* e) { return e ? (void*)e->stream : nullptr; }
 int tafl_engine_sync(tafl_engine* e) { TAFL_CHECK_E(e); cudaSetDevice(e->device); return sync_engine(e); }
 uint64_t tafl_launch_count(const tafl_engine* e) { return e ? e->launches : 0; }
+int tafl_engine_spec(const tafl_engine* e) { return e ? e->spec : TAFL_ERR_INVALID_ARG; }
+int tafl_engine_force_generic(tafl_engine* e, int on) {
+    TAFL_CHECK_E(e);
+    e->spec = on ? (int)SPEC_GENERIC : e->spec_detected;
+    return TAFL_OK;
+}
 tafl_state* tafl_states_device(tafl_engine* e) { return e ? e->d_states : nullptr; }
 
 int tafl_reset(tafl_engine* e, const uint32_t* h_ids, uint32_t n) {
@@ -490,7 +503,7 @@ int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_
     if (!d_moves) return TAFL_ERR_INVALID_ARG;
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    TAFL_WIDTH_DISPATCH(e, (k_step_moves<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_moves, 1u, nullptr, d_status)));
+    TAFL_SPEC_DISPATCH(e, (k_step_moves<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_moves, 1u, nullptr, d_status)));
     TAFL_LAUNCHED(e);
     return sync_engine(e);
 }
@@ -508,7 +521,7 @@ int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int 
     while (done < n_steps) {
         const uint32_t chunk = (n_steps - done) < (uint32_t)spl ? (n_steps - done) : (uint32_t)spl;
 #define TAFL_STEP_LAUNCH(MINB)                                                                                   \
-    TAFL_WIDTH_DISPATCH(e, (k_step_random<BB, MINB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(            \
+    TAFL_SPEC_DISPATCH(e, (k_step_random<BB, SP, MINB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(            \
                                cx, e->d_states, n, state_words(e->start), seed, e->game_id_base, e->ply, chunk, auto_reset, e->d_stats)))
         switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
             case 6: TAFL_STEP_LAUNCH(6); break;

@@ -35,6 +35,8 @@ struct tafl_engine {
     tafl::DevStats* d_stats = nullptr;
     unsigned long long* d_checksum = nullptr;
     uint64_t game_id_base = 0, ply = 0, launches = 0;
+    int spec = 0;                      // kernel specialisation in use (tafl::SPEC_*), 0 = generic
+    int spec_detected = 0;             // what the Ruleset + board matched at create time
     int step_minb = 4;                 // k_step_random variant: CTAs of 64 threads resident per SM
     // scratch for the by-value batch API (grown on demand)
     void* d_scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -53,6 +55,38 @@ void mcts_free(tafl_engine* e);
     do {                                                                    \
         cudaError_t _ce = (call);                                           \
         if (_ce != cudaSuccess) return tafl::set_cuda_error((e), _ce, #call); \
+    } while (0)
+
+// run `body` with BB / SP / cx bound to the engine's bitfield width and kernel specialisation
+#define TAFL_SPEC_DISPATCH(e, body)                                                                     \
+    do {                                                                                                \
+        if ((e)->width == 64) {                                                                         \
+            using BB = tafl::BB64;                                                                      \
+            if ((e)->spec == tafl::SPEC_BRANDUBH) {                                                     \
+                constexpr int SP = tafl::SPEC_BRANDUBH;                                                 \
+                const auto cx = tafl::spec_cast<SP>((e)->cx64);                                         \
+                body;                                                                                   \
+            } else {                                                                                    \
+                constexpr int SP = tafl::SPEC_GENERIC;                                                  \
+                const auto& cx = (e)->cx64;                                                             \
+                body;                                                                                   \
+            }                                                                                           \
+        } else {                                                                                        \
+            using BB = tafl::BB128;                                                                     \
+            if ((e)->spec == tafl::SPEC_COPENHAGEN) {                                                   \
+                constexpr int SP = tafl::SPEC_COPENHAGEN;                                               \
+                const auto cx = tafl::spec_cast<SP>((e)->cx128);                                        \
+                body;                                                                                   \
+            } else if ((e)->spec == tafl::SPEC_TABLUT) {                                                \
+                constexpr int SP = tafl::SPEC_TABLUT;                                                   \
+                const auto cx = tafl::spec_cast<SP>((e)->cx128);                                        \
+                body;                                                                                   \
+            } else {                                                                                    \
+                constexpr int SP = tafl::SPEC_GENERIC;                                                  \
+                const auto& cx = (e)->cx128;                                                            \
+                body;                                                                                   \
+            }                                                                                           \
+        }                                                                                               \
     } while (0)
 
 inline unsigned grid_for(uint32_t n, unsigned block) { return (n + block - 1) / block; }

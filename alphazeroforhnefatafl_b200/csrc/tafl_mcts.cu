@@ -47,9 +47,9 @@ __global__ void k_mcts_init(const tafl_state* __restrict__ states, uint32_t n, M
 }
 
 // `sims` x MCTS.search (mcts.py:55-136) for every tree; warp w of the grid owns tree w.
-template <class BB>
+template <class BB, int SP>
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
-k_mcts_sims(const __grid_constant__ Ctx<BB> cx, MctsView mv, uint32_t n_trees, uint32_t sims, double cpuct, double draw_value,
+k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, uint32_t sims, double cpuct, double draw_value,
             uint32_t* __restrict__ any_overflow) {
     const int lane = threadIdx.x & 31;
     const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
@@ -209,9 +209,9 @@ k_mcts_results(MctsView mv, uint32_t n_trees, tafl_move* __restrict__ r_moves, u
 }
 
 // play the chosen root move in every Ongoing game (do_valid_play, logic.rs:782-820)
-template <class BB>
+template <class BB, int SP>
 __global__ void __launch_bounds__(64)
-k_mcts_play_best(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
+k_mcts_play_best(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
                  const tafl_move* __restrict__ r_moves, const uint32_t* __restrict__ r_counts,
                  const uint32_t* __restrict__ r_best, uint8_t* __restrict__ status_out) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -354,7 +354,7 @@ int tafl_mcts_search_async(tafl_engine* e) {
     k_mcts_init<<<grid_for(n, 128), 128, 0, e->stream>>>(e->d_states, n, m->v);
     MCTS_LAUNCHED(e);
     const unsigned grid = grid_for(n, MCTS_WARPS);
-    MCTS_WIDTH_DISPATCH(e, (k_mcts_sims<BB><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->cfg.num_sims, m->cfg.cpuct,
+    TAFL_SPEC_DISPATCH(e, (k_mcts_sims<BB, SP><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->cfg.num_sims, m->cfg.cpuct,
                                                                                     m->cfg.draw_value, m->d_any_overflow)));
     MCTS_LAUNCHED(e);
     k_mcts_results<<<grid, MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->r_moves, m->r_visits, m->r_q, m->r_counts, m->r_best);
@@ -413,7 +413,7 @@ int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status) {
     cudaSetDevice(e->device);
     MctsPools* m = e->mcts;
     const uint32_t n = e->n_games;
-    MCTS_WIDTH_DISPATCH(e, (k_mcts_play_best<BB><<<grid_for(n, 64), 64, 0, e->stream>>>(cx, e->d_states, n, m->r_moves, m->r_counts,
+    TAFL_SPEC_DISPATCH(e, (k_mcts_play_best<BB, SP><<<grid_for(n, 64), 64, 0, e->stream>>>(cx, e->d_states, n, m->r_moves, m->r_counts,
                                                                                        m->r_best, e->d_status)));
     MCTS_LAUNCHED(e);
     if (h_status) {

@@ -68,8 +68,8 @@ __device__ __forceinline__ int nth_set_bit(BB128 b, int n) {
 // get_all_possible_moves (game/main.rs:33-43) by one warp: lane i takes the i-th piece (ascending
 // bit index), counts its plays with piece_rays, an exclusive shuffle scan gives its slot in the
 // canonical list.  Returns the list length (same value on every lane).  `out` may hold `cap` moves.
-template <class BB>
-__device__ __forceinline__ int warp_gen_moves(const Ctx<BB>& cx, const Pos<BB>& p, int def_side, tafl_move* out, int cap,
+template <class BB, int SP>
+__device__ __forceinline__ int warp_gen_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side, tafl_move* out, int cap,
                                               int lane) {
     const BB own = p.side(def_side), occ = p.occ();
     const int n_pieces = own.popc();

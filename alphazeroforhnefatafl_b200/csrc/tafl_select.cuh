@@ -50,20 +50,37 @@ template <class BB> struct MaxD;
 template <> struct MaxD<BB64> { static constexpr int v = 6; };
 template <> struct MaxD<BB128> { static constexpr int v = 10; };
 
-// count legal plays of `def_side`'s pieces on position p (status must be Ongoing)
+// longest ray the count loop has to walk: N-1 tiles when the board size is a compile-time constant
+template <class BB, int SP> struct RayLen { static constexpr int v = SpecTraits<SP>::N - 1; };
+template <class BB> struct RayLen<BB, SPEC_GENERIC> { static constexpr int v = MaxD<BB>::v; };
+
+// [s + d*step == throne] as a source-aligned tile set; folds to an immediate when N, dir and d are
+// compile-time constants (preset specialisations)
 template <class BB>
-TAFL_HD MoveSel<BB> count_moves(const Ctx<BB>& cx, const Pos<BB>& p, int def_side) {
+TAFL_HD BB throne_aligned(int N, int dir, int d) {
+    int r = N / 2, c = N / 2;
+    if (dir == DIR_VP) r -= d;
+    else if (dir == DIR_VM) r += d;
+    else if (dir == DIR_HP) c -= d;
+    else c += d;
+    return (r >= 0 && r < N && c >= 0 && c < N) ? BB::bit(r * BB::STRIDE + c) : BB::zero();
+}
+
+// count legal plays of `def_side`'s pieces on position p (status must be Ongoing)
+template <class BB, int SP>
+TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side) {
     constexpr int S = BB::STRIDE;
-    constexpr int MD = MaxD<BB>::v;
+    constexpr int MD = RayLen<BB, SP>::v;
+    static_assert((4 * MD) % 8 == 0, "CsaAcc folds its inputs in groups of 8");
     MoveSel<BB> ms;
     ms.def_side = def_side;
     const int k = def_side ? KIND_DS : KIND_AS;
     const BB occ = p.occ();
     // a blocked corner always ends a ray, so it can be treated as not walkable (logic.rs:190-193)
-    const BB walk = cx.board & ~occ & ~(cx.may_corner[k] ? BB::zero() : cx.corners);
+    const BB walk = cx.board & ~occ & ~(cx.f_may_corner(k) ? BB::zero() : cx.corners);
     const BB src = p.kind(k);
     const BB thr = cx.throne;
-    const bool noentry = cx.noentry[k] != 0, passblk = cx.pass_block[k] != 0, slow = cx.slow[k] != 0;
+    const bool noentry = cx.f_noentry(k) != 0, passblk = cx.f_pass_block(k) != 0, slow = cx.f_slow(k) != 0;
     CsaAcc<BB> acc;
     acc.init();
     int n = 0;
@@ -73,10 +90,18 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB>& cx, const Pos<BB>& p, int def_sid
 #pragma unroll
         for (int d = 1; d <= MD; ++d) {
             // X(s) = walkable(s + d*step); T(s) = [s + d*step == throne]
-            if (dir == DIR_VP) { X = X.template shr<S>(); T = T.template shr<S>(); }
-            else if (dir == DIR_VM) { X = X.template shl<S>(); T = T.template shl<S>(); }
-            else if (dir == DIR_HP) { X = X.template shr<1>() & cx.not_colL; T = T.template shr<1>(); }
-            else { X = X.template shl<1>() & cx.not_col0; T = T.template shl<1>(); }
+            if (dir == DIR_VP) X = X.template shr<S>();
+            else if (dir == DIR_VM) X = X.template shl<S>();
+            else if (dir == DIR_HP) X = X.template shr<1>() & cx.not_colL;
+            else X = X.template shl<1>() & cx.not_col0;
+            if constexpr (SP == SPEC_GENERIC) {
+                if (dir == DIR_VP) T = T.template shr<S>();
+                else if (dir == DIR_VM) T = T.template shl<S>();
+                else if (dir == DIR_HP) T = T.template shr<1>();
+                else T = T.template shl<1>();
+            } else {
+                T = throne_aligned<BB>(cx.n(), dir, d);
+            }
             E = E & X;
             if (passblk) E = E & ~Tprev;                  // logic.rs:194-200
             BB emit = noentry ? (E & ~T) : E;             // logic.rs:201-206 + play.rs:208-211
@@ -104,8 +129,8 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB>& cx, const Pos<BB>& p, int def_sid
 }
 
 // k-th legal play (0 <= k < ms.total) in canonical order
-template <class BB>
-TAFL_HD tafl_move select_move(const Ctx<BB>& cx, const Pos<BB>& p, const MoveSel<BB>& ms, uint32_t k) {
+template <class BB, int SP>
+TAFL_HD tafl_move select_move(const Ctx<BB, SP>& cx, const Pos<BB>& p, const MoveSel<BB>& ms, uint32_t k) {
     // word-level prefix
     uint32_t pw[5] = {0, 0, 0, 0, 0};
     int wsel = 0;
@@ -159,8 +184,8 @@ struct StepEvt {
     uint32_t turn;
 };
 // one random ply of a game that is Ongoing (the caller has already reset a finished game)
-template <class BB>
-TAFL_HD StepEvt random_step_ongoing(const Ctx<BB>& cx, tafl_state& s, uint64_t seed, uint64_t gid, uint64_t ply) {
+template <class BB, int SP>
+TAFL_HD StepEvt random_step_ongoing(const Ctx<BB, SP>& cx, tafl_state& s, uint64_t seed, uint64_t gid, uint64_t ply) {
     StepEvt ev;
     ev.stepped = ev.legal = ev.caps = ev.turn = 0;
     ev.status = 0;
@@ -177,8 +202,8 @@ TAFL_HD StepEvt random_step_ongoing(const Ctx<BB>& cx, tafl_state& s, uint64_t s
     ev.turn = s.turn;
     return ev;
 }
-template <class BB>
-TAFL_HD StepEvt random_step(const Ctx<BB>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
+template <class BB, int SP>
+TAFL_HD StepEvt random_step(const Ctx<BB, SP>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
                             uint64_t ply, bool auto_reset) {
     if (s.status != TAFL_STATUS_ONGOING) {
         if (!auto_reset) {
@@ -206,8 +231,8 @@ TAFL_HD void add_evt(StepStats& a, const StepEvt& e) {
         else a.win[e.status & 1][TAFL_STATUS_REASON(e.status)] += 1;
     }
 }
-template <class BB>
-TAFL_HD void random_step(const Ctx<BB>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
+template <class BB, int SP>
+TAFL_HD void random_step(const Ctx<BB, SP>& cx, tafl_state& s, const tafl_state& start, uint64_t seed, uint64_t gid,
                          uint64_t ply, bool auto_reset, StepStats& acc) {
     add_evt(acc, random_step(cx, s, start, seed, gid, ply, auto_reset));
 }
@@ -224,8 +249,8 @@ inline void fold_stats(const StepStats& a, tafl_stats* o) {
 template <class BB> TAFL_HD void put_bb(uint64_t o[2], BB b) { o[0] = b.lo64(); o[1] = b.hi64(); }
 
 // GameLogic::iter_plays(tile) (logic.rs:850-856): -1 == Err(NoPiece)
-template <class BB>
-TAFL_HD int piece_plays(const Ctx<BB>& cx, const tafl_state& st, int row, int col, tafl_move* out) {
+template <class BB, int SP>
+TAFL_HD int piece_plays(const Ctx<BB, SP>& cx, const tafl_state& st, int row, int col, tafl_move* out) {
     Pos<BB> p = load_pos(cx, st);
     const int s = idx_of<BB>(row, col);
     int kind;
@@ -233,7 +258,7 @@ TAFL_HD int piece_plays(const Ctx<BB>& cx, const tafl_state& st, int row, int co
     else if (Nib<BB>::raw_att(st, s)) kind = KIND_AS;
     else return -1;
     if (st.status != TAFL_STATUS_ONGOING) return 0;
-    if (row >= cx.N || col >= cx.N) return 0;
+    if (row >= cx.n() || col >= cx.n()) return 0;
     Rays r = piece_rays(cx, p.occ(), kind, row, col);
     int n = 0;
     for (int d = 0; d < 4; ++d)
@@ -246,8 +271,8 @@ TAFL_HD int piece_plays(const Ctx<BB>& cx, const tafl_state& st, int row, int co
     return n;
 }
 // GameLogic::get_captures (logic.rs:604-699) after moving the piece as do_valid_play does
-template <class BB>
-TAFL_HD tafl_play_effects query_captures(const Ctx<BB>& cx, const tafl_state& st, const tafl_play& pl) {
+template <class BB, int SP>
+TAFL_HD tafl_play_effects query_captures(const Ctx<BB, SP>& cx, const tafl_state& st, const tafl_play& pl) {
     tafl_play_effects fx;
     fx.captures[0] = fx.captures[1] = 0;
     fx.status = 0; fx.err = 0; fx.n_captures = 0;   // status is not part of a capture query
@@ -255,9 +280,9 @@ TAFL_HD tafl_play_effects query_captures(const Ctx<BB>& cx, const tafl_state& st
     Pos<BB> p = load_pos(cx, st);
     const int fr = pl.from_row, fc = pl.from_col, hz = pl.axis == TAFL_HORIZONTAL;
     const int tr = hz ? fr : fr + pl.disp, tc = hz ? fc + pl.disp : fc;
-    const BB fb = (fr < cx.N && fc < cx.N) ? BB::bit(idx_of<BB>(fr, fc)) : BB::zero();
+    const BB fb = (fr < cx.n() && fc < cx.n()) ? BB::bit(idx_of<BB>(fr, fc)) : BB::zero();
     const int pk = kind_at(p, fb);
-    if (pk == KIND_NONE || tr < 0 || tc < 0 || tr >= cx.N || tc >= cx.N) { fx.err = TAFL_NO_PIECE; return fx; }
+    if (pk == KIND_NONE || tr < 0 || tc < 0 || tr >= cx.n() || tc >= cx.n()) { fx.err = TAFL_NO_PIECE; return fx; }
     const BB tb = BB::bit(idx_of<BB>(tr, tc));
     const int piece_def = pk != KIND_AS;
     if (piece_def) { p.def = p.def | tb; p.att = p.att & ~tb; } else { p.att = p.att | tb; p.def = p.def & ~tb; }
@@ -269,8 +294,8 @@ TAFL_HD tafl_play_effects query_captures(const Ctx<BB>& cx, const tafl_state& st
     return fx;
 }
 // GameLogic::detect_shieldwall (logic.rs:535-569) on the board as given
-template <class BB>
-TAFL_HD tafl_play_effects query_shieldwall(const Ctx<BB>& cx, const tafl_state& st, const tafl_play& pl) {
+template <class BB, int SP>
+TAFL_HD tafl_play_effects query_shieldwall(const Ctx<BB, SP>& cx, const tafl_state& st, const tafl_play& pl) {
     tafl_play_effects fx;
     fx.captures[0] = fx.captures[1] = 0;
     fx.status = 0; fx.err = 0; fx.n_captures = 0xFF;
@@ -286,8 +311,8 @@ TAFL_HD tafl_play_effects query_shieldwall(const Ctx<BB>& cx, const tafl_state& 
     return fx;
 }
 // GameLogic::find_enclosure (logic.rs:309-401) [+ enclosure_secure logic.rs:408-463 -> *secure]
-template <class BB>
-TAFL_HD tafl_enclosure query_enclosure(const Ctx<BB>& cx, const tafl_state& st, const tafl_enclosure_query& q,
+template <class BB, int SP>
+TAFL_HD tafl_enclosure query_enclosure(const Ctx<BB, SP>& cx, const tafl_state& st, const tafl_enclosure_query& q,
                                        uint8_t* secure) {
     tafl_enclosure o;
     o.occupied[0] = o.occupied[1] = o.unoccupied[0] = o.unoccupied[1] = o.boundary[0] = o.boundary[1] = 0;
@@ -307,8 +332,8 @@ TAFL_HD tafl_enclosure query_enclosure(const Ctx<BB>& cx, const tafl_state& st, 
     return o;
 }
 // GameLogic::side_can_play (logic.rs:837-846)
-template <class BB>
-TAFL_HD uint8_t query_can_play(const Ctx<BB>& cx, const tafl_state& st, int def_side) {
+template <class BB, int SP>
+TAFL_HD uint8_t query_can_play(const Ctx<BB, SP>& cx, const tafl_state& st, int def_side) {
     if (st.status != TAFL_STATUS_ONGOING) return 0;  // every play validates as GameOver (logic.rs:165-167)
     return side_can_play(cx, load_pos(cx, st), def_side) ? 1 : 0;
 }

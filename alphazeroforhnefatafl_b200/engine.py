@@ -169,6 +169,14 @@ class LockstepGames:
     def sync(self):
         self._ck(lib().tafl_engine_sync(self._h))
 
+    @property
+    def spec(self):
+        """kernel specialisation in use: 0 generic, 1 Copenhagen 11x11, 2 Tablut 9x9, 3 Brandubh 7x7/u64"""
+        return int(lib().tafl_engine_spec(self._h))
+
+    def force_generic(self, on=True):
+        self._ck(lib().tafl_engine_force_generic(self._h, int(on)))
+
     # -- resident state -------------------------------------------------------------------------
     def reset(self, game_ids=None):
         if game_ids is None:

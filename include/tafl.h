@@ -271,6 +271,12 @@ int tafl_engine_info(const tafl_engine* e, uint32_t* n_games, int* width_bits, i
 /* cudaStream_t of the engine (for callers that want to order their own work / events) */
 void* tafl_engine_stream(const tafl_engine* e);
 int tafl_engine_sync(tafl_engine* e);
+/* Kernel specialisation in use: 0 = generic (rule flags read at run time), 1 = Copenhagen 11x11,
+ * 2 = Tablut 9x9, 3 = Brandubh 7x7 on u64 — chosen at create time when the Ruleset and board equal
+ * the preset (preset.rs:12-134); results are identical either way (tests run both).
+ * tafl_engine_force_generic(e, 1) switches the generic kernels on, (e, 0) back. */
+int tafl_engine_spec(const tafl_engine* e);
+int tafl_engine_force_generic(tafl_engine* e, int on);
 /* number of kernels this engine has launched so far (bench.py's gpu_launches) */
 uint64_t tafl_launch_count(const tafl_engine* e);
 

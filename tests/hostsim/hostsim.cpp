@@ -19,17 +19,40 @@ int dispatch(int width, F&& f) {
     return TAFL_ERR_INVALID_ARG;
 }
 template <class BB> void put(uint64_t o[2], BB b) { o[0] = b.lo64(); o[1] = b.hi64(); }
+
+// Build the Ctx and hand it to f — as the preset SPECIALISATION when the rules and board match one
+// (exactly the engine's choice, tafl_engine_create), else as the generic run-time Ctx.
+int g_force_generic = 0;
+int g_spec_used[SPEC_COUNT] = {0, 0, 0, 0};
+template <class BB, class F>
+void with_ctx(const tafl_rules& r, int N, F&& f) {
+    const Ctx<BB> cx = make_ctx<BB>(r, N);
+    if (!g_force_generic) {
+        if constexpr (BB::BITS == 64) {
+            if (spec_matches<SPEC_BRANDUBH>(cx)) { g_spec_used[SPEC_BRANDUBH]++; f(spec_cast<SPEC_BRANDUBH>(cx)); return; }
+        } else {
+            if (spec_matches<SPEC_COPENHAGEN>(cx)) { g_spec_used[SPEC_COPENHAGEN]++; f(spec_cast<SPEC_COPENHAGEN>(cx)); return; }
+            if (spec_matches<SPEC_TABLUT>(cx)) { g_spec_used[SPEC_TABLUT]++; f(spec_cast<SPEC_TABLUT>(cx)); return; }
+        }
+    }
+    g_spec_used[SPEC_GENERIC]++;
+    f(cx);
+}
 }  // namespace
 
 extern "C" {
+
+void sim_force_generic(int on) { g_force_generic = on; }
+int sim_spec_used(int spec) { return (spec >= 0 && spec < SPEC_COUNT) ? g_spec_used[spec] : -1; }
 
 int sim_validate_plays(const tafl_rules* r, int width, const tafl_state* st, const tafl_play* pl, uint32_t n,
                        uint8_t* out_err) {
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             out_err[i] = (uint8_t)validate_play(cx, st[i], pl[i], (st[i].flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
+            });
         }
         return 0;
     });
@@ -39,7 +62,7 @@ int sim_do_plays(const tafl_rules* r, int width, const tafl_state* st, const taf
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             tafl_play_effects fx{};
             int err = validate_play(cx, st[i], pl[i], (st[i].flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
             fx.err = (uint8_t)err;
@@ -52,6 +75,7 @@ int sim_do_plays(const tafl_rules* r, int width, const tafl_state* st, const taf
             }
             fx.status = out_st[i].status;
             if (out_fx) out_fx[i] = fx;
+            });
         }
         return 0;
     });
@@ -61,8 +85,9 @@ int sim_legal_moves_of(const tafl_rules* r, int width, const tafl_state* st, uin
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             counts[i] = (uint32_t)gen_moves(cx, st[i], moves + (size_t)i * TAFL_MAX_MOVES, TAFL_MAX_MOVES);
+            });
         }
         return 0;
     });
@@ -72,8 +97,9 @@ int sim_piece_plays(const tafl_rules* r, int width, const tafl_state* st, const 
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             counts[i] = piece_plays(cx, st[i], tiles_rc[2 * i], tiles_rc[2 * i + 1], moves + (size_t)i * 32);
+            });
         }
         return 0;
     });
@@ -83,8 +109,9 @@ int sim_get_captures(const tafl_rules* r, int width, const tafl_state* st, const
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             out[i] = query_captures(cx, st[i], pl[i]);
+            });
         }
         return 0;
     });
@@ -94,8 +121,9 @@ int sim_detect_shieldwall(const tafl_rules* r, int width, const tafl_state* st, 
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             out[i] = query_shieldwall(cx, st[i], pl[i]);
+            });
         }
         return 0;
     });
@@ -105,9 +133,10 @@ int sim_find_enclosure(const tafl_rules* r, int width, const tafl_state* st, con
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             uint8_t sec;
             out[i] = query_enclosure(cx, st[i], q[i], &sec);
+            });
         }
         return 0;
     });
@@ -117,8 +146,9 @@ int sim_enclosure_secure(const tafl_rules* r, int width, const tafl_state* st, c
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             query_enclosure(cx, st[i], q[i], &out[i]);
+            });
         }
         return 0;
     });
@@ -127,8 +157,9 @@ int sim_detect_exit_fort(const tafl_rules* r, int width, const tafl_state* st, u
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             out[i] = detect_exit_fort(cx, load_pos(cx, st[i]));
+            });
         }
         return 0;
     });
@@ -138,8 +169,9 @@ int sim_side_can_play(const tafl_rules* r, int width, const tafl_state* st, cons
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             out[i] = query_can_play(cx, st[i], sides[i] != 0);
+            });
         }
         return 0;
     });
@@ -151,14 +183,15 @@ int sim_random_playout(const tafl_rules* r, const tafl_state* start, int width, 
                        tafl_stats* stats) {
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
-        Ctx<BB> cx = make_ctx<BB>(*r, start->side_len);
         StepStats acc{};
-        for (uint32_t g = 0; g < n_games; ++g) {
-            tafl_state s = states[g];
-            for (uint32_t i = 0; i < n_steps; ++i)
-                random_step(cx, s, *start, seed, game_id_base + g, ply0 + i, auto_reset != 0, acc);
-            states[g] = s;
-        }
+        with_ctx<BB>(*r, start->side_len, [&](const auto& cx) {
+            for (uint32_t g = 0; g < n_games; ++g) {
+                tafl_state s = states[g];
+                for (uint32_t i = 0; i < n_steps; ++i)
+                    random_step(cx, s, *start, seed, game_id_base + g, ply0 + i, auto_reset != 0, acc);
+                states[g] = s;
+            }
+        });
         fold_stats(acc, stats);
         return 0;
     });
@@ -169,11 +202,12 @@ int sim_select_moves(const tafl_rules* r, int width, const tafl_state* st, const
     return dispatch(width, [&](auto z) {
         using BB = decltype(z);
         for (uint32_t i = 0; i < n; ++i) {
-            Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
             Pos<BB> p = load_pos(cx, st[i]);
             MoveSel<BB> ms = count_moves(cx, p, (st[i].flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
             out_counts[i] = (uint32_t)ms.total;
             out_moves[i] = (ms.total > 0) ? select_move(cx, p, ms, ks[i] % (uint32_t)ms.total) : (tafl_move)0xFFFF;
+            });
         }
         return 0;
     });

@@ -237,6 +237,13 @@ class HostSim:
     def by_value(self, rules, width):
         return ByValueImpl(self.lib, "sim_", rules, width)
 
+    def force_generic(self, on):
+        """1: always use the generic (run-time rule flags) code; 0: preset specialisations when they match."""
+        self.lib.sim_force_generic(int(on))
+
+    def spec_used(self, spec):
+        return self.lib.sim_spec_used(int(spec))
+
     def random_playout(self, rules, start_state, width, seed, n_games, n_steps, auto_reset=True, game_id_base=0, ply0=0,
                        states=None):
         if states is None:

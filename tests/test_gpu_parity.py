@@ -162,3 +162,34 @@ def test_gpu_full_size_properties(orc, built_lib):
     assert so.tobytes() == full[:64].tobytes()
     so, _ = orc.random_playout(rules, fen, 128, seed, 32, steps, game_id_base=n - 32, n_threads=8)
     assert so.tobytes() == full[n - 32:].tobytes()
+
+
+@pytest.mark.parametrize("name,preset,width,spec", [("copenhagen", A.PRESET_COPENHAGEN, 128, 1), ("tablut", A.PRESET_TABLUT, 128, 2),
+                                                    ("brandubh", A.PRESET_BRANDUBH, 64, 3), ("brandubh_u128", A.PRESET_BRANDUBH, 128, 0),
+                                                    ("koch", A.PRESET_KOCH, 64, 3)])   # Koch differs from Brandubh only in hostility MASKS (run-time data)
+def test_gpu_preset_specialisation_equals_generic(orc, built_lib, name, preset, width, spec):
+    """The preset-specialised kernels (compile-time rule flags) are picked for the preset rules + board,
+    and both they and the generic kernels (forced) reproduce the oracle: playouts and MCTS."""
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    so, so_stats = orc.random_playout(rules, fen, width, 77, 512, 700, game_id_base=5, n_threads=8)
+    roots = sample_positions(orc, rules, fen, width, 32, seed=88, max_steps=200)
+    ref = orc.mcts_search(rules, width, roots, 200, n_threads=8)
+    for generic in (False, True):
+        with E.LockstepGames(rules, fen, 512, 0, width) as g:
+            assert g.spec == spec
+            if generic:
+                g.force_generic(True)
+                assert g.spec == 0
+            g.set_game_id_base(5)
+            g.step_random(77, 700)
+            assert g.get_states().tobytes() == so.tobytes(), (name, generic)
+            assert g.stats().as_dict() == so_stats.as_dict()
+        with E.LockstepGames(rules, fen, len(roots), 0, width) as g:
+            if generic:
+                g.force_generic(True)
+            g.set_states(roots)
+            g.mcts_configure(200, 1.0, 1e-4)
+            g.mcts_search()
+            got = g.mcts_results()
+            assert np.array_equal(got["visits"], ref["visits"]) and np.array_equal(got["moves"], ref["moves"])
+            assert got["q"].tobytes() == ref["q"].tobytes()

@@ -91,3 +91,35 @@ def test_hostsim_select_kth_move(orc, sim, name, preset, width):
         nz = counts > 0
         exp = moves[np.arange(len(states))[nz], (ks[nz] % counts[nz])]
         assert np.array_equal(got[nz], exp)
+
+
+@pytest.mark.parametrize("name,preset,width,spec", [("copenhagen", A.PRESET_COPENHAGEN, 128, 1),
+                                                    ("tablut", A.PRESET_TABLUT, 128, 2),
+                                                    ("brandubh", A.PRESET_BRANDUBH, 64, 3)])
+def test_hostsim_preset_specialisation_equals_generic(orc, sim, name, preset, width, spec):
+    """The compile-time preset specialisations (SpecTraits, tafl_core.cuh) are selected for the preset
+    rules + board and give the same results as the generic run-time-flag code and as the oracle."""
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    rc, st0 = orc.state_from_fen(fen, width, A.ATTACKER)
+    so, so_stats = orc.random_playout(rules, fen, width, 33, 128, 900, n_threads=8)
+    used0, gen0 = sim.spec_used(spec), sim.spec_used(0)
+    a, a_stats = sim.random_playout(rules, st0, width, 33, 128, 900)
+    assert sim.spec_used(spec) == used0 + 1 and sim.spec_used(0) == gen0
+    sim.force_generic(1)
+    try:
+        b, b_stats = sim.random_playout(rules, st0, width, 33, 128, 900)
+        assert sim.spec_used(0) == gen0 + 1
+        rng = np.random.default_rng(3)
+        N = len(fen.split("/"))
+        states = random_boards(orc, rng, N, width, 400)
+        compare_by_value(orc.by_value(rules, width), sim.by_value(rules, width), states, width, rng)
+    finally:
+        sim.force_generic(0)
+    assert a.tobytes() == b.tobytes() == so.tobytes()
+    assert a_stats.as_dict() == b_stats.as_dict() == so_stats.as_dict()
+    # a preset Ruleset on another board size must fall back to the generic code
+    if preset == A.PRESET_COPENHAGEN:
+        g0 = sim.spec_used(0)
+        st7 = orc.state_from_fen(orc.preset_board(A.PRESET_BRANDUBH), 128, A.ATTACKER)[1]
+        sim.random_playout(rules, st7, 128, 1, 4, 20)
+        assert sim.spec_used(0) == g0 + 1
