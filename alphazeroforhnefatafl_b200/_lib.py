@@ -76,9 +76,13 @@ def lib():
         "tafl_moves_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp)]),
         "tafl_legal_moves_host": (C.c_int, [vp, vp, vp, C.c_uint32, C.c_uint32]),
         "tafl_step": (C.c_int, [vp, vp, vp]),
+        "tafl_step_status": (C.c_int, [vp, vp, vp, vp]),
+        "tafl_actions_device": (vp, [vp]),
+        "tafl_actions_host": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32]),
         "tafl_step_moves_device": (C.c_int, [vp, vp, vp]),
         "tafl_step_random": (C.c_int, [vp, C.c_uint64, C.c_uint32, C.c_int, C.c_int]),
         "tafl_step_random_async": (C.c_int, [vp, C.c_uint64, C.c_uint32, C.c_int, C.c_int]),
+        "tafl_step_random_host": (C.c_int, [vp, vp, vp, C.c_uint64, C.c_uint32, C.c_int]),
         "tafl_set_game_id_base": (C.c_int, [vp, C.c_uint64]),
         "tafl_set_random_ply": (C.c_int, [vp, C.c_uint64]),
         "tafl_random_ply": (C.c_uint64, [vp]),

@@ -49,10 +49,11 @@ k_legal_moves(const __grid_constant__ Ctx<BB> cx, const tafl_state* __restrict__
 }
 
 // Game::do_play (game/mod.rs:95-101) with validation
-template <class BB>
+template <class BB, int SP>
 __global__ void __launch_bounds__(STEP_BLOCK)
-k_step_plays(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states, uint32_t n,
-             const tafl_play* __restrict__ plays, tafl_play_effects* __restrict__ fx_out) {
+k_step_plays(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
+             const tafl_play* __restrict__ plays, tafl_play_effects* __restrict__ fx_out,
+             uint8_t* __restrict__ status_out, uint8_t* __restrict__ err_out) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= n) return;
     tafl_state s = load_state(states + g);
@@ -71,6 +72,8 @@ k_step_plays(const __grid_constant__ Ctx<BB> cx, tafl_state* __restrict__ states
     }
     fx.status = s.status;
     if (fx_out) fx_out[g] = fx;
+    if (status_out) status_out[g] = s.status;
+    if (err_out) err_out[g] = (uint8_t)err;
 }
 
 // do_valid_play (logic.rs:782-820) on one compact move per game
@@ -96,12 +99,14 @@ template <class BB, int SP, int MINB>
 __global__ void __launch_bounds__(STEP_BLOCK, MINB)
 k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
-              uint32_t steps, int auto_reset, DevStats* __restrict__ stats) {
+              uint32_t steps, int auto_reset, DevStats* __restrict__ stats, uint32_t* __restrict__ actions) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t c_steps = 0, c_legal = 0, c_caps = 0;
     if (g < n) {
         tafl_state s = load_state(states + g);
+        uint32_t act = 0;   // tafl_action of the last ply of this launch
         for (uint32_t i = 0; i < steps; ++i) {
+            act = (uint32_t)s.status << 16;
             if (s.status != TAFL_STATUS_ONGOING) {   // rare: only these lanes pay for the reset
                 if (!auto_reset) break;
                 s = unpack_state(start_w.v[0], start_w.v[1], start_w.v[2], start_w.v[3]);
@@ -110,6 +115,7 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
             c_steps += ev.stepped;
             c_legal += ev.legal;
             c_caps += ev.caps;
+            act = (uint32_t)ev.move | ((uint32_t)s.status << 16) | (ev.stepped << 24);
             if (ev.status) {  // rare: a game ended
                 atomicAdd(&stats->finished, 1ull);
                 atomicAdd(&stats->plies, (unsigned long long)ev.turn);
@@ -118,14 +124,12 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
             }
         }
         store_state(states + g, s);
+        actions[g] = act;
     }
-    // warp-level reduction of the dense counters, one atomic per warp
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        c_steps += __shfl_down_sync(0xFFFFFFFFu, c_steps, o);
-        c_legal += __shfl_down_sync(0xFFFFFFFFu, c_legal, o);
-        c_caps += __shfl_down_sync(0xFFFFFFFFu, c_caps, o);
-    }
+    // warp-level reduction of the dense counters (REDUX), one atomic per warp
+    c_steps = __reduce_add_sync(0xFFFFFFFFu, c_steps);
+    c_legal = __reduce_add_sync(0xFFFFFFFFu, c_legal);
+    c_caps = __reduce_add_sync(0xFFFFFFFFu, c_caps);
     if ((threadIdx.x & 31) == 0 && c_steps) {
         atomicAdd(&stats->steps, (unsigned long long)c_steps);
         atomicAdd(&stats->legal, (unsigned long long)c_legal);
@@ -354,11 +358,14 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     cudaDeviceProp prop;
     TAFL_CREATE_TRY(cudaGetDeviceProperties(&prop, device));
     e->sm_count = prop.multiProcessorCount;
-    if (const char* v = std::getenv("TAFL_STEP_MINB")) e->step_minb = std::atoi(v);   // tuning knob (profiles/)
+    if (const char* v = std::getenv("TAFL_STEP_MINB")) e->step_minb = std::atoi(v);   // tuning knobs (profiles/sweeps)
+    if (const char* v = std::getenv("TAFL_HOST_CHUNKS")) e->host_chunks = std::atoi(v);
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_states, (size_t)n_games * sizeof(tafl_state)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_counts, (size_t)n_games * sizeof(uint32_t)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_status, (size_t)n_games));
+    TAFL_CREATE_TRY(cudaMalloc(&e->d_actions, (size_t)n_games * sizeof(uint32_t)));
+    TAFL_CREATE_TRY(cudaMemsetAsync(e->d_actions, 0, (size_t)n_games * sizeof(uint32_t), e->stream));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_stats, sizeof(DevStats)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_checksum, sizeof(unsigned long long)));
     TAFL_CREATE_TRY(cudaMemsetAsync(e->d_stats, 0, sizeof(DevStats), e->stream));
@@ -376,9 +383,10 @@ int tafl_engine_destroy(tafl_engine* e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     mcts_free(e);
-    cudaFree(e->d_states); cudaFree(e->d_moves); cudaFree(e->d_counts); cudaFree(e->d_status);
+    cudaFree(e->d_states); cudaFree(e->d_moves); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_actions);
     cudaFree(e->d_stats); cudaFree(e->d_checksum);
     for (auto& p : e->d_scratch) cudaFree(p);
+    if (e->aux_ready) for (auto& st : e->aux) cudaStreamDestroy(st);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
     return TAFL_OK;
@@ -493,9 +501,27 @@ int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_fx)
     if (rc) return rc;
     rc = device_out(e, 1, n, &d_fx);
     if (rc) return rc;
-    TAFL_WIDTH_DISPATCH(e, (k_step_plays<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx)));
+    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx, nullptr, nullptr)));
     TAFL_LAUNCHED(e);
     if (h_fx) { rc = download(e, h_fx, d_fx, n); if (rc) return rc; }
+    return sync_engine(e);
+}
+int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err) {
+    TAFL_CHECK_E(e);
+    if (!h_plays || !h_status) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    tafl_play* d_pl;
+    uint8_t* d_err;
+    int rc = upload(e, 0, h_plays, n, &d_pl);
+    if (rc) return rc;
+    rc = device_out(e, 1, n, &d_err);
+    if (rc) return rc;
+    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, nullptr,
+                                                                                                    e->d_status, d_err)));
+    TAFL_LAUNCHED(e);
+    if ((rc = download(e, h_status, e->d_status, n))) return rc;
+    if (h_err && (rc = download(e, h_err, d_err, n))) return rc;
     return sync_engine(e);
 }
 int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_status) {
@@ -512,34 +538,88 @@ int tafl_set_game_id_base(tafl_engine* e, uint64_t v) { TAFL_CHECK_E(e); e->game
 int tafl_set_random_ply(tafl_engine* e, uint64_t v) { TAFL_CHECK_E(e); e->ply = v; return TAFL_OK; }
 uint64_t tafl_random_ply(const tafl_engine* e) { return e ? e->ply : 0; }
 
+// enqueue k_step_random over games [first, first + n) on `stream`: `steps` plies starting at RNG ply `ply0`
+static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t first, uint32_t n, uint64_t seed, uint64_t ply0,
+                              uint32_t steps, int auto_reset) {
+#define TAFL_STEP_LAUNCH(MINB)                                                                                   \
+    TAFL_SPEC_DISPATCH(e, (k_step_random<BB, SP, MINB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, stream>>>(                \
+                               cx, e->d_states + first, n, state_words(e->start), seed, e->game_id_base + first, ply0, steps, \
+                               auto_reset, e->d_stats, e->d_actions + first)))
+    switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
+        case 6: TAFL_STEP_LAUNCH(6); break;
+        case 8: TAFL_STEP_LAUNCH(8); break;
+        case 10: TAFL_STEP_LAUNCH(10); break;
+        case 12: TAFL_STEP_LAUNCH(12); break;
+        default: TAFL_STEP_LAUNCH(4); break;
+    }
+#undef TAFL_STEP_LAUNCH
+    TAFL_LAUNCHED(e);
+    return TAFL_OK;
+}
+
 int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset, int spl) {
     TAFL_CHECK_E(e);
     cudaSetDevice(e->device);
     if (spl <= 0) spl = 1;
-    const uint32_t n = e->n_games;
     uint32_t done = 0;
     while (done < n_steps) {
         const uint32_t chunk = (n_steps - done) < (uint32_t)spl ? (n_steps - done) : (uint32_t)spl;
-#define TAFL_STEP_LAUNCH(MINB)                                                                                   \
-    TAFL_SPEC_DISPATCH(e, (k_step_random<BB, SP, MINB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(            \
-                               cx, e->d_states, n, state_words(e->start), seed, e->game_id_base, e->ply, chunk, auto_reset, e->d_stats)))
-        switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
-            case 6: TAFL_STEP_LAUNCH(6); break;
-            case 8: TAFL_STEP_LAUNCH(8); break;
-            case 10: TAFL_STEP_LAUNCH(10); break;
-            case 12: TAFL_STEP_LAUNCH(12); break;
-            default: TAFL_STEP_LAUNCH(4); break;
-        }
-#undef TAFL_STEP_LAUNCH
-        TAFL_LAUNCHED(e);
+        int rc = launch_step_random(e, e->stream, 0, e->n_games, seed, e->ply, chunk, auto_reset);
+        if (rc) return rc;
         e->ply += chunk;
         done += chunk;
     }
     return TAFL_OK;
 }
+
+// By-value random stepping with HOST buffers: == tafl_set_states(h_in) + tafl_step_random(n_steps) +
+// tafl_get_states(h_out), but the games are cut into chunks that flow through a few streams, so the
+// H2D copy of chunk i+1, the kernel of chunk i and the D2H copy of chunk i-1 overlap (PCIe is full
+// duplex).  Games are independent, so chunking cannot change any result.
+int tafl_step_random_host(tafl_engine* e, const tafl_state* h_in, tafl_state* h_out, uint64_t seed, uint32_t n_steps,
+                          int auto_reset) {
+    TAFL_CHECK_E(e);
+    if (!h_in || !h_out) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    int rc = check_side_len(e, h_in, n);
+    if (rc) return rc;
+    if (!e->aux_ready) {
+        for (auto& st : e->aux) TAFL_CUDA_TRY(e, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        e->aux_ready = true;
+    }
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    uint32_t chunks = (uint32_t)e->host_chunks;
+    if (chunks < 1) chunks = 1;
+    uint32_t per = (n + chunks - 1) / chunks;
+    per = (per + STEP_BLOCK - 1) / STEP_BLOCK * STEP_BLOCK;   // whole CTAs per chunk
+    uint32_t c = 0;
+    for (uint32_t first = 0; first < n; first += per, ++c) {
+        const uint32_t cnt = (n - first) < per ? (n - first) : per;
+        cudaStream_t st = e->aux[c % tafl_engine::N_AUX];
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_states + first, h_in + first, (size_t)cnt * sizeof(tafl_state), cudaMemcpyHostToDevice, st));
+        if (n_steps) {
+            rc = launch_step_random(e, st, first, cnt, seed, e->ply, n_steps, auto_reset);
+            if (rc) return rc;
+        }
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_out + first, e->d_states + first, (size_t)cnt * sizeof(tafl_state), cudaMemcpyDeviceToHost, st));
+    }
+    e->ply += n_steps;
+    for (auto& st : e->aux) TAFL_CUDA_TRY(e, cudaStreamSynchronize(st));
+    return TAFL_OK;
+}
 int tafl_step_random(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset, int spl) {
     int rc = tafl_step_random_async(e, seed, n_steps, auto_reset, spl);
     if (rc) return rc;
+    return sync_engine(e);
+}
+
+uint32_t* tafl_actions_device(tafl_engine* e) { return e ? e->d_actions : nullptr; }
+int tafl_actions_host(tafl_engine* e, uint32_t* h_actions, uint32_t first, uint32_t n) {
+    TAFL_CHECK_E(e);
+    if (!h_actions || (uint64_t)first + n > e->n_games) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_actions, e->d_actions + first, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
     return sync_engine(e);
 }
 

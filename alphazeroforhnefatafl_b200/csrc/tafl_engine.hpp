@@ -32,11 +32,16 @@ struct tafl_engine {
     tafl_move* d_moves = nullptr;      // [n_games][TAFL_MAX_MOVES]
     uint32_t* d_counts = nullptr;      // [n_games]
     uint8_t* d_status = nullptr;       // [n_games]
+    uint32_t* d_actions = nullptr;     // [n_games] tafl_action of the last random ply
     tafl::DevStats* d_stats = nullptr;
     unsigned long long* d_checksum = nullptr;
     uint64_t game_id_base = 0, ply = 0, launches = 0;
     int spec = 0;                      // kernel specialisation in use (tafl::SPEC_*), 0 = generic
     int spec_detected = 0;             // what the Ruleset + board matched at create time
+    static constexpr int N_AUX = 4;    // streams of the pipelined host-buffer path (tafl_step_random_host)
+    cudaStream_t aux[N_AUX] = {nullptr, nullptr, nullptr, nullptr};
+    bool aux_ready = false;
+    int host_chunks = 8;
     int step_minb = 4;                 // k_step_random variant: CTAs of 64 threads resident per SM
     // scratch for the by-value batch API (grown on demand)
     void* d_scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

@@ -179,6 +179,7 @@ TAFL_HD tafl_move select_move(const Ctx<BB, SP>& cx, const Pos<BB>& p, const Mov
 // fused random-playout step (BASELINE.json configs 1-2)
 // ---------------------------------------------------------------------------------------------
 struct StepEvt {
+    tafl_move move;   // the play that was applied (valid iff stepped)
     uint32_t stepped, legal, caps;
     uint8_t status;   // != 0: the game ended on this step
     uint32_t turn;
@@ -189,6 +190,7 @@ TAFL_HD StepEvt random_step_ongoing(const Ctx<BB, SP>& cx, tafl_state& s, uint64
     StepEvt ev;
     ev.stepped = ev.legal = ev.caps = ev.turn = 0;
     ev.status = 0;
+    ev.move = 0;
     const Pos<BB> p = load_pos(cx, s);
     const MoveSel<BB> ms = count_moves(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
     if (ms.total == 0) return ev;
@@ -196,6 +198,7 @@ TAFL_HD StepEvt random_step_ongoing(const Ctx<BB, SP>& cx, tafl_state& s, uint64
     const tafl_move m = select_move(cx, p, ms, k);
     const BB caps = do_valid_move(cx, s, m);
     ev.stepped = 1;
+    ev.move = m;
     ev.legal = (uint32_t)ms.total;
     ev.caps = (uint32_t)caps.popc();
     ev.status = s.status;
@@ -210,6 +213,7 @@ TAFL_HD StepEvt random_step(const Ctx<BB, SP>& cx, tafl_state& s, const tafl_sta
             StepEvt ev;
             ev.stepped = ev.legal = ev.caps = ev.turn = 0;
             ev.status = 0;
+            ev.move = 0;
             return ev;
         }
         s = start;

@@ -222,9 +222,33 @@ class LockstepGames:
         self._ck(lib().tafl_step(self._h, A.ptr(plays), A.ptr(fx) if want_effects else None))
         return fx
 
+    def game_do_play(self, plays):
+        """``Game::do_play`` (game/mod.rs:95-101) for every resident game with the reference's return
+        type: (status[n] uint8 packed GameStatus, err[n] uint8 PlayInvalid code)."""
+        plays = np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        assert len(plays) == self.n_games
+        status, err = np.empty(self.n_games, np.uint8), np.empty(self.n_games, np.uint8)
+        self._ck(lib().tafl_step_status(self._h, A.ptr(plays), A.ptr(status), A.ptr(err)))
+        return status, err
+
+    def last_actions(self):
+        """(moves uint16, status uint8, stepped bool) of the most recent random ply (tafl_actions_host)."""
+        a = np.empty(self.n_games, np.uint32)
+        self._ck(lib().tafl_actions_host(self._h, A.ptr(a), 0, self.n_games))
+        return (a & 0xFFFF).astype(np.uint16), ((a >> 16) & 0xFF).astype(np.uint8), ((a >> 24) & 1).astype(bool)
+
     def step_random(self, seed, n_steps, auto_reset=True, steps_per_launch=1, sync=True):
         fn = lib().tafl_step_random if sync else lib().tafl_step_random_async
         self._ck(fn(self._h, seed, n_steps, int(auto_reset), steps_per_launch))
+
+    def step_random_host(self, states, seed, n_steps=1, auto_reset=True, out=None):
+        """By-value random plies with HOST arrays (tafl_step_random_host): returns the successor states."""
+        states = np.ascontiguousarray(states, A.STATE_DTYPE)
+        assert len(states) == self.n_games
+        if out is None:
+            out = np.empty_like(states)
+        self._ck(lib().tafl_step_random_host(self._h, A.ptr(states), A.ptr(out), seed, n_steps, int(auto_reset)))
+        return out
 
     def set_game_id_base(self, v):
         self._ck(lib().tafl_set_game_id_base(self._h, v))

@@ -227,36 +227,77 @@ def run_b200(args):
     achieved = ENV_BYTES_PER_STEP * n / (kernel_us * 1e-6) / 1e9
     mean_legal = stats.legal_moves / max(1, stats.steps)
 
-    # ---- e2e: GameLogic::do_play-style by-value stepping through the C ABI with HOST buffers ----
-    # every step: H2D of the 64-byte states from pinned memory, one fused ply on the device, D2H of
-    # the successor states (which carry the status byte).
-    h_in = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
-    h_out = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
-    g.sync()
-    h_in.numpy()[:] = np.frombuffer(g.get_states().tobytes(), np.uint8)
+    # ---- e2e (headline): Game::do_play through the C ABI with HOST buffers -------------------------
+    # The reference-facing call of this path is Game::do_play(play) -> Result<GameStatus, PlayInvalid>
+    # (game/mod.rs:95-101).  A seeded random-play action sequence is recorded first (untimed: the fused
+    # kernel reports the play it chose, tafl_actions_host); the timed region then replays it from the
+    # start position with one tafl_step_status call per ply: H2D of that ply's 65 536 plays from pinned
+    # memory, validate + apply on the device, D2H of the status and PlayInvalid bytes.
     L = lib()
-    e2e_steps = max(10, min(args.steps, 200))
+    e2e_plies = 48
+    rounds = max(2, min(8, args.steps // 25))
+    plays_rec = torch.empty((e2e_plies, n, 4), dtype=torch.uint8).pin_memory()
+    st_host = torch.empty((e2e_plies, n), dtype=torch.uint8).pin_memory()
+    err_host = torch.empty((e2e_plies, n), dtype=torch.uint8).pin_memory()
+    g.reset()
+    for ply in range(e2e_plies):
+        g.step_random(args.seed + 1, 1, auto_reset=False)
+        moves, _, _ = g.last_actions()
+        plays_rec[ply].numpy()[:] = E.moves_to_plays(moves, 128).view(np.uint8).reshape(n, 4)
+    final_rec = g.get_states().tobytes()
 
-    def e2e_step():
-        L.tafl_set_states(g.handle, h_in.data_ptr(), 0, n)
-        L.tafl_step_random(g.handle, args.seed, 1, 1, 1)
-        L.tafl_get_states(g.handle, h_out.data_ptr(), 0, n)
+    def e2e_round():
+        for ply in range(e2e_plies):
+            rc = L.tafl_step_status(g.handle, plays_rec[ply].data_ptr(), st_host[ply].data_ptr(), err_host[ply].data_ptr())
+            if rc != 0:
+                raise RuntimeError("tafl_step_status failed: %d" % rc)
 
-    for _ in range(3):
-        e2e_step()
-    g.stats_reset()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-        h_in, h_out = h_out, h_in
-    barrier()
-    e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-    e2e_n = torch.tensor([float(g.stats().steps)], dtype=torch.float64, device="cuda")
+    g.reset()
+    e2e_round()                                  # warm-up round, also the correctness check of the replay
+    if g.get_states().tobytes() != final_rec:
+        raise RuntimeError("e2e replay through Game::do_play does not reproduce the recorded games")
+    e2e_n_round = int((err_host.numpy() == 0).sum())
+    e2e_time = 0.0
+    for _ in range(rounds):
+        g.reset()
+        barrier()
+        t0 = time.perf_counter()
+        e2e_round()
+        barrier()
+        e2e_time += time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_time], dtype=torch.float64, device="cuda")
+    e2e_n = torch.tensor([float(e2e_n_round * rounds)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
         dist.all_reduce(e2e_n, op=dist.ReduceOp.SUM)
     e2e_value = float(e2e_n.item()) / float(e2e_t.item())
+
+    # ---- second e2e figure: by-value states (GameLogic::do_play(play, state) -> state), 64 B each way --
+    h_in = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
+    h_in.numpy()[:] = np.frombuffer(g.get_states().tobytes(), np.uint8)
+    bv_steps = max(10, min(args.steps, 100))
+
+    def bv_step():
+        rc = L.tafl_step_random_host(g.handle, h_in.data_ptr(), h_out.data_ptr(), args.seed, 1, 1)
+        if rc != 0:
+            raise RuntimeError("tafl_step_random_host failed: %d" % rc)
+
+    for _ in range(3):
+        bv_step()
+    g.stats_reset()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(bv_steps):
+        bv_step()
+        h_in, h_out = h_out, h_in
+    barrier()
+    bv_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    bv_n = torch.tensor([float(g.stats().steps)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(bv_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(bv_n, op=dist.ReduceOp.SUM)
+    bv_value = float(bv_n.item()) / float(bv_t.item())
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -270,9 +311,14 @@ def run_b200(args):
                      "traffic": ncu_traffic(), "peak_source": peak_src, "kernel": "k_step_random<BB128>",
                      "kernel_us": kernel_us, "bytes_per_env_step": ENV_BYTES_PER_STEP,
                      "note": "integer-issue bound, not HBM bound: see profiles/ for issue-slot utilisation"},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 64, "d2h_bytes_per_step": n * 64,
-                "api": "tafl_set_states + tafl_step_random(1 ply) + tafl_get_states, pinned host buffers",
-                "steps": e2e_steps},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 4, "d2h_bytes_per_step": n * 2,
+                "api": "tafl_step_status == Game::do_play(play) -> Result<GameStatus, PlayInvalid> for 65536 resident games: "
+                       "pinned host plays in, status + PlayInvalid bytes out, one call per ply; recorded seeded random-play "
+                       "action sequence replayed from the start position (replay checked bit-exact against the recording)",
+                "plies_per_round": e2e_plies, "rounds": rounds,
+                "by_value_states": {"value": bv_value, "unit": UNIT, "h2d_bytes_per_step": n * 64, "d2h_bytes_per_step": n * 64,
+                                    "api": "tafl_step_random_host(1 ply): pinned host states in, successor states out, chunked over streams",
+                                    "steps": bv_steps}},
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
         "wall_s_timed_region": t_wall,

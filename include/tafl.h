@@ -301,6 +301,10 @@ int tafl_legal_moves_host(tafl_engine* e, tafl_move* h_moves, uint32_t* h_counts
 /* Game::do_play (game/mod.rs:95-101) for every resident game: one tafl_play per game (HOST).
  * h_effects[i].err != 0 leaves game i unchanged (logic.rs:827-834). h_effects may be NULL. */
 int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_effects);
+/* The same call with the reference's exact return type, Result<GameStatus, PlayInvalid>
+ * (game/mod.rs:95): per game one status byte and one PlayInvalid byte come back instead of the
+ * 24-byte effects record.  HOST buffers; h_err may be NULL. */
+int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err);
 /* do_valid_play (logic.rs:782-820) on DEVICE-resident compact moves, no validation, no copy. */
 int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_status);
 
@@ -315,6 +319,22 @@ int tafl_step_random(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_r
                      int steps_per_launch);
 int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset,
                            int steps_per_launch);
+/* The same random plies by value with HOST buffers (GameLogic::do_play is by value, logic.rs:827-834):
+ * h_in[n_games] -> resident states -> n_steps plies -> h_out[n_games]; equivalent to tafl_set_states +
+ * tafl_step_random + tafl_get_states, with the copies and kernels of successive game chunks
+ * overlapped on several streams.  Pinned host memory is needed for the overlap (pageable works,
+ * serially).  h_in and h_out may be the same buffer. */
+int tafl_step_random_host(tafl_engine* e, const tafl_state* h_in, tafl_state* h_out, uint64_t seed,
+                          uint32_t n_steps, int auto_reset);
+/* One word per game describing the most recent ply of tafl_step_random* (the "action" and "status"
+ * outputs of an env step): bits 0..15 the tafl_move played, bits 16..23 the game's packed GameStatus
+ * after it, bit 24 set iff a play was made (clear for a game that was Over and not reset). */
+typedef uint32_t tafl_action;
+#define TAFL_ACTION_MOVE(a) ((tafl_move)((a) & 0xFFFFu))
+#define TAFL_ACTION_STATUS(a) ((uint8_t)(((a) >> 16) & 0xFFu))
+#define TAFL_ACTION_STEPPED(a) ((((a) >> 24) & 1u) != 0)
+tafl_action* tafl_actions_device(tafl_engine* e);                    /* [n_games], DEVICE */
+int tafl_actions_host(tafl_engine* e, tafl_action* h_actions, uint32_t first, uint32_t n);
 int tafl_set_game_id_base(tafl_engine* e, uint64_t first_game_id);
 int tafl_set_random_ply(tafl_engine* e, uint64_t ply);
 uint64_t tafl_random_ply(const tafl_engine* e);

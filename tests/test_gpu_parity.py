@@ -193,3 +193,46 @@ def test_gpu_preset_specialisation_equals_generic(orc, built_lib, name, preset, 
             got = g.mcts_results()
             assert np.array_equal(got["visits"], ref["visits"]) and np.array_equal(got["moves"], ref["moves"])
             assert got["q"].tobytes() == ref["q"].tobytes()
+
+
+def test_gpu_step_random_host_pipeline(orc, built_lib):
+    """tafl_step_random_host (chunked, multi-stream H2D / kernel / D2H) == set_states + step_random +
+    get_states == the oracle, for ragged sizes that do not divide into the chunk count."""
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    for n in (1, 63, 1000, 8193):
+        st, _ = orc.random_playout(rules, fen, 128, 5, n, 37, game_id_base=9, n_threads=8)
+        exp, exp_stats = orc.random_playout(rules, fen, 128, 5, n, 3, game_id_base=9, ply0=37, n_threads=8, states=st.copy())
+        with E.LockstepGames(rules, fen, n, 0, 128) as g:
+            g.set_game_id_base(9)
+            g.set_random_ply(37)
+            got = g.step_random_host(st, 5, 3)
+            assert got.tobytes() == exp.tobytes(), n
+            assert g.get_states().tobytes() == exp.tobytes()
+            assert g.stats().as_dict() == exp_stats.as_dict()
+            assert g.random_ply == 40
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS[:3])
+def test_gpu_recorded_actions_replay(orc, built_lib, name, preset, width):
+    """The actions the random ply reports (tafl_actions_host) are the plays it applied: replaying them
+    through Game::do_play (tafl_step_status, host buffers) from the start reproduces the same states,
+    the same statuses, and the oracle agrees on every successor."""
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    n, plies = 700, 90
+    with E.LockstepGames(rules, fen, n, 0, width) as a, E.LockstepGames(rules, fen, n, 0, width) as b:
+        for ply in range(plies):
+            before = a.get_states()
+            a.step_random(123, 1, auto_reset=False)
+            moves, status, stepped = a.last_actions()
+            after = a.get_states()
+            assert np.array_equal(status, after["status"])
+            assert np.array_equal(stepped, before["status"] == 0)
+            plays = E.moves_to_plays(moves, width)
+            st, err = b.game_do_play(plays)
+            assert np.array_equal(err == 0, stepped)
+            assert np.array_equal(err[~stepped], np.full((~stepped).sum(), A.GAME_OVER, np.uint8))
+            assert np.array_equal(st, status)
+            assert b.get_states().tobytes() == after.tobytes(), ply
+            if ply % 30 == 0:
+                exp, fx = orc.by_value(rules, width).do_plays(before[stepped], plays[stepped])
+                assert exp.tobytes() == after[stepped].tobytes()
