@@ -42,6 +42,7 @@ struct tafl_engine {
     cudaStream_t aux[N_AUX] = {nullptr, nullptr, nullptr, nullptr};
     bool aux_ready = false;
     int host_chunks = 8;
+    int mcts_minb = 8;                 // k_mcts_sims variant: CTAs of 4 warps resident per SM
     int step_minb = 4;                 // k_step_random variant: CTAs of 64 threads resident per SM
     // scratch for the by-value batch API (grown on demand)
     void* d_scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

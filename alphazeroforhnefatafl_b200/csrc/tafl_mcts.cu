@@ -47,8 +47,8 @@ __global__ void k_mcts_init(const tafl_state* __restrict__ states, uint32_t n, M
 }
 
 // `sims` x MCTS.search (mcts.py:55-136) for every tree; warp w of the grid owns tree w.
-template <class BB, int SP>
-__global__ void __launch_bounds__(MCTS_WARPS * 32)
+template <class BB, int SP, int MINB>
+__global__ void __launch_bounds__(MCTS_WARPS * 32, MINB)
 k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, uint32_t sims, double cpuct, double draw_value,
             uint32_t* __restrict__ any_overflow) {
     const int lane = threadIdx.x & 31;
@@ -56,10 +56,8 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
     if (tree >= n_trees) return;
     tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
     uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
-    uint32_t* const e_N = mv.e_N + (size_t)tree * mv.edge_cap;
-    double* const e_Q = mv.e_Q + (size_t)tree * mv.edge_cap;
-    uint32_t* const e_child = mv.e_child + (size_t)tree * mv.edge_cap;
-    tafl_move* const e_move = mv.e_move + (size_t)tree * mv.edge_cap;
+    uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
     uint32_t n_nodes = mv.t_nodes[tree], n_edges_used = mv.t_edges[tree];
     bool overflow = mv.t_overflow[tree] != 0;
     unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_edges = 0, c_term = 0;
@@ -81,11 +79,15 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
             if (!hdr_expanded(h.w)) {   // mcts.py:83-102  leaf: expand, Ns = 0, return -v with v = 0
                 const tafl_state s = load_state(n_state + node);
                 const Pos<BB> p = load_pos(cx, s);
-                const uint32_t room = mv.edge_cap - n_edges_used;
-                const int L = warp_gen_moves(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, e_move + n_edges_used, (int)room, lane);
-                if ((uint32_t)L > room) { overflow = true; break; }
-                for (int a = lane; a < L; a += 32) e_N[n_edges_used + a] = 0u;   // Nsa absent == 0
-                if (lane == 0) n_hdr[node] = make_uint4(n_edges_used, 0u, h.z, hdr_pack((uint32_t)L, hdr_pedge(h.w), 1u, es));
+                int n_pieces;
+                const int L = warp_build_ptab(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0,
+                                              n_ptab + (size_t)node * MCTS_PT_MAX, lane, &n_pieces);
+                if ((uint32_t)L > mv.edge_cap - n_edges_used || n_pieces > MCTS_PT_MAX) { overflow = true; break; }
+                MctsEdge z;
+                z.Q = 0.0; z.N = 0u; z.child = 0u;   // Nsa absent == 0
+                for (int a = lane; a < L; a += 32) edges[n_edges_used + a] = z;
+                if (lane == 0)
+                    n_hdr[node] = make_uint4(n_edges_used, 0u, h.z, hdr_pack((uint32_t)L, hdr_pedge(h.w), 1u, es, (uint32_t)n_pieces));
                 n_edges_used += (uint32_t)L;
                 c_edges += (unsigned long long)L;
                 c_depth += depth;
@@ -101,35 +103,51 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
             const double t_vis = c * sqrt((double)Ns);           // numerator for visited edges
             const double u_new = c * sqrt((double)Ns + MCTS_EPS);
             double best_u = -INFINITY;
-            uint32_t best_a = 0xFFFFFFFFu;
-            for (uint32_t a = lane; a < L; a += 32) {
-                const uint32_t N = e_N[base + a];
-                double u;
-                if (N > 0) u = e_Q[base + a] + t_vis / (double)(1u + N);
-                else u = u_new;
-                if (u > best_u) { best_u = u; best_a = a; }
+            uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
+            // four edges per lane in flight: the loads of a group are issued before any is used
+            for (uint32_t a0 = lane; a0 < L; a0 += 128) {
+                MctsEdge e4[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t a = a0 + 32u * j;
+                    if (a < L) e4[j] = edges[base + a];
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t a = a0 + 32u * j;
+                    if (a < L) {
+                        double u;
+                        if (e4[j].N > 0) u = e4[j].Q + t_vis / (double)(1u + e4[j].N);
+                        else u = u_new;
+                        if (u > best_u) { best_u = u; best_a = a; best_N = e4[j].N; best_child = e4[j].child; }
+                    }
+                }
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 const double ou = __shfl_xor_sync(0xFFFFFFFFu, best_u, o);
                 const uint32_t oa = __shfl_xor_sync(0xFFFFFFFFu, best_a, o);
-                if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; }
+                const uint32_t on = __shfl_xor_sync(0xFFFFFFFFu, best_N, o);
+                const uint32_t oc = __shfl_xor_sync(0xFFFFFFFFu, best_child, o);
+                if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; best_N = on; best_child = oc; }
             }
             const uint32_t a = best_a;
             uint32_t child;
-            if (e_N[base + a] == 0) {   // first traversal: getNextState (mcts.py:122-123)
+            if (best_N == 0) {   // first traversal: getNextState (mcts.py:122-123)
                 tafl_state s = load_state(n_state + node);
-                do_valid_move(cx, s, e_move[base + a]);
+                const tafl_move m = warp_decode_edge(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
+                                                     (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)a, lane);
+                do_valid_move(cx, s, m);
                 child = n_nodes++;
                 c_nodes += 1;
                 if (lane == 0) {
                     store_state(n_state + child, s);
                     n_hdr[child] = make_uint4(0u, 0u, node, hdr_pack(0, a, 0, es_code(s)));
-                    e_child[base + a] = child;
+                    edges[base + a].child = child;
                 }
                 __syncwarp();
             } else {
-                child = e_child[base + a];
+                child = best_child;
             }
             node = child;
             depth += 1;
@@ -141,15 +159,15 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
             if (h.z == MCTS_NO_PARENT) break;
             const uint32_t parent = h.z, a = hdr_pedge(h.w);
             uint4 ph = n_hdr[parent];
-            const uint32_t e = ph.x + a;
-            const uint32_t N = e_N[e];
+            MctsEdge* const ep = edges + ph.x + a;
+            const MctsEdge e = *ep;
             double q;
-            if (N > 0) q = ((double)N * e_Q[e] + v) / (double)(N + 1u);
+            if (e.N > 0) q = ((double)e.N * e.Q + v) / (double)(e.N + 1u);
             else q = v;
             __syncwarp();
             if (lane == 0) {
-                e_Q[e] = q;
-                e_N[e] = N + 1u;
+                ep->Q = q;
+                ep->N = e.N + 1u;
                 ph.y += 1u;   // Ns[s] += 1
                 n_hdr[parent] = ph;
             }
@@ -173,24 +191,41 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
 }
 
 // MCTS.getActionProb (mcts.py:40-47), temp = 0 with first-max: root visit counts, Q, moves, argmax
+template <class BB, int SP>
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
-k_mcts_results(MctsView mv, uint32_t n_trees, tafl_move* __restrict__ r_moves, uint32_t* __restrict__ r_visits,
-               double* __restrict__ r_q, uint32_t* __restrict__ r_counts, uint32_t* __restrict__ r_best) {
+k_mcts_results(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, tafl_move* __restrict__ r_moves,
+               uint32_t* __restrict__ r_visits, double* __restrict__ r_q, uint32_t* __restrict__ r_counts,
+               uint32_t* __restrict__ r_best) {
     const int lane = threadIdx.x & 31;
     const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
     if (tree >= n_trees) return;
     const uint4 h = mv.n_hdr[(size_t)tree * mv.node_cap];
     const uint32_t L = hdr_expanded(h.w) ? hdr_n_edges(h.w) : 0u, base = h.x;
-    const size_t eo = (size_t)tree * mv.edge_cap + base, ro = (size_t)tree * TAFL_MAX_MOVES;
+    const int n_pieces = (int)hdr_n_pieces(h.w);
+    const MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap + base;
+    const uint32_t* const ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;   // root = node 0
+    const tafl_state root = load_state(mv.n_state + (size_t)tree * mv.node_cap);
+    const int def_side = (root.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
+    const size_t ro = (size_t)tree * TAFL_MAX_MOVES;
     uint32_t best_n = 0, best_a = 0xFFFFFFFFu;
-    for (uint32_t a = lane; a < TAFL_MAX_MOVES; a += 32) {
+    for (uint32_t a0 = 0; a0 < TAFL_MAX_MOVES; a0 += 32) {
+        const uint32_t a = a0 + lane;
         uint32_t N = 0;
         double q = 0.0;
         tafl_move m = 0;
-        if (a < L) {
-            N = mv.e_N[eo + a];
-            m = mv.e_move[eo + a];
-            if (N > 0) q = mv.e_Q[eo + a];
+        if (a0 < L) {   // warp-uniform: the decode is a warp-wide operation
+            // every lane decodes its own edge: run the warp-cooperative decode once per lane index
+            for (int src = 0; src < 32; ++src) {
+                const int aa = (int)(a0 + src);
+                if ((uint32_t)aa >= L) break;
+                const tafl_move mm = warp_decode_edge(cx, ptab, n_pieces, def_side, aa, lane);
+                if (src == lane) m = mm;
+            }
+            if (a < L) {
+                const MctsEdge e = edges[a];
+                N = e.N;
+                if (N > 0) q = e.Q;
+            }
         }
         r_moves[ro + a] = m;
         r_visits[ro + a] = N;
@@ -267,8 +302,7 @@ namespace tafl {
 void mcts_free(tafl_engine* e) {
     MctsPools* m = e->mcts;
     if (!m) return;
-    cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.e_N); cudaFree(m->v.e_Q); cudaFree(m->v.e_child);
-    cudaFree(m->v.e_move); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
+    cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.n_ptab); cudaFree(m->v.edges); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
     cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best);
     cudaFree(m->d_any_overflow);
     delete m;
@@ -324,10 +358,8 @@ int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg) {
     } while (0)
     MCTS_ALLOC(m->v.n_state, n * nc * sizeof(tafl_state));
     MCTS_ALLOC(m->v.n_hdr, n * nc * sizeof(uint4));
-    MCTS_ALLOC(m->v.e_N, n * ec * sizeof(uint32_t));
-    MCTS_ALLOC(m->v.e_Q, n * ec * sizeof(double));
-    MCTS_ALLOC(m->v.e_child, n * ec * sizeof(uint32_t));
-    MCTS_ALLOC(m->v.e_move, n * ec * sizeof(tafl_move));
+    MCTS_ALLOC(m->v.n_ptab, n * nc * MCTS_PT_MAX * sizeof(uint32_t));
+    MCTS_ALLOC(m->v.edges, n * ec * sizeof(MctsEdge));
     MCTS_ALLOC(m->v.t_nodes, n * sizeof(uint32_t));
     MCTS_ALLOC(m->v.t_edges, n * sizeof(uint32_t));
     MCTS_ALLOC(m->v.t_overflow, n * sizeof(uint32_t));
@@ -354,10 +386,20 @@ int tafl_mcts_search_async(tafl_engine* e) {
     k_mcts_init<<<grid_for(n, 128), 128, 0, e->stream>>>(e->d_states, n, m->v);
     MCTS_LAUNCHED(e);
     const unsigned grid = grid_for(n, MCTS_WARPS);
-    TAFL_SPEC_DISPATCH(e, (k_mcts_sims<BB, SP><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->cfg.num_sims, m->cfg.cpuct,
-                                                                                    m->cfg.draw_value, m->d_any_overflow)));
+#define TAFL_MCTS_LAUNCH(MINB)                                                                                          \
+    TAFL_SPEC_DISPATCH(e, (k_mcts_sims<BB, SP, MINB><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->cfg.num_sims,   \
+                                                                                           m->cfg.cpuct, m->cfg.draw_value, \
+                                                                                           m->d_any_overflow)))
+    switch (e->mcts_minb) {   // resident CTAs of 4 warps per SM the kernel is compiled for (register cap)
+        case 4: TAFL_MCTS_LAUNCH(4); break;
+        case 6: TAFL_MCTS_LAUNCH(6); break;
+        case 10: TAFL_MCTS_LAUNCH(10); break;
+        default: TAFL_MCTS_LAUNCH(8); break;
+    }
+#undef TAFL_MCTS_LAUNCH
     MCTS_LAUNCHED(e);
-    k_mcts_results<<<grid, MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->r_moves, m->r_visits, m->r_q, m->r_counts, m->r_best);
+    TAFL_SPEC_DISPATCH(e, (k_mcts_results<BB, SP><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->r_moves, m->r_visits, m->r_q,
+                                                                                        m->r_counts, m->r_best)));
     MCTS_LAUNCHED(e);
     m->searched = true;
     return TAFL_OK;

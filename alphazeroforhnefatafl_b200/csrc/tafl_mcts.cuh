@@ -4,30 +4,34 @@
 //   select  (mcts.py:104-119)  warp-parallel PUCT argmax over the node's edges, f64, the exact
 //                              operation order of the oracle (oracle/mcts_oracle.hpp), strict '>'
 //                              first-max tie-break;
-//   expand  (mcts.py:83-102)   the new child's state is produced by do_valid_move (tafl_core.cuh),
-//                              its legal moves by a warp-cooperative generator (one piece per
-//                              lane, shuffle prefix sum to compact in canonical order);
+//   expand  (mcts.py:83-102)   the new child's state is produced by do_valid_move (tafl_core.cuh);
+//                              its legal moves are kept as a PIECE TABLE (tafl_select.cuh: one
+//                              32-bit entry per piece = tile + plays per direction, one piece per
+//                              lane, one coalesced store) instead of an explicit list — the move
+//                              behind an edge is decoded the one time the edge is first followed;
 //   backup  (mcts.py:125-136)  walk the parent links, incremental-mean Q, sign flip per ply.
 //
 // Build-defined semantics (the reference has no Game/NNet adapter): tree (node =
 // path), action index = position in the canonical move list, stub evaluator P = 1/L, v = 0,
 // terminal value +-1 / draw_value from the point of view of the side to move.
 #pragma once
-#include "tafl_core.cuh"
+#include "tafl_select.cuh"
 
 namespace tafl {
 
 // node header (16 B): x = edge_base, y = Ns, z = parent node (0xFFFFFFFF for the root),
-// w = n_edges[0:10) | parent_edge[10:20) | expanded[20] | es[21:23)
+// w = n_edges[0:10) | parent_edge[10:20) | expanded[20] | es[21:23) | n_pieces[23:30)
 enum { ES_ONGOING = 0, ES_WIN = 1, ES_LOSS = 2, ES_DRAW = 3 };   // for the side to move at the node
 #define MCTS_NO_PARENT 0xFFFFFFFFu
-__device__ __forceinline__ uint32_t hdr_pack(uint32_t n_edges, uint32_t pedge, uint32_t expanded, uint32_t es) {
-    return (n_edges & 1023u) | ((pedge & 1023u) << 10) | (expanded << 20) | (es << 21);
+__host__ __device__ __forceinline__ uint32_t hdr_pack(uint32_t n_edges, uint32_t pedge, uint32_t expanded, uint32_t es,
+                                                      uint32_t n_pieces = 0) {
+    return (n_edges & 1023u) | ((pedge & 1023u) << 10) | (expanded << 20) | (es << 21) | ((n_pieces & 127u) << 23);
 }
-__device__ __forceinline__ uint32_t hdr_n_edges(uint32_t w) { return w & 1023u; }
-__device__ __forceinline__ uint32_t hdr_pedge(uint32_t w) { return (w >> 10) & 1023u; }
-__device__ __forceinline__ uint32_t hdr_expanded(uint32_t w) { return (w >> 20) & 1u; }
-__device__ __forceinline__ uint32_t hdr_es(uint32_t w) { return (w >> 21) & 3u; }
+__host__ __device__ __forceinline__ uint32_t hdr_n_edges(uint32_t w) { return w & 1023u; }
+__host__ __device__ __forceinline__ uint32_t hdr_pedge(uint32_t w) { return (w >> 10) & 1023u; }
+__host__ __device__ __forceinline__ uint32_t hdr_expanded(uint32_t w) { return (w >> 20) & 1u; }
+__host__ __device__ __forceinline__ uint32_t hdr_es(uint32_t w) { return (w >> 21) & 3u; }
+__host__ __device__ __forceinline__ uint32_t hdr_n_pieces(uint32_t w) { return (w >> 23) & 127u; }
 
 // game.getGameEnded(board, 1) as a 2-bit code (oracle: Mcts::game_ended)
 __host__ __device__ __forceinline__ uint32_t es_code(const tafl_state& s) {
@@ -38,13 +42,19 @@ __host__ __device__ __forceinline__ uint32_t es_code(const tafl_state& s) {
     return winner_def == to_play_def ? ES_WIN : ES_LOSS;
 }
 
+// one edge (s, a): 16 bytes, one vector load per lane in select
+struct __align__(16) MctsEdge {
+    double Q;         // Qsa
+    uint32_t N;       // Nsa; 0 == "(s,a) not in Qsa"
+    uint32_t child;   // node reached by (s,a); valid iff N > 0
+};
+#define MCTS_PT_MAX 64   // piece-table entries per node (pieces of the side to move)
+
 struct MctsView {   // raw device pointers, passed to kernels by value
     tafl_state* n_state;   // [trees][node_cap]
     uint4* n_hdr;          // [trees][node_cap]
-    uint32_t* e_N;         // [trees][edge_cap]   Nsa
-    double* e_Q;           // [trees][edge_cap]   Qsa
-    uint32_t* e_child;     // [trees][edge_cap]   valid iff Nsa > 0
-    tafl_move* e_move;     // [trees][edge_cap]
+    uint32_t* n_ptab;      // [trees][node_cap][MCTS_PT_MAX]   piece table of the node's legal moves
+    MctsEdge* edges;       // [trees][edge_cap]
     uint32_t* t_nodes;     // [trees] nodes in use
     uint32_t* t_edges;     // [trees] edges in use
     uint32_t* t_overflow;  // [trees] 1 = edge pool exhausted (search of that tree stopped)
@@ -58,60 +68,64 @@ struct MctsView {   // raw device pointers, passed to kernels by value
 __device__ __forceinline__ int nth_set_bit(BB64 b, int n) {
     const uint32_t w0 = (uint32_t)b.v, w1 = (uint32_t)(b.v >> 32);
     const int c0 = __popc(w0);
-    return n < c0 ? (int)__fns(w0, 0, n + 1) : 32 + (int)__fns(w1, 0, n - c0 + 1);
+    return n < c0 ? nth_bit32(w0, n) : 32 + nth_bit32(w1, n - c0);
 }
 __device__ __forceinline__ int nth_set_bit(BB128 b, int n) {
     const int c = __popcll(b.lo);
     return n < c ? nth_set_bit(BB64{b.lo}, n) : 64 + nth_set_bit(BB64{b.hi}, n - c);
 }
 
-// get_all_possible_moves (game/main.rs:33-43) by one warp: lane i takes the i-th piece (ascending
-// bit index), counts its plays with piece_rays, an exclusive shuffle scan gives its slot in the
-// canonical list.  Returns the list length (same value on every lane).  `out` may hold `cap` moves.
+// Expansion by one warp: lane i takes the i-th piece of the side to move (ascending bit index),
+// piece_rays gives its plays per direction, the entry goes to ptab[i].  Returns the number of legal
+// moves L (same on every lane); *n_pieces_out = pieces written (> MCTS_PT_MAX: table overflow).
 template <class BB, int SP>
-__device__ __forceinline__ int warp_gen_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side, tafl_move* out, int cap,
-                                              int lane) {
+__device__ __forceinline__ int warp_build_ptab(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side,
+                                               uint32_t* __restrict__ ptab, int lane, int* n_pieces_out) {
     const BB own = p.side(def_side), occ = p.occ();
     const int n_pieces = own.popc();
+    *n_pieces_out = n_pieces;
     int total = 0;
+    for (int base = 0; base < n_pieces && base < MCTS_PT_MAX; base += 32) {
+        const int idx = base + lane;
+        uint32_t e = 0;
+        if (idx < n_pieces) {
+            const int s = nth_set_bit(own, idx);
+            const int row = s / BB::STRIDE, col = s - row * BB::STRIDE;
+            const bool is_king = def_side && BB::bit(s) == p.kbit;
+            e = pt_pack(s, is_king, piece_rays(cx, occ, is_king ? KIND_K : (def_side ? KIND_DS : KIND_AS), row, col));
+            ptab[idx] = e;
+        }
+        total += (int)__reduce_add_sync(0xFFFFFFFFu, (unsigned)pt_total(e));
+    }
+    return total;
+}
+// the move behind canonical action index a of a node with `n_pieces` table entries (a < L)
+template <class BB, int SP>
+__device__ __forceinline__ tafl_move warp_decode_edge(const Ctx<BB, SP>& cx, const uint32_t* __restrict__ ptab,
+                                                      int n_pieces, int def_side, int a, int lane) {
+    int before = 0;
+    tafl_move m = 0;
     for (int base = 0; base < n_pieces; base += 32) {
         const int idx = base + lane;
-        const bool active = idx < n_pieces;
-        int s = 0, row = 0, col = 0, c = 0;
-        Rays r;
-        r.m[0] = r.m[1] = r.m[2] = r.m[3] = 0;
-        if (active) {
-            s = nth_set_bit(own, idx);
-            row = s / BB::STRIDE;
-            col = s - row * BB::STRIDE;
-            const int k = def_side ? ((BB::bit(s) == p.kbit) ? KIND_K : KIND_DS) : KIND_AS;
-            r = piece_rays(cx, occ, k, row, col);
-            c = r.cnt[0] + r.cnt[1] + r.cnt[2] + r.cnt[3];
-        }
+        const uint32_t e = idx < n_pieces ? ptab[idx] : 0u;
+        const int c = pt_total(e);
         int incl = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
             if (lane >= o) incl += t;
         }
-        int off = total + incl - c;
-        total += __shfl_sync(0xFFFFFFFFu, incl, 31);
-        if (active) {
-#pragma unroll
-            for (int d = 0; d < 4; ++d) {
-                uint32_t m = r.m[d];
-                while (m) {
-                    int pos;
-                    if ((d & 1) == 0) { pos = __ffs(m) - 1; m &= m - 1; }
-                    else { pos = 31 - __clz(m); m &= ~(1u << pos); }
-                    const int to = (d < 2) ? idx_of<BB>(pos, col) : idx_of<BB>(row, pos);
-                    if (off < cap) out[off] = (tafl_move)(s | (to << 7));
-                    ++off;
-                }
-            }
+        const unsigned owns = __ballot_sync(0xFFFFFFFFu, a < before + incl);
+        if (owns) {   // the first lane whose running total exceeds a holds the piece
+            const int src = __ffs(owns) - 1;
+            const uint32_t es = __shfl_sync(0xFFFFFFFFu, e, src);
+            const int excl = __shfl_sync(0xFFFFFFFFu, before + incl - c, src);
+            m = pt_decode(cx, es, def_side, a - excl);
+            break;
         }
+        before += __shfl_sync(0xFFFFFFFFu, incl, 31);
     }
-    return total;
+    return m;
 }
 
 #endif  // __CUDACC__

@@ -342,4 +342,70 @@ TAFL_HD uint8_t query_can_play(const Ctx<BB, SP>& cx, const tafl_state& st, int 
     return side_can_play(cx, load_pos(cx, st), def_side) ? 1 : 0;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Piece table: the legal-move list of a position in compressed form (used by the MCTS node pools).
+// One 32-bit entry per piece of the side to move, pieces in ascending bit order:
+//   bits 0..6  tile index, bit 7 = the piece is the king, bits 8..23 = number of plays in each of the
+//   four directions (4 bits each, DIR_* order), bits 24..29 = their sum.
+// The plays of one direction are the tiles p+1, p+2, ... along the ray (ValidPlayIterator,
+// play.rs:189-225); the only tile a ray can pass without being allowed to stop on it is the empty
+// throne (play.rs:208-211), so the j-th play is recovered from the count alone: step j+1 tiles,
+// one more if the piece may not enter the throne and the walk reaches or crosses it.
+// The canonical move index a (game/main.rs:33-43) lives in the piece whose running total covers it.
+// ---------------------------------------------------------------------------------------------
+TAFL_HD uint32_t pt_pack(int tile, bool is_king, const Rays& r) {
+    const uint32_t total = (uint32_t)(r.cnt[0] + r.cnt[1] + r.cnt[2] + r.cnt[3]);
+    return (uint32_t)tile | (is_king ? 0x80u : 0u) | ((uint32_t)r.cnt[0] << 8) | ((uint32_t)r.cnt[1] << 12) |
+           ((uint32_t)r.cnt[2] << 16) | ((uint32_t)r.cnt[3] << 20) | (total << 24);
+}
+TAFL_HD int pt_total(uint32_t e) { return (int)((e >> 24) & 63u); }
+// j-th play (0 <= j < pt_total(e)) of the piece described by entry e
+template <class BB, int SP>
+TAFL_HD tafl_move pt_decode(const Ctx<BB, SP>& cx, uint32_t e, int def_side, int j) {
+    const int tile = (int)(e & 127u);
+    const int row = tile / BB::STRIDE, col = tile - row * BB::STRIDE;
+    const int k = (e & 0x80u) ? KIND_K : (def_side ? KIND_DS : KIND_AS);
+    const int c0 = (int)((e >> 8) & 15u), c1 = (int)((e >> 12) & 15u), c2 = (int)((e >> 16) & 15u);
+    int dir = 0;
+    if (j >= c0) { j -= c0; dir = 1; if (j >= c1) { j -= c1; dir = 2; if (j >= c2) { j -= c2; dir = 3; } } }
+    const int mid = cx.m();
+    const bool vertical = dir < 2;
+    const int p = vertical ? row : col, line = vertical ? col : row;
+    const bool hole = cx.f_noentry(k) && line == mid;   // the ray may cross the throne but not stop on it
+    int q;
+    if ((dir & 1) == 0) {
+        q = p + 1 + j;
+        if (hole && p < mid && q >= mid) ++q;
+    } else {
+        q = p - 1 - j;
+        if (hole && p > mid && q <= mid) --q;
+    }
+    const int to = vertical ? idx_of<BB>(q, col) : idx_of<BB>(row, q);
+    return (tafl_move)(tile | (to << 7));
+}
+// whole move list through the piece table (host check of the encoding; the kernels build the table
+// one piece per lane, tafl_mcts.cuh)
+template <class BB, int SP>
+TAFL_HD int pt_gen_moves(const Ctx<BB, SP>& cx, const tafl_state& st, tafl_move* out, int cap) {
+    if (st.status != TAFL_STATUS_ONGOING) return 0;
+    const Pos<BB> p = load_pos(cx, st);
+    const int def_side = (st.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
+    BB own = p.side(def_side);
+    const BB occ = p.occ();
+    int n = 0;
+    while (own.any()) {
+        const int s = own.ctz();
+        own = own & ~BB::bit(s);
+        const int row = s / BB::STRIDE, col = s - row * BB::STRIDE;
+        const bool is_king = def_side && BB::bit(s) == p.kbit;
+        const uint32_t e = pt_pack(s, is_king, piece_rays(cx, occ, is_king ? KIND_K : (def_side ? KIND_DS : KIND_AS), row, col));
+        for (int j = 0; j < pt_total(e); ++j) {
+            if (n < cap) out[n] = pt_decode(cx, e, def_side, j);
+            ++n;
+        }
+    }
+    return n;
+}
+
 }  // namespace tafl

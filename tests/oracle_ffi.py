@@ -256,6 +256,14 @@ class HostSim:
         assert rc == 0, rc
         return states, stats
 
+    def piece_table_moves(self, rules, width, states):
+        n = len(states)
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        counts = np.zeros(n, np.uint32)
+        rc = self.lib.sim_piece_table_moves(C.byref(rules), width, A.ptr(states), n, A.ptr(moves), A.ptr(counts))
+        assert rc == 0, rc
+        return moves, counts
+
     def select_moves(self, rules, width, states, ks):
         n = len(states)
         ks = np.ascontiguousarray(ks, np.uint32)

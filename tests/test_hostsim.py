@@ -123,3 +123,27 @@ def test_hostsim_preset_specialisation_equals_generic(orc, sim, name, preset, wi
         st7 = orc.state_from_fen(orc.preset_board(A.PRESET_BRANDUBH), 128, A.ATTACKER)[1]
         sim.random_playout(rules, st7, 128, 1, 4, 20)
         assert sim.spec_used(0) == g0 + 1
+
+
+def test_hostsim_piece_table_equals_move_list(orc, sim):
+    """The compressed per-piece move table of the MCTS node pools (pt_pack / pt_decode) expands to
+    exactly the canonical legal-move list, for the presets and for random rule variants (throne
+    rules, corner rights, slow pieces) on played and synthetic positions."""
+    rng = np.random.default_rng(2024)
+    def check(rules, width, states):
+        mo, co = orc.by_value(rules, width).legal_moves_of(states)
+        mt, ct = sim.piece_table_moves(rules, width, states)
+        assert np.array_equal(co, ct)
+        for i in range(len(states)):
+            assert np.array_equal(mo[i, :co[i]], mt[i, :ct[i]]), i
+    for name, preset, width in PRESET_CONFIGS:
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        check(rules, width, sample_positions(orc, rules, fen, width, 150, seed=5))
+        check(rules, width, random_boards(orc, rng, len(fen.split("/")), width, 300))
+    base = orc.preset_rules(A.PRESET_COPENHAGEN)
+    sets = [0, 0xFFFF, A.pieceset_type(A.KING), A.pieceset_type(A.SOLDIER), A.pieceset_side(A.ATTACKER), A.pieceset_side(A.DEFENDER)]
+    for trial in range(40):
+        r = base.copy(throne_movement=int(rng.integers(0, 5)), may_enter_corners=int(rng.choice(sets)),
+                      slow_pieces=int(rng.choice([0, 0, A.pieceset_type(A.KING), 0xFFFF, A.pieceset_side(A.DEFENDER)])))
+        N, width = [(7, 64), (9, 128), (11, 128), (7, 128)][trial % 4]
+        check(r, width, random_boards(orc, rng, N, width, 150))
