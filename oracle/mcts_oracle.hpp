@@ -22,6 +22,7 @@
 // contraction (compile with -ffp-contract=off).
 #pragma once
 #include <cmath>
+#include <functional>
 #include <limits>
 
 #include "tafl_oracle.hpp"
@@ -29,6 +30,54 @@
 namespace orc {
 
 static constexpr double MCTS_EPS = 1e-8;  // mcts.py:6
+
+// np.sum over a contiguous float64 vector, as mcts.py:88,99 call it.  numpy is a third-party
+// dependency of the reference that is not part of /root/reference (pinned here: numpy 2.3.5, the
+// version the golden vectors were generated with); its add-reduce is the published pairwise
+// summation: < 8 elements sequential; <= 128 elements eight stride-8 accumulators combined as
+// ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)) plus a sequential tail; larger inputs split at n/2 rounded
+// down to a multiple of 8.  The result is added to the identity 0.0.  Checked against np.sum in
+// tests/test_mcts_eval_golden.py.
+inline double np_pairwise_sum(const double* a, size_t n) {
+    if (n < 8) {
+        double res = 0.0;
+        for (size_t i = 0; i < n; ++i) res += a[i];
+        return res;
+    }
+    if (n <= 128) {
+        double r[8];
+        for (int j = 0; j < 8; ++j) r[j] = a[j];
+        size_t i = 8;
+        for (; i < n - (n % 8); i += 8)
+            for (int j = 0; j < 8; ++j) r[j] += a[i + j];
+        double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+        for (; i < n; ++i) res += a[i];
+        return res;
+    }
+    size_t n2 = n / 2;
+    n2 -= n2 % 8;
+    return np_pairwise_sum(a, n2) + np_pairwise_sum(a + n2, n - n2);
+}
+inline double np_sum(const double* a, size_t n) { return 0.0 + np_pairwise_sum(a, n); }
+
+// The deterministic TEST evaluator behind TAFL_EVAL_HASH (include/tafl.h): priors and value are a
+// hash of (seed, position, side to move), exactly representable in f32.  One state in 16 returns
+// all-zero priors so that the "all valid moves were masked" branch (mcts.py:91-99) is exercised.
+inline void hash_eval(uint64_t seed, const tafl_state& st, float* P /*[TAFL_MAX_MOVES]*/, float* v) {
+    const uint64_t side = (st.flags & TAFL_FLAG_DEF_TO_PLAY) ? 1u : 0u;
+    uint64_t h = splitmix64(st.def[1] ^ side);
+    h = splitmix64(st.def[0] ^ h);
+    h = splitmix64(st.att[1] ^ h);
+    h = splitmix64(st.att[0] ^ h);
+    h = splitmix64(seed ^ h);
+    const bool masked = (h & 15u) == 0;
+    for (uint32_t a = 0; a < TAFL_MAX_MOVES; ++a) {
+        const uint64_t x = splitmix64(h + (uint64_t)(a + 1) * 0x9E3779B97F4A7C15ull);
+        P[a] = masked ? 0.0f : (float)((x >> 40) + 1) * 5.9604644775390625e-08f;   // (0, 1], step 2^-24
+    }
+    const uint64_t y = splitmix64(h ^ 0xD1B54A32D192ED03ull);
+    *v = ((float)(int64_t)(y >> 40) - 8388608.0f) * 5.9604644775390625e-08f;        // [-0.5, 0.5)
+}
 
 template <class W>
 struct Mcts {
@@ -42,7 +91,12 @@ struct Mcts {
         std::vector<int32_t> child;   // node reached by (s,a), -1 = not created yet
         uint32_t Ns = 0;              // self.Ns[s]
         double P = 0.0;               // self.Ps[s][a], uniform over the valid moves
+        std::vector<double> Pa;       // evaluator mode: self.Ps[s][a] per action (masked, renormalised)
     };
+    // evaluator mode (nnet.predict, mcts.py:85): fills P[TAFL_MAX_MOVES] and v for a position.  The
+    // boundary is f32 (what a network emits), widened to f64 before masking (adapter: predict
+    // returns P.astype(float64), float(v)).  Unset = the uniform-prior / value-0 stub.
+    std::function<void(const GameState<W>&, float*, float*)> eval;
     const GameLogic& logic;
     double cpuct, draw_value;
     std::vector<Node> nodes;
@@ -81,6 +135,25 @@ struct Mcts {
             Node& n = nodes[idx];
             n.moves = logic.get_all_possible_moves(n.state);
             size_t L = n.moves.size();
+            double v_eval = 0.0;
+            if (eval) {  // mcts.py:85-99 with a real evaluator: mask, renormalise, uniform fallback
+                std::vector<float> pf(TAFL_MAX_MOVES);
+                float vf = 0.0f;
+                eval(n.state, pf.data(), &vf);
+                std::vector<double> ps(TAFL_MAX_MOVES), valids(TAFL_MAX_MOVES, 0.0);
+                for (size_t a = 0; a < L && a < TAFL_MAX_MOVES; ++a) valids[a] = 1.0;
+                for (size_t a = 0; a < TAFL_MAX_MOVES; ++a) ps[a] = (double)pf[a] * valids[a];   // :87
+                double sum = np_sum(ps.data(), ps.size());                                       // :88
+                if (sum > 0) {
+                    for (auto& x : ps) x /= sum;                                                 // :90
+                } else {
+                    for (size_t a = 0; a < TAFL_MAX_MOVES; ++a) ps[a] = ps[a] + valids[a];       // :98
+                    double s2 = np_sum(ps.data(), ps.size());
+                    for (auto& x : ps) x /= s2;                                                  // :99
+                }
+                n.Pa.assign(ps.begin(), ps.begin() + (std::ptrdiff_t)L);
+                v_eval = (double)vf;
+            }
             n.P = L ? 1.0 / (double)L : 0.0;
             n.Q.assign(L, 0.0);
             n.N.assign(L, 0);
@@ -89,7 +162,7 @@ struct Mcts {
             n.expanded = true;
             stats.edges += L;
             stats.depth_sum += (uint64_t)depth;
-            double v = 0.0;
+            double v = v_eval;
             return -v;
         }
         int best_act = -1;
@@ -98,10 +171,11 @@ struct Mcts {
             double cur_best = -std::numeric_limits<double>::infinity();
             for (size_t a = 0; a < n.moves.size(); ++a) {
                 double u;
+                const double P = eval ? n.Pa[a] : n.P;
                 if (n.N[a] > 0) {
-                    u = n.Q[a] + ((cpuct * n.P) * std::sqrt((double)n.Ns)) / (double)(1 + n.N[a]);
+                    u = n.Q[a] + ((cpuct * P) * std::sqrt((double)n.Ns)) / (double)(1 + n.N[a]);
                 } else {
-                    u = (cpuct * n.P) * std::sqrt((double)n.Ns + MCTS_EPS);
+                    u = (cpuct * P) * std::sqrt((double)n.Ns + MCTS_EPS);
                 }
                 if (u > cur_best) { cur_best = u; best_act = (int)a; }
             }

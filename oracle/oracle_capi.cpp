@@ -392,9 +392,10 @@ int orc_random_playout(const tafl_rules* r, const char* start_fen, int width, ui
 }
 
 // MCTS.getActionProb for n root states (fresh tree each), n_threads host threads.
-int orc_mcts_search(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
-                    double cpuct, double draw_value, int n_threads, tafl_move* moves, uint32_t* visits, double* q,
-                    uint32_t* counts, uint32_t* best, tafl_mcts_stats* stats) {
+static int mcts_search_impl(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                            double cpuct, double draw_value, int use_eval, uint64_t eval_seed, int n_threads,
+                            tafl_move* moves, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best,
+                            tafl_mcts_stats* stats) {
     return dispatch(width, [&](auto w) {
         using W = decltype(w);
         if (n_threads < 1) n_threads = 1;
@@ -409,6 +410,12 @@ int orc_mcts_search(const tafl_rules* r, int width, const tafl_state* roots, uin
                     unpack_state(roots[g], &s);
                     GameLogic logic(*r, s.board.side_len);
                     Mcts<W> m(logic, cpuct, draw_value);
+                    if (use_eval)
+                        m.eval = [eval_seed](const GameState<W>& gs, float* P, float* v) {
+                            tafl_state ps;
+                            pack_state(gs, &ps);
+                            hash_eval(eval_seed, ps, P, v);
+                        };
                     m.get_action_prob(s, num_sims);
                     auto& root = m.nodes[0];
                     size_t L = root.moves.size();
@@ -443,6 +450,26 @@ int orc_mcts_search(const tafl_rules* r, int width, const tafl_state* roots, uin
         return 0;
     });
 }
+
+int orc_mcts_search(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                    double cpuct, double draw_value, int n_threads, tafl_move* moves, uint32_t* visits, double* q,
+                    uint32_t* counts, uint32_t* best, tafl_mcts_stats* stats) {
+    return mcts_search_impl(r, width, roots, n, num_sims, cpuct, draw_value, 0, 0, n_threads, moves, visits, q, counts, best,
+                            stats);
+}
+// the same search with the TAFL_EVAL_HASH test evaluator (non-uniform priors, non-zero values)
+int orc_mcts_search_eval(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                         double cpuct, double draw_value, uint64_t eval_seed, int n_threads, tafl_move* moves,
+                         uint32_t* visits, double* q, uint32_t* counts, uint32_t* best, tafl_mcts_stats* stats) {
+    return mcts_search_impl(r, width, roots, n, num_sims, cpuct, draw_value, 1, eval_seed, n_threads, moves, visits, q, counts,
+                            best, stats);
+}
+// TAFL_EVAL_HASH for n packed states: P [n][TAFL_MAX_MOVES] f32, v [n] f32
+int orc_hash_eval(const tafl_state* st, uint32_t n, uint64_t seed, float* P, float* v) {
+    for (uint32_t i = 0; i < n; ++i) hash_eval(seed, st[i], P + (size_t)i * TAFL_MAX_MOVES, v + i);
+    return 0;
+}
+double orc_np_sum(const double* a, uint64_t n) { return np_sum(a, (size_t)n); }
 
 int orc_hw_threads(void) { return (int)std::thread::hardware_concurrency(); }
 

@@ -222,6 +222,44 @@ class Oracle:
         assert rc == 0, rc
         return dict(moves=moves, visits=visits, q=q, counts=counts, best=best, stats=stats)
 
+    def mcts_search_eval(self, rules, width, roots, num_sims, eval_seed, cpuct=1.0, draw_value=1e-4, n_threads=1):
+        """mcts_search with the TAFL_EVAL_HASH test evaluator instead of the stub."""
+        roots = np.ascontiguousarray(roots)
+        n = len(roots)
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        visits = np.zeros((n, A.MAX_MOVES), np.uint32)
+        q = np.zeros((n, A.MAX_MOVES), np.float64)
+        counts = np.zeros(n, np.uint32)
+        best = np.zeros(n, np.uint32)
+        stats = A.MctsStats()
+        f = self.lib.orc_mcts_search_eval
+        f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_uint64,
+                      C.c_int] + [C.c_void_p] * 6
+        f.restype = C.c_int
+        rc = f(C.addressof(rules), width, roots.ctypes.data, n, num_sims, cpuct, draw_value, eval_seed, n_threads,
+               moves.ctypes.data, visits.ctypes.data, q.ctypes.data, counts.ctypes.data, best.ctypes.data,
+               C.addressof(stats))
+        assert rc == 0, rc
+        return dict(moves=moves, visits=visits, q=q, counts=counts, best=best, stats=stats)
+
+    def hash_eval(self, states, seed):
+        states = np.ascontiguousarray(states)
+        n = len(states)
+        P = np.zeros((n, A.MAX_MOVES), np.float32)
+        v = np.zeros(n, np.float32)
+        f = self.lib.orc_hash_eval
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p]
+        f.restype = C.c_int
+        assert f(states.ctypes.data, n, seed, P.ctypes.data, v.ctypes.data) == 0
+        return P, v
+
+    def np_sum(self, a):
+        a = np.ascontiguousarray(a, np.float64)
+        f = self.lib.orc_np_sum
+        f.argtypes = [C.c_void_p, C.c_uint64]
+        f.restype = C.c_double
+        return f(a.ctypes.data, len(a))
+
     def hw_threads(self):
         return self.lib.orc_hw_threads()
 
