@@ -146,6 +146,17 @@ class MctsStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class LeafBatch(C.Structure):
+    """tafl_leaf_batch: device pointers of the pending evaluator batch (include/tafl.h)."""
+    _fields_ = [("d_states", C.c_void_p), ("d_planes", C.c_void_p), ("d_moves", C.c_void_p), ("d_counts", C.c_void_p),
+                ("d_priors", C.c_void_p), ("d_values", C.c_void_p), ("n_games", C.c_uint32), ("side_len", C.c_uint32),
+                ("stream", C.c_void_p)]
+
+
+EVALUATOR_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(LeafBatch))
+EVAL_STUB, EVAL_HASH = 0, 1
+
+assert C.sizeof(LeafBatch) == 64
 assert C.sizeof(State) == 64 and C.sizeof(Play) == 4 and C.sizeof(PlayEffects) == 24
 assert C.sizeof(Enclosure) == 56 and C.sizeof(EnclosureQuery) == 16 and C.sizeof(Rules) == 32
 

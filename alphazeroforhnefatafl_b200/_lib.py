@@ -106,6 +106,15 @@ def lib():
         "tafl_mcts_results_host": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]),
         "tafl_mcts_play_best": (C.c_int, [vp, vp]),
         "tafl_mcts_stats_get": (C.c_int, [vp, C.POINTER(A.MctsStats)]),
+        "tafl_mcts_begin": (C.c_int, [vp]),
+        "tafl_mcts_select_leaves": (C.c_int, [vp, C.POINTER(A.LeafBatch)]),
+        "tafl_mcts_expand_backup": (C.c_int, [vp]),
+        "tafl_mcts_finish": (C.c_int, [vp]),
+        "tafl_mcts_search_with": (C.c_int, [vp, A.EVALUATOR_FN, vp]),
+        "tafl_eval_builtin": (C.c_int, [vp, C.c_int, C.c_uint64]),
+        "tafl_mcts_search_builtin": (C.c_int, [vp, C.c_int, C.c_uint64]),
+        "tafl_leaf_batch_host": (C.c_int, [vp, vp, vp, vp, vp]),
+        "tafl_leaf_eval_host": (C.c_int, [vp, vp, vp]),
         "tafl_pack_records": (C.c_int, [vp, vp]),
     }
     for name, (res, args) in sig.items():

@@ -23,6 +23,15 @@ struct MctsPools {
     uint32_t* r_best = nullptr;
     uint32_t* d_any_overflow = nullptr;
     bool searched = false;
+    // evaluator hook (tafl_mcts_begin / select_leaves / expand_backup): the leaf batch of one round
+    tafl_state* l_state = nullptr;    // [n_games]
+    uint8_t* l_planes = nullptr;      // [n_games][side_len^2]  board_to_matrix
+    tafl_move* l_moves = nullptr;     // [n_games][TAFL_MAX_MOVES]
+    uint32_t* l_counts = nullptr;     // [n_games]
+    float* l_priors = nullptr;        // [n_games][TAFL_MAX_MOVES]  evaluator output
+    float* l_values = nullptr;        // [n_games]                  evaluator output
+    int phase = 0;                    // 0 idle, 1 begun / expanded, 2 leaves selected (evaluation pending)
+    uint32_t rounds = 0;              // simulations run since tafl_mcts_begin
 };
 
 }  // namespace tafl
@@ -43,7 +52,87 @@ __global__ void k_mcts_init(const tafl_state* __restrict__ states, uint32_t n, M
     mv.t_nodes[g] = 1;
     mv.t_edges[g] = 0;
     mv.t_overflow[g] = 0;
+    if (mv.t_pending) mv.t_pending[g] = MCTS_NO_PARENT;
     atomicAdd(&mv.stats[ST_NODES], 1ull);   // the root (oracle: Mcts::reset -> new_node)
+}
+
+// PUCT argmax over the L edges of one node by one warp (mcts.py:104-119): f64, the oracle's exact
+// operation order, strict '>' per lane, then a shuffle argmax that breaks ties toward the lower
+// action index = mcts.py's first-max.  PRIORS = false: uniform P = 1/L (stub evaluator);
+// PRIORS = true: per-action P read from `prior` (evaluator hook).
+template <bool PRIORS>
+__device__ __forceinline__ void warp_puct_select(const MctsEdge* __restrict__ ed, const double* __restrict__ prior, uint32_t L,
+                                                 uint32_t Ns, double cpuct, int lane, uint32_t& out_a, uint32_t& out_N,
+                                                 uint32_t& out_child) {
+    const double sq_vis = sqrt((double)Ns), sq_new = sqrt((double)Ns + MCTS_EPS);
+    const double c_uni = cpuct * (1.0 / (double)L);          // uniform prior over the valid moves
+    const double t_vis = c_uni * sq_vis;                      // numerator for visited edges
+    const double u_new = c_uni * sq_new;
+    double best_u = -INFINITY;
+    uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
+    // four edges per lane in flight: the loads of a group are issued before any is used
+    for (uint32_t a0 = lane; a0 < L; a0 += 128) {
+        MctsEdge e4[4];
+        double p4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + 32u * j;
+            if (a < L) {
+                e4[j] = ed[a];
+                if (PRIORS) p4[j] = prior[a];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + 32u * j;
+            if (a < L) {
+                double u;
+                if (PRIORS) {
+                    const double c = cpuct * p4[j];
+                    if (e4[j].N > 0) u = e4[j].Q + (c * sq_vis) / (double)(1u + e4[j].N);
+                    else u = c * sq_new;
+                } else {
+                    if (e4[j].N > 0) u = e4[j].Q + t_vis / (double)(1u + e4[j].N);
+                    else u = u_new;
+                }
+                if (u > best_u) { best_u = u; best_a = a; best_N = e4[j].N; best_child = e4[j].child; }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ou = __shfl_xor_sync(0xFFFFFFFFu, best_u, o);
+        const uint32_t oa = __shfl_xor_sync(0xFFFFFFFFu, best_a, o);
+        const uint32_t on = __shfl_xor_sync(0xFFFFFFFFu, best_N, o);
+        const uint32_t oc = __shfl_xor_sync(0xFFFFFFFFu, best_child, o);
+        if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; best_N = on; best_child = oc; }
+    }
+    out_a = best_a; out_N = best_N; out_child = best_child;
+}
+
+// backup (mcts.py:125-136): walk the parent links from `node`, incremental-mean Q, sign flip per ply
+__device__ __forceinline__ void warp_backup(uint4* __restrict__ n_hdr, MctsEdge* __restrict__ edges, uint32_t node, double v, int lane) {
+    while (true) {
+        const uint4 h = n_hdr[node];
+        if (h.z == MCTS_NO_PARENT) break;
+        const uint32_t parent = h.z, a = hdr_pedge(h.w);
+        uint4 ph = n_hdr[parent];
+        MctsEdge* const ep = edges + ph.x + a;
+        const MctsEdge e = *ep;
+        double q;
+        if (e.N > 0) q = ((double)e.N * e.Q + v) / (double)(e.N + 1u);
+        else q = v;
+        __syncwarp();
+        if (lane == 0) {
+            ep->Q = q;
+            ep->N = e.N + 1u;
+            ph.y += 1u;   // Ns[s] += 1
+            n_hdr[parent] = ph;
+        }
+        __syncwarp();
+        v = -v;
+        node = parent;
+    }
 }
 
 // `sims` x MCTS.search (mcts.py:55-136) for every tree; warp w of the grid owns tree w.
@@ -98,39 +187,8 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
             // ---- select (mcts.py:104-119) --------------------------------------------------------
             const uint32_t L = hdr_n_edges(h.w), base = h.x, Ns = h.y;
             if (L == 0) { v = 0.0; break; }   // Ongoing node without plays: oracle returns 0.0 unnegated
-            const double P = 1.0 / (double)L;                    // uniform prior over the valid moves
-            const double c = cpuct * P;
-            const double t_vis = c * sqrt((double)Ns);           // numerator for visited edges
-            const double u_new = c * sqrt((double)Ns + MCTS_EPS);
-            double best_u = -INFINITY;
-            uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
-            // four edges per lane in flight: the loads of a group are issued before any is used
-            for (uint32_t a0 = lane; a0 < L; a0 += 128) {
-                MctsEdge e4[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint32_t a = a0 + 32u * j;
-                    if (a < L) e4[j] = edges[base + a];
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint32_t a = a0 + 32u * j;
-                    if (a < L) {
-                        double u;
-                        if (e4[j].N > 0) u = e4[j].Q + t_vis / (double)(1u + e4[j].N);
-                        else u = u_new;
-                        if (u > best_u) { best_u = u; best_a = a; best_N = e4[j].N; best_child = e4[j].child; }
-                    }
-                }
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const double ou = __shfl_xor_sync(0xFFFFFFFFu, best_u, o);
-                const uint32_t oa = __shfl_xor_sync(0xFFFFFFFFu, best_a, o);
-                const uint32_t on = __shfl_xor_sync(0xFFFFFFFFu, best_N, o);
-                const uint32_t oc = __shfl_xor_sync(0xFFFFFFFFu, best_child, o);
-                if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; best_N = on; best_child = oc; }
-            }
+            uint32_t best_a, best_N, best_child;
+            warp_puct_select<false>(edges + base, nullptr, L, Ns, cpuct, lane, best_a, best_N, best_child);
             const uint32_t a = best_a;
             uint32_t child;
             if (best_N == 0) {   // first traversal: getNextState (mcts.py:122-123)
@@ -154,27 +212,7 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
         }
         if (overflow) break;
         // ---- backup (mcts.py:125-136) ----------------------------------------------------------------
-        while (true) {
-            const uint4 h = n_hdr[node];
-            if (h.z == MCTS_NO_PARENT) break;
-            const uint32_t parent = h.z, a = hdr_pedge(h.w);
-            uint4 ph = n_hdr[parent];
-            MctsEdge* const ep = edges + ph.x + a;
-            const MctsEdge e = *ep;
-            double q;
-            if (e.N > 0) q = ((double)e.N * e.Q + v) / (double)(e.N + 1u);
-            else q = v;
-            __syncwarp();
-            if (lane == 0) {
-                ep->Q = q;
-                ep->N = e.N + 1u;
-                ph.y += 1u;   // Ns[s] += 1
-                n_hdr[parent] = ph;
-            }
-            __syncwarp();
-            v = -v;
-            node = parent;
-        }
+        warp_backup(n_hdr, edges, node, v, lane);
         c_sims += 1;
     }
     if (lane == 0) {
@@ -292,6 +330,240 @@ k_pack_records(MctsView mv, const tafl_state* __restrict__ states, uint32_t n, u
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Evaluator hook: MCTS.search (mcts.py:55-136) cut at `nnet.predict` (mcts.py:85).
+// One round = one simulation in EVERY tree: k_mcts_select_leaf descends to the leaf and emits the
+// leaf batch, the evaluator (any code enqueued on the engine's stream) fills priors and values,
+// k_mcts_expand_backup masks / renormalises the priors exactly as mcts.py:87-99 does and backs the
+// value up.  A simulation that meets a terminal node completes inside the first phase.
+// ---------------------------------------------------------------------------------------------
+
+// board_to_matrix (game/main.rs:55-83): corners 20, throne 30, + 1 per soldier, + 5 for the king
+template <class BB, int SP>
+__device__ __forceinline__ void warp_board_planes(const Ctx<BB, SP>& cx, const Pos<BB>& p, uint8_t* __restrict__ out, int lane) {
+    const int n = cx.n(), mid = n / 2;
+    const BB occ = p.occ(), king = p.king();
+    for (int t = lane; t < n * n; t += 32) {
+        const int r = t / n, c = t - r * n, b = idx_of<BB>(r, c);
+        int v = 0;
+        if ((r == 0 || r == n - 1) && (c == 0 || c == n - 1)) v = 20;
+        if (r == mid && c == mid) v = 30;
+        if (occ.test(b)) v += king.test(b) ? 5 : 1;
+        out[t] = (uint8_t)v;
+    }
+}
+
+template <class BB, int SP>
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_mcts_select_leaf(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, double cpuct, double draw_value,
+                   tafl_state* __restrict__ l_state, uint8_t* __restrict__ l_planes, tafl_move* __restrict__ l_moves,
+                   uint32_t* __restrict__ l_counts, uint32_t* __restrict__ any_overflow) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (tree >= n_trees) return;
+    tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    const double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
+    uint32_t want = 0, pending = MCTS_NO_PARENT;
+    if (mv.t_overflow[tree] == 0 && mv.t_nodes[tree] < mv.node_cap) {
+        uint32_t node = 0, depth = 0;
+        while (true) {
+            const uint4 h = n_hdr[node];
+            const uint32_t es = hdr_es(h.w);
+            if (es != ES_ONGOING) {   // mcts.py:77-81: no evaluation, the simulation completes here
+                const double Es = es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value);
+                warp_backup(n_hdr, edges, node, -Es, lane);
+                if (lane == 0) {
+                    atomicAdd(&mv.stats[ST_TERMINAL], 1ull);
+                    atomicAdd(&mv.stats[ST_DEPTH], (unsigned long long)depth);
+                    atomicAdd(&mv.stats[ST_SIMS], 1ull);
+                }
+                break;
+            }
+            if (!hdr_expanded(h.w)) {   // mcts.py:83-86: leaf, ask the evaluator
+                const tafl_state s = load_state(n_state + node);
+                const Pos<BB> p = load_pos(cx, s);
+                const int def_side = (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
+                uint32_t* const ptab = n_ptab + (size_t)node * MCTS_PT_MAX;
+                int n_pieces;
+                const int L = warp_build_ptab(cx, p, def_side, ptab, lane, &n_pieces);
+                if ((uint32_t)L > mv.edge_cap - mv.t_edges[tree] || n_pieces > MCTS_PT_MAX || L > TAFL_MAX_MOVES) {
+                    if (lane == 0) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+                    break;
+                }
+                if (L == 0) {   // Ongoing position without plays: unreachable through do_play; expand empty, v = 0
+                    if (lane == 0) n_hdr[node] = make_uint4(mv.t_edges[tree], 0u, h.z, hdr_pack(0u, hdr_pedge(h.w), 1u, es, (uint32_t)n_pieces));
+                    __syncwarp();
+                    warp_backup(n_hdr, edges, node, -0.0, lane);
+                    if (lane == 0) atomicAdd(&mv.stats[ST_SIMS], 1ull);
+                    break;
+                }
+                __syncwarp();
+                // the leaf batch row: position, planes, canonical move list (action index -> move)
+                if (lane == 0) {
+                    store_state(l_state + tree, s);
+                    n_hdr[node] = make_uint4(0u, 0u, h.z, hdr_pack((uint32_t)L, hdr_pedge(h.w), 0u, es, (uint32_t)n_pieces));
+                }
+                warp_board_planes(cx, p, l_planes + (size_t)tree * (size_t)(cx.n() * cx.n()), lane);
+                tafl_move* const mo = l_moves + (size_t)tree * TAFL_MAX_MOVES;
+                int before = 0;
+                for (int base = 0; base < n_pieces; base += 32) {
+                    const int idx = base + lane;
+                    const uint32_t e = idx < n_pieces ? ptab[idx] : 0u;
+                    const int c = pt_total(e);
+                    int incl = c;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                        if (lane >= o) incl += t;
+                    }
+                    const int off = before + incl - c;
+                    for (int j = 0; j < c; ++j) mo[off + j] = pt_decode(cx, e, def_side, j);
+                    before += __shfl_sync(0xFFFFFFFFu, incl, 31);
+                }
+                want = (uint32_t)L;
+                pending = node;
+                if (lane == 0) atomicAdd(&mv.stats[ST_DEPTH], (unsigned long long)depth);
+                break;
+            }
+            const uint32_t L = hdr_n_edges(h.w), base = h.x, Ns = h.y;
+            if (L == 0) {
+                warp_backup(n_hdr, edges, node, 0.0, lane);
+                if (lane == 0) atomicAdd(&mv.stats[ST_SIMS], 1ull);
+                break;
+            }
+            uint32_t a, best_N, best_child;
+            warp_puct_select<true>(edges + base, prior + base, L, Ns, cpuct, lane, a, best_N, best_child);
+            uint32_t child;
+            if (best_N == 0) {   // first traversal: getNextState (mcts.py:122-123)
+                tafl_state s = load_state(n_state + node);
+                const tafl_move m = warp_decode_edge(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
+                                                     (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)a, lane);
+                do_valid_move(cx, s, m);
+                child = mv.t_nodes[tree];
+                __syncwarp();
+                if (lane == 0) {
+                    mv.t_nodes[tree] = child + 1u;
+                    store_state(n_state + child, s);
+                    n_hdr[child] = make_uint4(0u, 0u, node, hdr_pack(0, a, 0, es_code(s)));
+                    edges[base + a].child = child;
+                    atomicAdd(&mv.stats[ST_NODES], 1ull);
+                }
+                __syncwarp();
+            } else {
+                child = best_child;
+            }
+            node = child;
+            depth += 1;
+        }
+    }
+    if (lane == 0) {
+        l_counts[tree] = want;
+        mv.t_pending[tree] = pending;
+    }
+}
+
+// mcts.py:87-102 for the pending leaf of every tree, then the backup of -v (mcts.py:125-136).
+// np.sum (mcts.py:88,99) is numpy's pairwise add-reduce over the action_size = 512 vector: four
+// 128-element blocks of eight stride-8 accumulators — lane = 8*block + accumulator reproduces
+// its association order exactly (see oracle/mcts_oracle.hpp np_pairwise_sum).
+__device__ __forceinline__ double warp_np_sum512(const double (&x)[16], int lane) {
+    double r = x[0];
+#pragma unroll
+    for (int i = 1; i < 16; ++i) r += x[i];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) r += __shfl_xor_sync(0xFFFFFFFFu, r, o);
+    (void)lane;
+    return 0.0 + r;
+}
+
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_mcts_expand_backup(MctsView mv, uint32_t n_trees, const float* __restrict__ l_priors, const float* __restrict__ l_values) {
+    static_assert(TAFL_MAX_MOVES == 512, "np.sum restatement is laid out for action_size == 512");
+    const int lane = threadIdx.x & 31;
+    const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (tree >= n_trees) return;
+    const uint32_t node = mv.t_pending[tree];
+    if (node == MCTS_NO_PARENT) return;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
+    const uint4 h = n_hdr[node];
+    const uint32_t L = hdr_n_edges(h.w), base = mv.t_edges[tree];
+    const float* const pf = l_priors + (size_t)tree * TAFL_MAX_MOVES;
+    const int blk = lane >> 3, acc = lane & 7;
+    double x[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
+        x[i] = (double)pf[a] * (a < L ? 1.0 : 0.0);   // self.Ps[s] * valids  (mcts.py:87)
+    }
+    double sum = warp_np_sum512(x, lane);                 // mcts.py:88
+    if (!(sum > 0)) {                                      // mcts.py:91-99: all valid moves were masked
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
+            x[i] = x[i] + (a < L ? 1.0 : 0.0);
+        }
+        sum = warp_np_sum512(x, lane);
+    }
+    MctsEdge z;
+    z.Q = 0.0; z.N = 0u; z.child = 0u;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
+        if (a < L) {
+            prior[base + a] = x[i] / sum;                  // mcts.py:90 / :99
+            edges[base + a] = z;
+        }
+    }
+    const double v = (double)l_values[tree];
+    if (lane == 0) {
+        n_hdr[node] = make_uint4(base, 0u, h.z, h.w | (1u << 20));   // expanded, Ns = 0 (mcts.py:101)
+        mv.t_edges[tree] = base + L;
+        mv.t_pending[tree] = MCTS_NO_PARENT;
+        atomicAdd(&mv.stats[ST_EDGES], (unsigned long long)L);
+        atomicAdd(&mv.stats[ST_SIMS], 1ull);
+        atomicMax(&mv.stats[ST_MAXEDGES], (unsigned long long)(base + L));
+    }
+    __syncwarp();
+    warp_backup(n_hdr, edges, node, -v, lane);             // mcts.py:102: return -v
+}
+
+// built-in evaluators (device side of TAFL_EVAL_STUB / TAFL_EVAL_HASH), one warp per leaf
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_eval_builtin(int kind, uint64_t seed, const tafl_state* __restrict__ l_state, const uint32_t* __restrict__ l_counts, uint32_t n,
+               float* __restrict__ priors, float* __restrict__ values) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t g = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (g >= n || l_counts[g] == 0) return;
+    float* const P = priors + (size_t)g * TAFL_MAX_MOVES;
+    if (kind == TAFL_EVAL_STUB) {   // uniform over the action space, value 0 (the north-star stub)
+        for (int a = lane; a < TAFL_MAX_MOVES; a += 32) P[a] = 1.0f / (float)TAFL_MAX_MOVES;
+        if (lane == 0) values[g] = 0.0f;
+        return;
+    }
+    const tafl_state s = load_state(l_state + g);
+    const uint64_t side = (s.flags & TAFL_FLAG_DEF_TO_PLAY) ? 1u : 0u;
+    uint64_t h = splitmix64(s.def[1] ^ side);
+    h = splitmix64(s.def[0] ^ h);
+    h = splitmix64(s.att[1] ^ h);
+    h = splitmix64(s.att[0] ^ h);
+    h = splitmix64(seed ^ h);
+    const bool masked = (h & 15u) == 0;
+    for (int a = lane; a < TAFL_MAX_MOVES; a += 32) {
+        const uint64_t x = splitmix64(h + (uint64_t)(a + 1) * 0x9E3779B97F4A7C15ull);
+        P[a] = masked ? 0.0f : (float)((x >> 40) + 1) * 5.9604644775390625e-08f;
+    }
+    if (lane == 0) {
+        const uint64_t y = splitmix64(h ^ 0xD1B54A32D192ED03ull);
+        values[g] = ((float)(long long)(y >> 40) - 8388608.0f) * 5.9604644775390625e-08f;
+    }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -305,6 +577,8 @@ void mcts_free(tafl_engine* e) {
     cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.n_ptab); cudaFree(m->v.edges); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
     cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best);
     cudaFree(m->d_any_overflow);
+    cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
+    cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
     delete m;
     e->mcts = nullptr;
 }
@@ -489,6 +763,180 @@ int tafl_pack_records(tafl_engine* e, void* d_out) {
                                                                               m->r_visits, m->r_counts, m->r_best, (uint8_t*)d_out);
     MCTS_LAUNCHED(e);
     return TAFL_OK;
+}
+
+}  // extern "C"
+
+// ---- evaluator hook -------------------------------------------------------------------------
+static int eval_alloc(tafl_engine* e) {
+    MctsPools* m = e->mcts;
+    if (m->v.e_prior) return TAFL_OK;
+    const size_t n = e->n_games, cells = (size_t)e->N * e->N;
+#define EVAL_ALLOC(ptr, bytes)                                                                   \
+    do {                                                                                         \
+        cudaError_t _ce = cudaMalloc((void**)&(ptr), (bytes));                                   \
+        if (_ce != cudaSuccess) return set_cuda_error(e, _ce, "cudaMalloc(" #ptr ")");           \
+    } while (0)
+    EVAL_ALLOC(m->v.t_pending, n * sizeof(uint32_t));
+    EVAL_ALLOC(m->l_state, n * sizeof(tafl_state));
+    EVAL_ALLOC(m->l_planes, n * cells);
+    EVAL_ALLOC(m->l_moves, n * TAFL_MAX_MOVES * sizeof(tafl_move));
+    EVAL_ALLOC(m->l_counts, n * sizeof(uint32_t));
+    EVAL_ALLOC(m->l_priors, n * TAFL_MAX_MOVES * sizeof(float));
+    EVAL_ALLOC(m->l_values, n * sizeof(float));
+    EVAL_ALLOC(m->v.e_prior, n * (size_t)m->v.edge_cap * sizeof(double));   // last: marks the set complete
+#undef EVAL_ALLOC
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->l_priors, 0, n * TAFL_MAX_MOVES * sizeof(float), e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->l_values, 0, n * sizeof(float), e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->l_moves, 0, n * TAFL_MAX_MOVES * sizeof(tafl_move), e->stream));
+    return TAFL_OK;
+}
+
+static void fill_batch(tafl_engine* e, tafl_leaf_batch* b) {
+    MctsPools* m = e->mcts;
+    b->d_states = m->l_state; b->d_planes = m->l_planes; b->d_moves = m->l_moves; b->d_counts = m->l_counts;
+    b->d_priors = m->l_priors; b->d_values = m->l_values;
+    b->n_games = e->n_games; b->side_len = (uint32_t)e->N;
+    b->stream = (void*)e->stream;
+}
+
+extern "C" {
+
+int tafl_mcts_begin(tafl_engine* e) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    cudaSetDevice(e->device);
+    rc = eval_alloc(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    k_mcts_init<<<grid_for(e->n_games, 128), 128, 0, e->stream>>>(e->d_states, e->n_games, m->v);
+    MCTS_LAUNCHED(e);
+    m->phase = 1;
+    m->rounds = 0;
+    m->searched = false;
+    return TAFL_OK;
+}
+
+int tafl_mcts_select_leaves(tafl_engine* e, tafl_leaf_batch* out) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (m->phase != 1) { e->err = "tafl_mcts_select_leaves: call tafl_mcts_begin / tafl_mcts_expand_backup first"; return TAFL_ERR_INVALID_ARG; }
+    if (m->rounds >= m->cfg.num_sims) { e->err = "tafl_mcts_select_leaves: num_sims rounds already run (node pool is sized for num_sims)"; return TAFL_ERR_CAPACITY; }
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    TAFL_SPEC_DISPATCH(e, (k_mcts_select_leaf<BB, SP><<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(
+                              cx, m->v, n, m->cfg.cpuct, m->cfg.draw_value, m->l_state, m->l_planes, m->l_moves, m->l_counts,
+                              m->d_any_overflow)));
+    MCTS_LAUNCHED(e);
+    m->phase = 2;
+    if (out) fill_batch(e, out);
+    return TAFL_OK;
+}
+
+int tafl_mcts_expand_backup(tafl_engine* e) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (m->phase != 2) { e->err = "tafl_mcts_expand_backup: no leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    k_mcts_expand_backup<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->l_priors, m->l_values);
+    MCTS_LAUNCHED(e);
+    m->phase = 1;
+    m->rounds += 1;
+    return TAFL_OK;
+}
+
+int tafl_mcts_finish(tafl_engine* e) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (m->phase != 1) { e->err = "tafl_mcts_finish: a leaf batch is still pending (or no search was begun)"; return TAFL_ERR_INVALID_ARG; }
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    TAFL_SPEC_DISPATCH(e, (k_mcts_results<BB, SP><<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(
+                              cx, m->v, n, m->r_moves, m->r_visits, m->r_q, m->r_counts, m->r_best)));
+    MCTS_LAUNCHED(e);
+    m->searched = true;
+    m->phase = 0;
+    uint32_t of = 0;
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(&of, m->d_any_overflow, sizeof(of), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    if (of) {
+        e->err = "MCTS edge pool exhausted for at least one tree: raise tafl_mcts_config.edge_capacity";
+        return TAFL_ERR_CAPACITY;
+    }
+    return TAFL_OK;
+}
+
+int tafl_eval_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (evaluator != TAFL_EVAL_STUB && evaluator != TAFL_EVAL_HASH) return TAFL_ERR_INVALID_ARG;
+    if (!m->l_state) { e->err = "tafl_eval_builtin: no leaf batch (tafl_mcts_begin has not been called)"; return TAFL_ERR_INVALID_ARG; }
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    k_eval_builtin<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(evaluator, seed, m->l_state, m->l_counts, n, m->l_priors,
+                                                                              m->l_values);
+    MCTS_LAUNCHED(e);
+    return TAFL_OK;
+}
+
+// host copies of the pending leaf batch / host-computed evaluator outputs (callers without a CUDA runtime)
+int tafl_leaf_batch_host(tafl_engine* e, tafl_state* h_states, uint8_t* h_planes, tafl_move* h_moves, uint32_t* h_counts) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (m->phase != 2) { e->err = "tafl_leaf_batch_host: no leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
+    cudaSetDevice(e->device);
+    const size_t n = e->n_games, cells = (size_t)e->N * e->N;
+    if (h_states) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_states, m->l_state, n * sizeof(tafl_state), cudaMemcpyDeviceToHost, e->stream));
+    if (h_planes) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_planes, m->l_planes, n * cells, cudaMemcpyDeviceToHost, e->stream));
+    if (h_moves) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_moves, m->l_moves, n * TAFL_MAX_MOVES * sizeof(tafl_move), cudaMemcpyDeviceToHost, e->stream));
+    if (h_counts) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_counts, m->l_counts, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return TAFL_OK;
+}
+int tafl_leaf_eval_host(tafl_engine* e, const float* h_priors, const float* h_values) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (m->phase != 2 || !h_priors || !h_values) { e->err = "tafl_leaf_eval_host: no leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
+    cudaSetDevice(e->device);
+    const size_t n = e->n_games;
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(m->l_priors, h_priors, n * TAFL_MAX_MOVES * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(m->l_values, h_values, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return TAFL_OK;
+}
+
+int tafl_mcts_search_with(tafl_engine* e, tafl_evaluator_fn fn, void* user) {
+    if (!fn) return TAFL_ERR_INVALID_ARG;
+    int rc = tafl_mcts_begin(e);
+    if (rc) return rc;
+    tafl_leaf_batch b;
+    for (uint32_t i = 0; i < e->mcts->cfg.num_sims; ++i) {
+        rc = tafl_mcts_select_leaves(e, &b);
+        if (rc) return rc;
+        rc = fn(user, &b);
+        if (rc) { e->err = "evaluator callback failed"; e->mcts->phase = 0; return rc < 0 ? rc : TAFL_ERR_INVALID_ARG; }
+        rc = tafl_mcts_expand_backup(e);
+        if (rc) return rc;
+    }
+    return tafl_mcts_finish(e);
+}
+
+struct BuiltinEval { tafl_engine* e; int kind; uint64_t seed; };
+static int builtin_eval_cb(void* user, const tafl_leaf_batch*) {
+    BuiltinEval* b = (BuiltinEval*)user;
+    return tafl_eval_builtin(b->e, b->kind, b->seed);
+}
+int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
+    if (evaluator != TAFL_EVAL_STUB && evaluator != TAFL_EVAL_HASH) return TAFL_ERR_INVALID_ARG;
+    BuiltinEval b{e, evaluator, seed};
+    return tafl_mcts_search_with(e, builtin_eval_cb, &b);
 }
 
 }  // extern "C"

@@ -59,6 +59,8 @@ struct MctsView {   // raw device pointers, passed to kernels by value
     uint32_t* t_edges;     // [trees] edges in use
     uint32_t* t_overflow;  // [trees] 1 = edge pool exhausted (search of that tree stopped)
     unsigned long long* stats;   // sims, nodes, depth_sum, edges, terminal_hits, max_edges_used
+    double* e_prior;       // [trees][edge_cap]  Ps[s][a] (evaluator-hook searches only, else nullptr)
+    uint32_t* t_pending;   // [trees] leaf waiting for its evaluation between the two phases (or MCTS_NO_PARENT)
     uint32_t node_cap, edge_cap;
 };
 

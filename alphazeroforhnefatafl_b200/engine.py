@@ -82,6 +82,16 @@ def state_to_fen(st, width):
     return buf.value.decode()
 
 
+def board_to_matrix(st, width):
+    """board_to_matrix (game/main.rs:55-83) of ONE packed state: [side_len, side_len] uint8 with
+    corners 20, throne 30, +1 per soldier, +5 for the king (sides are not distinguished)."""
+    st = np.ascontiguousarray(st, A.STATE_DTYPE).reshape(-1)[:1]
+    n = int(st["side_len"][0])
+    out = np.zeros((n, n), np.uint8)
+    _check(lib().tafl_board_to_matrix(A.ptr(st), width, A.ptr(out), n * n))
+    return out
+
+
 def play_from_str(s):
     p = A.Play()
     _check(lib().tafl_play_from_str(s.encode(), C.byref(p)))
@@ -296,6 +306,60 @@ class LockstepGames:
         s = A.MctsStats()
         self._ck(lib().tafl_mcts_stats_get(self._h, C.byref(s)))
         return s
+
+    # -- evaluator hook: nnet.predict (mcts.py:85) as a batched device boundary ---------------------
+    def mcts_begin(self):
+        self._ck(lib().tafl_mcts_begin(self._h))
+
+    def mcts_select_leaves(self):
+        """Phase 1 of one simulation in every tree; returns the LeafBatch of device pointers."""
+        b = A.LeafBatch()
+        self._ck(lib().tafl_mcts_select_leaves(self._h, C.byref(b)))
+        return b
+
+    def mcts_expand_backup(self):
+        self._ck(lib().tafl_mcts_expand_backup(self._h))
+
+    def mcts_finish(self):
+        self._ck(lib().tafl_mcts_finish(self._h))
+
+    def eval_builtin(self, evaluator, seed=0):
+        self._ck(lib().tafl_eval_builtin(self._h, evaluator, seed))
+
+    def mcts_search_builtin(self, evaluator, seed=0):
+        self._ck(lib().tafl_mcts_search_builtin(self._h, evaluator, seed))
+
+    def mcts_search_with(self, fn):
+        """fn(batch: LeafBatch) enqueues the evaluator on batch.stream; called num_sims times."""
+        err = []
+
+        def tramp(_user, bp):
+            try:
+                fn(bp.contents)
+                return 0
+            except Exception as ex:   # noqa: BLE001  (must not unwind through the C frames)
+                err.append(ex)
+                return -1
+        cb = A.EVALUATOR_FN(tramp)
+        rc = lib().tafl_mcts_search_with(self._h, cb, None)
+        if err:
+            raise err[0]
+        self._ck(rc)
+
+    def leaf_batch_host(self):
+        n, cells = self.n_games, self.side_len * self.side_len
+        st = np.zeros(n, A.STATE_DTYPE)
+        planes = np.zeros((n, cells), np.uint8)
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        counts = np.zeros(n, np.uint32)
+        self._ck(lib().tafl_leaf_batch_host(self._h, A.ptr(st), A.ptr(planes), A.ptr(moves), A.ptr(counts)))
+        return dict(states=st, planes=planes, moves=moves, counts=counts)
+
+    def leaf_eval_host(self, priors, values):
+        priors = np.ascontiguousarray(priors, np.float32)
+        values = np.ascontiguousarray(values, np.float32)
+        assert priors.shape == (self.n_games, A.MAX_MOVES) and values.shape == (self.n_games,)
+        self._ck(lib().tafl_leaf_eval_host(self._h, A.ptr(priors), A.ptr(values)))
 
     def pack_records(self, d_out):
         self._ck(lib().tafl_pack_records(self._h, d_out))

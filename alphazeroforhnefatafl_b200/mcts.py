@@ -10,7 +10,8 @@ game on the GPU); names and argument meaning follow the reference:
     search()                          (mcts.py:55-136) -> runs the batched simulations only
 
 Differences that the reference leaves undefined and this build defines (SURVEY.md §A.11,
-DESIGN.md): the evaluator is the fixed stub (uniform priors over the legal moves, value 0); action
+DESIGN.md): the default evaluator is the fixed stub (uniform priors over the legal moves, value
+0) fused into one kernel; a real evaluator plugs in as ``nnet`` (see :class:`MCTS`); action
 index = position in the canonical legal-move list of the position; tree (not transposition-merged)
 node identity; temp == 0 picks the FIRST maximum instead of a random one among ties.
 """
@@ -24,9 +25,14 @@ EPS = 1e-8   # mcts.py:6
 class MCTS:
     def __init__(self, games, args=None, nnet=None):
         """games: engine.LockstepGames; args: object with numMCTSSims and cpuct (mcts.py:16-26).
-        nnet must be None: only the stub evaluator exists on this path."""
-        if nnet is not None:
-            raise NotImplementedError("only the uniform-prior / value-0 stub evaluator is built (BASELINE.json north_star)")
+
+        nnet: None -> the stub evaluator, whole search in one fused kernel.  Otherwise the batched
+        form of ``nnet.predict`` (mcts.py:85): an object with ``predict_batch(batch)`` that, for
+        the ``_abi.LeafBatch`` of device pointers it is given, enqueues work on ``batch.stream``
+        that writes ``d_priors`` [n, MAX_MOVES] f32 (action a = a-th canonical legal move of the
+        leaf, ``d_moves``) and ``d_values`` [n] f32 for every row with ``d_counts > 0``; or one of
+        the built-in device evaluators as ``("stub",)`` / ``("hash", seed)``."""
+        self.nnet = nnet
         self.games = games
         self.args = args or SimpleNamespace(numMCTSSims=800, cpuct=1.0)
         self.draw_value = getattr(self.args, "drawValue", 1e-4)
@@ -35,7 +41,14 @@ class MCTS:
 
     def search(self, sync=True):
         """numMCTSSims simulations from a fresh tree rooted at every game's current state."""
-        self.games.mcts_search(sync=sync)
+        from . import _abi as A
+        if self.nnet is None:
+            self.games.mcts_search(sync=sync)
+        elif isinstance(self.nnet, tuple):
+            kind = {"stub": A.EVAL_STUB, "hash": A.EVAL_HASH}[self.nnet[0]]
+            self.games.mcts_search_builtin(kind, int(self.nnet[1]) if len(self.nnet) > 1 else 0)
+        else:
+            self.games.mcts_search_with(self.nnet.predict_batch)
 
     def getActionProb(self, temp=1):  # noqa: N802  (reference name)
         """Returns (moves [n, MAX_MOVES] u16, probs [n, MAX_MOVES] f64, counts [n]): for game i the

@@ -435,6 +435,63 @@ typedef struct {
 int tafl_mcts_stats_get(tafl_engine* e, tafl_mcts_stats* out);
 
 /* ------------------------------------------------------------------------------------------
+ * Evaluator hook: `self.nnet.predict(canonicalBoard)` (src/mcts.py:85) as a
+ * batched DEVICE boundary.  A search is num_sims ROUNDS; one round runs one MCTS.search
+ * (mcts.py:55-136) in every tree, cut in two at the evaluator call:
+ *
+ *   tafl_mcts_begin(e)                    fresh trees rooted at the games' current states
+ *   repeat num_sims times:
+ *     tafl_mcts_select_leaves(e, &batch)  PUCT descent with per-action priors (mcts.py:104-123);
+ *                                         trees that reach a terminal node finish their
+ *                                         simulation here (mcts.py:77-81) and ask for nothing
+ *     <evaluator>                         any work enqueued on batch.stream that fills
+ *                                         batch.d_priors / batch.d_values for rows with
+ *                                         d_counts > 0 (other rows are ignored)
+ *     tafl_mcts_expand_backup(e)          mask + renormalise with numpy's np.sum order, the
+ *                                         "all valid moves were masked" fallback (mcts.py:87-99),
+ *                                         Ns = 0, backup of -v (mcts.py:101-102, 125-136)
+ *   tafl_mcts_finish(e)                   root results, as after tafl_mcts_search
+ *
+ * Action index a == position in the leaf's canonical legal-move list d_moves[row][a]; priors
+ * at a >= d_counts[row] are masked.  Priors and value cross the boundary as f32 (what a
+ * network emits) and are widened to f64 before any arithmetic.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct {
+    const tafl_state* d_states;   /* [n_games] leaf positions                                    */
+    const uint8_t*    d_planes;   /* [n_games][side_len^2] board_to_matrix (game/main.rs:55-83)  */
+    const tafl_move*  d_moves;    /* [n_games][TAFL_MAX_MOVES] canonical legal moves of the leaf */
+    const uint32_t*   d_counts;   /* [n_games] legal moves; 0 = no evaluation wanted this round  */
+    float*            d_priors;   /* [n_games][TAFL_MAX_MOVES] OUT                               */
+    float*            d_values;   /* [n_games] OUT, from the point of view of the side to move   */
+    uint32_t          n_games, side_len;
+    void*             stream;     /* cudaStream_t the evaluator must enqueue its work on         */
+} tafl_leaf_batch;
+typedef int (*tafl_evaluator_fn)(void* user, const tafl_leaf_batch* batch);   /* 0 = ok */
+
+int tafl_mcts_begin(tafl_engine* e);
+int tafl_mcts_select_leaves(tafl_engine* e, tafl_leaf_batch* out /* may be NULL */);
+int tafl_mcts_expand_backup(tafl_engine* e);
+int tafl_mcts_finish(tafl_engine* e);
+/* begin + num_sims x (select_leaves, fn(user, &batch), expand_backup) + finish */
+int tafl_mcts_search_with(tafl_engine* e, tafl_evaluator_fn fn, void* user);
+/* built-in device evaluators.  TAFL_EVAL_STUB: uniform priors over the action space, value 0
+ * (the north-star stub; results equal tafl_mcts_search bit for bit).  TAFL_EVAL_HASH: a
+ * deterministic TEST evaluator, priors and value are a hash of (seed, position, side to move):
+ *   h = splitmix64(seed ^ splitmix64(att[0] ^ splitmix64(att[1] ^ splitmix64(def[0] ^
+ *       splitmix64(def[1] ^ side)))));  all priors 0 if (h & 15) == 0 (exercises mcts.py:91-99),
+ *   else P[a] = ((splitmix64(h + (a+1)*0x9E3779B97F4A7C15) >> 40) + 1) * 2^-24;
+ *   v = ((splitmix64(h ^ 0xD1B54A32D192ED03) >> 40) - 2^23) * 2^-24.                          */
+#define TAFL_EVAL_STUB 0
+#define TAFL_EVAL_HASH 1
+int tafl_eval_builtin(tafl_engine* e, int evaluator, uint64_t seed);   /* fills the pending batch */
+/* the pending batch copied to HOST buffers (any may be NULL) / evaluator outputs taken from HOST
+ * buffers [n_games][TAFL_MAX_MOVES] f32 and [n_games] f32 — for callers without a CUDA runtime */
+int tafl_leaf_batch_host(tafl_engine* e, tafl_state* h_states, uint8_t* h_planes, tafl_move* h_moves,
+                         uint32_t* h_counts);
+int tafl_leaf_eval_host(tafl_engine* e, const float* h_priors, const float* h_values);
+int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed);
+
+/* ------------------------------------------------------------------------------------------
  * Self-play records (replay-buffer rows; nearest upstream analogue: write_to_file,
  * game/main.rs:86-132, with board_to_matrix :55-83 as the position encoding)
  * ---------------------------------------------------------------------------------------- */

@@ -72,3 +72,126 @@ def test_eval_oracle_matches_reference_mcts_py(orc, case):
     assert np.array_equal(got["visits"][0, :c], n)
     assert got["q"][0, :c].tobytes() == q.tobytes(), "Q differs from the reference in the last bits"
     assert got["stats"].nodes == case["n_nodes"]
+
+
+def _groups():
+    groups = {}
+    for case in CASES:
+        key = (case["preset"], case["width"], case["sims"], case["cpuct"], case["draw_value"], case["eval_seed"])
+        groups.setdefault(key, []).append(case)
+    return groups
+
+
+def _check(got, cases):
+    for i, case in enumerate(cases):
+        n, q = expected(case)
+        c = case["count"]
+        assert int(got["counts"][i]) == c
+        assert np.array_equal(got["visits"][i, :c], n), case["name"]
+        assert np.allclose(got["q"][i, :c], q, rtol=Q_RTOL, atol=0.0), case["name"]
+        assert got["q"][i, :c].tobytes() == q.tobytes(), case["name"]
+
+
+@pytest.mark.gpu
+def test_gpu_eval_search_matches_reference_mcts_py(orc, built_lib):
+    """built-in device evaluator, whole search on the device"""
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for
+    checked = 0
+    for (preset, width, sims, cpuct, dv, eseed), cases in _groups().items():
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        roots = np.concatenate([root_of(c) for c in cases])
+        with E.LockstepGames(rules, fen, len(cases), 0, width) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, cpuct, dv)
+            g.mcts_search_builtin(A.EVAL_HASH, eseed)
+            _check(g.mcts_results(), cases)
+            checked += len(cases)
+    assert checked == len(CASES)
+
+
+@pytest.mark.gpu
+def test_gpu_eval_boundary_with_host_priors(orc, built_lib):
+    """the real boundary: leaf batch out, priors / values computed OUTSIDE the library (here: on the
+    host by the oracle's copy of the hash evaluator, from the batch's leaf states), handed back"""
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for
+    done = 0
+    for (preset, width, sims, cpuct, dv, eseed), cases in _groups().items():
+        if sims > 400:
+            continue
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        bv = orc.by_value(rules, width)
+        roots = np.concatenate([root_of(c) for c in cases])
+        with E.LockstepGames(rules, fen, len(cases), 0, width) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, cpuct, dv)
+            g.mcts_begin()
+            for r in range(sims):
+                g.mcts_select_leaves()
+                b = g.leaf_batch_host()
+                live = b["counts"] > 0
+                if r == 0:
+                    assert live.all() and b["states"].tobytes() == roots.tobytes()
+                if r % 37 == 0 and live.any():   # the batch rows describe the leaf: moves and planes
+                    em, ec = bv.legal_moves_of(b["states"][live])
+                    assert np.array_equal(ec, b["counts"][live])
+                    for k, i in enumerate(np.nonzero(live)[0]):
+                        assert np.array_equal(b["moves"][i, :ec[k]], em[k, :ec[k]])
+                        assert np.array_equal(b["planes"][i], E.board_to_matrix(b["states"][i:i + 1], width).reshape(-1))
+                P, v = orc.hash_eval(b["states"], eseed)
+                P[~live] = np.nan      # rows that asked for nothing must be ignored
+                v[~live] = np.nan
+                g.leaf_eval_host(P, v)
+                g.mcts_expand_backup()
+            g.mcts_finish()
+            _check(g.mcts_results(), cases)
+            done += len(cases)
+    assert done >= 10
+
+
+@pytest.mark.gpu
+def test_gpu_stub_through_the_hook_equals_fused_search(orc, built_lib):
+    """TAFL_EVAL_STUB through select / evaluate / expand == the fused k_mcts_sims search, bit for bit"""
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for, sample_positions
+    for preset, width, sims in ((A.PRESET_COPENHAGEN, 128, 300), (A.PRESET_BRANDUBH, 64, 500)):
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        roots = sample_positions(orc, rules, fen, width, 96, seed=41, max_steps=150)
+        with E.LockstepGames(rules, fen, len(roots), 0, width) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, 1.25, 1e-4)
+            g.mcts_search()
+            a = g.mcts_results()
+            sa = g.mcts_stats().as_dict()
+            g.mcts_search_builtin(A.EVAL_STUB)
+            b = g.mcts_results()
+            sb = g.mcts_stats().as_dict()
+        for k in ("moves", "visits", "q", "counts", "best"):
+            assert a[k].tobytes() == b[k].tobytes(), k
+        for k in ("sims", "nodes", "depth_sum", "edges", "terminal_hits"):
+            assert sb[k] == 2 * sa[k], (k, sa[k], sb[k])
+
+
+@pytest.mark.gpu
+def test_gpu_eval_phase_errors(orc, built_lib):
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), board_for(orc, A.PRESET_BRANDUBH)
+    with E.LockstepGames(rules, fen, 4, 0, 64) as g:
+        g.mcts_configure(3, 1.0, 1e-4)
+        with pytest.raises(E.TaflError):
+            g.mcts_select_leaves()          # not begun
+        g.mcts_begin()
+        with pytest.raises(E.TaflError):
+            g.mcts_expand_backup()          # nothing pending
+        for _ in range(3):
+            g.mcts_select_leaves()
+            with pytest.raises(E.TaflError):
+                g.mcts_finish()             # evaluation pending
+            g.eval_builtin(A.EVAL_STUB)
+            g.mcts_expand_backup()
+        with pytest.raises(E.TaflError):
+            g.mcts_select_leaves()          # node pool is sized for num_sims rounds
+        g.mcts_finish()
+        assert g.mcts_results()["visits"].sum() == 4 * 2
