@@ -21,6 +21,7 @@ struct MctsPools {
     double* r_q = nullptr;
     uint32_t* r_counts = nullptr;
     uint32_t* r_best = nullptr;
+    double* r_probs = nullptr;        // [n_games][TAFL_MAX_MOVES], allocated by the first tafl_mcts_policy
     uint32_t* d_any_overflow = nullptr;
     bool searched = false;
     // evaluator hook (tafl_mcts_begin / select_leaves / expand_backup): the leaf batch of one round
@@ -279,6 +280,95 @@ k_mcts_results(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_t
         r_counts[tree] = L;
         r_best[tree] = best_n > 0 ? best_a : 0u;
     }
+}
+
+// MCTS.getActionProb's policy (mcts.py:40-53) and the move choice made from it, one warp per tree.
+//   temp == 0 : one-hot on the FIRST maximum (mcts.py:43-48 without the random tie choice)
+//   temp == 1 : probs = N / sum(N) — exact (x ** 1.0 == float(x), integer sum, one division)
+//   else      : probs = N^(1/temp) / sum(N^(1/temp))  (CUDA pow: within 1e-12 relative of CPython's)
+// The chosen action (what a Coach would draw with np.random.choice(p=probs); not in the reference,
+// build-defined): temp == 0 -> first max; temp == 1 -> the visit-proportional draw
+// k = pick_index(seed, game_id, ply, sum N), first a with cumsum(N) > k (integer, reproducible on
+// the host); else the same inverse-CDF walk over the f64 weights with u = 53 random bits.
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_mcts_policy(MctsView mv, uint32_t n_trees, uint64_t gid_base, const uint32_t* __restrict__ r_visits,
+              const uint32_t* __restrict__ r_counts, double temp, uint64_t seed, int choose, double* __restrict__ r_probs,
+              uint32_t* __restrict__ r_best) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (tree >= n_trees) return;
+    const uint32_t L = r_counts[tree];
+    const size_t ro = (size_t)tree * TAFL_MAX_MOVES;
+    // first maximum of the visit counts (r_best may hold an earlier draw)
+    uint32_t bn = 0, best = 0xFFFFFFFFu;
+    for (uint32_t a = lane; a < L; a += 32) {
+        const uint32_t N = r_visits[ro + a];
+        if (N > bn) { bn = N; best = a; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint32_t on = __shfl_xor_sync(0xFFFFFFFFu, bn, o), oa = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+        if (on > bn || (on == bn && oa < best)) { bn = on; best = oa; }
+    }
+    if (bn == 0) best = 0u;
+    if (temp == 0.0) {
+        if (r_probs) for (uint32_t a = lane; a < TAFL_MAX_MOVES; a += 32) r_probs[ro + a] = (a < L && a == best) ? 1.0 : 0.0;
+        if (choose && lane == 0) r_best[tree] = best;
+        return;
+    }
+    const bool t1 = temp == 1.0;
+    const double inv_t = 1.0 / temp;
+    // per-lane weights of the 16 actions a = 32*i + lane
+    double w[TAFL_MAX_MOVES / 32];
+    double part = 0.0;
+    unsigned long long ipart = 0;
+#pragma unroll
+    for (int i = 0; i < TAFL_MAX_MOVES / 32; ++i) {
+        const uint32_t a = 32u * i + lane;
+        const uint32_t N = a < L ? r_visits[ro + a] : 0u;
+        w[i] = t1 ? (double)N : (N ? pow((double)N, inv_t) : 0.0);
+        part += w[i];
+        ipart += N;
+    }
+    double sum = part;
+    unsigned long long isum = ipart;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+        isum += __shfl_xor_sync(0xFFFFFFFFu, isum, o);
+    }
+    if (t1) sum = (double)isum;
+    if (r_probs) {
+#pragma unroll
+        for (int i = 0; i < TAFL_MAX_MOVES / 32; ++i) r_probs[ro + 32u * i + lane] = sum > 0 ? w[i] / sum : 0.0;
+    }
+    if (!choose || L == 0 || !(sum > 0)) return;
+    const tafl_state root = load_state(mv.n_state + (size_t)tree * mv.node_cap);
+    const uint64_t x = splitmix64(seed ^ ((gid_base + tree) * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)root.turn * 0xBF58476D1CE4E5B9ull));
+    const unsigned long long k = mulhi64(x, isum);                                  // temp == 1
+    const double u = (double)(x >> 11) * 1.1102230246251565e-16 * sum;              // other temperatures
+    // inverse CDF in action order: rows of 32 consecutive actions, inclusive scan across the lanes
+    unsigned long long ibefore = 0;
+    double before = 0.0;
+    uint32_t pick = best;
+    for (int i = 0; i < TAFL_MAX_MOVES / 32; ++i) {
+        if (32u * i >= L) break;
+        const uint32_t a = 32u * i + lane;
+        unsigned long long iinc = a < L ? r_visits[ro + a] : 0u;
+        double inc = w[i];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long it = __shfl_up_sync(0xFFFFFFFFu, iinc, o);
+            const double ft = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= o) { iinc += it; inc += ft; }
+        }
+        const bool hit = t1 ? (ibefore + iinc > k) : (before + inc > u);
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, hit && a < L);
+        if (m) { pick = 32u * i + (uint32_t)(__ffs(m) - 1); break; }
+        ibefore += __shfl_sync(0xFFFFFFFFu, iinc, 31);
+        before += __shfl_sync(0xFFFFFFFFu, inc, 31);
+    }
+    if (lane == 0) r_best[tree] = pick;
 }
 
 // play the chosen root move in every Ongoing game (do_valid_play, logic.rs:782-820)
@@ -575,7 +665,7 @@ void mcts_free(tafl_engine* e) {
     MctsPools* m = e->mcts;
     if (!m) return;
     cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.n_ptab); cudaFree(m->v.edges); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
-    cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best);
+    cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best); cudaFree(m->r_probs);
     cudaFree(m->d_any_overflow);
     cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
     cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
@@ -734,6 +824,28 @@ int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status) {
     MCTS_LAUNCHED(e);
     if (h_status) {
         TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_status, e->d_status, n, cudaMemcpyDeviceToHost, e->stream));
+        TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    }
+    return TAFL_OK;
+}
+
+int tafl_mcts_policy(tafl_engine* e, double temp, int choose, uint64_t seed, double* h_probs) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (!m->searched) { e->err = "tafl_mcts_policy: no search results"; return TAFL_ERR_INVALID_ARG; }
+    if (!(temp >= 0.0)) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    if (h_probs && !m->r_probs) {
+        cudaError_t ce = cudaMalloc((void**)&m->r_probs, (size_t)n * TAFL_MAX_MOVES * sizeof(double));
+        if (ce != cudaSuccess) return set_cuda_error(e, ce, "cudaMalloc(r_probs)");
+    }
+    k_mcts_policy<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, e->game_id_base, m->r_visits, m->r_counts, temp,
+                                                                             seed, choose, h_probs ? m->r_probs : nullptr, m->r_best);
+    MCTS_LAUNCHED(e);
+    if (h_probs) {
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_probs, m->r_probs, (size_t)n * TAFL_MAX_MOVES * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
         TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     }
     return TAFL_OK;

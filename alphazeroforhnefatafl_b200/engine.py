@@ -297,6 +297,13 @@ class LockstepGames:
                                               A.ptr(best)))
         return dict(moves=moves, visits=visits, q=q, counts=counts, best=best)
 
+    def mcts_policy(self, temp=1.0, choose=False, seed=0, want_probs=True):
+        """getActionProb's policy (mcts.py:40-53) on the device; choose=True also draws the move
+        tafl_mcts_play_best will play from it.  Returns probs [n, MAX_MOVES] f64 (or None)."""
+        probs = np.zeros((self.n_games, A.MAX_MOVES), np.float64) if want_probs else None
+        self._ck(lib().tafl_mcts_policy(self._h, float(temp), int(choose), int(seed), A.ptr(probs) if want_probs else None))
+        return probs
+
     def mcts_play_best(self, want_status=True):
         st = np.zeros(self.n_games, np.uint8) if want_status else None
         self._ck(lib().tafl_mcts_play_best(self._h, A.ptr(st) if want_status else None))

@@ -55,19 +55,15 @@ class MCTS:
         first counts[i] entries are its legal moves in canonical order and their probabilities
         (mcts.py:40-53).  Games that are over have counts == 0."""
         self.search()
+        probs = self.games.mcts_policy(temp)   # mcts.py:43-53 on the device (temp 0: first max, no random tie choice)
         r = self.games.mcts_results()
-        visits = r["visits"].astype(np.float64)
-        n = len(visits)
-        probs = np.zeros_like(visits)
-        if temp == 0:   # mcts.py:43-48, first-max instead of np.random.choice among the ties
-            has = r["counts"] > 0
-            probs[np.arange(n)[has], r["best"][has]] = 1.0
-        else:           # mcts.py:50-53
-            c = visits ** (1.0 / temp)
-            s = c.sum(1, keepdims=True)
-            np.divide(c, s, out=probs, where=s > 0)
         self.last = r
         return r["moves"], probs, r["counts"]
+
+    def choose(self, temp=1, seed=0):
+        """Draw the move to play from the temp policy of the last search (the Coach's
+        np.random.choice(p=pi); build-defined counter-based draw, see include/tafl.h)."""
+        self.games.mcts_policy(temp, choose=True, seed=seed, want_probs=False)
 
     def play_best(self):
         """Apply the temp == 0 choice of the last search in every Ongoing game; returns statuses."""

@@ -120,12 +120,16 @@ class SelfPlay:
         with torch.cuda.device(games.device):
             self.rec = torch.zeros((games.n_games, A.REC_STRIDE), dtype=torch.uint8, device="cuda")
 
-    def move(self, gather=True, only_ongoing=True):
-        """One self-play move for every Ongoing game: search, play the first-max move, pack the
-        records, gather them.  Returns the gathered uint8 tensor on ``dst`` (None elsewhere)."""
+    def move(self, gather=True, only_ongoing=True, temp=0, seed=0):
+        """One self-play move for every Ongoing game: search, choose the move from the ``temp``
+        policy (mcts.py:43-53; temp 0 = first max, temp 1 = visit-proportional draw keyed by
+        (seed, game id, ply)), play it, pack the records, gather them.  Returns the gathered
+        uint8 tensor on ``dst`` (None elsewhere)."""
         g = self.g
         with torch.cuda.stream(self.stream):
             g.mcts_search(sync=False)
+            if temp != 0:
+                g.mcts_policy(temp, choose=True, seed=seed, want_probs=False)
             g.mcts_play_best(False)
             g.pack_records(self.rec.data_ptr())
             out = self.rec

@@ -426,6 +426,15 @@ int tafl_mcts_results_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_v
 int tafl_mcts_results_host(tafl_engine* e, uint32_t first, uint32_t n, tafl_move* h_moves,
                            uint32_t* h_visits, double* h_q, uint32_t* h_counts,
                            uint32_t* h_best);
+/* The policy of getActionProb (mcts.py:40-53) from the last search's root visit counts:
+ * temp == 0 one-hot on the first maximum; temp == 1 N/sum(N) (bit-exact with CPython); else
+ * N^(1/temp)/sum (within 1e-12 relative).  h_probs [n_games][TAFL_MAX_MOVES] f64 may be NULL.
+ * choose != 0 also replaces d_best by a move DRAWN from that policy (the Coach's
+ * np.random.choice(p=probs); build-defined, the reference has no Coach): temp == 1 ->
+ * k = mulhi64(splitmix64(seed ^ game_id*0x9E3779B97F4A7C15 ^ ply*0xBF58476D1CE4E5B9), sum N),
+ * first action with cumsum(N) > k; other temp > 0 -> the same walk over the f64 weights.
+ * tafl_mcts_play_best / tafl_pack_records then act on the drawn move. */
+int tafl_mcts_policy(tafl_engine* e, double temp, int choose, uint64_t seed, double* h_probs);
 /* play the chosen move (d_best) in every resident game that is Ongoing: do_valid_play */
 int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status /* may be NULL */);
 /* totals since configure: simulations run, nodes expanded, sum of path depths, sum of edges */

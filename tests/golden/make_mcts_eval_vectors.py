@@ -104,6 +104,33 @@ def main():
                        root_hex=root.tobytes().hex())
             cases.append(out)
             print(name, "L=%d" % out["count"], "sum N=%d" % sum(out["visits"]), "evals=%d masked=%d" % (out["evals"], out["masked_evals"]))
+    # getActionProb itself (mcts.py:28-53), temperatures 1, 0.5, 2 and 0, on fresh MCTS objects
+    policy = []
+    for name, preset, width, pseed, sims, eseed in (("copenhagen", A.PRESET_COPENHAGEN, 128, 27, 120, 107),
+                                                     ("brandubh", A.PRESET_BRANDUBH, 64, 28, 250, 108)):
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        pool = sample_positions(orc, rules, fen, width, 16, seed=pseed, max_steps=120)
+        pool = pool[pool["status"] == 0]
+        for i in range(3):
+            root = pool[i:i + 1].copy()
+            game = TaflGame(orc, rules, width, 1e-4)
+            out = dict(name=name, preset=preset, width=width, sims=sims, cpuct=1.0, draw_value=1e-4, eval_seed=eseed,
+                       root_hex=root.tobytes().hex(), probs={})
+            for temp in (1, 0.5, 2, 0):
+                m = ref_mcts.MCTS(game, HashNet(eseed), types.SimpleNamespace(numMCTSSims=sims, cpuct=1.0))
+                np.random.seed(0)
+                probs = m.getActionProb(Board(root, ()), temp=temp)
+                _, count = game._moves(Board(root, ()))
+                assert all(p == 0 for p in probs[count:])
+                if temp == 0:   # the reference picks randomly among ties; keep the tie set
+                    s = game.stringRepresentation(Board(root, ()))
+                    cnt = [int(m.Nsa.get((s, a), 0)) for a in range(count)]
+                    out["ties_t0"] = [a for a in range(count) if cnt[a] == max(cnt)]
+                    out["visits"] = cnt
+                else:
+                    out["probs"][str(temp)] = [float(x).hex() for x in probs[:count]]
+            policy.append(out)
+            print("policy", name, i)
     # evaluator known answers: P[:8] and v for a few positions (pins the numpy / C++ / CUDA copies)
     kat = []
     rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), board_for(orc, A.PRESET_COPENHAGEN)
@@ -116,7 +143,7 @@ def main():
     with open(path, "w") as f:
         json.dump(dict(provenance="generated by tests/golden/make_mcts_eval_vectors.py: UNMODIFIED reference src/mcts.py "
                                   "(class MCTS) with the TAFL_EVAL_HASH evaluator implemented in numpy; numpy %s" % np.__version__,
-                       cases=cases, evaluator_kat=kat), f, indent=1, sort_keys=True)
+                       cases=cases, evaluator_kat=kat, policy=policy), f, indent=1, sort_keys=True)
         f.write("\n")
     print("wrote", path, len(cases))
 

@@ -195,3 +195,69 @@ def test_gpu_eval_phase_errors(orc, built_lib):
             g.mcts_select_leaves()          # node pool is sized for num_sims rounds
         g.mcts_finish()
         assert g.mcts_results()["visits"].sum() == 4 * 2
+
+
+POLICY = GOLDEN["policy"]
+
+
+def _host_draw(visits, seed, gid, ply):
+    """include/tafl.h tafl_mcts_policy, temp == 1: k = mulhi64(splitmix64(..), sum N), first cumsum > k"""
+    M = (1 << 64) - 1
+
+    def sm(x):
+        x = (x + 0x9E3779B97F4A7C15) & M
+        x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & M
+        x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & M
+        return x ^ (x >> 31)
+    x = sm(seed ^ ((gid * 0x9E3779B97F4A7C15) & M) ^ ((ply * 0xBF58476D1CE4E5B9) & M))
+    k = (x * int(visits.sum())) >> 64
+    return int(np.searchsorted(np.cumsum(visits.astype(np.int64)), k, side="right"))
+
+
+@pytest.mark.gpu
+def test_gpu_policy_matches_reference_get_action_prob(orc, built_lib):
+    """MCTS.getActionProb (mcts.py:28-53) of the unmodified reference: temp 1 bit-exact, temp 0.5 / 2
+    within 1e-12, temp 0 one-hot inside the reference's tie set; the drawn move follows the ABI's rule"""
+    from types import SimpleNamespace
+    from alphazeroforhnefatafl_b200 import engine as E
+    from alphazeroforhnefatafl_b200.mcts import MCTS
+    from parity_cases import board_for
+    for name in sorted({c["name"] for c in POLICY}):
+        cases = [c for c in POLICY if c["name"] == name]
+        c0 = cases[0]
+        rules, fen = orc.preset_rules(c0["preset"]), board_for(orc, c0["preset"])
+        roots = np.concatenate([root_of(c) for c in cases])
+        with E.LockstepGames(rules, fen, len(cases), 0, c0["width"]) as g:
+            g.set_states(roots)
+            g.set_game_id_base(1000)
+            m = MCTS(g, SimpleNamespace(numMCTSSims=c0["sims"], cpuct=c0["cpuct"]), nnet=("hash", c0["eval_seed"]))
+            for temp in (1, 0.5, 2, 0):
+                moves, probs, counts = m.getActionProb(temp=temp)
+                for i, c in enumerate(cases):
+                    L = len(c["visits"])
+                    assert int(counts[i]) == L and not probs[i, L:].any()
+                    assert np.array_equal(m.last["visits"][i, :L], np.array(c["visits"], np.uint32))
+                    if temp == 0:
+                        assert probs[i, :L].sum() == 1.0 and int(np.argmax(probs[i, :L])) == c["ties_t0"][0]
+                        continue
+                    ref = np.array([float.fromhex(x) for x in c["probs"][str(temp)]])
+                    if temp == 1:
+                        assert probs[i, :L].tobytes() == ref.tobytes()
+                    else:
+                        assert np.allclose(probs[i, :L], ref, rtol=1e-12, atol=0.0)
+            # the draw: temp == 1 is an integer walk, reproducible on the host
+            for seed in (1, 2, 3, 99):
+                m.choose(temp=1, seed=seed)
+                best = g.mcts_results()["best"]
+                for i, c in enumerate(cases):
+                    ply = int(roots["turn"][i])
+                    assert int(best[i]) == _host_draw(np.array(c["visits"]), seed, 1000 + i, ply)
+            m.choose(temp=0)   # back to the first maximum
+            assert [int(b) for b in g.mcts_results()["best"]] == [int(np.argmax(c["visits"])) for c in cases]
+            # a drawn move is played and recorded
+            m.choose(temp=0.5, seed=5)
+            best = g.mcts_results()["best"]
+            for i, c in enumerate(cases):
+                assert c["visits"][int(best[i])] > 0
+            st = m.play_best()
+            assert len(st) == len(cases)
