@@ -119,9 +119,10 @@ struct Mcts {
         stats.nodes += 1;
         return (int)nodes.size() - 1;
     }
-    void reset(const GameState<W>& root) {
+    void reset(const GameState<W>& root_state) {
         nodes.clear();
-        new_node(root);
+        root = 0;
+        new_node(root_state);
     }
 
     // mcts.py:55-136
@@ -208,6 +209,23 @@ struct Mcts {
             search(0, 0);
             stats.sims += 1;
         }
+    }
+
+    // Tree reuse: the reference keeps ONE MCTS object per episode, so the statistics of the
+    // subtree below the move played survive into the next getActionProb (its dicts are never
+    // cleared, mcts.py:20-26).  `root` walks down the retained tree.
+    int root = 0;
+    void run_from_root(uint32_t num_sims) {
+        for (uint32_t i = 0; i < num_sims; ++i) {
+            search(root, 0);
+            stats.sims += 1;
+        }
+    }
+    // play action a at the root; false if (root, a) was never traversed (no child to descend to)
+    bool advance(int a) {
+        if (a < 0 || (size_t)a >= nodes[root].child.size() || nodes[root].child[a] < 0) return false;
+        root = nodes[root].child[a];
+        return true;
     }
 };
 

@@ -471,6 +471,75 @@ int orc_hash_eval(const tafl_state* st, uint32_t n, uint64_t seed, float* P, flo
 }
 double orc_np_sum(const double* a, uint64_t n) { return np_sum(a, (size_t)n); }
 
+// An episode prefix with ONE MCTS object per game (tree reuse, see Mcts::advance) or a fresh tree
+// per move: n_moves x (num_sims simulations from the current root, play the first-max move).
+// Outputs per (game, move): [n][n_moves][TAFL_MAX_MOVES] visits / q, [n][n_moves] counts / best;
+// final states [n].  use_eval != 0 -> TAFL_EVAL_HASH evaluator.
+int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                     uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
+                     int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best, tafl_state* final_states,
+                     tafl_mcts_stats* stats) {
+    return dispatch(width, [&](auto w) {
+        using W = decltype(w);
+        if (n_threads < 1) n_threads = 1;
+        std::vector<tafl_mcts_stats> part((size_t)n_threads);
+        std::vector<std::thread> th;
+        for (int t = 0; t < n_threads; ++t) {
+            uint32_t g0 = (uint32_t)((uint64_t)n * t / n_threads), g1 = (uint32_t)((uint64_t)n * (t + 1) / n_threads);
+            part[t] = tafl_mcts_stats{};
+            th.emplace_back([&, t, g0, g1] {
+                for (uint32_t g = g0; g < g1; ++g) {
+                    GameState<W> s;
+                    unpack_state(roots[g], &s);
+                    GameLogic logic(*r, s.board.side_len);
+                    Mcts<W> m(logic, cpuct, draw_value);
+                    if (use_eval)
+                        m.eval = [eval_seed](const GameState<W>& gs, float* P, float* v) {
+                            tafl_state ps;
+                            pack_state(gs, &ps);
+                            hash_eval(eval_seed, ps, P, v);
+                        };
+                    m.reset(s);
+                    for (uint32_t mv = 0; mv < n_moves; ++mv) {
+                        const size_t row = (size_t)g * n_moves + mv;
+                        counts[row] = 0;
+                        best[row] = 0;
+                        if (s.status != TAFL_STATUS_ONGOING) continue;
+                        m.run_from_root(num_sims);
+                        auto& rt = m.nodes[m.root];
+                        const size_t L = rt.moves.size();
+                        counts[row] = (uint32_t)L;
+                        uint32_t b = 0, bestn = 0;
+                        for (size_t a = 0; a < L && a < TAFL_MAX_MOVES; ++a) {
+                            visits[row * TAFL_MAX_MOVES + a] = rt.N[a];
+                            q[row * TAFL_MAX_MOVES + a] = rt.Q[a];
+                            if (rt.N[a] > bestn) { bestn = rt.N[a]; b = (uint32_t)a; }
+                        }
+                        best[row] = b;
+                        if (L == 0) continue;
+                        auto res = logic.do_valid_play(rt.moves[b], rt.state);
+                        s = res.first;
+                        if (!reuse || !m.advance((int)b)) m.reset(s);
+                    }
+                    pack_state(s, &final_states[g]);
+                    auto& ps = part[t];
+                    ps.sims += m.stats.sims; ps.nodes += m.stats.nodes; ps.depth_sum += m.stats.depth_sum;
+                    ps.edges += m.stats.edges; ps.terminal_hits += m.stats.terminal_hits;
+                }
+            });
+        }
+        for (auto& x : th) x.join();
+        if (stats) {
+            *stats = tafl_mcts_stats{};
+            for (auto& p : part) {
+                stats->sims += p.sims; stats->nodes += p.nodes; stats->depth_sum += p.depth_sum;
+                stats->edges += p.edges; stats->terminal_hits += p.terminal_hits;
+            }
+        }
+        return 0;
+    });
+}
+
 int orc_hw_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

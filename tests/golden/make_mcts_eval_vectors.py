@@ -131,6 +131,37 @@ def main():
                     out["probs"][str(temp)] = [float(x).hex() for x in probs[:count]]
             policy.append(out)
             print("policy", name, i)
+    # tree reuse: ONE reference MCTS object per episode (its dicts persist, mcts.py:20-26), first-max move played
+    episodes = []
+    for name, preset, width, pseed, sims, n_moves, eseed in (("copenhagen", A.PRESET_COPENHAGEN, 128, 29, 100, 6, 109),
+                                                              ("brandubh", A.PRESET_BRANDUBH, 64, 30, 200, 10, 110),
+                                                              ("brandubh_stub", A.PRESET_BRANDUBH, 64, 32, 200, 10, None),
+                                                              ("tablut_stub", A.PRESET_TABLUT, 128, 33, 150, 6, None)):
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        pool = sample_positions(orc, rules, fen, width, 16, seed=pseed, max_steps=100)
+        pool = pool[pool["status"] == 0]
+        for i in range(2):
+            root = pool[i:i + 1].copy()
+            game = TaflGame(orc, rules, width, 1e-4)
+            net = HashNet(eseed) if eseed is not None else base.StubNet()
+            m = ref_mcts.MCTS(game, net, types.SimpleNamespace(numMCTSSims=sims, cpuct=1.0))
+            b = Board(root, ())
+            moves = []
+            for _ in range(n_moves):
+                if game.getGameEnded(b, 1) != 0:
+                    break
+                for _ in range(sims):
+                    m.search(b)
+                s = game.stringRepresentation(b)
+                _, count = game._moves(b)
+                visits = [int(m.Nsa.get((s, a), 0)) for a in range(count)]
+                q = [float(m.Qsa.get((s, a), 0.0)).hex() for a in range(count)]
+                a = int(np.argmax(visits))
+                moves.append(dict(visits=visits, q_hex=q, best=a))
+                b, _ = game.getNextState(b, 1, a)
+            episodes.append(dict(name=name, preset=preset, width=width, sims=sims, cpuct=1.0, draw_value=1e-4, eval_seed=eseed,
+                                 root_hex=root.tobytes().hex(), n_moves=n_moves, moves=moves, final_hex=b.state.tobytes().hex()))
+            print("episode", name, i, [sum(mv["visits"]) for mv in moves])
     # evaluator known answers: P[:8] and v for a few positions (pins the numpy / C++ / CUDA copies)
     kat = []
     rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), board_for(orc, A.PRESET_COPENHAGEN)
@@ -143,7 +174,7 @@ def main():
     with open(path, "w") as f:
         json.dump(dict(provenance="generated by tests/golden/make_mcts_eval_vectors.py: UNMODIFIED reference src/mcts.py "
                                   "(class MCTS) with the TAFL_EVAL_HASH evaluator implemented in numpy; numpy %s" % np.__version__,
-                       cases=cases, evaluator_kat=kat, policy=policy), f, indent=1, sort_keys=True)
+                       cases=cases, evaluator_kat=kat, policy=policy, episodes=episodes), f, indent=1, sort_keys=True)
         f.write("\n")
     print("wrote", path, len(cases))
 

@@ -74,6 +74,33 @@ def test_eval_oracle_matches_reference_mcts_py(orc, case):
     assert got["stats"].nodes == case["n_nodes"]
 
 
+EPISODES = GOLDEN["episodes"]
+
+
+def _check_episode(ep, visits, q, counts, best, final, i=0):
+    for j, mv in enumerate(ep["moves"]):
+        L = len(mv["visits"])
+        assert int(counts[i, j]) == L, (ep["name"], j)
+        assert np.array_equal(visits[i, j, :L], np.array(mv["visits"], np.uint32)), (ep["name"], j)
+        ref_q = np.array([float.fromhex(x) for x in mv["q_hex"]])
+        assert q[i, j, :L].tobytes() == ref_q.tobytes(), (ep["name"], j)
+        assert int(best[i, j]) == mv["best"]
+    for j in range(len(ep["moves"]), ep["n_moves"]):
+        assert int(counts[i, j]) == 0          # the game ended before move j
+    assert final[i:i + 1].tobytes().hex() == ep["final_hex"]
+
+
+@pytest.mark.parametrize("ep", EPISODES, ids=["%s-%d" % (e["name"], i) for i, e in enumerate(EPISODES)])
+def test_oracle_tree_reuse_matches_reference_mcts_object_kept_across_moves(orc, ep):
+    """one reference MCTS object per episode (mcts.py:20-26 dicts persist) == Mcts::advance"""
+    rules = orc.preset_rules(ep["preset"])
+    root = np.frombuffer(bytes.fromhex(ep["root_hex"]), A.STATE_DTYPE).copy()
+    got = orc.mcts_episode(rules, ep["width"], root, ep["sims"], ep["n_moves"], True, cpuct=ep["cpuct"],
+                           draw_value=ep["draw_value"], eval_seed=ep["eval_seed"])
+    assert any(sum(mv["visits"]) > ep["sims"] for mv in ep["moves"][1:])   # reuse really carries visits over
+    _check_episode(ep, got["visits"], got["q"], got["counts"], got["best"], got["final"])
+
+
 def _groups():
     groups = {}
     for case in CASES:
