@@ -22,6 +22,7 @@ struct MctsPools {
     uint32_t* r_counts = nullptr;
     uint32_t* r_best = nullptr;
     double* r_probs = nullptr;        // [n_games][TAFL_MAX_MOVES], allocated by the first tafl_mcts_policy
+    uint32_t* remap = nullptr;        // [n_games][node_cap] scratch of k_mcts_reroot (tree reuse only)
     uint32_t* d_any_overflow = nullptr;
     bool searched = false;
     // evaluator hook (tafl_mcts_begin / select_leaves / expand_backup): the leaf batch of one round
@@ -196,6 +197,7 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
                 tafl_state s = load_state(n_state + node);
                 const tafl_move m = warp_decode_edge(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
                                                      (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)a, lane);
+                if (n_nodes >= mv.node_cap) { overflow = true; break; }   // only reachable with tree reuse
                 do_valid_move(cx, s, m);
                 child = n_nodes++;
                 c_nodes += 1;
@@ -371,6 +373,134 @@ k_mcts_policy(MctsView mv, uint32_t n_trees, uint64_t gid_base, const uint32_t* 
     if (lane == 0) r_best[tree] = pick;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tree reuse (TAFL_MCTS_TREE_REUSE): the reference keeps one MCTS object per episode, so the
+// subtree below the move played carries its Ns / Nsa / Qsa / Ps into the next getActionProb
+// (mcts.py:20-26 — the dicts are never cleared).  k_mcts_reroot makes the child reached by the
+// chosen root edge the new node 0 and compacts its subtree IN PLACE: nodes are created in
+// increasing index order with parent < child, and edge blocks are handed out in the same
+// order, so every kept node / edge block moves to a lower-or-equal address and an ascending
+// sweep never overwrites something it still has to read.  One warp per tree.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_mcts_reroot(MctsView mv, uint32_t n_trees, const uint32_t* __restrict__ r_counts, const uint32_t* __restrict__ r_best,
+              uint32_t* __restrict__ remap_all) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (tree >= n_trees) return;
+    tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    double* const prior = mv.e_prior ? mv.e_prior + (size_t)tree * mv.edge_cap : nullptr;
+    uint32_t* const remap = remap_all + (size_t)tree * mv.node_cap;
+    const uint32_t n_nodes = mv.t_nodes[tree];
+    const uint4 h0 = n_hdr[0];
+    uint32_t new_root = MCTS_NO_PARENT;
+    if (n_nodes > 0 && mv.t_overflow[tree] == 0 && hdr_es(h0.w) != ES_ONGOING) return;   // finished game: no move was played
+    if (n_nodes > 0 && mv.t_overflow[tree] == 0 && hdr_expanded(h0.w) && r_counts[tree] > 0) {
+        const MctsEdge e = edges[h0.x + r_best[tree]];
+        if (e.N > 0) new_root = e.child;
+    }
+    if (new_root == MCTS_NO_PARENT) {   // nothing to keep: the next search starts a fresh tree
+        if (lane == 0) { mv.t_nodes[tree] = 0; mv.t_edges[tree] = 0; }
+        return;
+    }
+    // pass 1: remap[i] = new index of node i, or NONE if it is outside the kept subtree
+    uint32_t kept = 0;
+    for (uint32_t base = 0; base < n_nodes; base += 32) {
+        const uint32_t i = base + lane;
+        const bool valid = i < n_nodes;
+        const uint32_t parent = valid ? n_hdr[i].z : MCTS_NO_PARENT;
+        bool keep = valid && i == new_root;
+        const bool has_parent = valid && i > new_root && parent != MCTS_NO_PARENT;
+        const bool in_chunk = has_parent && parent >= base;
+        if (has_parent && !in_chunk) keep = parent >= new_root && remap[parent] != MCTS_NO_PARENT;
+        while (true) {   // parents inside this chunk: propagate until stable
+            const bool pk = __shfl_sync(0xFFFFFFFFu, (int)keep, in_chunk ? (int)(parent - base) : 0) != 0;
+            const bool nk = keep || (in_chunk && pk);
+            const unsigned changed = __ballot_sync(0xFFFFFFFFu, nk != keep);
+            keep = nk;
+            if (!changed) break;
+        }
+        const unsigned km = __ballot_sync(0xFFFFFFFFu, keep);
+        if (valid) remap[i] = keep ? kept + (uint32_t)__popc(km & ((1u << lane) - 1u)) : MCTS_NO_PARENT;
+        kept += (uint32_t)__popc(km);
+        __syncwarp();
+    }
+    // pass 2: move the kept nodes and their edge blocks down, ascending
+    uint32_t e_used = 0;
+    for (uint32_t i = new_root; i < n_nodes; ++i) {
+        const uint32_t j = remap[i];
+        if (j == MCTS_NO_PARENT) continue;
+        uint4 h = n_hdr[i];
+        const bool expanded = hdr_expanded(h.w) != 0;
+        const uint32_t L = expanded ? hdr_n_edges(h.w) : 0u, old_base = h.x;
+        if (j != i) {
+            const uint32_t w0 = n_ptab[(size_t)i * MCTS_PT_MAX + lane], w1 = n_ptab[(size_t)i * MCTS_PT_MAX + 32 + lane];
+            tafl_state s;
+            if (lane == 0) s = load_state(n_state + i);
+            __syncwarp();
+            n_ptab[(size_t)j * MCTS_PT_MAX + lane] = w0;
+            n_ptab[(size_t)j * MCTS_PT_MAX + 32 + lane] = w1;
+            if (lane == 0) store_state(n_state + j, s);
+        }
+        for (uint32_t off = 0; off < L; off += 32) {
+            const uint32_t a = off + lane;
+            MctsEdge e;
+            double p = 0.0;
+            if (a < L) {
+                e = edges[old_base + a];
+                if (prior) p = prior[old_base + a];
+                e.child = e.N > 0 ? remap[e.child] : 0u;
+            }
+            __syncwarp();
+            if (a < L) {
+                edges[e_used + a] = e;
+                if (prior) prior[e_used + a] = p;
+            }
+            __syncwarp();
+        }
+        if (lane == 0) {
+            h.x = expanded ? e_used : 0u;
+            h.z = i == new_root ? MCTS_NO_PARENT : remap[h.z];
+            n_hdr[j] = h;
+        }
+        e_used += L;
+        __syncwarp();
+    }
+    if (lane == 0) { mv.t_nodes[tree] = kept; mv.t_edges[tree] = e_used; }
+}
+
+// start of a search with tree reuse: keep a carried tree whose root IS the game's current state,
+// start a fresh one otherwise (first move, game reset / states replaced by the caller, no child)
+__global__ void k_mcts_init_carry(const tafl_state* __restrict__ states, uint32_t n, MctsView mv) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const tafl_state s = load_state(states + g);
+    if (mv.t_nodes[g] > 0 && mv.t_overflow[g] == 0) {
+        const uint4* const p = reinterpret_cast<const uint4*>(states + g);
+        const uint4* const q = reinterpret_cast<const uint4*>(mv.n_state + (size_t)g * mv.node_cap);
+        bool same = true;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint4 x = p[k], y = q[k];
+            same = same && x.x == y.x && x.y == y.y && x.z == y.z && x.w == y.w;
+        }
+        if (same) {
+            if (mv.t_pending) mv.t_pending[g] = MCTS_NO_PARENT;
+            return;
+        }
+    }
+    store_state(mv.n_state + (size_t)g * mv.node_cap, s);
+    mv.n_hdr[(size_t)g * mv.node_cap] = make_uint4(0u, 0u, MCTS_NO_PARENT, hdr_pack(0, 0, 0, es_code(s)));
+    mv.t_nodes[g] = 1;
+    mv.t_edges[g] = 0;
+    mv.t_overflow[g] = 0;
+    if (mv.t_pending) mv.t_pending[g] = MCTS_NO_PARENT;
+    atomicAdd(&mv.stats[ST_NODES], 1ull);
+}
+
 // play the chosen root move in every Ongoing game (do_valid_play, logic.rs:782-820)
 template <class BB, int SP>
 __global__ void __launch_bounds__(64)
@@ -458,7 +588,7 @@ k_mcts_select_leaf(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t
     MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
     const double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
     uint32_t want = 0, pending = MCTS_NO_PARENT;
-    if (mv.t_overflow[tree] == 0 && mv.t_nodes[tree] < mv.node_cap) {
+    if (mv.t_overflow[tree] == 0) {
         uint32_t node = 0, depth = 0;
         while (true) {
             const uint4 h = n_hdr[node];
@@ -535,6 +665,10 @@ k_mcts_select_leaf(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t
                 do_valid_move(cx, s, m);
                 child = mv.t_nodes[tree];
                 __syncwarp();
+                if (child >= mv.node_cap) {
+                    if (lane == 0) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+                    break;
+                }
                 if (lane == 0) {
                     mv.t_nodes[tree] = child + 1u;
                     store_state(n_state + child, s);
@@ -665,7 +799,7 @@ void mcts_free(tafl_engine* e) {
     MctsPools* m = e->mcts;
     if (!m) return;
     cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.n_ptab); cudaFree(m->v.edges); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
-    cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best); cudaFree(m->r_probs);
+    cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best); cudaFree(m->r_probs); cudaFree(m->remap);
     cudaFree(m->d_any_overflow);
     cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
     cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
@@ -686,6 +820,15 @@ void mcts_free(tafl_engine* e) {
         TAFL_CUDA_TRY((e), cudaGetLastError());  \
     } while (0)
 
+// fresh trees, or (tree reuse) carried trees whose root still is the game's state
+static void launch_tree_init(tafl_engine* e) {
+    MctsPools* m = e->mcts;
+    if (m->cfg.flags & TAFL_MCTS_TREE_REUSE)
+        k_mcts_init_carry<<<grid_for(e->n_games, 128), 128, 0, e->stream>>>(e->d_states, e->n_games, m->v);
+    else
+        k_mcts_init<<<grid_for(e->n_games, 128), 128, 0, e->stream>>>(e->d_states, e->n_games, m->v);
+}
+
 static int need_mcts(tafl_engine* e) {
     if (!e) return TAFL_ERR_INVALID_ARG;
     if (!e->mcts) { e->err = "tafl_mcts_configure has not been called"; return TAFL_ERR_INVALID_ARG; }
@@ -698,8 +841,12 @@ int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg) {
     if (!e || !cfg || cfg->num_sims == 0 || !(cfg->draw_value != 0.0)) return TAFL_ERR_INVALID_ARG;
     cudaSetDevice(e->device);
     tafl_mcts_config c = *cfg;
-    if (c.edge_capacity == 0) c.edge_capacity = (c.num_sims + 1) * 160u;
-    if (e->mcts && e->mcts->cfg.num_sims == c.num_sims && e->mcts->cfg.edge_capacity == c.edge_capacity) {
+    const bool reuse = (c.flags & TAFL_MCTS_TREE_REUSE) != 0;
+    if (c.node_capacity == 0) c.node_capacity = (c.num_sims + 1) * (reuse ? 4u : 1u);
+    if (c.node_capacity < c.num_sims + 1) return TAFL_ERR_INVALID_ARG;
+    if (c.edge_capacity == 0) c.edge_capacity = c.node_capacity * 160u;
+    if (e->mcts && e->mcts->cfg.num_sims == c.num_sims && e->mcts->cfg.edge_capacity == c.edge_capacity &&
+        e->mcts->cfg.node_capacity == c.node_capacity && e->mcts->cfg.flags == c.flags) {
         e->mcts->cfg = c;   // same pools, possibly new cpuct / draw value
         return TAFL_OK;
     }
@@ -708,7 +855,7 @@ int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg) {
     MctsPools* m = new MctsPools();
     m->cfg = c;
     e->mcts = m;
-    const size_t n = e->n_games, nc = (size_t)c.num_sims + 1, ec = c.edge_capacity;
+    const size_t n = e->n_games, nc = (size_t)c.node_capacity, ec = c.edge_capacity;
     m->v.node_cap = (uint32_t)nc;
     m->v.edge_cap = (uint32_t)ec;
 #define MCTS_ALLOC(ptr, bytes)                                          \
@@ -734,7 +881,9 @@ int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg) {
     MCTS_ALLOC(m->r_counts, n * sizeof(uint32_t));
     MCTS_ALLOC(m->r_best, n * sizeof(uint32_t));
     MCTS_ALLOC(m->d_any_overflow, sizeof(uint32_t));
+    if (reuse) MCTS_ALLOC(m->remap, n * nc * sizeof(uint32_t));
 #undef MCTS_ALLOC
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->v.t_nodes, 0, n * sizeof(uint32_t), e->stream));   // no tree is carried yet
     TAFL_CUDA_TRY(e, cudaMemsetAsync(m->v.stats, 0, ST_COUNT * sizeof(unsigned long long), e->stream));
     TAFL_CUDA_TRY(e, cudaMemsetAsync(m->d_any_overflow, 0, sizeof(uint32_t), e->stream));
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -747,7 +896,7 @@ int tafl_mcts_search_async(tafl_engine* e) {
     cudaSetDevice(e->device);
     MctsPools* m = e->mcts;
     const uint32_t n = e->n_games;
-    k_mcts_init<<<grid_for(n, 128), 128, 0, e->stream>>>(e->d_states, n, m->v);
+    launch_tree_init(e);
     MCTS_LAUNCHED(e);
     const unsigned grid = grid_for(n, MCTS_WARPS);
 #define TAFL_MCTS_LAUNCH(MINB)                                                                                          \
@@ -822,6 +971,24 @@ int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status) {
     TAFL_SPEC_DISPATCH(e, (k_mcts_play_best<BB, SP><<<grid_for(n, 64), 64, 0, e->stream>>>(cx, e->d_states, n, m->r_moves, m->r_counts,
                                                                                        m->r_best, e->d_status)));
     MCTS_LAUNCHED(e);
+    if (h_status) {
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_status, e->d_status, n, cudaMemcpyDeviceToHost, e->stream));
+        TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    }
+    return TAFL_OK;
+}
+
+int tafl_mcts_advance(tafl_engine* e, uint8_t* h_status) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (!(m->cfg.flags & TAFL_MCTS_TREE_REUSE)) { e->err = "tafl_mcts_advance: configure with TAFL_MCTS_TREE_REUSE"; return TAFL_ERR_INVALID_ARG; }
+    rc = tafl_mcts_play_best(e, nullptr);
+    if (rc) return rc;
+    const uint32_t n = e->n_games;
+    k_mcts_reroot<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->r_counts, m->r_best, m->remap);
+    MCTS_LAUNCHED(e);
+    m->searched = false;   // the root results describe the previous root
     if (h_status) {
         TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_status, e->d_status, n, cudaMemcpyDeviceToHost, e->stream));
         TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -921,7 +1088,7 @@ int tafl_mcts_begin(tafl_engine* e) {
     rc = eval_alloc(e);
     if (rc) return rc;
     MctsPools* m = e->mcts;
-    k_mcts_init<<<grid_for(e->n_games, 128), 128, 0, e->stream>>>(e->d_states, e->n_games, m->v);
+    launch_tree_init(e);
     MCTS_LAUNCHED(e);
     m->phase = 1;
     m->rounds = 0;

@@ -279,8 +279,9 @@ class LockstepGames:
         return s
 
     # -- MCTS (src/mcts.py) -----------------------------------------------------------------------
-    def mcts_configure(self, num_sims, cpuct=1.0, draw_value=1e-4, edge_capacity=0):
-        cfg = A.MctsConfig(num_sims=num_sims, cpuct=cpuct, draw_value=draw_value, edge_capacity=edge_capacity)
+    def mcts_configure(self, num_sims, cpuct=1.0, draw_value=1e-4, edge_capacity=0, tree_reuse=False, node_capacity=0):
+        cfg = A.MctsConfig(num_sims=num_sims, cpuct=cpuct, draw_value=draw_value, edge_capacity=edge_capacity,
+                           flags=A.MCTS_TREE_REUSE if tree_reuse else 0, node_capacity=node_capacity)
         self._ck(lib().tafl_mcts_configure(self._h, C.byref(cfg)))
 
     def mcts_search(self, sync=True):
@@ -307,6 +308,12 @@ class LockstepGames:
     def mcts_play_best(self, want_status=True):
         st = np.zeros(self.n_games, np.uint8) if want_status else None
         self._ck(lib().tafl_mcts_play_best(self._h, A.ptr(st) if want_status else None))
+        return st
+
+    def mcts_advance(self, want_status=True):
+        """play the chosen move and re-root every tree at it (tree reuse, mcts.py:20-26)"""
+        st = np.zeros(self.n_games, np.uint8) if want_status else None
+        self._ck(lib().tafl_mcts_advance(self._h, A.ptr(st) if want_status else None))
         return st
 
     def mcts_stats(self):

@@ -404,11 +404,15 @@ int tafl_side_can_play(tafl_engine* e, const tafl_state* h_states, const uint8_t
  * MCTS: `class MCTS` (src/mcts.py:11-136) with the stub evaluator (uniform priors over the
  * legal moves, value 0), one search tree per resident game, f64 PUCT, first-max tie-break.
  * ---------------------------------------------------------------------------------------- */
+#define TAFL_MCTS_TREE_REUSE 1u   /* keep the subtree below the move played (tafl_mcts_advance) */
 typedef struct {
     uint32_t num_sims;          /* args.numMCTSSims (mcts.py:37)                          */
     double   cpuct;             /* args.cpuct (mcts.py:112)                               */
     double   draw_value;        /* getGameEnded value of a draw (non-zero; 1e-4 default)  */
-    uint32_t edge_capacity;     /* per-tree edge pool, 0 = default (num_sims+1)*160       */
+    uint32_t edge_capacity;     /* per-tree edge pool, 0 = default node_capacity*160      */
+    uint32_t flags;             /* TAFL_MCTS_*                                            */
+    uint32_t node_capacity;     /* per-tree node pool, 0 = default num_sims+1 (x4 with
+                                   tree reuse; a tree that outgrows it -> TAFL_ERR_CAPACITY) */
     uint32_t _pad;
 } tafl_mcts_config;
 
@@ -437,6 +441,14 @@ int tafl_mcts_results_host(tafl_engine* e, uint32_t first, uint32_t n, tafl_move
 int tafl_mcts_policy(tafl_engine* e, double temp, int choose, uint64_t seed, double* h_probs);
 /* play the chosen move (d_best) in every resident game that is Ongoing: do_valid_play */
 int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status /* may be NULL */);
+/* Tree reuse (cfg.flags & TAFL_MCTS_TREE_REUSE): the reference keeps ONE MCTS object per
+ * episode, so the statistics below the move played survive into the next getActionProb
+ * (mcts.py:20-26, the dicts are never cleared).  tafl_mcts_advance = tafl_mcts_play_best +
+ * re-rooting every tree at the child reached by the move (subtree compacted in place); the
+ * next tafl_mcts_search / tafl_mcts_begin then continues from the carried tree when its root
+ * still equals the game's state, and starts a fresh tree otherwise.  Call tafl_pack_records
+ * BEFORE advancing (the records describe the searched root). */
+int tafl_mcts_advance(tafl_engine* e, uint8_t* h_status /* may be NULL */);
 /* totals since configure: simulations run, nodes expanded, sum of path depths, sum of edges */
 typedef struct {
     uint64_t sims, nodes, depth_sum, edges, terminal_hits, max_edges_used;

@@ -504,7 +504,10 @@ int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, ui
                         const size_t row = (size_t)g * n_moves + mv;
                         counts[row] = 0;
                         best[row] = 0;
-                        if (s.status != TAFL_STATUS_ONGOING) continue;
+                        if (s.status != TAFL_STATUS_ONGOING) {   // getActionProb on a finished game: every search returns -Es
+                            m.run_from_root(num_sims);
+                            continue;
+                        }
                         m.run_from_root(num_sims);
                         auto& rt = m.nodes[m.root];
                         const size_t L = rt.moves.size();

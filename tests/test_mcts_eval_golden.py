@@ -288,3 +288,86 @@ def test_gpu_policy_matches_reference_get_action_prob(orc, built_lib):
                 assert c["visits"][int(best[i])] > 0
             st = m.play_best()
             assert len(st) == len(cases)
+
+
+def _run_episode_gpu(g, sims, n_moves, eval_seed, reuse=True):
+    n = g.n_games
+    visits = np.zeros((n, n_moves, A.MAX_MOVES), np.uint32)
+    q = np.zeros((n, n_moves, A.MAX_MOVES), np.float64)
+    counts = np.zeros((n, n_moves), np.uint32)
+    best = np.zeros((n, n_moves), np.uint32)
+    for j in range(n_moves):
+        if eval_seed is None:
+            g.mcts_search()
+        else:
+            g.mcts_search_builtin(A.EVAL_HASH, eval_seed)
+        r = g.mcts_results()
+        visits[:, j], q[:, j], counts[:, j], best[:, j] = r["visits"], r["q"], r["counts"], r["best"]
+        if reuse:
+            g.mcts_advance()
+        else:
+            g.mcts_play_best()
+    return visits, q, counts, best, g.get_states()
+
+
+@pytest.mark.gpu
+def test_gpu_tree_reuse_matches_reference_mcts_object_kept_across_moves(orc, built_lib):
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for
+    for name in sorted({e["name"] for e in EPISODES}):
+        eps = [e for e in EPISODES if e["name"] == name]
+        e0 = eps[0]
+        rules, fen = orc.preset_rules(e0["preset"]), board_for(orc, e0["preset"])
+        roots = np.concatenate([np.frombuffer(bytes.fromhex(e["root_hex"]), A.STATE_DTYPE) for e in eps])
+        with E.LockstepGames(rules, fen, len(eps), 0, e0["width"]) as g:
+            g.set_states(roots)
+            g.mcts_configure(e0["sims"], e0["cpuct"], e0["draw_value"], tree_reuse=True)
+            visits, q, counts, best, final = _run_episode_gpu(g, e0["sims"], e0["n_moves"], e0["eval_seed"])
+        for i, ep in enumerate(eps):
+            _check_episode(ep, visits, q, counts, best, final, i)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("preset,width,sims,n_moves,eval_seed", [
+    (A.PRESET_COPENHAGEN, 128, 160, 6, None), (A.PRESET_COPENHAGEN, 128, 120, 5, 77),
+    (A.PRESET_BRANDUBH, 64, 300, 12, None), (A.PRESET_TABLUT, 128, 200, 8, 78)])
+def test_gpu_tree_reuse_matches_oracle_at_scale(orc, built_lib, preset, width, sims, n_moves, eval_seed):
+    """many games, mid-game roots, games ending inside the episode: visits / Q / final states bit-exact"""
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for, sample_positions
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    roots = sample_positions(orc, rules, fen, width, 192, seed=51, max_steps=250)
+    exp = orc.mcts_episode(rules, width, roots, sims, n_moves, True, eval_seed=eval_seed, n_threads=8)
+    with E.LockstepGames(rules, fen, len(roots), 0, width) as g:
+        g.set_states(roots)
+        g.mcts_configure(sims, 1.0, 1e-4, tree_reuse=True)
+        visits, q, counts, best, final = _run_episode_gpu(g, sims, n_moves, eval_seed)
+        st = g.mcts_stats().as_dict()
+    assert np.array_equal(counts, exp["counts"])
+    assert np.array_equal(visits, exp["visits"])
+    assert q.tobytes() == exp["q"].tobytes()
+    assert np.array_equal(best, exp["best"])
+    assert final.tobytes() == exp["final"].tobytes()
+    assert (visits.sum(2)[:, 1:] > sims).any()       # statistics were carried over
+    for k in ("nodes", "edges", "terminal_hits", "depth_sum"):
+        assert st[k] == getattr(exp["stats"], k), k
+
+
+@pytest.mark.gpu
+def test_gpu_tree_reuse_dropped_when_states_are_replaced(orc, built_lib):
+    """a carried tree is only used while its root equals the game's state"""
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for, sample_positions
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), board_for(orc, A.PRESET_BRANDUBH)
+    roots = sample_positions(orc, rules, fen, 64, 32, seed=52, max_steps=60)
+    other = sample_positions(orc, rules, fen, 64, 32, seed=53, max_steps=60)
+    with E.LockstepGames(rules, fen, len(roots), 0, 64) as g:
+        g.mcts_configure(150, 1.0, 1e-4, tree_reuse=True)
+        g.set_states(roots)
+        g.mcts_search()
+        g.mcts_advance()
+        g.set_states(other)          # the caller replaced the positions: carried trees are stale
+        g.mcts_search()
+        got = g.mcts_results()
+    exp = orc.mcts_search(rules, 64, other, 150)
+    assert np.array_equal(got["visits"], exp["visits"]) and got["q"].tobytes() == exp["q"].tobytes()
