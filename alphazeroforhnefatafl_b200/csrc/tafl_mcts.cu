@@ -978,19 +978,30 @@ int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status) {
     return TAFL_OK;
 }
 
-int tafl_mcts_advance(tafl_engine* e, uint8_t* h_status) {
+int tafl_mcts_reroot(tafl_engine* e) {
     int rc = need_mcts(e);
     if (rc) return rc;
     MctsPools* m = e->mcts;
-    if (!(m->cfg.flags & TAFL_MCTS_TREE_REUSE)) { e->err = "tafl_mcts_advance: configure with TAFL_MCTS_TREE_REUSE"; return TAFL_ERR_INVALID_ARG; }
-    rc = tafl_mcts_play_best(e, nullptr);
-    if (rc) return rc;
+    if (!(m->cfg.flags & TAFL_MCTS_TREE_REUSE)) { e->err = "tafl_mcts_reroot: configure with TAFL_MCTS_TREE_REUSE"; return TAFL_ERR_INVALID_ARG; }
+    if (!m->searched) { e->err = "tafl_mcts_reroot: no search results to re-root at"; return TAFL_ERR_INVALID_ARG; }
+    cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
     k_mcts_reroot<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->r_counts, m->r_best, m->remap);
     MCTS_LAUNCHED(e);
     m->searched = false;   // the root results describe the previous root
+    return TAFL_OK;
+}
+
+int tafl_mcts_advance(tafl_engine* e, uint8_t* h_status) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    if (!(e->mcts->cfg.flags & TAFL_MCTS_TREE_REUSE)) { e->err = "tafl_mcts_advance: configure with TAFL_MCTS_TREE_REUSE"; return TAFL_ERR_INVALID_ARG; }
+    rc = tafl_mcts_play_best(e, nullptr);
+    if (rc) return rc;
+    rc = tafl_mcts_reroot(e);
+    if (rc) return rc;
     if (h_status) {
-        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_status, e->d_status, n, cudaMemcpyDeviceToHost, e->stream));
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_status, e->d_status, e->n_games, cudaMemcpyDeviceToHost, e->stream));
         TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     }
     return TAFL_OK;

@@ -316,6 +316,9 @@ class LockstepGames:
         self._ck(lib().tafl_mcts_advance(self._h, A.ptr(st) if want_status else None))
         return st
 
+    def mcts_reroot(self):
+        self._ck(lib().tafl_mcts_reroot(self._h))
+
     def mcts_stats(self):
         s = A.MctsStats()
         self._ck(lib().tafl_mcts_stats_get(self._h, C.byref(s)))

@@ -113,9 +113,15 @@ class SelfPlay:
     """MCTS self-play of this rank's shard of games; records of every move are gathered to
     ``dst``.  ``games`` is an engine.LockstepGames whose game-id base is already the shard's."""
 
-    def __init__(self, games, num_sims=800, cpuct=1.0, draw_value=1e-4, dst=0, group=None, edge_capacity=0):
+    def __init__(self, games, num_sims=800, cpuct=1.0, draw_value=1e-4, dst=0, group=None, edge_capacity=0,
+                 tree_reuse=False, evaluator=None):
+        """tree_reuse: one MCTS object per episode as in the reference (mcts.py:20-26) — the subtree
+        below the move played is kept.  evaluator: None = stub fused into the search kernel;
+        ("stub",) / ("hash", seed) = built-in device evaluators through the evaluator hook; or an
+        object with predict_batch(batch) (see mcts.MCTS)."""
         self.g, self.dst, self.group = games, dst, group
-        games.mcts_configure(num_sims, cpuct, draw_value, edge_capacity)
+        self.tree_reuse, self.evaluator = tree_reuse, evaluator
+        games.mcts_configure(num_sims, cpuct, draw_value, edge_capacity, tree_reuse=tree_reuse)
         self.stream = torch.cuda.ExternalStream(games.stream, device=games.device)
         with torch.cuda.device(games.device):
             self.rec = torch.zeros((games.n_games, A.REC_STRIDE), dtype=torch.uint8, device="cuda")
@@ -127,11 +133,19 @@ class SelfPlay:
         uint8 tensor on ``dst`` (None elsewhere)."""
         g = self.g
         with torch.cuda.stream(self.stream):
-            g.mcts_search(sync=False)
+            ev = self.evaluator
+            if ev is None:
+                g.mcts_search(sync=False)
+            elif isinstance(ev, tuple):
+                g.mcts_search_builtin({"stub": A.EVAL_STUB, "hash": A.EVAL_HASH}[ev[0]], int(ev[1]) if len(ev) > 1 else 0)
+            else:
+                g.mcts_search_with(ev.predict_batch)
             if temp != 0:
                 g.mcts_policy(temp, choose=True, seed=seed, want_probs=False)
             g.mcts_play_best(False)
             g.pack_records(self.rec.data_ptr())
+            if self.tree_reuse:
+                g.mcts_reroot()
             out = self.rec
             if only_ongoing:   # rows of games that were already over carry n_moves == 0
                 n_moves = self.rec[:, 12].to(torch.int32) | (self.rec[:, 13].to(torch.int32) << 8)

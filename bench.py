@@ -393,7 +393,39 @@ def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
            "includes": "k_mcts_init + k_mcts_sims + k_mcts_results + k_mcts_play_best + k_pack_records + torch record gather",
            "gpu_launches": int(g.launches - l0)}
     g.close()
+    # secondary numbers (rank-local, same trees / sims): the reference's own usage keeps one MCTS
+    # object per episode (tree reuse), and a real evaluator plugs in through the split-phase hook
+    for key, kw in (("tree_reuse", dict(tree_reuse=True)), ("evaluator_hook", dict(evaluator=("stub",)))):
+        try:
+            res[key] = _mcts_variant(args, E, SP, rank, local, torch, moves, **kw)
+        except Exception as ex:  # noqa: BLE001
+            res[key] = {"error": repr(ex)}
     return res
+
+
+def _mcts_variant(args, E, SP, rank, local, torch, moves, **kw):
+    n = args.mcts_games
+    g = E.LockstepGames(E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN, n, local, 128)
+    try:
+        g.set_game_id_base(rank * n)
+        g.step_random(args.seed, 20, auto_reset=True)
+        sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, **kw)
+        sp.move(gather=False)
+        s0, l0 = g.mcts_stats().as_dict(), g.launches
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(sp.stream)
+        for _ in range(moves):
+            sp.move(gather=False)
+        b.record(sp.stream)
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        s1 = g.mcts_stats().as_dict()
+        sims = s1["sims"] - s0["sims"]
+        return {"value": sims / (ms * 1e-3), "unit": "sims/s (this rank)", "ms_per_move": ms / moves, "moves_timed": moves,
+                "nodes_created_per_sim": (s1["nodes"] - s0["nodes"]) / max(1, sims), "mean_depth": (s1["depth_sum"] - s0["depth_sum"]) / max(1, sims),
+                "gpu_launches": int(g.launches - l0)}
+    finally:
+        g.close()
 
 
 if __name__ == "__main__":

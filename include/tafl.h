@@ -449,6 +449,7 @@ int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status /* may be NULL */);
  * still equals the game's state, and starts a fresh tree otherwise.  Call tafl_pack_records
  * BEFORE advancing (the records describe the searched root). */
 int tafl_mcts_advance(tafl_engine* e, uint8_t* h_status /* may be NULL */);
+int tafl_mcts_reroot(tafl_engine* e);   /* the re-rooting half alone: play_best, pack_records, reroot */
 /* totals since configure: simulations run, nodes expanded, sum of path depths, sum of edges */
 typedef struct {
     uint64_t sims, nodes, depth_sum, edges, terminal_hits, max_edges_used;

@@ -101,7 +101,8 @@ def test_replay_buffer_rolling_window():
 
 
 def test_mcts_policy_temperature():
-    """MCTS.getActionProb post-processing (mcts.py:43-53) on a fake engine."""
+    """MCTS.getActionProb plumbing (mcts.py:43-53) on a fake engine whose mcts_policy is the
+    reference formula (the device kernel is checked against the reference in the GPU tests)."""
     from alphazeroforhnefatafl_b200.mcts import MCTS
 
     class Fake:
@@ -110,6 +111,19 @@ def test_mcts_policy_temperature():
 
         def mcts_search(self, sync=True):
             pass
+
+        def mcts_policy(self, temp=1.0, choose=False, seed=0, want_probs=True):
+            r = self.mcts_results()
+            v = r["visits"].astype(np.float64)
+            p = np.zeros_like(v)
+            if temp == 0:
+                has = r["counts"] > 0
+                p[np.arange(len(v))[has], r["best"][has]] = 1.0
+            else:
+                c = v ** (1.0 / temp)
+                s = c.sum(1, keepdims=True)
+                np.divide(c, s, out=p, where=s > 0)
+            return p
 
         def mcts_results(self):
             v = np.zeros((2, A.MAX_MOVES), np.uint32)
