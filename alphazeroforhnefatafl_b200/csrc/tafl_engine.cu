@@ -99,9 +99,16 @@ template <class BB, int SP, int MINB>
 __global__ void __launch_bounds__(STEP_BLOCK, MINB)
 k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
-              uint32_t steps, int auto_reset, DevStats* __restrict__ stats, uint32_t* __restrict__ actions) {
+              uint32_t steps, int auto_reset, DevStats* __restrict__ stats, uint32_t* __restrict__ actions,
+              const unsigned long long* __restrict__ ply_base) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t c_steps = 0, c_legal = 0, c_caps = 0;
+    // Programmatic dependent launch (no-ops for a plain launch): wait for the previous ply's grid
+    // before touching its states, then let the next ply's grid start filling free CTA slots so its
+    // launch latency and ramp overlap this grid's tail.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;");
+    if (ply_base) ply0 += *ply_base;
     if (g < n) {
         tafl_state s = load_state(states + g);
         uint32_t act = 0;   // tafl_action of the last ply of this launch
@@ -359,6 +366,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     TAFL_CREATE_TRY(cudaGetDeviceProperties(&prop, device));
     e->sm_count = prop.multiProcessorCount;
     if (const char* v = std::getenv("TAFL_STEP_MINB")) e->step_minb = std::atoi(v);   // tuning knobs (profiles/sweeps)
+    if (const char* v = std::getenv("TAFL_STEP_GRAPH")) e->step_graph_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_CHUNKS")) e->host_chunks = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_MINB")) e->mcts_minb = std::atoi(v);
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
@@ -385,7 +393,8 @@ int tafl_engine_destroy(tafl_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     mcts_free(e);
     cudaFree(e->d_states); cudaFree(e->d_moves); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_actions);
-    cudaFree(e->d_stats); cudaFree(e->d_checksum);
+    cudaFree(e->d_stats); cudaFree(e->d_checksum); cudaFree(e->d_ply);
+    if (e->step_graph) cudaGraphExecDestroy(e->step_graph);
     for (auto& p : e->d_scratch) cudaFree(p);
     if (e->aux_ready) for (auto& st : e->aux) cudaStreamDestroy(st);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -540,21 +549,65 @@ int tafl_set_random_ply(tafl_engine* e, uint64_t v) { TAFL_CHECK_E(e); e->ply = 
 uint64_t tafl_random_ply(const tafl_engine* e) { return e ? e->ply : 0; }
 
 // enqueue k_step_random over games [first, first + n) on `stream`: `steps` plies starting at RNG ply `ply0`
+// (+ *d_ply_base when given); pdl = launch with the programmatic-stream-serialization attribute
 static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t first, uint32_t n, uint64_t seed, uint64_t ply0,
-                              uint32_t steps, int auto_reset) {
-#define TAFL_STEP_LAUNCH(MINB)                                                                                   \
-    TAFL_SPEC_DISPATCH(e, (k_step_random<BB, SP, MINB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, stream>>>(                \
-                               cx, e->d_states + first, n, state_words(e->start), seed, e->game_id_base + first, ply0, steps, \
-                               auto_reset, e->d_stats, e->d_actions + first)))
+                              uint32_t steps, int auto_reset, const unsigned long long* d_ply_base = nullptr, bool pdl = false) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid_for(n, STEP_BLOCK));
+    cfg.blockDim = dim3(STEP_BLOCK);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t lerr = cudaSuccess;
+#define TAFL_STEP_LAUNCH(MINB)                                                                                        \
+    TAFL_SPEC_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, k_step_random<BB, SP, MINB>, cx, e->d_states + first, n,     \
+                                                     state_words(e->start), seed, e->game_id_base + first, ply0, steps, \
+                                                     auto_reset, e->d_stats, e->d_actions + first, d_ply_base)))
     switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
+        case 4: TAFL_STEP_LAUNCH(4); break;
         case 6: TAFL_STEP_LAUNCH(6); break;
-        case 8: TAFL_STEP_LAUNCH(8); break;
         case 10: TAFL_STEP_LAUNCH(10); break;
         case 12: TAFL_STEP_LAUNCH(12); break;
-        default: TAFL_STEP_LAUNCH(4); break;
+        default: TAFL_STEP_LAUNCH(8); break;
     }
 #undef TAFL_STEP_LAUNCH
-    TAFL_LAUNCHED(e);
+    e->launches += 1;
+    TAFL_CUDA_TRY(e, lerr);
+    return TAFL_OK;
+}
+
+// n_steps single-ply launches as one graph: node i steps RNG ply *d_ply + i; nodes are joined by
+// programmatic edges (captured PDL launches).  Re-captured when (n_steps, seed, flags) change.
+static int step_graph_launch(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset) {
+    auto& k = e->step_graph_key;
+    if (!e->step_graph || k.seed != seed || k.steps != n_steps || k.auto_reset != auto_reset || k.minb != e->step_minb ||
+        k.spec != e->spec || k.gid_base != e->game_id_base) {
+        if (e->step_graph) { cudaGraphExecDestroy(e->step_graph); e->step_graph = nullptr; }
+        if (!e->d_ply) TAFL_CUDA_TRY(e, cudaMalloc(&e->d_ply, sizeof(unsigned long long)));
+        const uint64_t before = e->launches;
+        cudaGraph_t graph = nullptr;
+        TAFL_CUDA_TRY(e, cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+        int rc = TAFL_OK;
+        for (uint32_t i = 0; i < n_steps && rc == TAFL_OK; ++i)
+            rc = launch_step_random(e, e->stream, 0, e->n_games, seed, i, 1, auto_reset, e->d_ply, i > 0);
+        cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+        e->launches = before;   // capturing launched nothing
+        if (rc != TAFL_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        TAFL_CUDA_TRY(e, ce);
+        ce = cudaGraphInstantiate(&e->step_graph, graph, 0);
+        cudaGraphDestroy(graph);
+        TAFL_CUDA_TRY(e, ce);
+        k.seed = seed; k.steps = n_steps; k.auto_reset = auto_reset; k.minb = e->step_minb; k.spec = e->spec; k.gid_base = e->game_id_base;
+    }
+    const unsigned long long ply = e->ply;
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_ply, &ply, sizeof(ply), cudaMemcpyHostToDevice, e->stream));   // pageable: staged at call time
+    TAFL_CUDA_TRY(e, cudaGraphLaunch(e->step_graph, e->stream));
+    e->launches += n_steps;
+    e->ply += n_steps;
     return TAFL_OK;
 }
 
@@ -562,6 +615,7 @@ int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int 
     TAFL_CHECK_E(e);
     cudaSetDevice(e->device);
     if (spl <= 0) spl = 1;
+    if (spl == 1 && n_steps >= 4 && e->step_graph_on) return step_graph_launch(e, seed, n_steps, auto_reset);
     uint32_t done = 0;
     while (done < n_steps) {
         const uint32_t chunk = (n_steps - done) < (uint32_t)spl ? (n_steps - done) : (uint32_t)spl;

@@ -43,7 +43,12 @@ struct tafl_engine {
     bool aux_ready = false;
     int host_chunks = 8;
     int mcts_minb = 8;                 // k_mcts_sims variant: CTAs of 4 warps resident per SM
-    int step_minb = 4;                 // k_step_random variant: CTAs of 64 threads resident per SM
+    int step_minb = 8;                 // k_step_random variant: CTAs of 64 threads resident per SM (8: one wave for 65 536 games)
+    // lockstep plies as ONE CUDA graph of n_steps kernel nodes joined by programmatic (PDL) edges
+    int step_graph_on = 1;             // TAFL_STEP_GRAPH=0 falls back to plain launches
+    cudaGraphExec_t step_graph = nullptr;
+    struct { uint64_t seed = 0, gid_base = 0; uint32_t steps = 0; int auto_reset = 0, minb = 0, spec = 0; } step_graph_key;
+    unsigned long long* d_ply = nullptr;   // RNG ply of the first node of the graph (copied before each launch)
     // scratch for the by-value batch API (grown on demand)
     void* d_scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[6] = {0, 0, 0, 0, 0, 0};
