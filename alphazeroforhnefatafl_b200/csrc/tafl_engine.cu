@@ -367,6 +367,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     e->sm_count = prop.multiProcessorCount;
     if (const char* v = std::getenv("TAFL_STEP_MINB")) e->step_minb = std::atoi(v);   // tuning knobs (profiles/sweeps)
     if (const char* v = std::getenv("TAFL_STEP_GRAPH")) e->step_graph_on = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_STEP_PDL")) e->step_pdl_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_CHUNKS")) e->host_chunks = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_MINB")) e->mcts_minb = std::atoi(v);
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
@@ -593,7 +594,7 @@ static int step_graph_launch(tafl_engine* e, uint64_t seed, uint32_t n_steps, in
         TAFL_CUDA_TRY(e, cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
         int rc = TAFL_OK;
         for (uint32_t i = 0; i < n_steps && rc == TAFL_OK; ++i)
-            rc = launch_step_random(e, e->stream, 0, e->n_games, seed, i, 1, auto_reset, e->d_ply, i > 0);
+            rc = launch_step_random(e, e->stream, 0, e->n_games, seed, i, 1, auto_reset, e->d_ply, i > 0 && e->step_pdl_on);
         cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
         e->launches = before;   // capturing launched nothing
         if (rc != TAFL_OK) { if (graph) cudaGraphDestroy(graph); return rc; }

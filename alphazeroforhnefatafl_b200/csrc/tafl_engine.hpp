@@ -46,6 +46,7 @@ struct tafl_engine {
     int step_minb = 8;                 // k_step_random variant: CTAs of 64 threads resident per SM (8: one wave for 65 536 games)
     // lockstep plies as ONE CUDA graph of n_steps kernel nodes joined by programmatic (PDL) edges
     int step_graph_on = 1;             // TAFL_STEP_GRAPH=0 falls back to plain launches
+    int step_pdl_on = 1;               // TAFL_STEP_PDL=0: plain (full-serialisation) edges in the graph
     cudaGraphExec_t step_graph = nullptr;
     struct { uint64_t seed = 0, gid_base = 0; uint32_t steps = 0; int auto_reset = 0, minb = 0, spec = 0; } step_graph_key;
     unsigned long long* d_ply = nullptr;   // RNG ply of the first node of the graph (copied before each launch)
