@@ -32,6 +32,11 @@ struct MctsPools {
     uint32_t* l_counts = nullptr;     // [n_games]
     float* l_priors = nullptr;        // [n_games][TAFL_MAX_MOVES]  evaluator output
     float* l_values = nullptr;        // [n_games]                  evaluator output
+    cudaGraphExec_t round_graph = nullptr;   // num_sims rounds with a built-in evaluator (tafl_mcts_search_builtin)
+    int rg_kind = -1, rg_spec = -1;
+    uint64_t rg_seed = 0;
+    uint32_t rg_sims = 0;
+    double rg_cpuct = 0, rg_draw = 0;
     int phase = 0;                    // 0 idle, 1 begun / expanded, 2 leaves selected (evaluation pending)
     uint32_t rounds = 0;              // simulations run since tafl_mcts_begin
 };
@@ -801,6 +806,7 @@ void mcts_free(tafl_engine* e) {
     cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.n_ptab); cudaFree(m->v.edges); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
     cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best); cudaFree(m->r_probs); cudaFree(m->remap);
     cudaFree(m->d_any_overflow);
+    if (m->round_graph) cudaGraphExecDestroy(m->round_graph);
     cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
     cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
     delete m;
@@ -1225,8 +1231,39 @@ static int builtin_eval_cb(void* user, const tafl_leaf_batch*) {
 }
 int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
     if (evaluator != TAFL_EVAL_STUB && evaluator != TAFL_EVAL_HASH) return TAFL_ERR_INVALID_ARG;
-    BuiltinEval b{e, evaluator, seed};
-    return tafl_mcts_search_with(e, builtin_eval_cb, &b);
+    int rc = tafl_mcts_begin(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    // All num_sims rounds (select, evaluate, expand/backup) have static arguments: one CUDA graph,
+    // captured once per (evaluator, seed, config), replaces 3 x num_sims launches.
+    if (!m->round_graph || m->rg_kind != evaluator || m->rg_seed != seed || m->rg_sims != m->cfg.num_sims ||
+        m->rg_cpuct != m->cfg.cpuct || m->rg_draw != m->cfg.draw_value || m->rg_spec != e->spec) {
+        if (m->round_graph) { cudaGraphExecDestroy(m->round_graph); m->round_graph = nullptr; }
+        TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+        const uint64_t before = e->launches;
+        cudaGraph_t graph = nullptr;
+        TAFL_CUDA_TRY(e, cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+        for (uint32_t i = 0; i < m->cfg.num_sims && rc == TAFL_OK; ++i) {
+            rc = tafl_mcts_select_leaves(e, nullptr);
+            if (!rc) rc = tafl_eval_builtin(e, evaluator, seed);
+            if (!rc) rc = tafl_mcts_expand_backup(e);
+        }
+        cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+        e->launches = before;
+        m->phase = 1;
+        m->rounds = 0;
+        if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+        TAFL_CUDA_TRY(e, ce);
+        ce = cudaGraphInstantiate(&m->round_graph, graph, 0);
+        cudaGraphDestroy(graph);
+        TAFL_CUDA_TRY(e, ce);
+        m->rg_kind = evaluator; m->rg_seed = seed; m->rg_sims = m->cfg.num_sims; m->rg_cpuct = m->cfg.cpuct;
+        m->rg_draw = m->cfg.draw_value; m->rg_spec = e->spec;
+    }
+    TAFL_CUDA_TRY(e, cudaGraphLaunch(m->round_graph, e->stream));
+    e->launches += 3ull * m->cfg.num_sims;
+    m->rounds = m->cfg.num_sims;
+    return tafl_mcts_finish(e);
 }
 
 }  // extern "C"
