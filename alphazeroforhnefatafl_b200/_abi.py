@@ -171,6 +171,8 @@ STATE_DTYPE = np.dtype([
 PLAY_DTYPE = np.dtype([("from_row", "u1"), ("from_col", "u1"), ("axis", "u1"), ("disp", "i1")])
 EFFECTS_DTYPE = np.dtype([("captures", "<u8", (2,)), ("status", "u1"), ("err", "u1"), ("n_captures", "u1"),
                           ("_pad", "u1", (5,))])
+PLAY_RECORD_DTYPE = np.dtype([("play", PLAY_DTYPE), ("side", "u1"), ("_pad", "u1", (3,)), ("effects", EFFECTS_DTYPE)])
+assert PLAY_RECORD_DTYPE.itemsize == 32
 ENCLOSURE_DTYPE = np.dtype([("occupied", "<u8", (2,)), ("unoccupied", "<u8", (2,)), ("boundary", "<u8", (2,)),
                             ("found", "u1"), ("_pad", "u1", (7,))])
 ENCL_QUERY_DTYPE = np.dtype([("row", "u1"), ("col", "u1"), ("abort_on_edge", "u1"), ("abort_on_corner", "u1"),

@@ -98,6 +98,10 @@ def lib():
         "tafl_enclosure_secure": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
         "tafl_detect_exit_fort": (C.c_int, [vp, vp, C.c_uint32, vp]),
         "tafl_side_can_play": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+        "tafl_history_enable": (C.c_int, [vp, C.c_uint32]),
+        "tafl_undo_last_play": (C.c_int, [vp, vp]),
+        "tafl_history_len": (C.c_int, [vp, vp]),
+        "tafl_play_history": (C.c_int, [vp, C.c_uint32, vp, C.c_uint32, C.POINTER(C.c_uint32)]),
         "tafl_mcts_configure": (C.c_int, [vp, C.POINTER(A.MctsConfig)]),
         "tafl_mcts_search": (C.c_int, [vp]),
         "tafl_mcts_search_async": (C.c_int, [vp]),

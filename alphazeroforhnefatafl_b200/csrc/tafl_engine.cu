@@ -53,10 +53,11 @@ template <class BB, int SP>
 __global__ void __launch_bounds__(STEP_BLOCK)
 k_step_plays(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
              const tafl_play* __restrict__ plays, tafl_play_effects* __restrict__ fx_out,
-             uint8_t* __restrict__ status_out, uint8_t* __restrict__ err_out) {
+             uint8_t* __restrict__ status_out, uint8_t* __restrict__ err_out, HistView hv) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= n) return;
     tafl_state s = load_state(states + g);
+    const tafl_state before = s;
     const tafl_play pl = plays[g];
     tafl_play_effects fx;
     fx.captures[0] = fx.captures[1] = 0;
@@ -71,9 +72,41 @@ k_step_plays(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ st
         store_state(states + g, s);
     }
     fx.status = s.status;
+    if (!err && hv.st) {   // Game::do_play: state_history.push(old state), play_history.push(record)
+        const uint32_t len = hv.len[g], slot = len % hv.cap;
+        store_state(hv.st + (size_t)slot * hv.n + g, before);
+        tafl_play_record r;
+        r.play = pl;
+        r.side = (before.flags & TAFL_FLAG_DEF_TO_PLAY) ? TAFL_DEFENDER : TAFL_ATTACKER;
+        r._pad[0] = r._pad[1] = r._pad[2] = 0;
+        r.effects = fx;
+        hv.rec[(size_t)slot * hv.n + g] = r;
+        hv.len[g] = len + 1;
+        if (len + 1 - hv.floor[g] > hv.cap) hv.floor[g] = len + 1 - hv.cap;
+    }
     if (fx_out) fx_out[g] = fx;
     if (status_out) status_out[g] = s.status;
     if (err_out) err_out[g] = (uint8_t)err;
+}
+
+// Game::undo_last_play (game/mod.rs:103-108): pop the newest (state, record) pair of each selected game
+__global__ void k_undo(tafl_state* __restrict__ states, uint32_t n, const uint8_t* __restrict__ mask, HistView hv) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n || (mask && !mask[g])) return;
+    const uint32_t len = hv.len[g];
+    if (len <= hv.floor[g]) return;   // state_history.pop() == None: nothing to undo
+    const uint32_t slot = (len - 1) % hv.cap;
+    store_state(states + g, load_state(hv.st + (size_t)slot * hv.n + g));
+    hv.len[g] = len - 1;
+}
+// forget the history of games [first, first + n) or of the listed games
+__global__ void k_hist_clear(HistView hv, uint32_t first, uint32_t n, const uint32_t* __restrict__ ids) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t g = ids ? ids[i] : first + i;
+    if (g >= hv.n) return;
+    hv.len[g] = 0;
+    hv.floor[g] = 0;
 }
 
 // do_valid_play (logic.rs:782-820) on one compact move per game
@@ -395,6 +428,7 @@ int tafl_engine_destroy(tafl_engine* e) {
     mcts_free(e);
     cudaFree(e->d_states); cudaFree(e->d_moves); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_actions);
     cudaFree(e->d_stats); cudaFree(e->d_checksum); cudaFree(e->d_ply);
+    cudaFree(e->hist.st); cudaFree(e->hist.rec); cudaFree(e->hist.len); cudaFree(e->hist.floor);
     if (e->step_graph) cudaGraphExecDestroy(e->step_graph);
     for (auto& p : e->d_scratch) cudaFree(p);
     if (e->aux_ready) for (auto& st : e->aux) cudaStreamDestroy(st);
@@ -429,12 +463,14 @@ int tafl_reset(tafl_engine* e, const uint32_t* h_ids, uint32_t n) {
     if (!h_ids) {
         k_fill_states<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, state_words(e->start));
         TAFL_LAUNCHED(e);
+        if (e->hist.st) k_hist_clear<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->hist, 0, e->n_games, nullptr);
     } else if (n) {
         uint32_t* d_ids;
         int rc = upload(e, 0, h_ids, n, &d_ids);
         if (rc) return rc;
         k_reset_ids<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_states, d_ids, n, e->n_games, state_words(e->start));
         TAFL_LAUNCHED(e);
+        if (e->hist.st) k_hist_clear<<<grid_for(n, 256), 256, 0, e->stream>>>(e->hist, 0, n, d_ids);
     }
     return sync_engine(e);
 }
@@ -445,6 +481,7 @@ int tafl_set_states(tafl_engine* e, const tafl_state* h, uint32_t first, uint32_
     int rc = check_side_len(e, h, n);
     if (rc) return rc;
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_states + first, h, (size_t)n * sizeof(tafl_state), cudaMemcpyHostToDevice, e->stream));
+    if (e->hist.st && n) k_hist_clear<<<grid_for(n, 256), 256, 0, e->stream>>>(e->hist, first, n, nullptr);
     return sync_engine(e);
 }
 int tafl_get_states(tafl_engine* e, tafl_state* h, uint32_t first, uint32_t n) {
@@ -512,7 +549,7 @@ int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_fx)
     if (rc) return rc;
     rc = device_out(e, 1, n, &d_fx);
     if (rc) return rc;
-    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx, nullptr, nullptr)));
+    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx, nullptr, nullptr, e->hist)));
     TAFL_LAUNCHED(e);
     if (h_fx) { rc = download(e, h_fx, d_fx, n); if (rc) return rc; }
     return sync_engine(e);
@@ -529,7 +566,7 @@ int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status
     rc = device_out(e, 1, n, &d_err);
     if (rc) return rc;
     TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, nullptr,
-                                                                                                    e->d_status, d_err)));
+                                                                                                    e->d_status, d_err, e->hist)));
     TAFL_LAUNCHED(e);
     if ((rc = download(e, h_status, e->d_status, n))) return rc;
     if (h_err && (rc = download(e, h_err, d_err, n))) return rc;
@@ -542,6 +579,73 @@ int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_
     const uint32_t n = e->n_games;
     TAFL_SPEC_DISPATCH(e, (k_step_moves<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_moves, 1u, nullptr, d_status)));
     TAFL_LAUNCHED(e);
+    return sync_engine(e);
+}
+
+// ---- Game history / undo (game/mod.rs:77-108) -------------------------------------------------
+int tafl_history_enable(tafl_engine* e, uint32_t capacity) {
+    TAFL_CHECK_E(e);
+    if (capacity == 0) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    cudaFree(e->hist.st); cudaFree(e->hist.rec); cudaFree(e->hist.len); cudaFree(e->hist.floor);
+    e->hist = HistView{};
+    const size_t n = e->n_games;
+    HistView hv;
+    hv.cap = capacity;
+    hv.n = e->n_games;
+    TAFL_CUDA_TRY(e, cudaMalloc(&hv.len, n * sizeof(uint32_t)));
+    TAFL_CUDA_TRY(e, cudaMalloc(&hv.floor, n * sizeof(uint32_t)));
+    TAFL_CUDA_TRY(e, cudaMalloc(&hv.rec, n * capacity * sizeof(tafl_play_record)));
+    TAFL_CUDA_TRY(e, cudaMalloc(&hv.st, n * capacity * sizeof(tafl_state)));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(hv.len, 0, n * sizeof(uint32_t), e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(hv.floor, 0, n * sizeof(uint32_t), e->stream));
+    e->hist = hv;
+    return sync_engine(e);
+}
+static int need_hist(tafl_engine* e) {
+    if (!e->hist.st) { e->err = "tafl_history_enable has not been called"; return TAFL_ERR_INVALID_ARG; }
+    return TAFL_OK;
+}
+int tafl_undo_last_play(tafl_engine* e, const uint8_t* h_mask) {
+    TAFL_CHECK_E(e);
+    int rc = need_hist(e);
+    if (rc) return rc;
+    cudaSetDevice(e->device);
+    const uint32_t n = e->n_games;
+    uint8_t* d_mask = nullptr;
+    if (h_mask && (rc = upload(e, 0, h_mask, n, &d_mask))) return rc;
+    k_undo<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_states, n, d_mask, e->hist);
+    TAFL_LAUNCHED(e);
+    return sync_engine(e);
+}
+int tafl_history_len(tafl_engine* e, uint32_t* h_len) {
+    TAFL_CHECK_E(e);
+    int rc = need_hist(e);
+    if (rc) return rc;
+    if (!h_len) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_len, e->hist.len, (size_t)e->n_games * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    return sync_engine(e);
+}
+int tafl_play_history(tafl_engine* e, uint32_t game, tafl_play_record* h_out, uint32_t cap, uint32_t* n_out) {
+    TAFL_CHECK_E(e);
+    int rc = need_hist(e);
+    if (rc) return rc;
+    if (game >= e->n_games || !n_out || (cap && !h_out)) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    uint32_t lf[2];
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(&lf[0], e->hist.len + game, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(&lf[1], e->hist.floor + game, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    uint32_t held = lf[0] - lf[1];
+    if (held > cap) { lf[1] += held - cap; held = cap; }   // the newest `cap` records
+    for (uint32_t k = 0; k < held; ++k) {
+        const uint32_t slot = (lf[1] + k) % e->hist.cap;
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_out + k, e->hist.rec + (size_t)slot * e->hist.n + game, sizeof(tafl_play_record),
+                                         cudaMemcpyDeviceToHost, e->stream));
+    }
+    *n_out = held;
     return sync_engine(e);
 }
 

@@ -18,6 +18,16 @@ struct DevStats {
 
 struct MctsPools;  // tafl_mcts.cu
 
+// Game<T>::state_history / play_history (game/mod.rs:77-108) for every resident game: a ring of the
+// last `cap` (state before the play, PlayRecord) pairs per game, ply-major so a push is coalesced.
+struct HistView {
+    tafl_state* st = nullptr;          // [cap][n_games]
+    tafl_play_record* rec = nullptr;   // [cap][n_games]
+    uint32_t* len = nullptr;           // [n_games] plays recorded so far (Vec::len of play_history)
+    uint32_t* floor = nullptr;         // [n_games] oldest entry still held (len - floor <= cap)
+    uint32_t cap = 0, n = 0;
+};
+
 }  // namespace tafl
 
 struct tafl_engine {
@@ -54,6 +64,7 @@ struct tafl_engine {
     void* d_scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[6] = {0, 0, 0, 0, 0, 0};
     tafl::MctsPools* mcts = nullptr;
+    tafl::HistView hist;
     std::string err;
 };
 

@@ -260,6 +260,27 @@ class LockstepGames:
         self._ck(lib().tafl_step_random_host(self._h, A.ptr(states), A.ptr(out), seed, n_steps, int(auto_reset)))
         return out
 
+    # -- Game<T> history / undo (game/mod.rs:77-108) ------------------------------------------------
+    def history_enable(self, capacity):
+        """keep (state, PlayRecord) of the last `capacity` valid plays of do_play per game"""
+        self._ck(lib().tafl_history_enable(self._h, capacity))
+
+    def undo_last_play(self, mask=None):
+        """Game::undo_last_play in every game (or those with mask != 0); no-op where nothing is recorded"""
+        m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+        self._ck(lib().tafl_undo_last_play(self._h, None if m is None else A.ptr(m)))
+
+    def history_len(self):
+        out = np.zeros(self.n_games, np.uint32)
+        self._ck(lib().tafl_history_len(self._h, A.ptr(out)))
+        return out
+
+    def play_history(self, game, cap=1024):
+        out = np.zeros(cap, A.PLAY_RECORD_DTYPE)
+        n = C.c_uint32(0)
+        self._ck(lib().tafl_play_history(self._h, game, A.ptr(out), cap, C.byref(n)))
+        return out[:n.value]
+
     def set_game_id_base(self, v):
         self._ck(lib().tafl_set_game_id_base(self._h, v))
 

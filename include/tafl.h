@@ -305,6 +305,26 @@ int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_eff
  * (game/mod.rs:95): per game one status byte and one PlayInvalid byte come back instead of the
  * 24-byte effects record.  HOST buffers; h_err may be NULL. */
 int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err);
+/* Game<T>::play_history / state_history / undo_last_play (game/mod.rs:77-108) for every
+ * resident game.  After tafl_history_enable, every VALID play of tafl_step / tafl_step_status
+ * pushes (state before the play, PlayRecord) for its game — an invalid play pushes nothing,
+ * as in Game::do_play (mod.rs:96: the `?` returns before the push).  The reference Vecs are
+ * unbounded; here the last `capacity` plies per game are held (older ones are dropped).
+ * tafl_reset / tafl_set_states clear the history of the games they touch. */
+typedef struct {
+    tafl_play play;
+    uint8_t   side;              /* TAFL_ATTACKER | TAFL_DEFENDER: PlayRecord.side (play.rs:109) */
+    uint8_t   _pad[3];
+    tafl_play_effects effects;   /* captures + outcome (PlayEffects, game/mod.rs:54-61)          */
+} tafl_play_record;              /* 32 bytes */
+int tafl_history_enable(tafl_engine* e, uint32_t capacity);
+/* undo_last_play (mod.rs:103-108) in the games with h_mask[i] != 0 (NULL = every game); a game
+ * with no recorded play is left unchanged, as in the reference */
+int tafl_undo_last_play(tafl_engine* e, const uint8_t* h_mask);
+/* play_history.len() per game / the recorded plays of one game, oldest held first */
+int tafl_history_len(tafl_engine* e, uint32_t* h_len);
+int tafl_play_history(tafl_engine* e, uint32_t game, tafl_play_record* h_out, uint32_t cap,
+                      uint32_t* n_out);
 /* do_valid_play (logic.rs:782-820) on DEVICE-resident compact moves, no validation, no copy. */
 int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_status);
 
