@@ -13,6 +13,17 @@
 #define TAFL_HD inline
 #endif
 
+// Re-convergence points for the one-thread-per-game kernels: lanes that entered a region together
+// (TAFL_LANES_HERE) wait for each other again (TAFL_RECONVERGE) before a long common tail, so the
+// tail is issued once per warp instead of once per divergent group.  No-ops in the host build.
+#if defined(__CUDA_ARCH__)
+#define TAFL_LANES_HERE(m) const unsigned m = __activemask()
+#define TAFL_RECONVERGE(m) __syncwarp(m)
+#else
+#define TAFL_LANES_HERE(m) const unsigned m = 0u
+#define TAFL_RECONVERGE(m) (void)(m)
+#endif
+
 namespace tafl {
 
 TAFL_HD int popc32(uint32_t x) {

@@ -628,13 +628,15 @@ TAFL_HD bool enclosure_win_possible(const Ctx<BB, SP>& cx, const Pos<BB>& p, boo
     const BB fillable = (cx.board & ~p.occ()) | p.def;
     const BB stop = (abort_on_edge ? cx.edge : BB::zero()) | cx.corners;
     BB reg = p.def;
+    bool escaped = false;   // single exit: the lanes of a warp leave the loop together
     for (int it = 0; it < 128; ++it) {
-        if ((reg & stop).any()) return false;
-        BB grown = reg | (dilate4(cx, reg) & fillable);
+        escaped = (reg & stop).any();
+        if (escaped) break;
+        const BB grown = reg | (dilate4(cx, reg) & fillable);
         if (grown == reg) break;
         reg = grown;
     }
-    return !(reg & stop).any();
+    return !escaped;
 }
 // enclosure_secure (logic.rs:408-463)
 template <class BB, int SP>
@@ -714,35 +716,55 @@ TAFL_HD void track_play(tafl_state& s, uint32_t rec, int def_side, bool captures
 template <class BB, int SP>
 TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const tafl_state& s, int mover_def, int piece_kind,
                              int to_r, int to_c, BB caps) {
-    if (!p.side(!mover_def).any()) return TAFL_STATUS_WIN(TAFL_WIN_ALL_CAPTURED, mover_def);
+    // Single exit on purpose: the side-specific tests diverge inside a warp (mixed sides to move,
+    // data-dependent fill lengths) and the common tail — side_can_play — must be issued once.
+    TAFL_LANES_HERE(lanes);
+    uint8_t st = TAFL_STATUS_ONGOING;
+    bool done = false;
     const int N = cx.n();
-    if (!mover_def) {
-        if ((caps & p.kbit).any()) return TAFL_STATUS_WIN(TAFL_WIN_KING_CAPTURED, 0);
-        if (cx.r_enclosure_win() != TAFL_ENCL_NONE &&
-            enclosure_win_possible(cx, p, cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS)) {
+    if (!p.side(!mover_def).any()) {
+        st = TAFL_STATUS_WIN(TAFL_WIN_ALL_CAPTURED, mover_def);
+        done = true;
+    } else if (!mover_def) {
+        if ((caps & p.kbit).any()) {
+            st = TAFL_STATUS_WIN(TAFL_WIN_KING_CAPTURED, 0);
+            done = true;
+        } else if (cx.r_enclosure_win() != TAFL_ENCL_NONE &&
+                   enclosure_win_possible(cx, p, cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS)) {
             Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.def, p.att,
                                         cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS, true);
-            if (e.found && (e.region & p.occ()).popc() == p.def.popc() && enclosure_secure(cx, p, e, false, true))
-                return TAFL_STATUS_WIN(TAFL_WIN_ENCLOSED, 0);
+            if (e.found && (e.region & p.occ()).popc() == p.def.popc() && enclosure_secure(cx, p, e, false, true)) {
+                st = TAFL_STATUS_WIN(TAFL_WIN_ENCLOSED, 0);
+                done = true;
+            }
         }
     } else {
+        bool escaped = false;
         if (piece_kind == KIND_K) {
             const bool at_edge = to_r == 0 || to_r == N - 1 || to_c == 0 || to_c == N - 1;
             const bool at_corner = (to_r == 0 || to_r == N - 1) && (to_c == 0 || to_c == N - 1);
-            if (cx.r_edge_escape() ? at_edge : at_corner) return TAFL_STATUS_WIN(TAFL_WIN_KING_ESCAPED, 1);
+            escaped = cx.r_edge_escape() ? at_edge : at_corner;
         }
-        if (cx.r_exit_fort() && detect_exit_fort(cx, p)) return TAFL_STATUS_WIN(TAFL_WIN_EXIT_FORT, 1);
+        if (escaped) {
+            st = TAFL_STATUS_WIN(TAFL_WIN_KING_ESCAPED, 1);
+            done = true;
+        } else if (cx.r_exit_fort() && detect_exit_fort(cx, p)) {
+            st = TAFL_STATUS_WIN(TAFL_WIN_EXIT_FORT, 1);
+            done = true;
+        }
     }
-    if (cx.r_repetition_enabled()) {
+    if (!done && cx.r_repetition_enabled()) {
         uint32_t reps = mover_def ? s.def_reps : s.att_reps;
-        if (reps >= cx.r_n_repetitions())
-            return cx.r_repetition_is_loss() ? TAFL_STATUS_WIN(TAFL_WIN_REPETITION, !mover_def)
-                                               : TAFL_STATUS_DRAW(TAFL_DRAW_REPETITION);
+        if (reps >= cx.r_n_repetitions()) {
+            st = cx.r_repetition_is_loss() ? TAFL_STATUS_WIN(TAFL_WIN_REPETITION, !mover_def)
+                                           : TAFL_STATUS_DRAW(TAFL_DRAW_REPETITION);
+            done = true;
+        }
     }
-    if (!side_can_play(cx, p, !mover_def))
-        return cx.r_draw_on_no_plays() ? TAFL_STATUS_DRAW(TAFL_DRAW_NO_PLAYS)
-                                         : TAFL_STATUS_WIN(TAFL_WIN_NO_PLAYS, mover_def);
-    return TAFL_STATUS_ONGOING;
+    TAFL_RECONVERGE(lanes);
+    if (!done && !side_can_play(cx, p, !mover_def))
+        st = cx.r_draw_on_no_plays() ? TAFL_STATUS_DRAW(TAFL_DRAW_NO_PLAYS) : TAFL_STATUS_WIN(TAFL_WIN_NO_PLAYS, mover_def);
+    return st;
 }
 
 // ---------------------------------------------------------------------------------------------
