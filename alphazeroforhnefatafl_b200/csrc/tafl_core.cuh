@@ -449,11 +449,20 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
     else if (to_c == N - 1) { horizontal = 0; away = -1; }
     else return false;
     const BB own = p.side(mover_def), opp = p.side(!mover_def), occ = p.occ();
-    {   // a wall starts with an enemy piece right beside `to` along the edge (logic.rs:485-522: any
-        // other first tile ends the search with cnt == 0), so most edge moves leave here
+    {   // Exact pre-filter.  The search counts enemy pieces pinned by a piece of the mover, walking
+        // away from `to` along the edge, and needs cnt >= 2 (logic.rs:485-522); any other tile ends
+        // the run.  So a wall exists only if the first TWO tiles on one side of `to` are both pinned
+        // enemies — a mask test; the tile-by-tile walk below then runs for real candidates only.
         const BB tb0 = BB::bit(idx_of<BB>(to_r, to_c));
-        const BB along = horizontal ? (step_left(cx, tb0) | step_right(cx, tb0)) : (step_up(cx, tb0) | step_down(cx, tb0));
-        if (!(along & opp).any()) return false;
+        const BB pinned = opp & (horizontal ? (away > 0 ? step_up(cx, own) : step_down(cx, own))
+                                            : (away > 0 ? step_left(cx, own) : step_right(cx, own)));
+        const BB m1 = horizontal ? step_left(cx, tb0) : step_up(cx, tb0);
+        const BB m2 = horizontal ? step_left(cx, m1) : step_up(cx, m1);
+        const BB p1 = horizontal ? step_right(cx, tb0) : step_down(cx, tb0);
+        const BB p2 = horizontal ? step_right(cx, p1) : step_down(cx, p1);
+        const bool minus = (pinned & m1).any() && (pinned & m2).any();
+        const bool plus = (pinned & p1).any() && (pinned & p2).any();
+        if (!(minus || plus)) return false;
     }
     const bool cmc = cx.r_sw_corners_may_close() != 0;
     BB wall = BB::zero();
