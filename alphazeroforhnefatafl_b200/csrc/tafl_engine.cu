@@ -403,6 +403,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     if (const char* v = std::getenv("TAFL_STEP_PDL")) e->step_pdl_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_CHUNKS")) e->host_chunks = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_MINB")) e->mcts_minb = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_MCTS_G")) e->mcts_group = std::atoi(v);
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_states, (size_t)n_games * sizeof(tafl_state)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_counts, (size_t)n_games * sizeof(uint32_t)));

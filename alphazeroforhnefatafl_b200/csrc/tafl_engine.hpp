@@ -53,6 +53,7 @@ struct tafl_engine {
     bool aux_ready = false;
     int host_chunks = 8;
     int mcts_minb = 8;                 // k_mcts_sims variant: CTAs of 4 warps resident per SM
+    int mcts_group = 16;               // TAFL_MCTS_G: lanes per tree of k_mcts_sims_g (32/16/8); 0 = first-generation k_mcts_sims
     int step_minb = 8;                 // k_step_random variant: CTAs of 64 threads resident per SM (8: one wave for 65 536 games)
     // lockstep plies as ONE CUDA graph of n_steps kernel nodes joined by programmatic (PDL) edges
     int step_graph_on = 1;             // TAFL_STEP_GRAPH=0 falls back to plain launches

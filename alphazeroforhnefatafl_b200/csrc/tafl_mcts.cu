@@ -236,6 +236,195 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// k_mcts_sims_g: the same search with G lanes per tree (32/G trees per warp).  Everything up to the
+// choice of the edge to open is done per group; the expensive part of a simulation — do_valid_move
+// for the new child and the piece table of its expansion, identical straight-line code for every
+// tree — sits behind one full-warp convergence point, so it is issued ONCE for all trees of the
+// warp instead of once per tree.  The child is created and expanded from registers (no store ->
+// load round trip through its header and state).  Results are bit-identical to k_mcts_sims.
+// ---------------------------------------------------------------------------------------------
+template <int G>
+__device__ __forceinline__ void grp_puct_select(const MctsEdge* __restrict__ ed, uint32_t L, uint32_t Ns, double cpuct, unsigned gmask,
+                                                int gl, uint32_t& out_a, uint32_t& out_N, uint32_t& out_child) {
+    const double sq_vis = sqrt((double)Ns), sq_new = sqrt((double)Ns + MCTS_EPS);
+    const double c_uni = cpuct * (1.0 / (double)L);
+    const double t_vis = c_uni * sq_vis, u_new = c_uni * sq_new;
+    double best_u = -INFINITY;
+    uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
+    for (uint32_t a0 = gl; a0 < L; a0 += 4 * G) {
+        MctsEdge e4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) e4[j] = ed[a];
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) {
+                double u;
+                if (e4[j].N > 0) u = e4[j].Q + t_vis / (double)(1u + e4[j].N);
+                else u = u_new;
+                if (u > best_u) { best_u = u; best_a = a; best_N = e4[j].N; best_child = e4[j].child; }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        const double ou = __shfl_xor_sync(gmask, best_u, o, G);
+        const uint32_t oa = __shfl_xor_sync(gmask, best_a, o, G);
+        const uint32_t on = __shfl_xor_sync(gmask, best_N, o, G);
+        const uint32_t oc = __shfl_xor_sync(gmask, best_child, o, G);
+        if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; best_N = on; best_child = oc; }
+    }
+    out_a = best_a; out_N = best_N; out_child = best_child;
+}
+
+__device__ __forceinline__ void grp_backup(uint4* __restrict__ n_hdr, MctsEdge* __restrict__ edges, uint32_t node, double v,
+                                           unsigned gmask, int gl) {
+    while (true) {
+        const uint4 h = n_hdr[node];
+        if (h.z == MCTS_NO_PARENT) break;
+        const uint32_t parent = h.z, a = hdr_pedge(h.w);
+        uint4 ph = n_hdr[parent];
+        MctsEdge* const ep = edges + ph.x + a;
+        const MctsEdge e = *ep;
+        double q;
+        if (e.N > 0) q = ((double)e.N * e.Q + v) / (double)(e.N + 1u);
+        else q = v;
+        __syncwarp(gmask);
+        if (gl == 0) {
+            ep->Q = q;
+            ep->N = e.N + 1u;
+            ph.y += 1u;
+            n_hdr[parent] = ph;
+        }
+        __syncwarp(gmask);
+        v = -v;
+        node = parent;
+    }
+}
+
+template <class BB, int SP, int G, int MINB>
+__global__ void __launch_bounds__(MCTS_WARPS * 32, MINB)
+k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, uint32_t sims, double cpuct, double draw_value,
+              uint32_t* __restrict__ any_overflow) {
+    constexpr int TPW = 32 / G;
+    enum { M_NONE = 0, M_BACKUP, M_CREATE, M_EXPAND };
+    const int lane = threadIdx.x & 31, gl = lane % G, gshift = (lane / G) * G;
+    const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << (G & 31)) - 1u) << gshift);
+    const uint32_t tree_raw = (blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5)) * TPW + (uint32_t)(lane / G);
+    const bool live = tree_raw < n_trees;
+    const uint32_t tree = live ? tree_raw : 0u;
+    tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    uint32_t n_nodes = mv.t_nodes[tree], n_edges_used = mv.t_edges[tree];
+    bool overflow = mv.t_overflow[tree] != 0;
+    bool stop = !live || overflow;   // a stopped group only keeps the warp-wide convergence points
+    unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_edges = 0, c_term = 0;
+
+    for (uint32_t sim = 0; sim < sims; ++sim) {
+        int mode = M_NONE;
+        uint32_t node = 0, depth = 0, sel_a = 0, sel_base = 0;
+        uint4 h = make_uint4(0u, 0u, 0u, 0u);
+        double v = 0.0;
+        if (!stop) {
+            while (true) {   // ---- descend to the edge to open (mcts.py:104-123) or to a terminal node
+                h = n_hdr[node];
+                const uint32_t es = hdr_es(h.w);
+                if (es != ES_ONGOING) {   // mcts.py:77-81
+                    v = -(es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value));
+                    c_term += 1;
+                    c_depth += depth;
+                    mode = M_BACKUP;
+                    break;
+                }
+                if (!hdr_expanded(h.w)) { mode = M_EXPAND; break; }   // the root of a fresh tree
+                const uint32_t L = hdr_n_edges(h.w);
+                if (L == 0) { v = 0.0; mode = M_BACKUP; break; }
+                uint32_t a, bN, bchild;
+                grp_puct_select<G>(edges + h.x, L, h.y, cpuct, gmask, gl, a, bN, bchild);
+                if (bN == 0) { mode = M_CREATE; sel_a = a; sel_base = h.x; break; }
+                node = bchild;
+                depth += 1;
+            }
+        }
+        __syncwarp();   // every tree of the warp opens its new node together
+        if (mode == M_CREATE || mode == M_EXPAND) {
+            tafl_state s = load_state(n_state + node);
+            uint32_t target = node, parent = h.z, pedge = hdr_pedge(h.w), es = ES_ONGOING;
+            bool expand = true;
+            if (mode == M_CREATE) {   // getNextState (mcts.py:122-123)
+                if (n_nodes >= mv.node_cap) {   // only reachable with tree reuse
+                    overflow = true;
+                    expand = false;
+                } else {
+                    const tafl_move m = grp_decode_edge<G>(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
+                                                           (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)sel_a, gmask, gshift, gl);
+                    do_valid_move(cx, s, m);
+                    target = n_nodes++;
+                    c_nodes += 1;
+                    parent = node;
+                    pedge = sel_a;
+                    depth += 1;
+                    es = es_code(s);
+                    if (gl == 0) {
+                        store_state(n_state + target, s);
+                        edges[sel_base + sel_a].child = target;
+                    }
+                    if (es != ES_ONGOING) {   // the new node is terminal (mcts.py:77-81)
+                        if (gl == 0) n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack(0, pedge, 0, es));
+                        v = -(es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value));
+                        c_term += 1;
+                        c_depth += depth;
+                        expand = false;
+                    }
+                }
+            }
+            if (expand) {   // mcts.py:83-102: leaf, Ns = 0, return -v with v = 0
+                const Pos<BB> p = load_pos(cx, s);
+                int n_pieces;
+                const int L = grp_build_ptab<G>(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, n_ptab + (size_t)target * MCTS_PT_MAX, gmask,
+                                                gl, &n_pieces);
+                if ((uint32_t)L > mv.edge_cap - n_edges_used || n_pieces > MCTS_PT_MAX) {
+                    overflow = true;
+                    if (mode == M_CREATE && gl == 0) n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack(0, pedge, 0, es));
+                } else {
+                    MctsEdge z;
+                    z.Q = 0.0; z.N = 0u; z.child = 0u;
+                    for (int a = gl; a < L; a += G) edges[n_edges_used + a] = z;
+                    if (gl == 0) n_hdr[target] = make_uint4(n_edges_used, 0u, parent, hdr_pack((uint32_t)L, pedge, 1u, es, (uint32_t)n_pieces));
+                    n_edges_used += (uint32_t)L;
+                    c_edges += (unsigned long long)L;
+                    c_depth += depth;
+                    v = -0.0;
+                }
+            }
+            node = target;
+            __syncwarp(gmask);
+        }
+        if (overflow) stop = true;
+        if (!stop && mode != M_NONE) {   // ---- backup (mcts.py:125-136)
+            grp_backup(n_hdr, edges, node, v, gmask, gl);
+            c_sims += 1;
+        }
+    }
+    if (gl == 0 && live) {
+        mv.t_nodes[tree] = n_nodes;
+        mv.t_edges[tree] = n_edges_used;
+        if (overflow) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+        atomicAdd(&mv.stats[ST_SIMS], c_sims);
+        atomicAdd(&mv.stats[ST_NODES], c_nodes);
+        atomicAdd(&mv.stats[ST_DEPTH], c_depth);
+        atomicAdd(&mv.stats[ST_EDGES], c_edges);
+        atomicAdd(&mv.stats[ST_TERMINAL], c_term);
+        atomicMax(&mv.stats[ST_MAXEDGES], (unsigned long long)n_edges_used);
+    }
+}
+
 // MCTS.getActionProb (mcts.py:40-47), temp = 0 with first-max: root visit counts, Q, moves, argmax
 template <class BB, int SP>
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
@@ -909,13 +1098,25 @@ int tafl_mcts_search_async(tafl_engine* e) {
     TAFL_SPEC_DISPATCH(e, (k_mcts_sims<BB, SP, MINB><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->cfg.num_sims,   \
                                                                                            m->cfg.cpuct, m->cfg.draw_value, \
                                                                                            m->d_any_overflow)))
-    switch (e->mcts_minb) {   // resident CTAs of 4 warps per SM the kernel is compiled for (register cap)
-        case 4: TAFL_MCTS_LAUNCH(4); break;
-        case 6: TAFL_MCTS_LAUNCH(6); break;
-        case 10: TAFL_MCTS_LAUNCH(10); break;
-        default: TAFL_MCTS_LAUNCH(8); break;
+#define TAFL_MCTS_LAUNCH_G(G, MINB)                                                                                         \
+    TAFL_SPEC_DISPATCH(e, (k_mcts_sims_g<BB, SP, G, MINB><<<grid_for(n, MCTS_WARPS * (32 / G)), MCTS_WARPS * 32, 0, e->stream>>>( \
+                              cx, m->v, n, m->cfg.num_sims, m->cfg.cpuct, m->cfg.draw_value, m->d_any_overflow)))
+    if (e->mcts_group == 16) {        // lanes per tree (TAFL_MCTS_G): 2 trees per warp
+        TAFL_MCTS_LAUNCH_G(16, 4);
+    } else if (e->mcts_group == 8) {  // 4 trees per warp
+        TAFL_MCTS_LAUNCH_G(8, 4);
+    } else if (e->mcts_group == 32) { // one tree per warp, converged create + expand
+        TAFL_MCTS_LAUNCH_G(32, 4);
+    } else {
+        switch (e->mcts_minb) {   // the first-generation kernel: resident CTAs of 4 warps per SM (register cap)
+            case 4: TAFL_MCTS_LAUNCH(4); break;
+            case 6: TAFL_MCTS_LAUNCH(6); break;
+            case 10: TAFL_MCTS_LAUNCH(10); break;
+            default: TAFL_MCTS_LAUNCH(8); break;
+        }
     }
 #undef TAFL_MCTS_LAUNCH
+#undef TAFL_MCTS_LAUNCH_G
     MCTS_LAUNCHED(e);
     TAFL_SPEC_DISPATCH(e, (k_mcts_results<BB, SP><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->r_moves, m->r_visits, m->r_q,
                                                                                         m->r_counts, m->r_best)));

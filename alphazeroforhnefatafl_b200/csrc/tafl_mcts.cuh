@@ -130,6 +130,63 @@ __device__ __forceinline__ tafl_move warp_decode_edge(const Ctx<BB, SP>& cx, con
     return m;
 }
 
+// ---------------------------------------------------------------------------------------------
+// The same cooperative helpers for a GROUP of G lanes (G = 32, 16, 8) owning one tree, so that one
+// warp can carry 32/G trees: `gmask` = the group's lanes, `gl` = lane index inside the group.
+// ---------------------------------------------------------------------------------------------
+template <int G> __device__ __forceinline__ unsigned grp_ballot(unsigned gmask, int gshift, bool pred) {
+    const unsigned b = __ballot_sync(gmask, pred) >> gshift;
+    return G == 32 ? b : (b & ((1u << (G & 31)) - 1u));
+}
+template <int G, class BB, int SP>
+__device__ __forceinline__ int grp_build_ptab(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side, uint32_t* __restrict__ ptab,
+                                              unsigned gmask, int gl, int* n_pieces_out) {
+    const BB own = p.side(def_side), occ = p.occ();
+    const int n_pieces = own.popc();
+    *n_pieces_out = n_pieces;
+    int total = 0;
+    for (int base = 0; base < n_pieces && base < MCTS_PT_MAX; base += G) {
+        const int idx = base + gl;
+        uint32_t e = 0;
+        if (idx < n_pieces && idx < MCTS_PT_MAX) {
+            const int s = nth_set_bit(own, idx);
+            const int row = s / BB::STRIDE, col = s - row * BB::STRIDE;
+            const bool is_king = def_side && BB::bit(s) == p.kbit;
+            e = pt_pack(s, is_king, piece_rays(cx, occ, is_king ? KIND_K : (def_side ? KIND_DS : KIND_AS), row, col));
+            ptab[idx] = e;
+        }
+        total += (int)__reduce_add_sync(gmask, (unsigned)pt_total(e));
+    }
+    return total;
+}
+template <int G, class BB, int SP>
+__device__ __forceinline__ tafl_move grp_decode_edge(const Ctx<BB, SP>& cx, const uint32_t* __restrict__ ptab, int n_pieces,
+                                                     int def_side, int a, unsigned gmask, int gshift, int gl) {
+    int before = 0;
+    tafl_move m = 0;
+    for (int base = 0; base < n_pieces; base += G) {
+        const int idx = base + gl;
+        const uint32_t e = idx < n_pieces ? ptab[idx] : 0u;
+        const int c = pt_total(e);
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) {
+            const int t = __shfl_up_sync(gmask, incl, o, G);
+            if (gl >= o) incl += t;
+        }
+        const unsigned owns = grp_ballot<G>(gmask, gshift, a < before + incl);
+        if (owns) {   // the first lane whose running total exceeds a holds the piece
+            const int src = __ffs(owns) - 1;
+            const uint32_t es = __shfl_sync(gmask, e, src, G);
+            const int excl = __shfl_sync(gmask, before + incl - c, src, G);
+            m = pt_decode(cx, es, def_side, a - excl);
+            break;
+        }
+        before += __shfl_sync(gmask, incl, G - 1, G);
+    }
+    return m;
+}
+
 #endif  // __CUDACC__
 
 }  // namespace tafl

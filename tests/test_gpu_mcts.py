@@ -149,3 +149,33 @@ def test_gpu_selfplay_episode_vs_oracle(orc, built_lib):
             all_recs.append(recs)
         z = SP.backfill_outcomes(np.concatenate(all_recs))
         assert z.shape[0] == sum(len(r) for r in all_recs)
+
+
+def test_gpu_mcts_group_sizes_are_bit_identical(orc, built_lib, monkeypatch):
+    """k_mcts_sims_g with 32 / 16 / 8 lanes per tree (2 / 4 trees per warp, converged create + expand)
+    == the first-generation warp-per-tree kernel (TAFL_MCTS_G=0) == the oracle, incl. tree reuse over
+    several moves, trees that are not a multiple of the trees-per-CTA, and the capacity error"""
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    roots = sample_positions(orc, rules, fen, 128, 203, seed=61, max_steps=220)     # 203: ragged last CTA
+    sims, n_moves = 150, 4
+    exp = orc.mcts_episode(rules, 128, roots, sims, n_moves, True, n_threads=8)
+    for G in ("0", "32", "16", "8"):
+        monkeypatch.setenv("TAFL_MCTS_G", G)
+        with E.LockstepGames(rules, fen, len(roots), 0, 128) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, 1.0, 1e-4, tree_reuse=True)
+            for j in range(n_moves):
+                g.mcts_search()
+                r = g.mcts_results()
+                assert np.array_equal(r["counts"], exp["counts"][:, j]), (G, j)
+                assert np.array_equal(r["visits"], exp["visits"][:, j]), (G, j)
+                assert r["q"].tobytes() == exp["q"][:, j].tobytes(), (G, j)
+                g.mcts_advance()
+            assert g.get_states().tobytes() == exp["final"].tobytes()
+            st = g.mcts_stats().as_dict()
+            for k in ("sims", "nodes", "edges", "terminal_hits", "depth_sum"):
+                assert st[k] == getattr(exp["stats"], k), (G, k)
+        with E.LockstepGames(rules, fen, 5, 0, 128) as g:      # edge pool too small -> TAFL_ERR_CAPACITY
+            g.mcts_configure(64, 1.0, 1e-4, edge_capacity=500)
+            with pytest.raises(TaflError):
+                g.mcts_search()
