@@ -433,6 +433,44 @@ TAFL_HD bool side_can_play(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side
 
 // ---------------------------------------------------------------------------------------------
 // Captures
+// the tile-by-tile walk of dir_sw_search (logic.rs:471-530), reached only through the pre-filter
+template <class BB, int SP>
+TAFL_COLD bool shieldwall_walk(const Ctx<BB, SP>& cx, const Pos<BB>& p, int mover_def, int to_r, int to_c, int horizontal, int away,
+                               BB* caps) {
+    const int N = cx.n();
+    const BB own = p.side(mover_def), opp = p.side(!mover_def), occ = p.occ();
+    const bool cmc = cx.r_sw_corners_may_close() != 0;
+    BB wall = BB::zero();
+    bool found = false;
+    for (int dd = 0; dd < 2 && !found; ++dd) {
+        const int dir = dd == 0 ? -1 : 1;
+        wall = BB::zero();
+        int cnt = 0, r = to_r, c = to_c;
+        for (int it = 0; it < 12; ++it) {
+            if (horizontal) c += dir; else r += dir;
+            if (r < 0 || c < 0 || r >= N || c >= N) break;  // ran off the board: None
+            BB tb = BB::bit(idx_of<BB>(r, c));
+            bool is_occ = (occ & tb).any(), is_corner = (cx.corners & tb).any();
+            if (!(is_occ || (cmc && is_corner))) break;
+            if (!is_occ) { found = cnt >= 2; break; }  // empty closing corner
+            if ((opp & tb).any()) {
+                int pr = horizontal ? r + away : r, pc = horizontal ? c : c + away;
+                BB pin = BB::bit(idx_of<BB>(pr, pc));
+                if ((own & pin).any()) { wall = wall | tb; ++cnt; }
+                else break;  // not pinned by a piece of the mover
+            }
+            if ((own & tb).any() || (is_corner && cmc)) { found = cnt >= 2; break; }
+        }
+    }
+    if (!found) return false;
+    BB keep = BB::zero();
+    const int osk = mover_def ? KIND_AS : KIND_DS;
+    if (cx.f_sw_caps(osk)) keep = keep | ~p.kbit;
+    if (cx.f_sw_caps(KIND_K)) keep = keep | p.kbit;
+    *caps = wall & keep;
+    return true;
+}
+
 // ---------------------------------------------------------------------------------------------
 // detect_shieldwall (logic.rs:535-569) + dir_sw_search (logic.rs:471-530).
 // `mover_def` is state.side_to_play.  Returns true for Some(..) and the captured tiles in *caps.
@@ -464,36 +502,7 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
         const bool plus = (pinned & p1).any() && (pinned & p2).any();
         if (!(minus || plus)) return false;
     }
-    const bool cmc = cx.r_sw_corners_may_close() != 0;
-    BB wall = BB::zero();
-    bool found = false;
-    for (int dd = 0; dd < 2 && !found; ++dd) {
-        const int dir = dd == 0 ? -1 : 1;
-        wall = BB::zero();
-        int cnt = 0, r = to_r, c = to_c;
-        for (int it = 0; it < 12; ++it) {
-            if (horizontal) c += dir; else r += dir;
-            if (r < 0 || c < 0 || r >= N || c >= N) break;  // ran off the board: None
-            BB tb = BB::bit(idx_of<BB>(r, c));
-            bool is_occ = (occ & tb).any(), is_corner = (cx.corners & tb).any();
-            if (!(is_occ || (cmc && is_corner))) break;
-            if (!is_occ) { found = cnt >= 2; break; }  // empty closing corner
-            if ((opp & tb).any()) {
-                int pr = horizontal ? r + away : r, pc = horizontal ? c : c + away;
-                BB pin = BB::bit(idx_of<BB>(pr, pc));
-                if ((own & pin).any()) { wall = wall | tb; ++cnt; }
-                else break;  // not pinned by a piece of the mover
-            }
-            if ((own & tb).any() || (is_corner && cmc)) { found = cnt >= 2; break; }
-        }
-    }
-    if (!found) return false;
-    BB keep = BB::zero();
-    const int osk = mover_def ? KIND_AS : KIND_DS;
-    if (cx.f_sw_caps(osk)) keep = keep | ~p.kbit;
-    if (cx.f_sw_caps(KIND_K)) keep = keep | p.kbit;
-    *caps = wall & keep;
-    return true;
+    return shieldwall_walk(cx, p, mover_def, to_r, to_c, horizontal, away, caps);
 }
 
 // get_captures (logic.rs:604-699) on the post-move board.  piece_def / piece_kind describe the
@@ -674,6 +683,21 @@ TAFL_HD bool enclosure_secure(const Ctx<BB, SP>& cx, const Pos<BB>& p, const Enc
     }
     return ok;
 }
+// The full tests behind the cheap pre-filters are rare (a sealed position, a king on the edge inside
+// a defender fort): out of line, so that the per-ply instruction stream stays short and i-cache resident.
+template <class BB, int SP>
+TAFL_COLD bool enclosure_win_full(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
+    const bool woe = cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS;
+    Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.def, p.att, woe, true);
+    return e.found && (e.region & p.occ()).popc() == p.def.popc() && enclosure_secure(cx, p, e, false, true);
+}
+template <class BB, int SP>
+TAFL_COLD bool exit_fort_full(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
+    Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.king(), p.dsold(), false, true);
+    if (!e.found) return false;
+    return enclosure_secure(cx, p, e, true, false);
+}
+
 // detect_exit_fort (logic.rs:572-601)
 template <class BB, int SP>
 TAFL_HD bool detect_exit_fort(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
@@ -681,10 +705,10 @@ TAFL_HD bool detect_exit_fort(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
     if (!(p.kr == 0 || p.kr == N - 1 || p.kc == 0 || p.kc == N - 1)) return false;
     if (!p.kbit.any()) return false;
     // enclosed = PieceSet::from(King), enclosing = PieceSet::from(Defender); attackers are "neither"
-    Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.king(), p.dsold(), false, true);
-    if (!e.found) return false;
+    // find_enclosure -> king has an empty neighbour -> enclosure_secure (logic.rs:580-600); the empty-
+    // neighbour test has no side effects, so it is taken first and the fill runs out of line
     if (!(dilate4(cx, p.kbit) & ~p.occ()).any()) return false;
-    return enclosure_secure(cx, p, e, true, false);
+    return exit_fort_full(cx, p);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -740,9 +764,7 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const tafl
             done = true;
         } else if (cx.r_enclosure_win() != TAFL_ENCL_NONE &&
                    enclosure_win_possible(cx, p, cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS)) {
-            Encl<BB> e = find_enclosure(cx, p, p.kr, p.kc, p.def, p.att,
-                                        cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS, true);
-            if (e.found && (e.region & p.occ()).popc() == p.def.popc() && enclosure_secure(cx, p, e, false, true)) {
+            if (enclosure_win_full(cx, p)) {
                 st = TAFL_STATUS_WIN(TAFL_WIN_ENCLOSED, 0);
                 done = true;
             }

@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstring>
 
+#define TAFL_OUTLINE_RARE 1
 #include "tafl_engine.hpp"
 #include "tafl_mcts.cuh"
 #include "tafl_select.cuh"
