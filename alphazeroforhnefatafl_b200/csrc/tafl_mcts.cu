@@ -38,6 +38,8 @@ struct MctsPools {
     uint64_t rg_seed = 0;
     uint32_t rg_sims = 0;
     double rg_cpuct = 0, rg_draw = 0;
+    int tree_mode = 0;                // 0: every edge of an expanded node is initialised (k_mcts_sims, evaluator hook);
+                                      // 1: k_mcts_sims_g trees, edges written lazily up to index Ns (uniform-prior prefix)
     int phase = 0;                    // 0 idle, 1 begun / expanded, 2 leaves selected (evaluation pending)
     uint32_t rounds = 0;              // simulations run since tafl_mcts_begin
 };
@@ -246,11 +248,15 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
 // load round trip through its header and state).  Results are bit-identical to k_mcts_sims.
 // ---------------------------------------------------------------------------------------------
 template <int G>
-__device__ __forceinline__ void grp_puct_select(const MctsEdge* __restrict__ ed, uint32_t L, uint32_t Ns, double cpuct, unsigned gmask,
+__device__ __forceinline__ void grp_puct_select(const MctsEdge* __restrict__ ed, uint32_t Lall, uint32_t Ns, double cpuct, unsigned gmask,
                                                 int gl, uint32_t& out_a, uint32_t& out_N, uint32_t& out_child) {
     const double sq_vis = sqrt((double)Ns), sq_new = sqrt((double)Ns + MCTS_EPS);
-    const double c_uni = cpuct * (1.0 / (double)L);
+    const double c_uni = cpuct * (1.0 / (double)Lall);
     const double t_vis = c_uni * sq_vis, u_new = c_uni * sq_new;
+    // Under uniform priors every unvisited edge has the same u, and the first maximum takes the
+    // lowest index: edges are opened in index order, the visited ones are a prefix of length
+    // k <= Ns.  Edges behind index Ns cannot win against edge k, so only [0, min(L, Ns + 1)) is read.
+    const uint32_t L = Lall < Ns + 1u ? Lall : Ns + 1u;
     double best_u = -INFINITY;
     uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
     for (uint32_t a0 = gl; a0 < L; a0 += 4 * G) {
@@ -300,6 +306,13 @@ __device__ __forceinline__ void grp_backup(uint4* __restrict__ n_hdr, MctsEdge* 
             ep->N = e.N + 1u;
             ph.y += 1u;
             n_hdr[parent] = ph;
+            // edges are zeroed lazily: select reads [0, min(L, Ns + 1)), so edge index Ns becomes
+            // readable now (it is unvisited: the visited prefix is never longer than Ns)
+            if (ph.y < hdr_n_edges(ph.w)) {
+                MctsEdge z;
+                z.Q = 0.0; z.N = 0u; z.child = 0u;
+                edges[ph.x + ph.y] = z;
+            }
         }
         __syncwarp(gmask);
         v = -v;
@@ -394,10 +407,12 @@ k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tr
                     overflow = true;
                     if (mode == M_CREATE && gl == 0) n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack(0, pedge, 0, es));
                 } else {
-                    MctsEdge z;
-                    z.Q = 0.0; z.N = 0u; z.child = 0u;
-                    for (int a = gl; a < L; a += G) edges[n_edges_used + a] = z;
-                    if (gl == 0) n_hdr[target] = make_uint4(n_edges_used, 0u, parent, hdr_pack((uint32_t)L, pedge, 1u, es, (uint32_t)n_pieces));
+                    if (gl == 0) {
+                        MctsEdge z;
+                        z.Q = 0.0; z.N = 0u; z.child = 0u;
+                        if (L > 0) edges[n_edges_used] = z;   // Ns = 0: edge 0 is the only readable one (see grp_backup)
+                        n_hdr[target] = make_uint4(n_edges_used, 0u, parent, hdr_pack((uint32_t)L, pedge, 1u, es, (uint32_t)n_pieces));
+                    }
                     n_edges_used += (uint32_t)L;
                     c_edges += (unsigned long long)L;
                     c_depth += depth;
@@ -431,7 +446,7 @@ template <class BB, int SP>
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
 k_mcts_results(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, tafl_move* __restrict__ r_moves,
                uint32_t* __restrict__ r_visits, double* __restrict__ r_q, uint32_t* __restrict__ r_counts,
-               uint32_t* __restrict__ r_best) {
+               uint32_t* __restrict__ r_best, int prefix) {
     const int lane = threadIdx.x & 31;
     const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
     if (tree >= n_trees) return;
@@ -457,7 +472,7 @@ k_mcts_results(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_t
                 const tafl_move mm = warp_decode_edge(cx, ptab, n_pieces, def_side, aa, lane);
                 if (src == lane) m = mm;
             }
-            if (a < L) {
+            if (a < L && (!prefix || a <= h.y)) {   // prefix trees: edges behind index Ns were never written
                 const MctsEdge e = edges[a];
                 N = e.N;
                 if (N > 0) q = e.Q;
@@ -579,7 +594,7 @@ k_mcts_policy(MctsView mv, uint32_t n_trees, uint64_t gid_base, const uint32_t* 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
 k_mcts_reroot(MctsView mv, uint32_t n_trees, const uint32_t* __restrict__ r_counts, const uint32_t* __restrict__ r_best,
-              uint32_t* __restrict__ remap_all) {
+              uint32_t* __restrict__ remap_all, int prefix) {
     const int lane = threadIdx.x & 31;
     const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
     if (tree >= n_trees) return;
@@ -640,17 +655,18 @@ k_mcts_reroot(MctsView mv, uint32_t n_trees, const uint32_t* __restrict__ r_coun
             n_ptab[(size_t)j * MCTS_PT_MAX + 32 + lane] = w1;
             if (lane == 0) store_state(n_state + j, s);
         }
-        for (uint32_t off = 0; off < L; off += 32) {
+        const uint32_t Lc = (prefix && h.y + 1u < L) ? h.y + 1u : L;   // prefix trees: only [0, Ns] was ever written
+        for (uint32_t off = 0; off < Lc; off += 32) {
             const uint32_t a = off + lane;
             MctsEdge e;
             double p = 0.0;
-            if (a < L) {
+            if (a < Lc) {
                 e = edges[old_base + a];
                 if (prior) p = prior[old_base + a];
                 e.child = e.N > 0 ? remap[e.child] : 0u;
             }
             __syncwarp();
-            if (a < L) {
+            if (a < Lc) {
                 edges[e_used + a] = e;
                 if (prior) prior[e_used + a] = p;
             }
@@ -1017,8 +1033,11 @@ void mcts_free(tafl_engine* e) {
     } while (0)
 
 // fresh trees, or (tree reuse) carried trees whose root still is the game's state
-static void launch_tree_init(tafl_engine* e) {
+static void launch_tree_init(tafl_engine* e, int tree_mode) {
     MctsPools* m = e->mcts;
+    if ((m->cfg.flags & TAFL_MCTS_TREE_REUSE) && m->tree_mode != tree_mode)   // a carried tree of the other layout is dropped
+        cudaMemsetAsync(m->v.t_nodes, 0, (size_t)e->n_games * sizeof(uint32_t), e->stream);
+    m->tree_mode = tree_mode;
     if (m->cfg.flags & TAFL_MCTS_TREE_REUSE)
         k_mcts_init_carry<<<grid_for(e->n_games, 128), 128, 0, e->stream>>>(e->d_states, e->n_games, m->v);
     else
@@ -1092,7 +1111,7 @@ int tafl_mcts_search_async(tafl_engine* e) {
     cudaSetDevice(e->device);
     MctsPools* m = e->mcts;
     const uint32_t n = e->n_games;
-    launch_tree_init(e);
+    launch_tree_init(e, e->mcts_group == 32 || e->mcts_group == 16 || e->mcts_group == 8 ? 1 : 0);
     MCTS_LAUNCHED(e);
     const unsigned grid = grid_for(n, MCTS_WARPS);
 #define TAFL_MCTS_LAUNCH(MINB)                                                                                          \
@@ -1120,7 +1139,7 @@ int tafl_mcts_search_async(tafl_engine* e) {
 #undef TAFL_MCTS_LAUNCH_G
     MCTS_LAUNCHED(e);
     TAFL_SPEC_DISPATCH(e, (k_mcts_results<BB, SP><<<grid, MCTS_WARPS * 32, 0, e->stream>>>(cx, m->v, n, m->r_moves, m->r_visits, m->r_q,
-                                                                                        m->r_counts, m->r_best)));
+                                                                                        m->r_counts, m->r_best, m->tree_mode)));
     MCTS_LAUNCHED(e);
     m->searched = true;
     return TAFL_OK;
@@ -1194,7 +1213,7 @@ int tafl_mcts_reroot(tafl_engine* e) {
     if (!m->searched) { e->err = "tafl_mcts_reroot: no search results to re-root at"; return TAFL_ERR_INVALID_ARG; }
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    k_mcts_reroot<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->r_counts, m->r_best, m->remap);
+    k_mcts_reroot<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->r_counts, m->r_best, m->remap, m->tree_mode);
     MCTS_LAUNCHED(e);
     m->searched = false;   // the root results describe the previous root
     return TAFL_OK;
@@ -1307,7 +1326,7 @@ int tafl_mcts_begin(tafl_engine* e) {
     rc = eval_alloc(e);
     if (rc) return rc;
     MctsPools* m = e->mcts;
-    launch_tree_init(e);
+    launch_tree_init(e, 0);
     MCTS_LAUNCHED(e);
     m->phase = 1;
     m->rounds = 0;
@@ -1354,7 +1373,7 @@ int tafl_mcts_finish(tafl_engine* e) {
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
     TAFL_SPEC_DISPATCH(e, (k_mcts_results<BB, SP><<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(
-                              cx, m->v, n, m->r_moves, m->r_visits, m->r_q, m->r_counts, m->r_best)));
+                              cx, m->v, n, m->r_moves, m->r_visits, m->r_q, m->r_counts, m->r_best, m->tree_mode)));
     MCTS_LAUNCHED(e);
     m->searched = true;
     m->phase = 0;

@@ -179,3 +179,26 @@ def test_gpu_mcts_group_sizes_are_bit_identical(orc, built_lib, monkeypatch):
             g.mcts_configure(64, 1.0, 1e-4, edge_capacity=500)
             with pytest.raises(TaflError):
                 g.mcts_search()
+
+
+def test_gpu_tree_reuse_dropped_when_the_search_kind_changes(orc, built_lib):
+    """k_mcts_sims_g writes a node's edges lazily (only [0, Ns] is ever read under uniform priors); the
+    evaluator-hook kernels need every edge initialised.  A carried tree of the other kind is dropped."""
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
+    roots = sample_positions(orc, rules, fen, 64, 48, seed=71, max_steps=60)
+    with E.LockstepGames(rules, fen, len(roots), 0, 64) as g:
+        g.set_states(roots)
+        g.mcts_configure(120, 1.0, 1e-4, tree_reuse=True)
+        g.mcts_search()
+        g.mcts_advance()
+        after = g.get_states()
+        g.mcts_search_builtin(A.EVAL_STUB)          # other kind: fresh trees
+        got = g.mcts_results()
+        exp = orc.mcts_search(rules, 64, after, 120)
+        assert np.array_equal(got["visits"], exp["visits"]) and got["q"].tobytes() == exp["q"].tobytes()
+        g.mcts_advance()
+        after2 = g.get_states()
+        g.mcts_search()                              # and back
+        got = g.mcts_results()
+        exp = orc.mcts_search(rules, 64, after2, 120)
+        assert np.array_equal(got["visits"], exp["visits"]) and got["q"].tobytes() == exp["q"].tobytes()
