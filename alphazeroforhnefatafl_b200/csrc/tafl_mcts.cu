@@ -359,6 +359,15 @@ k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tr
                 if (!hdr_expanded(h.w)) { mode = M_EXPAND; break; }   // the root of a fresh tree
                 const uint32_t L = hdr_n_edges(h.w);
                 if (L == 0) { v = 0.0; mode = M_BACKUP; break; }
+                // the node's state and piece table are needed only if the selected edge is new — most
+                // simulations end that way one or two levels down — so they are prefetched into L1 here,
+                // under the edge loads and the PUCT arithmetic (registers are at the 128 cap that keeps
+                // all 2048 warps resident; a register prefetch cost a second wave)
+                if (gl < 3) {   // one 64-byte state line, two 128-byte piece-table lines
+                    const void* pf = gl == 0 ? (const void*)(n_state + node)
+                                             : (const void*)(n_ptab + (size_t)node * MCTS_PT_MAX + (gl - 1) * 32);
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+                }
                 uint32_t a, bN, bchild;
                 grp_puct_select<G>(edges + h.x, L, h.y, cpuct, gmask, gl, a, bN, bchild);
                 if (bN == 0) { mode = M_CREATE; sel_a = a; sel_base = h.x; break; }
