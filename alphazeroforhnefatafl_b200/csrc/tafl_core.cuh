@@ -286,15 +286,26 @@ template <class BB, int SP>
 TAFL_HD uint32_t extract_row(const Ctx<BB, SP>& cx, BB x, int row) {
     return x.extract32(row * BB::STRIDE) & ((1u << cx.n()) - 1u);
 }
+// Column gather by multiplication: after the shift the column's bits sit at multiples of STRIDE; the
+// multiplier sum_i 2^(T - (STRIDE-1) i) moves bit STRIDE*i to T + i, and no two partial products land
+// on the same bit (STRIDE (i-i') = (STRIDE-1)(j-j') has no solution inside one word), so there are no
+// carries.  The 64-bit multiplies run on the FMA pipe, which this integer code leaves idle.
+TAFL_HD uint32_t gather_col(BB64 t) {
+    constexpr uint64_t M = (1ull << 0) | (1ull << 7) | (1ull << 14) | (1ull << 21) | (1ull << 28) | (1ull << 35) | (1ull << 42);
+    constexpr uint64_t K = (1ull << 57) | (1ull << 51) | (1ull << 45) | (1ull << 39) | (1ull << 33) | (1ull << 27) | (1ull << 21);
+    return (uint32_t)(((t.v & M) * K) >> 57);
+}
+TAFL_HD uint32_t gather_col(BB128 t) {
+    constexpr uint64_t M6 = (1ull << 0) | (1ull << 11) | (1ull << 22) | (1ull << 33) | (1ull << 44) | (1ull << 55);
+    constexpr uint64_t M5 = (1ull << 0) | (1ull << 11) | (1ull << 22) | (1ull << 33) | (1ull << 44);
+    constexpr uint64_t K = (1ull << 58) | (1ull << 48) | (1ull << 38) | (1ull << 28) | (1ull << 18) | (1ull << 8);
+    const uint32_t lo = (uint32_t)(((t.lo & M6) * K) >> 58);            // rows 0..5: bits 0, 11, .., 55
+    const uint32_t hi = (uint32_t)((((t.hi >> 2) & M5) * K) >> 58);     // rows 6..10: bits 66, 77, .., 110
+    return lo | (hi << 6);
+}
 template <class BB, int SP>
 TAFL_HD uint32_t extract_col(const Ctx<BB, SP>& cx, BB x, int col) {
-    BB t = x.shrv(col);
-    uint32_t out = 0;
-#pragma unroll
-    for (int i = 0; i < 11; ++i) {
-        if (i < cx.n()) out |= (uint32_t)t.test(i * BB::STRIDE) << i;
-    }
-    return out;
+    return gather_col(x.shrv(col)) & ((1u << cx.n()) - 1u);
 }
 
 struct Rays {

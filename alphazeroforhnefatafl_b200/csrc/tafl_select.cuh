@@ -169,9 +169,20 @@ TAFL_HD tafl_move select_move(const Ctx<BB, SP>& cx, const Pos<BB>& p, const Mov
     for (int d = 0; d < 3; ++d) {
         if (dir == d && kk >= (uint32_t)r.cnt[d]) { kk -= r.cnt[d]; dir = d + 1; }
     }
-    const uint32_t m = dir == 0 ? r.m[0] : dir == 1 ? r.m[1] : dir == 2 ? r.m[2] : r.m[3];
-    const int pos = ray_nth(m, dir, (int)kk);
-    const int to = dir < 2 ? idx_of<BB>(pos, col) : idx_of<BB>(row, pos);
+    // the destinations of a ray are consecutive tiles from the piece outward, except for the one hole
+    // at the throne a non-king slides across (play.rs:208-211): position by arithmetic, as pt_decode
+    const bool vertical = dir < 2;
+    const int pp = vertical ? row : col, line = vertical ? col : row, mid = cx.m();
+    const bool hole = cx.f_noentry(kind) && line == mid;
+    int pos;
+    if ((dir & 1) == 0) {
+        pos = pp + 1 + (int)kk;
+        if (hole && pp < mid && pos >= mid) ++pos;
+    } else {
+        pos = pp - 1 - (int)kk;
+        if (hole && pp > mid && pos <= mid) --pos;
+    }
+    const int to = vertical ? idx_of<BB>(pos, col) : idx_of<BB>(row, pos);
     return (tafl_move)(s | (to << 7));
 }
 
