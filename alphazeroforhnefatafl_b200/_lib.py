@@ -102,6 +102,10 @@ def lib():
         "tafl_undo_last_play": (C.c_int, [vp, vp]),
         "tafl_history_len": (C.c_int, [vp, vp]),
         "tafl_play_history": (C.c_int, [vp, C.c_uint32, vp, C.c_uint32, C.POINTER(C.c_uint32)]),
+        "tafl_nccl_unique_id": (C.c_int, [vp]),
+        "tafl_nccl_comm_create": (C.c_int, [vp, vp, C.c_int, C.c_int, C.POINTER(vp)]),
+        "tafl_nccl_comm_destroy": (C.c_int, [vp]),
+        "tafl_gather_records": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, C.c_uint32, vp, C.c_uint64, vp]),
         "tafl_mcts_configure": (C.c_int, [vp, C.POINTER(A.MctsConfig)]),
         "tafl_mcts_search": (C.c_int, [vp]),
         "tafl_mcts_search_async": (C.c_int, [vp]),

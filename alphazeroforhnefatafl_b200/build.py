@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 LIB = os.path.join(HERE, "libtafl_b200.so")
-SOURCES = ["tafl_engine.cu", "tafl_mcts.cu", "tafl_host.cpp"]
+SOURCES = ["tafl_engine.cu", "tafl_mcts.cu", "tafl_comm.cu", "tafl_host.cpp"]
 HEADERS = ["tafl_bb.cuh", "tafl_core.cuh", "tafl_select.cuh", "tafl_ctx.hpp", "tafl_engine.hpp",
            "tafl_warp.cuh", "tafl_mcts.cuh"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -48,7 +48,7 @@ def build(force=False, verbose=False):
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs
+    cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))

@@ -53,6 +53,55 @@ def gather_records(local, dst=0, group=None):
     return None
 
 
+class NcclGather:
+    """The same gather through the C ABI alone (``tafl_gather_records``: NCCL resolved with dlopen,
+    counts all-gathered, rows sent straight to their offset on the root) — what a host without
+    PyTorch binds.  ``uid`` is the 128-byte ncclUniqueId made on rank 0 (``NcclGather.unique_id()``)
+    and shipped to the other ranks by any means."""
+
+    def __init__(self, games, uid, n_ranks, rank, root=0):
+        import ctypes as C
+        from ._lib import lib
+        self.g, self.n_ranks, self.rank, self.root = games, n_ranks, rank, root
+        self.comm = C.c_void_p()
+        buf = (C.c_char * 128).from_buffer_copy(bytes(uid))
+        games._ck(lib().tafl_nccl_comm_create(games._h, buf, n_ranks, rank, C.byref(self.comm)))
+
+    @staticmethod
+    def unique_id():
+        import ctypes as C
+        from ._lib import lib
+        buf = (C.c_char * 128)()
+        rc = lib().tafl_nccl_unique_id(buf)
+        if rc != 0:
+            raise RuntimeError("tafl_nccl_unique_id failed (%d): is libnccl.so.2 loadable?" % rc)
+        return bytes(buf)
+
+    def gather(self, local, recv=None):
+        """local: [n_local, REC_STRIDE] uint8 CUDA tensor; returns (rows tensor on the root / None, counts).
+        recv (root): [capacity, REC_STRIDE] uint8 CUDA tensor; default capacity = n_games * n_ranks rows,
+        pass a larger one when the shards are ragged."""
+        from ._lib import lib
+        assert local.dtype == torch.uint8 and local.dim() == 2 and local.shape[1] == A.REC_STRIDE and local.is_contiguous()
+        counts = np.zeros(self.n_ranks, np.uint32)
+        cap = 0
+        if self.rank == self.root:
+            if recv is None:
+                recv = torch.empty((self.g.n_games * self.n_ranks, A.REC_STRIDE), dtype=torch.uint8, device=local.device)
+            cap = recv.shape[0]
+        self.g._ck(lib().tafl_gather_records(self.g._h, self.comm, self.n_ranks, self.rank, self.root,
+                                             local.data_ptr() if local.shape[0] else None, local.shape[0],
+                                             recv.data_ptr() if recv is not None else None, cap, A.ptr(counts)))
+        self.g.sync()
+        return (recv[:int(counts.sum())] if self.rank == self.root else None), counts
+
+    def close(self):
+        from ._lib import lib
+        if self.comm:
+            lib().tafl_nccl_comm_destroy(self.comm)
+            self.comm = None
+
+
 def records_to_numpy(t):
     """[n, REC_STRIDE] uint8 tensor -> structured REC_DTYPE array (host)."""
     return np.ascontiguousarray(t.cpu().numpy()).view(REC_DTYPE).reshape(-1)

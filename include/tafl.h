@@ -553,6 +553,29 @@ typedef struct {
 #define TAFL_REC_STRIDE (56 + 2 * TAFL_REC_MOVES + 4 * TAFL_REC_MOVES)
 int tafl_pack_records(tafl_engine* e, void* d_out /* [n_games][TAFL_REC_STRIDE] */);
 
+
+/* ------------------------------------------------------------------------------------------
+ * Multi-GPU: games shard by id range, one process per GPU, and the ONLY
+ * exchange is the gather of the replay records to the replay-buffer rank — the batched
+ * counterpart of write_to_file collecting positions (game/main.rs:86-132).  NCCL is resolved
+ * at run time (dlopen of libnccl.so.2, a copy already in the process wins; TAFL_NCCL_LIB
+ * overrides), ncclUniqueId / ncclComm_t cross this ABI as 128 opaque bytes / a void*.
+ *   rank 0: tafl_nccl_unique_id(id); ship the 128 bytes to the other ranks by any means;
+ *   all   : tafl_nccl_comm_create(e, id, n_ranks, rank, &comm);
+ *   per move: tafl_pack_records(e, d_rows); tafl_gather_records(e, comm, n_ranks, rank, root,
+ *             d_rows, n_local, d_all, capacity_rows, h_counts).
+ * Ranks may hold different numbers of rows: the counts are all-gathered into h_counts
+ * [n_ranks] (HOST, valid on every rank), the rows then move with grouped ncclSend/ncclRecv to
+ * their final offset in d_all on the root, rank order == game-id order.  Work is enqueued on
+ * the engine's stream; the root's rows are complete after tafl_engine_sync. */
+int tafl_nccl_unique_id(void* out128);
+int tafl_nccl_comm_create(tafl_engine* e, const void* id128, int n_ranks, int rank, void** out_comm);
+int tafl_nccl_comm_destroy(void* comm);
+int tafl_gather_records(tafl_engine* e, void* comm, int n_ranks, int rank, int root,
+                        const void* d_send /* [n_local][TAFL_REC_STRIDE] */, uint32_t n_local,
+                        void* d_recv /* root only: [recv_capacity_rows][TAFL_REC_STRIDE] */,
+                        uint64_t recv_capacity_rows, uint32_t* h_counts /* [n_ranks] */);
+
 #ifdef __cplusplus
 }
 #endif

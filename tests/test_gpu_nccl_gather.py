@@ -1,0 +1,36 @@
+"""tafl_gather_records (C ABI, NCCL by dlopen): a one-rank communicator inside pytest (the GPU test box has
+one GPU); the N-rank check is scripts/nccl_gather_check.py under torchrun (gpurun --gpus 2), which
+compares the C-ABI gather with the torch.distributed gather row for row."""
+import numpy as np
+import pytest
+
+from alphazeroforhnefatafl_b200 import _abi as A
+
+pytestmark = pytest.mark.gpu
+
+
+def test_single_rank_gather(orc, built_lib):
+    import torch
+    from alphazeroforhnefatafl_b200 import engine as E
+    from alphazeroforhnefatafl_b200 import selfplay as SP
+    from parity_cases import board_for
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), board_for(orc, A.PRESET_BRANDUBH)
+    n = 24
+    with E.LockstepGames(rules, fen, n, 0, 64) as g:
+        g.set_game_id_base(700)
+        sp = SP.SelfPlay(g, num_sims=60)
+        rows = sp.move(gather=False)
+        torch.cuda.synchronize()
+        ng = SP.NcclGather(g, SP.NcclGather.unique_id(), 1, 0)
+        try:
+            got, counts = ng.gather(rows.contiguous())
+            assert list(counts) == [rows.shape[0]]
+            assert torch.equal(got.cpu(), rows.cpu())
+            recs = SP.records_to_numpy(got)
+            assert list(recs["h"]["game_id"]) == list(range(700, 700 + n))
+            empty, counts = ng.gather(rows[:0].contiguous())          # a rank may have nothing to send
+            assert list(counts) == [0] and empty.shape[0] == 0
+            with pytest.raises(E.TaflError):                           # root buffer too small
+                ng.gather(rows.contiguous(), recv=torch.empty((3, A.REC_STRIDE), dtype=torch.uint8, device="cuda"))
+        finally:
+            ng.close()
