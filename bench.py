@@ -108,7 +108,7 @@ def run_reference(args):
     el = time.perf_counter() - t0
     v = total / el
     sample = "%d games x %d plies per step (sample of the 65536-game workload), %d threads" % (games, plies, cores)
-    print(json.dumps({
+    _emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * el / max(1, args.steps), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u128 bitboards (2 x u64)", "data": "synthetic",
@@ -333,7 +333,7 @@ def run_b200(args):
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
     g.close()
     if rank == 0:
-        print(json.dumps(out))
+        _emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
@@ -428,8 +428,18 @@ def _mcts_variant(args, E, SP, rank, local, torch, moves, **kw):
         g.close()
 
 
+def _emit(line):
+    """the ONE JSON line, on the process's real stdout"""
+    os.write(_REAL_STDOUT, (line + "\n").encode())
+
+
 if __name__ == "__main__":
     a = parse()
+    # Libraries write to fd 1 behind Python's back (NCCL prints its version banner there when NCCL_DEBUG
+    # is set in the environment): everything but the JSON line goes to stderr.
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:
