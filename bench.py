@@ -309,6 +309,7 @@ def run_b200(args):
                    "sharding": "game-id ranges, no data-path collective", "mean_legal_moves": mean_legal},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                      "traffic": ncu_traffic(), "peak_source": peak_src, "kernel": "k_step_random<BB128>",
+                     "binding_limit": ncu_binding_limit(),
                      "kernel_us": kernel_us, "bytes_per_env_step": ENV_BYTES_PER_STEP,
                      "note": "integer-issue bound, not HBM bound: see profiles/ for issue-slot utilisation"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 4, "d2h_bytes_per_step": n * 2,
@@ -338,15 +339,31 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def ncu_traffic():
+def ncu_summary(kernel="k_step_random"):
+    """the committed ncu --set full summary of the kernel (profiles/ncu_summary.json, written by profiles/ncu_summary.py)"""
     p = os.path.join(ROOT, "profiles", "ncu_summary.json")
-    if os.path.exists(p):
-        try:
-            with open(p) as f:
-                return json.load(f).get("k_step_random", {}).get("dram_bytes_per_launch")
-        except Exception:
-            return None
-    return None
+    try:
+        with open(p) as f:
+            return json.load(f).get(kernel, {})
+    except Exception:
+        return {}
+
+
+def ncu_traffic():
+    return ncu_summary().get("dram_bytes_per_launch")
+
+
+def ncu_binding_limit():
+    """What actually bounds the step kernel (SURVEY.md §8d asks for it next to the HBM fraction): ALU-pipe and
+    issue-slot utilisation from the last committed ncu capture — evidence copied from profiles/, not measured in this run."""
+    d = ncu_summary()
+    g = lambda k: (d.get(k) or {}).get("avg")   # noqa: E731
+    alu, issue = g("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"), g("smsp__issue_active.avg.pct_of_peak_sustained_active")
+    if alu is None and issue is None:
+        return None
+    return {"alu_pipe_frac": None if alu is None else alu / 100.0, "issue_slot_frac": None if issue is None else issue / 100.0,
+            "warp_inst_per_launch": g("smsp__inst_executed.sum"), "registers": g("launch__registers_per_thread"),
+            "source": "profiles/ncu_summary.json (ncu --set full, last committed capture)"}
 
 
 def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
