@@ -48,45 +48,49 @@ k_legal_moves(const __grid_constant__ Ctx<BB> cx, const tafl_state* __restrict__
     counts[g] = (uint32_t)gen_moves(cx, s, moves + (size_t)g * TAFL_MAX_MOVES, TAFL_MAX_MOVES);
 }
 
-// Game::do_play (game/mod.rs:95-101) with validation
+// Game::do_play (game/mod.rs:95-101) with validation.  HostMirror: the caller's pinned result buffers,
+// written from here over PCIe (plays may likewise be the caller's pinned buffer).
 template <class BB, int SP>
 __global__ void __launch_bounds__(STEP_BLOCK)
 k_step_plays(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
              const tafl_play* __restrict__ plays, tafl_play_effects* __restrict__ fx_out,
-             uint8_t* __restrict__ status_out, uint8_t* __restrict__ err_out, HistView hv) {
-    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= n) return;
-    tafl_state s = load_state(states + g);
-    const tafl_state before = s;
-    const tafl_play pl = plays[g];
-    tafl_play_effects fx;
-    fx.captures[0] = fx.captures[1] = 0;
-    fx.n_captures = 0;
-    for (int i = 0; i < 5; ++i) fx._pad[i] = 0;
-    const int err = validate_play(cx, s, pl, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
-    fx.err = (uint8_t)err;
-    if (!err) {
-        BB caps = do_valid_play(cx, s, pl.from_row, pl.from_col, pl.axis == TAFL_HORIZONTAL, pl.disp);
-        put_bb(fx.captures, caps);
-        fx.n_captures = (uint8_t)caps.popc();
-        store_state(states + g, s);
+             uint8_t* __restrict__ status_out, uint8_t* __restrict__ err_out, HistView hv, HostMirror hm) {
+    const uint32_t g = blockIdx.x * STEP_BLOCK + threadIdx.x;
+    if (g < n) {
+        const tafl_play pl = plays[g];   // may be the caller's pinned buffer, read over PCIe: issue it first
+        tafl_state s = load_state(states + g);
+        const tafl_state before = s;
+        tafl_play_effects fx;
+        fx.captures[0] = fx.captures[1] = 0;
+        fx.n_captures = 0;
+        for (int i = 0; i < 5; ++i) fx._pad[i] = 0;
+        const int err = validate_play(cx, s, pl, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
+        fx.err = (uint8_t)err;
+        if (!err) {
+            BB caps = do_valid_play(cx, s, pl.from_row, pl.from_col, pl.axis == TAFL_HORIZONTAL, pl.disp);
+            put_bb(fx.captures, caps);
+            fx.n_captures = (uint8_t)caps.popc();
+            store_state(states + g, s);
+        }
+        fx.status = s.status;
+        if (!err && hv.st) {   // Game::do_play: state_history.push(old state), play_history.push(record)
+            const uint32_t len = hv.len[g], slot = len % hv.cap;
+            store_state(hv.st + (size_t)slot * hv.n + g, before);
+            tafl_play_record r;
+            r.play = pl;
+            r.side = (before.flags & TAFL_FLAG_DEF_TO_PLAY) ? TAFL_DEFENDER : TAFL_ATTACKER;
+            r._pad[0] = r._pad[1] = r._pad[2] = 0;
+            r.effects = fx;
+            hv.rec[(size_t)slot * hv.n + g] = r;
+            hv.len[g] = len + 1;
+            if (len + 1 - hv.floor[g] > hv.cap) hv.floor[g] = len + 1 - hv.cap;
+        }
+        if (fx_out) fx_out[g] = fx;
+        if (status_out) status_out[g] = s.status;
+        if (err_out) err_out[g] = (uint8_t)err;
+        if (hm.status) hm.status[g] = s.status;
+        if (hm.err) hm.err[g] = (uint8_t)err;
     }
-    fx.status = s.status;
-    if (!err && hv.st) {   // Game::do_play: state_history.push(old state), play_history.push(record)
-        const uint32_t len = hv.len[g], slot = len % hv.cap;
-        store_state(hv.st + (size_t)slot * hv.n + g, before);
-        tafl_play_record r;
-        r.play = pl;
-        r.side = (before.flags & TAFL_FLAG_DEF_TO_PLAY) ? TAFL_DEFENDER : TAFL_ATTACKER;
-        r._pad[0] = r._pad[1] = r._pad[2] = 0;
-        r.effects = fx;
-        hv.rec[(size_t)slot * hv.n + g] = r;
-        hv.len[g] = len + 1;
-        if (len + 1 - hv.floor[g] > hv.cap) hv.floor[g] = len + 1 - hv.cap;
-    }
-    if (fx_out) fx_out[g] = fx;
-    if (status_out) status_out[g] = s.status;
-    if (err_out) err_out[g] = (uint8_t)err;
 }
 
 // Game::undo_last_play (game/mod.rs:103-108): pop the newest (state, record) pair of each selected game
@@ -402,6 +406,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     if (const char* v = std::getenv("TAFL_STEP_GRAPH")) e->step_graph_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_STEP_PDL")) e->step_pdl_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_CHUNKS")) e->host_chunks = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_HOST_IO")) e->host_io = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_MINB")) e->mcts_minb = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_G")) e->mcts_group = std::atoi(v);
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
@@ -550,27 +555,48 @@ int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_fx)
     if (rc) return rc;
     rc = device_out(e, 1, n, &d_fx);
     if (rc) return rc;
-    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx, nullptr, nullptr, e->hist)));
+    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx, nullptr, nullptr, e->hist, HostMirror{})));
     TAFL_LAUNCHED(e);
     if (h_fx) { rc = download(e, h_fx, d_fx, n); if (rc) return rc; }
     return sync_engine(e);
+}
+// device alias of a page-locked, device-mapped host pointer (cudaHostAlloc / cudaHostRegister), else null
+static void* mapped_alias(const void* h) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
 }
 int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err) {
     TAFL_CHECK_E(e);
     if (!h_plays || !h_status) return TAFL_ERR_INVALID_ARG;
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    tafl_play* d_pl;
+    tafl_play* d_pl = nullptr;
     uint8_t* d_err;
-    int rc = upload(e, 0, h_plays, n, &d_pl);
-    if (rc) return rc;
+    int rc;
+    // One ply is ~8 us of kernel but four copy-engine / launch hand-offs; with pinned caller buffers the
+    // kernel reads the plays and writes the result bytes through their device aliases instead
+    // (host_io bit 0: inputs, bit 1: outputs), which leaves one launch + one sync per call:
+    // 41.4 -> 26.5 us per 65 536-game ply (profiles/sweeps/r01r_e2e_modes.txt).  Pageable buffers take
+    // the copy-engine path.  Tried and dropped: 128-byte result rows staged through shared memory (no
+    // change) and a pinned completion word polled by the host instead of the stream sync (2 us slower).
+    if (e->host_io & 1) d_pl = (tafl_play*)mapped_alias(h_plays);
+    HostMirror hm{};
+    if (e->host_io & 2) {
+        hm.status = (uint8_t*)mapped_alias(h_status);
+        hm.err = h_err ? (uint8_t*)mapped_alias(h_err) : nullptr;
+        if (!hm.status || (h_err && !hm.err)) hm = HostMirror{};
+    }
+    if (!d_pl && (rc = upload(e, 0, h_plays, n, &d_pl))) return rc;
     rc = device_out(e, 1, n, &d_err);
     if (rc) return rc;
     TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, nullptr,
-                                                                                                    e->d_status, d_err, e->hist)));
+                                                                                                    e->d_status, d_err, e->hist, hm)));
     TAFL_LAUNCHED(e);
-    if ((rc = download(e, h_status, e->d_status, n))) return rc;
-    if (h_err && (rc = download(e, h_err, d_err, n))) return rc;
+    if (!hm.status) {
+        if ((rc = download(e, h_status, e->d_status, n))) return rc;
+        if (h_err && (rc = download(e, h_err, d_err, n))) return rc;
+    }
     return sync_engine(e);
 }
 int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_status) {

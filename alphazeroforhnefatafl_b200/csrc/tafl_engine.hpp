@@ -28,6 +28,12 @@ struct HistView {
     uint32_t cap = 0, n = 0;
 };
 
+// device aliases of the caller's pinned result buffers (tafl_step_status), null = not in use
+struct HostMirror {
+    uint8_t* status = nullptr;
+    uint8_t* err = nullptr;
+};
+
 }  // namespace tafl
 
 struct tafl_engine {
@@ -52,6 +58,7 @@ struct tafl_engine {
     cudaStream_t aux[N_AUX] = {nullptr, nullptr, nullptr, nullptr};
     bool aux_ready = false;
     int host_chunks = 8;
+    int host_io = 3;   // tafl_step_status with pinned caller buffers: bit 0 kernel reads the plays in place, bit 1 writes results in place
     int mcts_minb = 8;                 // k_mcts_sims variant: CTAs of 4 warps resident per SM
     int mcts_group = 16;               // TAFL_MCTS_G: lanes per tree of k_mcts_sims_g (32/16/8); 0 = first-generation k_mcts_sims
     int step_minb = 8;                 // k_step_random variant: CTAs of 64 threads resident per SM (8: one wave for 65 536 games)

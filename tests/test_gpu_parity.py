@@ -239,6 +239,56 @@ def test_gpu_recorded_actions_replay(orc, built_lib, name, preset, width):
 
 
 @pytest.mark.gpu
+def test_gpu_do_play_pinned_buffers_in_place(orc, built_lib, monkeypatch):
+    """tafl_step_status with pinned caller buffers (the kernel reads the plays and writes the status /
+    PlayInvalid bytes in place over PCIe) == pageable buffers (copy engine) == TAFL_HOST_IO=0, for ragged
+    game counts, invalid plays included, with and without the PlayInvalid output; oracle on the successors."""
+    import torch
+    from alphazeroforhnefatafl_b200._lib import lib
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), board_for(orc, A.PRESET_COPENHAGEN)
+    for n in (1, 65, 4100):
+        with E.LockstepGames(rules, fen, n, 0, 128) as src:
+            seq = []
+            for ply in range(12):
+                src.step_random(11, 1, auto_reset=False)
+                pl = E.moves_to_plays(src.last_actions()[0], 128)
+                if ply == 4:
+                    pl.view(np.uint8).reshape(n, 4)[::7, 3] = 0      # zero displacement: invalid
+                seq.append(pl)
+        results = {}
+        for label, mode, pinned in (("in_place", "3", True), ("copy", "0", True), ("pageable", "3", False)):
+            monkeypatch.setenv("TAFL_HOST_IO", mode)
+            with E.LockstepGames(rules, fen, n, 0, 128) as g:
+                got = []
+                for ply, pl in enumerate(seq):
+                    before = g.get_states()
+                    if pinned:
+                        h_pl = torch.from_numpy(pl.view(np.uint8).reshape(n, 4).copy()).pin_memory()
+                        h_st = torch.full((n + 8,), 0xEE, dtype=torch.uint8).pin_memory()    # guard bytes after the rows
+                        h_er = torch.full((n + 8,), 0xEE, dtype=torch.uint8).pin_memory()
+                        want_err = ply % 2 == 0
+                        rc = lib().tafl_step_status(g.handle, h_pl.data_ptr(), h_st.data_ptr(), h_er.data_ptr() if want_err else None)
+                        assert rc == 0
+                        assert (h_st[n:] == 0xEE).all() and (h_er[n if want_err else 0:] == 0xEE).all()
+                        st, er = h_st[:n].numpy().copy(), (h_er[:n].numpy().copy() if want_err else None)
+                    else:
+                        st, er = g.game_do_play(pl)
+                    after = g.get_states()
+                    got.append((st.tobytes(), None if er is None else er.tobytes(), after.tobytes()))
+                    if label == "in_place" and er is not None:
+                        ok = er == 0
+                        exp, _ = orc.by_value(rules, 128).do_plays(before[ok], pl[ok])
+                        assert exp.tobytes() == after[ok].tobytes()
+                        assert after[~ok].tobytes() == before[~ok].tobytes()
+                        if ply == 4:
+                            assert (~ok).any()
+                results[label] = got
+        for a, b, c in zip(results["in_place"], results["copy"], results["pageable"]):
+            assert a[0] == b[0] == c[0] and a[2] == b[2] == c[2]
+            assert a[1] == b[1] and (a[1] is None or a[1] == c[1])
+
+
+@pytest.mark.gpu
 def test_gpu_graph_pdl_stepping_equals_plain_launches(orc, built_lib, monkeypatch):
     """n_steps single-ply launches as one CUDA graph with programmatic (PDL) edges == plain launches ==
     the oracle, across re-captures (changed n_steps / seed / game-id base) and launch-to-launch ply carry"""
