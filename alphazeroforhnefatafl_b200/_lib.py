@@ -115,6 +115,7 @@ def lib():
         "tafl_mcts_play_best": (C.c_int, [vp, vp]),
         "tafl_mcts_advance": (C.c_int, [vp, vp]),
         "tafl_mcts_reroot": (C.c_int, [vp]),
+        "tafl_mcts_root_noise": (C.c_int, [vp, vp, C.c_double]),
         "tafl_mcts_stats_get": (C.c_int, [vp, C.POINTER(A.MctsStats)]),
         "tafl_mcts_policy": (C.c_int, [vp, C.c_double, C.c_int, C.c_uint64, vp]),
         "tafl_mcts_begin": (C.c_int, [vp]),

@@ -33,6 +33,10 @@ struct MctsPools {
     uint32_t* l_counts = nullptr;     // [n_games]
     float* l_priors = nullptr;        // [n_games][TAFL_MAX_MOVES]  evaluator output
     float* l_values = nullptr;        // [n_games]                  evaluator output
+    double* d_noise = nullptr;        // [n_games][TAFL_MAX_MOVES] root exploration noise (tafl_mcts_root_noise), eps below
+    double noise_eps = 0.0;
+    uint8_t* t_noised = nullptr;      // [n_games] this search's root already carries the noise
+    double rg_eps = 0.0;
     cudaGraphExec_t round_graph = nullptr;   // num_sims rounds with a built-in evaluator (tafl_mcts_search_builtin)
     int rg_kind = -1, rg_spec = -1;
     uint64_t rg_seed = 0;
@@ -924,6 +928,24 @@ __device__ __forceinline__ double warp_np_sum512(const double (&x)[16], int lane
     return 0.0 + r;
 }
 
+// Root exploration noise (the reference's TODO at src/mcts.rs:53; oracle: Mcts::noise_root): once per
+// search, P[a] <- (1 - eps) * P[a] + eps * noise[a] on the root's priors as soon as the root is
+// expanded (first round of a fresh tree, or before the first round of a carried one).
+__global__ void __launch_bounds__(MCTS_WARPS * 32)
+k_mcts_root_noise(MctsView mv, uint32_t n_trees, const double* __restrict__ noise, double eps, uint8_t* __restrict__ noised) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t tree = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
+    if (tree >= n_trees || noised[tree]) return;
+    const uint4 h = mv.n_hdr[(size_t)tree * mv.node_cap];
+    if (!hdr_expanded(h.w)) return;
+    double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap + h.x;
+    const double* const nz = noise + (size_t)tree * TAFL_MAX_MOVES;
+    const uint32_t L = hdr_n_edges(h.w);
+    for (uint32_t a = lane; a < L; a += 32) prior[a] = (1.0 - eps) * prior[a] + eps * nz[a];
+    __syncwarp();
+    if (lane == 0) noised[tree] = 1;
+}
+
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
 k_mcts_expand_backup(MctsView mv, uint32_t n_trees, const float* __restrict__ l_priors, const float* __restrict__ l_values) {
     static_assert(TAFL_MAX_MOVES == 512, "np.sum restatement is laid out for action_size == 512");
@@ -1024,6 +1046,7 @@ void mcts_free(tafl_engine* e) {
     if (m->round_graph) cudaGraphExecDestroy(m->round_graph);
     cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
     cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
+    cudaFree(m->d_noise); cudaFree(m->t_noised);
     delete m;
     e->mcts = nullptr;
 }
@@ -1119,6 +1142,10 @@ int tafl_mcts_search_async(tafl_engine* e) {
     if (rc) return rc;
     cudaSetDevice(e->device);
     MctsPools* m = e->mcts;
+    if (m->noise_eps != 0.0) {
+        e->err = "tafl_mcts_search: root noise is set, but the fused stub search has implicit uniform priors (use the evaluator path)";
+        return TAFL_ERR_INVALID_ARG;
+    }
     const uint32_t n = e->n_games;
     launch_tree_init(e, e->mcts_group == 32 || e->mcts_group == 16 || e->mcts_group == 8 ? 1 : 0);
     MCTS_LAUNCHED(e);
@@ -1337,9 +1364,33 @@ int tafl_mcts_begin(tafl_engine* e) {
     MctsPools* m = e->mcts;
     launch_tree_init(e, 0);
     MCTS_LAUNCHED(e);
+    if (m->noise_eps != 0.0) {   // carried (already expanded) roots take the noise now, fresh ones after round 1
+        TAFL_CUDA_TRY(e, cudaMemsetAsync(m->t_noised, 0, e->n_games, e->stream));
+        k_mcts_root_noise<<<grid_for(e->n_games, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, e->n_games, m->d_noise, m->noise_eps, m->t_noised);
+        MCTS_LAUNCHED(e);
+    }
     m->phase = 1;
     m->rounds = 0;
     m->searched = false;
+    return TAFL_OK;
+}
+
+int tafl_mcts_root_noise(tafl_engine* e, const double* noise, double eps) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    MctsPools* m = e->mcts;
+    if (m->phase == 2) { e->err = "tafl_mcts_root_noise: a leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
+    if (!(eps >= 0.0 && eps <= 1.0)) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    if (!noise || eps == 0.0) { m->noise_eps = 0.0; return TAFL_OK; }
+    const size_t bytes = (size_t)e->n_games * TAFL_MAX_MOVES * sizeof(double);
+    if (!m->d_noise) {
+        TAFL_CUDA_TRY(e, cudaMalloc((void**)&m->d_noise, bytes));
+        TAFL_CUDA_TRY(e, cudaMalloc((void**)&m->t_noised, e->n_games));
+    }
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(m->d_noise, noise, bytes, cudaMemcpyDefault, e->stream));   // host or device source
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    m->noise_eps = eps;
     return TAFL_OK;
 }
 
@@ -1369,6 +1420,10 @@ int tafl_mcts_expand_backup(tafl_engine* e) {
     const uint32_t n = e->n_games;
     k_mcts_expand_backup<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->l_priors, m->l_values);
     MCTS_LAUNCHED(e);
+    if (m->noise_eps != 0.0 && m->rounds == 0) {   // the roots expanded by this first round
+        k_mcts_root_noise<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->d_noise, m->noise_eps, m->t_noised);
+        MCTS_LAUNCHED(e);
+    }
     m->phase = 1;
     m->rounds += 1;
     return TAFL_OK;
@@ -1467,7 +1522,7 @@ int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
     // All num_sims rounds (select, evaluate, expand/backup) have static arguments: one CUDA graph,
     // captured once per (evaluator, seed, config), replaces 3 x num_sims launches.
     if (!m->round_graph || m->rg_kind != evaluator || m->rg_seed != seed || m->rg_sims != m->cfg.num_sims ||
-        m->rg_cpuct != m->cfg.cpuct || m->rg_draw != m->cfg.draw_value || m->rg_spec != e->spec) {
+        m->rg_cpuct != m->cfg.cpuct || m->rg_draw != m->cfg.draw_value || m->rg_spec != e->spec || m->rg_eps != m->noise_eps) {
         if (m->round_graph) { cudaGraphExecDestroy(m->round_graph); m->round_graph = nullptr; }
         TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         const uint64_t before = e->launches;
@@ -1488,10 +1543,10 @@ int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
         cudaGraphDestroy(graph);
         TAFL_CUDA_TRY(e, ce);
         m->rg_kind = evaluator; m->rg_seed = seed; m->rg_sims = m->cfg.num_sims; m->rg_cpuct = m->cfg.cpuct;
-        m->rg_draw = m->cfg.draw_value; m->rg_spec = e->spec;
+        m->rg_draw = m->cfg.draw_value; m->rg_spec = e->spec; m->rg_eps = m->noise_eps;
     }
     TAFL_CUDA_TRY(e, cudaGraphLaunch(m->round_graph, e->stream));
-    e->launches += 3ull * m->cfg.num_sims;
+    e->launches += 3ull * m->cfg.num_sims + (m->noise_eps != 0.0 ? 1 : 0);
     m->rounds = m->cfg.num_sims;
     return tafl_mcts_finish(e);
 }

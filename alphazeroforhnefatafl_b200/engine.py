@@ -142,6 +142,7 @@ class LockstepGames:
         _check(lib().tafl_engine_info(self._h, C.byref(n), C.byref(w), C.byref(sl), C.byref(dev), C.byref(sm)))
         self.n_games, self.width, self.side_len, self.device, self.sm_count = n.value, w.value, sl.value, dev.value, sm.value
         self.start_fen = start_fen
+        self.game_id_base = 0
 
     # -- lifetime -------------------------------------------------------------------------------
     def close(self):
@@ -283,6 +284,7 @@ class LockstepGames:
 
     def set_game_id_base(self, v):
         self._ck(lib().tafl_set_game_id_base(self._h, v))
+        self.game_id_base = int(v)
 
     def set_random_ply(self, v):
         self._ck(lib().tafl_set_random_ply(self._h, v))
@@ -339,6 +341,26 @@ class LockstepGames:
 
     def mcts_reroot(self):
         self._ck(lib().tafl_mcts_reroot(self._h))
+
+    def mcts_root_noise(self, noise, eps):
+        """Root exploration noise for the evaluator-path searches that follow (tafl_mcts_root_noise):
+        priors of each root become (1 - eps) * P + eps * noise[game]; noise None / eps 0 switches it off."""
+        if noise is None or eps == 0:
+            self._ck(lib().tafl_mcts_root_noise(self._h, None, 0.0))
+            return
+        noise = np.ascontiguousarray(noise, np.float64)
+        assert noise.shape == (self.n_games, A.MAX_MOVES)
+        self._ck(lib().tafl_mcts_root_noise(self._h, A.ptr(noise), float(eps)))
+
+    def dirichlet_root_noise(self, alpha, seed):
+        """Dirichlet(alpha) rows over each game's legal root moves (zeros beyond), numpy Generator(seed)."""
+        counts = self.legal_moves()[1]
+        rng = np.random.default_rng(seed)
+        noise = np.zeros((self.n_games, A.MAX_MOVES), np.float64)
+        for g, L in enumerate(counts):
+            if L:
+                noise[g, :L] = rng.dirichlet(np.full(int(L), float(alpha)))
+        return noise
 
     def mcts_stats(self):
         s = A.MctsStats()

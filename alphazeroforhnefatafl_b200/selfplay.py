@@ -163,13 +163,18 @@ class SelfPlay:
     ``dst``.  ``games`` is an engine.LockstepGames whose game-id base is already the shard's."""
 
     def __init__(self, games, num_sims=800, cpuct=1.0, draw_value=1e-4, dst=0, group=None, edge_capacity=0,
-                 tree_reuse=False, evaluator=None):
+                 tree_reuse=False, evaluator=None, root_noise=None):
         """tree_reuse: one MCTS object per episode as in the reference (mcts.py:20-26) — the subtree
         below the move played is kept.  evaluator: None = stub fused into the search kernel;
         ("stub",) / ("hash", seed) = built-in device evaluators through the evaluator hook; or an
-        object with predict_batch(batch) (see mcts.MCTS)."""
+        object with predict_batch(batch) (see mcts.MCTS).  root_noise: (alpha, eps) = Dirichlet(alpha)
+        exploration noise mixed into each root's priors with weight eps (the reference's TODO at
+        src/mcts.rs:53; evaluator searches only), drawn per move from numpy Generator(seed of move())."""
         self.g, self.dst, self.group = games, dst, group
         self.tree_reuse, self.evaluator = tree_reuse, evaluator
+        if root_noise is not None and evaluator is None:
+            raise ValueError("root_noise needs an evaluator (the fused stub search has implicit uniform priors)")
+        self.root_noise, self.moves_done = root_noise, 0
         games.mcts_configure(num_sims, cpuct, draw_value, edge_capacity, tree_reuse=tree_reuse)
         self.stream = torch.cuda.ExternalStream(games.stream, device=games.device)
         with torch.cuda.device(games.device):
@@ -183,6 +188,10 @@ class SelfPlay:
         g = self.g
         with torch.cuda.stream(self.stream):
             ev = self.evaluator
+            if self.root_noise is not None:
+                alpha, eps = self.root_noise
+                g.mcts_root_noise(g.dirichlet_root_noise(alpha, (int(seed), g.game_id_base, self.moves_done)), eps)
+            self.moves_done += 1
             if ev is None:
                 g.mcts_search(sync=False)
             elif isinstance(ev, tuple):

@@ -470,6 +470,15 @@ int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status /* may be NULL */);
  * BEFORE advancing (the records describe the searched root). */
 int tafl_mcts_advance(tafl_engine* e, uint8_t* h_status /* may be NULL */);
 int tafl_mcts_reroot(tafl_engine* e);   /* the re-rooting half alone: play_best, pack_records, reroot */
+/* Root exploration noise (the reference's TODO at src/mcts.rs:53 "add Dirichlet noise"; src/mcts.py has
+ * none, so this is build-defined and pinned by the oracle only): in every evaluator-path search that
+ * follows, the priors of each game's root become (1 - eps) * P[a] + eps * noise[game][a], a < L, once per
+ * search -- when the root is expanded, or before the first round when tree reuse carried an expanded
+ * root.  `noise` is caller-drawn (Dirichlet(alpha) over the root's L legal moves, zeros beyond),
+ * [n_games][TAFL_MAX_MOVES] f64 in host or device memory, copied by this call and in force until the
+ * next call; NULL or eps == 0 switches it off.  The fused stub search (tafl_mcts_search) has implicit
+ * uniform priors and refuses to run while noise is set.  Call after tafl_mcts_configure. */
+int tafl_mcts_root_noise(tafl_engine* e, const double* noise, double eps);
 /* totals since configure: simulations run, nodes expanded, sum of path depths, sum of edges */
 typedef struct {
     uint64_t sims, nodes, depth_sum, edges, terminal_hits, max_edges_used;

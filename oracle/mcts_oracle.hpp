@@ -97,6 +97,18 @@ struct Mcts {
     // boundary is f32 (what a network emits), widened to f64 before masking (adapter: predict
     // returns P.astype(float64), float(v)).  Unset = the uniform-prior / value-0 stub.
     std::function<void(const GameState<W>&, float*, float*)> eval;
+    // Root exploration noise (the reference's TODO at src/mcts.rs:53, absent from src/mcts.py; build-defined):
+    // the priors of the node a search starts from become (1 - eps) * P[a] + eps * noise[a], once per
+    // search, when that node is expanded or -- with a retained tree -- before the first simulation.
+    std::vector<double> root_noise;
+    double noise_eps = 0.0;
+    bool root_noised = false;
+    void noise_root() {
+        Node& n = nodes[root];
+        if (noise_eps == 0.0 || root_noised || !n.expanded || !eval) return;
+        for (size_t a = 0; a < n.Pa.size(); ++a) n.Pa[a] = (1.0 - noise_eps) * n.Pa[a] + noise_eps * root_noise[a];
+        root_noised = true;
+    }
     const GameLogic& logic;
     double cpuct, draw_value;
     std::vector<Node> nodes;
@@ -163,6 +175,7 @@ struct Mcts {
             n.expanded = true;
             stats.edges += L;
             stats.depth_sum += (uint64_t)depth;
+            if (idx == root) noise_root();
             double v = v_eval;
             return -v;
         }
@@ -205,6 +218,7 @@ struct Mcts {
     // mcts.py:28-53 with temp = 0 and first-max tie-break
     void get_action_prob(const GameState<W>& root, uint32_t num_sims) {
         reset(root);
+        root_noised = false;
         for (uint32_t i = 0; i < num_sims; ++i) {
             search(0, 0);
             stats.sims += 1;
@@ -216,6 +230,8 @@ struct Mcts {
     // cleared, mcts.py:20-26).  `root` walks down the retained tree.
     int root = 0;
     void run_from_root(uint32_t num_sims) {
+        root_noised = false;
+        noise_root();
         for (uint32_t i = 0; i < num_sims; ++i) {
             search(root, 0);
             stats.sims += 1;

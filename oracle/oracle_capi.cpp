@@ -475,10 +475,12 @@ double orc_np_sum(const double* a, uint64_t n) { return np_sum(a, (size_t)n); }
 // per move: n_moves x (num_sims simulations from the current root, play the first-max move).
 // Outputs per (game, move): [n][n_moves][TAFL_MAX_MOVES] visits / q, [n][n_moves] counts / best;
 // final states [n].  use_eval != 0 -> TAFL_EVAL_HASH evaluator.
-int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
-                     uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
-                     int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best, tafl_state* final_states,
-                     tafl_mcts_stats* stats) {
+// `noise` (optional): root exploration noise [n][n_moves][TAFL_MAX_MOVES] f64, mixed in with weight eps
+// (Mcts::noise_root; evaluator searches only).
+int orc_mcts_episode_noise(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                           uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
+                           int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best,
+                           tafl_state* final_states, tafl_mcts_stats* stats, const double* noise, double eps) {
     return dispatch(width, [&](auto w) {
         using W = decltype(w);
         if (n_threads < 1) n_threads = 1;
@@ -504,6 +506,10 @@ int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, ui
                         const size_t row = (size_t)g * n_moves + mv;
                         counts[row] = 0;
                         best[row] = 0;
+                        if (noise) {
+                            m.noise_eps = eps;
+                            m.root_noise.assign(noise + row * TAFL_MAX_MOVES, noise + (row + 1) * TAFL_MAX_MOVES);
+                        }
                         if (s.status != TAFL_STATUS_ONGOING) {   // getActionProb on a finished game: every search returns -Es
                             m.run_from_root(num_sims);
                             continue;
@@ -541,6 +547,14 @@ int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, ui
         }
         return 0;
     });
+}
+
+int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                     uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
+                     int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best, tafl_state* final_states,
+                     tafl_mcts_stats* stats) {
+    return orc_mcts_episode_noise(r, width, roots, n, num_sims, n_moves, reuse, cpuct, draw_value, use_eval, eval_seed, n_threads,
+                                  visits, q, counts, best, final_states, stats, nullptr, 0.0);
 }
 
 int orc_hw_threads(void) { return (int)std::thread::hardware_concurrency(); }

@@ -243,8 +243,9 @@ class Oracle:
         return dict(moves=moves, visits=visits, q=q, counts=counts, best=best, stats=stats)
 
     def mcts_episode(self, rules, width, roots, num_sims, n_moves, reuse, cpuct=1.0, draw_value=1e-4, eval_seed=None,
-                     n_threads=1):
-        """n_moves self-play moves per root with one MCTS object per game (reuse) or a fresh tree per move."""
+                     n_threads=1, noise=None, eps=0.0):
+        """n_moves self-play moves per root with one MCTS object per game (reuse) or a fresh tree per move;
+        noise [n][n_moves][MAX_MOVES] f64 = root exploration noise mixed in with weight eps."""
         roots = np.ascontiguousarray(roots)
         n = len(roots)
         visits = np.zeros((n, n_moves, A.MAX_MOVES), np.uint32)
@@ -253,13 +254,17 @@ class Oracle:
         best = np.zeros((n, n_moves), np.uint32)
         final = np.zeros(n, A.STATE_DTYPE)
         stats = A.MctsStats()
-        f = self.lib.orc_mcts_episode
+        if noise is not None:
+            noise = np.ascontiguousarray(noise, np.float64)
+            assert noise.shape == (n, n_moves, A.MAX_MOVES)
+        f = self.lib.orc_mcts_episode_noise
         f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_double, C.c_double,
-                      C.c_int, C.c_uint64, C.c_int] + [C.c_void_p] * 6
+                      C.c_int, C.c_uint64, C.c_int] + [C.c_void_p] * 7 + [C.c_double]
         f.restype = C.c_int
         rc = f(C.addressof(rules), width, roots.ctypes.data, n, num_sims, n_moves, int(reuse), cpuct, draw_value,
                int(eval_seed is not None), int(eval_seed or 0), n_threads, visits.ctypes.data, q.ctypes.data,
-               counts.ctypes.data, best.ctypes.data, final.ctypes.data, C.addressof(stats))
+               counts.ctypes.data, best.ctypes.data, final.ctypes.data, C.addressof(stats),
+               None if noise is None else noise.ctypes.data, float(eps))
         assert rc == 0, rc
         return dict(visits=visits, q=q, counts=counts, best=best, final=final, stats=stats)
 

@@ -151,6 +151,35 @@ def test_gpu_selfplay_episode_vs_oracle(orc, built_lib):
         assert z.shape[0] == sum(len(r) for r in all_recs)
 
 
+def test_gpu_selfplay_root_noise_vs_oracle(orc, built_lib):
+    """SelfPlay(root_noise=(alpha, eps)) with the hash evaluator and tree reuse: the Dirichlet rows the
+    driver draws per move, fed to the oracle, give the same visit counts and the same games"""
+    from alphazeroforhnefatafl_b200 import selfplay as SP
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
+    n, sims, moves = 40, 80, 6
+    with E.LockstepGames(rules, fen, n, 0, 64) as g:
+        g.set_game_id_base(300)
+        g.step_random(8, 12, auto_reset=False)
+        roots = g.get_states()
+        with pytest.raises(ValueError):
+            SP.SelfPlay(g, num_sims=sims, root_noise=(0.3, 0.25))
+        sp = SP.SelfPlay(g, num_sims=sims, tree_reuse=True, evaluator=("hash", 4), root_noise=(0.3, 0.25))
+        noise = np.zeros((n, moves, A.MAX_MOVES))
+        visits = np.zeros((n, moves, A.MAX_MOVES), np.uint32)
+        for mv in range(moves):
+            noise[:, mv] = g.dirichlet_root_noise(0.3, (21, 300, mv))      # what move() draws: (seed, id base, move index)
+            L = g.legal_moves()[1]
+            live = g.get_states()["status"] == 0
+            assert np.allclose(noise[live, mv].sum(1), 1.0) and (noise[np.arange(n), mv, np.maximum(L, 1) - 1][live] > 0).all()
+            sp.move(gather=False, seed=21)
+            g.sync()
+            visits[:, mv] = g.mcts_results()["visits"]
+        final = g.get_states()
+    exp = orc.mcts_episode(rules, 64, roots, sims, moves, True, eval_seed=4, n_threads=8, noise=noise, eps=0.25)
+    assert np.array_equal(visits, exp["visits"])
+    assert final.tobytes() == exp["final"].tobytes()
+
+
 def test_gpu_mcts_group_sizes_are_bit_identical(orc, built_lib, monkeypatch):
     """k_mcts_sims_g with 32 / 16 / 8 lanes per tree (2 / 4 trees per warp, converged create + expand)
     == the first-generation warp-per-tree kernel (TAFL_MCTS_G=0) == the oracle, incl. tree reuse over

@@ -371,3 +371,84 @@ def test_gpu_tree_reuse_dropped_when_states_are_replaced(orc, built_lib):
         got = g.mcts_results()
     exp = orc.mcts_search(rules, 64, other, 150)
     assert np.array_equal(got["visits"], exp["visits"]) and got["q"].tobytes() == exp["q"].tobytes()
+
+
+# ---- root exploration noise (src/mcts.rs:53 TODO; build-defined, pinned by the oracle) ------------------
+def _noise_rows(n, n_moves, seed):
+    rng = np.random.default_rng(seed)
+    z = rng.gamma(0.3, size=(n, n_moves, A.MAX_MOVES))
+    return z / z[:, :, :64].sum(2, keepdims=True)
+
+
+def test_oracle_root_noise_semantics(orc):
+    """eps = 0 leaves the search untouched; eps = 1 with a one-hot row forces every simulation through
+    that root action; the noise is applied once per search, also to a root carried by tree reuse."""
+    from parity_cases import board_for, sample_positions
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), board_for(orc, A.PRESET_BRANDUBH)
+    roots = sample_positions(orc, rules, fen, 64, 6, seed=61, max_steps=40)
+    base = orc.mcts_episode(rules, 64, roots, 60, 3, True, eval_seed=9)
+    z = _noise_rows(len(roots), 3, 1)
+    same = orc.mcts_episode(rules, 64, roots, 60, 3, True, eval_seed=9, noise=z, eps=0.0)
+    assert np.array_equal(base["visits"], same["visits"]) and base["q"].tobytes() == same["q"].tobytes()
+    mixed = orc.mcts_episode(rules, 64, roots, 60, 3, True, eval_seed=9, noise=z, eps=0.25)
+    assert not np.array_equal(base["visits"], mixed["visits"])
+    onehot = np.zeros_like(z)
+    onehot[:, :, 2] = 1.0
+    forced = orc.mcts_episode(rules, 64, roots, 60, 3, True, eval_seed=9, noise=onehot, eps=1.0)
+    for g in range(len(roots)):     # the simulation after the root's expansion sees u > 0 on action 2 only
+        if forced["counts"][g, 0] > 2:
+            assert forced["visits"][g, 0, 2] >= 1
+    # a root carried by tree reuse takes that move's noise too: rows that differ at move 1 only
+    z2 = z.copy()
+    z2[:, 1] = _noise_rows(len(roots), 1, 5)[:, 0]
+    other = orc.mcts_episode(rules, 64, roots, 60, 3, True, eval_seed=9, noise=z2, eps=0.25)
+    assert np.array_equal(other["visits"][:, 0], mixed["visits"][:, 0])
+    assert not np.array_equal(other["visits"][:, 1], mixed["visits"][:, 1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("preset,width,sims,n_moves,reuse", [
+    (A.PRESET_COPENHAGEN, 128, 100, 4, True), (A.PRESET_BRANDUBH, 64, 200, 8, True), (A.PRESET_TABLUT, 128, 120, 5, False)])
+def test_gpu_root_noise_matches_oracle(orc, built_lib, preset, width, sims, n_moves, reuse):
+    """tafl_mcts_root_noise: visits / Q / chosen moves / final states bit-exact with the oracle's noise_root,
+    fresh trees and carried trees, through the graph-launched built-in evaluator and the split-phase calls"""
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for, sample_positions
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    roots = sample_positions(orc, rules, fen, width, 96, seed=62, max_steps=200)
+    n = len(roots)
+    z = _noise_rows(n, n_moves, 2)
+    exp = orc.mcts_episode(rules, width, roots, sims, n_moves, reuse, eval_seed=31, n_threads=8, noise=z, eps=0.25)
+    for split in (False, True):
+        with E.LockstepGames(rules, fen, n, 0, width) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, 1.0, 1e-4, tree_reuse=reuse)
+            visits = np.zeros((n, n_moves, A.MAX_MOVES), np.uint32)
+            q = np.zeros((n, n_moves, A.MAX_MOVES), np.float64)
+            best = np.zeros((n, n_moves), np.uint32)
+            for j in range(n_moves):
+                g.mcts_root_noise(z[:, j], 0.25)
+                if split:
+                    g.mcts_begin()
+                    for _ in range(sims):
+                        g.mcts_select_leaves()
+                        g.eval_builtin(A.EVAL_HASH, 31)
+                        g.mcts_expand_backup()
+                    g.mcts_finish()
+                else:
+                    g.mcts_search_builtin(A.EVAL_HASH, 31)
+                r = g.mcts_results()
+                visits[:, j], q[:, j], best[:, j] = r["visits"], r["q"], r["best"]
+                g.mcts_advance() if reuse else g.mcts_play_best()
+            final = g.get_states()
+            # noise is refused by the fused stub search, and can be switched off again
+            with pytest.raises(Exception):
+                g.mcts_search()
+            g.mcts_root_noise(None, 0.0)
+            g.mcts_search()
+        assert np.array_equal(visits, exp["visits"]), split
+        assert q.tobytes() == exp["q"].tobytes(), split
+        assert np.array_equal(best, exp["best"])
+        assert final.tobytes() == exp["final"].tobytes()
+    plain = orc.mcts_episode(rules, width, roots, sims, n_moves, reuse, eval_seed=31, n_threads=8)
+    assert not np.array_equal(plain["visits"], exp["visits"])
