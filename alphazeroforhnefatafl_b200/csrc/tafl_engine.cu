@@ -599,6 +599,28 @@ int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status
     }
     return sync_engine(e);
 }
+// page-locked host memory for the HOST-buffer calls (see tafl_step_status)
+int tafl_host_alloc(size_t bytes, void** out) {
+    if (!out || bytes == 0) return TAFL_ERR_INVALID_ARG;
+    *out = nullptr;
+    if (cudaHostAlloc(out, bytes, cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) { cudaGetLastError(); return TAFL_ERR_CUDA; }
+    return TAFL_OK;
+}
+int tafl_host_free(void* p) {
+    if (!p) return TAFL_OK;
+    if (cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return TAFL_ERR_INVALID_ARG; }
+    return TAFL_OK;
+}
+int tafl_host_register(void* p, size_t bytes) {
+    if (!p || bytes == 0) return TAFL_ERR_INVALID_ARG;
+    if (cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped) != cudaSuccess) { cudaGetLastError(); return TAFL_ERR_CUDA; }
+    return TAFL_OK;
+}
+int tafl_host_unregister(void* p) {
+    if (!p) return TAFL_ERR_INVALID_ARG;
+    if (cudaHostUnregister(p) != cudaSuccess) { cudaGetLastError(); return TAFL_ERR_INVALID_ARG; }
+    return TAFL_OK;
+}
 int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_status) {
     TAFL_CHECK_E(e);
     if (!d_moves) return TAFL_ERR_INVALID_ARG;

@@ -129,6 +129,31 @@ def moves_to_plays(moves, width):
     return out
 
 
+class PinnedArray:
+    """numpy view of page-locked host memory from tafl_host_alloc: buffers of this kind let the HOST-buffer
+    calls (tafl_step_status) run without copy-engine staging.  Keep the object alive while `.a` is in use."""
+
+    def __init__(self, shape, dtype):
+        dtype = np.dtype(dtype)
+        nbytes = max(1, int(np.prod(shape)) * dtype.itemsize)
+        self._p = C.c_void_p()
+        _check(lib().tafl_host_alloc(nbytes, C.byref(self._p)))
+        buf = (C.c_uint8 * nbytes).from_address(self._p.value)
+        self.a = np.frombuffer(buf, np.uint8)[:int(np.prod(shape)) * dtype.itemsize].view(dtype).reshape(shape)
+
+    def close(self):
+        if self._p:
+            self.a = None
+            lib().tafl_host_free(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001  interpreter shutdown
+            pass
+
+
 class LockstepGames:
     """``n_games`` resident games on one GPU, advanced in lockstep (Game, game/mod.rs:76-116)."""
 
@@ -143,12 +168,17 @@ class LockstepGames:
         self.n_games, self.width, self.side_len, self.device, self.sm_count = n.value, w.value, sl.value, dev.value, sm.value
         self.start_fen = start_fen
         self.game_id_base = 0
+        self._pin = None
 
     # -- lifetime -------------------------------------------------------------------------------
     def close(self):
         if self._h:
             lib().tafl_engine_destroy(self._h)
             self._h = C.c_void_p()
+        if self._pin is not None:
+            for p in self._pin:
+                p.close()
+            self._pin = None
 
     def __del__(self):
         try:
@@ -238,9 +268,12 @@ class LockstepGames:
         type: (status[n] uint8 packed GameStatus, err[n] uint8 PlayInvalid code)."""
         plays = np.ascontiguousarray(plays, A.PLAY_DTYPE)
         assert len(plays) == self.n_games
-        status, err = np.empty(self.n_games, np.uint8), np.empty(self.n_games, np.uint8)
-        self._ck(lib().tafl_step_status(self._h, A.ptr(plays), A.ptr(status), A.ptr(err)))
-        return status, err
+        if self._pin is None:   # page-locked staging: the kernel reads / writes these in place (tafl_step_status)
+            self._pin = (PinnedArray(self.n_games, A.PLAY_DTYPE), PinnedArray(self.n_games, np.uint8), PinnedArray(self.n_games, np.uint8))
+        p_pl, p_st, p_er = self._pin
+        p_pl.a[:] = plays
+        self._ck(lib().tafl_step_status(self._h, A.ptr(p_pl.a), A.ptr(p_st.a), A.ptr(p_er.a)))
+        return p_st.a.copy(), p_er.a.copy()
 
     def last_actions(self):
         """(moves uint16, status uint8, stepped bool) of the most recent random ply (tafl_actions_host)."""

@@ -271,8 +271,19 @@ def test_gpu_do_play_pinned_buffers_in_place(orc, built_lib, monkeypatch):
                         assert rc == 0
                         assert (h_st[n:] == 0xEE).all() and (h_er[n if want_err else 0:] == 0xEE).all()
                         st, er = h_st[:n].numpy().copy(), (h_er[:n].numpy().copy() if want_err else None)
-                    else:
-                        st, er = g.game_do_play(pl)
+                    else:      # plain numpy memory -> the copy-engine path; the last plies on an array pinned in place
+                        pl2 = np.ascontiguousarray(pl).copy()
+                        st, er = np.empty(n, np.uint8), np.empty(n, np.uint8)
+                        reg = ply >= 9 and lib().tafl_host_register(A.ptr(pl2), pl2.nbytes) == 0
+                        assert lib().tafl_step_status(g.handle, A.ptr(pl2), A.ptr(st), A.ptr(er)) == 0
+                        if reg:
+                            assert lib().tafl_host_unregister(A.ptr(pl2)) == 0
+                        if ply == 11:   # and the Python mirror (pinned staging inside game_do_play) on a copy of the game
+                            with E.LockstepGames(rules, fen, n, 0, 128) as g2:
+                                g2.set_states(before)
+                                st2, er2 = g2.game_do_play(pl)
+                                assert st2.tobytes() == st.tobytes() and er2.tobytes() == er.tobytes()
+                                assert g2.get_states().tobytes() == g.get_states().tobytes()
                     after = g.get_states()
                     got.append((st.tobytes(), None if er is None else er.tobytes(), after.tobytes()))
                     if label == "in_place" and er is not None:
