@@ -131,13 +131,17 @@ k_step_moves(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ st
 }
 
 // The fused random-playout step (K4): count -> pick -> select -> apply -> outcome, `steps`
-// plies per launch with the state held in registers in between.
-template <class BB, int SP, int MINB>
+// plies per launch with the state held in registers in between.  BYVAL (tafl_step_random_host): the
+// states come from the staged copy of the caller's array (`src`); a row whose side_len is not the
+// engine's is rejected here (flag raised, the game keeps its resident state) instead of by a host
+// loop over 4 MiB of input before anything is enqueued.
+template <class BB, int SP, int MINB, bool BYVAL = false>
 __global__ void __launch_bounds__(STEP_BLOCK, MINB)
 k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
               uint32_t steps, int auto_reset, DevStats* __restrict__ stats, uint32_t* __restrict__ actions,
-              const unsigned long long* __restrict__ ply_base) {
+              const unsigned long long* __restrict__ ply_base, const tafl_state* __restrict__ src = nullptr,
+              uint32_t* __restrict__ rejected = nullptr) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t c_steps = 0, c_legal = 0, c_caps = 0;
     // Programmatic dependent launch (no-ops for a plain launch): wait for the previous ply's grid
@@ -146,8 +150,13 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;");
     if (ply_base) ply0 += *ply_base;
-    if (g < n) {
-        tafl_state s = load_state(states + g);
+    bool live = g < n;
+    if (BYVAL && live && src[g].side_len != (uint8_t)cx.n()) {
+        atomicOr(rejected, 1u);
+        live = false;
+    }
+    if (live) {
+        tafl_state s = load_state((BYVAL ? src : states) + g);
         uint32_t act = 0;   // tafl_action of the last ply of this launch
         for (uint32_t i = 0; i < steps; ++i) {
             act = (uint32_t)s.status << 16;
@@ -720,7 +729,8 @@ static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t firs
 #define TAFL_STEP_LAUNCH(MINB)                                                                                        \
     TAFL_SPEC_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, k_step_random<BB, SP, MINB>, cx, e->d_states + first, n,     \
                                                      state_words(e->start), seed, e->game_id_base + first, ply0, steps, \
-                                                     auto_reset, e->d_stats, e->d_actions + first, d_ply_base)))
+                                                     auto_reset, e->d_stats, e->d_actions + first, d_ply_base,         \
+                                                     (const tafl_state*)nullptr, (uint32_t*)nullptr)))
     switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
         case 4: TAFL_STEP_LAUNCH(4); break;
         case 6: TAFL_STEP_LAUNCH(6); break;
@@ -791,12 +801,21 @@ int tafl_step_random_host(tafl_engine* e, const tafl_state* h_in, tafl_state* h_
     if (!h_in || !h_out) return TAFL_ERR_INVALID_ARG;
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    int rc = check_side_len(e, h_in, n);
-    if (rc) return rc;
+    int rc;
     if (!e->aux_ready) {
         for (auto& st : e->aux) TAFL_CUDA_TRY(e, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         e->aux_ready = true;
     }
+    if (n_steps == 0) {   // set + get: validate on the host, nothing to overlap
+        if ((rc = tafl_set_states(e, h_in, 0, n))) return rc;
+        return tafl_get_states(e, h_out, 0, n);
+    }
+    // rows are staged next to the resident states and validated (side_len) by the step kernel itself
+    void* p;
+    if ((rc = scratch(e, 6, (size_t)n * sizeof(tafl_state) + 16, &p))) return rc;
+    tafl_state* const d_in = (tafl_state*)p;
+    uint32_t* const d_rej = (uint32_t*)(d_in + n);
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(d_rej, 0, sizeof(uint32_t), e->stream));
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     uint32_t chunks = (uint32_t)e->host_chunks;
     if (chunks < 1) chunks = 1;
@@ -806,15 +825,24 @@ int tafl_step_random_host(tafl_engine* e, const tafl_state* h_in, tafl_state* h_
     for (uint32_t first = 0; first < n; first += per, ++c) {
         const uint32_t cnt = (n - first) < per ? (n - first) : per;
         cudaStream_t st = e->aux[c % tafl_engine::N_AUX];
-        TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_states + first, h_in + first, (size_t)cnt * sizeof(tafl_state), cudaMemcpyHostToDevice, st));
-        if (n_steps) {
-            rc = launch_step_random(e, st, first, cnt, seed, e->ply, n_steps, auto_reset);
-            if (rc) return rc;
-        }
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(d_in + first, h_in + first, (size_t)cnt * sizeof(tafl_state), cudaMemcpyHostToDevice, st));
+        cudaError_t lerr = cudaSuccess;
+        TAFL_SPEC_DISPATCH(e, ((k_step_random<BB, SP, 8, true><<<grid_for(cnt, STEP_BLOCK), STEP_BLOCK, 0, st>>>(
+                                   cx, e->d_states + first, cnt, state_words(e->start), seed, e->game_id_base + first, e->ply, n_steps,
+                                   auto_reset, e->d_stats, e->d_actions + first, nullptr, d_in + first, d_rej)),
+                               lerr = cudaGetLastError()));
+        TAFL_CUDA_TRY(e, lerr);
+        e->launches += 1;
         TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_out + first, e->d_states + first, (size_t)cnt * sizeof(tafl_state), cudaMemcpyDeviceToHost, st));
     }
     e->ply += n_steps;
     for (auto& st : e->aux) TAFL_CUDA_TRY(e, cudaStreamSynchronize(st));
+    uint32_t rej = 0;
+    TAFL_CUDA_TRY(e, cudaMemcpy(&rej, d_rej, sizeof(rej), cudaMemcpyDeviceToHost));
+    if (rej) {
+        e->err = "state side_len does not match the engine's board (those games kept their resident state)";
+        return TAFL_ERR_INVALID_ARG;
+    }
     return TAFL_OK;
 }
 int tafl_step_random(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset, int spl) {

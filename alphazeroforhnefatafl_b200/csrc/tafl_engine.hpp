@@ -57,7 +57,7 @@ struct tafl_engine {
     static constexpr int N_AUX = 4;    // streams of the pipelined host-buffer path (tafl_step_random_host)
     cudaStream_t aux[N_AUX] = {nullptr, nullptr, nullptr, nullptr};
     bool aux_ready = false;
-    int host_chunks = 8;
+    int host_chunks = 4;   // profiles/sweeps/r01r_e2e_modes.txt
     int host_io = 3;   // tafl_step_status with pinned caller buffers: bit 0 kernel reads the plays in place, bit 1 writes results in place
     int mcts_minb = 8;                 // k_mcts_sims variant: CTAs of 4 warps resident per SM
     int mcts_group = 16;               // TAFL_MCTS_G: lanes per tree of k_mcts_sims_g (32/16/8); 0 = first-generation k_mcts_sims
@@ -69,8 +69,8 @@ struct tafl_engine {
     struct { uint64_t seed = 0, gid_base = 0; uint32_t steps = 0; int auto_reset = 0, minb = 0, spec = 0; } step_graph_key;
     unsigned long long* d_ply = nullptr;   // RNG ply of the first node of the graph (copied before each launch)
     // scratch for the by-value batch API (grown on demand)
-    void* d_scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t scratch_bytes[6] = {0, 0, 0, 0, 0, 0};
+    void* d_scratch[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratch_bytes[7] = {0, 0, 0, 0, 0, 0, 0};
     tafl::MctsPools* mcts = nullptr;
     tafl::HistView hist;
     std::string err;

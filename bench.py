@@ -381,19 +381,21 @@ def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
     sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0)     # search + first-max move + pack + gather to rank 0
     stream = sp.stream
     moves = 3
-    sp.move()                                              # warm-up move
+    for _ in range(2):                                     # warm-up moves (NCCL channels, allocator blocks of the gather)
+        sp.move()
     s0 = g.mcts_stats().as_dict()
     l0 = g.launches
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(moves + 1)]
     barrier()
-    a.record(stream)
+    marks[0].record(stream)
     n_rec = 0
-    for _ in range(moves):
+    for i in range(moves):
         out = sp.move()
         n_rec += 0 if out is None else out.shape[0]
-    b.record(stream)
+        marks[i + 1].record(stream)
     barrier()
-    ms = a.elapsed_time(b)
+    ms = marks[0].elapsed_time(marks[-1])
+    ms_moves = [marks[i].elapsed_time(marks[i + 1]) for i in range(moves)]
     s1 = g.mcts_stats().as_dict()
     sims = s1["sims"] - s0["sims"]
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
@@ -408,7 +410,7 @@ def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
     hbm_peak, _, _ = peaks()
     res = {"metric": "copenhagen_11x11_mcts_sims_per_s", "value": v, "unit": "sims/s", "trees_per_gpu": n,
            "sims_per_move": args.mcts_sims, "moves_timed": moves, "ms_per_move": float(t.item()) / moves,
-           "mean_depth": d_bar, "mean_edges_per_node": l_bar, "bytes_per_sim_model": b_sim,
+           "ms_each_move_rank0": ms_moves, "mean_depth": d_bar, "mean_edges_per_node": l_bar, "bytes_per_sim_model": b_sim,
            "roofline": {"bound": "hbm", "achieved": v / world * b_sim / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": v / world * b_sim / 1e9 / hbm_peak},
            "records_gathered_on_rank0": int(n_rec), "record_bytes": 1592,

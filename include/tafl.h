@@ -355,7 +355,9 @@ int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int 
  * h_in[n_games] -> resident states -> n_steps plies -> h_out[n_games]; equivalent to tafl_set_states +
  * tafl_step_random + tafl_get_states, with the copies and kernels of successive game chunks
  * overlapped on several streams.  Pinned host memory is needed for the overlap (pageable works,
- * serially).  h_in and h_out may be the same buffer. */
+ * serially).  h_in and h_out may be the same buffer.  Rows are validated on the device: a row whose
+ * side_len is not the engine's is not applied (that game keeps its resident state, which is what
+ * h_out then holds for it) and the call returns TAFL_ERR_INVALID_ARG after the other games stepped. */
 int tafl_step_random_host(tafl_engine* e, const tafl_state* h_in, tafl_state* h_out, uint64_t seed,
                           uint32_t n_steps, int auto_reset);
 /* One word per game describing the most recent ply of tafl_step_random* (the "action" and "status"

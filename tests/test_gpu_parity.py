@@ -11,6 +11,7 @@ import pytest
 import kat_runner
 from alphazeroforhnefatafl_b200 import _abi as A
 from alphazeroforhnefatafl_b200 import engine as E
+from alphazeroforhnefatafl_b200.engine import TaflError
 from parity_cases import PRESET_CONFIGS, board_for, compare_by_value, random_boards, sample_positions
 from product_host import GpuImplFactory, ProductHost
 
@@ -210,6 +211,18 @@ def test_gpu_step_random_host_pipeline(orc, built_lib):
             assert g.get_states().tobytes() == exp.tobytes()
             assert g.stats().as_dict() == exp_stats.as_dict()
             assert g.random_ply == 40
+            if n >= 63:   # a row for another board size is rejected on the device: that game keeps its resident state
+                bad = exp.copy()
+                bad["side_len"][[5, n - 1]] = 9
+                keep = g.get_states()
+                with pytest.raises(TaflError):
+                    g.step_random_host(bad, 5, 1)
+                after = g.get_states()
+                assert after[[5, n - 1]].tobytes() == keep[[5, n - 1]].tobytes()
+                ok = np.ones(n, bool)
+                ok[[5, n - 1]] = False
+                exp2, _ = orc.random_playout(rules, fen, 128, 5, n, 1, game_id_base=9, ply0=40, n_threads=8, states=exp.copy())
+                assert after[ok].tobytes() == exp2[ok].tobytes()
 
 
 @pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS[:3])
