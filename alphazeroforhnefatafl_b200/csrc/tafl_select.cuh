@@ -66,6 +66,28 @@ TAFL_HD BB throne_aligned(int N, int dir, int d) {
     return (r >= 0 && r < N && c >= 0 && c < N) ? BB::bit(r * BB::STRIDE + c) : BB::zero();
 }
 
+// board columns lo..hi of every row as a tile set; folds to an immediate when its arguments are constants
+template <class BB>
+TAFL_HD BB cols_between(int N, int lo, int hi) {
+    BB r = BB::zero();
+    for (int row = 0; row < N; ++row)
+        for (int c = lo; c <= hi; ++c) r = r | BB::bit(row * BB::STRIDE + c);
+    return r;
+}
+// bit-sliced x + y of two 4-plane numbers -> 5 planes
+template <class BB>
+TAFL_HD void add4(const BB (&x)[4], const BB (&y)[4], BB (&out)[5]) {
+    BB c = x[0] & y[0];
+    out[0] = x[0] ^ y[0];
+#pragma unroll
+    for (int i = 1; i < 4; ++i) {
+        const BB u = x[i] ^ y[i];
+        out[i] = u ^ c;
+        c = (x[i] & y[i]) | (c & u);
+    }
+    out[4] = c;
+}
+
 // count legal plays of `def_side`'s pieces on position p (status must be Ongoing)
 template <class BB, int SP>
 TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side) {
@@ -81,39 +103,88 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def
     const BB src = p.kind(k);
     const BB thr = cx.throne;
     const bool noentry = cx.f_noentry(k) != 0, passblk = cx.f_pass_block(k) != 0, slow = cx.f_slow(k) != 0;
-    CsaAcc<BB> acc;
-    acc.init();
-    int n = 0;
+    if constexpr (SP != SPEC_GENERIC) {
+        // Preset rules have no pass-block and no slow pieces, so along one ray the sets E_1 >= E_2 >= ... are
+        // nested and a piece's number of plays that way is the LENGTH of its run: its binary digits come
+        // straight from the nested sets (no adder per distance), and the four directions are then added
+        // bit-sliced.  A non-king piece passes an empty throne without stopping on it (noentry): the run that
+        // crosses the throne is one shorter, which keeps the sets nested if its tail is moved up by one.
+        static_assert(MD <= 10, "digit formulas cover runs of up to 10 tiles");
+        BB dig[4][4];
 #pragma unroll
-    for (int dir = 0; dir < 4; ++dir) {
-        BB X = walk, E = src, T = thr, Tprev = BB::zero();
+        for (int dir = 0; dir < 4; ++dir) {
+            BB X = walk, E = src;
+            BB m[MD + 2];
 #pragma unroll
-        for (int d = 1; d <= MD; ++d) {
-            // X(s) = walkable(s + d*step); T(s) = [s + d*step == throne]
-            if (dir == DIR_VP) X = X.template shr<S>();
-            else if (dir == DIR_VM) X = X.template shl<S>();
-            else if (dir == DIR_HP) X = X.template shr<1>() & cx.not_colL;
-            else X = X.template shl<1>() & cx.not_col0;
-            if constexpr (SP == SPEC_GENERIC) {
-                if (dir == DIR_VP) T = T.template shr<S>();
-                else if (dir == DIR_VM) T = T.template shl<S>();
-                else if (dir == DIR_HP) T = T.template shr<1>();
-                else T = T.template shl<1>();
-            } else {
-                T = throne_aligned<BB>(cx.n(), dir, d);
+            for (int d = 1; d <= MD; ++d) {
+                // X(s) = walkable(s + d*step); sideways the source column must leave room for d steps
+                if (dir == DIR_VP) { X = X.template shr<S>(); E = E & X; }
+                else if (dir == DIR_VM) { X = X.template shl<S>(); E = E & X; }
+                else if (dir == DIR_HP) { X = X.template shr<1>(); E = E & X & cols_between<BB>(cx.n(), 0, cx.n() - 1 - d); }
+                else { X = X.template shl<1>(); E = E & X & cols_between<BB>(cx.n(), d, cx.n() - 1); }
+                m[d] = E;
             }
-            E = E & X;
-            if (passblk) E = E & ~Tprev;                  // logic.rs:194-200
-            BB emit = noentry ? (E & ~T) : E;             // logic.rs:201-206 + play.rs:208-211
-            if (slow && d > 1) emit = BB::zero();         // logic.rs:207-210
-            acc.add(emit, n);
-            ++n;
-            Tprev = T;
+            m[MD + 1] = BB::zero();
+            if (noentry) {
+                BB U = BB::zero();   // sources whose ray has reached the throne by distance d
+#pragma unroll
+                for (int d = 1; d <= MD; ++d) {
+                    U = U | throne_aligned<BB>(cx.n(), dir, d);
+                    m[d] = (m[d] & ~U) | (m[d + 1] & U);
+                }
+            }
+            auto M = [&](int d) { return d <= MD ? m[d] : BB::zero(); };
+            dig[dir][0] = (M(1) & ~M(2)) | (M(3) & ~M(4)) | (M(5) & ~M(6)) | (M(7) & ~M(8)) | (M(9) & ~M(10));
+            dig[dir][1] = (M(2) & ~M(4)) | (M(6) & ~M(8)) | M(10);
+            dig[dir][2] = M(4) & ~M(8);
+            dig[dir][3] = M(8);
         }
+        // (VP + VM) + (HP + HM), ripple-carry over bit planes; a piece has at most 2(N-1) <= 20 plays
+        BB a[5], b[5];
+        add4(dig[0], dig[1], a);
+        add4(dig[2], dig[3], b);
+        BB c = a[0] & b[0];
+        ms.plane[0] = a[0] ^ b[0];
+#pragma unroll
+        for (int i = 1; i < 5; ++i) {
+            ms.plane[i] = a[i] ^ b[i] ^ c;
+            c = (a[i] & b[i]) | (c & (a[i] ^ b[i]));
+        }
+    } else {
+        CsaAcc<BB> acc;
+        acc.init();
+        int n = 0;
+#pragma unroll
+        for (int dir = 0; dir < 4; ++dir) {
+            BB X = walk, E = src, T = thr, Tprev = BB::zero();
+#pragma unroll
+            for (int d = 1; d <= MD; ++d) {
+                // X(s) = walkable(s + d*step); T(s) = [s + d*step == throne]
+                if (dir == DIR_VP) X = X.template shr<S>();
+                else if (dir == DIR_VM) X = X.template shl<S>();
+                else if (dir == DIR_HP) X = X.template shr<1>() & cx.not_colL;
+                else X = X.template shl<1>() & cx.not_col0;
+                if constexpr (SP == SPEC_GENERIC) {
+                    if (dir == DIR_VP) T = T.template shr<S>();
+                    else if (dir == DIR_VM) T = T.template shl<S>();
+                    else if (dir == DIR_HP) T = T.template shr<1>();
+                    else T = T.template shl<1>();
+                } else {
+                    T = throne_aligned<BB>(cx.n(), dir, d);
+                }
+                E = E & X;
+                if (passblk) E = E & ~Tprev;                  // logic.rs:194-200
+                BB emit = noentry ? (E & ~T) : E;             // logic.rs:201-206 + play.rs:208-211
+                if (slow && d > 1) emit = BB::zero();         // logic.rs:207-210
+                acc.add(emit, n);
+                ++n;
+                Tprev = T;
+            }
+        }
+        // flush pending partial sums when the number of inputs is not a multiple of 8 (BB64: 24 = 3*8 ok)
+        ms.plane[0] = acc.ones; ms.plane[1] = acc.twos; ms.plane[2] = acc.fours; ms.plane[3] = acc.eights;
+        ms.plane[4] = acc.sixteens;
     }
-    // flush pending partial sums when the number of inputs is not a multiple of 8 (BB64: 24 = 3*8 ok)
-    ms.plane[0] = acc.ones; ms.plane[1] = acc.twos; ms.plane[2] = acc.fours; ms.plane[3] = acc.eights;
-    ms.plane[4] = acc.sixteens;
     if (def_side && (p.def & p.kbit).any()) {
         Rays r = piece_rays(cx, occ, KIND_K, p.kr, p.kc);
         int ck = r.cnt[0] + r.cnt[1] + r.cnt[2] + r.cnt[3];
