@@ -497,21 +497,20 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
     else if (to_c == 0) { horizontal = 0; away = 1; }
     else if (to_c == N - 1) { horizontal = 0; away = -1; }
     else return false;
-    const BB own = p.side(mover_def), opp = p.side(!mover_def), occ = p.occ();
+    const BB own = p.side(mover_def), opp = p.side(!mover_def);
     {   // Exact pre-filter.  The search counts enemy pieces pinned by a piece of the mover, walking
         // away from `to` along the edge, and needs cnt >= 2 (logic.rs:485-522); any other tile ends
         // the run.  So a wall exists only if the first TWO tiles on one side of `to` are both pinned
-        // enemies — a mask test; the tile-by-tile walk below then runs for real candidates only.
-        const BB tb0 = BB::bit(idx_of<BB>(to_r, to_c));
-        const BB pinned = opp & (horizontal ? (away > 0 ? step_up(cx, own) : step_down(cx, own))
-                                            : (away > 0 ? step_left(cx, own) : step_right(cx, own)));
-        const BB m1 = horizontal ? step_left(cx, tb0) : step_up(cx, tb0);
-        const BB m2 = horizontal ? step_left(cx, m1) : step_up(cx, m1);
-        const BB p1 = horizontal ? step_right(cx, tb0) : step_down(cx, tb0);
-        const BB p2 = horizontal ? step_right(cx, p1) : step_down(cx, p1);
-        const bool minus = (pinned & m1).any() && (pinned & m2).any();
-        const bool plus = (pinned & p1).any() && (pinned & p2).any();
-        if (!(minus || plus)) return false;
+        // enemies: eight single-tile tests in index arithmetic (this runs at ~8 lanes of every warp, so
+        // it is kept to a few dozen instructions); the tile-by-tile walk runs for real candidates only.
+        const int t = idx_of<BB>(to_r, to_c);
+        const int de = horizontal ? 1 : BB::STRIDE;               // along the edge
+        const int in = (horizontal ? BB::STRIDE : 1) * away;      // from the edge tile to its inward neighbour
+        const int x = horizontal ? to_c : to_r;                   // position along the edge
+        auto pinned = [&](int i) { return opp.test(i) & own.test(i + in); };
+        const bool minus = (x >= 2) & pinned(t - de) & pinned(t - 2 * de);
+        const bool plus = (x + 2 <= N - 1) & pinned(t + de) & pinned(t + 2 * de);
+        if (!(minus | plus)) return false;
     }
     return shieldwall_walk(cx, p, mover_def, to_r, to_c, horizontal, away, caps);
 }
