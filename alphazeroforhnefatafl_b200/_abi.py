@@ -7,7 +7,7 @@ import ctypes as C
 import numpy as np
 
 MAX_MOVES = 512
-REC_MOVES = 256
+REC_MOVES = MAX_MOVES
 REC_STRIDE = 56 + 2 * REC_MOVES + 4 * REC_MOVES
 
 ATTACKER, DEFENDER = 0, 8

@@ -132,6 +132,9 @@ def lib():
         "tafl_leaf_batch_host": (C.c_int, [vp, vp, vp, vp, vp]),
         "tafl_leaf_eval_host": (C.c_int, [vp, vp, vp]),
         "tafl_pack_records": (C.c_int, [vp, vp]),
+        "tafl_pack_records_compact": (C.c_int, [vp, vp, vp, vp]),
+        "tafl_reset_finished": (C.c_int, [vp, C.POINTER(C.c_uint32)]),
+        "tafl_mcts_overflow": (C.c_int, [vp, C.POINTER(C.c_uint32)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol

@@ -51,15 +51,25 @@ NcclApi& nccl() {
         api.h = dlopen(n, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
         if (api.h) break;
     }
+    std::string why;   // dlerror() of every failed attempt (the call clears the message, so read it once each)
+    auto try_open = [&](const char* path) {
+        dlerror();
+        void* h = dlopen(path, RTLD_NOW | RTLD_GLOBAL);
+        if (!h) {
+            const char* de = dlerror();
+            why += std::string(why.empty() ? "" : "; ") + path + ": " + (de ? de : "dlopen failed");
+        }
+        return h;
+    };
     if (!api.h) {
-        if (const char* p = std::getenv("TAFL_NCCL_LIB")) api.h = dlopen(p, RTLD_NOW | RTLD_GLOBAL);
+        if (const char* p = std::getenv("TAFL_NCCL_LIB")) api.h = try_open(p);
         for (const char* n : names) {
             if (api.h) break;
-            api.h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            api.h = try_open(n);
         }
     }
     if (!api.h) {
-        api.err = std::string("libnccl.so.2 not found (set TAFL_NCCL_LIB): ") + (dlerror() ? dlerror() : "");
+        api.err = "libnccl.so.2 not found (set TAFL_NCCL_LIB): " + why;
         return api;
     }
 #define TAFL_BIND(field, sym)                                                   \
@@ -149,27 +159,44 @@ int tafl_gather_records(tafl_engine* e, void* comm_, int n_ranks, int rank, int 
         TAFL_CUDA_TRY(e, cudaMalloc(&d_sink, (size_t)total * TAFL_REC_STRIDE));
         d_recv = d_sink;
     }
-    // 2. payload: every rank -> root, rows land at their final offset (rank order == game-id order)
-    TAFL_NCCL_TRY(e, n.GroupStart());
-    if (rank == root) {
-        uint64_t off = 0;
-        for (int r = 0; r < n_ranks; ++r) {
-            const size_t bytes = (size_t)h_counts[r] * TAFL_REC_STRIDE;
-            if (bytes) {
-                if (r == root)
-                    TAFL_CUDA_TRY(e, cudaMemcpyAsync((char*)d_recv + off, d_send, bytes, cudaMemcpyDeviceToDevice, e->stream));
-                else
-                    TAFL_NCCL_TRY(e, n.Recv((char*)d_recv + off, bytes, kUint8, r, comm, e->stream));
-            }
-            off += bytes;
-        }
-    } else if (n_local) {
-        TAFL_NCCL_TRY(e, n.Send(d_send, (size_t)n_local * TAFL_REC_STRIDE, kUint8, root, comm, e->stream));
+    // 2. payload: every rank -> root, rows land at their final offset (rank order == game-id order).
+    // Nothing returns from inside the group: the first error is kept, ncclGroupEnd always runs (an open
+    // group would poison every later collective of this thread), then the sink is released.
+    cudaError_t cerr = cudaSuccess;
+    ncclResult_t nerr = 0;
+    const char* nwhat = "";
+    uint64_t own_off = 0;
+    if (rank == root && n_local) {   // the root's own rows: a plain device copy, outside the group
+        for (int r = 0; r < root; ++r) own_off += (uint64_t)h_counts[r] * TAFL_REC_STRIDE;
+        cerr = cudaMemcpyAsync((char*)d_recv + own_off, d_send, (size_t)n_local * TAFL_REC_STRIDE, cudaMemcpyDeviceToDevice, e->stream);
     }
-    TAFL_NCCL_TRY(e, n.GroupEnd());
+    nerr = n.GroupStart();
+    if (nerr) nwhat = "ncclGroupStart";
+    else {
+        if (rank == root) {
+            uint64_t off = 0;
+            for (int r = 0; r < n_ranks; ++r) {
+                const size_t bytes = (size_t)h_counts[r] * TAFL_REC_STRIDE;
+                if (bytes && r != root && !nerr) {
+                    nerr = n.Recv((char*)d_recv + off, bytes, kUint8, r, comm, e->stream);
+                    if (nerr) nwhat = "ncclRecv";
+                }
+                off += bytes;
+            }
+        } else if (n_local) {
+            nerr = n.Send(d_send, (size_t)n_local * TAFL_REC_STRIDE, kUint8, root, comm, e->stream);
+            if (nerr) nwhat = "ncclSend";
+        }
+        const ncclResult_t gerr = n.GroupEnd();
+        if (!nerr && gerr) { nerr = gerr; nwhat = "ncclGroupEnd"; }
+    }
     if (d_sink) {
         cudaStreamSynchronize(e->stream);
         cudaFree(d_sink);
+    }
+    if (cerr != cudaSuccess) return set_cuda_error(e, cerr, "cudaMemcpyAsync(root rows)");
+    if (nerr) return nccl_fail(e, nerr, nwhat);
+    if (d_sink) {
         e->err = "tafl_gather_records: receive buffer too small on the root (h_counts holds the rows per rank)";
         return TAFL_ERR_CAPACITY;
     }

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "tafl_engine.hpp"
+#include "tafl_mcts.cuh"
 #include "tafl_select.cuh"
 
 using namespace tafl;
@@ -21,23 +22,50 @@ constexpr int STEP_BLOCK = 64;   // threads per CTA for the per-game kernels (se
 // NOTE: the start position travels as StateWords (plain uint4 words) and is rebuilt with
 // unpack_state: assigning a tafl_state kernel parameter to a local that is modified afterwards
 // (`s = start` on auto-reset) made nvcc 12.9 reload att[0] from the parameter at the final store.
-__global__ void k_fill_states(tafl_state* __restrict__ states, uint32_t n, const __grid_constant__ StateWords start) {
+// `episode` (may be null): the restart counter of each game id, bumped whenever its game starts over
+__global__ void k_fill_states(tafl_state* __restrict__ states, uint32_t n, const __grid_constant__ StateWords start,
+                              uint32_t* __restrict__ episode) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g < n) {
         uint4* q = reinterpret_cast<uint4*>(states + g);
         q[0] = start.v[0]; q[1] = start.v[1]; q[2] = start.v[2]; q[3] = start.v[3];
+        if (episode) episode[g] += 1u;
     }
 }
 __global__ void k_reset_ids(tafl_state* __restrict__ states, const uint32_t* __restrict__ ids, uint32_t n,
-                            uint32_t n_games, const __grid_constant__ StateWords start) {
+                            uint32_t n_games, const __grid_constant__ StateWords start, uint32_t* __restrict__ episode) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && ids[i] < n_games) {
         uint4* q = reinterpret_cast<uint4*>(states + ids[i]);
         q[0] = start.v[0]; q[1] = start.v[1]; q[2] = start.v[2]; q[3] = start.v[3];
+        atomicAdd(&episode[ids[i]], 1u);   // an id may be listed twice
     }
 }
+__global__ void k_bump_episodes(uint32_t* __restrict__ episode, uint32_t first, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) episode[first + i] += 1u;
+}
+// restart every finished game (self-play sweep: all trees stay busy); counts the restarts
+__global__ void k_reset_finished(tafl_state* __restrict__ states, uint32_t n, const __grid_constant__ StateWords start,
+                                 uint32_t* __restrict__ episode, HistView hv, uint32_t* __restrict__ n_reset) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    bool hit = false;
+    if (g < n) {
+        const uint32_t meta = reinterpret_cast<const uint4*>(states + g)[3].x;
+        if ((meta >> 24) != TAFL_STATUS_ONGOING) {
+            hit = true;
+            uint4* q = reinterpret_cast<uint4*>(states + g);
+            q[0] = start.v[0]; q[1] = start.v[1]; q[2] = start.v[2]; q[3] = start.v[3];
+            episode[g] += 1u;
+            if (hv.st) { hv.len[g] = 0; hv.floor[g] = 0; }
+        }
+    }
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(n_reset, (uint32_t)__popc(m));
+}
 
-// get_all_possible_moves (game/main.rs:33-43), one game per thread
+// get_all_possible_moves (game/main.rs:33-43), one game per thread: first-generation kernel, kept as the
+// comparison point (TAFL_LM_G=1): scalar u16 stores, consecutive lanes write 1 KB apart.
 template <class BB>
 __global__ void __launch_bounds__(STEP_BLOCK)
 k_legal_moves(const __grid_constant__ Ctx<BB> cx, const tafl_state* __restrict__ states, uint32_t n,
@@ -46,6 +74,76 @@ k_legal_moves(const __grid_constant__ Ctx<BB> cx, const tafl_state* __restrict__
     if (g >= n) return;
     tafl_state s = load_state(states + g);
     counts[g] = (uint32_t)gen_moves(cx, s, moves + (size_t)g * TAFL_MAX_MOVES, TAFL_MAX_MOVES);
+}
+
+// get_all_possible_moves (game/main.rs:33-43 over ValidPlayIterator, play.rs:186-226), warp-cooperative:
+// a group of G lanes owns one game.  Lane i takes the i-th piece of the side to move (ascending bit
+// index = canonical order) and gets its four ray lengths from piece_rays; a __shfl_up prefix sum over
+// the per-piece totals gives every lane the list offset of its piece; each lane writes its piece's
+// plays (tile arithmetic, no per-move decode) into the game's shared-memory row; the group then copies
+// the row out with 16-byte vector stores, consecutive lanes writing consecutive addresses — the list
+// leaves the SM as full 32-byte sectors instead of the 2-byte scatter of the thread-per-game kernel.
+constexpr int LM_BLOCK = 128;
+template <class BB, int SP, int G>
+__global__ void __launch_bounds__(LM_BLOCK)
+k_legal_moves_g(const __grid_constant__ Ctx<BB, SP> cx, const tafl_state* __restrict__ states, uint32_t n,
+                tafl_move* __restrict__ moves, uint32_t* __restrict__ counts) {
+    constexpr int GPB = LM_BLOCK / G;   // games per CTA
+    constexpr int S = BB::STRIDE;
+    __shared__ __align__(16) tafl_move rows[GPB][TAFL_MAX_MOVES];
+    const int lane = threadIdx.x & 31, gl = lane % G, gshift = (lane / G) * G;
+    const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << (G & 31)) - 1u) << gshift);
+    const int slot = threadIdx.x / G;
+    const uint32_t g_raw = blockIdx.x * GPB + (uint32_t)slot;
+    const bool live = g_raw < n;
+    const uint32_t g = live ? g_raw : n - 1u;   // a dead group mirrors the last game and writes nothing
+    tafl_move* const row = rows[slot];
+    // the lanes of a group read the same three words: one transaction per word, broadcast by the LSU
+    const uint4* const q = reinterpret_cast<const uint4*>(states + g);
+    const uint4 a = q[0], d = q[1];
+    const uint32_t meta = q[3].x;
+    tafl_state st;
+    st.att[0] = (uint64_t)a.x | ((uint64_t)a.y << 32); st.att[1] = (uint64_t)a.z | ((uint64_t)a.w << 32);
+    st.def[0] = (uint64_t)d.x | ((uint64_t)d.y << 32); st.def[1] = (uint64_t)d.z | ((uint64_t)d.w << 32);
+    const bool ongoing = (meta >> 24) == TAFL_STATUS_ONGOING;   // logic.rs:165-167: a finished game has no plays
+    const int def_side = ((meta >> 16) & TAFL_FLAG_DEF_TO_PLAY) != 0;
+    const Pos<BB> p = load_pos(cx, st);
+    const BB own = p.side(def_side), occ = p.occ();
+    const int n_pieces = ongoing ? own.popc() : 0;
+    int before = 0;
+    for (int base = 0; base < n_pieces; base += G) {
+        const int idx = base + gl;
+        int c = 0, tile = 0, row_i = 0, col_i = 0, kind = KIND_AS;
+        Rays r;
+        r.cnt[0] = r.cnt[1] = r.cnt[2] = r.cnt[3] = 0;
+        if (idx < n_pieces) {
+            tile = nth_set_bit(own, idx);
+            row_i = tile / S;
+            col_i = tile - row_i * S;
+            kind = def_side ? ((BB::bit(tile) == p.kbit) ? KIND_K : KIND_DS) : KIND_AS;
+            r = piece_rays(cx, occ, kind, row_i, col_i);
+            c = r.cnt[0] + r.cnt[1] + r.cnt[2] + r.cnt[3];
+        }
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) {
+            const int t = __shfl_up_sync(gmask, incl, o, G);
+            if (gl >= o) incl += t;
+        }
+        emit_piece_plays(cx, tile, row_i, col_i, kind, r, row, before + incl - c, TAFL_MAX_MOVES);
+        before += __shfl_sync(gmask, incl, G - 1, G);
+    }
+    const int L = before;   // the same on every lane of the group
+    const int Lc = L < TAFL_MAX_MOVES ? L : TAFL_MAX_MOVES;
+    if (gl < 8 && Lc + gl < ((Lc + 7) & ~7)) row[Lc + gl] = 0;   // the unused tail of the last vector
+    __syncwarp(gmask);
+    if (live) {
+        const uint4* const src = reinterpret_cast<const uint4*>(row);
+        uint4* const dst = reinterpret_cast<uint4*>(moves + (size_t)g * TAFL_MAX_MOVES);
+        const int nvec = (Lc + 7) >> 3;
+        for (int v = gl; v < nvec; v += G) dst[v] = src[v];
+        if (gl == 0) counts[g] = (uint32_t)L;
+    }
 }
 
 // Game::do_play (game/mod.rs:95-101) with validation.  HostMirror: the caller's pinned result buffers,
@@ -321,6 +419,16 @@ int scratch(tafl_engine* e, int slot, size_t bytes, void** out) {
         TAFL_CUDA_TRY((e), cudaGetLastError());                          \
     } while (0)
 
+// Game::do_play is the reference's only mutator, so its histories are always complete (game/mod.rs:95-108).
+// The batch mutators that have no reference counterpart (random stepping, compact-move stepping, the MCTS
+// move) do not record plays; they forget the history of the games they advance instead of leaving a
+// history with holes behind (tafl_undo_last_play then has nothing to undo, as after tafl_set_states).
+namespace tafl {
+void hist_forget_all(tafl_engine* e) {
+    if (e->hist.st) k_hist_clear<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->hist, 0, e->n_games, nullptr);
+}
+}  // namespace tafl
+
 static int sync_engine(tafl_engine* e) {
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     return TAFL_OK;
@@ -418,6 +526,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     if (const char* v = std::getenv("TAFL_HOST_IO")) e->host_io = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_MINB")) e->mcts_minb = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_G")) e->mcts_group = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_LM_G")) e->lm_group = std::atoi(v);
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_states, (size_t)n_games * sizeof(tafl_state)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_counts, (size_t)n_games * sizeof(uint32_t)));
@@ -426,8 +535,10 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     TAFL_CREATE_TRY(cudaMemsetAsync(e->d_actions, 0, (size_t)n_games * sizeof(uint32_t), e->stream));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_stats, sizeof(DevStats)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_checksum, sizeof(unsigned long long)));
+    TAFL_CREATE_TRY(cudaMalloc(&e->d_episode, (size_t)n_games * sizeof(uint32_t)));
+    TAFL_CREATE_TRY(cudaMemsetAsync(e->d_episode, 0, (size_t)n_games * sizeof(uint32_t), e->stream));
     TAFL_CREATE_TRY(cudaMemsetAsync(e->d_stats, 0, sizeof(DevStats), e->stream));
-    k_fill_states<<<grid_for(n_games, 256), 256, 0, e->stream>>>(e->d_states, n_games, state_words(e->start));
+    k_fill_states<<<grid_for(n_games, 256), 256, 0, e->stream>>>(e->d_states, n_games, state_words(e->start), nullptr);
     e->launches += 1;
     TAFL_CREATE_TRY(cudaGetLastError());
     TAFL_CREATE_TRY(cudaStreamSynchronize(e->stream));
@@ -442,7 +553,7 @@ int tafl_engine_destroy(tafl_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     mcts_free(e);
     cudaFree(e->d_states); cudaFree(e->d_moves); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_actions);
-    cudaFree(e->d_stats); cudaFree(e->d_checksum); cudaFree(e->d_ply);
+    cudaFree(e->d_stats); cudaFree(e->d_checksum); cudaFree(e->d_ply); cudaFree(e->d_episode);
     cudaFree(e->hist.st); cudaFree(e->hist.rec); cudaFree(e->hist.len); cudaFree(e->hist.floor);
     if (e->step_graph) cudaGraphExecDestroy(e->step_graph);
     for (auto& p : e->d_scratch) cudaFree(p);
@@ -476,14 +587,14 @@ int tafl_reset(tafl_engine* e, const uint32_t* h_ids, uint32_t n) {
     TAFL_CHECK_E(e);
     cudaSetDevice(e->device);
     if (!h_ids) {
-        k_fill_states<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, state_words(e->start));
+        k_fill_states<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, state_words(e->start), e->d_episode);
         TAFL_LAUNCHED(e);
         if (e->hist.st) k_hist_clear<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->hist, 0, e->n_games, nullptr);
     } else if (n) {
         uint32_t* d_ids;
         int rc = upload(e, 0, h_ids, n, &d_ids);
         if (rc) return rc;
-        k_reset_ids<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_states, d_ids, n, e->n_games, state_words(e->start));
+        k_reset_ids<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_states, d_ids, n, e->n_games, state_words(e->start), e->d_episode);
         TAFL_LAUNCHED(e);
         if (e->hist.st) k_hist_clear<<<grid_for(n, 256), 256, 0, e->stream>>>(e->hist, 0, n, d_ids);
     }
@@ -496,8 +607,25 @@ int tafl_set_states(tafl_engine* e, const tafl_state* h, uint32_t first, uint32_
     int rc = check_side_len(e, h, n);
     if (rc) return rc;
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_states + first, h, (size_t)n * sizeof(tafl_state), cudaMemcpyHostToDevice, e->stream));
+    if (n) k_bump_episodes<<<grid_for(n, 256), 256, 0, e->stream>>>(e->d_episode, first, n);   // replaced positions start new episodes
     if (e->hist.st && n) k_hist_clear<<<grid_for(n, 256), 256, 0, e->stream>>>(e->hist, first, n, nullptr);
     return sync_engine(e);
+}
+int tafl_reset_finished(tafl_engine* e, uint32_t* h_n) {
+    TAFL_CHECK_E(e);
+    cudaSetDevice(e->device);
+    void* p;
+    int rc = scratch(e, 4, sizeof(uint32_t), &p);
+    if (rc) return rc;
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(p, 0, sizeof(uint32_t), e->stream));
+    k_reset_finished<<<grid_for(e->n_games, 256), 256, 0, e->stream>>>(e->d_states, e->n_games, state_words(e->start), e->d_episode,
+                                                                      e->hist, (uint32_t*)p);
+    TAFL_LAUNCHED(e);
+    if (h_n) {
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_n, p, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+        return sync_engine(e);
+    }
+    return TAFL_OK;
 }
 int tafl_get_states(tafl_engine* e, tafl_state* h, uint32_t first, uint32_t n) {
     TAFL_CHECK_E(e);
@@ -521,7 +649,14 @@ int tafl_moves_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_counts) 
     return TAFL_OK;
 }
 static int legal_moves_enqueue(tafl_engine* e, const tafl_state* d_states, uint32_t n, tafl_move* d_moves, uint32_t* d_counts) {
-    TAFL_WIDTH_DISPATCH(e, (k_legal_moves<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, d_states, n, d_moves, d_counts)));
+    if (n == 0) return TAFL_OK;
+    if (e->lm_group == 16) {          // lanes per game (TAFL_LM_G)
+        TAFL_SPEC_DISPATCH(e, (k_legal_moves_g<BB, SP, 16><<<grid_for(n, LM_BLOCK / 16), LM_BLOCK, 0, e->stream>>>(cx, d_states, n, d_moves, d_counts)));
+    } else if (e->lm_group == 8) {
+        TAFL_SPEC_DISPATCH(e, (k_legal_moves_g<BB, SP, 8><<<grid_for(n, LM_BLOCK / 8), LM_BLOCK, 0, e->stream>>>(cx, d_states, n, d_moves, d_counts)));
+    } else {                          // first generation: one game per thread
+        TAFL_WIDTH_DISPATCH(e, (k_legal_moves<BB><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, d_states, n, d_moves, d_counts)));
+    }
     TAFL_LAUNCHED(e);
     return TAFL_OK;
 }
@@ -637,6 +772,7 @@ int tafl_step_moves_device(tafl_engine* e, const tafl_move* d_moves, uint8_t* d_
     const uint32_t n = e->n_games;
     TAFL_SPEC_DISPATCH(e, (k_step_moves<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_moves, 1u, nullptr, d_status)));
     TAFL_LAUNCHED(e);
+    hist_forget_all(e);   // only Game::do_play (tafl_step / tafl_step_status) records history
     return sync_engine(e);
 }
 
@@ -779,6 +915,7 @@ int tafl_step_random_async(tafl_engine* e, uint64_t seed, uint32_t n_steps, int 
     TAFL_CHECK_E(e);
     cudaSetDevice(e->device);
     if (spl <= 0) spl = 1;
+    if (n_steps) hist_forget_all(e);
     if (spl == 1 && n_steps >= 4 && e->step_graph_on) return step_graph_launch(e, seed, n_steps, auto_reset);
     uint32_t done = 0;
     while (done < n_steps) {
@@ -810,6 +947,7 @@ int tafl_step_random_host(tafl_engine* e, const tafl_state* h_in, tafl_state* h_
         if ((rc = tafl_set_states(e, h_in, 0, n))) return rc;
         return tafl_get_states(e, h_out, 0, n);
     }
+    hist_forget_all(e);
     // rows are staged next to the resident states and validated (side_len) by the step kernel itself
     void* p;
     if ((rc = scratch(e, 6, (size_t)n * sizeof(tafl_state) + 16, &p))) return rc;

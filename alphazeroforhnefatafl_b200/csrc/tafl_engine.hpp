@@ -48,6 +48,7 @@ struct tafl_engine {
     tafl_move* d_moves = nullptr;      // [n_games][TAFL_MAX_MOVES]
     uint32_t* d_counts = nullptr;      // [n_games]
     uint8_t* d_status = nullptr;       // [n_games]
+    uint32_t* d_episode = nullptr;     // [n_games] restarts of each game id (record header: (game_id, episode) names an episode)
     uint32_t* d_actions = nullptr;     // [n_games] tafl_action of the last random ply
     tafl::DevStats* d_stats = nullptr;
     unsigned long long* d_checksum = nullptr;
@@ -61,6 +62,7 @@ struct tafl_engine {
     int host_io = 3;   // tafl_step_status with pinned caller buffers: bit 0 kernel reads the plays in place, bit 1 writes results in place
     int mcts_minb = 8;                 // k_mcts_sims variant: CTAs of 4 warps resident per SM
     int mcts_group = 16;               // TAFL_MCTS_G: lanes per tree of k_mcts_sims_g (32/16/8); 0 = first-generation k_mcts_sims
+    int lm_group = 8;                  // TAFL_LM_G: lanes per game of k_legal_moves_g (16/8); 1 = thread-per-game k_legal_moves
     int step_minb = 8;                 // k_step_random variant: CTAs of 64 threads resident per SM (8: one wave for 65 536 games)
     // lockstep plies as ONE CUDA graph of n_steps kernel nodes joined by programmatic (PDL) edges
     int step_graph_on = 1;             // TAFL_STEP_GRAPH=0 falls back to plain launches
@@ -81,6 +83,7 @@ namespace tafl {
 int set_cuda_error(tafl_engine* e, cudaError_t ce, const char* what);
 int scratch(tafl_engine* e, int slot, size_t bytes, void** out);
 void mcts_free(tafl_engine* e);
+void hist_forget_all(tafl_engine* e);   // tafl_engine.cu
 
 #define TAFL_CUDA_TRY(e, call)                                              \
     do {                                                                    \

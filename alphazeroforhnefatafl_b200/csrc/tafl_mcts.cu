@@ -25,6 +25,7 @@ struct MctsPools {
     double* r_probs = nullptr;        // [n_games][TAFL_MAX_MOVES], allocated by the first tafl_mcts_policy
     uint32_t* remap = nullptr;        // [n_games][node_cap] scratch of k_mcts_reroot (tree reuse only)
     uint32_t* d_any_overflow = nullptr;
+    uint32_t* row_of = nullptr;       // [n_games + 1] compacted record row of each game (+ the row count), tafl_pack_records_compact
     bool searched = false;
     // evaluator hook (tafl_mcts_begin / select_leaves / expand_backup): the leaf batch of one round
     tafl_state* l_state = nullptr;    // [n_games]
@@ -55,6 +56,8 @@ namespace {
 constexpr int MCTS_WARPS = 4;                 // trees per CTA
 constexpr double MCTS_EPS = 1e-8;             // mcts.py:6
 enum { ST_SIMS = 0, ST_NODES, ST_DEPTH, ST_EDGES, ST_TERMINAL, ST_MAXEDGES, ST_COUNT };
+// why a tree stopped (t_overflow[tree], OR-ed into the engine-wide word that the host reads)
+enum { OVF_EDGES = 1u, OVF_NODES = 2u, OVF_PIECES = 4u };
 
 // fresh tree per game, rooted at the game's current state (MCTS.__init__ + first getActionProb)
 __global__ void k_mcts_init(const tafl_state* __restrict__ states, uint32_t n, MctsView mv) {
@@ -162,7 +165,7 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
     uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
     MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
     uint32_t n_nodes = mv.t_nodes[tree], n_edges_used = mv.t_edges[tree];
-    bool overflow = mv.t_overflow[tree] != 0;
+    uint32_t overflow = mv.t_overflow[tree];
     unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_edges = 0, c_term = 0;
 
     for (uint32_t sim = 0; sim < sims && !overflow; ++sim) {
@@ -185,7 +188,10 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
                 int n_pieces;
                 const int L = warp_build_ptab(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0,
                                               n_ptab + (size_t)node * MCTS_PT_MAX, lane, &n_pieces);
-                if ((uint32_t)L > mv.edge_cap - n_edges_used || n_pieces > MCTS_PT_MAX) { overflow = true; break; }
+                if ((uint32_t)L > mv.edge_cap - n_edges_used || n_pieces > MCTS_PT_MAX) {
+                    overflow = n_pieces > MCTS_PT_MAX ? OVF_PIECES : OVF_EDGES;
+                    break;
+                }
                 MctsEdge z;
                 z.Q = 0.0; z.N = 0u; z.child = 0u;   // Nsa absent == 0
                 for (int a = lane; a < L; a += 32) edges[n_edges_used + a] = z;
@@ -209,7 +215,7 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
                 tafl_state s = load_state(n_state + node);
                 const tafl_move m = warp_decode_edge(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
                                                      (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)a, lane);
-                if (n_nodes >= mv.node_cap) { overflow = true; break; }   // only reachable with tree reuse
+                if (n_nodes >= mv.node_cap) { overflow = OVF_NODES; break; }   // only reachable with tree reuse
                 do_valid_move(cx, s, m);
                 child = n_nodes++;
                 c_nodes += 1;
@@ -233,7 +239,7 @@ k_mcts_sims(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tree
     if (lane == 0) {
         mv.t_nodes[tree] = n_nodes;
         mv.t_edges[tree] = n_edges_used;
-        if (overflow) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+        if (overflow) { mv.t_overflow[tree] = overflow; atomicOr(any_overflow, overflow); }
         atomicAdd(&mv.stats[ST_SIMS], c_sims);
         atomicAdd(&mv.stats[ST_NODES], c_nodes);
         atomicAdd(&mv.stats[ST_DEPTH], c_depth);
@@ -340,8 +346,8 @@ k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tr
     uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
     MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
     uint32_t n_nodes = mv.t_nodes[tree], n_edges_used = mv.t_edges[tree];
-    bool overflow = mv.t_overflow[tree] != 0;
-    bool stop = !live || overflow;   // a stopped group only keeps the warp-wide convergence points
+    uint32_t overflow = mv.t_overflow[tree];
+    bool stop = !live || overflow != 0;   // a stopped group only keeps the warp-wide convergence points
     unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_edges = 0, c_term = 0;
 
     for (uint32_t sim = 0; sim < sims; ++sim) {
@@ -386,7 +392,7 @@ k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tr
             bool expand = true;
             if (mode == M_CREATE) {   // getNextState (mcts.py:122-123)
                 if (n_nodes >= mv.node_cap) {   // only reachable with tree reuse
-                    overflow = true;
+                    overflow = OVF_NODES;
                     expand = false;
                 } else {
                     const tafl_move m = grp_decode_edge<G>(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
@@ -417,7 +423,7 @@ k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tr
                 const int L = grp_build_ptab<G>(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, n_ptab + (size_t)target * MCTS_PT_MAX, gmask,
                                                 gl, &n_pieces);
                 if ((uint32_t)L > mv.edge_cap - n_edges_used || n_pieces > MCTS_PT_MAX) {
-                    overflow = true;
+                    overflow = n_pieces > MCTS_PT_MAX ? OVF_PIECES : OVF_EDGES;
                     if (mode == M_CREATE && gl == 0) n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack(0, pedge, 0, es));
                 } else {
                     if (gl == 0) {
@@ -444,7 +450,7 @@ k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tr
     if (gl == 0 && live) {
         mv.t_nodes[tree] = n_nodes;
         mv.t_edges[tree] = n_edges_used;
-        if (overflow) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+        if (overflow) { mv.t_overflow[tree] = overflow; atomicOr(any_overflow, overflow); }
         atomicAdd(&mv.stats[ST_SIMS], c_sims);
         atomicAdd(&mv.stats[ST_NODES], c_nodes);
         atomicAdd(&mv.stats[ST_DEPTH], c_depth);
@@ -742,15 +748,21 @@ k_mcts_play_best(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict_
 }
 
 // one replay-buffer row per game: header (root position, side, chosen move, status after it) +
-// root moves + visit counts, fixed stride (include/tafl.h TAFL_REC_STRIDE); one warp per game
+// root moves + visit counts, fixed stride (include/tafl.h TAFL_REC_STRIDE); one warp per game.
+// `row_of` (may be null): compacted row index of each game, 0xFFFFFFFF = the game emits no row.
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
 k_pack_records(MctsView mv, const tafl_state* __restrict__ states, uint32_t n, uint64_t gid_base,
                const tafl_move* __restrict__ r_moves, const uint32_t* __restrict__ r_visits,
-               const uint32_t* __restrict__ r_counts, const uint32_t* __restrict__ r_best, uint8_t* __restrict__ out) {
+               const uint32_t* __restrict__ r_counts, const uint32_t* __restrict__ r_best,
+               const uint32_t* __restrict__ episode, const uint32_t* __restrict__ row_of, uint8_t* __restrict__ out) {
+    static_assert(TAFL_REC_MOVES == TAFL_MAX_MOVES, "a record row holds every legal move of its root");
+    static_assert(sizeof(tafl_record_header) == 56 && TAFL_REC_STRIDE % 8 == 0, "record layout");
     const int lane = threadIdx.x & 31;
     const uint32_t g = blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5);
     if (g >= n) return;
-    uint8_t* rec = out + (size_t)g * TAFL_REC_STRIDE;
+    const uint32_t row = row_of ? row_of[g] : g;
+    if (row == 0xFFFFFFFFu) return;
+    uint8_t* rec = out + (size_t)row * TAFL_REC_STRIDE;
     const uint32_t cnt = r_counts[g];
     if (lane == 0) {
         const tafl_state root = load_state(mv.n_state + (size_t)g * mv.node_cap);
@@ -763,14 +775,54 @@ k_pack_records(MctsView mv, const tafl_state* __restrict__ states, uint32_t n, u
         h.status = cur.status;
         h.att[0] = root.att[0]; h.att[1] = root.att[1]; h.def[0] = root.def[0]; h.def[1] = root.def[1];
         h.best = (uint16_t)r_best[g];
-        h._pad[0] = h._pad[1] = h._pad[2] = 0;
+        h._pad = 0;
+        h.episode = episode[g];
         *reinterpret_cast<tafl_record_header*>(rec) = h;
     }
-    uint16_t* mo = reinterpret_cast<uint16_t*>(rec + sizeof(tafl_record_header));
-    uint32_t* vo = reinterpret_cast<uint32_t*>(rec + sizeof(tafl_record_header) + 2 * TAFL_REC_MOVES);
-    for (uint32_t a = lane; a < TAFL_REC_MOVES; a += 32) {
-        mo[a] = a < cnt ? r_moves[(size_t)g * TAFL_MAX_MOVES + a] : (uint16_t)0;
-        vo[a] = a < cnt ? r_visits[(size_t)g * TAFL_MAX_MOVES + a] : 0u;
+    // 8-byte vectors: 4 moves / 2 visit counts per lane per store (rows are 8-byte aligned: 56 + 2*512 + 4*512)
+    const uint2* const ms = reinterpret_cast<const uint2*>(r_moves + (size_t)g * TAFL_MAX_MOVES);
+    const uint2* const vs = reinterpret_cast<const uint2*>(r_visits + (size_t)g * TAFL_MAX_MOVES);
+    uint2* const mo = reinterpret_cast<uint2*>(rec + sizeof(tafl_record_header));
+    uint2* const vo = reinterpret_cast<uint2*>(rec + sizeof(tafl_record_header) + 2 * TAFL_REC_MOVES);
+    const uint2 zero = make_uint2(0u, 0u);
+    for (uint32_t i = lane; i < TAFL_REC_MOVES / 4; i += 32) {   // k_mcts_results zero-fills the rows behind cnt
+        mo[i] = 4u * i < cnt ? ms[i] : zero;
+    }
+    for (uint32_t i = lane; i < TAFL_REC_MOVES / 2; i += 32) {
+        vo[i] = 2u * i < cnt ? vs[i] : zero;
+    }
+}
+
+// stable compaction of the searched games (r_counts > 0) in game order: row_of[g] = number of searched
+// games before g, one CTA walks the array in chunks of its size (n_games is a few thousand trees)
+__global__ void __launch_bounds__(1024)
+k_record_rows(const uint32_t* __restrict__ r_counts, uint32_t n, uint32_t* __restrict__ row_of, uint32_t* __restrict__ d_count,
+              uint32_t* __restrict__ h_count) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t base_s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) base_s = 0;
+    __syncthreads();
+    for (uint32_t g0 = 0; g0 < n; g0 += blockDim.x) {
+        const uint32_t g = g0 + threadIdx.x;
+        const bool keep = g < n && r_counts[g] > 0;
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, keep);
+        if (lane == 0) warp_tot[warp] = (uint32_t)__popc(m);
+        __syncthreads();
+        uint32_t before = base_s;
+        for (int w = 0; w < warp; ++w) before += warp_tot[w];
+        if (g < n) row_of[g] = keep ? before + (uint32_t)__popc(m & ((1u << lane) - 1u)) : 0xFFFFFFFFu;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t t = 0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += warp_tot[w];
+            base_s += t;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (d_count) *d_count = base_s;
+        if (h_count) *h_count = base_s;   // device alias of the caller's pinned word
     }
 }
 
@@ -835,7 +887,8 @@ k_mcts_select_leaf(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t
                 int n_pieces;
                 const int L = warp_build_ptab(cx, p, def_side, ptab, lane, &n_pieces);
                 if ((uint32_t)L > mv.edge_cap - mv.t_edges[tree] || n_pieces > MCTS_PT_MAX || L > TAFL_MAX_MOVES) {
-                    if (lane == 0) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+                    const uint32_t why = (n_pieces > MCTS_PT_MAX || L > TAFL_MAX_MOVES) ? OVF_PIECES : OVF_EDGES;
+                    if (lane == 0) { mv.t_overflow[tree] = why; atomicOr(any_overflow, why); }
                     break;
                 }
                 if (L == 0) {   // Ongoing position without plays: unreachable through do_play; expand empty, v = 0
@@ -890,7 +943,7 @@ k_mcts_select_leaf(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t
                 child = mv.t_nodes[tree];
                 __syncwarp();
                 if (child >= mv.node_cap) {
-                    if (lane == 0) { mv.t_overflow[tree] = 1; atomicOr(any_overflow, 1u); }
+                    if (lane == 0) { mv.t_overflow[tree] = OVF_NODES; atomicOr(any_overflow, OVF_NODES); }
                     break;
                 }
                 if (lane == 0) {
@@ -1042,7 +1095,7 @@ void mcts_free(tafl_engine* e) {
     if (!m) return;
     cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.n_ptab); cudaFree(m->v.edges); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
     cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best); cudaFree(m->r_probs); cudaFree(m->remap);
-    cudaFree(m->d_any_overflow);
+    cudaFree(m->d_any_overflow); cudaFree(m->row_of);
     if (m->round_graph) cudaGraphExecDestroy(m->round_graph);
     cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
     cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
@@ -1067,6 +1120,8 @@ void mcts_free(tafl_engine* e) {
 // fresh trees, or (tree reuse) carried trees whose root still is the game's state
 static void launch_tree_init(tafl_engine* e, int tree_mode) {
     MctsPools* m = e->mcts;
+    // every tree is re-initialised (or re-validated) below: the engine-wide overflow word describes THIS search only
+    cudaMemsetAsync(m->d_any_overflow, 0, sizeof(uint32_t), e->stream);
     if ((m->cfg.flags & TAFL_MCTS_TREE_REUSE) && m->tree_mode != tree_mode)   // a carried tree of the other layout is dropped
         cudaMemsetAsync(m->v.t_nodes, 0, (size_t)e->n_games * sizeof(uint32_t), e->stream);
     m->tree_mode = tree_mode;
@@ -1074,6 +1129,18 @@ static void launch_tree_init(tafl_engine* e, int tree_mode) {
         k_mcts_init_carry<<<grid_for(e->n_games, 128), 128, 0, e->stream>>>(e->d_states, e->n_games, m->v);
     else
         k_mcts_init<<<grid_for(e->n_games, 128), 128, 0, e->stream>>>(e->d_states, e->n_games, m->v);
+}
+
+
+// engine-wide overflow word -> error (the word is cleared at the start of every search)
+static int overflow_error(tafl_engine* e, uint32_t of) {
+    if (!of) return TAFL_OK;
+    std::string msg = "MCTS search stopped early in at least one tree:";
+    if (of & OVF_EDGES) msg += " edge pool exhausted (raise tafl_mcts_config.edge_capacity);";
+    if (of & OVF_NODES) msg += " node pool exhausted (raise tafl_mcts_config.node_capacity; with tree reuse the carried subtree counts);";
+    if (of & OVF_PIECES) msg += " a position has more pieces / legal moves than a node can hold;";
+    e->err = msg;
+    return TAFL_ERR_CAPACITY;
 }
 
 static int need_mcts(tafl_engine* e) {
@@ -1187,11 +1254,7 @@ int tafl_mcts_search(tafl_engine* e) {
     uint32_t of = 0;
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(&of, e->mcts->d_any_overflow, sizeof(of), cudaMemcpyDeviceToHost, e->stream));
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-    if (of) {
-        e->err = "MCTS edge pool exhausted for at least one tree: raise tafl_mcts_config.edge_capacity";
-        return TAFL_ERR_CAPACITY;
-    }
-    return TAFL_OK;
+    return overflow_error(e, of);
 }
 
 int tafl_mcts_results_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_visits, double** d_q, uint32_t** d_counts,
@@ -1234,6 +1297,7 @@ int tafl_mcts_play_best(tafl_engine* e, uint8_t* h_status) {
     TAFL_SPEC_DISPATCH(e, (k_mcts_play_best<BB, SP><<<grid_for(n, 64), 64, 0, e->stream>>>(cx, e->d_states, n, m->r_moves, m->r_counts,
                                                                                        m->r_best, e->d_status)));
     MCTS_LAUNCHED(e);
+    hist_forget_all(e);   // not a Game::do_play: see tafl_engine.cu
     if (h_status) {
         TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_status, e->d_status, n, cudaMemcpyDeviceToHost, e->stream));
         TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -1313,8 +1377,45 @@ int tafl_pack_records(tafl_engine* e, void* d_out) {
     MctsPools* m = e->mcts;
     const uint32_t n = e->n_games;
     k_pack_records<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, e->d_states, n, e->game_id_base, m->r_moves,
-                                                                              m->r_visits, m->r_counts, m->r_best, (uint8_t*)d_out);
+                                                                              m->r_visits, m->r_counts, m->r_best, e->d_episode, nullptr,
+                                                                              (uint8_t*)d_out);
     MCTS_LAUNCHED(e);
+    return TAFL_OK;
+}
+
+int tafl_pack_records_compact(tafl_engine* e, void* d_out, uint32_t* d_count, uint32_t* h_count) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    if (!d_out || !e->mcts->searched) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    MctsPools* m = e->mcts;
+    const uint32_t n = e->n_games;
+    if (!m->row_of) TAFL_CUDA_TRY(e, cudaMalloc((void**)&m->row_of, ((size_t)n + 1) * sizeof(uint32_t)));
+    uint32_t* h_alias = nullptr;   // pinned host word: written by the kernel itself, no copy-engine hand-off
+    if (h_count) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, h_count) == cudaSuccess && a.type == cudaMemoryTypeHost) h_alias = (uint32_t*)a.devicePointer;
+        else cudaGetLastError();
+    }
+    uint32_t* const d_cnt = d_count ? d_count : m->row_of + n;
+    k_record_rows<<<1, 1024, 0, e->stream>>>(m->r_counts, n, m->row_of, d_cnt, h_alias);
+    MCTS_LAUNCHED(e);
+    k_pack_records<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, e->d_states, n, e->game_id_base, m->r_moves,
+                                                                              m->r_visits, m->r_counts, m->r_best, e->d_episode, m->row_of,
+                                                                              (uint8_t*)d_out);
+    MCTS_LAUNCHED(e);
+    if (h_count && !h_alias)   // pageable destination: staged copy (the host still must not read it before the stream reaches here)
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_count, d_cnt, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    return TAFL_OK;
+}
+
+int tafl_mcts_overflow(tafl_engine* e, uint32_t* h_flags) {
+    int rc = need_mcts(e);
+    if (rc) return rc;
+    if (!h_flags) return TAFL_ERR_INVALID_ARG;
+    cudaSetDevice(e->device);
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_flags, e->mcts->d_any_overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     return TAFL_OK;
 }
 
@@ -1444,11 +1545,7 @@ int tafl_mcts_finish(tafl_engine* e) {
     uint32_t of = 0;
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(&of, m->d_any_overflow, sizeof(of), cudaMemcpyDeviceToHost, e->stream));
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-    if (of) {
-        e->err = "MCTS edge pool exhausted for at least one tree: raise tafl_mcts_config.edge_capacity";
-        return TAFL_ERR_CAPACITY;
-    }
-    return TAFL_OK;
+    return overflow_error(e, of);
 }
 
 int tafl_eval_builtin(tafl_engine* e, int evaluator, uint64_t seed) {

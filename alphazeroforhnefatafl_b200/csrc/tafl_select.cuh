@@ -466,6 +466,56 @@ TAFL_HD tafl_move pt_decode(const Ctx<BB, SP>& cx, uint32_t e, int def_side, int
     const int to = vertical ? idx_of<BB>(q, col) : idx_of<BB>(row, q);
     return (tafl_move)(tile | (to << 7));
 }
+// The plays of ONE piece in ValidPlayIterator order (V+, V-, H+, H-, distance ascending; play.rs:189-225),
+// written to out[off ...] by tile arithmetic alone: the destinations of a ray are consecutive tiles from the
+// piece outward, and the one tile a ray can cross without stopping is the empty throne (play.rs:208-211,
+// noentry) — one extra step when the walk reaches it.  Returns the offset behind the last play; writes
+// behind `cap` are dropped.  Used per lane by k_legal_moves_g (out = the game's shared-memory row).
+template <class BB, int SP>
+TAFL_HD int emit_piece_plays(const Ctx<BB, SP>& cx, int tile, int row, int col, int kind, const Rays& r, tafl_move* out, int off,
+                             int cap) {
+    constexpr int S = BB::STRIDE;
+    const int mid = cx.m();
+    const bool ne = cx.f_noentry(kind);
+#pragma unroll
+    for (int dir = 0; dir < 4; ++dir) {
+        const int cnt = r.cnt[dir];
+        const int step = (dir == DIR_VP ? S : dir == DIR_VM ? -S : dir == DIR_HP ? 1 : -1) * 128;   // on the `to` field
+        const int pp = dir < 2 ? row : col, line = dir < 2 ? col : row;
+        int hole_at = 99;   // play index whose destination lies just behind the throne
+        if (ne && line == mid) {
+            if ((dir & 1) == 0) { if (pp < mid) hole_at = mid - pp - 1; }
+            else if (pp > mid) hole_at = pp - mid - 1;
+        }
+        int m = tile * 129;   // from | to << 7 with to == from
+        for (int j = 0; j < cnt; ++j) {
+            m += step;
+            if (j == hole_at) m += step;
+            if (off < cap) out[off] = (tafl_move)m;
+            ++off;
+        }
+    }
+    return off;
+}
+// host restatement of k_legal_moves_g's per-piece path (tests/hostsim): pieces ascending, emit_piece_plays each
+template <class BB, int SP>
+TAFL_HD int emit_gen_moves(const Ctx<BB, SP>& cx, const tafl_state& st, tafl_move* out, int cap) {
+    if (st.status != TAFL_STATUS_ONGOING) return 0;
+    const Pos<BB> p = load_pos(cx, st);
+    const int def_side = (st.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
+    BB own = p.side(def_side);
+    const BB occ = p.occ();
+    int off = 0;
+    while (own.any()) {
+        const int s = own.ctz();
+        own = own & ~BB::bit(s);
+        const int row = s / BB::STRIDE, col = s - row * BB::STRIDE;
+        const int kind = def_side ? ((BB::bit(s) == p.kbit) ? KIND_K : KIND_DS) : KIND_AS;
+        off = emit_piece_plays(cx, s, row, col, kind, piece_rays(cx, occ, kind, row, col), out, off, cap);
+    }
+    return off;
+}
+
 // whole move list through the piece table (host check of the encoding; the kernels build the table
 // one piece per lane, tafl_mcts.cuh)
 template <class BB, int SP>

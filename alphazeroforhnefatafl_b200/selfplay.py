@@ -17,7 +17,7 @@ import torch.distributed as dist
 from . import _abi as A
 
 REC_HEADER = np.dtype([("game_id", "<u8"), ("ply", "<u4"), ("n_moves", "<u2"), ("side", "u1"), ("status", "u1"),
-                       ("att", "<u8", (2,)), ("def", "<u8", (2,)), ("best", "<u2"), ("_pad", "<u2", (3,))])
+                       ("att", "<u8", (2,)), ("def", "<u8", (2,)), ("best", "<u2"), ("_pad", "<u2"), ("episode", "<u4")])
 assert REC_HEADER.itemsize == 56
 REC_DTYPE = np.dtype([("h", REC_HEADER), ("moves", "<u2", (A.REC_MOVES,)), ("visits", "<u4", (A.REC_MOVES,))])
 assert REC_DTYPE.itemsize == A.REC_STRIDE
@@ -113,12 +113,12 @@ def backfill_outcomes(recs, draw_value=0.0):
     assign the episode result to every position of the episode)."""
     z = np.full(len(recs), np.nan)
     h = recs["h"]
-    final = {}
-    for gid, st in zip(h["game_id"], h["status"]):
+    final = {}   # one game id hosts many episodes (tafl_reset_finished): the key is (game_id, episode)
+    for gid, ep, st in zip(h["game_id"], h["episode"], h["status"]):
         if st & 0x80:
-            final[int(gid)] = int(st)
+            final[(int(gid), int(ep))] = int(st)
     for i in range(len(recs)):
-        st = final.get(int(h["game_id"][i]))
+        st = final.get((int(h["game_id"][i]), int(h["episode"][i])))
         if st is None:
             continue
         if (st & 0xC0) == 0xC0:

@@ -568,13 +568,32 @@ typedef struct {
     uint8_t  status;            /* status AFTER the chosen move   */
     uint64_t att[2], def[2];    /* position the search was run on */
     uint16_t best;              /* index of the move played       */
-    uint16_t _pad[3];
+    uint16_t _pad;
+    uint32_t episode;           /* how often this game id has been restarted (tafl_reset /
+                                 * tafl_reset_finished): (game_id, episode) names one episode */
 } tafl_record_header;           /* 56 bytes */
 /* pack one record per resident game into a DEVICE buffer:
- * header + moves[TAFL_REC_MOVES] u16 + visits[TAFL_REC_MOVES] u32, fixed stride */
-#define TAFL_REC_MOVES 256
+ * header + moves[TAFL_REC_MOVES] u16 + visits[TAFL_REC_MOVES] u32, fixed stride.  A row holds
+ * every legal move of its root (TAFL_REC_MOVES == TAFL_MAX_MOVES: nothing is ever truncated). */
+#define TAFL_REC_MOVES TAFL_MAX_MOVES
 #define TAFL_REC_STRIDE (56 + 2 * TAFL_REC_MOVES + 4 * TAFL_REC_MOVES)
 int tafl_pack_records(tafl_engine* e, void* d_out /* [n_games][TAFL_REC_STRIDE] */);
+/* The same rows, but only for the games that were searched (Ongoing at search time, n_moves > 0),
+ * compacted in game order on the device: row k of d_out is the k-th such game.  The number of rows
+ * goes to d_count (DEVICE u32, may be NULL) and to h_count (HOST u32, may be NULL; written when
+ * the work enqueued here has run — pass pinned memory and wait for the stream / an event).
+ * No host synchronisation: the replay-record path never stalls the next search. */
+int tafl_pack_records_compact(tafl_engine* e, void* d_out /* [n_games][TAFL_REC_STRIDE] */,
+                              uint32_t* d_count, uint32_t* h_count);
+/* Restart every finished game from the engine's start position (episode counter + 1, history of
+ * those games forgotten): the self-play sweep keeps all n_games trees busy.  *h_n (may be NULL)
+ * receives the number of games restarted (forces a stream sync). */
+int tafl_reset_finished(tafl_engine* e, uint32_t* h_n);
+/* engine-wide MCTS overflow flags of the LAST search (0 = every tree ran all its simulations;
+ * bit 0 edge pool, bit 1 node pool, bit 2 piece table); syncs the engine stream.  The asynchronous
+ * search calls do not report TAFL_ERR_CAPACITY themselves: callers of tafl_mcts_search_async
+ * check here before trusting the results. */
+int tafl_mcts_overflow(tafl_engine* e, uint32_t* h_flags);
 
 
 /* ------------------------------------------------------------------------------------------

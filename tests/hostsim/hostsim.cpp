@@ -191,6 +191,19 @@ int sim_piece_table_moves(const tafl_rules* r, int width, const tafl_state* st, 
     });
 }
 
+// the per-piece tile-arithmetic emission of k_legal_moves_g (emit_piece_plays), pieces ascending
+int sim_emit_moves(const tafl_rules* r, int width, const tafl_state* st, uint32_t n, tafl_move* moves, uint32_t* counts) {
+    return dispatch(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) {
+            with_ctx<BB>(*r, st[i].side_len, [&](const auto& cx) {
+                counts[i] = (uint32_t)emit_gen_moves(cx, st[i], moves + (size_t)i * TAFL_MAX_MOVES, TAFL_MAX_MOVES);
+            });
+        }
+        return 0;
+    });
+}
+
 // Random playouts through the fused count+select+apply path the step kernel uses.
 int sim_random_playout(const tafl_rules* r, const tafl_state* start, int width, uint64_t seed, uint64_t game_id_base,
                        uint32_t n_games, uint64_t ply0, uint32_t n_steps, int auto_reset, tafl_state* states,

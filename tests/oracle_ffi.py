@@ -30,14 +30,31 @@ def build_oracle():
     return so
 
 
-def build_hostsim():
-    so = os.path.join(HOSTSIM_DIR, "libhostsim.so")
+SAN_FLAGS = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"]
+
+
+def build_hostsim(sanitize=None):
+    """sanitize=True (or TAFL_HOSTSIM_SAN=1): the same harness built with ASan + UBSan
+    (libhostsim_san.so; the loading process needs libasan preloaded, see test_hostsim.py)."""
+    if sanitize is None:
+        sanitize = os.environ.get("TAFL_HOSTSIM_SAN") == "1"
+    so = os.path.join(HOSTSIM_DIR, "libhostsim_san.so" if sanitize else "libhostsim.so")
     deps = [os.path.join(HOSTSIM_DIR, "hostsim.cpp"), os.path.join(ROOT, "include", "tafl.h")]
     deps += [os.path.join(CSRC, f) for f in ("tafl_bb.cuh", "tafl_core.cuh", "tafl_select.cuh", "tafl_ctx.hpp")]
     if _newer(so, deps):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
+        opt = SAN_FLAGS if sanitize else ["-O2"]
+        subprocess.check_call(["g++"] + opt + ["-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
                                "-Wno-unknown-pragmas", "-o", so, os.path.join(HOSTSIM_DIR, "hostsim.cpp")])
     return so
+
+
+def sanitizer_runtime():
+    """path of g++'s libasan.so (to LD_PRELOAD into a python that loads libhostsim_san.so), or None"""
+    try:
+        p = subprocess.check_output(["g++", "-print-file-name=libasan.so"], text=True).strip()
+    except Exception:  # noqa: BLE001
+        return None
+    return p if os.path.isabs(p) and os.path.exists(p) else None
 
 
 class ByValueImpl:
@@ -325,6 +342,14 @@ class HostSim:
         moves = np.zeros((n, A.MAX_MOVES), np.uint16)
         counts = np.zeros(n, np.uint32)
         rc = self.lib.sim_piece_table_moves(C.byref(rules), width, A.ptr(states), n, A.ptr(moves), A.ptr(counts))
+        assert rc == 0, rc
+        return moves, counts
+
+    def emit_moves(self, rules, width, states):
+        n = len(states)
+        moves = np.zeros((n, A.MAX_MOVES), np.uint16)
+        counts = np.zeros(n, np.uint32)
+        rc = self.lib.sim_emit_moves(C.byref(rules), width, A.ptr(states), n, A.ptr(moves), A.ptr(counts))
         assert rc == 0, rc
         return moves, counts
 

@@ -133,9 +133,11 @@ def test_hostsim_piece_table_equals_move_list(orc, sim):
     def check(rules, width, states):
         mo, co = orc.by_value(rules, width).legal_moves_of(states)
         mt, ct = sim.piece_table_moves(rules, width, states)
-        assert np.array_equal(co, ct)
+        me, ce = sim.emit_moves(rules, width, states)   # the per-piece tile arithmetic of k_legal_moves_g
+        assert np.array_equal(co, ct) and np.array_equal(co, ce)
         for i in range(len(states)):
             assert np.array_equal(mo[i, :co[i]], mt[i, :ct[i]]), i
+            assert np.array_equal(mo[i, :co[i]], me[i, :ce[i]]), i
     for name, preset, width in PRESET_CONFIGS:
         rules, fen = orc.preset_rules(preset), board_for(orc, preset)
         check(rules, width, sample_positions(orc, rules, fen, width, 150, seed=5))
@@ -147,3 +149,25 @@ def test_hostsim_piece_table_equals_move_list(orc, sim):
                       slow_pieces=int(rng.choice([0, 0, A.pieceset_type(A.KING), 0xFFFF, A.pieceset_side(A.DEFENDER)])))
         N, width = [(7, 64), (9, 128), (11, 128), (7, 128)][trial % 4]
         check(r, width, random_boards(orc, rng, N, width, 150))
+
+
+def test_hostsim_under_sanitizers():
+    """The differential tests of this file once more, with the kernel math built with ASan + UBSan
+    (-fno-sanitize-recover): out-of-range shifts, bad extract32 / bit() arguments, out-of-bounds walks
+    abort the run.  compute-sanitizer is closed on the GPU pool, so this is the memory-safety check
+    the shared __host__ __device__ code gets."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("TAFL_HOSTSIM_SAN") == "1":
+        pytest.skip("this IS the sanitizer run")
+    rt = F.sanitizer_runtime()
+    if rt is None:
+        pytest.skip("g++ has no libasan.so on this machine")
+    F.build_hostsim(sanitize=True)
+    env = dict(os.environ, TAFL_HOSTSIM_SAN="1", LD_PRELOAD=rt,
+               ASAN_OPTIONS="detect_leaks=0:abort_on_error=1", UBSAN_OPTIONS="print_stacktrace=1:halt_on_error=1")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_hostsim.py"), "-x", "-q", "-p", "no:cacheprovider"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-4000:] + "\n" + r.stderr[-4000:]
