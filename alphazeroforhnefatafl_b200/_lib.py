@@ -73,6 +73,7 @@ def lib():
         "tafl_get_states": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32]),
         "tafl_states_device": (vp, [vp]),
         "tafl_legal_moves": (C.c_int, [vp, vp, vp]),
+        "tafl_legal_moves_async": (C.c_int, [vp, vp, vp]),
         "tafl_moves_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp)]),
         "tafl_legal_moves_host": (C.c_int, [vp, vp, vp, C.c_uint32, C.c_uint32]),
         "tafl_step": (C.c_int, [vp, vp, vp]),
@@ -110,6 +111,7 @@ def lib():
         "tafl_nccl_comm_create": (C.c_int, [vp, vp, C.c_int, C.c_int, C.POINTER(vp)]),
         "tafl_nccl_comm_destroy": (C.c_int, [vp]),
         "tafl_gather_records": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, C.c_uint32, vp, C.c_uint64, vp]),
+        "tafl_gather_records_on": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp, C.c_uint32, vp, C.c_uint64, vp, vp]),
         "tafl_mcts_configure": (C.c_int, [vp, C.POINTER(A.MctsConfig)]),
         "tafl_mcts_search": (C.c_int, [vp]),
         "tafl_mcts_search_async": (C.c_int, [vp]),

@@ -135,6 +135,11 @@ int tafl_nccl_comm_destroy(void* comm) {
 
 int tafl_gather_records(tafl_engine* e, void* comm_, int n_ranks, int rank, int root, const void* d_send, uint32_t n_local,
                         void* d_recv, uint64_t recv_capacity_rows, uint32_t* h_counts) {
+    return tafl_gather_records_on(e, comm_, n_ranks, rank, root, d_send, n_local, d_recv, recv_capacity_rows, h_counts, nullptr);
+}
+
+int tafl_gather_records_on(tafl_engine* e, void* comm_, int n_ranks, int rank, int root, const void* d_send, uint32_t n_local,
+                           void* d_recv, uint64_t recv_capacity_rows, uint32_t* h_counts, void* stream_) {
     if (!e || !comm_ || n_ranks < 1 || rank < 0 || rank >= n_ranks || root < 0 || root >= n_ranks || !h_counts)
         return TAFL_ERR_INVALID_ARG;
     if (n_local && !d_send) return TAFL_ERR_INVALID_ARG;
@@ -142,16 +147,17 @@ int tafl_gather_records(tafl_engine* e, void* comm_, int n_ranks, int rank, int 
     if (!n.h) { e->err = n.err; return TAFL_ERR_CUDA; }
     ncclComm_t comm = (ncclComm_t)comm_;
     cudaSetDevice(e->device);
+    const cudaStream_t stream = stream_ ? (cudaStream_t)stream_ : e->stream;
     // 1. row counts of every rank (device staging: slot 0 = own count, slot 1 = all counts)
     uint32_t* d_cnt;
     void* p;
     int rc = scratch(e, 5, (size_t)(n_ranks + 1) * sizeof(uint32_t), &p);
     if (rc) return rc;
     d_cnt = (uint32_t*)p;
-    TAFL_CUDA_TRY(e, cudaMemcpyAsync(d_cnt, &n_local, sizeof(uint32_t), cudaMemcpyHostToDevice, e->stream));
-    TAFL_NCCL_TRY(e, n.AllGather(d_cnt, d_cnt + 1, 1, kUint32, comm, e->stream));
-    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_counts, d_cnt + 1, (size_t)n_ranks * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
-    TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(d_cnt, &n_local, sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+    TAFL_NCCL_TRY(e, n.AllGather(d_cnt, d_cnt + 1, 1, kUint32, comm, stream));
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_counts, d_cnt + 1, (size_t)n_ranks * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+    TAFL_CUDA_TRY(e, cudaStreamSynchronize(stream));
     uint64_t total = 0;
     for (int r = 0; r < n_ranks; ++r) total += h_counts[r];
     void* d_sink = nullptr;   // root buffer too small: the exchange must still happen (the senders are committed to it)
@@ -168,7 +174,7 @@ int tafl_gather_records(tafl_engine* e, void* comm_, int n_ranks, int rank, int 
     uint64_t own_off = 0;
     if (rank == root && n_local) {   // the root's own rows: a plain device copy, outside the group
         for (int r = 0; r < root; ++r) own_off += (uint64_t)h_counts[r] * TAFL_REC_STRIDE;
-        cerr = cudaMemcpyAsync((char*)d_recv + own_off, d_send, (size_t)n_local * TAFL_REC_STRIDE, cudaMemcpyDeviceToDevice, e->stream);
+        cerr = cudaMemcpyAsync((char*)d_recv + own_off, d_send, (size_t)n_local * TAFL_REC_STRIDE, cudaMemcpyDeviceToDevice, stream);
     }
     nerr = n.GroupStart();
     if (nerr) nwhat = "ncclGroupStart";
@@ -178,20 +184,20 @@ int tafl_gather_records(tafl_engine* e, void* comm_, int n_ranks, int rank, int 
             for (int r = 0; r < n_ranks; ++r) {
                 const size_t bytes = (size_t)h_counts[r] * TAFL_REC_STRIDE;
                 if (bytes && r != root && !nerr) {
-                    nerr = n.Recv((char*)d_recv + off, bytes, kUint8, r, comm, e->stream);
+                    nerr = n.Recv((char*)d_recv + off, bytes, kUint8, r, comm, stream);
                     if (nerr) nwhat = "ncclRecv";
                 }
                 off += bytes;
             }
         } else if (n_local) {
-            nerr = n.Send(d_send, (size_t)n_local * TAFL_REC_STRIDE, kUint8, root, comm, e->stream);
+            nerr = n.Send(d_send, (size_t)n_local * TAFL_REC_STRIDE, kUint8, root, comm, stream);
             if (nerr) nwhat = "ncclSend";
         }
         const ncclResult_t gerr = n.GroupEnd();
         if (!nerr && gerr) { nerr = gerr; nwhat = "ncclGroupEnd"; }
     }
     if (d_sink) {
-        cudaStreamSynchronize(e->stream);
+        cudaStreamSynchronize(stream);
         cudaFree(d_sink);
     }
     if (cerr != cudaSuccess) return set_cuda_error(e, cerr, "cudaMemcpyAsync(root rows)");

@@ -673,6 +673,17 @@ int tafl_legal_moves(tafl_engine* e, tafl_move* d_moves, uint32_t* d_counts) {
     if (rc) return rc;
     return sync_engine(e);
 }
+int tafl_legal_moves_async(tafl_engine* e, tafl_move* d_moves, uint32_t* d_counts) {
+    TAFL_CHECK_E(e);
+    cudaSetDevice(e->device);
+    if (!d_moves || !d_counts) {
+        int rc = ensure_moves(e);
+        if (rc) return rc;
+        if (!d_moves) d_moves = e->d_moves;
+        if (!d_counts) d_counts = e->d_counts;
+    }
+    return legal_moves_enqueue(e, e->d_states, e->n_games, d_moves, d_counts);
+}
 int tafl_legal_moves_host(tafl_engine* e, tafl_move* h_moves, uint32_t* h_counts, uint32_t first, uint32_t n) {
     TAFL_CHECK_E(e);
     if (!h_moves || !h_counts || (uint64_t)first + n > e->n_games) return TAFL_ERR_INVALID_ARG;

@@ -797,7 +797,7 @@ k_pack_records(MctsView mv, const tafl_state* __restrict__ states, uint32_t n, u
 // games before g, one CTA walks the array in chunks of its size (n_games is a few thousand trees)
 __global__ void __launch_bounds__(1024)
 k_record_rows(const uint32_t* __restrict__ r_counts, uint32_t n, uint32_t* __restrict__ row_of, uint32_t* __restrict__ d_count,
-              uint32_t* __restrict__ h_count) {
+              uint32_t* __restrict__ h_count, const uint32_t* __restrict__ any_overflow) {
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t base_s;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -822,7 +822,7 @@ k_record_rows(const uint32_t* __restrict__ r_counts, uint32_t n, uint32_t* __res
     }
     if (threadIdx.x == 0) {
         if (d_count) *d_count = base_s;
-        if (h_count) *h_count = base_s;   // device alias of the caller's pinned word
+        if (h_count) { h_count[0] = base_s; h_count[1] = *any_overflow; }   // device alias of the caller's pinned words
     }
 }
 
@@ -1398,14 +1398,16 @@ int tafl_pack_records_compact(tafl_engine* e, void* d_out, uint32_t* d_count, ui
         else cudaGetLastError();
     }
     uint32_t* const d_cnt = d_count ? d_count : m->row_of + n;
-    k_record_rows<<<1, 1024, 0, e->stream>>>(m->r_counts, n, m->row_of, d_cnt, h_alias);
+    k_record_rows<<<1, 1024, 0, e->stream>>>(m->r_counts, n, m->row_of, d_cnt, h_alias, m->d_any_overflow);
     MCTS_LAUNCHED(e);
     k_pack_records<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, e->d_states, n, e->game_id_base, m->r_moves,
                                                                               m->r_visits, m->r_counts, m->r_best, e->d_episode, m->row_of,
                                                                               (uint8_t*)d_out);
     MCTS_LAUNCHED(e);
-    if (h_count && !h_alias)   // pageable destination: staged copy (the host still must not read it before the stream reaches here)
+    if (h_count && !h_alias) {   // pageable destination: staged copies (the host still must not read it before the stream reaches here)
         TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_count, d_cnt, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+        TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_count + 1, m->d_any_overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    }
     return TAFL_OK;
 }
 

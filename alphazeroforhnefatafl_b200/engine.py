@@ -457,6 +457,23 @@ class LockstepGames:
     def pack_records(self, d_out):
         self._ck(lib().tafl_pack_records(self._h, d_out))
 
+    def pack_records_compact(self, d_out, h_count=None, d_count=None):
+        """rows of the searched games only, compacted in game order on the device; h_count: pointer to two
+        pinned uint32 (rows, overflow flags of the search), written when the enqueued work has run"""
+        self._ck(lib().tafl_pack_records_compact(self._h, d_out, d_count, h_count))
+
+    def reset_finished(self, want_count=False):
+        """restart every finished game from the start position (episode counter + 1)"""
+        n = C.c_uint32(0)
+        self._ck(lib().tafl_reset_finished(self._h, C.byref(n) if want_count else None))
+        return n.value if want_count else None
+
+    def mcts_overflow(self):
+        """overflow flags of the last search (0 = complete; 1 edge pool, 2 node pool, 4 piece table); syncs"""
+        f = C.c_uint32(0)
+        self._ck(lib().tafl_mcts_overflow(self._h, C.byref(f)))
+        return f.value
+
     # -- GameLogic by-value batch API (logic.rs) --------------------------------------------------
     def validate_play(self, states, plays):
         states, plays = np.ascontiguousarray(states, A.STATE_DTYPE), np.ascontiguousarray(plays, A.PLAY_DTYPE)

@@ -2,16 +2,26 @@
 """bench.py — Copenhagen 11x11 env steps/s (BASELINE.json configs[1]: 65 536 lockstep games of
 random legal play on one B200) plus MCTS simulations/s, through libtafl_b200.so.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload tablut_mcts]
 
-One bench "step" = `--plies` lockstep plies of all resident games (default 64 launches of the
-fused step kernel, the state round-trips HBM after every ply); the L2 is flushed between timed
-steps.  Prints ONE JSON line (see DESIGN.md §measurement for every field).
+One bench "step" = `plies_per_step` lockstep plies of all resident games (one launch of the fused step
+kernel per ply, the state round-trips HBM after every ply); the L2 is flushed between timed steps.
+Whatever --steps is, the work per step is scaled so that every timed region (env, do_play e2e, MCTS)
+lasts at least --min-region-s seconds: these are sustained figures, not bursts.  Prints ONE JSON line
+(DESIGN.md §4 explains every field):
+
+    value / roofline      fused random-play env step, states resident in HBM      (configs[1])
+    e2e                   Game::do_play through the C ABI with pinned host buffers (headline)
+    legal_moves           get_all_possible_moves, 65 536 games per launch          (north-star K1)
+    mcts                  Copenhagen 800 sims/move, 4096 trees, self-play sweep with record gather (configs[2], [4])
+    mcts_tablut           the same on Tablut 9x9                                   (configs[3])
+    cpu_baseline, c1_brandubh_cpu, mcts.cpu_baseline, mcts_tablut.cpu_baseline     the oracle on the host cores
 """
 import argparse
-import ctypes as C
 import json
+import math
 import os
+import subprocess
 import sys
 import threading
 import time
@@ -21,22 +31,26 @@ sys.path.insert(0, ROOT)
 
 ENV_BYTES_PER_STEP = 136          # 64 B state read + 64 B state write + 4 B action + 4 B status
 METRIC, UNIT = "copenhagen_11x11_env_steps_per_s", "env steps/s"
+DTYPE = "u128 (two u64 bitboard words per side)"
 
 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="copenhagen_env", choices=["copenhagen_env", "tablut_mcts"],
+                    help="tablut_mcts: BASELINE configs[3] alone, as the headline line (the default run carries it as mcts_tablut)")
     ap.add_argument("--games", type=int, default=65536)
-    ap.add_argument("--plies", type=int, default=64, help="lockstep plies per bench step")
+    ap.add_argument("--plies", type=int, default=64, help="lockstep plies per graph launch (a step is a whole number of these)")
     ap.add_argument("--seed", type=int, default=20261104)
+    ap.add_argument("--min-region-s", type=float, default=1.2, help="every timed region lasts at least this long")
     ap.add_argument("--no-mcts", action="store_true")
     ap.add_argument("--mcts-games", type=int, default=4096)
     ap.add_argument("--mcts-sims", type=int, default=800)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="length of each CPU baseline loop")
     return ap.parse_args()
 
 
@@ -49,9 +63,16 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", {}
 
 
+def git_head():
+    try:
+        return subprocess.check_output(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], text=True, stderr=subprocess.DEVNULL).strip()
+    except Exception:  # noqa: BLE001  (the GPU box has no .git)
+        return None
+
+
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle (C++ restatement of the reference crate; the Rust crate itself cannot be
-# built in this image) on the host cores, one game per thread.
+# built in this image: no cargo / rustc) on the host cores, one game / one tree per thread.
 # ------------------------------------------------------------------------------------------------
 def oracle_handle():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -59,43 +80,77 @@ def oracle_handle():
     return oracle_ffi.oracle()
 
 
-def cpu_playout_rate(orc, seconds, seed, plies):
-    """steps/s of the oracle random-playout loop with every host thread busy, on a bounded sample."""
+def preset_ids():
     from alphazeroforhnefatafl_b200 import _abi as A
-    cores = max(1, orc.hw_threads())
-    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
-    games = cores * 8
-    st, _ = orc.random_playout(rules, fen, 128, seed, games, 16, n_threads=cores)   # warm
-    steps = 0
+    return {"copenhagen": A.PRESET_COPENHAGEN, "tablut": A.PRESET_TABLUT, "brandubh": A.PRESET_BRANDUBH}
+
+
+def cpu_playout_rate(orc, seconds, seed, preset="copenhagen", width=128, threads=None, games_per_thread=8, plies=2048):
+    """steps/s of the oracle random-playout loop (auto-reset) on a bounded sample.  Each call runs
+    games x plies plies (>= 100 ms of work, so thread start-up is noise)."""
+    cores = max(1, orc.hw_threads()) if threads is None else threads
+    pid = preset_ids()[preset]
+    rules, fen = orc.preset_rules(pid), orc.preset_board(pid)
+    games = cores * games_per_thread
+    st, _ = orc.random_playout(rules, fen, width, seed, games, 64, n_threads=cores)   # warm
+    steps, finished, ply = 0, 0, 64
     t0 = time.perf_counter()
-    ply = 16
     while True:
-        st, stats = orc.random_playout(rules, fen, 128, seed, games, plies, ply0=ply, n_threads=cores, states=st)
+        st, stats = orc.random_playout(rules, fen, width, seed, games, plies, ply0=ply, n_threads=cores, states=st)
         steps += stats.steps
+        finished += stats.games_finished
         ply += plies
         el = time.perf_counter() - t0
         if el >= seconds:
             break
-    return steps / el, cores, "%d games x %d plies (auto-reset), %d threads, %.1f s" % (games, ply - 16, cores, el)
+    sample = "%d games x %d plies (random legal play to terminal, auto-restart), %d threads, %.1f s, %d games finished" % (
+        games, ply - 64, cores, el, finished)
+    return steps / el, cores, sample
+
+
+def cpu_mcts_rate(orc, seconds, seed, sims, preset="copenhagen"):
+    """sims/s of the oracle MCTS (mcts.py restated, stub evaluator), one tree per host thread at a time"""
+    cores = max(1, orc.hw_threads())
+    pid = preset_ids()[preset]
+    rules, fen = orc.preset_rules(pid), orc.preset_board(pid)
+    trees = cores * 16
+    roots, _ = orc.random_playout(rules, fen, 128, seed, trees, 20, n_threads=cores)     # 20-ply positions, as the GPU leg
+    orc.mcts_search(rules, 128, roots[:cores], sims, n_threads=cores)                    # warm
+    done, calls = 0, 0
+    t0 = time.perf_counter()
+    while True:
+        r = orc.mcts_search(rules, 128, roots, sims, n_threads=cores)
+        done += r["stats"].sims
+        calls += 1
+        el = time.perf_counter() - t0
+        if el >= seconds:
+            break
+    v = done / el
+    return {"value": v, "unit": "sims/s", "per_core": v / cores, "cores": cores, "kind": "port",
+            "sample": "%d calls x %d trees x %d sims (20-ply %s positions, fresh tree per search), %d threads, %.1f s" % (
+                calls, trees, sims, preset, cores, el)}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from alphazeroforhnefatafl_b200 import _abi as A
     orc = oracle_handle()
     cores = max(1, orc.hw_threads())
-    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
-    # each step is a bounded sample of the 65 536-game workload: `games` games x `plies` plies
-    games = cores * 4
-    budget = 150.0 / max(1, args.steps + args.warmup)
-    st, _ = orc.random_playout(rules, fen, 128, args.seed, games, 8, n_threads=cores)
+    pid = preset_ids()["copenhagen"]
+    rules, fen = orc.preset_rules(pid), orc.preset_board(pid)
+    # Each step is a bounded sample of the 65 536-game workload: cores x 8 games x `plies` plies, sized
+    # from a calibration call so that one step is >= 150 ms of work (thread start-up is noise) and the
+    # whole run stays within ~2 minutes.
+    games = cores * 8
+    st, _ = orc.random_playout(rules, fen, 128, args.seed, games, 64, n_threads=cores)
     t0 = time.perf_counter()
-    st, s0 = orc.random_playout(rules, fen, 128, args.seed, games, 32, ply0=8, n_threads=cores, states=st)
+    st, s0 = orc.random_playout(rules, fen, 128, args.seed, games, 512, ply0=64, n_threads=cores, states=st)
     rate = s0.steps / (time.perf_counter() - t0)
-    plies = int(max(1, min(args.plies, rate * min(budget, 0.5) / games)))
-    ply = 40
+    total_calls = max(1, args.steps + args.warmup)
+    per_call_s = min(max(0.15, args.min_region_s / max(1, args.steps)), 120.0 / total_calls)
+    plies = int(max(64, rate * per_call_s / games))
+    ply = 576
     for _ in range(args.warmup):
         st, _ = orc.random_playout(rules, fen, 128, args.seed, games, plies, ply0=ply, n_threads=cores, states=st)
         ply += plies
@@ -107,13 +162,14 @@ def run_reference(args):
         ply += plies
     el = time.perf_counter() - t0
     v = total / el
-    sample = "%d games x %d plies per step (sample of the 65536-game workload), %d threads" % (games, plies, cores)
+    sample = "%d games x %d plies per step (sample of the 65536-game workload, auto-restart), %d threads, %.2f s timed" % (
+        games, plies, cores, el)
     _emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * el / max(1, args.steps), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u128 bitboards (2 x u64)", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
         "config": {"workload": "Copenhagen 11x11 random-play env stepping (BASELINE configs[1]), CPU oracle port of "
-                               "the reference crate (Rust toolchain unavailable)", "sample": sample},
+                               "the reference crate (Rust toolchain unavailable on this box)", "sample": sample},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -152,7 +208,7 @@ class Clocks(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.01)
 
     def summary(self):
         s = sorted(self.samples)
@@ -160,22 +216,56 @@ class Clocks(threading.Thread):
                 "power_w_max": max(self.power) if self.power else None, "samples": len(s)}
 
 
+class Ctx:
+    """what every leg needs: ranks, barrier, reductions"""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.args, self.torch, self.dist = args, torch, dist
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device — libtafl_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, x, op="max"):
+        t = self.torch.tensor([float(x)], dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+
 def run_b200(args):
+    cx = Ctx(args)
+    torch = cx.torch
+    if args.workload == "tablut_mcts":
+        from alphazeroforhnefatafl_b200 import engine as E
+        res = bench_mcts(cx, E, "tablut")
+        if cx.rank == 0:
+            _emit(json.dumps({
+                "metric": res["metric"], "value": res["value"], "unit": "sims/s", "n_gpus": cx.world, "steps": res["moves_timed"],
+                "warmup": 2, "ms_per_step": res["ms_per_move"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64 PUCT over " + DTYPE, "data": "synthetic",
+                "config": {"workload": "Tablut 9x9 MCTS self-play, 800 sims/move, %d trees per GPU, game-sharded (BASELINE configs[3])" % args.mcts_games},
+                "roofline": res["roofline"], "cpu_baseline": res.get("cpu_baseline"), "e2e": res.get("e2e"),
+                "gpu_launches": res["gpu_launches"], "detail": res}))
+        if cx.world > 1:
+            cx.dist.destroy_process_group()
+        return
+
     import numpy as np
-    import torch
-    import torch.distributed as dist
-    from alphazeroforhnefatafl_b200 import _abi as A
     from alphazeroforhnefatafl_b200 import engine as E
     from alphazeroforhnefatafl_b200._lib import lib
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — libtafl_b200 has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world, local = cx.rank, cx.world, cx.local
     hbm_peak, peak_src, _ = peaks()
     n, P = args.games, args.plies
     rules, fen = E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN
@@ -183,19 +273,25 @@ def run_b200(args):
     g.set_game_id_base(rank * n)           # games shard by id range; no data-path collective
     stream = torch.cuda.ExternalStream(g.stream, device=local)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")    # > 126 MB L2
+    barrier = cx.barrier
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def one_step():
+    def graph_launch():
         g.step_random(args.seed, P, auto_reset=True, steps_per_launch=1, sync=False)
 
     with torch.cuda.stream(stream):
+        # warm-up (also brings the games to steady state: auto-reset keeps a mix of openings, middle games, endings)
         for _ in range(max(3, args.warmup)):
             flush.zero_()
-            one_step()
+            for _ in range(4):
+                graph_launch()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(4):
+            graph_launch()
+        b.record(stream)
+        torch.cuda.synchronize()
+        t_graph = cx.reduce(a.elapsed_time(b) * 1e-3 / 4)                         # seconds per P plies
+        reps = max(1, int(math.ceil(args.min_region_s / max(1, args.steps) / t_graph)))
         barrier()
         g.stats_reset()
         clk = Clocks(local)
@@ -207,7 +303,8 @@ def run_b200(args):
         for a, b in evs:
             flush.zero_()                  # L2 flush between timed iterations (not inside the events)
             a.record(stream)
-            one_step()
+            for _ in range(reps):
+                graph_launch()
             b.record(stream)
         barrier()
         t_wall = time.perf_counter() - t_wall0
@@ -216,79 +313,82 @@ def run_b200(args):
         clk.join()
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     stats = g.stats()
-    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
-    steps_done = torch.tensor([stats.steps], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(steps_done, op=dist.ReduceOp.SUM)
-    dev_ms_max, total_steps = float(t.item()), float(steps_done.item())
+    dev_ms_max, total_steps = cx.reduce(dev_ms), cx.reduce(stats.steps, "sum")
     value = total_steps / (dev_ms_max * 1e-3)
-    kernel_us = 1e3 * dev_ms / max(1, args.steps * P)          # average launch duration (this rank)
+    plies_per_step = reps * P
+    kernel_us = 1e3 * dev_ms / max(1, args.steps * plies_per_step)          # average launch duration (this rank)
     achieved = ENV_BYTES_PER_STEP * n / (kernel_us * 1e-6) / 1e9
     mean_legal = stats.legal_moves / max(1, stats.steps)
+    steady = g.get_states()                                                 # steady-state positions for the other legs
+
+    legal = bench_legal_moves(cx, E, g, stream, flush, hbm_peak)
 
     # ---- e2e (headline): Game::do_play through the C ABI with HOST buffers -------------------------
     # The reference-facing call of this path is Game::do_play(play) -> Result<GameStatus, PlayInvalid>
-    # (game/mod.rs:95-101).  A seeded random-play action sequence is recorded first (untimed: the fused
-    # kernel reports the play it chose, tafl_actions_host); the timed region then replays it from the
-    # start position with one tafl_step_status call per ply: H2D of that ply's 65 536 plays from pinned
-    # memory, validate + apply on the device, D2H of the status and PlayInvalid bytes.
+    # (game/mod.rs:95-101).  A seeded random-play action sequence is recorded first from the STEADY-STATE
+    # positions of the leg above (untimed: the fused kernel reports the play it chose, tafl_actions_host),
+    # with auto-restart, so the sequence holds captures, wins and draws at their natural rate; the timed
+    # region replays it with one tafl_step_status call per ply — H2D of that ply's 65 536 plays from
+    # pinned memory, validate + apply on the device, D2H of the status and PlayInvalid bytes — followed
+    # by tafl_reset_finished (asynchronous: what a host does when it sees a finished status: Game::new).
     L = lib()
-    e2e_plies = 48
-    rounds = max(2, min(8, args.steps // 25))
+    e2e_plies = 256
     plays_rec = torch.empty((e2e_plies, n, 4), dtype=torch.uint8).pin_memory()
     st_host = torch.empty((e2e_plies, n), dtype=torch.uint8).pin_memory()
     err_host = torch.empty((e2e_plies, n), dtype=torch.uint8).pin_memory()
-    g.reset()
+    g.set_states(steady)
+    terminals = 0
     for ply in range(e2e_plies):
-        g.step_random(args.seed + 1, 1, auto_reset=False)
-        moves, _, _ = g.last_actions()
+        g.step_random(args.seed + 1, 1, auto_reset=True)
+        moves, status, _ = g.last_actions()
+        terminals += int((status != 0).sum())
         plays_rec[ply].numpy()[:] = E.moves_to_plays(moves, 128).view(np.uint8).reshape(n, 4)
     final_rec = g.get_states().tobytes()
-
     # argument pointers taken once: indexing a torch tensor costs microseconds a compiled host does not pay
     e2e_ptrs = [(plays_rec[p].data_ptr(), st_host[p].data_ptr(), err_host[p].data_ptr()) for p in range(e2e_plies)]
-    step_status, handle = L.tafl_step_status, g.handle
+    step_status, reset_finished, handle = L.tafl_step_status, L.tafl_reset_finished, g.handle
 
     def e2e_round():
         for p_in, p_st, p_err in e2e_ptrs:
-            rc = step_status(handle, p_in, p_st, p_err)
+            rc = reset_finished(handle, None)           # games that ended on the previous ply start over (no host sync)
+            if rc == 0:
+                rc = step_status(handle, p_in, p_st, p_err)
             if rc != 0:
                 raise RuntimeError("tafl_step_status failed: %d" % rc)
 
-    g.reset()
+    g.set_states(steady)
+    t0 = time.perf_counter()
     e2e_round()                                  # warm-up round, also the correctness check of the replay
+    t_round = time.perf_counter() - t0
     if g.get_states().tobytes() != final_rec:
         raise RuntimeError("e2e replay through Game::do_play does not reproduce the recorded games")
-    e2e_n_round = int((err_host.numpy() == 0).sum())
+    if int((err_host.numpy() != 0).sum()) != 0:
+        raise RuntimeError("e2e replay: a recorded play was rejected")
+    rounds = max(2, int(math.ceil(args.min_region_s / cx.reduce(t_round))))
     e2e_time = 0.0
     for _ in range(rounds):
-        g.reset()
+        g.set_states(steady)
         barrier()
         t0 = time.perf_counter()
         e2e_round()
         barrier()
         e2e_time += time.perf_counter() - t0
-    e2e_t = torch.tensor([e2e_time], dtype=torch.float64, device="cuda")
-    e2e_n = torch.tensor([float(e2e_n_round * rounds)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(e2e_n, op=dist.ReduceOp.SUM)
-    e2e_value = float(e2e_n.item()) / float(e2e_t.item())
+    e2e_value = cx.reduce(float(n) * e2e_plies * rounds, "sum") / cx.reduce(e2e_time)
 
     # ---- second e2e figure: by-value states (GameLogic::do_play(play, state) -> state), 64 B each way --
     h_in = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
     h_out = torch.empty(n * 64, dtype=torch.uint8).pin_memory()
-    h_in.numpy()[:] = np.frombuffer(g.get_states().tobytes(), np.uint8)
-    bv_steps = max(10, min(args.steps, 100))
+    h_in.numpy()[:] = np.frombuffer(steady.tobytes(), np.uint8)
 
     def bv_step():
         rc = L.tafl_step_random_host(g.handle, h_in.data_ptr(), h_out.data_ptr(), args.seed, 1, 1)
         if rc != 0:
             raise RuntimeError("tafl_step_random_host failed: %d" % rc)
 
-    for _ in range(3):
+    t0 = time.perf_counter()
+    for _ in range(5):
         bv_step()
+    bv_steps = max(10, int(math.ceil(args.min_region_s / cx.reduce((time.perf_counter() - t0) / 5))))
     g.stats_reset()
     barrier()
     t0 = time.perf_counter()
@@ -296,55 +396,112 @@ def run_b200(args):
         bv_step()
         h_in, h_out = h_out, h_in
     barrier()
-    bv_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-    bv_n = torch.tensor([float(g.stats().steps)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(bv_t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(bv_n, op=dist.ReduceOp.SUM)
-    bv_value = float(bv_n.item()) / float(bv_t.item())
+    bv_value = cx.reduce(g.stats().steps, "sum") / cx.reduce(time.perf_counter() - t0)
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms_max / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u128 bitboards (2 x u64)", "data": "synthetic",
+        "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
         "config": {"workload": "Copenhagen 11x11 random-play env stepping, %d lockstep games per GPU (BASELINE configs[1])" % n,
-                   "games_per_gpu": n, "plies_per_step": P, "steps_per_launch": 1, "auto_reset": True,
+                   "games_per_gpu": n, "plies_per_step": plies_per_step, "steps_per_launch": 1, "auto_reset": True,
                    "l2": "flushed between timed iterations (256 MiB memset, outside the events)",
-                   "sharding": "game-id ranges, no data-path collective", "mean_legal_moves": mean_legal},
+                   "sharding": "game-id ranges, no data-path collective", "mean_legal_moves": mean_legal,
+                   "timed_region_s": dev_ms_max * 1e-3},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                     "traffic": ncu_traffic(), "peak_source": peak_src, "kernel": "k_step_random<BB128>",
-                     "binding_limit": ncu_binding_limit(),
+                     "traffic": ncu_traffic("k_step_random"), "peak_source": peak_src, "kernel": "k_step_random<BB128, Copenhagen>",
+                     "binding_limit": ncu_binding_limit("k_step_random"),
                      "kernel_us": kernel_us, "bytes_per_env_step": ENV_BYTES_PER_STEP,
-                     "note": "integer-issue bound, not HBM bound: see profiles/ for issue-slot utilisation"},
+                     "note": "integer-issue bound, not HBM bound: binding_limit carries the ALU-pipe / issue-slot fractions of the committed ncu capture"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 4, "d2h_bytes_per_step": n * 2,
                 "api": "tafl_step_status == Game::do_play(play) -> Result<GameStatus, PlayInvalid> for 65536 resident games: "
                        "pinned host plays in, status + PlayInvalid bytes out, one call per ply (the kernel reads / writes the "
-                       "pinned buffers over PCIe itself, bytes per step as listed); recorded seeded random-play "
-                       "action sequence replayed from the start position (replay checked bit-exact against the recording)",
-                "plies_per_round": e2e_plies, "rounds": rounds,
+                       "pinned buffers over PCIe itself, bytes per step as listed), then tafl_reset_finished; a recorded seeded "
+                       "random-play action sequence over steady-state positions with auto-restart is replayed (checked bit-exact)",
+                "plies_per_round": e2e_plies, "rounds": rounds, "timed_region_s": cx.reduce(e2e_time),
+                "games_ended_in_the_sequence": terminals,
                 "by_value_states": {"value": bv_value, "unit": UNIT, "h2d_bytes_per_step": n * 64, "d2h_bytes_per_step": n * 64,
                                     "api": "tafl_step_random_host(1 ply): pinned host states in, successor states out, chunked over streams",
                                     "steps": bv_steps}},
+        "legal_moves": legal,
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
         "wall_s_timed_region": t_wall,
+        "git": git_head(),
     }
-    if not args.no_mcts:
-        try:
-            out["mcts"] = bench_mcts(args, E, rank, world, local, barrier, dist if world > 1 else None, torch)
-        except Exception as ex:  # the env-step line must survive an MCTS failure, loudly
-            out["mcts"] = {"error": repr(ex)}
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, cores, sample = cpu_playout_rate(oracle_handle(), args.cpu_seconds, args.seed, 64)
-        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
     g.close()
+    del flush
+    if not args.no_mcts:
+        for key, preset in (("mcts", "copenhagen"), ("mcts_tablut", "tablut")):
+            try:
+                out[key] = bench_mcts(cx, E, preset)
+            except Exception as ex:  # the env-step line must survive an MCTS failure, loudly
+                out[key] = {"error": repr(ex)}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        orc = oracle_handle()
+        v, cores, sample = cpu_playout_rate(orc, args.cpu_seconds, args.seed)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        # C1 (BASELINE configs[0]): Brandubh 7x7, ONE game on ONE core, random legal play to terminal with restart
+        v1, _, sample1 = cpu_playout_rate(orc, args.cpu_seconds, args.seed, preset="brandubh", width=64, threads=1,
+                                          games_per_thread=1, plies=40000)
+        out["c1_brandubh_cpu"] = {"metric": "brandubh_7x7_single_game_env_steps_per_s", "value": v1, "unit": UNIT, "cores": 1,
+                                  "kind": "port", "sample": sample1}
     if rank == 0:
         _emit(json.dumps(out))
     if world > 1:
-        dist.destroy_process_group()
+        cx.dist.destroy_process_group()
 
 
-def ncu_summary(kernel="k_step_random"):
+def bench_legal_moves(cx, E, g, stream, flush, hbm_peak):
+    """K1: tafl_legal_moves (get_all_possible_moves, game/main.rs:33-43) on the resident steady-state games —
+    device time per launch with the L2 flushed, and the small-batch (2048 games, latency-bound) launch."""
+    torch, args = cx.torch, cx.args
+    from alphazeroforhnefatafl_b200._lib import lib
+    L = lib()
+    n = g.n_games
+    d_moves, d_counts = g.legal_moves_device()                 # allocates + warms
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            L.tafl_legal_moves_async(g.handle, None, None)
+        reps = 40
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        for a, b in evs:
+            flush.zero_()
+            a.record(stream)
+            L.tafl_legal_moves_async(g.handle, None, None)
+            b.record(stream)
+        torch.cuda.synchronize()
+    us = sorted(1e3 * a.elapsed_time(b) for a, b in evs)
+    us_med = us[len(us) // 2]
+    moves, counts = g.legal_moves(0, min(n, 8192))
+    l_bar = float(counts.mean())
+    bytes_per_game = 64 + 4 + 2 * l_bar
+    res = {"kernel": "k_legal_moves_g<BB128, Copenhagen, G=%s>" % os.environ.get("TAFL_LM_G", "8"), "games": n, "us_per_launch": us_med,
+           "us_min": us[0], "mean_legal_moves": l_bar, "bytes_per_game": bytes_per_game,
+           "roofline": {"bound": "hbm", "achieved": bytes_per_game * n / (us_med * 1e-6) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": bytes_per_game * n / (us_med * 1e-6) / 1e9 / hbm_peak, "traffic": ncu_traffic("k_legal_moves_g"),
+                        "binding_limit": ncu_binding_limit("k_legal_moves_g")},
+           "includes": "device time of one launch (CUDA events around tafl_legal_moves_async), L2 flushed before each launch, median of 40"}
+    # 2048 games: one launch is latency-bound
+    small = E.LockstepGames(g.rules, g.start_fen, 2048, cx.local, 128)
+    try:
+        small.set_states(g.get_states(0, 2048))
+        sst = torch.cuda.ExternalStream(small.stream, device=cx.local)
+        small.legal_moves_device()
+        with torch.cuda.stream(sst):
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(40)]
+            for a, b in evs:
+                a.record(sst)
+                L.tafl_legal_moves_async(small.handle, None, None)
+                b.record(sst)
+            torch.cuda.synchronize()
+        us2 = sorted(1e3 * a.elapsed_time(b) for a, b in evs)
+        res["us_per_launch_2048_games"] = us2[len(us2) // 2]
+    finally:
+        small.close()
+    return res
+
+
+def ncu_summary(kernel):
     """the committed ncu --set full summary of the kernel (profiles/ncu_summary.json, written by profiles/ncu_summary.py)"""
     p = os.path.join(ROOT, "profiles", "ncu_summary.json")
     try:
@@ -354,97 +511,198 @@ def ncu_summary(kernel="k_step_random"):
         return {}
 
 
-def ncu_traffic():
-    return ncu_summary().get("dram_bytes_per_launch")
+def ncu_traffic(kernel):
+    return ncu_summary(kernel).get("dram_bytes_per_launch")
 
 
-def ncu_binding_limit():
-    """What actually bounds the step kernel (SURVEY.md §8d asks for it next to the HBM fraction): ALU-pipe and
-    issue-slot utilisation from the last committed ncu capture — evidence copied from profiles/, not measured in this run."""
-    d = ncu_summary()
+def ncu_binding_limit(kernel):
+    """What actually bounds the kernel (SURVEY.md §8d asks for it next to the HBM fraction): ALU-pipe and issue-slot
+    utilisation of the last committed ncu capture — evidence copied from profiles/, NOT measured in this run; `capture`
+    names the capture's tag and the commit it was taken on, so a stale capture is visible next to `git` of this run."""
+    d = ncu_summary(kernel)
     g = lambda k: (d.get(k) or {}).get("avg")   # noqa: E731
     alu, issue = g("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"), g("smsp__issue_active.avg.pct_of_peak_sustained_active")
     if alu is None and issue is None:
         return None
     return {"alu_pipe_frac": None if alu is None else alu / 100.0, "issue_slot_frac": None if issue is None else issue / 100.0,
-            "warp_inst_per_launch": g("smsp__inst_executed.sum"), "registers": g("launch__registers_per_thread"),
-            "source": "profiles/ncu_summary.json (ncu --set full, last committed capture)"}
+            "warp_inst_per_launch": g("smsp__inst_executed.sum"), "lanes_per_inst": g("smsp__thread_inst_executed_per_inst_executed.ratio"),
+            "warps_active_frac": None if g("sm__warps_active.avg.pct_of_peak_sustained_active") is None else g("sm__warps_active.avg.pct_of_peak_sustained_active") / 100.0,
+            "registers": g("launch__registers_per_thread"), "ncu_kernel_us": g("gpu__time_duration.sum"),
+            "capture": {"tag": d.get("tag"), "commit": d.get("commit"), "file": "profiles/ncu_summary.json"},
+            "source": "ncu --set full --clock-control none (cold cache, serialised): shares and fractions carry over, absolute times do not"}
 
 
-def bench_mcts(args, E, rank, world, local, barrier, dist, torch):
-    """Copenhagen MCTS, 800 sims/move, stub evaluator, 4096 trees per GPU (BASELINE configs[2])."""
-    n = args.mcts_games
-    g = E.LockstepGames(E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN, n, local, 128)
-    g.set_game_id_base(rank * n)
-    g.step_random(args.seed, 20, auto_reset=True)          # start the trees from 20-ply positions
+def bench_mcts(cx, E, preset):
+    """MCTS 800 sims/move, stub evaluator, 4096 trees per GPU (BASELINE configs[2] Copenhagen / configs[3] Tablut) as a
+    self-play generation sweep (configs[4]): every move = search + first-max move + compacted records + gather to the
+    replay-buffer rank (C-ABI NCCL, side stream, overlapped with the next search); finished games restart."""
+    args, torch = cx.args, cx.torch
+    import numpy as np
+    from alphazeroforhnefatafl_b200 import _abi as A
     from alphazeroforhnefatafl_b200 import selfplay as SP
-    sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0)     # search + first-max move + pack + gather to rank 0
+    n = args.mcts_games
+    rules = getattr(E.preset.rules, preset.upper())
+    fen = getattr(E.preset.boards, preset.upper())
+    hbm_peak, _, _ = peaks()
+
+    def fresh():
+        gg = E.LockstepGames(rules, fen, n, cx.local, 128)
+        gg.set_game_id_base(cx.rank * n)
+        gg.step_random(args.seed, 20, auto_reset=True)          # start the trees from 20-ply positions
+        return gg
+
+    g = fresh()
+    sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, overlap=True, restart_finished=True)
+    replay = SP.DeviceReplayBuffer(n * cx.world * 64, cx.local) if cx.rank == 0 else None   # HBM-resident rolling window
     stream = sp.stream
-    moves = 3
-    for _ in range(2):                                     # warm-up moves (NCCL channels, allocator blocks of the gather)
+    t0 = time.perf_counter()
+    for _ in range(3):                                     # warm-up moves (NCCL channels, allocator blocks)
         sp.move()
+    sp.flush()
+    torch.cuda.synchronize()
+    moves = max(20, int(math.ceil(args.min_region_s / cx.reduce((time.perf_counter() - t0) / 3))))
     s0 = g.mcts_stats().as_dict()
     l0 = g.launches
-    marks = [torch.cuda.Event(enable_timing=True) for _ in range(moves + 1)]
-    barrier()
-    marks[0].record(stream)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    cx.barrier()
+    t_w0 = time.perf_counter()
+    ev0.record(stream)
     n_rec = 0
     for i in range(moves):
         out = sp.move()
-        n_rec += 0 if out is None else out.shape[0]
-        marks[i + 1].record(stream)
-    barrier()
-    ms = marks[0].elapsed_time(marks[-1])
-    ms_moves = [marks[i].elapsed_time(marks[i + 1]) for i in range(moves)]
+        if out is not None and replay is not None:
+            n_rec += out.shape[0]
+            replay.extend(out, sp.side)
+    out = sp.flush()
+    if out is not None and replay is not None:
+        n_rec += out.shape[0]
+        replay.extend(out, sp.side)
+    ev1.record(stream)
+    cx.barrier()
+    t_wall = time.perf_counter() - t_w0
+    ms = ev0.elapsed_time(ev1)
     s1 = g.mcts_stats().as_dict()
     sims = s1["sims"] - s0["sims"]
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    c = torch.tensor([float(sims)], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    t_max, c_sum = cx.reduce(max(ms, t_wall * 1e3)), cx.reduce(sims, "sum")     # the slower of device span and host span
     nodes, depth, edges = s1["nodes"] - s0["nodes"], s1["depth_sum"] - s0["depth_sum"], s1["edges"] - s0["edges"]
     d_bar, l_bar = depth / max(1, sims), edges / max(1, nodes)
     b_sim = d_bar * (16 + 12 * l_bar) + (144 + 18 * l_bar) + 32 * d_bar
-    v = float(c.item()) / (float(t.item()) * 1e-3)
-    hbm_peak, _, _ = peaks()
-    res = {"metric": "copenhagen_11x11_mcts_sims_per_s", "value": v, "unit": "sims/s", "trees_per_gpu": n,
-           "sims_per_move": args.mcts_sims, "moves_timed": moves, "ms_per_move": float(t.item()) / moves,
-           "ms_each_move_rank0": ms_moves, "mean_depth": d_bar, "mean_edges_per_node": l_bar, "bytes_per_sim_model": b_sim,
-           "roofline": {"bound": "hbm", "achieved": v / world * b_sim / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                        "frac": v / world * b_sim / 1e9 / hbm_peak},
-           "records_gathered_on_rank0": int(n_rec), "record_bytes": 1592,
-           "includes": "k_mcts_init + k_mcts_sims + k_mcts_results + k_mcts_play_best + k_pack_records + torch record gather",
+    v = c_sum / (t_max * 1e-3)
+    kern = "k_mcts_sims_g"
+    traffic_launch = ncu_traffic(kern)
+    cap = ncu_summary(kern)
+    cap_sims = cap.get("sims_per_launch")
+    per_sim = traffic_launch / cap_sims if traffic_launch and cap_sims else None
+    res = {"metric": "%s_mcts_sims_per_s" % ("copenhagen_11x11" if preset == "copenhagen" else "tablut_9x9"), "value": v, "unit": "sims/s",
+           "trees_per_gpu": n, "sims_per_move": args.mcts_sims, "moves_timed": moves, "ms_per_move": t_max / moves,
+           "timed_region_s": t_max * 1e-3, "device_ms_rank0": ms, "wall_ms_rank0": t_wall * 1e3,
+           "mean_depth": d_bar, "mean_edges_per_node": l_bar, "bytes_per_sim_model": b_sim,
+           "roofline": {"bound": "hbm", "achieved": v / cx.world * b_sim / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": v / cx.world * b_sim / 1e9 / hbm_peak,
+                        "basis": "SURVEY §8d MODEL bytes per simulation (every edge of every visited node read) — the kernel moves far less, see frac_measured",
+                        "traffic": per_sim, "traffic_unit": "DRAM bytes per simulation (ncu dram__bytes_read+write of one bench-size launch / its simulations)",
+                        "frac_measured": None if per_sim is None else v / cx.world * per_sim / 1e9 / hbm_peak,
+                        "binding_limit": ncu_binding_limit(kern)},
+           "selfplay_sweep": {"records_gathered_on_rank0": int(n_rec), "record_bytes": A.REC_STRIDE,
+                              "replay_window_rows": None if replay is None else len(replay),
+                              "gather": "tafl_gather_records_on (C-ABI NCCL, ragged, side stream, overlapped)" if sp.ng is not None else "single rank: rows stay on the device",
+                              "restart_finished": True},
+           "includes": "k_mcts_init + k_mcts_sims_g + k_mcts_results + k_mcts_play_best + k_record_rows + k_pack_records + k_reset_finished + record gather + replay-window insert",
            "gpu_launches": int(g.launches - l0)}
+    if replay is not None:      # z back-fill of the window (host; outside the timed region) — episodes that ran to a terminal
+        t0 = time.perf_counter()
+        recs = replay.as_array()
+        z = SP.backfill_outcomes(recs)
+        res["selfplay_sweep"].update({"backfill_s": time.perf_counter() - t0, "rows_with_outcome": int((~np.isnan(z)).sum()),
+                                      "episodes_finished": int(((recs["h"]["status"] & 0x80) != 0).sum())})
+    sp.close()
     g.close()
+
+    # ---- e2e through the C ABI with HOST buffers: root states in, visit counts / moves / choice out, every move ----
+    g = fresh()
+    try:
+        res["e2e"] = mcts_e2e(cx, E, g)
+    except Exception as ex:  # noqa: BLE001
+        res["e2e"] = {"error": repr(ex)}
+    finally:
+        g.close()
     # secondary numbers (rank-local, same trees / sims): the reference's own usage keeps one MCTS
     # object per episode (tree reuse), and a real evaluator plugs in through the split-phase hook
-    for key, kw in (("tree_reuse", dict(tree_reuse=True)), ("evaluator_hook", dict(evaluator=("stub",)))):
-        try:
-            res[key] = _mcts_variant(args, E, SP, rank, local, torch, moves, **kw)
-        except Exception as ex:  # noqa: BLE001
-            res[key] = {"error": repr(ex)}
+    if preset == "copenhagen":
+        for key, kw in (("tree_reuse", dict(tree_reuse=True)), ("evaluator_hook", dict(evaluator=("stub",)))):
+            try:
+                res[key] = _mcts_variant(cx, E, SP, fresh, **kw)
+            except Exception as ex:  # noqa: BLE001
+                res[key] = {"error": repr(ex)}
+    if cx.rank == 0 and cx.world == 1 and not args.no_cpu_baseline:
+        res["cpu_baseline"] = cpu_mcts_rate(oracle_handle(), args.cpu_seconds, args.seed, args.mcts_sims, preset)
     return res
 
 
-def _mcts_variant(args, E, SP, rank, local, torch, moves, **kw):
-    n = args.mcts_games
-    g = E.LockstepGames(E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN, n, local, 128)
+def mcts_e2e(cx, E, g):
+    """MCTS.getActionProb for every game through the C ABI with HOST buffers: pinned root states in (tafl_set_states),
+    search, moves + visit counts + counts + choice out (tafl_mcts_results_host), the move played (tafl_mcts_play_best ->
+    status bytes), successor states out (tafl_get_states)."""
+    import numpy as np
+    from alphazeroforhnefatafl_b200 import _abi as A
+    from alphazeroforhnefatafl_b200._lib import lib
+    args = cx.args
+    L, n, h = lib(), g.n_games, g.handle
+    g.mcts_configure(args.mcts_sims, 1.0, 1e-4)
+    st = E.PinnedArray(n, A.STATE_DTYPE)
+    mv, vis = E.PinnedArray((n, A.MAX_MOVES), np.uint16), E.PinnedArray((n, A.MAX_MOVES), np.uint32)
+    cnt, best, status = E.PinnedArray(n, np.uint32), E.PinnedArray(n, np.uint32), E.PinnedArray(n, np.uint8)
+    st.a[:] = g.get_states()
+
+    def one_move():
+        for rc in (L.tafl_set_states(h, A.ptr(st.a), 0, n), L.tafl_mcts_search(h),
+                   L.tafl_mcts_results_host(h, 0, n, A.ptr(mv.a), A.ptr(vis.a), None, A.ptr(cnt.a), A.ptr(best.a)),
+                   L.tafl_mcts_play_best(h, A.ptr(status.a)), L.tafl_get_states(h, A.ptr(st.a), 0, n)):
+            if rc != 0:
+                raise RuntimeError("MCTS e2e call failed: %d %s" % (rc, L.tafl_last_error(h).decode()))
+
+    t0 = time.perf_counter()
+    for _ in range(2):
+        one_move()
+    moves = max(10, int(math.ceil(args.min_region_s / cx.reduce((time.perf_counter() - t0) / 2))))
+    s0 = g.mcts_stats().as_dict()["sims"]
+    cx.barrier()
+    t0 = time.perf_counter()
+    for _ in range(moves):
+        one_move()
+    cx.barrier()
+    el = cx.reduce(time.perf_counter() - t0)
+    sims = cx.reduce(g.mcts_stats().as_dict()["sims"] - s0, "sum")
+    out = {"value": sims / el, "unit": "sims/s", "moves": moves, "ms_per_move": 1e3 * el / moves, "timed_region_s": el,
+           "h2d_bytes_per_step": n * 64, "d2h_bytes_per_step": n * (A.MAX_MOVES * 6 + 4 + 4 + 1 + 64),
+           "api": "tafl_set_states + tafl_mcts_search + tafl_mcts_results_host + tafl_mcts_play_best + tafl_get_states, pinned host buffers, per move"}
+    for p in (st, mv, vis, cnt, best, status):
+        p.close()
+    return out
+
+
+def _mcts_variant(cx, E, SP, fresh, **kw):
+    args, torch = cx.args, cx.torch
+    g = fresh()
     try:
-        g.set_game_id_base(rank * n)
-        g.step_random(args.seed, 20, auto_reset=True)
-        sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, **kw)
+        sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, restart_finished=True, overlap=True, **kw)
+        t0 = time.perf_counter()
         sp.move(gather=False)
+        sp.flush(gather=False)
+        torch.cuda.synchronize()
+        moves = max(5, int(math.ceil(0.6 * args.min_region_s / (time.perf_counter() - t0))))
         s0, l0 = g.mcts_stats().as_dict(), g.launches
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(sp.stream)
         for _ in range(moves):
             sp.move(gather=False)
+        sp.flush(gather=False)
         b.record(sp.stream)
         torch.cuda.synchronize()
         ms = a.elapsed_time(b)
         s1 = g.mcts_stats().as_dict()
         sims = s1["sims"] - s0["sims"]
+        sp.close()
         return {"value": sims / (ms * 1e-3), "unit": "sims/s (this rank)", "ms_per_move": ms / moves, "moves_timed": moves,
                 "nodes_created_per_sim": (s1["nodes"] - s0["nodes"]) / max(1, sims), "mean_depth": (s1["depth_sum"] - s0["depth_sum"]) / max(1, sims),
                 "gpu_launches": int(g.launches - l0)}

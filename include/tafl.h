@@ -293,6 +293,7 @@ tafl_state* tafl_states_device(tafl_engine* e);
  * ascending (play.rs:157,166-183,189-225).  d_moves is [n_games][TAFL_MAX_MOVES] tafl_move,
  * d_counts [n_games]; both DEVICE buffers (NULL = engine-owned, see tafl_moves_device). */
 int tafl_legal_moves(tafl_engine* e, tafl_move* d_moves, uint32_t* d_counts);
+int tafl_legal_moves_async(tafl_engine* e, tafl_move* d_moves, uint32_t* d_counts);   /* enqueue only, no stream sync */
 int tafl_moves_device(tafl_engine* e, tafl_move** d_moves, uint32_t** d_counts);
 /* same, results copied to HOST buffers */
 int tafl_legal_moves_host(tafl_engine* e, tafl_move* h_moves, uint32_t* h_counts,
@@ -580,9 +581,10 @@ typedef struct {
 int tafl_pack_records(tafl_engine* e, void* d_out /* [n_games][TAFL_REC_STRIDE] */);
 /* The same rows, but only for the games that were searched (Ongoing at search time, n_moves > 0),
  * compacted in game order on the device: row k of d_out is the k-th such game.  The number of rows
- * goes to d_count (DEVICE u32, may be NULL) and to h_count (HOST u32, may be NULL; written when
- * the work enqueued here has run — pass pinned memory and wait for the stream / an event).
- * No host synchronisation: the replay-record path never stalls the next search. */
+ * goes to d_count (DEVICE u32, may be NULL) and to h_count[0]; h_count[1] receives the overflow
+ * flags of the search the rows come from (see tafl_mcts_overflow).  h_count (HOST u32[2], may be
+ * NULL) is written when the work enqueued here has run — pass pinned memory and wait for the
+ * stream / an event.  No host synchronisation: the replay-record path never stalls the next search. */
 int tafl_pack_records_compact(tafl_engine* e, void* d_out /* [n_games][TAFL_REC_STRIDE] */,
                               uint32_t* d_count, uint32_t* h_count);
 /* Restart every finished game from the engine's start position (episode counter + 1, history of
@@ -617,6 +619,13 @@ int tafl_gather_records(tafl_engine* e, void* comm, int n_ranks, int rank, int r
                         const void* d_send /* [n_local][TAFL_REC_STRIDE] */, uint32_t n_local,
                         void* d_recv /* root only: [recv_capacity_rows][TAFL_REC_STRIDE] */,
                         uint64_t recv_capacity_rows, uint32_t* h_counts /* [n_ranks] */);
+/* The same exchange enqueued on `stream` (a cudaStream_t of the engine's device; NULL = the engine's
+ * stream) — the caller orders it behind tafl_pack_records with an event, so the gather of move k
+ * overlaps the search of move k+1 on the engine's stream and the one host wait this call contains
+ * (the all-gathered row counts) never stalls the search. */
+int tafl_gather_records_on(tafl_engine* e, void* comm, int n_ranks, int rank, int root,
+                           const void* d_send, uint32_t n_local, void* d_recv,
+                           uint64_t recv_capacity_rows, uint32_t* h_counts, void* stream);
 
 #ifdef __cplusplus
 }

@@ -24,12 +24,14 @@ def main():
     g = E.LockstepGames(E.preset.rules.BRANDUBH, E.preset.boards.BRANDUBH, n, local, 64)
     g.set_game_id_base(rank * 100000)
     g.step_random(3, 10 + 5 * rank, auto_reset=False)
-    sp = SP.SelfPlay(g, num_sims=100)
+    from alphazeroforhnefatafl_b200 import _abi as A  # noqa: E402
+    sp = SP.SelfPlay(g, num_sims=100, native_gather=False)
     uid = [SP.NcclGather.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     ng = SP.NcclGather(g, uid[0], world, rank)
-    recv = torch.empty((world * (512 + 64 * world), 1592), dtype=torch.uint8, device="cuda") if rank == 0 else None
+    recv = torch.empty((world * (512 + 64 * world), A.REC_STRIDE), dtype=torch.uint8, device="cuda") if rank == 0 else None
     ok = True
+    seen = []
     for mv in range(12):
         rows = sp.move(gather=False).contiguous()
         torch.cuda.synchronize()
@@ -38,8 +40,30 @@ def main():
         if rank == 0:
             same = a.shape == b.shape and torch.equal(a.cpu(), b.cpu())
             ok = ok and same
+            seen.append(b.cpu().clone())
             print("move %2d rows per rank %s  c-abi == torch.distributed: %s" % (mv, list(counts), same), flush=True)
     ng.close()
+    sp.close()
+    g.close()
+    # The product path: SelfPlay with the native gather on its side stream, collection deferred by one move
+    # (overlap=True).  The same games from the same start must yield the same rows, move for move.
+    g = E.LockstepGames(E.preset.rules.BRANDUBH, E.preset.boards.BRANDUBH, n, local, 64)
+    g.set_game_id_base(rank * 100000)
+    g.step_random(3, 10 + 5 * rank, auto_reset=False)
+    sp = SP.SelfPlay(g, num_sims=100, overlap=True)
+    assert sp.ng is not None
+    got = []
+    for mv in range(12):
+        out = sp.move()
+        if mv > 0 and rank == 0:
+            got.append(out.cpu().clone())
+    out = sp.flush()
+    if rank == 0:
+        got.append(out.cpu().clone())
+        same = len(got) == len(seen) and all(x.shape == y.shape and torch.equal(x, y) for x, y in zip(got, seen))
+        ok = ok and same
+        print("SelfPlay(overlap=True, native side-stream gather) == torch path over 12 moves: %s" % same, flush=True)
+    sp.close()
     g.close()
     dist.barrier()
     if rank == 0:

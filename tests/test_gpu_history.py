@@ -88,3 +88,29 @@ def test_history_differential(orc, built_lib, preset, width, cap):
         # set_states / reset forget the history of the games they touch
         g.reset()
         assert not g.history_len().any()
+
+
+def test_history_is_forgotten_by_mutators_that_do_not_record(orc, built_lib):
+    """ADVICE r01: only Game::do_play records (state, play).  The batch mutators without a reference counterpart
+    (random stepping, the MCTS move) forget the history of the games they advance, so undo_last_play never
+    jumps back over unrecorded plies and play_history never has holes."""
+    from alphazeroforhnefatafl_b200 import engine as E
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
+    n = 16
+    with E.LockstepGames(rules, fen, n, 0, 64) as g:
+        g.history_enable(8)
+        mv, cnt = g.legal_moves()
+        g.game_do_play(E.moves_to_plays(mv[:, 0], 64))
+        assert (g.history_len() == 1).all()
+        g.step_random(3, 2, auto_reset=False)
+        assert (g.history_len() == 0).all()
+        before = g.get_states()
+        g.undo_last_play()                                   # nothing recorded: no-op, as after set_states
+        assert g.get_states().tobytes() == before.tobytes()
+        mv, cnt = g.legal_moves()
+        g.game_do_play(E.moves_to_plays(mv[:, 0], 64))
+        assert (g.history_len() == 1).all()
+        g.mcts_configure(30)
+        g.mcts_search()
+        g.mcts_play_best(False)
+        assert (g.history_len() == 0).all()

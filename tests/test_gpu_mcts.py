@@ -80,6 +80,139 @@ def test_gpu_mcts_capacity_error(orc, built_lib):
         assert ei.value.code == A.ERR_CAPACITY
 
 
+def test_gpu_overflow_flag_is_per_search(orc, built_lib):
+    """the engine-wide overflow word used to stay set for ever.  A search that exhausts a pool
+    reports TAFL_ERR_CAPACITY with the pool named; the next search on the same engine, with room, is clean."""
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), orc.preset_board(A.PRESET_COPENHAGEN)
+    with E.LockstepGames(rules, fen, 8, 0, 128) as g:
+        roots = g.get_states()
+        g.mcts_configure(64, 1.0, 1e-4, edge_capacity=500)
+        with pytest.raises(TaflError) as ei:
+            g.mcts_search()
+        assert ei.value.code == A.ERR_CAPACITY and "edge pool" in str(ei.value)
+        g.mcts_search(sync=False)                     # the asynchronous call does not report ...
+        assert g.mcts_overflow() == 1                 # ... tafl_mcts_overflow does (bit 0: edge pool)
+        g.mcts_configure(64, 1.0, 1e-4, edge_capacity=500, tree_reuse=False, node_capacity=65)   # same pools: no reallocation
+        with pytest.raises(TaflError):
+            g.mcts_search()
+        g.mcts_configure(64, 1.0, 1e-4)               # pools with room
+        g.mcts_search()                               # TAFL_OK
+        assert g.mcts_overflow() == 0
+        exp = orc.mcts_search(rules, 128, roots, 64)
+        assert np.array_equal(g.mcts_results()["visits"], exp["visits"])
+        # node pool: a carried tree outgrows node_capacity
+        g.mcts_configure(64, 1.0, 1e-4, tree_reuse=True, node_capacity=70)
+        with pytest.raises(TaflError) as ei:
+            for _ in range(6):
+                g.mcts_search()
+                g.mcts_advance()
+        assert ei.value.code == A.ERR_CAPACITY and "node pool" in str(ei.value)
+        g.reset()
+        g.mcts_configure(64, 1.0, 1e-4)
+        g.mcts_search()
+        assert g.mcts_overflow() == 0
+
+
+def test_gpu_records_compact_and_episodes(orc, built_lib):
+    """tafl_pack_records_compact == the rows of tafl_pack_records with n_moves > 0, in game order, with the row count
+    and overflow word delivered to pinned host memory; tafl_reset_finished restarts finished games and bumps the
+    episode counter the record header carries."""
+    import torch
+    from alphazeroforhnefatafl_b200 import selfplay as SP
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
+    n = 300
+    with E.LockstepGames(rules, fen, n, 0, 64) as g:
+        g.step_random(9, 70, auto_reset=False)        # a good part of the games is over
+        over0 = g.get_states()["status"] != 0
+        assert 0 < over0.sum() < n
+        g.mcts_configure(80)
+        g.mcts_search()
+        g.mcts_play_best(False)
+        full = torch.zeros((n, A.REC_STRIDE), dtype=torch.uint8, device="cuda")
+        comp = torch.full((n, A.REC_STRIDE), 0xEE, dtype=torch.uint8, device="cuda")
+        pin = E.PinnedArray(2, np.uint32)
+        pin.a[:] = 77
+        g.pack_records(full.data_ptr())
+        g.pack_records_compact(comp.data_ptr(), A.ptr(pin.a))
+        g.sync()
+        rf = SP.records_to_numpy(full)
+        keep = rf["h"]["n_moves"] > 0
+        assert np.array_equal(keep, ~over0)
+        assert int(pin.a[0]) == keep.sum() and int(pin.a[1]) == 0
+        rc = SP.records_to_numpy(comp[:int(pin.a[0])])
+        assert rc.tobytes() == rf[keep].tobytes()
+        assert (comp[int(pin.a[0]):].cpu().numpy() == 0xEE).all()      # nothing written behind the last row
+        assert not rf["h"]["episode"].any()
+        # restart the finished games: new episode, start position; the others are untouched
+        before = g.get_states()
+        fin = before["status"] != 0
+        assert g.reset_finished(want_count=True) == fin.sum()
+        after = g.get_states()
+        start = orc.state_from_fen(fen, 64, A.ATTACKER)[1][0]
+        assert after[fin].tobytes() == np.repeat(start, fin.sum()).tobytes() and after[~fin].tobytes() == before[~fin].tobytes()
+        g.mcts_search()
+        g.mcts_play_best(False)
+        g.pack_records(full.data_ptr())
+        g.sync()
+        rf2 = SP.records_to_numpy(full)
+        assert np.array_equal(rf2["h"]["episode"], fin.astype(np.uint32))
+        assert (rf2["h"]["n_moves"] > 0).all()
+        # outcomes are back-filled per (game id, episode): an episode-0 result never leaks into episode 1
+        z = SP.backfill_outcomes(np.concatenate([rf[keep], rf2]))
+        z2 = z[keep.sum():]
+        ended2 = (rf2["h"]["status"] & 0x80) != 0
+        assert np.isnan(z2[fin & ~ended2]).all() and not np.isnan(z2[ended2]).any()
+        pin.close()
+
+
+def test_gpu_record_holds_a_high_mobility_root(orc, built_lib):
+    """a root with more than 256 legal moves used to be truncated silently.  A record row now
+    holds TAFL_MAX_MOVES moves; checked on a synthetic 11x11 position with > 256 plays."""
+    import torch
+    from alphazeroforhnefatafl_b200 import selfplay as SP
+    rules = orc.preset_rules(A.PRESET_COPENHAGEN)
+    rng = np.random.default_rng(4)
+    best, best_st = 0, None
+    for _ in range(300):   # 24 attackers scattered thinly, the king in a corner region
+        cells = rng.permutation([(r, c) for r in range(11) for c in range(11) if (r, c) not in ((5, 5), (0, 0), (0, 10), (10, 0), (10, 10), (1, 1))])[:24]
+        grid = [["." for _ in range(11)] for _ in range(11)]
+        for r, c in cells:
+            grid[r][c] = "t"
+        grid[1][1] = "K"
+        rows = []
+        for r in range(11):
+            srow, run = "", 0
+            for ch in grid[r]:
+                if ch == ".":
+                    run += 1
+                else:
+                    srow += (str(run) if run else "") + ch
+                    run = 0
+            rows.append(srow + (str(run) if run else ""))
+        rc, st = orc.state_from_fen("/".join(rows), 128, A.ATTACKER)
+        assert rc == 0
+        c = int(orc.by_value(rules, 128).legal_moves_of(st)[1][0])
+        if c > best:
+            best, best_st = c, st
+    assert best > 256
+    with E.LockstepGames(rules, orc.preset_board(A.PRESET_COPENHAGEN), 2, 0, 128) as g:
+        g.set_states(np.repeat(best_st, 2))
+        g.mcts_configure(best + 40, 1.0, 1e-4)
+        g.mcts_search()
+        res = g.mcts_results()
+        g.mcts_play_best(False)
+        buf = torch.zeros((2, A.REC_STRIDE), dtype=torch.uint8, device="cuda")
+        g.pack_records(buf.data_ptr())
+        g.sync()
+        rec = SP.records_to_numpy(buf)
+        exp = orc.mcts_search(rules, 128, np.repeat(best_st, 2), best + 40)
+        for i in range(2):
+            assert rec["h"]["n_moves"][i] == best == exp["counts"][i]
+            assert np.array_equal(rec["moves"][i, :best], exp["moves"][i, :best]) and not rec["moves"][i, best:].any()
+            assert np.array_equal(rec["visits"][i, :best], exp["visits"][i, :best]) and rec["visits"][i, :best].sum() == best + 39
+            assert rec["h"]["best"][i] == exp["best"][i] == res["best"][i]
+
+
 def test_gpu_pack_records(orc, built_lib):
     import torch
     rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
@@ -98,7 +231,7 @@ def test_gpu_pack_records(orc, built_lib):
         after = g.get_states()
     raw = buf.cpu().numpy().reshape(n, A.REC_STRIDE)
     hdr = np.dtype([("game_id", "<u8"), ("ply", "<u4"), ("n_moves", "<u2"), ("side", "u1"), ("status", "u1"),
-                    ("att", "<u8", (2,)), ("def", "<u8", (2,)), ("best", "<u2"), ("_pad", "<u2", (3,))])
+                    ("att", "<u8", (2,)), ("def", "<u8", (2,)), ("best", "<u2"), ("_pad", "<u2"), ("episode", "<u4")])
     assert hdr.itemsize == 56
     for i in range(n):
         h = raw[i, :56].view(hdr)[0]

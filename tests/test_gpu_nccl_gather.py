@@ -1,6 +1,7 @@
-"""tafl_gather_records (C ABI, NCCL by dlopen): a one-rank communicator inside pytest (the GPU test box has
-one GPU); the N-rank check is scripts/nccl_gather_check.py under torchrun (gpurun --gpus 2), which
-compares the C-ABI gather with the torch.distributed gather row for row."""
+"""tafl_gather_records (C ABI, NCCL by dlopen): a one-rank communicator inside pytest, and — when the box
+has at least two GPUs — scripts/nccl_gather_check.py under torch.distributed.run with two ranks on ragged
+shards: the C-ABI gather against the torch.distributed gather row for row, and SelfPlay's side-stream
+overlap path against both."""
 import numpy as np
 import pytest
 
@@ -21,6 +22,7 @@ def test_single_rank_gather(orc, built_lib):
         sp = SP.SelfPlay(g, num_sims=60)
         rows = sp.move(gather=False)
         torch.cuda.synchronize()
+        assert rows.shape[0] == n                                        # every game was Ongoing: nothing compacted away
         ng = SP.NcclGather(g, SP.NcclGather.unique_id(), 1, 0)
         try:
             got, counts = ng.gather(rows.contiguous())
@@ -34,3 +36,22 @@ def test_single_rank_gather(orc, built_lib):
                 ng.gather(rows.contiguous(), recv=torch.empty((3, A.REC_STRIDE), dtype=torch.uint8, device="cuda"))
         finally:
             ng.close()
+
+
+def test_two_rank_gather_on_ragged_shards(built_lib):
+    import os
+    import socket
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(port), os.path.join(root, "scripts", "nccl_gather_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "NCCL GATHER CHECK OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

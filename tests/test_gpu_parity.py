@@ -341,3 +341,29 @@ def test_gpu_graph_pdl_stepping_equals_plain_launches(orc, built_lib, monkeypatc
         got = g.get_states()
     exp, _ = orc.random_playout(rules, fen, 128, 5, n, 128, game_id_base=77, n_threads=8)
     assert got.tobytes() == exp.tobytes()
+
+
+@pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS[:3])
+def test_gpu_legal_move_kernels_agree(orc, built_lib, monkeypatch, name, preset, width):
+    """get_all_possible_moves three ways — thread per game (TAFL_LM_G=1) and the warp-cooperative kernel with 8 and 16
+    lanes per game — against the oracle: same counts, same moves, same canonical order; finished games list nothing;
+    rows are written in whole 16-byte vectors whose unused tail is zero."""
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    n = 777                                   # not a multiple of any CTA's game count
+    rc, st0 = orc.state_from_fen(fen, width, A.ATTACKER)
+    states = np.concatenate([sample_positions(orc, rules, fen, width, 300, seed=13, max_steps=240),
+                             random_boards(orc, np.random.default_rng(8), len(fen.split("/")), width, n - 300)])
+    em, ec = orc.by_value(rules, width).legal_moves_of(states)
+    assert (ec == 0).any() and (ec > 0).any()
+    for G in ("1", "8", "16"):
+        monkeypatch.setenv("TAFL_LM_G", G)
+        with E.LockstepGames(rules, fen, n, 0, width) as g:
+            g.set_states(states)
+            mv, cnt = g.legal_moves()
+            assert np.array_equal(cnt, ec), G
+            for i in range(n):
+                assert np.array_equal(mv[i, :cnt[i]], em[i, :ec[i]]), (G, i)
+                if G != "1":
+                    assert not mv[i, cnt[i]:(cnt[i] + 7) // 8 * 8].any(), (G, i)
+            m2, c2 = g.legal_moves_of(states[:100])          # the by-value entry point runs the same kernel
+            assert np.array_equal(c2, ec[:100])

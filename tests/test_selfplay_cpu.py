@@ -88,6 +88,15 @@ def test_backfill_outcomes():
     assert list(z[:3]) == [1.0, -1.0, 1.0]
     assert list(z[3:5]) == [0.0, 0.0]
     assert np.isnan(z[5])
+    # one game id hosts several episodes (tafl_reset_finished): the result of episode 0 must not leak into episode 1
+    recs = np.zeros(5, SP.REC_DTYPE)
+    h = recs["h"]
+    h["game_id"] = 9
+    h["episode"] = [0, 0, 1, 1, 2]
+    h["side"] = [A.ATTACKER, A.DEFENDER, A.ATTACKER, A.DEFENDER, A.ATTACKER]
+    h["status"] = [0, A.status_win(A.WIN_KING_ESCAPED, True), 0, A.status_win(A.WIN_KING_CAPTURED, False), 0]
+    z = SP.backfill_outcomes(recs)
+    assert list(z[:4]) == [-1.0, 1.0, 1.0, -1.0] and np.isnan(z[4])
 
 
 def test_replay_buffer_rolling_window():
