@@ -9,7 +9,7 @@ import os
 from . import _abi as A
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libtafl_b200.so")
+LIB_PATH = os.environ.get("TAFL_LIB") or os.path.join(HERE, "libtafl_b200.so")   # TAFL_LIB: an A/B build variant (build.py --suffix)
 
 _lib = None
 

@@ -491,18 +491,40 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
     if (!cx.r_shieldwall_enabled()) return false;
     const int N = cx.n();
     if (to_r < 0 || to_c < 0 || to_r >= N || to_c >= N) return false;
+    const BB own = p.side(mover_def), opp = p.side(!mover_def);
+#if !defined(TAFL_SW_PREFILTER_V1)
+    {   // Exact pre-filter, as tile sets, so that every lane of a warp runs the same few dozen instructions
+        // whether or not its move landed on an edge.  The search counts enemy pieces pinned by a piece of the
+        // mover, walking away from `to` along the edge, and needs cnt >= 2 (logic.rs:485-522); any other tile
+        // ends the run.  So a wall exists only if the first TWO tiles on one side of `to` are both pinned
+        // enemies.  Ph / Pv = pinned enemies on the horizontal / vertical edges (the pinning piece sits one
+        // step inward); they are confined to the two edge rows / columns, so the shifted tests cannot wrap.
+        constexpr int S = BB::STRIDE;
+        const BB tob = BB::bit(idx_of<BB>(to_r, to_c));
+        const BB hrows = cx.row0 | cx.rowL;
+        const BB Ph = opp & ((cx.row0 & own.template shr<S>()) | (cx.rowL & own.template shl<S>()));
+        const BB Pv = opp & ((cx.col0 & own.template shr<1>()) | (cx.colL & own.template shl<1>()));
+        const BB hit_h = hrows & ((Ph.template shr<1>() & Ph.template shr<2>()) | (Ph.template shl<1>() & Ph.template shl<2>()));
+        const BB hit_v = (cx.col0 | cx.colL) & ~hrows &
+                         ((Pv.template shr<S>() & Pv.template shr<2 * S>()) | (Pv.template shl<S>() & Pv.template shl<2 * S>()));
+        if (!(tob & (hit_h | hit_v)).any()) return false;
+    }
+    int horizontal, away;  // away: +1 / -1 along the other axis (rows first: a corner tile searches along its row)
+    if (to_r == 0) { horizontal = 1; away = 1; }
+    else if (to_r == N - 1) { horizontal = 1; away = -1; }
+    else if (to_c == 0) { horizontal = 0; away = 1; }
+    else { horizontal = 0; away = -1; }
+#else
     int horizontal, away;  // away: +1 / -1 along the other axis
     if (to_r == 0) { horizontal = 1; away = 1; }
     else if (to_r == N - 1) { horizontal = 1; away = -1; }
     else if (to_c == 0) { horizontal = 0; away = 1; }
     else if (to_c == N - 1) { horizontal = 0; away = -1; }
     else return false;
-    const BB own = p.side(mover_def), opp = p.side(!mover_def);
     {   // Exact pre-filter.  The search counts enemy pieces pinned by a piece of the mover, walking
         // away from `to` along the edge, and needs cnt >= 2 (logic.rs:485-522); any other tile ends
         // the run.  So a wall exists only if the first TWO tiles on one side of `to` are both pinned
-        // enemies: eight single-tile tests in index arithmetic (this runs at ~8 lanes of every warp, so
-        // it is kept to a few dozen instructions); the tile-by-tile walk runs for real candidates only.
+        // enemies: eight single-tile tests in index arithmetic; the tile-by-tile walk runs for real candidates only.
         const int t = idx_of<BB>(to_r, to_c);
         const int de = horizontal ? 1 : BB::STRIDE;               // along the edge
         const int in = (horizontal ? BB::STRIDE : 1) * away;      // from the edge tile to its inward neighbour
@@ -512,6 +534,7 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
         const bool plus = (x + 2 <= N - 1) & pinned(t + de) & pinned(t + 2 * de);
         if (!(minus | plus)) return false;
     }
+#endif
     return shieldwall_walk(cx, p, mover_def, to_r, to_c, horizontal, away, caps);
 }
 

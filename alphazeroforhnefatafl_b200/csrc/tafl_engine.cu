@@ -233,7 +233,7 @@ k_step_moves(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ st
 // states come from the staged copy of the caller's array (`src`); a row whose side_len is not the
 // engine's is rejected here (flag raised, the game keeps its resident state) instead of by a host
 // loop over 4 MiB of input before anything is enqueued.
-template <class BB, int SP, int MINB, bool BYVAL = false>
+template <class BB, int SP, int MINB, bool BYVAL = false, bool SINGLE = false>
 __global__ void __launch_bounds__(STEP_BLOCK, MINB)
 k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
@@ -256,10 +256,11 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
     if (live) {
         tafl_state s = load_state((BYVAL ? src : states) + g);
         uint32_t act = 0;   // tafl_action of the last ply of this launch
-        for (uint32_t i = 0; i < steps; ++i) {
+        // one ply; false = this game stops stepping (finished, no auto-reset)
+        auto ply = [&](uint32_t i) {
             act = (uint32_t)s.status << 16;
             if (s.status != TAFL_STATUS_ONGOING) {   // rare: only these lanes pay for the reset
-                if (!auto_reset) break;
+                if (!auto_reset) return false;
                 s = unpack_state(start_w.v[0], start_w.v[1], start_w.v[2], start_w.v[3]);
             }
             StepEvt ev = random_step_ongoing(cx, s, seed, gid_base + g, ply0 + i);
@@ -273,6 +274,13 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
                 if (TAFL_STATUS_IS_DRAW(ev.status)) atomicAdd(&stats->draw[TAFL_STATUS_REASON(ev.status) & 1], 1ull);
                 else atomicAdd(&stats->win[ev.status & 1][TAFL_STATUS_REASON(ev.status)], 1ull);
             }
+            return true;
+        };
+        if constexpr (SINGLE) {   // the lockstep graph launches one ply per kernel: no loop-carried copies of the state
+            ply(0);
+        } else {
+            for (uint32_t i = 0; i < steps; ++i)
+                if (!ply(i)) break;
         }
         store_state(states + g, s);
         actions[g] = act;
@@ -521,6 +529,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     e->sm_count = prop.multiProcessorCount;
     if (const char* v = std::getenv("TAFL_STEP_MINB")) e->step_minb = std::atoi(v);   // tuning knobs (profiles/sweeps)
     if (const char* v = std::getenv("TAFL_STEP_GRAPH")) e->step_graph_on = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_STEP_SINGLE")) e->step_single = std::atoi(v);
     if (const char* v = std::getenv("TAFL_STEP_PDL")) e->step_pdl_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_CHUNKS")) e->host_chunks = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_IO")) e->host_io = std::atoi(v);
@@ -873,11 +882,16 @@ static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t firs
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
     cudaError_t lerr = cudaSuccess;
-#define TAFL_STEP_LAUNCH(MINB)                                                                                        \
-    TAFL_SPEC_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, k_step_random<BB, SP, MINB>, cx, e->d_states + first, n,     \
+#define TAFL_STEP_LAUNCH_(MINB, SINGLE)                                                                               \
+    TAFL_SPEC_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, k_step_random<BB, SP, MINB, false, SINGLE>, cx, e->d_states + first, n, \
                                                      state_words(e->start), seed, e->game_id_base + first, ply0, steps, \
                                                      auto_reset, e->d_stats, e->d_actions + first, d_ply_base,         \
                                                      (const tafl_state*)nullptr, (uint32_t*)nullptr)))
+#define TAFL_STEP_LAUNCH(MINB)                                     \
+    do {                                                           \
+        if (steps == 1 && e->step_single && MINB == 8) TAFL_STEP_LAUNCH_(8, true); \
+        else TAFL_STEP_LAUNCH_(MINB, false);                       \
+    } while (0)
     switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
         case 4: TAFL_STEP_LAUNCH(4); break;
         case 6: TAFL_STEP_LAUNCH(6); break;
@@ -886,6 +900,7 @@ static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t firs
         default: TAFL_STEP_LAUNCH(8); break;
     }
 #undef TAFL_STEP_LAUNCH
+#undef TAFL_STEP_LAUNCH_
     e->launches += 1;
     TAFL_CUDA_TRY(e, lerr);
     return TAFL_OK;

@@ -65,6 +65,7 @@ struct tafl_engine {
     int lm_group = 8;                  // TAFL_LM_G: lanes per game of k_legal_moves_g (16/8); 1 = thread-per-game k_legal_moves
     int step_minb = 8;                 // k_step_random variant: CTAs of 64 threads resident per SM (8: one wave for 65 536 games)
     // lockstep plies as ONE CUDA graph of n_steps kernel nodes joined by programmatic (PDL) edges
+    int step_single = 1;               // TAFL_STEP_SINGLE=0: one-ply launches run the general multi-ply kernel
     int step_graph_on = 1;             // TAFL_STEP_GRAPH=0 falls back to plain launches
     int step_pdl_on = 1;               // TAFL_STEP_PDL=0: plain (full-serialisation) edges in the graph
     cudaGraphExec_t step_graph = nullptr;

@@ -17,7 +17,9 @@ namespace tafl {
 
 template <class BB>
 struct MoveSel {
-    BB plane[5];
+    BB plane[5];   // bit b of the per-tile count (before the correction below)
+    BB minus;      // tiles whose count is one less than the planes say: a soldier whose run crosses the empty
+                   // throne cannot stop there (play.rs:208-211); kept apart so that no bit-sliced decrement is needed
     int total;
     int def_side;
 };
@@ -103,6 +105,70 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def
     const BB src = p.kind(k);
     const BB thr = cx.throne;
     const bool noentry = cx.f_noentry(k) != 0, passblk = cx.f_pass_block(k) != 0, slow = cx.f_slow(k) != 0;
+    ms.minus = BB::zero();
+#if !defined(TAFL_COUNT_NESTED)
+    if constexpr (SP != SPEC_GENERIC) {
+        // Preset rules have no pass-block and no slow pieces, so a piece's number of plays along one ray is the
+        // LENGTH n of its run of walkable tiles (the empty throne counts as walkable here; see `minus`).  The binary
+        // digits of n come from run-length DOUBLING: R1, R2, R4, R8 = "the next 1, 2, 4, 8 tiles are walkable"
+        // (R2 = R1 & R1>>1 step, R4 = R2 & R2>>2 steps, ...), then b3 = R8, b2 = R4 & ~R8, and the lower digits are
+        // read off the same masks shifted past the part already accounted for (b1 from R2 moved 0 / 4 / 8 steps,
+        // b0 from R1 moved 0 / 2 / ... / 8 steps).  10 shifts and 11 logic ops per word and direction instead of the
+        // 10 shift+AND steps, the throne fix-up and the digit formulas of the distance-by-distance chain.
+        // Sideways no column guards are needed: the walk mask of a rightward ray drops column 0 (a run that wraps
+        // into the next row would have to include its column-0 tile), of a leftward ray the last column.
+        static_assert(MD <= 10, "digit formulas cover runs of up to 10 tiles");
+        BB dig[4][4];
+#pragma unroll
+        for (int dir = 0; dir < 4; ++dir) {
+            const BB Wd = dir == DIR_HP ? (walk & cx.not_col0) : dir == DIR_HM ? (walk & cx.not_colL) : walk;
+            // value of X at the tile k steps ahead, aligned to the source tile
+            auto T1 = [&](BB X) { return dir == DIR_VP ? X.template shr<S>() : dir == DIR_VM ? X.template shl<S>() : dir == DIR_HP ? X.template shr<1>() : X.template shl<1>(); };
+            auto T2 = [&](BB X) { return dir == DIR_VP ? X.template shr<2 * S>() : dir == DIR_VM ? X.template shl<2 * S>() : dir == DIR_HP ? X.template shr<2>() : X.template shl<2>(); };
+            auto T4 = [&](BB X) { return dir == DIR_VP ? X.template shr<4 * S>() : dir == DIR_VM ? X.template shl<4 * S>() : dir == DIR_HP ? X.template shr<4>() : X.template shl<4>(); };
+            auto T6 = [&](BB X) { return dir == DIR_VP ? X.template shr<6 * S>() : dir == DIR_VM ? X.template shl<6 * S>() : dir == DIR_HP ? X.template shr<6>() : X.template shl<6>(); };
+            auto T8 = [&](BB X) { return dir == DIR_VP ? X.template shr<8 * S>() : dir == DIR_VM ? X.template shl<8 * S>() : dir == DIR_HP ? X.template shr<8>() : X.template shl<8>(); };
+            const BB R1 = T1(Wd);
+            const BB R2 = R1 & T1(R1);
+            const BB R4 = R2 & T2(R2);
+            const BB R8 = MD >= 8 ? (R4 & T4(R4)) : BB::zero();
+            const BB b3 = R8;
+            const BB b2 = R4 & ~R8;
+            // b1: two more walkable tiles behind the 0 / 4 / 8 already counted
+            const BB hi2 = MD >= 10 ? (R8 & T8(R2)) : BB::zero();                 // n >= 10
+            const BB mid2 = MD >= 6 ? (b2 & T4(R2)) : BB::zero();                 // n in {6, 7}
+            const BB b1 = (R2 & ~R4) | mid2 | hi2;
+            // b0: one more walkable tile behind the even part 8 b3 + 4 b2 + 2 b1
+            const BB x0 = (R1 & ~b1) | (T2(R1) & b1);                             // even part 0 / 2
+            const BB x1 = MD >= 5 ? ((T4(R1) & ~b1) | ((MD >= 7 ? T6(R1) : BB::zero()) & b1)) : BB::zero();   // 4 / 6
+            const BB x2 = MD >= 9 ? (T8(R1) & ~b1) : BB::zero();                  // 8 (10 is the longest run: no tile behind it)
+            const BB b0 = (~R4 & x0) | (b2 & x1) | (b3 & x2);
+            dig[dir][0] = b0; dig[dir][1] = b1; dig[dir][2] = b2; dig[dir][3] = b3;
+            if (noentry) {
+                // sources on the throne's line whose run reaches the throne: d tiles before it with n >= d
+                const BB ge3 = R2 & T2(R1), ge5 = R4 & T4(R1);
+                BB reach = (R1 & throne_aligned<BB>(cx.n(), dir, 1)) | (R2 & throne_aligned<BB>(cx.n(), dir, 2)) |
+                           (ge3 & throne_aligned<BB>(cx.n(), dir, 3));
+                if (cx.m() >= 4) reach = reach | (R4 & throne_aligned<BB>(cx.n(), dir, 4));
+                if (cx.m() >= 5) reach = reach | (ge5 & throne_aligned<BB>(cx.n(), dir, 5));
+                static_assert(SpecTraits<SP>::N / 2 <= 5, "reach covers thrones up to 5 tiles from the edge");
+                ms.minus = ms.minus | reach;
+            }
+        }
+        // (VP + VM) + (HP + HM), ripple-carry over bit planes; a piece has at most 2(N-1) <= 20 plays
+        BB a[5], b[5];
+        add4(dig[0], dig[1], a);
+        add4(dig[2], dig[3], b);
+        BB c = a[0] & b[0];
+        ms.plane[0] = (a[0] ^ b[0]) & src;
+#pragma unroll
+        for (int i = 1; i < 5; ++i) {
+            ms.plane[i] = (a[i] ^ b[i] ^ c) & src;
+            c = (a[i] & b[i]) | (c & (a[i] ^ b[i]));
+        }
+        ms.minus = ms.minus & src;
+    } else {
+#else
     if constexpr (SP != SPEC_GENERIC) {
         // Preset rules have no pass-block and no slow pieces, so along one ray the sets E_1 >= E_2 >= ... are
         // nested and a piece's number of plays that way is the LENGTH of its run: its binary digits come
@@ -151,6 +217,7 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def
             c = (a[i] & b[i]) | (c & (a[i] ^ b[i]));
         }
     } else {
+#endif
         CsaAcc<BB> acc;
         acc.init();
         int n = 0;
@@ -192,7 +259,7 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def
         for (int b = 0; b < 5; ++b)
             if ((ck >> b) & 1) ms.plane[b] = ms.plane[b] | p.kbit;
     }
-    int total = 0;
+    int total = -ms.minus.popc();
 #pragma unroll
     for (int b = 0; b < 5; ++b) total += ms.plane[b].popc() << b;
     ms.total = total;
@@ -203,12 +270,12 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def
 template <class BB, int SP>
 TAFL_HD tafl_move select_move(const Ctx<BB, SP>& cx, const Pos<BB>& p, const MoveSel<BB>& ms, uint32_t k) {
     // word-level prefix
-    uint32_t pw[5] = {0, 0, 0, 0, 0};
+    uint32_t pw[5] = {0, 0, 0, 0, 0}, pm = 0;
     int wsel = 0;
     bool done = false;
 #pragma unroll
     for (int j = 0; j < BB::WORDS; ++j) {
-        uint32_t w = 0;
+        uint32_t w = 0u - (uint32_t)popc32(ms.minus.word(j));
 #pragma unroll
         for (int b = 0; b < 5; ++b) w += (uint32_t)popc32(ms.plane[b].word(j)) << b;
         const bool here = !done && k < w;
@@ -216,6 +283,7 @@ TAFL_HD tafl_move select_move(const Ctx<BB, SP>& cx, const Pos<BB>& p, const Mov
             wsel = j;
 #pragma unroll
             for (int b = 0; b < 5; ++b) pw[b] = ms.plane[b].word(j);
+            pm = ms.minus.word(j);
             done = true;
         }
         if (!done) k -= w;
@@ -225,7 +293,7 @@ TAFL_HD tafl_move select_move(const Ctx<BB, SP>& cx, const Pos<BB>& p, const Mov
 #pragma unroll
     for (int half = 16; half >= 1; half >>= 1) {
         const uint32_t m = ((1u << half) - 1u) << lo;
-        uint32_t w = 0;
+        uint32_t w = 0u - (uint32_t)popc32(pm & m);
 #pragma unroll
         for (int b = 0; b < 5; ++b) w += (uint32_t)popc32(pw[b] & m) << b;
         if (k >= w) { k -= w; lo += half; }
@@ -475,8 +543,11 @@ template <class BB, int SP>
 TAFL_HD int emit_piece_plays(const Ctx<BB, SP>& cx, int tile, int row, int col, int kind, const Rays& r, tafl_move* out, int off,
                              int cap) {
     constexpr int S = BB::STRIDE;
+    constexpr int MD = RayLen<BB, SP>::v;   // a ray holds at most N-1 plays
     const int mid = cx.m();
     const bool ne = cx.f_noentry(kind);
+    const int total = r.cnt[0] + r.cnt[1] + r.cnt[2] + r.cnt[3];
+    if (off + total > cap) return off + total;   // cannot happen on boards up to 11x11 (L <= 4 (N^2 - 1) = 480 < 512)
 #pragma unroll
     for (int dir = 0; dir < 4; ++dir) {
         const int cnt = r.cnt[dir];
@@ -488,12 +559,15 @@ TAFL_HD int emit_piece_plays(const Ctx<BB, SP>& cx, int tile, int row, int col, 
             else if (pp > mid) hole_at = pp - mid - 1;
         }
         int m = tile * 129;   // from | to << 7 with to == from
-        for (int j = 0; j < cnt; ++j) {
+        // fully unrolled, stores predicated on j < cnt: no data-dependent trip count, so the lanes of a warp
+        // (one piece each, rays of very different lengths) stay converged
+#pragma unroll
+        for (int j = 0; j < MD; ++j) {
             m += step;
             if (j == hole_at) m += step;
-            if (off < cap) out[off] = (tafl_move)m;
-            ++off;
+            if (j < cnt) out[off + j] = (tafl_move)m;
         }
+        off += cnt;
     }
     return off;
 }

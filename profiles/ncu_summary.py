@@ -1,7 +1,11 @@
 #!/usr/bin/env python
 """Summarise `ncu --set full` reports (.ncu-rep) into the small text/JSON files kept under profiles/.
 
-    python profiles/ncu_summary.py <tag> <name>=<report.ncu-rep> [...]
+    python profiles/ncu_summary.py <tag> <name>=<report.ncu-rep>[@key=number...] [...]
+
+`@key=number` attaches facts about the captured launch that ncu cannot know (e.g. sims_per_launch of the
+MCTS capture); the tag and the commit the capture was taken on (git HEAD, or NCU_COMMIT) are stored with
+every entry, so bench.py can show a stale capture for what it is.
 
 For every report: the raw-page metrics that carry the roofline argument (duration, DRAM bytes,
 registers, occupancy, issue-slot and ALU-pipe utilisation, divergence, stall reasons), averaged over
@@ -28,6 +32,10 @@ METRICS = [
     "sm__inst_executed_pipe_alu.sum", "sm__inst_executed_pipe_fp64.sum", "sm__inst_executed_pipe_lsu.sum",
     "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
     "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct", "smsp__warps_eligible.avg.per_cycle_active",
+    "l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_st.sum",
+    "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_st.sum", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_xu.sum", "sm__inst_executed_pipe_fma.sum",
     "smsp__inst_executed_op_local_ld.sum", "smsp__inst_executed_op_local_st.sum",
     "smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio",
     "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
@@ -109,9 +117,20 @@ def main():
     tag = sys.argv[1]
     merged_path = os.path.join(HERE, "ncu_summary.json")
     merged = json.load(open(merged_path)) if os.path.exists(merged_path) else {}
+    commit = os.environ.get("NCU_COMMIT")
+    if not commit:
+        try:
+            commit = subprocess.check_output(["git", "-C", HERE, "rev-parse", "--short", "HEAD"], text=True).strip()
+        except Exception:  # noqa: BLE001
+            commit = None
     for arg in sys.argv[2:]:
         name, rep = arg.split("=", 1)
+        rep, *extras = rep.split("@")
         s = raw_summary(rep)
+        s["commit"] = commit
+        for kv in extras:
+            k, v = kv.split("=", 1)
+            s[k] = float(v)
         rd = s.get("dram__bytes_read.sum", {"avg": 0, "unit": "byte"})
         wr = s.get("dram__bytes_write.sum", {"avg": 0, "unit": "byte"})
         scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}

@@ -100,15 +100,17 @@ def test_gpu_overflow_flag_is_per_search(orc, built_lib):
         assert g.mcts_overflow() == 0
         exp = orc.mcts_search(rules, 128, roots, 64)
         assert np.array_equal(g.mcts_results()["visits"], exp["visits"])
-        # node pool: a carried tree outgrows node_capacity
-        g.mcts_configure(64, 1.0, 1e-4, tree_reuse=True, node_capacity=70)
+    # node pool: a carried subtree + num_sims new nodes outgrow node_capacity (Brandubh: few moves, deep trees)
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), orc.preset_board(A.PRESET_BRANDUBH)
+    with E.LockstepGames(rules, fen, 8, 0, 64) as g:
+        g.mcts_configure(400, 1.0, 1e-4, tree_reuse=True, node_capacity=401)
         with pytest.raises(TaflError) as ei:
-            for _ in range(6):
+            for _ in range(8):
                 g.mcts_search()
                 g.mcts_advance()
         assert ei.value.code == A.ERR_CAPACITY and "node pool" in str(ei.value)
         g.reset()
-        g.mcts_configure(64, 1.0, 1e-4)
+        g.mcts_configure(400, 1.0, 1e-4)
         g.mcts_search()
         assert g.mcts_overflow() == 0
 
