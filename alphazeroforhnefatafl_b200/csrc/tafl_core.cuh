@@ -492,7 +492,7 @@ TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
     const int N = cx.n();
     if (to_r < 0 || to_c < 0 || to_r >= N || to_c >= N) return false;
     const BB own = p.side(mover_def), opp = p.side(!mover_def);
-#if !defined(TAFL_SW_PREFILTER_V1)
+#if defined(TAFL_SW_PREFILTER_TILES)   // measured r02b: 11.63 us per ply against 11.40 us for the index form below; kept for reference
     {   // Exact pre-filter, as tile sets, so that every lane of a warp runs the same few dozen instructions
         // whether or not its move landed on an edge.  The search counts enemy pieces pinned by a piece of the
         // mover, walking away from `to` along the edge, and needs cnt >= 2 (logic.rs:485-522); any other tile

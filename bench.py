@@ -475,7 +475,7 @@ def bench_legal_moves(cx, E, g, stream, flush, hbm_peak):
     moves, counts = g.legal_moves(0, min(n, 8192))
     l_bar = float(counts.mean())
     bytes_per_game = 64 + 4 + 2 * l_bar
-    res = {"kernel": "k_legal_moves_g<BB128, Copenhagen, G=%s>" % os.environ.get("TAFL_LM_G", "8"), "games": n, "us_per_launch": us_med,
+    res = {"kernel": "k_legal_moves_g<BB128, Copenhagen, G=%s>" % os.environ.get("TAFL_LM_G", "8 (16 for the 2048-game launch)"), "games": n, "us_per_launch": us_med,
            "us_min": us[0], "mean_legal_moves": l_bar, "bytes_per_game": bytes_per_game,
            "roofline": {"bound": "hbm", "achieved": bytes_per_game * n / (us_med * 1e-6) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": bytes_per_game * n / (us_med * 1e-6) / 1e9 / hbm_peak, "traffic": ncu_traffic("k_legal_moves_g"),
