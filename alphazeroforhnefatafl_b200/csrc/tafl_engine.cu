@@ -540,6 +540,8 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     if (const char* v = std::getenv("TAFL_MCTS_MINB")) e->mcts_minb = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_G")) e->mcts_group = std::atoi(v);
     if (const char* v = std::getenv("TAFL_LM_G")) e->lm_group = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_HOOK_GEN")) e->hook_gen = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_HOOK_FUSE")) e->hook_fuse = std::atoi(v);
     TAFL_CREATE_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_states, (size_t)n_games * sizeof(tafl_state)));
     TAFL_CREATE_TRY(cudaMalloc(&e->d_counts, (size_t)n_games * sizeof(uint32_t)));

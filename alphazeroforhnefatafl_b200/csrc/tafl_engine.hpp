@@ -62,6 +62,8 @@ struct tafl_engine {
     int host_io = 3;   // tafl_step_status with pinned caller buffers: bit 0 kernel reads the plays in place, bit 1 writes results in place
     int mcts_minb = 8;                 // k_mcts_sims variant: CTAs of 4 warps resident per SM
     int mcts_group = 16;               // TAFL_MCTS_G: lanes per tree of k_mcts_sims_g (32/16/8); 0 = first-generation k_mcts_sims
+    int hook_gen = 2;                  // TAFL_HOOK_GEN: evaluator-hook kernels, 2 = k_mcts_hook_round (G lanes per tree), 1 = warp-per-tree pair
+    int hook_fuse = 1;                 // TAFL_HOOK_FUSE: built-in searches fuse expand + next descent into one launch
     int lm_group = 0;                  // TAFL_LM_G: lanes per game of k_legal_moves_g (16/8; 0 = by batch size); 1 = thread-per-game k_legal_moves
     int step_minb = 8;                 // k_step_random variant: CTAs of 64 threads resident per SM (8: one wave for 65 536 games)
     // lockstep plies as ONE CUDA graph of n_steps kernel nodes joined by programmatic (PDL) edges

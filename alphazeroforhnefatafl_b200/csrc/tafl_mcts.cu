@@ -39,7 +39,8 @@ struct MctsPools {
     uint8_t* t_noised = nullptr;      // [n_games] this search's root already carries the noise
     double rg_eps = 0.0;
     cudaGraphExec_t round_graph = nullptr;   // num_sims rounds with a built-in evaluator (tafl_mcts_search_builtin)
-    int rg_kind = -1, rg_spec = -1;
+    int rg_kind = -1, rg_spec = -1, rg_gen = -1;
+    uint64_t rg_launches = 0;
     uint64_t rg_seed = 0;
     uint32_t rg_sims = 0;
     double rg_cpuct = 0, rg_draw = 0;
@@ -298,6 +299,7 @@ __device__ __forceinline__ void grp_puct_select(const MctsEdge* __restrict__ ed,
     out_a = best_a; out_N = best_N; out_child = best_child;
 }
 
+template <bool LAZY = true>
 __device__ __forceinline__ void grp_backup(uint4* __restrict__ n_hdr, MctsEdge* __restrict__ edges, uint32_t node, double v,
                                            unsigned gmask, int gl) {
     while (true) {
@@ -317,8 +319,9 @@ __device__ __forceinline__ void grp_backup(uint4* __restrict__ n_hdr, MctsEdge* 
             ph.y += 1u;
             n_hdr[parent] = ph;
             // edges are zeroed lazily: select reads [0, min(L, Ns + 1)), so edge index Ns becomes
-            // readable now (it is unvisited: the visited prefix is never longer than Ns)
-            if (ph.y < hdr_n_edges(ph.w)) {
+            // readable now (it is unvisited: the visited prefix is never longer than Ns).  Trees with
+            // per-action priors (evaluator hook) initialise every edge at expansion: LAZY = false.
+            if (LAZY && ph.y < hdr_n_edges(ph.w)) {
                 MctsEdge z;
                 z.Q = 0.0; z.N = 0u; z.child = 0u;
                 edges[ph.x + ph.y] = z;
@@ -1052,6 +1055,281 @@ k_mcts_expand_backup(MctsView mv, uint32_t n_trees, const float* __restrict__ l_
     warp_backup(n_hdr, edges, node, -v, lane);             // mcts.py:102: return -v
 }
 
+// ---------------------------------------------------------------------------------------------
+// Second-generation evaluator-hook kernel: G lanes per tree (32/G trees per warp) and BOTH halves of a
+// round in one launch — phase 1 finishes the previous round (mask / renormalise the evaluator's priors,
+// mcts.py:87-102, and back its value up), phase 2 runs the next descent to a leaf and emits the leaf
+// batch row.  A search of `sims` rounds is then  select | eval | (expand+select | eval) x (sims-1) | expand:
+// two launches per simulation instead of three, and the descent's create step (do_valid_move + the piece
+// table of the new child, the expensive straight-line part) is issued once per warp for all its trees,
+// as in k_mcts_sims_g.  The split C-ABI calls use the same kernel with one phase switched off.
+// Results are bit-identical to k_mcts_select_leaf + k_mcts_expand_backup (tested).
+// ---------------------------------------------------------------------------------------------
+template <int G>
+__device__ __forceinline__ void grp_puct_select_priors(const MctsEdge* __restrict__ ed, const double* __restrict__ prior, uint32_t L,
+                                                       uint32_t Ns, double cpuct, unsigned gmask, int gl, uint32_t& out_a,
+                                                       uint32_t& out_N, uint32_t& out_child) {
+    const double sq_vis = sqrt((double)Ns), sq_new = sqrt((double)Ns + MCTS_EPS);
+    double best_u = -INFINITY;
+    uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
+    for (uint32_t a0 = gl; a0 < L; a0 += 4 * G) {
+        MctsEdge e4[4];
+        double p4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) { e4[j] = ed[a]; p4[j] = prior[a]; }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) {
+                const double c = cpuct * p4[j];
+                double u;
+                if (e4[j].N > 0) u = e4[j].Q + (c * sq_vis) / (double)(1u + e4[j].N);
+                else u = c * sq_new;
+                if (u > best_u) { best_u = u; best_a = a; best_N = e4[j].N; best_child = e4[j].child; }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        const double ou = __shfl_xor_sync(gmask, best_u, o, G);
+        const uint32_t oa = __shfl_xor_sync(gmask, best_a, o, G);
+        const uint32_t on = __shfl_xor_sync(gmask, best_N, o, G);
+        const uint32_t oc = __shfl_xor_sync(gmask, best_child, o, G);
+        if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; best_N = on; best_child = oc; }
+    }
+    out_a = best_a; out_N = best_N; out_child = best_child;
+}
+
+// mcts.py:87-102 for the pending leaf of ONE tree by the full warp, then the backup of -v (the body of
+// k_mcts_expand_backup; np.sum needs all 32 lanes: lane = 8 * block + accumulator)
+__device__ __forceinline__ void warp_expand_backup_tree(const MctsView& mv, uint32_t tree, const float* __restrict__ l_priors,
+                                                        const float* __restrict__ l_values, int lane) {
+    const uint32_t node = mv.t_pending[tree];
+    if (node == MCTS_NO_PARENT) return;   // warp-uniform
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
+    const uint4 h = n_hdr[node];
+    const uint32_t L = hdr_n_edges(h.w), base = mv.t_edges[tree];
+    const float* const pf = l_priors + (size_t)tree * TAFL_MAX_MOVES;
+    const int blk = lane >> 3, acc = lane & 7;
+    double x[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
+        x[i] = (double)pf[a] * (a < L ? 1.0 : 0.0);   // self.Ps[s] * valids  (mcts.py:87)
+    }
+    double sum = warp_np_sum512(x, lane);                 // mcts.py:88
+    if (!(sum > 0)) {                                      // mcts.py:91-99: all valid moves were masked
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
+            x[i] = x[i] + (a < L ? 1.0 : 0.0);
+        }
+        sum = warp_np_sum512(x, lane);
+    }
+    MctsEdge z;
+    z.Q = 0.0; z.N = 0u; z.child = 0u;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
+        if (a < L) {
+            prior[base + a] = x[i] / sum;                  // mcts.py:90 / :99
+            edges[base + a] = z;
+        }
+    }
+    const double v = (double)l_values[tree];
+    __syncwarp();
+    if (lane == 0) {
+        n_hdr[node] = make_uint4(base, 0u, h.z, h.w | (1u << 20));   // expanded, Ns = 0 (mcts.py:101)
+        mv.t_edges[tree] = base + L;
+        mv.t_pending[tree] = MCTS_NO_PARENT;
+        atomicAdd(&mv.stats[ST_EDGES], (unsigned long long)L);
+        atomicAdd(&mv.stats[ST_SIMS], 1ull);
+        atomicMax(&mv.stats[ST_MAXEDGES], (unsigned long long)(base + L));
+    }
+    __syncwarp();
+    warp_backup(n_hdr, edges, node, -v, lane);             // mcts.py:102: return -v
+}
+
+template <class BB, int SP, int G>
+__global__ void __launch_bounds__(MCTS_WARPS * 32, 4)
+k_mcts_hook_round(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, double cpuct, double draw_value,
+                  tafl_state* __restrict__ l_state, uint8_t* __restrict__ l_planes, tafl_move* __restrict__ l_moves,
+                  uint32_t* __restrict__ l_counts, const float* __restrict__ l_priors, const float* __restrict__ l_values,
+                  uint32_t* __restrict__ any_overflow, int do_expand, int do_select) {
+    constexpr int TPW = 32 / G;
+    enum { M_NONE = 0, M_BACKUP, M_CREATE, M_LEAF };
+    const int lane = threadIdx.x & 31, gl = lane % G, gshift = (lane / G) * G;
+    const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << (G & 31)) - 1u) << gshift);
+    const uint32_t warp_tree0 = (blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5)) * TPW;
+    // ---- phase 1: the leaves evaluated since the last round (full warp per tree, one tree after the other)
+    if (do_expand) {
+#pragma unroll 1
+        for (int t = 0; t < TPW; ++t) {
+            const uint32_t tr = warp_tree0 + (uint32_t)t;
+            if (tr < n_trees) warp_expand_backup_tree(mv, tr, l_priors, l_values, lane);
+        }
+        __syncwarp();
+    }
+    if (!do_select) return;
+    // ---- phase 2: MCTS.search down to the next leaf (mcts.py:55-123), G lanes per tree
+    const uint32_t tree_raw = warp_tree0 + (uint32_t)(lane / G);
+    const bool live = tree_raw < n_trees;
+    const uint32_t tree = live ? tree_raw : 0u;
+    tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    const double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
+    uint32_t overflow = 0, want = 0, pending = MCTS_NO_PARENT;
+    const bool stop = !live || mv.t_overflow[tree] != 0;
+    int mode = M_NONE;
+    uint32_t node = 0, depth = 0, sel_a = 0, sel_base = 0;
+    uint4 h = make_uint4(0u, 0u, 0u, 0u);
+    double v = 0.0;
+    unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_term = 0;
+    if (!stop) {
+        while (true) {
+            h = n_hdr[node];
+            const uint32_t es = hdr_es(h.w);
+            if (es != ES_ONGOING) {   // mcts.py:77-81: no evaluation, the simulation completes here
+                v = -(es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value));
+                c_term += 1;
+                c_depth += depth;
+                mode = M_BACKUP;
+                break;
+            }
+            if (!hdr_expanded(h.w)) { mode = M_LEAF; break; }   // the root of a fresh tree
+            const uint32_t L = hdr_n_edges(h.w);
+            if (L == 0) { v = 0.0; mode = M_BACKUP; break; }
+            uint32_t a, bN, bchild;
+            grp_puct_select_priors<G>(edges + h.x, prior + h.x, L, h.y, cpuct, gmask, gl, a, bN, bchild);
+            if (bN == 0) { mode = M_CREATE; sel_a = a; sel_base = h.x; break; }
+            node = bchild;
+            depth += 1;
+        }
+    }
+    __syncwarp();   // every tree of the warp opens its new node together
+    if (mode == M_CREATE || mode == M_LEAF) {
+        tafl_state s = load_state(n_state + node);
+        uint32_t target = node, parent = h.z, pedge = hdr_pedge(h.w), es = ES_ONGOING;
+        bool leaf = true;
+        if (mode == M_CREATE) {   // getNextState (mcts.py:122-123)
+            const uint32_t n_nodes = mv.t_nodes[tree];
+            if (n_nodes >= mv.node_cap) {
+                overflow = OVF_NODES;
+                leaf = false;
+                mode = M_NONE;
+            } else {
+                const tafl_move m = grp_decode_edge<G>(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
+                                                       (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)sel_a, gmask, gshift, gl);
+                do_valid_move(cx, s, m);
+                target = n_nodes;
+                c_nodes += 1;
+                parent = node;
+                pedge = sel_a;
+                depth += 1;
+                es = es_code(s);
+                __syncwarp(gmask);   // every lane has read t_nodes
+                if (gl == 0) {
+                    mv.t_nodes[tree] = n_nodes + 1u;
+                    store_state(n_state + target, s);
+                    edges[sel_base + sel_a].child = target;
+                }
+                if (es != ES_ONGOING) {   // the new node is terminal (mcts.py:77-81)
+                    if (gl == 0) n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack(0, pedge, 0, es));
+                    v = -(es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value));
+                    c_term += 1;
+                    c_depth += depth;
+                    leaf = false;
+                    mode = M_BACKUP;
+                }
+            }
+        }
+        if (leaf) {   // mcts.py:83-86: ask the evaluator
+            const Pos<BB> p = load_pos(cx, s);
+            const int def_side = (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
+            uint32_t* const ptab = n_ptab + (size_t)target * MCTS_PT_MAX;
+            int n_pieces;
+            const int L = grp_build_ptab<G>(cx, p, def_side, ptab, gmask, gl, &n_pieces);
+            if ((uint32_t)L > mv.edge_cap - mv.t_edges[tree] || n_pieces > MCTS_PT_MAX || L > TAFL_MAX_MOVES) {
+                overflow = (n_pieces > MCTS_PT_MAX || L > TAFL_MAX_MOVES) ? OVF_PIECES : OVF_EDGES;
+                if (mode == M_CREATE && gl == 0) n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack(0, pedge, 0, es));
+                mode = M_NONE;
+            } else if (L == 0) {   // Ongoing position without plays: unreachable through do_play; expand empty, v = 0
+                if (gl == 0) n_hdr[target] = make_uint4(mv.t_edges[tree], 0u, parent, hdr_pack(0u, pedge, 1u, es, (uint32_t)n_pieces));
+                v = -0.0;
+                mode = M_BACKUP;
+            } else {
+                // the leaf batch row: position, planes, canonical move list (action index -> move)
+                if (gl == 0) {
+                    store_state(l_state + tree, s);
+                    n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack((uint32_t)L, pedge, 0u, es, (uint32_t)n_pieces));
+                }
+                {   // board_to_matrix (game/main.rs:55-83)
+                    const int n = cx.n(), mid = n / 2;
+                    const BB occ = p.occ(), king = p.king();
+                    uint8_t* const out = l_planes + (size_t)tree * (size_t)(n * n);
+                    for (int t = gl; t < n * n; t += G) {
+                        const int r = t / n, c = t - r * n, b = idx_of<BB>(r, c);
+                        int val = 0;
+                        if ((r == 0 || r == n - 1) && (c == 0 || c == n - 1)) val = 20;
+                        if (r == mid && c == mid) val = 30;
+                        if (occ.test(b)) val += king.test(b) ? 5 : 1;
+                        out[t] = (uint8_t)val;
+                    }
+                }
+                tafl_move* const mo = l_moves + (size_t)tree * TAFL_MAX_MOVES;
+                int before = 0;
+                for (int base = 0; base < n_pieces; base += G) {
+                    const int idx = base + gl;
+                    const uint32_t e = idx < n_pieces ? ptab[idx] : 0u;   // written by this same lane in grp_build_ptab
+                    const int c = pt_total(e);
+                    int incl = c;
+#pragma unroll
+                    for (int o = 1; o < G; o <<= 1) {
+                        const int t = __shfl_up_sync(gmask, incl, o, G);
+                        if (gl >= o) incl += t;
+                    }
+                    const int off = before + incl - c;
+                    for (int j = 0; j < c; ++j) mo[off + j] = pt_decode(cx, e, def_side, j);
+                    before += __shfl_sync(gmask, incl, G - 1, G);
+                }
+                want = (uint32_t)L;
+                pending = target;
+                c_depth += depth;
+                mode = M_NONE;
+            }
+            if (mode == M_BACKUP) node = target;
+        } else if (mode == M_BACKUP) {
+            node = target;
+        }
+        __syncwarp(gmask);
+    }
+    if (mode == M_BACKUP) {   // terminal node / empty expansion: the simulation completes without the evaluator
+        grp_backup<false>(n_hdr, edges, node, v, gmask, gl);
+        c_sims += 1;
+    }
+    if (gl == 0 && live) {
+        if (!stop) {
+            l_counts[tree] = want;
+            mv.t_pending[tree] = pending;
+        } else {
+            l_counts[tree] = 0u;
+            mv.t_pending[tree] = MCTS_NO_PARENT;
+        }
+        if (overflow) { mv.t_overflow[tree] = overflow; atomicOr(any_overflow, overflow); }
+        if (c_sims) atomicAdd(&mv.stats[ST_SIMS], c_sims);
+        if (c_nodes) atomicAdd(&mv.stats[ST_NODES], c_nodes);
+        if (c_depth) atomicAdd(&mv.stats[ST_DEPTH], c_depth);
+        if (c_term) atomicAdd(&mv.stats[ST_TERMINAL], c_term);
+    }
+}
+
 // built-in evaluators (device side of TAFL_EVAL_STUB / TAFL_EVAL_HASH), one warp per leaf
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
 k_eval_builtin(int kind, uint64_t seed, const tafl_state* __restrict__ l_state, const uint32_t* __restrict__ l_counts, uint32_t n,
@@ -1456,6 +1734,23 @@ static void fill_batch(tafl_engine* e, tafl_leaf_batch* b) {
     b->stream = (void*)e->stream;
 }
 
+// one launch of the second-generation hook kernel (phase 1 = expand + backup of the evaluated leaves, phase 2 = descent)
+static int hook_round_launch(tafl_engine* e, int do_expand, int do_select) {
+    MctsPools* m = e->mcts;
+    const uint32_t n = e->n_games;
+    const int G = (e->mcts_group == 32 || e->mcts_group == 8) ? e->mcts_group : 16;
+#define TAFL_HOOK_LAUNCH(GG)                                                                                                        \
+    TAFL_SPEC_DISPATCH(e, (k_mcts_hook_round<BB, SP, GG><<<grid_for(n, MCTS_WARPS * (32 / GG)), MCTS_WARPS * 32, 0, e->stream>>>(     \
+                              cx, m->v, n, m->cfg.cpuct, m->cfg.draw_value, m->l_state, m->l_planes, m->l_moves, m->l_counts,       \
+                              m->l_priors, m->l_values, m->d_any_overflow, do_expand, do_select)))
+    if (G == 32) TAFL_HOOK_LAUNCH(32);
+    else if (G == 8) TAFL_HOOK_LAUNCH(8);
+    else TAFL_HOOK_LAUNCH(16);
+#undef TAFL_HOOK_LAUNCH
+    MCTS_LAUNCHED(e);
+    return TAFL_OK;
+}
+
 extern "C" {
 
 int tafl_mcts_begin(tafl_engine* e) {
@@ -1505,10 +1800,15 @@ int tafl_mcts_select_leaves(tafl_engine* e, tafl_leaf_batch* out) {
     if (m->rounds >= m->cfg.num_sims) { e->err = "tafl_mcts_select_leaves: num_sims rounds already run (node pool is sized for num_sims)"; return TAFL_ERR_CAPACITY; }
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    TAFL_SPEC_DISPATCH(e, (k_mcts_select_leaf<BB, SP><<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(
-                              cx, m->v, n, m->cfg.cpuct, m->cfg.draw_value, m->l_state, m->l_planes, m->l_moves, m->l_counts,
-                              m->d_any_overflow)));
-    MCTS_LAUNCHED(e);
+    if (e->hook_gen >= 2) {
+        rc = hook_round_launch(e, 0, 1);
+        if (rc) return rc;
+    } else {   // first generation: one warp per tree (TAFL_HOOK_GEN=1; kept as the comparison point)
+        TAFL_SPEC_DISPATCH(e, (k_mcts_select_leaf<BB, SP><<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(
+                                  cx, m->v, n, m->cfg.cpuct, m->cfg.draw_value, m->l_state, m->l_planes, m->l_moves, m->l_counts,
+                                  m->d_any_overflow)));
+        MCTS_LAUNCHED(e);
+    }
     m->phase = 2;
     if (out) fill_batch(e, out);
     return TAFL_OK;
@@ -1521,8 +1821,13 @@ int tafl_mcts_expand_backup(tafl_engine* e) {
     if (m->phase != 2) { e->err = "tafl_mcts_expand_backup: no leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    k_mcts_expand_backup<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->l_priors, m->l_values);
-    MCTS_LAUNCHED(e);
+    if (e->hook_gen >= 2) {
+        rc = hook_round_launch(e, 1, 0);
+        if (rc) return rc;
+    } else {
+        k_mcts_expand_backup<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->l_priors, m->l_values);
+        MCTS_LAUNCHED(e);
+    }
     if (m->noise_eps != 0.0 && m->rounds == 0) {   // the roots expanded by this first round
         k_mcts_root_noise<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, n, m->d_noise, m->noise_eps, m->t_noised);
         MCTS_LAUNCHED(e);
@@ -1621,18 +1926,33 @@ int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
     // All num_sims rounds (select, evaluate, expand/backup) have static arguments: one CUDA graph,
     // captured once per (evaluator, seed, config), replaces 3 x num_sims launches.
     if (!m->round_graph || m->rg_kind != evaluator || m->rg_seed != seed || m->rg_sims != m->cfg.num_sims ||
-        m->rg_cpuct != m->cfg.cpuct || m->rg_draw != m->cfg.draw_value || m->rg_spec != e->spec || m->rg_eps != m->noise_eps) {
+        m->rg_cpuct != m->cfg.cpuct || m->rg_draw != m->cfg.draw_value || m->rg_spec != e->spec || m->rg_eps != m->noise_eps ||
+        m->rg_gen != e->hook_gen * 2 + e->hook_fuse) {
         if (m->round_graph) { cudaGraphExecDestroy(m->round_graph); m->round_graph = nullptr; }
         TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         const uint64_t before = e->launches;
         cudaGraph_t graph = nullptr;
         TAFL_CUDA_TRY(e, cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+        const bool fuse = e->hook_gen >= 2 && e->hook_fuse;
         for (uint32_t i = 0; i < m->cfg.num_sims && rc == TAFL_OK; ++i) {
-            rc = tafl_mcts_select_leaves(e, nullptr);
+            // round i: descent -> evaluator -> expand + backup.  Second generation: the expand + backup of round
+            // i is fused into the launch that runs the descent of round i + 1 (two launches per simulation);
+            // the root-noise kernel has to sit between the two after round 0, so that pair stays split.
+            const bool fused_in = fuse && i > 0 && !(m->noise_eps != 0.0 && i == 1);
+            if (fused_in) {
+                rc = hook_round_launch(e, 1, 1);
+                m->rounds += 1;
+            } else {
+                if (fuse && i > 0) rc = tafl_mcts_expand_backup(e);      // the split pair (root noise after round 0)
+                if (!rc) rc = tafl_mcts_select_leaves(e, nullptr);
+            }
             if (!rc) rc = tafl_eval_builtin(e, evaluator, seed);
-            if (!rc) rc = tafl_mcts_expand_backup(e);
+            if (!rc && !fuse) rc = tafl_mcts_expand_backup(e);
+            if (!rc && fuse) m->phase = 2;
         }
+        if (!rc && fuse) rc = tafl_mcts_expand_backup(e);   // the last round's leaves
         cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+        m->rg_launches = e->launches - before;   // kernels in the graph
         e->launches = before;
         m->phase = 1;
         m->rounds = 0;
@@ -1642,10 +1962,10 @@ int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
         cudaGraphDestroy(graph);
         TAFL_CUDA_TRY(e, ce);
         m->rg_kind = evaluator; m->rg_seed = seed; m->rg_sims = m->cfg.num_sims; m->rg_cpuct = m->cfg.cpuct;
-        m->rg_draw = m->cfg.draw_value; m->rg_spec = e->spec; m->rg_eps = m->noise_eps;
+        m->rg_draw = m->cfg.draw_value; m->rg_spec = e->spec; m->rg_eps = m->noise_eps; m->rg_gen = e->hook_gen * 2 + e->hook_fuse;
     }
     TAFL_CUDA_TRY(e, cudaGraphLaunch(m->round_graph, e->stream));
-    e->launches += 3ull * m->cfg.num_sims + (m->noise_eps != 0.0 ? 1 : 0);
+    e->launches += m->rg_launches;
     m->rounds = m->cfg.num_sims;
     return tafl_mcts_finish(e);
 }

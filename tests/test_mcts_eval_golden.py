@@ -452,3 +452,42 @@ def test_gpu_root_noise_matches_oracle(orc, built_lib, preset, width, sims, n_mo
         assert final.tobytes() == exp["final"].tobytes()
     plain = orc.mcts_episode(rules, width, roots, sims, n_moves, reuse, eval_seed=31, n_threads=8)
     assert not np.array_equal(plain["visits"], exp["visits"])
+
+
+@pytest.mark.gpu
+def test_gpu_hook_generations_are_bit_identical(orc, built_lib, monkeypatch):
+    """The evaluator-hook search three ways — first-generation warp-per-tree kernel pair (TAFL_HOOK_GEN=1), the
+    second-generation G-lanes-per-tree kernel with its two phases in separate launches (TAFL_HOOK_FUSE=0) and fused
+    (expand + next descent in one launch), G = 8 / 16 / 32 — against the oracle with the hash evaluator: visits, Q,
+    statistics; a tree count that is not a multiple of the trees per CTA; games that end inside the search."""
+    from alphazeroforhnefatafl_b200 import engine as E
+    from parity_cases import board_for, sample_positions
+    for preset, width, sims in ((A.PRESET_COPENHAGEN, 128, 90), (A.PRESET_BRANDUBH, 64, 260)):
+        rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+        roots = sample_positions(orc, rules, fen, width, 203, seed=97, max_steps=230)
+        exp = orc.mcts_search_eval(rules, width, roots, sims, 5, cpuct=1.3, draw_value=0.2, n_threads=8)
+        for gen, fuse, G in (("1", "1", "16"), ("2", "0", "16"), ("2", "1", "16"), ("2", "1", "8"), ("2", "1", "32")):
+            monkeypatch.setenv("TAFL_HOOK_GEN", gen)
+            monkeypatch.setenv("TAFL_HOOK_FUSE", fuse)
+            monkeypatch.setenv("TAFL_MCTS_G", G)
+            with E.LockstepGames(rules, fen, len(roots), 0, width) as g:
+                g.set_states(roots)
+                g.mcts_configure(sims, 1.3, 0.2)
+                g.mcts_search_builtin(A.EVAL_HASH, 5)
+                got = g.mcts_results()
+                st = g.mcts_stats().as_dict()
+                key = (preset, gen, fuse, G)
+                assert np.array_equal(got["counts"], exp["counts"]), key
+                assert np.array_equal(got["visits"], exp["visits"]), key
+                assert got["q"].tobytes() == exp["q"].tobytes(), key
+                for k in ("sims", "nodes", "edges", "terminal_hits", "depth_sum"):
+                    assert st[k] == getattr(exp["stats"], k), (key, k)
+                # the split C-ABI calls drive the same kernels: one more search, phase by phase, stub evaluator
+                g.mcts_begin()
+                for _ in range(12):
+                    g.mcts_select_leaves()
+                    g.eval_builtin(A.EVAL_STUB)
+                    g.mcts_expand_backup()
+                g.mcts_finish()
+                r12 = g.mcts_results()
+                assert (r12["visits"].sum(1)[roots["status"] == 0] == 11).all(), key
