@@ -135,7 +135,7 @@ class Stats(C.Structure):
 
 class MctsConfig(C.Structure):
     _fields_ = [("num_sims", C.c_uint32), ("cpuct", C.c_double), ("draw_value", C.c_double),
-                ("edge_capacity", C.c_uint32), ("flags", C.c_uint32), ("node_capacity", C.c_uint32), ("_pad", C.c_uint32)]
+                ("edge_capacity", C.c_uint32), ("flags", C.c_uint32), ("node_capacity", C.c_uint32), ("vl_width", C.c_uint32)]
 
 
 MCTS_TREE_REUSE = 1

@@ -463,6 +463,257 @@ k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_tr
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// k_mcts_sims_vl: the fused stub search with VIRTUAL LOSS — up to W <= G simulations in flight per tree
+// (north star: "select (PUCT with virtual loss)"; intent at src/mcts.rs:49-55; semantics defined and
+// pinned by oracle/mcts_oracle.hpp::run_from_root_vl; W = 1 is mcts.py's sequential search).
+// One batch of w simulations of a tree, by its group of G lanes:
+//   select   the w descents run one after the other (each sees the virtual losses of the earlier ones);
+//            lane i keeps the outcome of simulation i: the leaf, the edge to open and its decoded move;
+//   create   do_valid_move for ALL new children of the batch at once, one lane per child — the
+//            straight-line part that k_mcts_sims_g issues once per simulation with every lane of the
+//            group computing the same child is issued once per batch with every lane computing its own;
+//   expand   piece tables of the new children, group-cooperative, one child after the other;
+//   backup   in simulation order: virtual losses removed, real update (mcts.py:125-136).
+// The virtual-loss counts live in the top byte of the words they qualify: edge.N = Nsa | vl << 24,
+// node header .y = Ns | vl(node) << 24 (a search leaves them zero).  The uniform-prior prefix rule of
+// k_mcts_sims_g carries over with Ns_eff = Ns + vl(node): edges are first touched in index order, so
+// select reads [0, min(L, Ns_eff + 1)) and the edge that becomes readable is zeroed when Ns_eff grows.
+// ---------------------------------------------------------------------------------------------
+#define MCTS_VL_ONE (1u << 24)
+#define MCTS_VL_MASK 0x00FFFFFFu
+template <int G>
+__device__ __forceinline__ void grp_puct_select_vl(const MctsEdge* __restrict__ ed, uint32_t Lall, uint32_t ns_raw, double cpuct,
+                                                   unsigned gmask, int gl, uint32_t& out_a, uint32_t& out_Nraw, uint32_t& out_child) {
+    const uint32_t ns_eff = (ns_raw & MCTS_VL_MASK) + (ns_raw >> 24);
+    const double sq_vis = sqrt((double)ns_eff), sq_new = sqrt((double)ns_eff + MCTS_EPS);
+    const double c_uni = cpuct * (1.0 / (double)Lall);
+    const double t_vis = c_uni * sq_vis, u_new = c_uni * sq_new;
+    const uint32_t L = Lall < ns_eff + 1u ? Lall : ns_eff + 1u;
+    double best_u = -INFINITY;
+    uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
+    for (uint32_t a0 = gl; a0 < L; a0 += 4 * G) {
+        MctsEdge e4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) e4[j] = ed[a];
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) {
+                const uint32_t N = e4[j].N & MCTS_VL_MASK, vl = e4[j].N >> 24, nn = N + vl;
+                double u;
+                if (nn > 0) {
+                    const double qv = vl ? ((double)N * e4[j].Q - (double)vl) / (double)nn : e4[j].Q;
+                    u = qv + t_vis / (double)(1u + nn);
+                } else {
+                    u = u_new;
+                }
+                if (u > best_u) { best_u = u; best_a = a; best_N = e4[j].N; best_child = e4[j].child; }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        const double ou = __shfl_xor_sync(gmask, best_u, o, G);
+        const uint32_t oa = __shfl_xor_sync(gmask, best_a, o, G);
+        const uint32_t on = __shfl_xor_sync(gmask, best_N, o, G);
+        const uint32_t oc = __shfl_xor_sync(gmask, best_child, o, G);
+        if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; best_N = on; best_child = oc; }
+    }
+    out_a = best_a; out_Nraw = best_N; out_child = best_child;
+}
+
+// backup of one simulation of a batch: its virtual losses come off, the real update goes on
+__device__ __forceinline__ void grp_backup_vl(uint4* __restrict__ n_hdr, MctsEdge* __restrict__ edges, uint32_t node, double v,
+                                              unsigned gmask, int gl) {
+    while (true) {
+        const uint4 h = n_hdr[node];
+        if (h.z == MCTS_NO_PARENT) break;
+        const uint32_t parent = h.z, a = hdr_pedge(h.w);
+        uint4 ph = n_hdr[parent];
+        MctsEdge* const ep = edges + ph.x + a;
+        const MctsEdge e = *ep;
+        const uint32_t N = e.N & MCTS_VL_MASK, vl = e.N >> 24;
+        double q;
+        if (N > 0) q = ((double)N * e.Q + v) / (double)(N + 1u);
+        else q = v;
+        __syncwarp(gmask);
+        if (gl == 0) {
+            ep->Q = q;
+            ep->N = (N + 1u) | ((vl - 1u) << 24);
+            ph.y = ((ph.y & MCTS_VL_MASK) + 1u) | (((ph.y >> 24) - 1u) << 24);   // Ns += 1, one virtual loss less: Ns_eff unchanged
+            n_hdr[parent] = ph;
+        }
+        __syncwarp(gmask);
+        v = -v;
+        node = parent;
+    }
+}
+
+template <class BB, int SP, int G>
+__global__ void __launch_bounds__(MCTS_WARPS * 32, 4)
+k_mcts_sims_vl(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, uint32_t sims, uint32_t W, double cpuct,
+               double draw_value, uint32_t* __restrict__ any_overflow) {
+    constexpr int TPW = 32 / G;
+    enum { K_NONE = 0, K_TERM, K_ROOT, K_EMPTY, K_NEW, K_COLL };
+    const int lane = threadIdx.x & 31, gl = lane % G, gshift = (lane / G) * G;
+    const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << (G & 31)) - 1u) << gshift);
+    const uint32_t tree_raw = (blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5)) * TPW + (uint32_t)(lane / G);
+    const bool live = tree_raw < n_trees;
+    const uint32_t tree = live ? tree_raw : 0u;
+    tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    uint32_t n_nodes = mv.t_nodes[tree], n_edges_used = mv.t_edges[tree];
+    uint32_t overflow = mv.t_overflow[tree];
+    bool stop = !live || overflow != 0;
+    unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_edges = 0, c_term = 0;
+    if (W > (uint32_t)G) W = (uint32_t)G;
+    if (W < 1u) W = 1u;
+    uint32_t done = 0;
+    // every group of the warp takes part in the warp-wide convergence points until the slowest one is through
+    while (__any_sync(0xFFFFFFFFu, !stop && done < sims)) {
+        const bool active = !stop && done < sims;
+        uint32_t w = 0;
+        if (active) {
+            const uint4 h0 = n_hdr[0];
+            w = sims - done < W ? sims - done : W;
+            if (!hdr_expanded(h0.w) && hdr_es(h0.w) == ES_ONGOING) w = 1;   // one simulation per batch while the root is unexpanded
+        }
+        // ---- select: simulation i of the batch is remembered by lane i of the group
+        int my_kind = K_NONE;
+        uint32_t my_leaf = 0, my_parent = 0, my_pedge = 0, my_depth = 0;
+        tafl_move my_move = 0;
+        double my_v = 0.0;
+        for (uint32_t i = 0; i < w; ++i) {
+            int kind = K_NONE;
+            uint32_t node = 0, depth = 0, leaf = 0, parent = 0, pedge = 0;
+            tafl_move mvv = 0;
+            double v = 0.0;
+            while (true) {
+                uint4 h = n_hdr[node];
+                const uint32_t es = hdr_es(h.w);
+                if (es != ES_ONGOING) {   // mcts.py:77-81
+                    v = -(es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value));
+                    kind = K_TERM; leaf = node;
+                    break;
+                }
+                if (!hdr_expanded(h.w)) { kind = K_ROOT; leaf = node; break; }
+                const uint32_t L = hdr_n_edges(h.w);
+                if (L == 0) { kind = K_EMPTY; leaf = node; v = 0.0; break; }
+                uint32_t a, bNraw, bchild;
+                grp_puct_select_vl<G>(edges + h.x, L, h.y, cpuct, gmask, gl, a, bNraw, bchild);
+                depth += 1;
+                const bool fresh = (bNraw & MCTS_VL_MASK) == 0;        // (s,a) not in Qsa
+                const bool collide = fresh && (bNraw >> 24) != 0;      // ... and an earlier simulation of this batch is opening it
+                uint32_t child = bchild;
+                if (fresh && !collide) {
+                    if (n_nodes >= mv.node_cap) { overflow = OVF_NODES; break; }   // only reachable with tree reuse
+                    child = n_nodes++;
+                    c_nodes += 1;
+                    const tafl_state ps = load_state(n_state + node);
+                    mvv = grp_decode_edge<G>(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
+                                             (ps.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)a, gmask, gshift, gl);
+                }
+                __syncwarp(gmask);
+                if (gl == 0) {   // the virtual loss of this simulation on (s,a) and on s
+                    MctsEdge* const ep = edges + h.x + a;
+                    ep->N = bNraw + MCTS_VL_ONE;
+                    if (fresh && !collide) ep->child = child;
+                    const uint32_t ns_eff = (h.y & MCTS_VL_MASK) + (h.y >> 24) + 1u;
+                    reinterpret_cast<uint32_t*>(n_hdr + node)[1] = h.y + MCTS_VL_ONE;
+                    if (ns_eff < L) {   // the edge that becomes readable (untouched so far)
+                        MctsEdge z;
+                        z.Q = 0.0; z.N = 0u; z.child = 0u;
+                        edges[h.x + ns_eff] = z;
+                    }
+                }
+                __syncwarp(gmask);
+                if (fresh) {
+                    kind = collide ? K_COLL : K_NEW;
+                    leaf = child; parent = node; pedge = a;
+                    break;
+                }
+                node = child;
+            }
+            if (overflow) break;
+            if (gl == (int)i) { my_kind = kind; my_leaf = leaf; my_parent = parent; my_pedge = pedge; my_depth = depth; my_move = mvv; my_v = v; }
+        }
+        if (overflow) { stop = true; w = 0; my_kind = K_NONE; }
+        __syncwarp();   // ---- create: every new child of every tree of the warp, one lane each
+        if (my_kind == K_NEW) {
+            tafl_state s = load_state(n_state + my_parent);
+            do_valid_move(cx, s, my_move);
+            store_state(n_state + my_leaf, s);
+            n_hdr[my_leaf] = make_uint4(0u, 0u, my_parent, hdr_pack(0, my_pedge, 0, es_code(s)));
+        }
+        __syncwarp();
+        // ---- expand (mcts.py:83-102, stub evaluator), one leaf after the other, group-cooperative
+        for (uint32_t i = 0; i < w; ++i) {
+            const int kind = __shfl_sync(gmask, my_kind, (int)i, G);
+            const uint32_t leaf = __shfl_sync(gmask, my_leaf, (int)i, G);
+            const uint32_t depth = __shfl_sync(gmask, my_depth, (int)i, G);
+            if (kind == K_NONE || kind == K_EMPTY) continue;
+            c_depth += depth;
+            if (kind == K_TERM) { c_term += 1; continue; }
+            const uint4 h = n_hdr[leaf];
+            const uint32_t es = hdr_es(h.w);
+            double v = -0.0;
+            if (es != ES_ONGOING) {   // the new (or collided) child is terminal
+                v = -(es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value));
+                c_term += 1;
+            } else if (kind != K_COLL) {
+                const tafl_state s = load_state(n_state + leaf);
+                const Pos<BB> p = load_pos(cx, s);
+                int n_pieces;
+                const int L = grp_build_ptab<G>(cx, p, (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, n_ptab + (size_t)leaf * MCTS_PT_MAX, gmask,
+                                                gl, &n_pieces);
+                if ((uint32_t)L > mv.edge_cap - n_edges_used || n_pieces > MCTS_PT_MAX) {
+                    overflow = n_pieces > MCTS_PT_MAX ? OVF_PIECES : OVF_EDGES;
+                    break;
+                }
+                if (gl == 0) {
+                    MctsEdge z;
+                    z.Q = 0.0; z.N = 0u; z.child = 0u;
+                    if (L > 0) edges[n_edges_used] = z;   // Ns_eff = 0: edge 0 is the only readable one
+                    n_hdr[leaf] = make_uint4(n_edges_used, 0u, h.z, hdr_pack((uint32_t)L, hdr_pedge(h.w), 1u, es, (uint32_t)n_pieces));
+                }
+                n_edges_used += (uint32_t)L;
+                c_edges += (unsigned long long)L;
+            }
+            if (gl == (int)i) my_v = v;
+        }
+        if (overflow) { stop = true; w = 0; }
+        __syncwarp(gmask);
+        // ---- backup, in simulation order
+        for (uint32_t i = 0; i < w; ++i) {
+            const int kind = __shfl_sync(gmask, my_kind, (int)i, G);
+            const uint32_t leaf = __shfl_sync(gmask, my_leaf, (int)i, G);
+            const double v = __shfl_sync(gmask, my_v, (int)i, G);
+            if (kind == K_NONE) continue;
+            grp_backup_vl(n_hdr, edges, leaf, v, gmask, gl);
+            c_sims += 1;
+        }
+        done += w;
+        if (active && w == 0) stop = true;
+    }
+    if (gl == 0 && live) {
+        mv.t_nodes[tree] = n_nodes;
+        mv.t_edges[tree] = n_edges_used;
+        if (overflow) { mv.t_overflow[tree] = overflow; atomicOr(any_overflow, overflow); }
+        atomicAdd(&mv.stats[ST_SIMS], c_sims);
+        atomicAdd(&mv.stats[ST_NODES], c_nodes);
+        atomicAdd(&mv.stats[ST_DEPTH], c_depth);
+        atomicAdd(&mv.stats[ST_EDGES], c_edges);
+        atomicAdd(&mv.stats[ST_TERMINAL], c_term);
+        atomicMax(&mv.stats[ST_MAXEDGES], (unsigned long long)n_edges_used);
+    }
+}
+
 // MCTS.getActionProb (mcts.py:40-47), temp = 0 with first-max: root visit counts, Q, moves, argmax
 template <class BB, int SP>
 __global__ void __launch_bounds__(MCTS_WARPS * 32)
@@ -1103,12 +1354,11 @@ __device__ __forceinline__ void grp_puct_select_priors(const MctsEdge* __restric
     out_a = best_a; out_N = best_N; out_child = best_child;
 }
 
-// mcts.py:87-102 for the pending leaf of ONE tree by the full warp, then the backup of -v (the body of
-// k_mcts_expand_backup; np.sum needs all 32 lanes: lane = 8 * block + accumulator)
-__device__ __forceinline__ void warp_expand_backup_tree(const MctsView& mv, uint32_t tree, const float* __restrict__ l_priors,
-                                                        const float* __restrict__ l_values, int lane) {
-    const uint32_t node = mv.t_pending[tree];
-    if (node == MCTS_NO_PARENT) return;   // warp-uniform
+// mcts.py:87-101 for the pending leaf `node` of ONE tree by the full warp (np.sum needs all 32 lanes: lane = 8 * block +
+// accumulator holds the 16 evaluator outputs pfv[i] = priors[block * 128 + accumulator + 8 i], loaded by the caller so
+// that the loads of all the warp's trees are in flight together).  The backup of -v is left to the tree's own group.
+__device__ __forceinline__ void warp_expand_tree(const MctsView& mv, uint32_t tree, uint32_t node, const float (&pfv)[16],
+                                                 const float* __restrict__ l_priors, int lane) {
     uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
     MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
     double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
@@ -1120,10 +1370,11 @@ __device__ __forceinline__ void warp_expand_backup_tree(const MctsView& mv, uint
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
         const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
-        x[i] = (double)pf[a] * (a < L ? 1.0 : 0.0);   // self.Ps[s] * valids  (mcts.py:87)
+        x[i] = (double)pfv[i] * (a < L ? 1.0 : 0.0);   // self.Ps[s] * valids  (mcts.py:87)
     }
     double sum = warp_np_sum512(x, lane);                 // mcts.py:88
-    if (!(sum > 0)) {                                      // mcts.py:91-99: all valid moves were masked
+    const bool fallback = !(sum > 0);                      // mcts.py:91-99: all valid moves were masked
+    if (fallback) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
             const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
@@ -1131,17 +1382,16 @@ __device__ __forceinline__ void warp_expand_backup_tree(const MctsView& mv, uint
         }
         sum = warp_np_sum512(x, lane);
     }
+    // Ps /= sum for the valid actions, one action per lane (the np.sum layout above would leave 24 of the 32 lanes idle
+    // here): the numerator is recomputed from the evaluator output with the same operations, so the quotient is the same
     MctsEdge z;
     z.Q = 0.0; z.N = 0u; z.child = 0u;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        const uint32_t a = (uint32_t)(blk * 128 + acc + 8 * i);
-        if (a < L) {
-            prior[base + a] = x[i] / sum;                  // mcts.py:90 / :99
-            edges[base + a] = z;
-        }
+    for (uint32_t a = (uint32_t)lane; a < L; a += 32u) {
+        double xa = (double)pf[a] * 1.0;
+        if (fallback) xa = xa + 1.0;
+        prior[base + a] = xa / sum;                        // mcts.py:90 / :99
+        edges[base + a] = z;
     }
-    const double v = (double)l_values[tree];
     __syncwarp();
     if (lane == 0) {
         n_hdr[node] = make_uint4(base, 0u, h.z, h.w | (1u << 20));   // expanded, Ns = 0 (mcts.py:101)
@@ -1151,8 +1401,6 @@ __device__ __forceinline__ void warp_expand_backup_tree(const MctsView& mv, uint
         atomicAdd(&mv.stats[ST_SIMS], 1ull);
         atomicMax(&mv.stats[ST_MAXEDGES], (unsigned long long)(base + L));
     }
-    __syncwarp();
-    warp_backup(n_hdr, edges, node, -v, lane);             // mcts.py:102: return -v
 }
 
 template <class BB, int SP, int G>
@@ -1166,13 +1414,33 @@ k_mcts_hook_round(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t 
     const int lane = threadIdx.x & 31, gl = lane % G, gshift = (lane / G) * G;
     const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << (G & 31)) - 1u) << gshift);
     const uint32_t warp_tree0 = (blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5)) * TPW;
-    // ---- phase 1: the leaves evaluated since the last round (full warp per tree, one tree after the other)
+    // ---- phase 1: the leaves evaluated since the last round.  Normalising the priors needs the full warp per tree
+    // (np.sum's association order), so the warp's trees take turns — with the evaluator outputs of all of them
+    // requested up front — and each tree's own group then backs its value up, all groups at once.
     if (do_expand) {
-#pragma unroll 1
+        const uint32_t my_tree = warp_tree0 + (uint32_t)(lane / G);
+        const uint32_t my_pending = my_tree < n_trees ? mv.t_pending[my_tree] : MCTS_NO_PARENT;
+        const double my_v = my_pending != MCTS_NO_PARENT ? (double)l_values[my_tree] : 0.0;
+        float pfv[TPW][16];
+        uint32_t pend[TPW];
+        const int blk = lane >> 3, acc = lane & 7;
+#pragma unroll
         for (int t = 0; t < TPW; ++t) {
             const uint32_t tr = warp_tree0 + (uint32_t)t;
-            if (tr < n_trees) warp_expand_backup_tree(mv, tr, l_priors, l_values, lane);
+            pend[t] = tr < n_trees ? mv.t_pending[tr] : MCTS_NO_PARENT;   // warp-uniform
+            if (pend[t] != MCTS_NO_PARENT) {
+                const float* const pf = l_priors + (size_t)tr * TAFL_MAX_MOVES;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) pfv[t][i] = pf[blk * 128 + acc + 8 * i];
+            }
         }
+#pragma unroll
+        for (int t = 0; t < TPW; ++t)
+            if (pend[t] != MCTS_NO_PARENT) warp_expand_tree(mv, warp_tree0 + (uint32_t)t, pend[t], pfv[t], l_priors, lane);
+        __syncwarp();
+        if (my_pending != MCTS_NO_PARENT)   // mcts.py:102: return -v
+            grp_backup<false>(mv.n_hdr + (size_t)my_tree * mv.node_cap, mv.edges + (size_t)my_tree * mv.edge_cap, my_pending, -my_v,
+                              gmask, gl);
         __syncwarp();
     }
     if (!do_select) return;
@@ -1295,8 +1563,14 @@ k_mcts_hook_round(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t 
                         const int t = __shfl_up_sync(gmask, incl, o, G);
                         if (gl >= o) incl += t;
                     }
-                    const int off = before + incl - c;
-                    for (int j = 0; j < c; ++j) mo[off + j] = pt_decode(cx, e, def_side, j);
+                    if (c > 0) {   // the piece's plays by tile arithmetic (emit_piece_plays == pt_decode for j = 0 .. c-1)
+                        const int tile = (int)(e & 127u), row = tile / BB::STRIDE;
+                        Rays r;
+                        r.cnt[0] = (int)((e >> 8) & 15u); r.cnt[1] = (int)((e >> 12) & 15u);
+                        r.cnt[2] = (int)((e >> 16) & 15u); r.cnt[3] = (int)((e >> 20) & 15u);
+                        emit_piece_plays(cx, tile, row, tile - row * BB::STRIDE, (e & 0x80u) ? KIND_K : (def_side ? KIND_DS : KIND_AS), r, mo,
+                                         before + incl - c, TAFL_MAX_MOVES);
+                    }
                     before += __shfl_sync(gmask, incl, G - 1, G);
                 }
                 want = (uint32_t)L;
@@ -1437,6 +1711,7 @@ int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg) {
     if (c.node_capacity == 0) c.node_capacity = (c.num_sims + 1) * (reuse ? 4u : 1u);
     if (c.node_capacity < c.num_sims + 1) return TAFL_ERR_INVALID_ARG;
     if (c.edge_capacity == 0) c.edge_capacity = c.node_capacity * 160u;
+    if (c.vl_width > 16) { e->err = "tafl_mcts_configure: vl_width is at most 16"; return TAFL_ERR_INVALID_ARG; }
     if (e->mcts && e->mcts->cfg.num_sims == c.num_sims && e->mcts->cfg.edge_capacity == c.edge_capacity &&
         e->mcts->cfg.node_capacity == c.node_capacity && e->mcts->cfg.flags == c.flags) {
         e->mcts->cfg = c;   // same pools, possibly new cpuct / draw value
@@ -1492,7 +1767,7 @@ int tafl_mcts_search_async(tafl_engine* e) {
         return TAFL_ERR_INVALID_ARG;
     }
     const uint32_t n = e->n_games;
-    launch_tree_init(e, e->mcts_group == 32 || e->mcts_group == 16 || e->mcts_group == 8 ? 1 : 0);
+    launch_tree_init(e, (m->cfg.vl_width > 1 || e->mcts_group == 32 || e->mcts_group == 16 || e->mcts_group == 8) ? 1 : 0);
     MCTS_LAUNCHED(e);
     const unsigned grid = grid_for(n, MCTS_WARPS);
 #define TAFL_MCTS_LAUNCH(MINB)                                                                                          \
@@ -1502,7 +1777,10 @@ int tafl_mcts_search_async(tafl_engine* e) {
 #define TAFL_MCTS_LAUNCH_G(G, MINB)                                                                                         \
     TAFL_SPEC_DISPATCH(e, (k_mcts_sims_g<BB, SP, G, MINB><<<grid_for(n, MCTS_WARPS * (32 / G)), MCTS_WARPS * 32, 0, e->stream>>>( \
                               cx, m->v, n, m->cfg.num_sims, m->cfg.cpuct, m->cfg.draw_value, m->d_any_overflow)))
-    if (e->mcts_group == 16) {        // lanes per tree (TAFL_MCTS_G): 2 trees per warp
+    if (m->cfg.vl_width > 1) {        // virtual loss: vl_width (<= 16) simulations in flight per tree, 16 lanes per tree
+        TAFL_SPEC_DISPATCH(e, (k_mcts_sims_vl<BB, SP, 16><<<grid_for(n, MCTS_WARPS * 2), MCTS_WARPS * 32, 0, e->stream>>>(
+                                  cx, m->v, n, m->cfg.num_sims, m->cfg.vl_width, m->cfg.cpuct, m->cfg.draw_value, m->d_any_overflow)));
+    } else if (e->mcts_group == 16) {        // lanes per tree (TAFL_MCTS_G): 2 trees per warp
         TAFL_MCTS_LAUNCH_G(16, 4);
     } else if (e->mcts_group == 8) {  // 4 trees per warp
         TAFL_MCTS_LAUNCH_G(8, 4);

@@ -335,9 +335,10 @@ class LockstepGames:
         return s
 
     # -- MCTS (src/mcts.py) -----------------------------------------------------------------------
-    def mcts_configure(self, num_sims, cpuct=1.0, draw_value=1e-4, edge_capacity=0, tree_reuse=False, node_capacity=0):
+    def mcts_configure(self, num_sims, cpuct=1.0, draw_value=1e-4, edge_capacity=0, tree_reuse=False, node_capacity=0, vl_width=0):
+        """vl_width > 1: virtual loss, that many simulations in flight per tree (fused stub search only)"""
         cfg = A.MctsConfig(num_sims=num_sims, cpuct=cpuct, draw_value=draw_value, edge_capacity=edge_capacity,
-                           flags=A.MCTS_TREE_REUSE if tree_reuse else 0, node_capacity=node_capacity)
+                           flags=A.MCTS_TREE_REUSE if tree_reuse else 0, node_capacity=node_capacity, vl_width=vl_width)
         self._ck(lib().tafl_mcts_configure(self._h, C.byref(cfg)))
 
     def mcts_search(self, sync=True):

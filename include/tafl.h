@@ -448,7 +448,11 @@ typedef struct {
     uint32_t flags;             /* TAFL_MCTS_*                                            */
     uint32_t node_capacity;     /* per-tree node pool, 0 = default num_sims+1 (x4 with
                                    tree reuse; a tree that outgrows it -> TAFL_ERR_CAPACITY) */
-    uint32_t _pad;
+    uint32_t vl_width;          /* virtual loss: simulations in flight per tree in tafl_mcts_search (0 / 1 = mcts.py's
+                                   sequential search; up to 16).  Build-defined semantics, restated in
+                                   oracle/mcts_oracle.hpp::run_from_root_vl: a batch of vl_width descents each sees
+                                   the earlier ones as losses (n = N + vl, q = (N Q - vl) / n), then the new leaves
+                                   are expanded together and the batch is backed up in order.  Stub evaluator only. */
 } tafl_mcts_config;
 
 /* allocate node/edge pools for every resident game (idempotent for an equal config) */

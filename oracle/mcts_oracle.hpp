@@ -21,9 +21,11 @@
 // The arithmetic of select / expand / backup follows mcts.py line by line, in f64, with no FMA
 // contraction (compile with -ffp-contract=off).
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <functional>
 #include <limits>
+#include <utility>
 
 #include "tafl_oracle.hpp"
 
@@ -90,6 +92,8 @@ struct Mcts {
         std::vector<uint32_t> N;      // self.Nsa[(s,a)]; 0 == "(s,a) not in Qsa"
         std::vector<int32_t> child;   // node reached by (s,a), -1 = not created yet
         uint32_t Ns = 0;              // self.Ns[s]
+        std::vector<uint32_t> VL;     // virtual-loss mode: simulations of the current batch that hold (s,a) on their path
+        uint32_t vln = 0;             //                    ... that pass through s
         double P = 0.0;               // self.Ps[s][a], uniform over the valid moves
         std::vector<double> Pa;       // evaluator mode: self.Ps[s][a] per action (masked, renormalised)
     };
@@ -170,6 +174,7 @@ struct Mcts {
             n.P = L ? 1.0 / (double)L : 0.0;
             n.Q.assign(L, 0.0);
             n.N.assign(L, 0);
+            n.VL.assign(L, 0);
             n.child.assign(L, -1);
             n.Ns = 0;
             n.expanded = true;
@@ -230,11 +235,126 @@ struct Mcts {
     // cleared, mcts.py:20-26).  `root` walks down the retained tree.
     int root = 0;
     void run_from_root(uint32_t num_sims) {
+        if (vl_width > 1 && !eval) { run_from_root_vl(num_sims); return; }
         root_noised = false;
         noise_root();
         for (uint32_t i = 0; i < num_sims; ++i) {
             search(root, 0);
             stats.sims += 1;
+        }
+    }
+
+    // -----------------------------------------------------------------------------------------------------------
+    // Virtual-loss mode (north star: "select (PUCT with virtual loss)"; intent at src/mcts.rs:49-55; NOT in mcts.py,
+    // so build-defined and pinned only by this restatement): `vl_width` simulations are in flight per tree.
+    // One batch = w <= vl_width simulations, run in three sweeps, each in simulation-index order:
+    //   select   every simulation descends from the root with PUCT over the statistics AS IF each simulation that
+    //            currently holds an edge on its path had already lost there: n = N + vl, q = (N Q - vl) / n,
+    //            Ns_eff = Ns + vl(node); it then adds itself to vl along its own path.  A simulation stops at a
+    //            terminal node, at the (unexpanded) root, at the first edge nobody has followed yet (it creates the
+    //            child), or — collision — at an edge whose child another simulation of the same batch is creating.
+    //   expand   the new leaves are expanded (stub evaluator: uniform priors, v = 0); a collision takes the same
+    //            value as the simulation that created the child.
+    //   backup   every simulation removes its virtual losses and applies the real update of mcts.py:125-136.
+    // While the root is unexpanded a batch holds one simulation.  With vl_width == 1 no simulation ever sees a
+    // virtual loss, and the result is mcts.py's, bit for bit (the golden vectors guard that).
+    // Stub evaluator only (the evaluator-hook path batches across trees instead).
+    // -----------------------------------------------------------------------------------------------------------
+    uint32_t vl_width = 1;
+    void run_from_root_vl(uint32_t num_sims) {
+        enum { K_TERM = 1, K_ROOT, K_EMPTY, K_NEW, K_COLL };
+        struct Sim { std::vector<std::pair<int, int>> path; int leaf = 0, kind = 0; uint32_t depth = 0; double v = 0.0; };
+        uint32_t done = 0;
+        while (done < num_sims) {
+            uint32_t w = std::min<uint32_t>(vl_width, num_sims - done);
+            if (!nodes[root].expanded && nodes[root].Es == 0.0) w = 1;
+            std::vector<Sim> sims(w);
+            for (uint32_t i = 0; i < w; ++i) {   // ---- select
+                Sim& S = sims[i];
+                int idx = root;
+                while (true) {
+                    if (nodes[idx].Es != 0.0) { S.kind = K_TERM; S.leaf = idx; S.v = -nodes[idx].Es; break; }
+                    if (!nodes[idx].expanded) { S.kind = K_ROOT; S.leaf = idx; break; }
+                    const size_t L = nodes[idx].moves.size();
+                    if (L == 0) { S.kind = K_EMPTY; S.leaf = idx; S.v = 0.0; break; }
+                    int a = -1;
+                    {
+                        Node& n = nodes[idx];
+                        const uint32_t ns_eff = n.Ns + n.vln;
+                        const double t_vis = (cpuct * n.P) * std::sqrt((double)ns_eff);
+                        const double u_new = (cpuct * n.P) * std::sqrt((double)ns_eff + MCTS_EPS);
+                        double cur_best = -std::numeric_limits<double>::infinity();
+                        for (size_t k = 0; k < L; ++k) {
+                            const uint32_t nn = n.N[k] + n.VL[k];
+                            double u;
+                            if (nn > 0) {
+                                const double qv = n.VL[k] ? ((double)n.N[k] * n.Q[k] - (double)n.VL[k]) / (double)nn : n.Q[k];
+                                u = qv + t_vis / (double)(1u + nn);
+                            } else {
+                                u = u_new;
+                            }
+                            if (u > cur_best) { cur_best = u; a = (int)k; }
+                        }
+                    }
+                    const uint32_t vl_before = nodes[idx].VL[a];
+                    nodes[idx].VL[a] += 1;
+                    nodes[idx].vln += 1;
+                    S.path.push_back({idx, a});
+                    S.depth += 1;
+                    if (nodes[idx].N[a] == 0) {
+                        if (vl_before > 0) { S.kind = K_COLL; S.leaf = nodes[idx].child[a]; break; }
+                        auto res = logic.do_valid_play(nodes[idx].moves[a], nodes[idx].state);
+                        const int ch = new_node(res.first);
+                        nodes[idx].child[a] = ch;
+                        S.kind = K_NEW;
+                        S.leaf = ch;
+                        break;
+                    }
+                    idx = nodes[idx].child[a];
+                }
+            }
+            for (uint32_t i = 0; i < w; ++i) {   // ---- expand
+                Sim& S = sims[i];
+                Node& n = nodes[S.leaf];
+                if (S.kind == K_EMPTY) continue;
+                stats.depth_sum += S.depth;
+                if (S.kind == K_TERM) { stats.terminal_hits += 1; continue; }
+                if (n.Es != 0.0) { S.v = -n.Es; stats.terminal_hits += 1; continue; }   // new / collided child is terminal
+                if (S.kind == K_COLL) { S.v = -0.0; continue; }
+                n.moves = logic.get_all_possible_moves(n.state);
+                const size_t L = n.moves.size();
+                n.P = L ? 1.0 / (double)L : 0.0;
+                n.Q.assign(L, 0.0);
+                n.N.assign(L, 0);
+                n.VL.assign(L, 0);
+                n.child.assign(L, -1);
+                n.Ns = 0;
+                n.vln = 0;
+                n.expanded = true;
+                stats.edges += L;
+                S.v = -0.0;
+            }
+            for (uint32_t i = 0; i < w; ++i) {   // ---- backup (mcts.py:125-136), virtual losses removed
+                Sim& S = sims[i];
+                double v = S.v;
+                for (size_t k = S.path.size(); k-- > 0;) {
+                    Node& n = nodes[S.path[k].first];
+                    const int a = S.path[k].second;
+                    n.VL[a] -= 1;
+                    n.vln -= 1;
+                    if (n.N[a] > 0) {
+                        n.Q[a] = ((double)n.N[a] * n.Q[a] + v) / (double)(n.N[a] + 1);
+                        n.N[a] += 1;
+                    } else {
+                        n.Q[a] = v;
+                        n.N[a] = 1;
+                    }
+                    n.Ns += 1;
+                    v = -v;
+                }
+            }
+            stats.sims += w;
+            done += w;
         }
     }
     // play action a at the root; false if (root, a) was never traversed (no child to descend to)

@@ -477,10 +477,11 @@ double orc_np_sum(const double* a, uint64_t n) { return np_sum(a, (size_t)n); }
 // final states [n].  use_eval != 0 -> TAFL_EVAL_HASH evaluator.
 // `noise` (optional): root exploration noise [n][n_moves][TAFL_MAX_MOVES] f64, mixed in with weight eps
 // (Mcts::noise_root; evaluator searches only).
-int orc_mcts_episode_noise(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
-                           uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
-                           int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best,
-                           tafl_state* final_states, tafl_mcts_stats* stats, const double* noise, double eps) {
+}  // extern "C"
+static int mcts_episode_impl(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                             uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
+                             int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best,
+                             tafl_state* final_states, tafl_mcts_stats* stats, const double* noise, double eps, uint32_t vl_width) {
     return dispatch(width, [&](auto w) {
         using W = decltype(w);
         if (n_threads < 1) n_threads = 1;
@@ -495,6 +496,7 @@ int orc_mcts_episode_noise(const tafl_rules* r, int width, const tafl_state* roo
                     unpack_state(roots[g], &s);
                     GameLogic logic(*r, s.board.side_len);
                     Mcts<W> m(logic, cpuct, draw_value);
+                    m.vl_width = vl_width ? vl_width : 1;
                     if (use_eval)
                         m.eval = [eval_seed](const GameState<W>& gs, float* P, float* v) {
                             tafl_state ps;
@@ -547,6 +549,23 @@ int orc_mcts_episode_noise(const tafl_rules* r, int width, const tafl_state* roo
         }
         return 0;
     });
+}
+
+extern "C" {
+int orc_mcts_episode_noise(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                           uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
+                           int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best,
+                           tafl_state* final_states, tafl_mcts_stats* stats, const double* noise, double eps) {
+    return mcts_episode_impl(r, width, roots, n, num_sims, n_moves, reuse, cpuct, draw_value, use_eval, eval_seed, n_threads, visits,
+                             q, counts, best, final_states, stats, noise, eps, 1);
+}
+// the stub-evaluator episode with `vl_width` simulations in flight per tree (Mcts::run_from_root_vl)
+int orc_mcts_episode_vl(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                        uint32_t n_moves, int reuse, double cpuct, double draw_value, uint32_t vl_width, int n_threads,
+                        uint32_t* visits, double* q, uint32_t* counts, uint32_t* best, tafl_state* final_states,
+                        tafl_mcts_stats* stats) {
+    return mcts_episode_impl(r, width, roots, n, num_sims, n_moves, reuse, cpuct, draw_value, 0, 0, n_threads, visits, q, counts,
+                             best, final_states, stats, nullptr, 0.0, vl_width);
 }
 
 int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,

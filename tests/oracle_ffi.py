@@ -285,6 +285,26 @@ class Oracle:
         assert rc == 0, rc
         return dict(visits=visits, q=q, counts=counts, best=best, final=final, stats=stats)
 
+    def mcts_episode_vl(self, rules, width, roots, num_sims, n_moves, reuse, vl_width, cpuct=1.0, draw_value=1e-4, n_threads=1):
+        """the stub-evaluator episode with vl_width simulations in flight per tree (virtual loss)"""
+        roots = np.ascontiguousarray(roots)
+        n = len(roots)
+        visits = np.zeros((n, n_moves, A.MAX_MOVES), np.uint32)
+        q = np.zeros((n, n_moves, A.MAX_MOVES), np.float64)
+        counts = np.zeros((n, n_moves), np.uint32)
+        best = np.zeros((n, n_moves), np.uint32)
+        final = np.zeros(n, A.STATE_DTYPE)
+        stats = A.MctsStats()
+        f = self.lib.orc_mcts_episode_vl
+        f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_double, C.c_double,
+                      C.c_uint32, C.c_int] + [C.c_void_p] * 6
+        f.restype = C.c_int
+        rc = f(C.addressof(rules), width, roots.ctypes.data, n, num_sims, n_moves, int(reuse), cpuct, draw_value, int(vl_width),
+               n_threads, visits.ctypes.data, q.ctypes.data, counts.ctypes.data, best.ctypes.data, final.ctypes.data,
+               C.addressof(stats))
+        assert rc == 0, rc
+        return dict(visits=visits, q=q, counts=counts, best=best, final=final, stats=stats)
+
     def hash_eval(self, states, seed):
         states = np.ascontiguousarray(states)
         n = len(states)

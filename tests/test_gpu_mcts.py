@@ -347,3 +347,36 @@ def test_gpu_tree_reuse_dropped_when_the_search_kind_changes(orc, built_lib):
         got = g.mcts_results()
         exp = orc.mcts_search(rules, 64, after2, 120)
         assert np.array_equal(got["visits"], exp["visits"]) and got["q"].tobytes() == exp["q"].tobytes()
+
+
+@pytest.mark.parametrize("name,preset,width,sims", [("copenhagen", A.PRESET_COPENHAGEN, 128, 130), ("brandubh", A.PRESET_BRANDUBH, 64, 300),
+                                                    ("tablut", A.PRESET_TABLUT, 128, 200)])
+def test_gpu_virtual_loss_matches_oracle(orc, built_lib, name, preset, width, sims):
+    """k_mcts_sims_vl (W simulations in flight per tree) against oracle/mcts_oracle.hpp::run_from_root_vl at W = 1, 2, 4,
+    8, 16: visit counts, Q, statistics and the games played, over several moves with tree reuse, from positions that
+    include finished games and endgames (terminal leaves, collisions on narrow nodes).  W = 1 is the sequential search."""
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    roots = sample_positions(orc, rules, fen, width, 203, seed=41, max_steps=260)
+    n_moves = 3
+    seq = orc.mcts_episode(rules, width, roots, sims, n_moves, True, n_threads=8)
+    for W in (1, 2, 4, 8, 16):
+        exp = orc.mcts_episode_vl(rules, width, roots, sims, n_moves, True, W, n_threads=8)
+        if W == 1:
+            assert np.array_equal(exp["visits"], seq["visits"]) and exp["q"].tobytes() == seq["q"].tobytes()
+        with E.LockstepGames(rules, fen, len(roots), 0, width) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, 1.0, 1e-4, tree_reuse=True, vl_width=W)
+            for j in range(n_moves):
+                g.mcts_search()
+                r = g.mcts_results()
+                assert np.array_equal(r["counts"], exp["counts"][:, j]), (W, j)
+                assert np.array_equal(r["visits"], exp["visits"][:, j]), (W, j)
+                assert r["q"].tobytes() == exp["q"][:, j].tobytes(), (W, j)
+                g.mcts_advance()
+            assert g.get_states().tobytes() == exp["final"].tobytes(), W
+            st = g.mcts_stats().as_dict()
+            for k in ("sims", "nodes", "edges", "terminal_hits", "depth_sum"):
+                assert st[k] == getattr(exp["stats"], k), (W, k)
+    with E.LockstepGames(rules, fen, 4, 0, width) as g:
+        with pytest.raises(TaflError):
+            g.mcts_configure(sims, 1.0, 1e-4, vl_width=17)

@@ -83,3 +83,25 @@ def test_gpu_mcts_matches_reference_mcts_py(orc, built_lib):
             assert int(got["best"][i]) == int(np.argmax(n))
             checked += 1
     assert checked == len(CASES)
+
+
+def test_oracle_virtual_loss_width_1_is_the_sequential_search(orc):
+    """The virtual-loss restatement (Mcts::run_from_root_vl) with one simulation in flight is mcts.py's search bit for
+    bit — visits, Q, final states and statistics over several moves with and without tree reuse; wider batches keep
+    the simulation count and differ only in where the visits go."""
+    import numpy as np
+    from alphazeroforhnefatafl_b200 import _abi as A
+    from parity_cases import sample_positions
+    for preset, width, sims in ((A.PRESET_BRANDUBH, 64, 150), (A.PRESET_COPENHAGEN, 128, 90), (A.PRESET_TABLUT, 128, 120)):
+        rules, fen = orc.preset_rules(preset), orc.preset_board(A.PRESET_BRANDUBH if preset == A.PRESET_KOCH else preset)
+        roots = sample_positions(orc, rules, fen, width, 20, seed=3, max_steps=200)
+        for reuse in (False, True):
+            a = orc.mcts_episode(rules, width, roots, sims, 3, reuse, n_threads=4)
+            b = orc.mcts_episode_vl(rules, width, roots, sims, 3, reuse, 1, n_threads=4)
+            assert np.array_equal(a["visits"], b["visits"]) and a["q"].tobytes() == b["q"].tobytes()
+            assert a["final"].tobytes() == b["final"].tobytes() and a["stats"].as_dict() == b["stats"].as_dict()
+            for W in (4, 16):
+                c = orc.mcts_episode_vl(rules, width, roots, sims, 3, reuse, W, n_threads=4)
+                assert c["stats"].sims == a["stats"].sims
+                live = roots["status"] == 0
+                assert (c["visits"][:, 0].sum(1)[live] == sims - 1).all()      # the first simulation expands the root
