@@ -364,7 +364,7 @@ def run_b200(args):
         raise RuntimeError("e2e replay through Game::do_play does not reproduce the recorded games")
     if int((err_host.numpy() != 0).sum()) != 0:
         raise RuntimeError("e2e replay: a recorded play was rejected")
-    rounds = max(2, int(math.ceil(args.min_region_s / cx.reduce(t_round))))
+    rounds = max(2, int(math.ceil(1.25 * args.min_region_s / cx.reduce(t_round))))
     e2e_time = 0.0
     for _ in range(rounds):
         g.set_states(steady)
@@ -560,7 +560,7 @@ def bench_mcts(cx, E, preset):
         sp.move()
     sp.flush()
     torch.cuda.synchronize()
-    moves = max(20, int(math.ceil(args.min_region_s / cx.reduce((time.perf_counter() - t0) / 3))))
+    moves = max(20, int(math.ceil(1.4 * args.min_region_s / cx.reduce((time.perf_counter() - t0) / 3))))
     s0 = g.mcts_stats().as_dict()
     l0 = g.launches
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -634,6 +634,14 @@ def bench_mcts(cx, E, preset):
                 res[key] = _mcts_variant(cx, E, SP, fresh, **kw)
             except Exception as ex:  # noqa: BLE001
                 res[key] = {"error": repr(ex)}
+        try:
+            res["virtual_loss"] = _mcts_virtual_loss(cx, fresh)
+        except Exception as ex:  # noqa: BLE001
+            res["virtual_loss"] = {"error": repr(ex)}
+        try:
+            res["selfplay_sweep_to_terminal"] = _sweep_to_terminal(cx, E, SP, rules, fen)
+        except Exception as ex:  # noqa: BLE001
+            res["selfplay_sweep_to_terminal"] = {"error": repr(ex)}
     if cx.rank == 0 and cx.world == 1 and not args.no_cpu_baseline:
         res["cpu_baseline"] = cpu_mcts_rate(oracle_handle(), args.cpu_seconds, args.seed, args.mcts_sims, preset)
     return res
@@ -706,6 +714,70 @@ def _mcts_variant(cx, E, SP, fresh, **kw):
         return {"value": sims / (ms * 1e-3), "unit": "sims/s (this rank)", "ms_per_move": ms / moves, "moves_timed": moves,
                 "nodes_created_per_sim": (s1["nodes"] - s0["nodes"]) / max(1, sims), "mean_depth": (s1["depth_sum"] - s0["depth_sum"]) / max(1, sims),
                 "gpu_launches": int(g.launches - l0)}
+    finally:
+        g.close()
+
+
+def _mcts_virtual_loss(cx, fresh):
+    """sims/s of the fused stub search against the virtual-loss width W (north star: PUCT with virtual loss; W = 1 is
+    mcts.py's sequential search, W > 1 the batched schedule of oracle/mcts_oracle.hpp::run_from_root_vl), this rank"""
+    torch = cx.torch
+    out = {"unit": "sims/s (this rank)", "trees": cx.args.mcts_games, "sims_per_move": cx.args.mcts_sims, "by_width": {}}
+    for W in (1, 2, 4, 8, 16):
+        g = fresh()
+        try:
+            g.mcts_configure(cx.args.mcts_sims, 1.0, 1e-4, vl_width=W)
+            st = torch.cuda.ExternalStream(g.stream, device=cx.local)
+            g.mcts_search()
+            s0 = g.mcts_stats().as_dict()["sims"]
+            with torch.cuda.stream(st):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(st)
+                for _ in range(8):
+                    g.mcts_search(sync=False)
+                b.record(st)
+                torch.cuda.synchronize()
+            out["by_width"][str(W)] = (g.mcts_stats().as_dict()["sims"] - s0) / (a.elapsed_time(b) * 1e-3)
+        finally:
+            g.close()
+    return out
+
+
+def _sweep_to_terminal(cx, E, SP, rules, fen):
+    """configs[4] evidence that the sweep runs episodes to their end: the same self-play loop started from a steady-state
+    MIXTURE of game stages (300 random plies with auto-restart), so games finish, restart (episode + 1) and get their
+    outcome back-filled inside a short run; records go through the same gather."""
+    import numpy as np
+    args, torch = cx.args, cx.torch
+    n = args.mcts_games
+    g = E.LockstepGames(rules, fen, n, cx.local, 128)
+    try:
+        g.set_game_id_base(cx.rank * n)
+        g.step_random(args.seed + 7, 300, auto_reset=True)
+        sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, overlap=True, restart_finished=True)
+        replay = SP.DeviceReplayBuffer(n * cx.world * 48, cx.local) if cx.rank == 0 else None
+        moves = 40
+        cx.barrier()
+        t0 = time.perf_counter()
+        for _ in range(moves):
+            out = sp.move()
+            if out is not None and replay is not None:
+                replay.extend(out, sp.side)
+        out = sp.flush()
+        if out is not None and replay is not None:
+            replay.extend(out, sp.side)
+        cx.barrier()
+        el = time.perf_counter() - t0
+        res = {"moves": moves, "seconds": cx.reduce(el), "trees_per_gpu": n}
+        if replay is not None:
+            t0 = time.perf_counter()
+            recs = replay.as_array()
+            z = SP.backfill_outcomes(recs)
+            ended = (recs["h"]["status"] & 0x80) != 0
+            res.update({"rows": int(len(recs)), "episodes_finished": int(ended.sum()), "rows_with_outcome": int((~np.isnan(z)).sum()),
+                        "max_episode_index": int(recs["h"]["episode"].max()) if len(recs) else 0, "backfill_s": time.perf_counter() - t0})
+        sp.close()
+        return res
     finally:
         g.close()
 
