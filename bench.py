@@ -555,12 +555,16 @@ def bench_mcts(cx, E, preset):
     sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, overlap=True, restart_finished=True)
     replay = SP.DeviceReplayBuffer(n * cx.world * 64, cx.local) if cx.rank == 0 else None   # HBM-resident rolling window
     stream = sp.stream
-    t0 = time.perf_counter()
     for _ in range(3):                                     # warm-up moves (NCCL channels, allocator blocks)
         sp.move()
     sp.flush()
     torch.cuda.synchronize()
-    moves = max(20, int(math.ceil(1.4 * args.min_region_s / cx.reduce((time.perf_counter() - t0) / 3))))
+    t0 = time.perf_counter()
+    for _ in range(4):                                     # calibration: how many moves make min_region_s
+        sp.move()
+    sp.flush()
+    torch.cuda.synchronize()
+    moves = max(20, int(math.ceil(1.25 * args.min_region_s / cx.reduce((time.perf_counter() - t0) / 4))))
     s0 = g.mcts_stats().as_dict()
     l0 = g.launches
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -754,7 +758,9 @@ def _sweep_to_terminal(cx, E, SP, rules, fen):
     try:
         g.set_game_id_base(cx.rank * n)
         g.step_random(args.seed + 7, 300, auto_reset=True)
-        sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, overlap=True, restart_finished=True)
+        # endgame positions have few pieces and long rays: more edges per node than the default pool (160 per node) assumes
+        sp = SP.SelfPlay(g, num_sims=args.mcts_sims, cpuct=1.0, overlap=True, restart_finished=True,
+                         edge_capacity=(args.mcts_sims + 1) * 320)
         replay = SP.DeviceReplayBuffer(n * cx.world * 48, cx.local) if cx.rank == 0 else None
         moves = 40
         cx.barrier()
