@@ -182,6 +182,27 @@ assert STATE_DTYPE.itemsize == 64 and PLAY_DTYPE.itemsize == 4 and EFFECTS_DTYPE
 assert ENCLOSURE_DTYPE.itemsize == 56 and ENCL_QUERY_DTYPE.itemsize == 16
 
 
+# large boards (BitfieldBoardState<U256> / <U512>): tafl_state_w, tafl_play_effects_w, tafl_enclosure_w
+W_MAX_PLAYS = 2048
+STATE_W_DTYPE = np.dtype([
+    ("att", "<u8", (8,)), ("def", "<u8", (8,)), ("recent", "<u4", (4,)),
+    ("att_reps", "u1"), ("def_reps", "u1"), ("flags", "u1"), ("status", "u1"),
+    ("turn", "<u4"), ("plays_since_capture", "<u4"), ("ring_head", "u1"), ("side_len", "u1"), ("_pad", "u1", (2,)),
+])
+EFFECTS_W_DTYPE = np.dtype([("captures", "<u8", (8,)), ("status", "u1"), ("err", "u1"), ("n_captures", "u1"), ("_pad", "u1", (5,))])
+ENCLOSURE_W_DTYPE = np.dtype([("occupied", "<u8", (8,)), ("unoccupied", "<u8", (8,)), ("boundary", "<u8", (8,)),
+                              ("found", "u1"), ("_pad", "u1", (7,))])
+assert STATE_W_DTYPE.itemsize == 160 and EFFECTS_W_DTYPE.itemsize == 72 and ENCLOSURE_W_DTYPE.itemsize == 200
+
+
+def is_wide(width):
+    return width in (256, 512)
+
+
+def state_dtype(width):
+    return STATE_W_DTYPE if is_wide(width) else STATE_DTYPE
+
+
 def ptr(arr, ctype=None):
     """ctypes pointer to a contiguous numpy array's buffer."""
     assert arr.flags["C_CONTIGUOUS"]
@@ -195,11 +216,15 @@ def width_for(side_len):
         return 64
     if side_len <= 11:
         return 128
-    raise ValueError("boards larger than 11x11 (U256/U512 bitfields) are out of scope")
+    if side_len <= 15:
+        return 256
+    if side_len <= 21:
+        return 512
+    raise ValueError("no bitfield holds a board larger than 21x21")
 
 
 def stride_for(width):
-    return 7 if width == 64 else 11
+    return {64: 7, 128: 11, 256: 15, 512: 21}[width]   # bitfield.rs:178-181
 
 
 def tile_bit(width, row, col):
@@ -207,8 +232,10 @@ def tile_bit(width, row, col):
 
 
 def bb_to_tiles(width, words):
-    """tile bitboard (two u64 words) -> sorted list of (row, col)."""
-    v = int(words[0]) | (int(words[1]) << 64)
+    """tile bitboard (two u64 words; eight for the wide widths) -> sorted list of (row, col)."""
+    v = 0
+    for k, x in enumerate(words):
+        v |= int(x) << (64 * k)
     s = stride_for(width)
     out = []
     i = 0

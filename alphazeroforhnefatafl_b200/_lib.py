@@ -133,6 +133,22 @@ def lib():
         "tafl_mcts_search_builtin": (C.c_int, [vp, C.c_int, C.c_uint64]),
         "tafl_leaf_batch_host": (C.c_int, [vp, vp, vp, vp, vp]),
         "tafl_leaf_eval_host": (C.c_int, [vp, vp, vp]),
+        "tafl_w_state_from_fen": (C.c_int, [C.c_char_p, C.c_int, C.c_int, vp]),
+        "tafl_w_state_to_fen": (C.c_int, [vp, C.c_int, C.c_char_p, C.c_size_t]),
+        "tafl_w_board_move_piece": (C.c_int, [vp, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8, C.c_uint8]),
+        "tafl_wide_create": (C.c_int, [C.POINTER(A.Rules), C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
+        "tafl_wide_destroy": (C.c_int, [vp]),
+        "tafl_wide_last_error": (C.c_char_p, [vp]),
+        "tafl_w_validate_plays": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+        "tafl_w_do_plays": (C.c_int, [vp, vp, vp, C.c_uint32, vp, vp]),
+        "tafl_w_legal_plays_of": (C.c_int, [vp, vp, C.c_uint32, vp, vp]),
+        "tafl_w_piece_plays": (C.c_int, [vp, vp, vp, C.c_uint32, vp, vp]),
+        "tafl_w_get_captures": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+        "tafl_w_detect_shieldwall": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+        "tafl_w_find_enclosure": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+        "tafl_w_enclosure_secure": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
+        "tafl_w_detect_exit_fort": (C.c_int, [vp, vp, C.c_uint32, vp]),
+        "tafl_w_side_can_play": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
         "tafl_pack_records": (C.c_int, [vp, vp]),
         "tafl_pack_records_compact": (C.c_int, [vp, vp, vp, vp]),
         "tafl_reset_finished": (C.c_int, [vp, C.POINTER(C.c_uint32)]),

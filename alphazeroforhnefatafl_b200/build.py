@@ -11,9 +11,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 LIB = os.path.join(HERE, "libtafl_b200.so")
-SOURCES = ["tafl_engine.cu", "tafl_mcts.cu", "tafl_comm.cu", "tafl_host.cpp"]
+SOURCES = ["tafl_engine.cu", "tafl_mcts.cu", "tafl_comm.cu", "tafl_wide.cu", "tafl_host.cpp"]
 HEADERS = ["tafl_bb.cuh", "tafl_core.cuh", "tafl_select.cuh", "tafl_ctx.hpp", "tafl_engine.hpp",
-           "tafl_warp.cuh", "tafl_mcts.cuh"]
+           "tafl_warp.cuh", "tafl_mcts.cuh", "tafl_wide.cuh"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-fmad=false",                      # MCTS PUCT must round like the f64 oracle (no FMA contraction)

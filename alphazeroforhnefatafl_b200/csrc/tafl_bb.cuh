@@ -165,8 +165,154 @@ TAFL_HD BB128 operator~(BB128 a) { return BB128{~a.lo, ~a.hi}; }
 TAFL_HD bool operator==(BB128 a, BB128 b) { return a.lo == b.lo && a.hi == b.hi; }
 TAFL_HD bool operator!=(BB128 a, BB128 b) { return !(a == b); }
 
+// ---------------------------------------------------------------------------------------------
+// BitfieldBoardState<U256> (row stride 15) and <U512> (row stride 21), bitfield.rs:180-181: boards up to
+// 15x15 / 21x21 as NW 64-bit words.  Used by the by-value rules kernels (tafl_wide.cu); the word loops have
+// compile-time bounds and unroll.  The same operations as BB64 / BB128, nothing board-size specific.
+// ---------------------------------------------------------------------------------------------
+template <int NW, int STRIDE_>
+struct BBW {
+    uint64_t w[NW];
+    static constexpr int BITS = 64 * NW;
+    static constexpr int STRIDE = STRIDE_;
+    static constexpr int WORDS = 2 * NW;
+    TAFL_HD static BBW zero() {
+        BBW r;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) r.w[i] = 0;
+        return r;
+    }
+    TAFL_HD static BBW bit(int i) {
+        BBW r = zero();
+#pragma unroll
+        for (int k = 0; k < NW; ++k)
+            if (i >= 64 * k && i < 64 * (k + 1)) r.w[k] = 1ull << (i - 64 * k);
+        return r;
+    }
+    TAFL_HD uint32_t word(int i) const { return (uint32_t)(w[i >> 1] >> (32 * (i & 1))); }
+    TAFL_HD bool any() const {
+        uint64_t a = 0;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) a |= w[i];
+        return a != 0;
+    }
+    TAFL_HD bool test(int i) const {
+        if (i < 0 || i >= BITS) return false;
+        uint64_t v = 0;
+#pragma unroll
+        for (int k = 0; k < NW; ++k)
+            if ((i >> 6) == k) v = w[k];
+        return ((v >> (i & 63)) & 1) != 0;
+    }
+    TAFL_HD int popc() const {
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) c += popc64(w[i]);
+        return c;
+    }
+    TAFL_HD int ctz() const {
+        int r = BITS;
+#pragma unroll
+        for (int i = NW - 1; i >= 0; --i)
+            if (w[i]) r = 64 * i + ctz64(w[i]);
+        return r;
+    }
+    TAFL_HD BBW shlv(int k) const {
+        if (k <= 0) return *this;
+        BBW r = zero();
+        if (k >= BITS) return r;
+        const int ws = k >> 6, bs = k & 63;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            uint64_t lo = 0, hi = 0;   // r.w[i] = w[i - ws] << bs | w[i - ws - 1] >> (64 - bs)
+#pragma unroll
+            for (int j = 0; j < NW; ++j) {
+                if (j == i - ws) lo = w[j];
+                if (j == i - ws - 1) hi = w[j];
+            }
+            r.w[i] = (lo << bs) | (bs ? (hi >> (64 - bs)) : 0ull);
+        }
+        return r;
+    }
+    TAFL_HD BBW shrv(int k) const {
+        if (k <= 0) return *this;
+        BBW r = zero();
+        if (k >= BITS) return r;
+        const int ws = k >> 6, bs = k & 63;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            uint64_t lo = 0, hi = 0;   // r.w[i] = w[i + ws] >> bs | w[i + ws + 1] << (64 - bs)
+#pragma unroll
+            for (int j = 0; j < NW; ++j) {
+                if (j == i + ws) lo = w[j];
+                if (j == i + ws + 1) hi = w[j];
+            }
+            r.w[i] = (lo >> bs) | (bs ? (hi << (64 - bs)) : 0ull);
+        }
+        return r;
+    }
+    template <int K> TAFL_HD BBW shl() const {
+        if (K == 0) return *this;
+        BBW r = zero();
+        if (K >= BITS) return r;
+        constexpr int ws = (K >> 6), bs = (K & 63);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            const uint64_t lo = (i - ws >= 0 && i - ws < NW) ? w[(i - ws >= 0 && i - ws < NW) ? i - ws : 0] : 0ull;
+            const uint64_t hi = (i - ws - 1 >= 0 && i - ws - 1 < NW) ? w[(i - ws - 1 >= 0 && i - ws - 1 < NW) ? i - ws - 1 : 0] : 0ull;
+            r.w[i] = (lo << bs) | (bs ? (hi >> ((64 - bs) & 63)) : 0ull);
+        }
+        return r;
+    }
+    template <int K> TAFL_HD BBW shr() const {
+        if (K == 0) return *this;
+        BBW r = zero();
+        if (K >= BITS) return r;
+        constexpr int ws = (K >> 6), bs = (K & 63);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            const uint64_t lo = (i + ws < NW) ? w[(i + ws < NW) ? i + ws : 0] : 0ull;
+            const uint64_t hi = (i + ws + 1 < NW) ? w[(i + ws + 1 < NW) ? i + ws + 1 : 0] : 0ull;
+            r.w[i] = (lo >> bs) | (bs ? (hi << ((64 - bs) & 63)) : 0ull);
+        }
+        return r;
+    }
+    TAFL_HD uint32_t extract32(int k) const { return (uint32_t)shrv(k).w[0]; }
+};
+template <int NW, int S> TAFL_HD BBW<NW, S> operator&(BBW<NW, S> a, BBW<NW, S> b) {
+#pragma unroll
+    for (int i = 0; i < NW; ++i) a.w[i] &= b.w[i];
+    return a;
+}
+template <int NW, int S> TAFL_HD BBW<NW, S> operator|(BBW<NW, S> a, BBW<NW, S> b) {
+#pragma unroll
+    for (int i = 0; i < NW; ++i) a.w[i] |= b.w[i];
+    return a;
+}
+template <int NW, int S> TAFL_HD BBW<NW, S> operator^(BBW<NW, S> a, BBW<NW, S> b) {
+#pragma unroll
+    for (int i = 0; i < NW; ++i) a.w[i] ^= b.w[i];
+    return a;
+}
+template <int NW, int S> TAFL_HD BBW<NW, S> operator~(BBW<NW, S> a) {
+#pragma unroll
+    for (int i = 0; i < NW; ++i) a.w[i] = ~a.w[i];
+    return a;
+}
+template <int NW, int S> TAFL_HD bool operator==(BBW<NW, S> a, BBW<NW, S> b) {
+    uint64_t d = 0;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) d |= a.w[i] ^ b.w[i];
+    return d == 0;
+}
+template <int NW, int S> TAFL_HD bool operator!=(BBW<NW, S> a, BBW<NW, S> b) { return !(a == b); }
+using BB256 = BBW<4, 15>;   // bitfield.rs:180
+using BB512 = BBW<8, 21>;   // bitfield.rs:181
+
 template <int WBITS> struct BBSel;
 template <> struct BBSel<64> { using type = BB64; };
 template <> struct BBSel<128> { using type = BB128; };
+template <> struct BBSel<256> { using type = BB256; };
+template <> struct BBSel<512> { using type = BB512; };
 
 }  // namespace tafl

@@ -199,6 +199,7 @@ TAFL_HD BB king_bit(const Ctx<BB, SP>& cx, int kr, int kc) {
 
 template <class BB> struct Nib;
 template <> struct Nib<BB64> {
+    using State = tafl_state;
     TAFL_HD static void load(const tafl_state& s, Pos<BB64>& p) {
         p.att = BB64{s.att[0] & 0x0FFFFFFFFFFFFFFFull};
         p.def = BB64{s.def[0] & 0x0FFFFFFFFFFFFFFFull};
@@ -216,6 +217,7 @@ template <> struct Nib<BB64> {
     TAFL_HD static bool raw_def(const tafl_state& s, int i) { return i < 64 && ((s.def[0] >> i) & 1); }
 };
 template <> struct Nib<BB128> {
+    using State = tafl_state;
     TAFL_HD static void load(const tafl_state& s, Pos<BB128>& p) {
         p.att = BB128{s.att[0], s.att[1] & 0x0FFFFFFFFFFFFFFFull};
         p.def = BB128{s.def[0], s.def[1] & 0x0FFFFFFFFFFFFFFFull};
@@ -236,15 +238,37 @@ template <> struct Nib<BB128> {
     }
 };
 
-template <class BB, int SP>
-TAFL_HD Pos<BB> load_pos(const Ctx<BB, SP>& cx, const tafl_state& s) {
+// BitfieldBoardState<U256> / <U512> in tafl_state_w: NW words per side, king nibbles in the top 4 bits of the last one
+template <int NW, int S> struct Nib<BBW<NW, S>> {
+    using State = tafl_state_w;
+    using BB = BBW<NW, S>;
+    TAFL_HD static void load(const tafl_state_w& s, Pos<BB>& p) {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) { p.att.w[i] = s.att[i]; p.def.w[i] = s.def[i]; }
+        p.att.w[NW - 1] &= 0x0FFFFFFFFFFFFFFFull;
+        p.def.w[NW - 1] &= 0x0FFFFFFFFFFFFFFFull;
+        p.kr = (int)(s.def[NW - 1] >> 60);
+        p.kc = (int)(s.att[NW - 1] >> 60);
+    }
+    TAFL_HD static void store(const Pos<BB>& p, tafl_state_w& s) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s.att[i] = i < NW ? p.att.w[i < NW ? i : 0] : 0ull; s.def[i] = i < NW ? p.def.w[i < NW ? i : 0] : 0ull; }
+        s.att[NW - 1] |= (uint64_t)p.kc << 60;
+        s.def[NW - 1] |= (uint64_t)p.kr << 60;
+    }
+    TAFL_HD static bool raw_att(const tafl_state_w& s, int i) { return i >= 0 && i < BB::BITS && ((s.att[i >> 6] >> (i & 63)) & 1); }
+    TAFL_HD static bool raw_def(const tafl_state_w& s, int i) { return i >= 0 && i < BB::BITS && ((s.def[i >> 6] >> (i & 63)) & 1); }
+};
+
+template <class BB, int SP, class ST>
+TAFL_HD Pos<BB> load_pos(const Ctx<BB, SP>& cx, const ST& s) {
     Pos<BB> p;
     Nib<BB>::load(s, p);
     p.kbit = king_bit(cx, p.kr, p.kc);
     return p;
 }
-template <class BB>
-TAFL_HD void store_pos(const Pos<BB>& p, tafl_state& s) { Nib<BB>::store(p, s); }
+template <class BB, class ST>
+TAFL_HD void store_pos(const Pos<BB>& p, ST& s) { Nib<BB>::store(p, s); }
 
 // one-tile steps of a tile set, results clipped to the board
 template <class BB, int SP> TAFL_HD BB step_up(const Ctx<BB, SP>&, BB x) { return x.template shr<BB::STRIDE>(); }              // row-1
@@ -302,6 +326,13 @@ TAFL_HD uint32_t gather_col(BB128 t) {
     const uint32_t lo = (uint32_t)(((t.lo & M6) * K) >> 58);            // rows 0..5: bits 0, 11, .., 55
     const uint32_t hi = (uint32_t)((((t.hi >> 2) & M5) * K) >> 58);     // rows 6..10: bits 66, 77, .., 110
     return lo | (hi << 6);
+}
+template <int NW, int S>
+TAFL_HD uint32_t gather_col(BBW<NW, S> t) {   // wide boards: the rules kernels are not the hot path, a plain bit loop
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 21 && i * S < 64 * NW; ++i) r |= (uint32_t)((t.w[(i * S) >> 6] >> ((i * S) & 63)) & 1ull) << i;
+    return r;
 }
 template <class BB, int SP>
 TAFL_HD uint32_t extract_col(const Ctx<BB, SP>& cx, BB x, int col) {
@@ -402,8 +433,8 @@ TAFL_HD int gen_moves_side(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side
     }
     return n;
 }
-template <class BB, int SP>
-TAFL_HD int gen_moves(const Ctx<BB, SP>& cx, const tafl_state& st, tafl_move* out, int cap) {
+template <class BB, int SP, class ST>
+TAFL_HD int gen_moves(const Ctx<BB, SP>& cx, const ST& st, tafl_move* out, int cap) {
     if (st.status != TAFL_STATUS_ONGOING) return 0;  // logic.rs:165-167
     Pos<BB> p = load_pos(cx, st);
     return gen_moves_side(cx, p, (st.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, out, cap);
@@ -457,7 +488,7 @@ TAFL_COLD bool shieldwall_walk(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
         const int dir = dd == 0 ? -1 : 1;
         wall = BB::zero();
         int cnt = 0, r = to_r, c = to_c;
-        for (int it = 0; it < 12; ++it) {
+        for (int it = 0; it <= N; ++it) {   // at most N - 1 tiles along an edge
             if (horizontal) c += dir; else r += dir;
             if (r < 0 || c < 0 || r >= N || c >= N) break;  // ran off the board: None
             BB tb = BB::bit(idx_of<BB>(r, c));
@@ -652,7 +683,7 @@ TAFL_HD Encl<BB> find_enclosure(const Ctx<BB, SP>& cx, const Pos<BB>& p, int r, 
     const BB stop = (abort_on_edge ? cx.edge : BB::zero()) | (abort_on_corner ? cx.corners : BB::zero());
     BB reg = BB::bit(idx_of<BB>(r, c)) & fillable;
     if (!reg.any()) return e;
-    for (int it = 0; it < 128; ++it) {
+    for (int it = 0; it < BB::BITS; ++it) {
         if ((reg & stop).any()) return e;
         BB grown = reg | (dilate4(cx, reg) & fillable);
         if (grown == reg) break;
@@ -680,7 +711,7 @@ TAFL_HD bool enclosure_win_possible(const Ctx<BB, SP>& cx, const Pos<BB>& p, boo
     const BB stop = (abort_on_edge ? cx.edge : BB::zero()) | cx.corners;
     BB reg = p.def;
     bool escaped = false;   // single exit: the lanes of a warp leave the loop together
-    for (int it = 0; it < 128; ++it) {
+    for (int it = 0; it < BB::BITS; ++it) {
         escaped = (reg & stop).any();
         if (escaped) break;
         const BB grown = reg | (dilate4(cx, reg) & fillable);
@@ -752,7 +783,8 @@ TAFL_HD uint32_t pack_rec(int from_r, int from_c, int horizontal, int disp, int 
                   (horizontal ? TAFL_REC_HORIZONTAL : 0u);
     return (uint32_t)(from_r & 0xFF) | ((uint32_t)(from_c & 0xFF) << 8) | ((uint32_t)(disp & 0xFF) << 16) | (fl << 24);
 }
-TAFL_HD void track_play(tafl_state& s, uint32_t rec, int def_side, bool captures) {
+template <class ST>
+TAFL_HD void track_play(ST& s, uint32_t rec, int def_side, bool captures) {
     const uint32_t head = s.ring_head & 3u;
     uint32_t first = s.recent[0];
     first = head == 1 ? s.recent[1] : first;
@@ -779,8 +811,8 @@ TAFL_HD void track_play(tafl_state& s, uint32_t rec, int def_side, bool captures
 // ---------------------------------------------------------------------------------------------
 // get_game_outcome (logic.rs:702-771) — returns the packed status (0 = still Ongoing)
 // ---------------------------------------------------------------------------------------------
-template <class BB, int SP>
-TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const tafl_state& s, int mover_def, int piece_kind,
+template <class BB, int SP, class ST>
+TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const ST& s, int mover_def, int piece_kind,
                              int to_r, int to_c, BB caps) {
     // Single exit on purpose: the side-specific tests diverge inside a warp (mixed sides to move,
     // data-dependent fill lengths) and the common tail — side_can_play — must be issued once.
@@ -835,8 +867,8 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const tafl
 // do_valid_play (logic.rs:782-820).  (from, axis, disp) is the Play; the caller guarantees a
 // piece on `from` and an in-bounds destination.  Returns the captured tiles.
 // ---------------------------------------------------------------------------------------------
-template <class BB, int SP>
-TAFL_HD BB do_valid_play(const Ctx<BB, SP>& cx, tafl_state& s, int from_r, int from_c, int horizontal, int disp) {
+template <class BB, int SP, class ST>
+TAFL_HD BB do_valid_play(const Ctx<BB, SP>& cx, ST& s, int from_r, int from_c, int horizontal, int disp) {
     Pos<BB> p = load_pos(cx, s);
     const int mover_def = (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
     const int to_r = horizontal ? from_r : from_r + disp, to_c = horizontal ? from_c + disp : from_c;
@@ -871,8 +903,8 @@ TAFL_HD BB do_valid_move(const Ctx<BB, SP>& cx, tafl_state& s, tafl_move m) {
 }
 
 // validate_play_for_side (logic.rs:159-214)
-template <class BB, int SP>
-TAFL_HD int validate_play(const Ctx<BB, SP>& cx, const tafl_state& s, const tafl_play& pl, int side_def) {
+template <class BB, int SP, class ST>
+TAFL_HD int validate_play(const Ctx<BB, SP>& cx, const ST& s, const tafl_play& pl, int side_def) {
     if (s.status != TAFL_STATUS_ONGOING) return TAFL_GAME_OVER;
     const int N = cx.n();
     const int fr = pl.from_row, fc = pl.from_col;

@@ -540,3 +540,120 @@ class LockstepGames:
         out = np.zeros(len(states), np.uint8)
         self._ck(lib().tafl_side_can_play(self._h, A.ptr(states), A.ptr(sides), len(states), A.ptr(out)))
         return out
+
+
+class WideLogic:
+    """``GameLogic`` over the large bitfields — ``BitfieldBoardState<U256>`` (up to 15x15) and ``<U512>`` (up to
+    21x21), game/board/state.rs:337-340 — by value: every method takes a batch of ``_abi.STATE_W_DTYPE`` states and
+    runs one CUDA kernel over it (``tafl_w_*``, include/tafl.h "Large boards").  Move lists are ``PLAY_DTYPE`` arrays
+    (a tile index of a 21x21 board does not fit the compact ``tafl_move``)."""
+
+    def __init__(self, rules, side_len, width=0, device=0):
+        self._h = C.c_void_p()
+        self.rules, self.side_len = rules, side_len
+        self.width = width or A.width_for(side_len)
+        rc = lib().tafl_wide_create(C.byref(rules), side_len, self.width, device, C.byref(self._h))
+        if rc != 0:
+            raise TaflError(rc, lib().tafl_wide_last_error(None).decode())
+
+    def close(self):
+        if self._h:
+            lib().tafl_wide_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise TaflError(rc, lib().tafl_wide_last_error(self._h).decode())
+
+    @staticmethod
+    def state_from_fen(fen, width, side=A.ATTACKER):
+        st = np.zeros(1, A.STATE_W_DTYPE)
+        _check(lib().tafl_w_state_from_fen(fen.encode(), width, side, A.ptr(st)))
+        return st
+
+    @staticmethod
+    def state_to_fen(st, width):
+        buf = C.create_string_buffer(1024)
+        _check(lib().tafl_w_state_to_fen(A.ptr(np.ascontiguousarray(st, A.STATE_W_DTYPE)), width, buf, 1024))
+        return buf.value.decode()
+
+    @staticmethod
+    def move_piece(st, width, frm, to):
+        _check(lib().tafl_w_board_move_piece(A.ptr(st), width, frm[0], frm[1], to[0], to[1]))
+
+    def _st(self, states):
+        return np.ascontiguousarray(states, A.STATE_W_DTYPE)
+
+    def validate_plays(self, states, plays):
+        states, plays = self._st(states), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_w_validate_plays(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(out)))
+        return out
+
+    def do_plays(self, states, plays):
+        states, plays = self._st(states), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        out, fx = np.zeros(len(states), A.STATE_W_DTYPE), np.zeros(len(states), A.EFFECTS_W_DTYPE)
+        self._ck(lib().tafl_w_do_plays(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(out), A.ptr(fx)))
+        return out, fx
+
+    def legal_plays_of(self, states):
+        states = self._st(states)
+        plays = np.zeros((len(states), A.W_MAX_PLAYS), A.PLAY_DTYPE)
+        counts = np.zeros(len(states), np.uint32)
+        self._ck(lib().tafl_w_legal_plays_of(self._h, A.ptr(states), len(states), A.ptr(plays), A.ptr(counts)))
+        return plays, counts
+
+    def piece_plays(self, states, tiles_rc):
+        states, tiles_rc = self._st(states), np.ascontiguousarray(tiles_rc, np.uint8)
+        plays = np.zeros((len(states), 64), A.PLAY_DTYPE)
+        counts = np.zeros(len(states), np.int32)
+        self._ck(lib().tafl_w_piece_plays(self._h, A.ptr(states), A.ptr(tiles_rc), len(states), A.ptr(plays), A.ptr(counts)))
+        return plays, counts
+
+    def get_captures(self, states, plays):
+        states, plays = self._st(states), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        fx = np.zeros(len(states), A.EFFECTS_W_DTYPE)
+        self._ck(lib().tafl_w_get_captures(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(fx)))
+        return fx
+
+    def detect_shieldwall(self, states, plays):
+        states, plays = self._st(states), np.ascontiguousarray(plays, A.PLAY_DTYPE)
+        fx = np.zeros(len(states), A.EFFECTS_W_DTYPE)
+        self._ck(lib().tafl_w_detect_shieldwall(self._h, A.ptr(states), A.ptr(plays), len(states), A.ptr(fx)))
+        return fx
+
+    def find_enclosure(self, states, queries):
+        states, queries = self._st(states), np.ascontiguousarray(queries, A.ENCL_QUERY_DTYPE)
+        out = np.zeros(len(states), A.ENCLOSURE_W_DTYPE)
+        self._ck(lib().tafl_w_find_enclosure(self._h, A.ptr(states), A.ptr(queries), len(states), A.ptr(out)))
+        return out
+
+    def enclosure_secure(self, states, queries):
+        states, queries = self._st(states), np.ascontiguousarray(queries, A.ENCL_QUERY_DTYPE)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_w_enclosure_secure(self._h, A.ptr(states), A.ptr(queries), len(states), A.ptr(out)))
+        return out
+
+    def detect_exit_fort(self, states):
+        states = self._st(states)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_w_detect_exit_fort(self._h, A.ptr(states), len(states), A.ptr(out)))
+        return out
+
+    def side_can_play(self, states, sides):
+        states, sides = self._st(states), np.ascontiguousarray(sides, np.uint8)
+        out = np.zeros(len(states), np.uint8)
+        self._ck(lib().tafl_w_side_can_play(self._h, A.ptr(states), A.ptr(sides), len(states), A.ptr(out)))
+        return out

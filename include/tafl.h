@@ -631,6 +631,53 @@ int tafl_gather_records_on(tafl_engine* e, void* comm, int n_ranks, int rank, in
                            const void* d_send, uint32_t n_local, void* d_recv,
                            uint64_t recv_capacity_rows, uint32_t* h_counts, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Large boards: BitfieldBoardState<U256> (row stride 15, up to 15x15) and <U512> (row stride 21,
+ * up to 21x21) — LargeBasicBoardState / HugeBasicBoardState, game/board/state.rs:337-340,
+ * game/bitfield.rs:180-181.  The reference instantiates its width-generic logic tests on them
+ * (game/game/logic.rs:1015-1021,1081-1087); no preset or benchmark configuration uses them, so
+ * this is the by-value GameLogic surface (logic.rs:61-880) only: no resident games, no MCTS.
+ * Same bit layout as the reference: tile (r, c) = bit r * stride + c, king row / column in the top
+ * four bits of the defender / attacker word.  Width 256 uses words 0..3 of each array, 512 all 8.
+ * Tile indices no longer fit a tafl_move, so move lists are lists of tafl_play.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct {
+    uint64_t att[8], def[8];
+    uint32_t recent[4];
+    uint8_t  att_reps, def_reps, flags, status;
+    uint32_t turn, plays_since_capture;
+    uint8_t  ring_head, side_len, _pad[2];
+} tafl_state_w;                 /* 160 bytes */
+typedef struct { uint64_t captures[8]; uint8_t status, err, n_captures, _pad[5]; } tafl_play_effects_w;   /* 72 bytes */
+typedef struct { uint64_t occupied[8], unoccupied[8], boundary[8]; uint8_t found, _pad[7]; } tafl_enclosure_w;   /* 200 bytes */
+#define TAFL_W_MAX_PLAYS 2048   /* capacity of one position's play list: 4 (N^2 - 1) <= 1760 for N = 21 */
+
+/* host helpers on wide states (width_bits 256 | 512): GameState::new(fen, side), Display, move_piece */
+int tafl_w_state_from_fen(const char* fen, int width_bits, int side_to_play, tafl_state_w* out);
+int tafl_w_state_to_fen(const tafl_state_w* st, int width_bits, char* buf, size_t buf_len);
+int tafl_w_board_move_piece(tafl_state_w* st, int width_bits, uint8_t from_row, uint8_t from_col,
+                            uint8_t to_row, uint8_t to_col);
+
+/* GameLogic::new(rules, side_len) for a wide bitfield (logic.rs:70-72); device = CUDA ordinal */
+typedef struct tafl_wide tafl_wide;
+int tafl_wide_create(const tafl_rules* rules, int side_len, int width_bits, int device, tafl_wide** out);
+int tafl_wide_destroy(tafl_wide* w);
+const char* tafl_wide_last_error(const tafl_wide* w);
+/* by-value batch calls, HOST arrays in and out, one CUDA kernel each (the wide twins of the calls above) */
+int tafl_w_validate_plays(tafl_wide* w, const tafl_state_w* h_states, const tafl_play* h_plays, uint32_t n, uint8_t* h_err);
+int tafl_w_do_plays(tafl_wide* w, const tafl_state_w* h_states, const tafl_play* h_plays, uint32_t n,
+                    tafl_state_w* h_out_states, tafl_play_effects_w* h_out_fx);
+int tafl_w_legal_plays_of(tafl_wide* w, const tafl_state_w* h_states, uint32_t n,
+                          tafl_play* h_plays /* [n][TAFL_W_MAX_PLAYS] */, uint32_t* h_counts);
+int tafl_w_piece_plays(tafl_wide* w, const tafl_state_w* h_states, const uint8_t* h_tiles_rc, uint32_t n,
+                       tafl_play* h_plays /* [n][64] */, int32_t* h_counts /* -1 == Err(NoPiece) */);
+int tafl_w_get_captures(tafl_wide* w, const tafl_state_w* h_states, const tafl_play* h_plays, uint32_t n, tafl_play_effects_w* h_out);
+int tafl_w_detect_shieldwall(tafl_wide* w, const tafl_state_w* h_states, const tafl_play* h_plays, uint32_t n, tafl_play_effects_w* h_out);
+int tafl_w_find_enclosure(tafl_wide* w, const tafl_state_w* h_states, const tafl_enclosure_query* h_q, uint32_t n, tafl_enclosure_w* h_out);
+int tafl_w_enclosure_secure(tafl_wide* w, const tafl_state_w* h_states, const tafl_enclosure_query* h_q, uint32_t n, uint8_t* h_out);
+int tafl_w_detect_exit_fort(tafl_wide* w, const tafl_state_w* h_states, uint32_t n, uint8_t* h_out);
+int tafl_w_side_can_play(tafl_wide* w, const tafl_state_w* h_states, const uint8_t* h_sides, uint32_t n, uint8_t* h_out);
+
 #ifdef __cplusplus
 }
 #endif

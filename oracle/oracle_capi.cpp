@@ -578,4 +578,210 @@ int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, ui
 
 int orc_hw_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
+// ---- large boards (U256 / U512): the by-value calls over tafl_state_w, mirrors of include/tafl.h's tafl_w_* ----------
+}  // extern "C"
+namespace {
+template <class F>
+int dispatch_w(int width, F&& f) {
+    if (width == 256) return f(U256{});
+    if (width == 512) return f(U512{});
+    return TAFL_ERR_INVALID_ARG;
+}
+template <class W>
+void bb_set_w(uint64_t out[8], const std::set<Tile>& tiles) {
+    for (int i = 0; i < 8; ++i) out[i] = 0;
+    for (auto& t : tiles) {
+        unsigned b = (unsigned)t.row * Board<W>::RW + t.col;
+        out[b >> 6] |= 1ull << (b & 63);
+    }
+}
+}  // namespace
+extern "C" {
+int orc_w_state_from_fen(const char* fen, int width, int side, tafl_state_w* out) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        GameState<W> s;
+        int rc = GameState<W>::create(fen, side ? Side::Defender : Side::Attacker, &s);
+        if (rc) return rc;
+        pack_state_w(s, out);
+        return 0;
+    });
+}
+int orc_w_move_piece(tafl_state_w* st, int width, int fr, int fc, int tr, int tc) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        GameState<W> s;
+        unpack_state_w(*st, &s);
+        Tile t{(uint8_t)fr, (uint8_t)fc};
+        if (!s.board.get_piece(t)) return (int)TAFL_ERR_NO_PIECE;
+        s.board.move_piece(t, Tile{(uint8_t)tr, (uint8_t)tc});
+        pack_state_w(s, st);
+        return 0;
+    });
+}
+int orc_w_validate_plays(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, uint8_t* out_err) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            out_err[i] = (uint8_t)logic.validate_play(play_from_pod(pl[i]), s);
+        }
+        return 0;
+    });
+}
+int orc_w_do_plays(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, tafl_state_w* out_st,
+                   tafl_play_effects_w* out_fx) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s, ns;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            PlayRecord rec;
+            int err = logic.do_play(play_from_pod(pl[i]), s, &ns, &rec);
+            tafl_play_effects_w fx{};
+            fx.err = (uint8_t)err;
+            if (err) { out_st[i] = st[i]; fx.status = st[i].status; }
+            else {
+                pack_state_w(ns, &out_st[i]);
+                std::set<Tile> tiles;
+                for (auto& c : rec.effects.captures) tiles.insert(c.tile);
+                bb_set_w<W>(fx.captures, tiles);
+                fx.n_captures = (uint8_t)tiles.size();
+                fx.status = ns.status;
+            }
+            if (out_fx) out_fx[i] = fx;
+        }
+        return 0;
+    });
+}
+int orc_w_legal_plays_of(const tafl_rules* r, int width, const tafl_state_w* st, uint32_t n, tafl_play* plays, uint32_t* counts) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            auto v = logic.get_all_possible_moves(s);
+            counts[i] = (uint32_t)v.size();
+            for (size_t k = 0; k < v.size() && k < TAFL_W_MAX_PLAYS; ++k) plays[(size_t)i * TAFL_W_MAX_PLAYS + k] = play_to_pod(v[k]);
+        }
+        return 0;
+    });
+}
+int orc_w_piece_plays(const tafl_rules* r, int width, const tafl_state_w* st, const uint8_t* tiles_rc, uint32_t n, tafl_play* plays,
+                      int32_t* counts) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            std::vector<Play> v;
+            bool ok = logic.iter_plays(Tile{tiles_rc[2 * i], tiles_rc[2 * i + 1]}, s, &v);
+            counts[i] = ok ? (int32_t)v.size() : -1;
+            for (size_t k = 0; k < v.size() && k < 64; ++k) plays[(size_t)i * 64 + k] = play_to_pod(v[k]);
+        }
+        return 0;
+    });
+}
+int orc_w_get_captures(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, tafl_play_effects_w* out) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            Play p = play_from_pod(pl[i]);
+            tafl_play_effects_w fx{};
+            if (!s.board.get_piece(p.from)) { fx.err = TAFL_NO_PIECE; out[i] = fx; continue; }
+            Piece mp = s.board.move_piece(p.from, p.to());
+            auto caps = logic.get_captures(p, mp, s);
+            std::set<Tile> tiles;
+            for (auto& c : caps) tiles.insert(c.tile);
+            bb_set_w<W>(fx.captures, tiles);
+            fx.n_captures = (uint8_t)tiles.size();
+            out[i] = fx;
+        }
+        return 0;
+    });
+}
+int orc_w_detect_shieldwall(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, tafl_play_effects_w* out) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            auto res = logic.detect_shieldwall(play_from_pod(pl[i]), s);
+            tafl_play_effects_w fx{};
+            if (!res) fx.n_captures = 0xFF;
+            else { bb_set_w<W>(fx.captures, *res); fx.n_captures = (uint8_t)res->size(); }
+            out[i] = fx;
+        }
+        return 0;
+    });
+}
+int orc_w_find_enclosure(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_enclosure_query* q, uint32_t n, tafl_enclosure_w* out) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            auto e = logic.find_enclosure(Tile{q[i].row, q[i].col}, PieceSet{q[i].enclosed_pieces}, PieceSet{q[i].enclosing_pieces},
+                                          q[i].abort_on_edge, q[i].abort_on_corner, s.board);
+            tafl_enclosure_w o{};
+            if (e) {
+                o.found = 1;
+                bb_set_w<W>(o.occupied, e->occupied);
+                bb_set_w<W>(o.unoccupied, e->unoccupied);
+                bb_set_w<W>(o.boundary, e->boundary);
+            }
+            out[i] = o;
+        }
+        return 0;
+    });
+}
+int orc_w_enclosure_secure(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_enclosure_query* q, uint32_t n, uint8_t* out) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            auto e = logic.find_enclosure(Tile{q[i].row, q[i].col}, PieceSet{q[i].enclosed_pieces}, PieceSet{q[i].enclosing_pieces},
+                                          q[i].abort_on_edge, q[i].abort_on_corner, s.board);
+            out[i] = e ? (uint8_t)logic.enclosure_secure(*e, q[i].inside_safe, q[i].outside_safe, s.board) : 0xFF;
+        }
+        return 0;
+    });
+}
+int orc_w_detect_exit_fort(const tafl_rules* r, int width, const tafl_state_w* st, uint32_t n, uint8_t* out) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            out[i] = logic.detect_exit_fort(s.board) ? 1 : 0;
+        }
+        return 0;
+    });
+}
+int orc_w_side_can_play(const tafl_rules* r, int width, const tafl_state_w* st, const uint8_t* sides, uint32_t n, uint8_t* out) {
+    return dispatch_w(width, [&](auto w) {
+        using W = decltype(w);
+        for (uint32_t i = 0; i < n; ++i) {
+            GameState<W> s;
+            unpack_state_w(st[i], &s);
+            GameLogic logic(*r, s.board.side_len);
+            out[i] = logic.side_can_play(sides[i] ? Side::Defender : Side::Attacker, s) ? 1 : 0;
+        }
+        return 0;
+    });
+}
+
 }  // extern "C"

@@ -113,9 +113,56 @@ struct Play {  // play.rs:23-27
 // ---------------------------------------------------------------------------------------------
 // bitfield.rs + board/state.rs
 // ---------------------------------------------------------------------------------------------
+// primitive_types::U256 / U512 (a dependency of the reference that is not in its tree; only the operations the
+// board code uses: shifts, bit logic, comparison with zero, truncation): NW little-endian 64-bit words.
+template <int NW>
+struct BigU {
+    uint64_t w[NW];
+    BigU() { for (auto& x : w) x = 0; }
+    BigU(uint64_t v) { for (auto& x : w) x = 0; w[0] = v; }   // NOLINT: the board code writes `W x = 0`, `(W)1 << sh`
+    explicit operator uint64_t() const { return w[0]; }
+    explicit operator uint8_t() const { return (uint8_t)w[0]; }
+    explicit operator bool() const { for (auto x : w) if (x) return true; return false; }
+    BigU operator<<(unsigned k) const {
+        BigU r;
+        if (k >= 64u * NW) return r;
+        const unsigned ws = k / 64, bs = k % 64;
+        for (int i = NW - 1; i >= (int)ws; --i) {
+            r.w[i] = w[i - ws] << bs;
+            if (bs && i - (int)ws - 1 >= 0) r.w[i] |= w[i - ws - 1] >> (64 - bs);
+        }
+        return r;
+    }
+    BigU operator>>(unsigned k) const {
+        BigU r;
+        if (k >= 64u * NW) return r;
+        const unsigned ws = k / 64, bs = k % 64;
+        for (int i = 0; i + (int)ws < NW; ++i) {
+            r.w[i] = w[i + ws] >> bs;
+            if (bs && i + (int)ws + 1 < NW) r.w[i] |= w[i + ws + 1] << (64 - bs);
+        }
+        return r;
+    }
+    BigU operator&(const BigU& o) const { BigU r; for (int i = 0; i < NW; ++i) r.w[i] = w[i] & o.w[i]; return r; }
+    BigU operator|(const BigU& o) const { BigU r; for (int i = 0; i < NW; ++i) r.w[i] = w[i] | o.w[i]; return r; }
+    BigU operator~() const { BigU r; for (int i = 0; i < NW; ++i) r.w[i] = ~w[i]; return r; }
+    BigU& operator&=(const BigU& o) { for (int i = 0; i < NW; ++i) w[i] &= o.w[i]; return *this; }
+    BigU& operator|=(const BigU& o) { for (int i = 0; i < NW; ++i) w[i] |= o.w[i]; return *this; }
+    bool operator==(const BigU& o) const { for (int i = 0; i < NW; ++i) if (w[i] != o.w[i]) return false; return true; }
+    bool operator!=(const BigU& o) const { return !(*this == o); }
+    bool operator>(int z) const { (void)z; return (bool)*this; }   // only ever `> 0`
+};
+using U256 = BigU<4>;
+using U512 = BigU<8>;
+
 template <class W> struct BitTraits;
 template <> struct BitTraits<uint64_t> { static constexpr int ROW_WIDTH = 7, BITS = 64; };   // bitfield.rs:178
 template <> struct BitTraits<u128> { static constexpr int ROW_WIDTH = 11, BITS = 128; };     // bitfield.rs:179
+template <> struct BitTraits<U256> { static constexpr int ROW_WIDTH = 15, BITS = 256; };     // bitfield.rs:180
+template <> struct BitTraits<U512> { static constexpr int ROW_WIDTH = 21, BITS = 512; };     // bitfield.rs:181
+inline int popcount_w(uint64_t w) { return __builtin_popcountll(w); }
+inline int popcount_w(u128 w) { return __builtin_popcountll((uint64_t)w) + __builtin_popcountll((uint64_t)(w >> 64)); }
+template <int NW> inline int popcount_w(const BigU<NW>& w) { int c = 0; for (auto x : w.w) c += __builtin_popcountll(x); return c; }
 
 template <class W>
 struct Board {  // board/state.rs:117-121
@@ -171,9 +218,7 @@ struct Board {  // board/state.rs:117-121
     bool tile_occupied(Tile t) const {  // board/state.rs:189-193
         return ((defenders | attackers) & tile_mask(t)) > 0;
     }
-    static int popcount(W w) {
-        return __builtin_popcountll((uint64_t)w) + (sizeof(W) > 8 ? __builtin_popcountll((uint64_t)((u128)w >> 64)) : 0);
-    }
+    static int popcount(W w) { return popcount_w(w); }
     uint8_t count_pieces(Side s) const {  // board/state.rs:195-200
         W w = (s == Side::Attacker ? attackers : defenders);
         return (uint8_t)popcount((W)(w << 4));
@@ -1112,6 +1157,39 @@ inline void unpack_state(const tafl_state& i, GameState<W>* s) {
         s->board.attackers = ((u128)i.att[1] << 64) | i.att[0];
         s->board.defenders = ((u128)i.def[1] << 64) | i.def[0];
     }
+    s->board.side_len = i.side_len;
+    for (int k = 0; k < 4; ++k) s->repetitions.queue[k] = unpack_record(i.recent[k]);
+    s->repetitions.attacker_reps = i.att_reps;
+    s->repetitions.defender_reps = i.def_reps;
+    s->repetitions.attacker_mid_pair = (i.flags & TAFL_FLAG_ATT_MID) != 0;
+    s->repetitions.defender_mid_pair = (i.flags & TAFL_FLAG_DEF_MID) != 0;
+    s->repetitions.first_i = i.ring_head & 3;
+    s->side_to_play = (i.flags & TAFL_FLAG_DEF_TO_PLAY) ? Side::Defender : Side::Attacker;
+    s->status = i.status;
+    s->turn = i.turn;
+    s->plays_since_capture = i.plays_since_capture;
+}
+// tafl_state_w <-> GameState<U256 / U512>
+template <int NW>
+inline void pack_state_w(const GameState<BigU<NW>>& s, tafl_state_w* o) {
+    *o = tafl_state_w{};
+    for (int i = 0; i < NW; ++i) { o->att[i] = s.board.attackers.w[i]; o->def[i] = s.board.defenders.w[i]; }
+    for (int i = 0; i < 4; ++i) o->recent[i] = pack_record(s.repetitions.queue[i]);
+    o->att_reps = (uint8_t)(s.repetitions.attacker_reps > 255 ? 255 : s.repetitions.attacker_reps);
+    o->def_reps = (uint8_t)(s.repetitions.defender_reps > 255 ? 255 : s.repetitions.defender_reps);
+    o->flags = (s.repetitions.attacker_mid_pair ? TAFL_FLAG_ATT_MID : 0) |
+               (s.repetitions.defender_mid_pair ? TAFL_FLAG_DEF_MID : 0) |
+               (s.side_to_play == Side::Defender ? TAFL_FLAG_DEF_TO_PLAY : 0);
+    o->status = s.status;
+    o->turn = (uint32_t)s.turn;
+    o->plays_since_capture = (uint32_t)s.plays_since_capture;
+    o->ring_head = (uint8_t)s.repetitions.first_i;
+    o->side_len = s.board.side_len;
+}
+template <int NW>
+inline void unpack_state_w(const tafl_state_w& i, GameState<BigU<NW>>* s) {
+    *s = GameState<BigU<NW>>{};
+    for (int k = 0; k < NW; ++k) { s->board.attackers.w[k] = i.att[k]; s->board.defenders.w[k] = i.def[k]; }
     s->board.side_len = i.side_len;
     for (int k = 0; k < 4; ++k) s->repetitions.queue[k] = unpack_record(i.recent[k]);
     s->repetitions.attacker_reps = i.att_reps;

@@ -8,6 +8,7 @@
 
 #include "../../alphazeroforhnefatafl_b200/csrc/tafl_ctx.hpp"
 #include "../../alphazeroforhnefatafl_b200/csrc/tafl_select.cuh"
+#include "../../alphazeroforhnefatafl_b200/csrc/tafl_wide.cuh"
 
 using namespace tafl;
 
@@ -187,6 +188,106 @@ int sim_piece_table_moves(const tafl_rules* r, int width, const tafl_state* st, 
                 counts[i] = (uint32_t)pt_gen_moves(cx, st[i], moves + (size_t)i * TAFL_MAX_MOVES, TAFL_MAX_MOVES);
             });
         }
+        return 0;
+    });
+}
+
+// ---- large boards (BB256 / BB512, tafl_state_w): the device functions behind tafl_w_* (csrc/tafl_wide.cuh) -------
+}  // extern "C"
+namespace {
+template <class F>
+int dispatch_w(int width, F&& f) {
+    if (width == 256) return f(BB256{});
+    if (width == 512) return f(BB512{});
+    return TAFL_ERR_INVALID_ARG;
+}
+}  // namespace
+extern "C" {
+int sim_w_validate_plays(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, uint8_t* out) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) {
+            const Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            out[i] = (uint8_t)validate_play(cx, st[i], pl[i], (st[i].flags & TAFL_FLAG_DEF_TO_PLAY) != 0);
+        }
+        return 0;
+    });
+}
+int sim_w_do_plays(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, tafl_state_w* out_st,
+                   tafl_play_effects_w* out_fx) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) {
+            const Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            out_st[i] = st[i];
+            const tafl_play_effects_w fx = do_play_w(cx, out_st[i], pl[i]);
+            if (out_fx) out_fx[i] = fx;
+        }
+        return 0;
+    });
+}
+int sim_w_legal_plays_of(const tafl_rules* r, int width, const tafl_state_w* st, uint32_t n, tafl_play* plays, uint32_t* counts) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) {
+            const Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            counts[i] = (uint32_t)gen_plays(cx, st[i], plays + (size_t)i * TAFL_W_MAX_PLAYS, TAFL_W_MAX_PLAYS);
+        }
+        return 0;
+    });
+}
+int sim_w_piece_plays(const tafl_rules* r, int width, const tafl_state_w* st, const uint8_t* rc, uint32_t n, tafl_play* plays, int32_t* counts) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) {
+            const Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            counts[i] = piece_plays_w(cx, st[i], rc[2 * i], rc[2 * i + 1], plays + (size_t)i * 64, 64);
+        }
+        return 0;
+    });
+}
+int sim_w_get_captures(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, tafl_play_effects_w* out) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) out[i] = query_captures_w(make_ctx<BB>(*r, st[i].side_len), st[i], pl[i]);
+        return 0;
+    });
+}
+int sim_w_detect_shieldwall(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_play* pl, uint32_t n, tafl_play_effects_w* out) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) out[i] = query_shieldwall_w(make_ctx<BB>(*r, st[i].side_len), st[i], pl[i]);
+        return 0;
+    });
+}
+int sim_w_find_enclosure(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_enclosure_query* q, uint32_t n, tafl_enclosure_w* out) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) { uint8_t sec; out[i] = query_enclosure_w(make_ctx<BB>(*r, st[i].side_len), st[i], q[i], &sec); }
+        return 0;
+    });
+}
+int sim_w_enclosure_secure(const tafl_rules* r, int width, const tafl_state_w* st, const tafl_enclosure_query* q, uint32_t n, uint8_t* out) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) query_enclosure_w(make_ctx<BB>(*r, st[i].side_len), st[i], q[i], &out[i]);
+        return 0;
+    });
+}
+int sim_w_detect_exit_fort(const tafl_rules* r, int width, const tafl_state_w* st, uint32_t n, uint8_t* out) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) {
+            const Ctx<BB> cx = make_ctx<BB>(*r, st[i].side_len);
+            out[i] = detect_exit_fort(cx, load_pos(cx, st[i])) ? 1 : 0;
+        }
+        return 0;
+    });
+}
+int sim_w_side_can_play(const tafl_rules* r, int width, const tafl_state_w* st, const uint8_t* sides, uint32_t n, uint8_t* out) {
+    return dispatch_w(width, [&](auto z) {
+        using BB = decltype(z);
+        for (uint32_t i = 0; i < n; ++i) out[i] = query_can_play_w(make_ctx<BB>(*r, st[i].side_len), st[i], sides[i] != 0);
         return 0;
     });
 }

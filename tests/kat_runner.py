@@ -116,7 +116,11 @@ def run_case(case, width, host, make_impl):
                 assert n >= 0, where(i)
                 got = []
                 for m in moves[0, :n]:
-                    frm, to = A.move_from_to(width, m)
+                    if A.is_wide(width):   # wide boards list plays, not compact moves
+                        frm = (int(m["from_row"]), int(m["from_col"]))
+                        to = (frm[0], frm[1] + int(m["disp"])) if m["axis"] == A.HORIZONTAL else (frm[0] + int(m["disp"]), frm[1])
+                    else:
+                        frm, to = A.move_from_to(width, m)
                     assert list(frm) == s["tile"], where(i)
                     got.append(list(to))
                 assert len(set(map(tuple, got))) == n, where(i)
@@ -167,10 +171,12 @@ def run_case(case, width, host, make_impl):
 
 
 def run_all(host, make_impl, widths=(64, 128)):
+    """widths 256 / 512: every case also runs on the large bitfields (the reference instantiates its width-generic
+    tests on all four, game/game/logic.rs:1015-1021,1081-1087; a 7x7 or 9x9 position sits in any wider row stride)"""
     data = load()
     total = 0
     for case in data["cases"]:
-        for w in case["widths"]:
-            if w in widths:
+        for w in widths:
+            if w in case["widths"] or (A.is_wide(w) and case["side_len"] <= (15 if w == 256 else 21)):
                 total += run_case(case, w, host, make_impl)
     return total

@@ -40,7 +40,7 @@ def build_hostsim(sanitize=None):
         sanitize = os.environ.get("TAFL_HOSTSIM_SAN") == "1"
     so = os.path.join(HOSTSIM_DIR, "libhostsim_san.so" if sanitize else "libhostsim.so")
     deps = [os.path.join(HOSTSIM_DIR, "hostsim.cpp"), os.path.join(ROOT, "include", "tafl.h")]
-    deps += [os.path.join(CSRC, f) for f in ("tafl_bb.cuh", "tafl_core.cuh", "tafl_select.cuh", "tafl_ctx.hpp")]
+    deps += [os.path.join(CSRC, f) for f in ("tafl_bb.cuh", "tafl_core.cuh", "tafl_select.cuh", "tafl_ctx.hpp", "tafl_wide.cuh")]
     if _newer(so, deps):
         opt = SAN_FLAGS if sanitize else ["-O2"]
         subprocess.check_call(["g++"] + opt + ["-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
@@ -143,6 +143,72 @@ class ByValueImpl:
         return out
 
 
+class ByValueImplW:
+    """The by-value API over the large bitfields (widths 256 / 512, tafl_state_w): oracle (orc_w_) and hostsim (sim_w_)."""
+
+    def __init__(self, lib, prefix, rules, width):
+        self.lib, self.prefix, self.rules, self.width = lib, prefix, rules, width
+
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    def _call(self, name, *args):
+        rc = self._f(name)(C.byref(self.rules), self.width, *args)
+        assert rc == 0, (name, rc)
+
+    def validate_plays(self, states, plays):
+        out = np.zeros(len(states), np.uint8)
+        self._call("validate_plays", A.ptr(states), A.ptr(plays), len(states), A.ptr(out))
+        return out
+
+    def do_plays(self, states, plays):
+        out, fx = np.zeros(len(states), A.STATE_W_DTYPE), np.zeros(len(states), A.EFFECTS_W_DTYPE)
+        self._call("do_plays", A.ptr(states), A.ptr(plays), len(states), A.ptr(out), A.ptr(fx))
+        return out, fx
+
+    def legal_plays_of(self, states):
+        plays, counts = np.zeros((len(states), A.W_MAX_PLAYS), A.PLAY_DTYPE), np.zeros(len(states), np.uint32)
+        self._call("legal_plays_of", A.ptr(states), len(states), A.ptr(plays), A.ptr(counts))
+        return plays, counts
+
+    def piece_plays(self, states, tiles_rc):
+        tiles_rc = np.ascontiguousarray(tiles_rc, np.uint8)
+        plays, counts = np.zeros((len(states), 64), A.PLAY_DTYPE), np.zeros(len(states), np.int32)
+        self._call("piece_plays", A.ptr(states), A.ptr(tiles_rc), len(states), A.ptr(plays), A.ptr(counts))
+        return plays, counts
+
+    def get_captures(self, states, plays):
+        fx = np.zeros(len(states), A.EFFECTS_W_DTYPE)
+        self._call("get_captures", A.ptr(states), A.ptr(plays), len(states), A.ptr(fx))
+        return fx
+
+    def detect_shieldwall(self, states, plays):
+        fx = np.zeros(len(states), A.EFFECTS_W_DTYPE)
+        self._call("detect_shieldwall", A.ptr(states), A.ptr(plays), len(states), A.ptr(fx))
+        return fx
+
+    def find_enclosure(self, states, queries):
+        out = np.zeros(len(states), A.ENCLOSURE_W_DTYPE)
+        self._call("find_enclosure", A.ptr(states), A.ptr(queries), len(states), A.ptr(out))
+        return out
+
+    def enclosure_secure(self, states, queries):
+        out = np.zeros(len(states), np.uint8)
+        self._call("enclosure_secure", A.ptr(states), A.ptr(queries), len(states), A.ptr(out))
+        return out
+
+    def detect_exit_fort(self, states):
+        out = np.zeros(len(states), np.uint8)
+        self._call("detect_exit_fort", A.ptr(states), len(states), A.ptr(out))
+        return out
+
+    def side_can_play(self, states, sides):
+        sides = np.ascontiguousarray(sides, np.uint8)
+        out = np.zeros(len(states), np.uint8)
+        self._call("side_can_play", A.ptr(states), A.ptr(sides), len(states), A.ptr(out))
+        return out
+
+
 class Oracle:
     """ctypes face of oracle/liboracle.so."""
 
@@ -166,6 +232,10 @@ class Oracle:
         return self.lib.orc_preset_board_fen(preset).decode()
 
     def state_from_fen(self, fen, width, side=A.ATTACKER):
+        if A.is_wide(width):
+            st = np.zeros(1, A.STATE_W_DTYPE)
+            rc = self.lib.orc_w_state_from_fen(fen.encode(), width, 1 if side == A.DEFENDER else 0, A.ptr(st))
+            return rc, st
         st = np.zeros(1, A.STATE_DTYPE)
         rc = self.lib.orc_state_from_fen(fen.encode(), width, 1 if side == A.DEFENDER else 0, A.ptr(st))
         return rc, st
@@ -209,6 +279,8 @@ class Oracle:
         assert self.lib.orc_track_play(A.ptr(st), width, 1 if side == A.DEFENDER else 0, C.byref(play), int(captures)) == 0
 
     def by_value(self, rules, width):
+        if A.is_wide(width):
+            return ByValueImplW(self.lib, "orc_w_", rules, width)
         return ByValueImpl(self.lib, "orc_", rules, width)
 
     def random_playout(self, rules, fen, width, seed, n_games, n_steps, auto_reset=True, game_id_base=0, ply0=0,
@@ -336,6 +408,8 @@ class HostSim:
                                                 C.c_uint64, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
 
     def by_value(self, rules, width):
+        if A.is_wide(width):
+            return ByValueImplW(self.lib, "sim_w_", rules, width)
         return ByValueImpl(self.lib, "sim_", rules, width)
 
     def force_generic(self, on):
@@ -417,7 +491,10 @@ class OracleHost:
         return self.o.state_from_fen(fen, width, side)
 
     def move_piece(self, st, width, frm, to):
-        rc, _ = self.o.board_op(st, width, 6, frm[0], frm[1], to[0], to[1])
+        if A.is_wide(width):
+            rc = self.o.lib.orc_w_move_piece(A.ptr(st), width, frm[0], frm[1], to[0], to[1])
+        else:
+            rc, _ = self.o.board_op(st, width, 6, frm[0], frm[1], to[0], to[1])
         assert rc == 0, rc
 
     def play_from_str(self, s):

@@ -151,3 +151,76 @@ def random_boards(orc, rng, N, width, n, density=None, edge_bias=True):
         assert rc == 0
         out[i] = st[0]
     return out
+
+
+def wide_random_boards(orc, rng, N, width, n):
+    """random NxN positions on a wide bitfield: both sides scattered, a king somewhere, either side to move"""
+    out = np.zeros(n, A.STATE_W_DTYPE)
+    for i in range(n):
+        d = rng.uniform(0.08, 0.45)
+        rows = []
+        kr, kc = rng.integers(0, N, 2)
+        for r in range(N):
+            s, run = "", 0
+            for c in range(N):
+                ch = "."
+                if (r, c) == (kr, kc) and rng.random() < 0.95:
+                    ch = "K"
+                elif rng.random() < d * (1.5 if r in (0, 1, N - 2, N - 1) or c in (0, 1, N - 2, N - 1) else 0.8):
+                    ch = "t" if rng.random() < 0.55 else "T"
+                if ch == ".":
+                    run += 1
+                else:
+                    s += (str(run) if run else "") + ch
+                    run = 0
+            rows.append(s + (str(run) if run else ""))
+        rc, st = orc.state_from_fen("/".join(rows), width, A.DEFENDER if rng.random() < 0.5 else A.ATTACKER)
+        assert rc == 0
+        out[i] = st[0]
+    return out
+
+
+def compare_wide(ref, test, states, N, rng):
+    """every wide by-value entry point of `test` against `ref` on `states`"""
+    n = len(states)
+    pr, cr = ref.legal_plays_of(states)
+    pt, ct = test.legal_plays_of(states)
+    assert np.array_equal(cr, ct)
+    for i in range(n):
+        assert pr[i, :cr[i]].tobytes() == pt[i, :ct[i]].tobytes(), i
+    plays = np.zeros(n, A.PLAY_DTYPE)
+    for i in range(n):
+        if cr[i] and rng.random() < 0.85:
+            plays[i] = pr[i, rng.integers(cr[i])]
+        else:
+            fr, fc = rng.integers(0, N + 1, 2)
+            hz = rng.random() < 0.5
+            plays[i] = (fr, fc, A.HORIZONTAL if hz else A.VERTICAL, int(rng.integers(-N, N + 1)))
+    assert np.array_equal(ref.validate_plays(states, plays), test.validate_plays(states, plays))
+    sr, fr_ = ref.do_plays(states, plays)
+    st_, ft = test.do_plays(states, plays)
+    assert fr_.tobytes() == ft.tobytes()
+    assert sr.tobytes() == st_.tobytes()
+    legal = fr_["err"] == 0
+    if legal.any():
+        assert ref.get_captures(states[legal], plays[legal]).tobytes() == test.get_captures(states[legal], plays[legal]).tobytes()
+    assert ref.detect_shieldwall(states, plays).tobytes() == test.detect_shieldwall(states, plays).tobytes()
+    tiles = rng.integers(0, N, (n, 2)).astype(np.uint8)
+    a, ca = ref.piece_plays(states, tiles)
+    b, cb = test.piece_plays(states, tiles)
+    assert np.array_equal(ca, cb)
+    for i in range(n):
+        if ca[i] > 0:
+            assert a[i, :ca[i]].tobytes() == b[i, :cb[i]].tobytes(), i
+    q = np.zeros(n, A.ENCL_QUERY_DTYPE)
+    q["row"], q["col"] = tiles[:, 0], tiles[:, 1]
+    q["abort_on_edge"], q["abort_on_corner"] = rng.integers(0, 2, n), rng.integers(0, 2, n)
+    sets = [0xFFFF, A.pieceset_side(A.DEFENDER), A.pieceset_side(A.ATTACKER), A.pieceset_type(A.KING), A.pieceset_type(A.SOLDIER), 0]
+    q["enclosed_pieces"], q["enclosing_pieces"] = rng.choice(sets, n), rng.choice(sets, n)
+    q["inside_safe"], q["outside_safe"] = rng.integers(0, 2, n), rng.integers(0, 2, n)
+    assert ref.find_enclosure(states, q).tobytes() == test.find_enclosure(states, q).tobytes()
+    assert np.array_equal(ref.enclosure_secure(states, q), test.enclosure_secure(states, q))
+    assert np.array_equal(ref.detect_exit_fort(states), test.detect_exit_fort(states))
+    sides = rng.integers(0, 2, n).astype(np.uint8)
+    assert np.array_equal(ref.side_can_play(states, sides), test.side_can_play(states, sides))
+    return sr[legal]

@@ -18,12 +18,17 @@ class ProductHost:
         return E.preset_board(pid)
 
     def state_from_fen(self, fen, width, side):
+        if A.is_wide(width):
+            st = np.zeros(1, A.STATE_W_DTYPE)
+            rc = lib().tafl_w_state_from_fen(fen.encode(), width, side, A.ptr(st))
+            return rc, st
         st = np.zeros(1, A.STATE_DTYPE)
         rc = lib().tafl_state_from_fen(fen.encode(), width, side, A.ptr(st))
         return rc, st
 
     def move_piece(self, st, width, frm, to):
-        rc = lib().tafl_board_move_piece(A.ptr(st), width, frm[0], frm[1], to[0], to[1])
+        f = lib().tafl_w_board_move_piece if A.is_wide(width) else lib().tafl_board_move_piece
+        rc = f(A.ptr(st), width, frm[0], frm[1], to[0], to[1])
         assert rc == 0, rc
 
     def play_from_str(self, s):
@@ -78,11 +83,14 @@ class GpuImplFactory:
     def __call__(self, rules, width, side_len):
         key = (bytes(rules), width, side_len)
         if key not in self.cache:
-            fen = "/".join([str(side_len)] * side_len)
-            self.cache[key] = GpuByValue(E.LockstepGames(rules.copy(), fen, 1, self.device, width))
+            if A.is_wide(width):   # large bitfields: the by-value WideLogic is the implementation itself
+                self.cache[key] = E.WideLogic(rules.copy(), side_len, width, self.device)
+            else:
+                fen = "/".join([str(side_len)] * side_len)
+                self.cache[key] = GpuByValue(E.LockstepGames(rules.copy(), fen, 1, self.device, width))
         return self.cache[key]
 
     def close(self):
         for v in self.cache.values():
-            v.e.close()
+            (v if isinstance(v, E.WideLogic) else v.e).close()
         self.cache.clear()

@@ -12,7 +12,8 @@ import kat_runner
 from alphazeroforhnefatafl_b200 import _abi as A
 from alphazeroforhnefatafl_b200 import engine as E
 from alphazeroforhnefatafl_b200.engine import TaflError
-from parity_cases import PRESET_CONFIGS, board_for, compare_by_value, random_boards, sample_positions
+from parity_cases import (PRESET_CONFIGS, board_for, compare_by_value, compare_wide, random_boards, sample_positions,
+                          wide_random_boards)
 from product_host import GpuImplFactory, ProductHost
 
 pytestmark = pytest.mark.gpu
@@ -367,3 +368,38 @@ def test_gpu_legal_move_kernels_agree(orc, built_lib, monkeypatch, name, preset,
                     assert not mv[i, cnt[i]:(cnt[i] + 7) // 8 * 8].any(), (G, i)
             m2, c2 = g.legal_moves_of(states[:100])          # the by-value entry point runs the same kernel
             assert np.array_equal(c2, ec[:100])
+
+
+def test_gpu_reference_kats_on_large_bitfields(gpu):
+    """SURVEY §8f.4 / VERDICT r01 item 9: the reference's unit tests on BitfieldBoardState<U256> / <U512> (the widths its
+    generic tests are instantiated at, game/game/logic.rs:1015-1021,1081-1087) through the CUDA path (tafl_w_*)."""
+    n = kat_runner.run_all(ProductHost(), gpu, widths=(256, 512))
+    assert n >= 160
+
+
+@pytest.mark.parametrize("width,N", [(256, 13), (256, 15), (512, 19), (512, 21), (512, 11)])
+def test_gpu_large_boards_vs_oracle(orc, built_lib, width, N):
+    """15x15 / 21x21-class boards through the C ABI's tafl_w_* kernels against the oracle: every by-value query on
+    random boards and on their successors, Copenhagen rules and rule variants; FEN text round trip on the host."""
+    rng = np.random.default_rng(2000 + width + N)
+    base = orc.preset_rules(A.PRESET_COPENHAGEN)
+    for trial in range(3):
+        rules = base if trial == 0 else base.copy(throne_movement=int(rng.integers(0, 5)), king_strength=int(rng.integers(0, 3)),
+                                                   edge_escape=int(rng.integers(0, 2)), hostility_edge=int(rng.choice([0, 0xFFFF])),
+                                                   linnaean_capture=int(rng.integers(0, 2)), enclosure_win=int(rng.integers(0, 3)))
+        states = wide_random_boards(orc, rng, N, width, 200)
+        with E.WideLogic(rules, N, width) as w:
+            nxt = compare_wide(orc.by_value(rules, width), w, states, N, rng)
+            if len(nxt):
+                compare_wide(orc.by_value(rules, width), w, nxt, N, rng)
+            for st in states[:10]:
+                fen = E.WideLogic.state_to_fen(st, width)
+                back = E.WideLogic.state_from_fen(fen, width, A.DEFENDER if st["flags"] & A.FLAG_DEF_TO_PLAY else A.ATTACKER)
+                if N <= 16:   # a king beyond row / column 15 does not survive the four-bit nibbles (reference behaviour)
+                    assert np.array_equal(back["att"][0], st["att"]) and np.array_equal(back["def"][0], st["def"])
+    with pytest.raises(TaflError):
+        E.WideLogic(base, 16, 256)          # a 16x16 board does not fit the 256-bit field
+    with E.WideLogic(base, N, width) as w:
+        bad = wide_random_boards(orc, rng, N - 1, width, 1)
+        with pytest.raises(TaflError):
+            w.validate_plays(bad, np.zeros(1, A.PLAY_DTYPE))     # side_len mismatch

@@ -8,12 +8,39 @@ import pytest
 import kat_runner
 import oracle_ffi as F
 from alphazeroforhnefatafl_b200 import _abi as A
-from parity_cases import PRESET_CONFIGS, board_for, compare_by_value, random_boards, sample_positions
+from parity_cases import (PRESET_CONFIGS, board_for, compare_by_value, compare_wide, random_boards, sample_positions,
+                          wide_random_boards)
 
 
 def test_hostsim_reference_kats(orc, sim):
     n = kat_runner.run_all(F.OracleHost(), lambda rules, width, side_len: sim.by_value(rules, width))
     assert n >= 150
+
+
+def test_hostsim_reference_kats_on_large_bitfields(orc, sim):
+    """The reference's own unit tests on BitfieldBoardState<U256> / <U512> (row strides 15 / 21): the oracle first
+    (its restatement of the reference at those widths must give the reference's answers), then the kernels' device
+    functions (csrc/tafl_wide.cuh over tafl_core.cuh) compiled for the host."""
+    n_orc = kat_runner.run_all(F.OracleHost(), lambda rules, width, side_len: orc.by_value(rules, width), widths=(256, 512))
+    n_sim = kat_runner.run_all(F.OracleHost(), lambda rules, width, side_len: sim.by_value(rules, width), widths=(256, 512))
+    assert n_orc == n_sim and n_orc >= 160
+
+
+@pytest.mark.parametrize("width,N", [(256, 13), (256, 15), (512, 19), (512, 21), (512, 11)])
+def test_hostsim_large_boards_vs_oracle(orc, sim, width, N):
+    """15x15 / 21x21-class boards (and an 11x11 board in the 512-bit layout) under Copenhagen rules and a few rule
+    variants: every by-value query of the device functions against the oracle, on random boards and on the
+    positions reached by playing one legal play from each."""
+    rng = np.random.default_rng(1000 + width + N)
+    base = orc.preset_rules(A.PRESET_COPENHAGEN)
+    for trial in range(3):
+        rules = base if trial == 0 else base.copy(throne_movement=int(rng.integers(0, 5)), king_strength=int(rng.integers(0, 3)),
+                                                   edge_escape=int(rng.integers(0, 2)), hostility_edge=int(rng.choice([0, 0xFFFF])),
+                                                   linnaean_capture=int(rng.integers(0, 2)), enclosure_win=int(rng.integers(0, 3)))
+        states = wide_random_boards(orc, rng, N, width, 60)
+        nxt = compare_wide(orc.by_value(rules, width), sim.by_value(rules, width), states, N, rng)
+        if len(nxt):
+            compare_wide(orc.by_value(rules, width), sim.by_value(rules, width), nxt, N, rng)
 
 
 @pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS)
