@@ -43,7 +43,7 @@ if [ -n "$NCU_WHAT" ]; then
       step) PAT=k_step_random; SKIP=3; CNT=2;;
       legal) PAT=k_legal_moves_g; SKIP=1; CNT=2;;
       mcts) PAT=k_mcts_sims_g; SKIP=0; CNT=1;;
-      hook) PAT="k_mcts_select_leaf|k_mcts_expand_backup"; SKIP=100; CNT=4;;
+      hook) PAT="k_mcts_hook_round"; SKIP=300; CNT=2;;
     esac
     timeout 1500 ncu --set full --clock-control none --import-source on -k "regex:$PAT" -s $SKIP -c $CNT -o gpurun_out/prof_${K}_$TAG -f $CMD > gpurun_out/ncu_${K}_$TAG.log 2>&1
     echo "ncu $K exit $?"
