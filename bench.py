@@ -208,7 +208,7 @@ class Clocks(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.01)
+            time.sleep(0.02)
 
     def summary(self):
         s = sorted(self.samples)
@@ -593,7 +593,7 @@ def bench_mcts(cx, E, preset):
     b_sim = d_bar * (16 + 12 * l_bar) + (144 + 18 * l_bar) + 32 * d_bar
     v = c_sum / (t_max * 1e-3)
     kern = "k_mcts_sims_g"
-    traffic_launch = ncu_traffic(kern)
+    traffic_launch = ncu_traffic(kern) if preset == "copenhagen" else None      # the committed capture is the Copenhagen bench size
     cap = ncu_summary(kern)
     cap_sims = cap.get("sims_per_launch")
     per_sim = traffic_launch / cap_sims if traffic_launch and cap_sims else None
@@ -606,7 +606,7 @@ def bench_mcts(cx, E, preset):
                         "basis": "SURVEY §8d MODEL bytes per simulation (every edge of every visited node read) — the kernel moves far less, see frac_measured",
                         "traffic": per_sim, "traffic_unit": "DRAM bytes per simulation (ncu dram__bytes_read+write of one bench-size launch / its simulations)",
                         "frac_measured": None if per_sim is None else v / cx.world * per_sim / 1e9 / hbm_peak,
-                        "binding_limit": ncu_binding_limit(kern)},
+                        "binding_limit": ncu_binding_limit(kern) if preset == "copenhagen" else None},
            "selfplay_sweep": {"records_gathered_on_rank0": int(n_rec), "record_bytes": A.REC_STRIDE,
                               "replay_window_rows": None if replay is None else len(replay),
                               "gather": "tafl_gather_records_on (C-ABI NCCL, ragged, side stream, overlapped)" if sp.ng is not None else "single rank: rows stay on the device",
