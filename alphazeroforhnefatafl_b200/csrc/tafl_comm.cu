@@ -140,8 +140,8 @@ int tafl_gather_records(tafl_engine* e, void* comm_, int n_ranks, int rank, int 
 
 int tafl_gather_records_on(tafl_engine* e, void* comm_, int n_ranks, int rank, int root, const void* d_send, uint32_t n_local,
                            void* d_recv, uint64_t recv_capacity_rows, uint32_t* h_counts, void* stream_) {
-    if (!e || !comm_ || n_ranks < 1 || rank < 0 || rank >= n_ranks || root < 0 || root >= n_ranks || !h_counts)
-        return TAFL_ERR_INVALID_ARG;
+    if (!e || !comm_ || n_ranks < 1 || rank < 0 || rank >= n_ranks || root < 0 || root >= n_ranks) return TAFL_ERR_INVALID_ARG;
+    if (!h_counts && rank == root) return TAFL_ERR_INVALID_ARG;   // the root needs the counts to post its receives
     if (n_local && !d_send) return TAFL_ERR_INVALID_ARG;
     NcclApi& n = nccl();
     if (!n.h) { e->err = n.err; return TAFL_ERR_CUDA; }
@@ -156,6 +156,10 @@ int tafl_gather_records_on(tafl_engine* e, void* comm_, int n_ranks, int rank, i
     d_cnt = (uint32_t*)p;
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(d_cnt, &n_local, sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
     TAFL_NCCL_TRY(e, n.AllGather(d_cnt, d_cnt + 1, 1, kUint32, comm, stream));
+    if (!h_counts) {   // a sending rank that does not ask for the counts: nothing to wait for, the call stays asynchronous
+        if (n_local) TAFL_NCCL_TRY(e, n.Send(d_send, (size_t)n_local * TAFL_REC_STRIDE, kUint8, root, comm, stream));
+        return TAFL_OK;
+    }
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_counts, d_cnt + 1, (size_t)n_ranks * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(stream));
     uint64_t total = 0;

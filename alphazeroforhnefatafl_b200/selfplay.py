@@ -77,14 +77,16 @@ class NcclGather:
             raise RuntimeError("tafl_nccl_unique_id failed (%d): is libnccl.so.2 loadable?" % rc)
         return bytes(buf)
 
-    def gather(self, local, recv=None, stream=None):
+    def gather(self, local, recv=None, stream=None, wait=True):
         """local: [n_local, REC_STRIDE] uint8 CUDA tensor; returns (rows tensor on the root / None, counts).
         recv (root): [capacity, REC_STRIDE] uint8 CUDA tensor; default capacity = n_games * n_ranks rows,
         pass a larger one when the shards are ragged.  stream: a torch.cuda.Stream to run the exchange on
-        (None = the engine's stream); the call returns when the rows have landed."""
+        (None = the engine's stream); the call returns when the rows have landed.  wait=False (ranks other than the
+        root): only enqueue — no row counts come back, the host does not block."""
         from ._lib import lib
         assert local.dtype == torch.uint8 and local.dim() == 2 and local.shape[1] == A.REC_STRIDE and local.is_contiguous()
         counts = np.zeros(self.n_ranks, np.uint32)
+        nowait = not wait and self.rank != self.root
         cap = 0
         if self.rank == self.root:
             if recv is None:
@@ -92,8 +94,10 @@ class NcclGather:
             cap = recv.shape[0]
         self.g._ck(lib().tafl_gather_records_on(self.g._h, self.comm, self.n_ranks, self.rank, self.root,
                                                 local.data_ptr() if local.shape[0] else None, local.shape[0],
-                                                recv.data_ptr() if recv is not None else None, cap, A.ptr(counts),
+                                                recv.data_ptr() if recv is not None else None, cap, None if nowait else A.ptr(counts),
                                                 stream.cuda_stream if stream is not None else None))
+        if nowait:
+            return None, None
         if stream is not None:
             stream.synchronize()
         else:
@@ -245,6 +249,7 @@ class SelfPlay:
         with torch.cuda.device(games.device):
             self.rec = [torch.zeros((games.n_games, A.REC_STRIDE), dtype=torch.uint8, device="cuda") for _ in range(2)]
             self.ev_pack = [torch.cuda.Event() for _ in range(2)]
+            self.ev_sent = [None, None]                  # side-stream event behind the last send of each row buffer
             self.side = torch.cuda.Stream()
         self.cnt = E.PinnedArray((2, 2), np.uint32)      # [buffer][rows, overflow flags], written by the device
         self.pending = None                              # buffer whose rows have not been collected yet
@@ -262,6 +267,7 @@ class SelfPlay:
 
     def close(self):
         if self.ng is not None:
+            self.side.synchronize()      # sends enqueued without waiting are out before the communicator goes
             self.ng.close()
             self.ng = None
         if self.cnt is not None:
@@ -291,6 +297,9 @@ class SelfPlay:
             if temp != 0:
                 g.mcts_policy(temp, choose=True, seed=seed, want_probs=False)
             g.mcts_play_best(False)
+            if self.ev_sent[b] is not None:   # the rows this buffer held two moves ago have left (device-side wait only)
+                self.stream.wait_event(self.ev_sent[b])
+                self.ev_sent[b] = None
             if only_ongoing:   # rows of the searched games only, compacted on the device
                 g.pack_records_compact(self.rec[b].data_ptr(), A.ptr(self.cnt.a[b]))
             else:
@@ -329,5 +338,9 @@ class SelfPlay:
             with torch.cuda.stream(self.stream):
                 return gather_records(rows, self.dst, self.group)
         self.side.wait_event(self.ev_pack[b])
-        out, _ = self.ng.gather(rows, self.recv[b] if self.recv is not None else None, stream=self.side)
+        # the root waits for the row counts and the rows; every other rank only enqueues its send and carries on
+        out, _ = self.ng.gather(rows, self.recv[b] if self.recv is not None else None, stream=self.side, wait=self.rank == self.dst)
+        ev = torch.cuda.Event()
+        ev.record(self.side)
+        self.ev_sent[b] = ev
         return out

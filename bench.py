@@ -763,6 +763,9 @@ def _sweep_to_terminal(cx, E, SP, rules, fen):
                          edge_capacity=(args.mcts_sims + 1) * 320)
         replay = SP.DeviceReplayBuffer(n * cx.world * 48, cx.local) if cx.rank == 0 else None
         moves = 40
+        for _ in range(2):                                 # warm-up: the gather's communicator connects on first use
+            sp.move()
+        sp.flush()
         cx.barrier()
         t0 = time.perf_counter()
         for _ in range(moves):

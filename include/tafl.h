@@ -626,7 +626,8 @@ int tafl_gather_records(tafl_engine* e, void* comm, int n_ranks, int rank, int r
 /* The same exchange enqueued on `stream` (a cudaStream_t of the engine's device; NULL = the engine's
  * stream) — the caller orders it behind tafl_pack_records with an event, so the gather of move k
  * overlaps the search of move k+1 on the engine's stream and the one host wait this call contains
- * (the all-gathered row counts) never stalls the search. */
+ * (the all-gathered row counts) never stalls the search.  A rank other than the root may pass
+ * h_counts == NULL: it then only enqueues (count exchange + its send) and returns without waiting. */
 int tafl_gather_records_on(tafl_engine* e, void* comm, int n_ranks, int rank, int root,
                            const void* d_send, uint32_t n_local, void* d_recv,
                            uint64_t recv_capacity_rows, uint32_t* h_counts, void* stream);
