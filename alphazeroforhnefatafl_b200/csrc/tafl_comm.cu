@@ -161,7 +161,12 @@ int tafl_gather_records_on(tafl_engine* e, void* comm_, int n_ranks, int rank, i
         return TAFL_OK;
     }
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_counts, d_cnt + 1, (size_t)n_ranks * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-    TAFL_CUDA_TRY(e, cudaStreamSynchronize(stream));
+    // The root waits here for the slowest rank's count.  A blocking-sync event yields the core instead of spinning on
+    // it: eight ranks with their NCCL proxy threads share the host's cores, and a spinning waiter takes one from a
+    // rank that still has launches to enqueue.
+    if (!e->ev_block) TAFL_CUDA_TRY(e, cudaEventCreateWithFlags(&e->ev_block, cudaEventBlockingSync | cudaEventDisableTiming));
+    TAFL_CUDA_TRY(e, cudaEventRecord(e->ev_block, stream));
+    TAFL_CUDA_TRY(e, cudaEventSynchronize(e->ev_block));
     uint64_t total = 0;
     for (int r = 0; r < n_ranks; ++r) total += h_counts[r];
     void* d_sink = nullptr;   // root buffer too small: the exchange must still happen (the senders are committed to it)

@@ -571,6 +571,7 @@ int tafl_engine_destroy(tafl_engine* e) {
     cudaFree(e->d_stats); cudaFree(e->d_checksum); cudaFree(e->d_ply); cudaFree(e->d_episode);
     cudaFree(e->hist.st); cudaFree(e->hist.rec); cudaFree(e->hist.len); cudaFree(e->hist.floor);
     if (e->step_graph) cudaGraphExecDestroy(e->step_graph);
+    if (e->ev_block) cudaEventDestroy(e->ev_block);
     for (auto& p : e->d_scratch) cudaFree(p);
     if (e->aux_ready) for (auto& st : e->aux) cudaStreamDestroy(st);
     if (e->stream) cudaStreamDestroy(e->stream);

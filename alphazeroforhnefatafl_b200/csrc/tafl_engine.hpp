@@ -40,6 +40,7 @@ struct tafl_engine {
     int device = 0, width = 0, N = 0, sm_count = 0;
     uint32_t n_games = 0;
     cudaStream_t stream = nullptr;
+    cudaEvent_t ev_block = nullptr;    // blocking-sync event for host waits that may be long (tafl_gather_records_on)
     tafl_rules rules{};
     tafl_state start{};
     tafl::Ctx<tafl::BB64> cx64;

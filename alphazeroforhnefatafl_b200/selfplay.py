@@ -23,6 +23,14 @@ REC_DTYPE = np.dtype([("h", REC_HEADER), ("moves", "<u2", (A.REC_MOVES,)), ("vis
 assert REC_DTYPE.itemsize == A.REC_STRIDE
 
 
+def _wait(stream):
+    """host wait for a stream through a blocking-sync event: the waiting thread sleeps instead of spinning on a core
+    that another rank's launch thread or an NCCL proxy thread could use (eight ranks share one host)"""
+    ev = torch.cuda.Event(blocking=True)
+    ev.record(stream)
+    ev.synchronize()
+
+
 def gather_records(local, dst=0, group=None):
     """Gather [n_local, REC_STRIDE] uint8 record tensors of every rank to rank ``dst``.
 
@@ -99,7 +107,7 @@ class NcclGather:
         if nowait:
             return None, None
         if stream is not None:
-            stream.synchronize()
+            _wait(stream)
         else:
             self.g.sync()
         return (recv[:int(counts.sum())] if self.rank == self.root else None), counts
@@ -190,7 +198,7 @@ class DeviceReplayBuffer:
             if k > first:
                 self.buf[:k - first].copy_(rows[first:])
         if stream is not None:
-            stream.synchronize()     # the source rows may be overwritten two moves from now
+            _wait(stream)            # the source rows may be overwritten two moves from now
         self.head = (self.head + k) % self.max_entries
         self.n = min(self.max_entries, self.n + k)
 
@@ -248,7 +256,7 @@ class SelfPlay:
             native_gather = self.world > 1 and dist.get_backend(group) == "nccl"
         with torch.cuda.device(games.device):
             self.rec = [torch.zeros((games.n_games, A.REC_STRIDE), dtype=torch.uint8, device="cuda") for _ in range(2)]
-            self.ev_pack = [torch.cuda.Event() for _ in range(2)]
+            self.ev_pack = [torch.cuda.Event(blocking=True) for _ in range(2)]
             self.ev_sent = [None, None]                  # side-stream event behind the last send of each row buffer
             self.side = torch.cuda.Stream()
         self.cnt = E.PinnedArray((2, 2), np.uint32)      # [buffer][rows, overflow flags], written by the device
