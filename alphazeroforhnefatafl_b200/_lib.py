@@ -78,6 +78,7 @@ def lib():
         "tafl_legal_moves_host": (C.c_int, [vp, vp, vp, C.c_uint32, C.c_uint32]),
         "tafl_step": (C.c_int, [vp, vp, vp]),
         "tafl_step_status": (C.c_int, [vp, vp, vp, vp]),
+        "tafl_step_status_restart": (C.c_int, [vp, vp, vp, vp]),
         "tafl_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
         "tafl_host_free": (C.c_int, [vp]),
         "tafl_host_register": (C.c_int, [vp, C.c_size_t]),

@@ -156,11 +156,17 @@ template <class BB, int SP>
 __global__ void __launch_bounds__(STEP_BLOCK)
 k_step_plays(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
              const tafl_play* __restrict__ plays, tafl_play_effects* __restrict__ fx_out,
-             uint8_t* __restrict__ status_out, uint8_t* __restrict__ err_out, HistView hv, HostMirror hm) {
+             uint8_t* __restrict__ status_out, uint8_t* __restrict__ err_out, HistView hv, HostMirror hm,
+             const __grid_constant__ StateWords start_w, uint32_t* __restrict__ restart_episode) {
     const uint32_t g = blockIdx.x * STEP_BLOCK + threadIdx.x;
     if (g < n) {
         const tafl_play pl = plays[g];   // may be the caller's pinned buffer, read over PCIe: issue it first
         tafl_state s = load_state(states + g);
+        if (restart_episode && s.status != TAFL_STATUS_ONGOING) {   // tafl_step_status_restart: Game::new for a game that had ended
+            s = unpack_state(start_w.v[0], start_w.v[1], start_w.v[2], start_w.v[3]);
+            restart_episode[g] += 1u;
+            if (hv.st) { hv.len[g] = 0; hv.floor[g] = 0; }
+        }
         const tafl_state before = s;
         tafl_play_effects fx;
         fx.captures[0] = fx.captures[1] = 0;
@@ -730,7 +736,7 @@ int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_fx)
     if (rc) return rc;
     rc = device_out(e, 1, n, &d_fx);
     if (rc) return rc;
-    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx, nullptr, nullptr, e->hist, HostMirror{})));
+    TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, d_fx, nullptr, nullptr, e->hist, HostMirror{}, state_words(e->start), nullptr)));
     TAFL_LAUNCHED(e);
     if (h_fx) { rc = download(e, h_fx, d_fx, n); if (rc) return rc; }
     return sync_engine(e);
@@ -741,7 +747,14 @@ static void* mapped_alias(const void* h) {
     if (cudaPointerGetAttributes(&a, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
 }
+static int step_status_impl(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err, bool restart);
 int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err) {
+    return step_status_impl(e, h_plays, h_status, h_err, false);
+}
+int tafl_step_status_restart(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err) {
+    return step_status_impl(e, h_plays, h_status, h_err, true);
+}
+static int step_status_impl(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err, bool restart) {
     TAFL_CHECK_E(e);
     if (!h_plays || !h_status) return TAFL_ERR_INVALID_ARG;
     cudaSetDevice(e->device);
@@ -766,7 +779,8 @@ int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status
     rc = device_out(e, 1, n, &d_err);
     if (rc) return rc;
     TAFL_SPEC_DISPATCH(e, (k_step_plays<BB, SP><<<grid_for(n, STEP_BLOCK), STEP_BLOCK, 0, e->stream>>>(cx, e->d_states, n, d_pl, nullptr,
-                                                                                                    e->d_status, d_err, e->hist, hm)));
+                                                                                                    e->d_status, d_err, e->hist, hm,
+                                                                                                    state_words(e->start), restart ? e->d_episode : nullptr)));
     TAFL_LAUNCHED(e);
     if (!hm.status) {
         if ((rc = download(e, h_status, e->d_status, n))) return rc;

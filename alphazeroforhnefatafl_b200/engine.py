@@ -263,16 +263,18 @@ class LockstepGames:
         self._ck(lib().tafl_step(self._h, A.ptr(plays), A.ptr(fx) if want_effects else None))
         return fx
 
-    def game_do_play(self, plays):
+    def game_do_play(self, plays, restart_finished=False):
         """``Game::do_play`` (game/mod.rs:95-101) for every resident game with the reference's return
-        type: (status[n] uint8 packed GameStatus, err[n] uint8 PlayInvalid code)."""
+        type: (status[n] uint8 packed GameStatus, err[n] uint8 PlayInvalid code).  restart_finished: games that
+        had ended are first replaced by new ones, in the same launch (tafl_step_status_restart)."""
         plays = np.ascontiguousarray(plays, A.PLAY_DTYPE)
         assert len(plays) == self.n_games
         if self._pin is None:   # page-locked staging: the kernel reads / writes these in place (tafl_step_status)
             self._pin = (PinnedArray(self.n_games, A.PLAY_DTYPE), PinnedArray(self.n_games, np.uint8), PinnedArray(self.n_games, np.uint8))
         p_pl, p_st, p_er = self._pin
         p_pl.a[:] = plays
-        self._ck(lib().tafl_step_status(self._h, A.ptr(p_pl.a), A.ptr(p_st.a), A.ptr(p_er.a)))
+        fn = lib().tafl_step_status_restart if restart_finished else lib().tafl_step_status
+        self._ck(fn(self._h, A.ptr(p_pl.a), A.ptr(p_st.a), A.ptr(p_er.a)))
         return p_st.a.copy(), p_er.a.copy()
 
     def last_actions(self):

@@ -329,8 +329,9 @@ def run_b200(args):
     # positions of the leg above (untimed: the fused kernel reports the play it chose, tafl_actions_host),
     # with auto-restart, so the sequence holds captures, wins and draws at their natural rate; the timed
     # region replays it with one tafl_step_status call per ply — H2D of that ply's 65 536 plays from
-    # pinned memory, validate + apply on the device, D2H of the status and PlayInvalid bytes — followed
-    # by tafl_reset_finished (asynchronous: what a host does when it sees a finished status: Game::new).
+    # pinned memory, validate + apply on the device, D2H of the status and PlayInvalid bytes; games that had
+    # ended are replaced by new ones in the same launch (tafl_step_status_restart == tafl_reset_finished +
+    # tafl_step_status: what a host does when it sees a finished status, Game::new).
     L = lib()
     e2e_plies = 256
     plays_rec = torch.empty((e2e_plies, n, 4), dtype=torch.uint8).pin_memory()
@@ -346,15 +347,13 @@ def run_b200(args):
     final_rec = g.get_states().tobytes()
     # argument pointers taken once: indexing a torch tensor costs microseconds a compiled host does not pay
     e2e_ptrs = [(plays_rec[p].data_ptr(), st_host[p].data_ptr(), err_host[p].data_ptr()) for p in range(e2e_plies)]
-    step_status, reset_finished, handle = L.tafl_step_status, L.tafl_reset_finished, g.handle
+    step_status, handle = L.tafl_step_status_restart, g.handle
 
     def e2e_round():
         for p_in, p_st, p_err in e2e_ptrs:
-            rc = reset_finished(handle, None)           # games that ended on the previous ply start over (no host sync)
-            if rc == 0:
-                rc = step_status(handle, p_in, p_st, p_err)
+            rc = step_status(handle, p_in, p_st, p_err)   # games that ended on the previous ply start over, then the play
             if rc != 0:
-                raise RuntimeError("tafl_step_status failed: %d" % rc)
+                raise RuntimeError("tafl_step_status_restart failed: %d" % rc)
 
     g.set_states(steady)
     t0 = time.perf_counter()
@@ -413,9 +412,9 @@ def run_b200(args):
                      "kernel_us": kernel_us, "bytes_per_env_step": ENV_BYTES_PER_STEP,
                      "note": "integer-issue bound, not HBM bound: binding_limit carries the ALU-pipe / issue-slot fractions of the committed ncu capture"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 4, "d2h_bytes_per_step": n * 2,
-                "api": "tafl_step_status == Game::do_play(play) -> Result<GameStatus, PlayInvalid> for 65536 resident games: "
+                "api": "tafl_step_status_restart == Game::new for the games that had ended + Game::do_play(play) -> Result<GameStatus, PlayInvalid> for 65536 resident games: "
                        "pinned host plays in, status + PlayInvalid bytes out, one call per ply (the kernel reads / writes the "
-                       "pinned buffers over PCIe itself, bytes per step as listed), then tafl_reset_finished; a recorded seeded "
+                       "pinned buffers over PCIe itself, bytes per step as listed); a recorded seeded "
                        "random-play action sequence over steady-state positions with auto-restart is replayed (checked bit-exact)",
                 "plies_per_round": e2e_plies, "rounds": rounds, "timed_region_s": cx.reduce(e2e_time),
                 "games_ended_in_the_sequence": terminals,

@@ -310,6 +310,11 @@ int tafl_step(tafl_engine* e, const tafl_play* h_plays, tafl_play_effects* h_eff
  * three copy-engine hand-offs (26.5 vs 41.4 us per 65 536-game ply on a B200); pageable buffers are
  * staged through the copy engine.  Same results either way. */
 int tafl_step_status(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err);
+/* tafl_reset_finished + tafl_step_status in ONE launch: a game that had ended before this call is first
+ * replaced by a new one (`Game::new`, game/mod.rs:84-93: start position, episode counter + 1, history
+ * forgotten) and the play is then applied to it.  What a host driving many games does anyway when it
+ * sees a finished status; fusing it saves a launch per ply on the host-buffer path. */
+int tafl_step_status_restart(tafl_engine* e, const tafl_play* h_plays, uint8_t* h_status, uint8_t* h_err);
 /* Page-locked host memory for the HOST-buffer calls, so a host language needs no CUDA binding of its
  * own: tafl_host_alloc returns `bytes` of pinned, device-mapped memory (free with tafl_host_free);
  * tafl_host_register pins an existing allocation in place (e.g. a Rust Vec's buffer) until

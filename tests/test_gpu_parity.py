@@ -403,3 +403,29 @@ def test_gpu_large_boards_vs_oracle(orc, built_lib, width, N):
         bad = wide_random_boards(orc, rng, N - 1, width, 1)
         with pytest.raises(TaflError):
             w.validate_plays(bad, np.zeros(1, A.PLAY_DTYPE))     # side_len mismatch
+
+
+def test_gpu_do_play_with_restart_equals_reset_then_do_play(orc, built_lib):
+    """tafl_step_status_restart == tafl_reset_finished + tafl_step_status, ply for ply, over games that keep ending:
+    states, status / PlayInvalid bytes, and the episode counters the replay records carry."""
+    rules, fen = orc.preset_rules(A.PRESET_BRANDUBH), board_for(orc, A.PRESET_BRANDUBH)
+    n, plies = 512, 160
+    rng = np.random.default_rng(17)
+    with E.LockstepGames(rules, fen, n, 0, 64) as a, E.LockstepGames(rules, fen, n, 0, 64) as b:
+        ended = 0
+        for ply in range(plies):
+            st = a.get_states()
+            fresh = np.repeat(orc.state_from_fen(fen, 64, A.ATTACKER)[1], n)
+            cur = np.where((st["status"] != 0)[:, None], fresh.view(np.uint8).reshape(n, 64), st.view(np.uint8).reshape(n, 64))
+            cur = np.ascontiguousarray(cur).view(A.STATE_DTYPE).reshape(n)      # the positions the plays will meet
+            mv, cnt = orc.by_value(rules, 64).legal_moves_of(cur)
+            pick = mv[np.arange(n), rng.integers(0, 1 << 30, n) % np.maximum(cnt, 1)]
+            plays = E.moves_to_plays(pick, 64)
+            plays["disp"][::37] = 0                                              # a few invalid plays
+            sa, ea = a.game_do_play(plays, restart_finished=True)
+            b.reset_finished()
+            sb, eb = b.game_do_play(plays)
+            assert np.array_equal(sa, sb) and np.array_equal(ea, eb), ply
+            assert a.get_states().tobytes() == b.get_states().tobytes(), ply
+            ended += int((sa != 0).sum())
+        assert ended > n        # every game ended at least once on average: the restart path was exercised
