@@ -97,6 +97,8 @@ def lib():
         "tafl_validate_plays": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
         "tafl_do_plays": (C.c_int, [vp, vp, vp, C.c_uint32, vp, vp]),
         "tafl_legal_moves_of": (C.c_int, [vp, vp, C.c_uint32, vp, vp]),
+        "tafl_legal_moves_of_static": (C.c_int, [vp, vp, C.c_uint32, vp, vp]),
+        "tafl_static_max_games": (C.c_uint32, []),
         "tafl_piece_plays": (C.c_int, [vp, vp, vp, C.c_uint32, vp, vp]),
         "tafl_get_captures": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),
         "tafl_detect_shieldwall": (C.c_int, [vp, vp, vp, C.c_uint32, vp]),

@@ -4,6 +4,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <string>
 #include <vector>
 
 #include "tafl_engine.hpp"
@@ -1189,6 +1191,82 @@ int tafl_side_can_play(tafl_engine* e, const tafl_state* h_st, const uint8_t* h_
     TAFL_WIDTH_DISPATCH(e, (k_bv_can_play<BB><<<grid_for(n, 128), 128, 0, e->stream>>>(cx, d_st, d_sides, n, d_out)));
     TAFL_LAUNCHED(e);
     if ((rc = download(e, h_out, d_out, n))) return rc;
+    return sync_engine(e);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// tafl_legal_moves_of_static: tafl_legal_moves_of without any device allocation
+// ---------------------------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot
+// call cudaMalloc (code under graph capture, tight serving loops, harnesses that forbid it).  The device
+// staging that tafl_legal_moves_of keeps in the engine's grown-on-demand scratch slots (states in, move
+// rows and counts out) lives in ONE file-scope array instead: every GPU that loads the library holds
+// TAFL_STATIC_SCRATCH_BYTES of it until the process exits.  All calls on a device share the array and it keeps
+// the previous call's contents, so the move rows are cleared on the stream before every launch, and two calls
+// that overlap on the GPU (two engines / two streams on one device) race: callers serialise them.
+namespace {
+
+constexpr size_t SS_STATES_OFF = 0;
+constexpr size_t SS_MOVES_OFF = SS_STATES_OFF + (size_t)TAFL_STATIC_MAX_GAMES * sizeof(tafl_state);
+constexpr size_t SS_COUNTS_OFF = SS_MOVES_OFF + (size_t)TAFL_STATIC_MAX_GAMES * TAFL_MAX_MOVES * sizeof(tafl_move);
+constexpr size_t SS_BYTES = SS_COUNTS_OFF + (size_t)TAFL_STATIC_MAX_GAMES * sizeof(uint32_t);
+static_assert(SS_BYTES == TAFL_STATIC_SCRATCH_BYTES, "include/tafl.h states the size of the static scratch");
+static_assert(SS_MOVES_OFF % 256 == 0 && SS_COUNTS_OFF % 256 == 0, "sections stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_static_scratch[SS_BYTES];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: the address a kernel
+// may use comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int SS_MAX_DEVICES = 64;
+std::mutex g_ss_mutex;
+unsigned char* g_ss_ptr[SS_MAX_DEVICES] = {};
+
+int static_scratch_for(tafl_engine* e, unsigned char** out) {
+    if (e->device < 0 || e->device >= SS_MAX_DEVICES) { e->err = "device index beyond the static scratch table"; return TAFL_ERR_UNSUPPORTED; }
+    std::lock_guard<std::mutex> lk(g_ss_mutex);
+    if (!g_ss_ptr[e->device]) {
+        TAFL_CUDA_TRY(e, cudaSetDevice(e->device));
+        void* p = nullptr;
+        TAFL_CUDA_TRY(e, cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) { e->err = "cudaGetSymbolAddress returned a null address for the static scratch"; return TAFL_ERR_CUDA; }
+        g_ss_ptr[e->device] = (unsigned char*)p;
+    }
+    *out = g_ss_ptr[e->device];
+    return TAFL_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+uint32_t tafl_static_max_games(void) { return TAFL_STATIC_MAX_GAMES; }
+
+int tafl_legal_moves_of_static(tafl_engine* e, const tafl_state* h_st, uint32_t n, tafl_move* h_moves, uint32_t* h_counts) {
+    TAFL_CHECK_E(e);
+    if (n > TAFL_STATIC_MAX_GAMES) {
+        e->err = "tafl_legal_moves_of_static: n = " + std::to_string(n) + " states exceed the static scratch (TAFL_STATIC_MAX_GAMES = " +
+                 std::to_string((unsigned)TAFL_STATIC_MAX_GAMES) + "); split the batch or use tafl_legal_moves_of";
+        return TAFL_ERR_CAPACITY;
+    }
+    if (n && (!h_st || !h_moves || !h_counts)) return TAFL_ERR_INVALID_ARG;
+    TAFL_CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc = check_side_len(e, h_st, n);
+    if (rc) return rc;
+    if (!n) return TAFL_OK;
+    unsigned char* base;
+    if ((rc = static_scratch_for(e, &base))) return rc;
+    tafl_state* d_st = (tafl_state*)(base + SS_STATES_OFF);
+    tafl_move* d_mv = (tafl_move*)(base + SS_MOVES_OFF);
+    uint32_t* d_cnt = (uint32_t*)(base + SS_COUNTS_OFF);
+    const size_t mv_bytes = (size_t)n * TAFL_MAX_MOVES * sizeof(tafl_move);
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(d_st, h_st, (size_t)n * sizeof(tafl_state), cudaMemcpyHostToDevice, e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(d_mv, 0, mv_bytes, e->stream));          // rows past a game's count read as zero
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(d_cnt, 0, (size_t)n * sizeof(uint32_t), e->stream));
+    if ((rc = legal_moves_enqueue(e, d_st, n, d_mv, d_cnt))) return rc;
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_moves, d_mv, mv_bytes, cudaMemcpyDeviceToHost, e->stream));
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_counts, d_cnt, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
     return sync_engine(e);
 }
 

@@ -498,6 +498,15 @@ class LockstepGames:
         self._ck(lib().tafl_legal_moves_of(self._h, A.ptr(states), len(states), A.ptr(moves), A.ptr(counts)))
         return moves, counts
 
+    def legal_moves_of_static(self, states):
+        """legal_moves_of through tafl_legal_moves_of_static: device staging in the library's static array, no device
+        allocation; at most lib().tafl_static_max_games() states per call (TAFL_ERR_CAPACITY beyond)"""
+        states = np.ascontiguousarray(states, A.STATE_DTYPE)
+        moves = np.zeros((len(states), A.MAX_MOVES), np.uint16)
+        counts = np.zeros(len(states), np.uint32)
+        self._ck(lib().tafl_legal_moves_of_static(self._h, A.ptr(states), len(states), A.ptr(moves), A.ptr(counts)))
+        return moves, counts
+
     def iter_plays(self, states, tiles_rc):
         states = np.ascontiguousarray(states, A.STATE_DTYPE)
         tiles_rc = np.ascontiguousarray(tiles_rc, np.uint8)

@@ -407,6 +407,21 @@ int tafl_do_plays(tafl_engine* e, const tafl_state* h_states, const tafl_play* h
 /* get_all_possible_moves (game/main.rs:33-43) for arbitrary states */
 int tafl_legal_moves_of(tafl_engine* e, const tafl_state* h_states, uint32_t n,
                         tafl_move* h_moves /* [n][TAFL_MAX_MOVES] */, uint32_t* h_counts);
+/* tafl_legal_moves_of with NO device allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments, same results (rows of
+ * h_moves past h_counts[i] are zero).  The device staging (states in, move rows and counts out) is a
+ * file-scope `static __device__` array of TAFL_STATIC_SCRATCH_BYTES that every GPU which loads the
+ * library holds until the process exits; the call makes no cudaMalloc / cudaFree / allocating
+ * library call.  n > TAFL_STATIC_MAX_GAMES -> TAFL_ERR_CAPACITY with a message in tafl_last_error.
+ * All calls on one device share the array: calls that overlap on the GPU (two engines or two
+ * threads on the same device) race, so callers serialise them. */
+#define TAFL_STATIC_MAX_GAMES 2048u
+#define TAFL_STATIC_SCRATCH_BYTES \
+    (TAFL_STATIC_MAX_GAMES * (sizeof(tafl_state) + TAFL_MAX_MOVES * sizeof(tafl_move) + sizeof(uint32_t)))
+uint32_t tafl_static_max_games(void);
+int tafl_legal_moves_of_static(tafl_engine* e, const tafl_state* h_states, uint32_t n,
+                               tafl_move* h_moves /* [n][TAFL_MAX_MOVES] */, uint32_t* h_counts);
 /* GameLogic::iter_plays(tile) (logic.rs:850-856, play.rs:139-226): plays of the piece on one
  * tile (either side); h_counts[i] = -1 mirrors Err(BoardError::NoPiece) */
 int tafl_piece_plays(tafl_engine* e, const tafl_state* h_states, const uint8_t* h_tiles_rc,
