@@ -460,10 +460,12 @@ public:
     int width() const { return width_; }
     tafl_engine* handle() const { return e_.get(); }
 
-    std::vector<Result<GameStatus, PlayInvalid>> do_play(const std::vector<Play>& plays) {
+    // restart_finished: a game whose status is Over is first replaced by a new one (Game::new, what a host does when it
+    // sees a finished status) and the play is applied to that — same launch (tafl_step_status_restart)
+    std::vector<Result<GameStatus, PlayInvalid>> do_play(const std::vector<Play>& plays, bool restart_finished = false) {
         if (plays.size() != n_) throw std::logic_error("Games::do_play: one Play per game");
         for (uint32_t i = 0; i < n_; ++i) h_plays_[i] = plays[i].to_c();
-        detail::check(tafl_step_status(e_.get(), h_plays_, h_status_, h_err_), e_.get(), "do_play");
+        detail::check((restart_finished ? tafl_step_status_restart : tafl_step_status)(e_.get(), h_plays_, h_status_, h_err_), e_.get(), "do_play");
         std::vector<Result<GameStatus, PlayInvalid>> out;
         out.reserve(n_);
         for (uint32_t i = 0; i < n_; ++i) {
@@ -471,6 +473,11 @@ public:
             else out.push_back(GameStatus{h_status_[i]});
         }
         return out;
+    }
+    uint32_t restart_finished() {   // Game::new for every game whose status is Over; returns how many
+        uint32_t n = 0;
+        detail::check(tafl_reset_finished(e_.get(), &n), e_.get(), "restart_finished");
+        return n;
     }
     void undo_last_play(const std::vector<uint8_t>* mask = nullptr) {   // game/mod.rs:103-108
         detail::check(tafl_undo_last_play(e_.get(), mask ? mask->data() : nullptr), e_.get(), "undo_last_play");

@@ -112,6 +112,11 @@ static int selftest_game() {
     if (!res[0].is_ok() || !res[1].is_err() || !res[2].is_ok()) return 17;
     b.step_random(3, 40);
     if (b.stats().steps != 120) return 18;
+    if (b.restart_finished() > 3) return 19;   // Game::new for finished games: every game is Ongoing afterwards
+    auto lp2 = b.legal_plays();
+    if (lp2[0].empty() || lp2[1].empty() || lp2[2].empty()) return 20;
+    auto res2 = b.do_play({lp2[0][0], lp2[1][0], lp2[2][0]}, /*restart_finished=*/true);
+    if (!res2[0].is_ok() || !res2[1].is_ok() || !res2[2].is_ok()) return 21;
     return 0;
 }
 
