@@ -685,7 +685,12 @@ TAFL_HD Encl<BB> find_enclosure(const Ctx<BB, SP>& cx, const Pos<BB>& p, int r, 
     if (!reg.any()) return e;
     for (int it = 0; it < BB::BITS; ++it) {
         if ((reg & stop).any()) return e;
-        BB grown = reg | (dilate4(cx, reg) & fillable);
+        const BB around = dilate4(cx, reg);
+        // a piece of neither set beside the region means None whatever the rest of the fill finds (the region only
+        // grows): leave at the first contact instead of flooding the open board first (the exit-fort test of a king
+        // on the edge in an ordinary position: an attacker is met within a step or two)
+        if ((around & neither).any()) return e;
+        BB grown = reg | (around & fillable);
         if (grown == reg) break;
         reg = grown;
     }
@@ -709,6 +714,7 @@ template <class BB, int SP>
 TAFL_HD bool enclosure_win_possible(const Ctx<BB, SP>& cx, const Pos<BB>& p, bool abort_on_edge) {
     const BB fillable = (cx.board & ~p.occ()) | p.def;
     const BB stop = (abort_on_edge ? cx.edge : BB::zero()) | cx.corners;
+#if !defined(TAFL_ENCL_TWO_SIDED)
     BB reg = p.def;
     bool escaped = false;   // single exit: the lanes of a warp leave the loop together
     for (int it = 0; it < BB::BITS; ++it) {
@@ -719,6 +725,24 @@ TAFL_HD bool enclosure_win_possible(const Ctx<BB, SP>& cx, const Pos<BB>& p, boo
         reg = grown;
     }
     return !escaped;
+#else
+    // Tried (r02n): reachability is symmetric, so the fill can run from both ends — from the defenders and from the abort
+    // tiles — until the fronts meet: half the trips for the warp's slowest lane, two independent dilations per trip.
+    // Measured 10.96 us per ply against 10.79 us for the one-sided fill above; kept for reference only.
+    BB a = p.def, b = stop & fillable;
+    bool escaped = false;   // single exit: the lanes of a warp leave the loop together
+    for (int it = 0; it < BB::BITS; ++it) {
+        escaped = (a & b).any();
+        if (escaped) break;
+        const BB ga = a | (dilate4(cx, a) & fillable), gb = b | (dilate4(cx, b) & fillable);
+        escaped = (ga & b).any();   // fronts one step apart: no second trip for that
+        if (escaped) break;
+        if (ga == a || gb == b) break;   // one side is complete without having met the other
+        a = ga;
+        b = gb;
+    }
+    return !escaped;
+#endif
 }
 // enclosure_secure (logic.rs:408-463)
 template <class BB, int SP>
@@ -771,7 +795,9 @@ TAFL_HD bool detect_exit_fort(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
     // enclosed = PieceSet::from(King), enclosing = PieceSet::from(Defender); attackers are "neither"
     // find_enclosure -> king has an empty neighbour -> enclosure_secure (logic.rs:580-600); the empty-
     // neighbour test has no side effects, so it is taken first and the fill runs out of line
-    if (!(dilate4(cx, p.kbit) & ~p.occ()).any()) return false;
+    const BB beside = dilate4(cx, p.kbit);
+    if (!(beside & ~p.occ()).any()) return false;
+    if ((beside & p.att).any()) return false;   // an attacker beside the king is beside the region: find_enclosure is None
     return exit_fort_full(cx, p);
 }
 
