@@ -240,6 +240,16 @@ k_step_moves(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ st
     if (status_out) status_out[g] = s.status;
 }
 
+// Chaining pays once a grid has more than four 64-thread CTAs per SM (measured: 40 960 games 10.0 -> 7.6 us per ply, 65 536
+// 10.3 -> 8.95, 196 608 24.4 -> 22.7; below that the token hand-off costs more than the tail it hides: 32 768 games 6.8 -> 7.4)
+// and stops paying when the grid is many waves deep (524 288 games: 59.3 -> 60.1)
+constexpr uint32_t CHAIN_MIN_CTAS_PER_SM = 4, CHAIN_MAX_CTAS_PER_SM = 28;
+#if !defined(TAFL_CHAIN_SLEEP)
+#define TAFL_CHAIN_SLEEP 40
+#endif
+constexpr int CHAIN_POS_BITS = 12;                    // nodes per graph that can be chained (token = launch sequence | node)
+constexpr uint32_t CHAIN_SPIN_LIMIT = 1u << 22;       // ~ 0.3 s of polling: a lost token raises the time-out word instead of hanging
+
 // The fused random-playout step (K4): count -> pick -> select -> apply -> outcome, `steps`
 // plies per launch with the state held in registers in between.  BYVAL (tafl_step_random_host): the
 // states come from the staged copy of the caller's array (`src`); a row whose side_len is not the
@@ -251,22 +261,51 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
               uint32_t steps, int auto_reset, DevStats* __restrict__ stats, uint32_t* __restrict__ actions,
               const unsigned long long* __restrict__ ply_base, const tafl_state* __restrict__ src = nullptr,
-              uint32_t* __restrict__ rejected = nullptr) {
+              uint32_t* __restrict__ rejected = nullptr, uint32_t* chain = nullptr) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t c_steps = 0, c_legal = 0, c_caps = 0;
-    // Programmatic dependent launch (no-ops for a plain launch): wait for the previous ply's grid
-    // before touching its states, then let the next ply's grid start filling free CTA slots so its
-    // launch latency and ramp overlap this grid's tail.
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    asm volatile("griddepcontrol.launch_dependents;");
+    // CTA chaining (graph nodes only, `chain` = one word per CTA + a time-out word): game g at ply i+1 needs nothing
+    // but game g at ply i, i.e. CTA b of this node needs CTA b of the previous node and no other.  A node of the
+    // chain therefore lets its successor launch at once, waits for the token its own predecessor CTA publishes
+    // after storing its states (release / acquire at GPU scope) instead of for the whole previous grid, and
+    // publishes its own.  The time of a grid is the time of its slowest warp (a rare long path: a fill that runs to
+    // the end, a finished game); chained, the next ply's CTAs run in the slots the early finishers leave.
+    const bool chained = SINGLE && chain != nullptr;
+    const uint32_t chain_pos = (uint32_t)ply0;          // node index inside the graph
+    uint32_t chain_seq = 0;
+    if (chained && chain_pos > 0) {
+        asm volatile("griddepcontrol.launch_dependents;");
+    } else {
+        // Programmatic dependent launch (no-ops for a plain launch): wait for the previous ply's grid
+        // before touching its states, then let the next ply's grid start filling free CTA slots so its
+        // launch latency and ramp overlap this grid's tail.
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;");
+    }
     if (ply_base) ply0 += *ply_base;
+    if (chained) {
+        chain_seq = (uint32_t)ply_base[1] << CHAIN_POS_BITS;
+        if (chain_pos > 0) {
+            if (threadIdx.x == 0) {
+                const uint32_t want = chain_seq | chain_pos;
+                uint32_t got, spins = 0;
+                while (true) {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(got) : "l"(chain + blockIdx.x) : "memory");
+                    if (got == want) break;
+                    if (++spins > CHAIN_SPIN_LIMIT) { atomicOr(chain + gridDim.x, 1u); break; }   // reported by the host, never a hang
+                    if (TAFL_CHAIN_SLEEP) __nanosleep(TAFL_CHAIN_SLEEP);
+                }
+            }
+            __syncthreads();
+        }
+    }
     bool live = g < n;
     if (BYVAL && live && src[g].side_len != (uint8_t)cx.n()) {
         atomicOr(rejected, 1u);
         live = false;
     }
     if (live) {
-        tafl_state s = load_state((BYVAL ? src : states) + g);
+        tafl_state s = chained ? load_state_cg(states + g) : load_state((BYVAL ? src : states) + g);
         uint32_t act = 0;   // tafl_action of the last ply of this launch
         // one ply; false = this game stops stepping (finished, no auto-reset)
         auto ply = [&](uint32_t i) {
@@ -296,6 +335,15 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
         }
         store_state(states + g, s);
         actions[g] = act;
+    }
+    if (chained) {
+        __syncthreads();                               // every state of this CTA is stored
+        if (threadIdx.x == 0) {
+            const uint32_t token = chain_seq | (chain_pos + 1u);   // release: ordered after the barrier, hence after every thread's stores
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(chain + blockIdx.x), "r"(token) : "memory");
+        }
+        // completion order of the nodes stays the launch order: this grid does not end before its predecessor has
+        if (chain_pos > 0) asm volatile("griddepcontrol.wait;" ::: "memory");
     }
     // warp-level reduction of the dense counters (REDUX), one atomic per warp
     c_steps = __reduce_add_sync(0xFFFFFFFFu, c_steps);
@@ -451,6 +499,16 @@ void hist_forget_all(tafl_engine* e) {
 
 static int sync_engine(tafl_engine* e) {
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    if (e->d_chain && e->chain_dirty) {   // a chained step graph ran since the last look at its time-out word
+        uint32_t lost = 0;
+        TAFL_CUDA_TRY(e, cudaMemcpy(&lost, e->d_chain + e->chain_ctas, sizeof(lost), cudaMemcpyDeviceToHost));
+        e->chain_dirty = false;
+        if (lost) {
+            cudaMemset(e->d_chain + e->chain_ctas, 0, sizeof(uint32_t));
+            e->err = "chained step graph: a CTA never saw its predecessor's token (TAFL_STEP_CHAIN=0 disables chaining); states are not valid";
+            return TAFL_ERR_CUDA;
+        }
+    }
     return TAFL_OK;
 }
 static int check_side_len(tafl_engine* e, const tafl_state* st, uint32_t n) {
@@ -543,6 +601,7 @@ int tafl_engine_create(const tafl_rules* rules, const char* start_fen, int width
     if (const char* v = std::getenv("TAFL_STEP_GRAPH")) e->step_graph_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_STEP_SINGLE")) e->step_single = std::atoi(v);
     if (const char* v = std::getenv("TAFL_STEP_PDL")) e->step_pdl_on = std::atoi(v);
+    if (const char* v = std::getenv("TAFL_STEP_CHAIN")) e->step_chain_on = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_CHUNKS")) e->host_chunks = std::atoi(v);
     if (const char* v = std::getenv("TAFL_HOST_IO")) e->host_io = std::atoi(v);
     if (const char* v = std::getenv("TAFL_MCTS_MINB")) e->mcts_minb = std::atoi(v);
@@ -576,7 +635,7 @@ int tafl_engine_destroy(tafl_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     mcts_free(e);
     cudaFree(e->d_states); cudaFree(e->d_moves); cudaFree(e->d_counts); cudaFree(e->d_status); cudaFree(e->d_actions);
-    cudaFree(e->d_stats); cudaFree(e->d_checksum); cudaFree(e->d_ply); cudaFree(e->d_episode);
+    cudaFree(e->d_stats); cudaFree(e->d_checksum); cudaFree(e->d_ply); cudaFree(e->d_chain); cudaFree(e->d_episode);
     cudaFree(e->hist.st); cudaFree(e->hist.rec); cudaFree(e->hist.len); cudaFree(e->hist.floor);
     if (e->step_graph) cudaGraphExecDestroy(e->step_graph);
     if (e->ev_block) cudaEventDestroy(e->ev_block);
@@ -897,7 +956,8 @@ uint64_t tafl_random_ply(const tafl_engine* e) { return e ? e->ply : 0; }
 // enqueue k_step_random over games [first, first + n) on `stream`: `steps` plies starting at RNG ply `ply0`
 // (+ *d_ply_base when given); pdl = launch with the programmatic-stream-serialization attribute
 static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t first, uint32_t n, uint64_t seed, uint64_t ply0,
-                              uint32_t steps, int auto_reset, const unsigned long long* d_ply_base = nullptr, bool pdl = false) {
+                              uint32_t steps, int auto_reset, const unsigned long long* d_ply_base = nullptr, bool pdl = false,
+                              uint32_t* d_chain = nullptr) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid_for(n, STEP_BLOCK));
     cfg.blockDim = dim3(STEP_BLOCK);
@@ -913,7 +973,7 @@ static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t firs
     TAFL_SPEC_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, k_step_random<BB, SP, MINB, false, SINGLE>, cx, e->d_states + first, n, \
                                                      state_words(e->start), seed, e->game_id_base + first, ply0, steps, \
                                                      auto_reset, e->d_stats, e->d_actions + first, d_ply_base,         \
-                                                     (const tafl_state*)nullptr, (uint32_t*)nullptr)))
+                                                     (const tafl_state*)nullptr, (uint32_t*)nullptr, d_chain)))
 #define TAFL_STEP_LAUNCH(MINB)                                     \
     do {                                                           \
         if (steps == 1 && e->step_single && MINB == 8) TAFL_STEP_LAUNCH_(8, true); \
@@ -937,16 +997,30 @@ static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t firs
 // programmatic edges (captured PDL launches).  Re-captured when (n_steps, seed, flags) change.
 static int step_graph_launch(tafl_engine* e, uint64_t seed, uint32_t n_steps, int auto_reset) {
     auto& k = e->step_graph_key;
+    // CTA chaining needs the single-ply kernel, programmatic edges and a node index that fits the token
+    // ... and pays when the grid is about one wave of CTAs (TAFL_STEP_CHAIN: 0 off, 1 by batch size, 2 always)
+    const uint32_t n_ctas = grid_for(e->n_games, STEP_BLOCK);
+    const bool chain_fits = e->step_chain_on == 2 || (n_ctas > CHAIN_MIN_CTAS_PER_SM * (uint32_t)e->sm_count && n_ctas <= CHAIN_MAX_CTAS_PER_SM * (uint32_t)e->sm_count);
+    const int chain = e->step_chain_on && chain_fits && e->step_pdl_on && e->step_single && e->step_minb == 8 && n_steps < (1u << CHAIN_POS_BITS);
     if (!e->step_graph || k.seed != seed || k.steps != n_steps || k.auto_reset != auto_reset || k.minb != e->step_minb ||
-        k.spec != e->spec || k.gid_base != e->game_id_base) {
+        k.spec != e->spec || k.gid_base != e->game_id_base || k.chain != chain) {
         if (e->step_graph) { cudaGraphExecDestroy(e->step_graph); e->step_graph = nullptr; }
-        if (!e->d_ply) TAFL_CUDA_TRY(e, cudaMalloc(&e->d_ply, sizeof(unsigned long long)));
+        if (!e->d_ply) TAFL_CUDA_TRY(e, cudaMalloc(&e->d_ply, 2 * sizeof(unsigned long long)));
+        const uint32_t ctas = grid_for(e->n_games, STEP_BLOCK);
+        if (chain && (!e->d_chain || e->chain_ctas != ctas)) {
+            if (e->d_chain) cudaFree(e->d_chain);
+            e->d_chain = nullptr;
+            TAFL_CUDA_TRY(e, cudaMalloc(&e->d_chain, ((size_t)ctas + 1) * sizeof(uint32_t)));
+            TAFL_CUDA_TRY(e, cudaMemsetAsync(e->d_chain, 0, ((size_t)ctas + 1) * sizeof(uint32_t), e->stream));
+            e->chain_ctas = ctas;
+        }
         const uint64_t before = e->launches;
         cudaGraph_t graph = nullptr;
         TAFL_CUDA_TRY(e, cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
         int rc = TAFL_OK;
         for (uint32_t i = 0; i < n_steps && rc == TAFL_OK; ++i)
-            rc = launch_step_random(e, e->stream, 0, e->n_games, seed, i, 1, auto_reset, e->d_ply, i > 0 && e->step_pdl_on);
+            rc = launch_step_random(e, e->stream, 0, e->n_games, seed, i, 1, auto_reset, e->d_ply, i > 0 && e->step_pdl_on,
+                                    chain ? e->d_chain : nullptr);
         cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
         e->launches = before;   // capturing launched nothing
         if (rc != TAFL_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -955,10 +1029,12 @@ static int step_graph_launch(tafl_engine* e, uint64_t seed, uint32_t n_steps, in
         cudaGraphDestroy(graph);
         TAFL_CUDA_TRY(e, ce);
         k.seed = seed; k.steps = n_steps; k.auto_reset = auto_reset; k.minb = e->step_minb; k.spec = e->spec; k.gid_base = e->game_id_base;
+        k.chain = chain;
     }
-    const unsigned long long ply = e->ply;
-    TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_ply, &ply, sizeof(ply), cudaMemcpyHostToDevice, e->stream));   // pageable: staged at call time
+    const unsigned long long ply[2] = {e->ply, ++e->chain_seq};   // the sequence number makes every token of every launch distinct
+    TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_ply, ply, sizeof(ply), cudaMemcpyHostToDevice, e->stream));   // pageable: staged at call time
     TAFL_CUDA_TRY(e, cudaGraphLaunch(e->step_graph, e->stream));
+    e->chain_dirty = chain != 0;
     e->launches += n_steps;
     e->ply += n_steps;
     return TAFL_OK;

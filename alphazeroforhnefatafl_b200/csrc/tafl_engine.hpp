@@ -72,8 +72,13 @@ struct tafl_engine {
     int step_graph_on = 1;             // TAFL_STEP_GRAPH=0 falls back to plain launches
     int step_pdl_on = 1;               // TAFL_STEP_PDL=0: plain (full-serialisation) edges in the graph
     cudaGraphExec_t step_graph = nullptr;
-    struct { uint64_t seed = 0, gid_base = 0; uint32_t steps = 0; int auto_reset = 0, minb = 0, spec = 0; } step_graph_key;
-    unsigned long long* d_ply = nullptr;   // RNG ply of the first node of the graph (copied before each launch)
+    struct { uint64_t seed = 0, gid_base = 0; uint32_t steps = 0; int auto_reset = 0, minb = 0, spec = 0, chain = 0; } step_graph_key;
+    unsigned long long* d_ply = nullptr;   // [2]: RNG ply of the first node of the graph, graph-launch sequence number (copied before each launch)
+    int step_chain_on = 1;             // TAFL_STEP_CHAIN=0: every node waits for the whole previous grid (griddepcontrol.wait)
+    uint32_t* d_chain = nullptr;       // [CTAs + 1] token per CTA of the chained step graph, then the time-out word
+    uint32_t chain_ctas = 0;
+    bool chain_dirty = false;
+    unsigned long long chain_seq = 0;  // graph launches so far
     // scratch for the by-value batch API (grown on demand)
     void* d_scratch[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[7] = {0, 0, 0, 0, 0, 0, 0};
@@ -161,6 +166,11 @@ __device__ __forceinline__ tafl_state unpack_state(const uint4 a, const uint4 d,
 __device__ __forceinline__ tafl_state load_state(const tafl_state* p) {
     const uint4* q = reinterpret_cast<const uint4*>(p);
     return unpack_state(q[0], q[1], q[2], q[3]);
+}
+// the same through L2 only (ld.global.cg): for states another CTA of a still-running grid has just published
+__device__ __forceinline__ tafl_state load_state_cg(const tafl_state* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    return unpack_state(__ldcg(q), __ldcg(q + 1), __ldcg(q + 2), __ldcg(q + 3));
 }
 __device__ __forceinline__ void store_state(tafl_state* p, const tafl_state& s) {
     uint4* q = reinterpret_cast<uint4*>(p);

@@ -344,6 +344,37 @@ def test_gpu_graph_pdl_stepping_equals_plain_launches(orc, built_lib, monkeypatc
     assert got.tobytes() == exp.tobytes()
 
 
+def test_gpu_chained_step_graph_equals_whole_grid_dependencies(orc, built_lib, monkeypatch):
+    """The step graph with CTA-to-CTA tokens (TAFL_STEP_CHAIN; default for grids of about one wave, forced here with 2)
+    == the same graph with whole-grid dependencies == plain launches == the oracle: states, statistics and the
+    actions of the last ply, over several graph launches, re-captures and a batch that is not a whole number of CTAs."""
+    rules, fen = orc.preset_rules(A.PRESET_COPENHAGEN), board_for(orc, A.PRESET_COPENHAGEN)
+    for n, plan in ((65536 + 17, [(5, 64), (5, 64), (7, 33), (7, 64)]), (3000, [(5, 64), (5, 64), (9, 17), (9, 40)])):
+        finals = {}
+        for mode, env in (("chained", {"TAFL_STEP_CHAIN": "2"}), ("grid", {"TAFL_STEP_CHAIN": "0"}), ("plain", {"TAFL_STEP_GRAPH": "0"})):
+            for k in ("TAFL_STEP_CHAIN", "TAFL_STEP_GRAPH"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            with E.LockstepGames(rules, fen, n, 0, 128) as g:
+                g.set_game_id_base(77)
+                for seed, steps in plan:
+                    g.step_random(seed, steps, steps_per_launch=1)
+                moves, status, stepped = g.last_actions()
+                finals[mode] = (g.get_states().tobytes(), g.stats().as_dict(), moves.tobytes(), status.tobytes(), g.launches)
+        assert finals["chained"] == finals["grid"] == finals["plain"], n
+    for k in ("TAFL_STEP_CHAIN", "TAFL_STEP_GRAPH"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("TAFL_STEP_CHAIN", "2")
+    with E.LockstepGames(rules, fen, 3000, 0, 128) as g:
+        g.set_game_id_base(77)
+        g.step_random(5, 64, steps_per_launch=1)
+        g.step_random(5, 64, steps_per_launch=1)
+        got = g.get_states()
+    exp, _ = orc.random_playout(rules, fen, 128, 5, 3000, 128, game_id_base=77, n_threads=8)
+    assert got.tobytes() == exp.tobytes()
+
+
 @pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS[:3])
 def test_gpu_legal_move_kernels_agree(orc, built_lib, monkeypatch, name, preset, width):
     """get_all_possible_moves three ways — thread per game (TAFL_LM_G=1) and the warp-cooperative kernel with 8 and 16
