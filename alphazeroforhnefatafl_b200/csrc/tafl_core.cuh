@@ -441,6 +441,45 @@ TAFL_HD int gen_moves(const Ctx<BB, SP>& cx, const ST& st, tafl_move* out, int c
 }
 
 // side_can_play (logic.rs:837-846): does any piece of the side have a legal play?
+// Timing-only builds (scripts/gpu_ablate.sh, build.py -DTAFL_ABL_<BLOCK>): one block of a ply switched off, to read what it
+// costs in TIME — the instruction counts do not say (profiles/sweeps/r02n_step_ablation.txt).  Results are wrong by construction.
+#define TAFL_ABL_ENCL_ON 1
+#define TAFL_ABL_EXITFORT_ON 1
+#define TAFL_ABL_CANPLAY_ON 1
+#define TAFL_ABL_SW_ON 1
+#define TAFL_ABL_REP_ON 1
+#if defined(TAFL_ABL_ENCL)
+#undef TAFL_ABL_ENCL_ON
+#define TAFL_ABL_ENCL_ON 0
+#endif
+#if defined(TAFL_ABL_EXITFORT)
+#undef TAFL_ABL_EXITFORT_ON
+#define TAFL_ABL_EXITFORT_ON 0
+#endif
+#if defined(TAFL_ABL_CANPLAY)
+#undef TAFL_ABL_CANPLAY_ON
+#define TAFL_ABL_CANPLAY_ON 0
+#endif
+#if defined(TAFL_ABL_SW)
+#undef TAFL_ABL_SW_ON
+#define TAFL_ABL_SW_ON 0
+#endif
+#if defined(TAFL_ABL_REP)
+#undef TAFL_ABL_REP_ON
+#define TAFL_ABL_REP_ON 0
+#endif
+#define TAFL_ABL_KING_ON 1
+#define TAFL_ABL_CAPS_ON 1
+#if defined(TAFL_ABL_KING)
+#undef TAFL_ABL_KING_ON
+#define TAFL_ABL_KING_ON 0
+#endif
+#if defined(TAFL_ABL_CAPS)
+#undef TAFL_ABL_CAPS_ON
+#define TAFL_ABL_CAPS_ON 0
+#endif
+#define TAFL_ABL_KEEP(B) (TAFL_ABL_##B##_ON != 0)
+
 template <class BB, int SP>
 TAFL_HD bool side_can_play(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side) {
     BB empty = cx.board & ~p.occ();
@@ -450,7 +489,11 @@ TAFL_HD bool side_can_play(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def_side
     {
         const int ks = def_side ? KIND_DS : KIND_AS;
         const BB srcS = def_side ? p.dsold() : p.att;
-        if ((dilate4(cx, srcS) & empty & ~cx.dest_block[ks]).any()) return true;
+        const BB free = empty & ~cx.dest_block[ks];
+#if !defined(TAFL_CANPLAY_NO_SHORTCUT)
+        if ((step_right(cx, srcS) & free).any()) return true;   // some soldier can step one tile to the right: nearly always
+#endif
+        if ((dilate4(cx, srcS) & free).any()) return true;
         if (def_side && (dilate4(cx, p.king()) & empty & ~cx.dest_block[KIND_K]).any()) return true;
     }
     bool any = false;
@@ -519,7 +562,7 @@ TAFL_COLD bool shieldwall_walk(const Ctx<BB, SP>& cx, const Pos<BB>& p, int move
 template <class BB, int SP>
 TAFL_HD bool detect_shieldwall(const Ctx<BB, SP>& cx, const Pos<BB>& p, int mover_def, int to_r, int to_c, BB* caps) {
     *caps = BB::zero();
-    if (!cx.r_shieldwall_enabled()) return false;
+    if (!TAFL_ABL_KEEP(SW) || !cx.r_shieldwall_enabled()) return false;
     const int N = cx.n();
     if (to_r < 0 || to_c < 0 || to_r >= N || to_c >= N) return false;
     const BB own = p.side(mover_def), opp = p.side(!mover_def);
@@ -577,7 +620,7 @@ TAFL_HD BB get_captures(const Ctx<BB, SP>& cx, const Pos<BB>& p, int piece_def, 
     BB caps = BB::zero();
     const int N = cx.n();
     const bool to_in = to_r >= 0 && to_c >= 0 && to_r < N && to_c < N;
-    if (to_in && (piece_kind != KIND_K || cx.f_king_captures())) {
+    if (TAFL_ABL_KEEP(CAPS) && to_in && (piece_kind != KIND_K || cx.f_king_captures())) {
         const BB tob = BB::bit(idx_of<BB>(to_r, to_c));
         const BB opp = p.side(!piece_def);
         const BB kingb = p.king();
@@ -638,7 +681,16 @@ TAFL_HD BB get_captures(const Ctx<BB, SP>& cx, const Pos<BB>& p, int piece_def, 
             if (taken) caps = caps | n;
         }
     }
+    // A shield wall starts with an enemy piece on the edge tile next to `to` (the first tile dir_sw_search looks at must be
+    // a pinned enemy, logic.rs:485-522): one uniform test for every lane, so that only the few with such a neighbour enter
+    // the edge case analysis below (a quarter of all moves land on an edge)
     BB walled;
+#if !defined(TAFL_SW_NO_QUICK_REJECT)
+    if (to_in && cx.r_shieldwall_enabled()) {
+        const BB tob = BB::bit(idx_of<BB>(to_r, to_c));
+        if (!(tob & cx.edge).any() || !(dilate4(cx, tob) & cx.edge & p.side(!mover_def)).any()) return caps;
+    }
+#endif
     if (detect_shieldwall(cx, p, mover_def, to_r, to_c, &walled)) caps = caps | walled;  // logic.rs:691-696
     return caps;
 }
@@ -786,6 +838,29 @@ TAFL_COLD bool exit_fort_full(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
     return enclosure_secure(cx, p, e, true, false);
 }
 
+// Exact pre-filter for the exit-fort test.  find_enclosure(king; enclosed = King, enclosing = defenders, abort on corner) is
+// None when the king's region — the empty tiles connected to the king's tile — holds a corner or touches an attacker
+// (a piece of neither set), i.e. when it holds a VOID tile: an empty corner or an empty tile beside an attacker.  On an
+// ordinary board attackers are everywhere, so a fill from the void tiles meets the fill from the king within a step
+// or two, where the fill from the king alone needs as many steps as the open area is wide.  Both fills run through
+// empty tiles only; when either is complete without having met the other they never meet.
+template <class BB, int SP>
+TAFL_HD bool exit_fort_possible(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
+    const BB empty = cx.board & ~p.occ();
+    BB k = p.kbit;
+    BB v = (dilate4(cx, p.att) | cx.corners) & (empty | p.kbit);
+    bool voided = false;   // single exit: the lanes of a warp leave the loop together
+    for (int it = 0; it < BB::BITS; ++it) {
+        voided = (k & v).any();
+        if (voided) break;
+        const BB gk = k | (dilate4(cx, k) & empty), gv = v | (dilate4(cx, v) & empty);
+        if (gk == k || gv == v) break;
+        k = gk;
+        v = gv;
+    }
+    return !voided;
+}
+
 // detect_exit_fort (logic.rs:572-601)
 template <class BB, int SP>
 TAFL_HD bool detect_exit_fort(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
@@ -798,6 +873,9 @@ TAFL_HD bool detect_exit_fort(const Ctx<BB, SP>& cx, const Pos<BB>& p) {
     const BB beside = dilate4(cx, p.kbit);
     if (!(beside & ~p.occ()).any()) return false;
     if ((beside & p.att).any()) return false;   // an attacker beside the king is beside the region: find_enclosure is None
+#if !defined(TAFL_EXITFORT_NO_PREFILTER)
+    if (!exit_fort_possible(cx, p)) return false;
+#endif
     return exit_fort_full(cx, p);
 }
 
@@ -853,7 +931,7 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const ST& 
         if ((caps & p.kbit).any()) {
             st = TAFL_STATUS_WIN(TAFL_WIN_KING_CAPTURED, 0);
             done = true;
-        } else if (cx.r_enclosure_win() != TAFL_ENCL_NONE &&
+        } else if (TAFL_ABL_KEEP(ENCL) && cx.r_enclosure_win() != TAFL_ENCL_NONE &&
                    enclosure_win_possible(cx, p, cx.r_enclosure_win() == TAFL_ENCL_WITHOUT_EDGE_ACCESS)) {
             if (enclosure_win_full(cx, p)) {
                 st = TAFL_STATUS_WIN(TAFL_WIN_ENCLOSED, 0);
@@ -870,12 +948,12 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const ST& 
         if (escaped) {
             st = TAFL_STATUS_WIN(TAFL_WIN_KING_ESCAPED, 1);
             done = true;
-        } else if (cx.r_exit_fort() && detect_exit_fort(cx, p)) {
+        } else if (TAFL_ABL_KEEP(EXITFORT) && cx.r_exit_fort() && detect_exit_fort(cx, p)) {
             st = TAFL_STATUS_WIN(TAFL_WIN_EXIT_FORT, 1);
             done = true;
         }
     }
-    if (!done && cx.r_repetition_enabled()) {
+    if (TAFL_ABL_KEEP(REP) && !done && cx.r_repetition_enabled()) {
         uint32_t reps = mover_def ? s.def_reps : s.att_reps;
         if (reps >= cx.r_n_repetitions()) {
             st = cx.r_repetition_is_loss() ? TAFL_STATUS_WIN(TAFL_WIN_REPETITION, !mover_def)
@@ -884,7 +962,7 @@ TAFL_HD uint8_t game_outcome(const Ctx<BB, SP>& cx, const Pos<BB>& p, const ST& 
         }
     }
     TAFL_RECONVERGE(lanes);
-    if (!done && !side_can_play(cx, p, !mover_def))
+    if (TAFL_ABL_KEEP(CANPLAY) && !done && !side_can_play(cx, p, !mover_def))
         st = cx.r_draw_on_no_plays() ? TAFL_STATUS_DRAW(TAFL_DRAW_NO_PLAYS) : TAFL_STATUS_WIN(TAFL_WIN_NO_PLAYS, mover_def);
     return st;
 }

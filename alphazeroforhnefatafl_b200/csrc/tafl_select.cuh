@@ -252,7 +252,7 @@ TAFL_HD MoveSel<BB> count_moves(const Ctx<BB, SP>& cx, const Pos<BB>& p, int def
         ms.plane[0] = acc.ones; ms.plane[1] = acc.twos; ms.plane[2] = acc.fours; ms.plane[3] = acc.eights;
         ms.plane[4] = acc.sixteens;
     }
-    if (def_side && (p.def & p.kbit).any()) {
+    if (TAFL_ABL_KEEP(KING) && def_side && (p.def & p.kbit).any()) {
         Rays r = piece_rays(cx, occ, KIND_K, p.kr, p.kc);
         int ck = r.cnt[0] + r.cnt[1] + r.cnt[2] + r.cnt[3];
 #pragma unroll
