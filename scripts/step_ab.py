@@ -15,23 +15,24 @@ from alphazeroforhnefatafl_b200._lib import lib  # noqa: E402
 
 label = sys.argv[1] if len(sys.argv) > 1 else "run"
 n = int(os.environ.get("AB_GAMES", "65536"))
+P = int(os.environ.get("AB_PLIES", "64"))          # plies per graph launch
 g = E.LockstepGames(E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN, n, 0, 128)
 st = torch.cuda.ExternalStream(g.stream, device=0)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 L = lib()
 with torch.cuda.stream(st):
     for _ in range(6):
-        g.step_random(20261104, 64, auto_reset=True, steps_per_launch=1, sync=False)
+        g.step_random(20261104, P, auto_reset=True, steps_per_launch=1, sync=False)
     best = []
     for rep in range(5):
         flush.zero_()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(st)
-        for _ in range(16):
-            g.step_random(20261104, 64, auto_reset=True, steps_per_launch=1, sync=False)
+        for _ in range(1024 // P):
+            g.step_random(20261104, P, auto_reset=True, steps_per_launch=1, sync=False)
         b.record(st)
         torch.cuda.synchronize()
-        best.append(1e3 * a.elapsed_time(b) / (16 * 64))
+        best.append(1e3 * a.elapsed_time(b) / (1024 // P * P))
     g.legal_moves_device()
     lm = []
     for rep in range(20):
