@@ -232,6 +232,28 @@ class Ctx:
         if self.world > 1:
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
 
+        self.affinity0, self.bound_cpus = os.sched_getaffinity(0), None
+        self.bind_near_gpu()
+
+    def bind_near_gpu(self):
+        """Keep this rank's host thread — the one that launches, waits and allocates the pinned buffers — on the CPUs
+        NVML names as closest to its GPU (same NUMA node / PCIe root), within what the process may use.  The CPU
+        baseline legs undo it (all_cpus) so that they see every core."""
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.local)
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(self.affinity0) + 64) // 64)
+            near = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1} & self.affinity0
+            if near and near != self.affinity0:
+                os.sched_setaffinity(0, near)
+                self.bound_cpus = len(near)
+        except Exception:  # noqa: BLE001  (no NVML, no such call, not permitted: stay where we are)
+            pass
+
+    def all_cpus(self):
+        os.sched_setaffinity(0, self.affinity0)
+
     def barrier(self):
         if self.world > 1:
             self.dist.barrier()
@@ -240,7 +262,7 @@ class Ctx:
     def reduce(self, x, op="max"):
         t = self.torch.tensor([float(x)], dtype=self.torch.float64, device="cuda")
         if self.world > 1:
-            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+            self.dist.all_reduce(t, op={"max": self.dist.ReduceOp.MAX, "min": self.dist.ReduceOp.MIN}.get(op, self.dist.ReduceOp.SUM))
         return float(t.item())
 
 
@@ -405,6 +427,7 @@ def run_b200(args):
                    "games_per_gpu": n, "plies_per_step": plies_per_step, "steps_per_launch": 1, "auto_reset": True,
                    "l2": "flushed between timed iterations (256 MiB memset, outside the events)",
                    "sharding": "game-id ranges, no data-path collective", "mean_legal_moves": mean_legal,
+                   "host_thread_cpus": cx.bound_cpus if cx.bound_cpus else len(cx.affinity0),
                    "timed_region_s": dev_ms_max * 1e-3},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                      "traffic": ncu_traffic("k_step_random"), "peak_source": peak_src, "kernel": "k_step_random<BB128, Copenhagen>",
@@ -417,6 +440,7 @@ def run_b200(args):
                        "pinned buffers over PCIe itself, bytes per step as listed); a recorded seeded "
                        "random-play action sequence over steady-state positions with auto-restart is replayed (checked bit-exact)",
                 "plies_per_round": e2e_plies, "rounds": rounds, "timed_region_s": cx.reduce(e2e_time),
+                "timed_region_s_fastest_rank": cx.reduce(e2e_time, "min"),
                 "games_ended_in_the_sequence": terminals,
                 "by_value_states": {"value": bv_value, "unit": UNIT, "h2d_bytes_per_step": n * 64, "d2h_bytes_per_step": n * 64,
                                     "api": "tafl_step_random_host(1 ply): pinned host states in, successor states out, chunked over streams",
@@ -437,6 +461,7 @@ def run_b200(args):
                 out[key] = {"error": repr(ex)}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         orc = oracle_handle()
+        cx.all_cpus()
         v, cores, sample = cpu_playout_rate(orc, args.cpu_seconds, args.seed)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         # C1 (BASELINE configs[0]): Brandubh 7x7, ONE game on ONE core, random legal play to terminal with restart
@@ -646,7 +671,9 @@ def bench_mcts(cx, E, preset):
         except Exception as ex:  # noqa: BLE001
             res["selfplay_sweep_to_terminal"] = {"error": repr(ex)}
     if cx.rank == 0 and cx.world == 1 and not args.no_cpu_baseline:
+        cx.all_cpus()
         res["cpu_baseline"] = cpu_mcts_rate(oracle_handle(), args.cpu_seconds, args.seed, args.mcts_sims, preset)
+        cx.bind_near_gpu()
     return res
 
 
