@@ -94,6 +94,7 @@ struct Mcts {
         uint32_t Ns = 0;              // self.Ns[s]
         std::vector<uint32_t> VL;     // virtual-loss mode: simulations of the current batch that hold (s,a) on their path
         uint32_t vln = 0;             //                    ... that pass through s
+        double v_leaf = 0.0;          //                    the evaluator's value when s was expanded (a collision takes it)
         double P = 0.0;               // self.Ps[s][a], uniform over the valid moves
         std::vector<double> Pa;       // evaluator mode: self.Ps[s][a] per action (masked, renormalised)
     };
@@ -149,6 +150,14 @@ struct Mcts {
             return -nodes[idx].Es;
         }
         if (!nodes[idx].expanded) {  // mcts.py:83-102
+            stats.depth_sum += (uint64_t)depth;
+            return -expand(idx);
+        }
+        return search_expanded(idx, depth);
+    }
+    // mcts.py:83-101: Ps, Vs, Ns of a leaf; returns the evaluator's v (0 for the stub)
+    double expand(int idx) {
+        {
             Node& n = nodes[idx];
             n.moves = logic.get_all_possible_moves(n.state);
             size_t L = n.moves.size();
@@ -177,13 +186,15 @@ struct Mcts {
             n.VL.assign(L, 0);
             n.child.assign(L, -1);
             n.Ns = 0;
+            n.vln = 0;
+            n.v_leaf = v_eval;
             n.expanded = true;
             stats.edges += L;
-            stats.depth_sum += (uint64_t)depth;
             if (idx == root) noise_root();
-            double v = v_eval;
-            return -v;
+            return v_eval;
         }
+    }
+    double search_expanded(int idx, int depth) {
         int best_act = -1;
         {  // mcts.py:104-119
             Node& n = nodes[idx];
@@ -235,7 +246,7 @@ struct Mcts {
     // cleared, mcts.py:20-26).  `root` walks down the retained tree.
     int root = 0;
     void run_from_root(uint32_t num_sims) {
-        if (vl_width > 1 && !eval) { run_from_root_vl(num_sims); return; }
+        if (vl_width > 1) { run_from_root_vl(num_sims); return; }
         root_noised = false;
         noise_root();
         for (uint32_t i = 0; i < num_sims; ++i) {
@@ -253,18 +264,21 @@ struct Mcts {
     //            Ns_eff = Ns + vl(node); it then adds itself to vl along its own path.  A simulation stops at a
     //            terminal node, at the (unexpanded) root, at the first edge nobody has followed yet (it creates the
     //            child), or — collision — at an edge whose child another simulation of the same batch is creating.
-    //   expand   the new leaves are expanded (stub evaluator: uniform priors, v = 0); a collision takes the same
-    //            value as the simulation that created the child.
+    //   expand   the new leaves are expanded (mcts.py:83-101 with the evaluator in use; stub: uniform priors, v = 0); a
+    //            collision takes the same value as the simulation that created the child.
     //   backup   every simulation removes its virtual losses and applies the real update of mcts.py:125-136.
     // While the root is unexpanded a batch holds one simulation.  With vl_width == 1 no simulation ever sees a
     // virtual loss, and the result is mcts.py's, bit for bit (the golden vectors guard that).
-    // Stub evaluator only (the evaluator-hook path batches across trees instead).
+    // With an evaluator the batch is what one evaluator call sees per tree: vl_width leaves (the hook's leaf batch is
+    // then n_trees x vl_width rows).
     // -----------------------------------------------------------------------------------------------------------
     uint32_t vl_width = 1;
     void run_from_root_vl(uint32_t num_sims) {
         enum { K_TERM = 1, K_ROOT, K_EMPTY, K_NEW, K_COLL };
         struct Sim { std::vector<std::pair<int, int>> path; int leaf = 0, kind = 0; uint32_t depth = 0; double v = 0.0; };
         uint32_t done = 0;
+        root_noised = false;
+        noise_root();
         while (done < num_sims) {
             uint32_t w = std::min<uint32_t>(vl_width, num_sims - done);
             if (!nodes[root].expanded && nodes[root].Es == 0.0) w = 1;
@@ -281,17 +295,17 @@ struct Mcts {
                     {
                         Node& n = nodes[idx];
                         const uint32_t ns_eff = n.Ns + n.vln;
-                        const double t_vis = (cpuct * n.P) * std::sqrt((double)ns_eff);
-                        const double u_new = (cpuct * n.P) * std::sqrt((double)ns_eff + MCTS_EPS);
+                        const double sq_vis = std::sqrt((double)ns_eff), sq_new = std::sqrt((double)ns_eff + MCTS_EPS);
                         double cur_best = -std::numeric_limits<double>::infinity();
                         for (size_t k = 0; k < L; ++k) {
                             const uint32_t nn = n.N[k] + n.VL[k];
+                            const double c = cpuct * (eval ? n.Pa[k] : n.P);
                             double u;
                             if (nn > 0) {
                                 const double qv = n.VL[k] ? ((double)n.N[k] * n.Q[k] - (double)n.VL[k]) / (double)nn : n.Q[k];
-                                u = qv + t_vis / (double)(1u + nn);
+                                u = qv + (c * sq_vis) / (double)(1u + nn);
                             } else {
-                                u = u_new;
+                                u = c * sq_new;
                             }
                             if (u > cur_best) { cur_best = u; a = (int)k; }
                         }
@@ -320,19 +334,8 @@ struct Mcts {
                 stats.depth_sum += S.depth;
                 if (S.kind == K_TERM) { stats.terminal_hits += 1; continue; }
                 if (n.Es != 0.0) { S.v = -n.Es; stats.terminal_hits += 1; continue; }   // new / collided child is terminal
-                if (S.kind == K_COLL) { S.v = -0.0; continue; }
-                n.moves = logic.get_all_possible_moves(n.state);
-                const size_t L = n.moves.size();
-                n.P = L ? 1.0 / (double)L : 0.0;
-                n.Q.assign(L, 0.0);
-                n.N.assign(L, 0);
-                n.VL.assign(L, 0);
-                n.child.assign(L, -1);
-                n.Ns = 0;
-                n.vln = 0;
-                n.expanded = true;
-                stats.edges += L;
-                S.v = -0.0;
+                if (S.kind == K_COLL) { S.v = -n.v_leaf; continue; }   // the value the simulation that opened the child got
+                S.v = -expand(S.leaf);
             }
             for (uint32_t i = 0; i < w; ++i) {   // ---- backup (mcts.py:125-136), virtual losses removed
                 Sim& S = sims[i];

@@ -568,6 +568,15 @@ int orc_mcts_episode_vl(const tafl_rules* r, int width, const tafl_state* roots,
                              best, final_states, stats, nullptr, 0.0, vl_width);
 }
 
+// virtual loss with the TAFL_EVAL_HASH evaluator (what the evaluator hook runs with vl_width > 1) and optional root noise
+int orc_mcts_episode_vl_eval(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
+                             uint32_t n_moves, int reuse, double cpuct, double draw_value, uint32_t vl_width, int use_eval,
+                             uint64_t eval_seed, int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best,
+                             tafl_state* final_states, tafl_mcts_stats* stats, const double* noise, double eps) {
+    return mcts_episode_impl(r, width, roots, n, num_sims, n_moves, reuse, cpuct, draw_value, use_eval, eval_seed, n_threads, visits,
+                             q, counts, best, final_states, stats, noise, eps, vl_width);
+}
+
 int orc_mcts_episode(const tafl_rules* r, int width, const tafl_state* roots, uint32_t n, uint32_t num_sims,
                      uint32_t n_moves, int reuse, double cpuct, double draw_value, int use_eval, uint64_t eval_seed,
                      int n_threads, uint32_t* visits, double* q, uint32_t* counts, uint32_t* best, tafl_state* final_states,

@@ -377,6 +377,31 @@ class Oracle:
         assert rc == 0, rc
         return dict(visits=visits, q=q, counts=counts, best=best, final=final, stats=stats)
 
+
+    def mcts_episode_vl_eval(self, rules, width, roots, num_sims, n_moves, reuse, vl_width, eval_seed=None, cpuct=1.0,
+                             draw_value=1e-4, n_threads=1, noise=None, eps=0.0):
+        """virtual loss with an evaluator: eval_seed None = stub, else the TAFL_EVAL_HASH test evaluator (+ optional root noise)"""
+        roots = np.ascontiguousarray(roots)
+        n = len(roots)
+        visits = np.zeros((n, n_moves, A.MAX_MOVES), np.uint32)
+        q = np.zeros((n, n_moves, A.MAX_MOVES), np.float64)
+        counts = np.zeros((n, n_moves), np.uint32)
+        best = np.zeros((n, n_moves), np.uint32)
+        final = np.zeros(n, A.STATE_DTYPE)
+        stats = A.MctsStats()
+        if noise is not None:
+            noise = np.ascontiguousarray(noise, np.float64)
+            assert noise.shape == (n, n_moves, A.MAX_MOVES)
+        f = self.lib.orc_mcts_episode_vl_eval
+        f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_double, C.c_double,
+                      C.c_uint32, C.c_int, C.c_uint64, C.c_int] + [C.c_void_p] * 7 + [C.c_double]
+        f.restype = C.c_int
+        rc = f(C.addressof(rules), width, roots.ctypes.data, n, num_sims, n_moves, int(reuse), cpuct, draw_value, int(vl_width),
+               0 if eval_seed is None else 1, 0 if eval_seed is None else int(eval_seed), n_threads, visits.ctypes.data,
+               q.ctypes.data, counts.ctypes.data, best.ctypes.data, final.ctypes.data, C.addressof(stats),
+               None if noise is None else noise.ctypes.data, float(eps))
+        assert rc == 0, rc
+        return dict(visits=visits, q=q, counts=counts, best=best, final=final, stats=stats)
     def hash_eval(self, states, seed):
         states = np.ascontiguousarray(states)
         n = len(states)
