@@ -34,6 +34,12 @@ struct MctsPools {
     uint32_t* l_counts = nullptr;     // [n_games]
     float* l_priors = nullptr;        // [n_games][TAFL_MAX_MOVES]  evaluator output
     float* l_values = nullptr;        // [n_games]                  evaluator output
+    // virtual loss through the hook (cfg.vl_width = W > 1): the leaf batch has n_games x W rows, row = game * W + simulation
+    uint32_t l_width = 1;             // W the leaf buffers are sized for
+    uint32_t* b_leaf = nullptr;       // [n_games][16] leaf of each simulation of the pending batch
+    uint8_t* b_kind = nullptr;        // [n_games][16]
+    uint32_t* b_w = nullptr;          // [n_games] simulations in the pending batch
+    uint32_t* b_done = nullptr;       // [n_games] simulations finished since tafl_mcts_begin
     double* d_noise = nullptr;        // [n_games][TAFL_MAX_MOVES] root exploration noise (tafl_mcts_root_noise), eps below
     double noise_eps = 0.0;
     uint8_t* t_noised = nullptr;      // [n_games] this search's root already carries the noise
@@ -1357,14 +1363,13 @@ __device__ __forceinline__ void grp_puct_select_priors(const MctsEdge* __restric
 // mcts.py:87-101 for the pending leaf `node` of ONE tree by the full warp (np.sum needs all 32 lanes: lane = 8 * block +
 // accumulator holds the 16 evaluator outputs pfv[i] = priors[block * 128 + accumulator + 8 i], loaded by the caller so
 // that the loads of all the warp's trees are in flight together).  The backup of -v is left to the tree's own group.
-__device__ __forceinline__ void warp_expand_tree(const MctsView& mv, uint32_t tree, uint32_t node, const float (&pfv)[16],
-                                                 const float* __restrict__ l_priors, int lane) {
+__device__ __forceinline__ void warp_expand_leaf(const MctsView& mv, uint32_t tree, uint32_t node, const float (&pfv)[16],
+                                                 const float* __restrict__ pf, int lane, bool single) {
     uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
     MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
     double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
     const uint4 h = n_hdr[node];
     const uint32_t L = hdr_n_edges(h.w), base = mv.t_edges[tree];
-    const float* const pf = l_priors + (size_t)tree * TAFL_MAX_MOVES;
     const int blk = lane >> 3, acc = lane & 7;
     double x[16];
 #pragma unroll
@@ -1396,10 +1401,57 @@ __device__ __forceinline__ void warp_expand_tree(const MctsView& mv, uint32_t tr
     if (lane == 0) {
         n_hdr[node] = make_uint4(base, 0u, h.z, h.w | (1u << 20));   // expanded, Ns = 0 (mcts.py:101)
         mv.t_edges[tree] = base + L;
-        mv.t_pending[tree] = MCTS_NO_PARENT;
         atomicAdd(&mv.stats[ST_EDGES], (unsigned long long)L);
-        atomicAdd(&mv.stats[ST_SIMS], 1ull);
         atomicMax(&mv.stats[ST_MAXEDGES], (unsigned long long)(base + L));
+        if (single) {   // one leaf per tree and round (k_mcts_hook_round): the simulation is counted here
+            mv.t_pending[tree] = MCTS_NO_PARENT;
+            atomicAdd(&mv.stats[ST_SIMS], 1ull);
+        }
+    }
+}
+__device__ __forceinline__ void warp_expand_tree(const MctsView& mv, uint32_t tree, uint32_t node, const float (&pfv)[16],
+                                                 const float* __restrict__ l_priors, int lane) {
+    warp_expand_leaf(mv, tree, node, pfv, l_priors + (size_t)tree * TAFL_MAX_MOVES, lane, true);
+}
+
+// one row of the leaf batch: the position, its board_to_matrix planes and its canonical move list, by the tree's group
+template <class BB, int SP, int G>
+__device__ __forceinline__ void grp_emit_leaf_row(const Ctx<BB, SP>& cx, const tafl_state& s, const Pos<BB>& p, int def_side,
+                                                  const uint32_t* __restrict__ ptab, int n_pieces, tafl_state* __restrict__ o_state,
+                                                  uint8_t* __restrict__ o_planes, tafl_move* __restrict__ mo, unsigned gmask, int gl) {
+    if (gl == 0) store_state(o_state, s);
+    {   // board_to_matrix (game/main.rs:55-83)
+        const int n = cx.n(), mid = n / 2;
+        const BB occ = p.occ(), king = p.king();
+        for (int t = gl; t < n * n; t += G) {
+            const int r = t / n, c = t - r * n, b = idx_of<BB>(r, c);
+            int val = 0;
+            if ((r == 0 || r == n - 1) && (c == 0 || c == n - 1)) val = 20;
+            if (r == mid && c == mid) val = 30;
+            if (occ.test(b)) val += king.test(b) ? 5 : 1;
+            o_planes[t] = (uint8_t)val;
+        }
+    }
+    int before = 0;
+    for (int base = 0; base < n_pieces; base += G) {
+        const int idx = base + gl;
+        const uint32_t e = idx < n_pieces ? ptab[idx] : 0u;   // written by this same lane in grp_build_ptab
+        const int c = pt_total(e);
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) {
+            const int t = __shfl_up_sync(gmask, incl, o, G);
+            if (gl >= o) incl += t;
+        }
+        if (c > 0) {   // the piece's plays by tile arithmetic (emit_piece_plays == pt_decode for j = 0 .. c-1)
+            const int tile = (int)(e & 127u), row = tile / BB::STRIDE;
+            Rays r;
+            r.cnt[0] = (int)((e >> 8) & 15u); r.cnt[1] = (int)((e >> 12) & 15u);
+            r.cnt[2] = (int)((e >> 16) & 15u); r.cnt[3] = (int)((e >> 20) & 15u);
+            emit_piece_plays(cx, tile, row, tile - row * BB::STRIDE, (e & 0x80u) ? KIND_K : (def_side ? KIND_DS : KIND_AS), r, mo,
+                             before + incl - c, TAFL_MAX_MOVES);
+        }
+        before += __shfl_sync(gmask, incl, G - 1, G);
     }
 }
 
@@ -1534,45 +1586,9 @@ k_mcts_hook_round(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t 
                 mode = M_BACKUP;
             } else {
                 // the leaf batch row: position, planes, canonical move list (action index -> move)
-                if (gl == 0) {
-                    store_state(l_state + tree, s);
-                    n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack((uint32_t)L, pedge, 0u, es, (uint32_t)n_pieces));
-                }
-                {   // board_to_matrix (game/main.rs:55-83)
-                    const int n = cx.n(), mid = n / 2;
-                    const BB occ = p.occ(), king = p.king();
-                    uint8_t* const out = l_planes + (size_t)tree * (size_t)(n * n);
-                    for (int t = gl; t < n * n; t += G) {
-                        const int r = t / n, c = t - r * n, b = idx_of<BB>(r, c);
-                        int val = 0;
-                        if ((r == 0 || r == n - 1) && (c == 0 || c == n - 1)) val = 20;
-                        if (r == mid && c == mid) val = 30;
-                        if (occ.test(b)) val += king.test(b) ? 5 : 1;
-                        out[t] = (uint8_t)val;
-                    }
-                }
-                tafl_move* const mo = l_moves + (size_t)tree * TAFL_MAX_MOVES;
-                int before = 0;
-                for (int base = 0; base < n_pieces; base += G) {
-                    const int idx = base + gl;
-                    const uint32_t e = idx < n_pieces ? ptab[idx] : 0u;   // written by this same lane in grp_build_ptab
-                    const int c = pt_total(e);
-                    int incl = c;
-#pragma unroll
-                    for (int o = 1; o < G; o <<= 1) {
-                        const int t = __shfl_up_sync(gmask, incl, o, G);
-                        if (gl >= o) incl += t;
-                    }
-                    if (c > 0) {   // the piece's plays by tile arithmetic (emit_piece_plays == pt_decode for j = 0 .. c-1)
-                        const int tile = (int)(e & 127u), row = tile / BB::STRIDE;
-                        Rays r;
-                        r.cnt[0] = (int)((e >> 8) & 15u); r.cnt[1] = (int)((e >> 12) & 15u);
-                        r.cnt[2] = (int)((e >> 16) & 15u); r.cnt[3] = (int)((e >> 20) & 15u);
-                        emit_piece_plays(cx, tile, row, tile - row * BB::STRIDE, (e & 0x80u) ? KIND_K : (def_side ? KIND_DS : KIND_AS), r, mo,
-                                         before + incl - c, TAFL_MAX_MOVES);
-                    }
-                    before += __shfl_sync(gmask, incl, G - 1, G);
-                }
+                if (gl == 0) n_hdr[target] = make_uint4(0u, 0u, parent, hdr_pack((uint32_t)L, pedge, 0u, es, (uint32_t)n_pieces));
+                grp_emit_leaf_row<BB, SP, G>(cx, s, p, def_side, ptab, n_pieces, l_state + tree, l_planes + (size_t)tree * (size_t)(cx.n() * cx.n()),
+                                             l_moves + (size_t)tree * TAFL_MAX_MOVES, gmask, gl);
                 want = (uint32_t)L;
                 pending = target;
                 c_depth += depth;
@@ -1597,6 +1613,269 @@ k_mcts_hook_round(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t 
             mv.t_pending[tree] = MCTS_NO_PARENT;
         }
         if (overflow) { mv.t_overflow[tree] = overflow; atomicOr(any_overflow, overflow); }
+        if (c_sims) atomicAdd(&mv.stats[ST_SIMS], c_sims);
+        if (c_nodes) atomicAdd(&mv.stats[ST_NODES], c_nodes);
+        if (c_depth) atomicAdd(&mv.stats[ST_DEPTH], c_depth);
+        if (c_term) atomicAdd(&mv.stats[ST_TERMINAL], c_term);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Virtual loss through the evaluator hook: W leaves per tree and round, so that one evaluator call sees a batch of
+// n_trees x W rows (row = tree * W + simulation).  The schedule is oracle/mcts_oracle.hpp::run_from_root_vl with an
+// evaluator: phase 2 selects the W simulations of a batch in index order under virtual loss, creates the new
+// children (one lane per child, as k_mcts_sims_vl) and emits a leaf row for every new, non-terminal leaf; after the
+// evaluator phase 1 expands those leaves in order (mask / renormalise, mcts.py:87-101) and backs every simulation
+// up in order, taking its virtual losses off; a collision takes the value of the simulation that opened the child.
+// What crosses the launch boundary is the batch table (kind and leaf of each simulation) and the per-tree count of
+// simulations done.  Every edge of an expanded node is initialised (no prefix rule with real priors).
+// ---------------------------------------------------------------------------------------------
+struct VlBatch {
+    uint32_t* leaf;   // [n_trees][16]
+    uint8_t* kind;    // [n_trees][16]
+    uint32_t* w;      // [n_trees] simulations of the pending batch
+    uint32_t* done;   // [n_trees] simulations finished since tafl_mcts_begin
+};
+enum { VK_NONE = 0, VK_TERM, VK_ROOT, VK_EMPTY, VK_NEW, VK_COLL };
+
+template <int G>
+__device__ __forceinline__ void grp_puct_select_priors_vl(const MctsEdge* __restrict__ ed, const double* __restrict__ prior, uint32_t L,
+                                                          uint32_t ns_raw, double cpuct, unsigned gmask, int gl, uint32_t& out_a,
+                                                          uint32_t& out_Nraw, uint32_t& out_child) {
+    const uint32_t ns_eff = (ns_raw & MCTS_VL_MASK) + (ns_raw >> 24);
+    const double sq_vis = sqrt((double)ns_eff), sq_new = sqrt((double)ns_eff + MCTS_EPS);
+    double best_u = -INFINITY;
+    uint32_t best_a = 0xFFFFFFFFu, best_N = 0, best_child = 0;
+    for (uint32_t a0 = gl; a0 < L; a0 += 4 * G) {
+        MctsEdge e4[4];
+        double p4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) { e4[j] = ed[a]; p4[j] = prior[a]; }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = a0 + (uint32_t)(G * j);
+            if (a < L) {
+                const uint32_t N = e4[j].N & MCTS_VL_MASK, vl = e4[j].N >> 24, nn = N + vl;
+                const double c = cpuct * p4[j];
+                double u;
+                if (nn > 0) {
+                    const double qv = vl ? ((double)N * e4[j].Q - (double)vl) / (double)nn : e4[j].Q;
+                    u = qv + (c * sq_vis) / (double)(1u + nn);
+                } else {
+                    u = c * sq_new;
+                }
+                if (u > best_u) { best_u = u; best_a = a; best_N = e4[j].N; best_child = e4[j].child; }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        const double ou = __shfl_xor_sync(gmask, best_u, o, G);
+        const uint32_t oa = __shfl_xor_sync(gmask, best_a, o, G);
+        const uint32_t on = __shfl_xor_sync(gmask, best_N, o, G);
+        const uint32_t oc = __shfl_xor_sync(gmask, best_child, o, G);
+        if (ou > best_u || (ou == best_u && oa < best_a)) { best_u = ou; best_a = oa; best_N = on; best_child = oc; }
+    }
+    out_a = best_a; out_Nraw = best_N; out_child = best_child;
+}
+
+template <class BB, int SP>
+__global__ void __launch_bounds__(MCTS_WARPS * 32, 4)
+k_mcts_hook_vl(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, uint32_t sims, uint32_t W, double cpuct,
+               double draw_value, tafl_state* __restrict__ l_state, uint8_t* __restrict__ l_planes, tafl_move* __restrict__ l_moves,
+               uint32_t* __restrict__ l_counts, const float* __restrict__ l_priors, float* __restrict__ l_values, VlBatch vb,
+               uint32_t* __restrict__ any_overflow, int do_expand, int do_select) {
+    constexpr int G = 16, TPW = 32 / G;
+    const int lane = threadIdx.x & 31, gl = lane % G, gshift = (lane / G) * G;
+    const unsigned gmask = ((1u << G) - 1u) << gshift;
+    const uint32_t warp_tree0 = (blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5)) * TPW;
+    const uint32_t tree_raw = warp_tree0 + (uint32_t)(lane / G);
+    const bool live = tree_raw < n_trees;
+    const uint32_t tree = live ? tree_raw : 0u;
+    uint4* const n_hdr = mv.n_hdr + (size_t)tree * mv.node_cap;
+    MctsEdge* const edges = mv.edges + (size_t)tree * mv.edge_cap;
+    unsigned long long c_sims = 0, c_nodes = 0, c_depth = 0, c_term = 0;
+    // ---- phase 1: the batch evaluated since the last round
+    if (do_expand) {
+        // expansions, simulation order inside a tree; np.sum needs the full warp, so the warp's trees take turns
+#pragma unroll 1
+        for (int t = 0; t < TPW; ++t) {
+            const uint32_t tr = warp_tree0 + (uint32_t)t;
+            if (tr >= n_trees) continue;
+            const uint32_t w = vb.w[tr];
+            const int blk = lane >> 3, acc = lane & 7;
+#pragma unroll 1
+            for (uint32_t i = 0; i < w; ++i) {
+                const int kind = (int)vb.kind[(size_t)tr * 16 + i];
+                if (kind != VK_NEW && kind != VK_ROOT) continue;
+                const uint32_t leaf = vb.leaf[(size_t)tr * 16 + i];
+                const uint4 h = mv.n_hdr[(size_t)tr * mv.node_cap + leaf];
+                if (hdr_es(h.w) != ES_ONGOING || hdr_expanded(h.w)) continue;   // terminal child / empty expansion: no evaluation
+                const float* const pf = l_priors + ((size_t)tr * W + i) * TAFL_MAX_MOVES;
+                float pfv[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) pfv[k] = pf[blk * 128 + acc + 8 * k];
+                warp_expand_leaf(mv, tr, leaf, pfv, pf, lane, false);
+                __syncwarp();
+            }
+        }
+        __syncwarp();
+        // backups, simulation order, every tree's own group
+        const uint32_t w = live ? vb.w[tree] : 0u;
+        const int my_kind = (live && (uint32_t)gl < w) ? (int)vb.kind[(size_t)tree * 16 + gl] : VK_NONE;
+        const uint32_t my_leaf = (live && (uint32_t)gl < w) ? vb.leaf[(size_t)tree * 16 + gl] : 0u;
+        for (uint32_t i = 0; i < w; ++i) {
+            const int kind = __shfl_sync(gmask, my_kind, (int)i, G);
+            const uint32_t leaf = __shfl_sync(gmask, my_leaf, (int)i, G);
+            if (kind == VK_NONE) continue;
+            double v = 0.0;
+            if (kind != VK_EMPTY) {
+                const uint32_t es = hdr_es(n_hdr[leaf].w);
+                if (es != ES_ONGOING) {
+                    v = -(es == ES_WIN ? 1.0 : (es == ES_LOSS ? -1.0 : draw_value));
+                } else {
+                    uint32_t src = i;   // a collision takes the value of the simulation that opened the child
+                    if (kind == VK_COLL) {
+                        const unsigned opener = __ballot_sync(gmask, my_kind == VK_NEW && my_leaf == leaf && (uint32_t)gl < i) >> gshift;
+                        src = opener ? (uint32_t)(__ffs((int)opener) - 1) : i;
+                    }
+                    v = -(double)l_values[(size_t)tree * W + src];
+                }
+            }
+            grp_backup_vl(n_hdr, edges, leaf, v, gmask, gl);
+            c_sims += 1;
+        }
+        if (gl == 0 && live && w) {
+            vb.done[tree] += w;
+            vb.w[tree] = 0u;
+        }
+        __syncwarp();
+    }
+    if (do_select) {
+        // ---- phase 2: the next batch (run_from_root_vl, select sweep), G lanes per tree
+        tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
+        uint32_t* const n_ptab = mv.n_ptab + (size_t)tree * mv.node_cap * MCTS_PT_MAX;
+        const double* const prior = mv.e_prior + (size_t)tree * mv.edge_cap;
+        uint32_t overflow = 0, n_nodes = mv.t_nodes[tree];
+        if (W > (uint32_t)G) W = (uint32_t)G;
+        uint32_t w = 0;
+        if (live && mv.t_overflow[tree] == 0) {
+            const uint32_t done = vb.done[tree];
+            if (done < sims) {
+                w = sims - done < W ? sims - done : W;
+                const uint4 h0 = n_hdr[0];
+                if (!hdr_expanded(h0.w) && hdr_es(h0.w) == ES_ONGOING) w = 1;   // one simulation per batch while the root is unexpanded
+            }
+        }
+        int my_kind = VK_NONE;
+        uint32_t my_leaf = 0, my_parent = 0, my_pedge = 0;
+        tafl_move my_move = 0;
+        for (uint32_t i = 0; i < w; ++i) {
+            int kind = VK_NONE;
+            uint32_t node = 0, depth = 0, leaf = 0, parent = 0, pedge = 0;
+            tafl_move mvv = 0;
+            while (true) {
+                const uint4 h = n_hdr[node];
+                if (hdr_es(h.w) != ES_ONGOING) { kind = VK_TERM; leaf = node; c_term += 1; break; }   // mcts.py:77-81
+                if (!hdr_expanded(h.w)) { kind = VK_ROOT; leaf = node; break; }
+                const uint32_t L = hdr_n_edges(h.w);
+                if (L == 0) { kind = VK_EMPTY; leaf = node; break; }
+                uint32_t a, bNraw, bchild;
+                grp_puct_select_priors_vl<G>(edges + h.x, prior + h.x, L, h.y, cpuct, gmask, gl, a, bNraw, bchild);
+                depth += 1;
+                const bool fresh = (bNraw & MCTS_VL_MASK) == 0;        // (s,a) not in Qsa
+                const bool collide = fresh && (bNraw >> 24) != 0;      // ... and an earlier simulation of this batch is opening it
+                uint32_t child = bchild;
+                if (fresh && !collide) {
+                    if (n_nodes >= mv.node_cap) { overflow = OVF_NODES; break; }
+                    child = n_nodes++;
+                    c_nodes += 1;
+                    const tafl_state ps = load_state(n_state + node);
+                    mvv = grp_decode_edge<G>(cx, n_ptab + (size_t)node * MCTS_PT_MAX, (int)hdr_n_pieces(h.w),
+                                             (ps.flags & TAFL_FLAG_DEF_TO_PLAY) != 0, (int)a, gmask, gshift, gl);
+                }
+                __syncwarp(gmask);
+                if (gl == 0) {   // the virtual loss of this simulation on (s,a) and on s
+                    MctsEdge* const ep = edges + h.x + a;
+                    ep->N = bNraw + MCTS_VL_ONE;
+                    if (fresh && !collide) ep->child = child;
+                    reinterpret_cast<uint32_t*>(n_hdr + node)[1] = h.y + MCTS_VL_ONE;
+                }
+                __syncwarp(gmask);
+                if (fresh) {
+                    kind = collide ? VK_COLL : VK_NEW;
+                    leaf = child; parent = node; pedge = a;
+                    break;
+                }
+                node = child;
+            }
+            if (overflow) break;
+            if (kind != VK_EMPTY) c_depth += depth;
+            if (gl == (int)i) { my_kind = kind; my_leaf = leaf; my_parent = parent; my_pedge = pedge; my_move = mvv; }
+        }
+        if (overflow) { w = 0; my_kind = VK_NONE; }
+        __syncwarp();   // ---- create: every new child of every tree of the warp, one lane each
+        if (my_kind == VK_NEW) {
+            tafl_state s = load_state(n_state + my_parent);
+            do_valid_move(cx, s, my_move);
+            store_state(n_state + my_leaf, s);
+            n_hdr[my_leaf] = make_uint4(0u, 0u, my_parent, hdr_pack(0, my_pedge, 0, es_code(s)));
+        }
+        __syncwarp();
+        // ---- leaf rows, one simulation after the other, group-cooperative
+        uint32_t pend_edges = 0;
+        for (uint32_t i = 0; i < W; ++i) {
+            const int kind = __shfl_sync(gmask, my_kind, (int)i, G);
+            const uint32_t leaf = __shfl_sync(gmask, my_leaf, (int)i, G);
+            const size_t row = (size_t)tree * W + i;
+            uint32_t want = 0;
+            if (i < w && !overflow && (kind == VK_NEW || kind == VK_ROOT || kind == VK_COLL)) {
+                const uint4 h = n_hdr[leaf];
+                const uint32_t es = hdr_es(h.w);
+                if (es != ES_ONGOING) {
+                    c_term += 1;   // the new (or collided) child is terminal
+                } else if (kind != VK_COLL) {
+                    const tafl_state s = load_state(n_state + leaf);
+                    const Pos<BB> p = load_pos(cx, s);
+                    const int def_side = (s.flags & TAFL_FLAG_DEF_TO_PLAY) != 0;
+                    uint32_t* const ptab = n_ptab + (size_t)leaf * MCTS_PT_MAX;
+                    int n_pieces;
+                    const int L = grp_build_ptab<G>(cx, p, def_side, ptab, gmask, gl, &n_pieces);
+                    if ((uint32_t)L > mv.edge_cap - mv.t_edges[tree] - pend_edges || n_pieces > MCTS_PT_MAX || L > TAFL_MAX_MOVES) {
+                        overflow = (n_pieces > MCTS_PT_MAX || L > TAFL_MAX_MOVES) ? OVF_PIECES : OVF_EDGES;
+                    } else if (L == 0) {   // Ongoing position without plays: unreachable through do_play; expand empty, v = 0
+                        if (gl == 0) {
+                            n_hdr[leaf] = make_uint4(mv.t_edges[tree], 0u, h.z, hdr_pack(0u, hdr_pedge(h.w), 1u, es, (uint32_t)n_pieces));
+                            l_values[row] = 0.0f;
+                        }
+                    } else {
+                        if (gl == 0) n_hdr[leaf] = make_uint4(0u, 0u, h.z, hdr_pack((uint32_t)L, hdr_pedge(h.w), 0u, es, (uint32_t)n_pieces));
+                        grp_emit_leaf_row<BB, SP, G>(cx, s, p, def_side, ptab, n_pieces, l_state + row, l_planes + row * (size_t)(cx.n() * cx.n()),
+                                                     l_moves + row * TAFL_MAX_MOVES, gmask, gl);
+                        want = (uint32_t)L;
+                        pend_edges += (uint32_t)L;
+                    }
+                }
+            }
+            if (gl == 0 && live) l_counts[row] = want;
+            __syncwarp(gmask);
+        }
+        if (live) {
+            if ((uint32_t)gl < w && !overflow) {
+                vb.kind[(size_t)tree * 16 + gl] = (uint8_t)my_kind;
+                vb.leaf[(size_t)tree * 16 + gl] = my_leaf;
+            }
+            if (gl == 0) {
+                vb.w[tree] = overflow ? 0u : w;
+                mv.t_nodes[tree] = n_nodes;
+                if (overflow) { mv.t_overflow[tree] = overflow; atomicOr(any_overflow, overflow); }
+            }
+        }
+    }
+    if (gl == 0 && live) {
         if (c_sims) atomicAdd(&mv.stats[ST_SIMS], c_sims);
         if (c_nodes) atomicAdd(&mv.stats[ST_NODES], c_nodes);
         if (c_depth) atomicAdd(&mv.stats[ST_DEPTH], c_depth);
@@ -1642,15 +1921,30 @@ k_eval_builtin(int kind, uint64_t seed, const tafl_state* __restrict__ l_state, 
 // ---------------------------------------------------------------------------------------------
 namespace tafl {
 
+// W leaves per tree and round through the evaluator hook (1 = the sequential search of mcts.py)
+static inline uint32_t hook_width(const tafl_mcts_config& c) { return c.vl_width > 1 ? c.vl_width : 1u; }
+// rounds a hook search needs: a fresh tree spends one batch of one simulation on its root, then ceil((sims - 1) / W)
+static inline uint32_t hook_rounds(const tafl_mcts_config& c) {
+    const uint32_t W = hook_width(c);
+    return W == 1 ? c.num_sims : (c.num_sims ? 1u + (c.num_sims - 1u + W - 1u) / W : 0u);
+}
+// the evaluator-hook buffers (sized by vl_width) and the graph that holds their addresses
+static void eval_free(MctsPools* m) {
+    if (m->round_graph) { cudaGraphExecDestroy(m->round_graph); m->round_graph = nullptr; }
+    cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
+    cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
+    cudaFree(m->b_leaf); cudaFree(m->b_kind); cudaFree(m->b_w); cudaFree(m->b_done);
+    m->v.e_prior = nullptr; m->v.t_pending = nullptr;
+    m->l_state = nullptr; m->l_planes = nullptr; m->l_moves = nullptr; m->l_counts = nullptr; m->l_priors = nullptr; m->l_values = nullptr;
+    m->b_leaf = nullptr; m->b_kind = nullptr; m->b_w = nullptr; m->b_done = nullptr;
+}
 void mcts_free(tafl_engine* e) {
     MctsPools* m = e->mcts;
     if (!m) return;
     cudaFree(m->v.n_state); cudaFree(m->v.n_hdr); cudaFree(m->v.n_ptab); cudaFree(m->v.edges); cudaFree(m->v.t_nodes); cudaFree(m->v.t_edges); cudaFree(m->v.t_overflow); cudaFree(m->v.stats);
     cudaFree(m->r_moves); cudaFree(m->r_visits); cudaFree(m->r_q); cudaFree(m->r_counts); cudaFree(m->r_best); cudaFree(m->r_probs); cudaFree(m->remap);
     cudaFree(m->d_any_overflow); cudaFree(m->row_of);
-    if (m->round_graph) cudaGraphExecDestroy(m->round_graph);
-    cudaFree(m->v.e_prior); cudaFree(m->v.t_pending);
-    cudaFree(m->l_state); cudaFree(m->l_planes); cudaFree(m->l_moves); cudaFree(m->l_counts); cudaFree(m->l_priors); cudaFree(m->l_values);
+    eval_free(m);
     cudaFree(m->d_noise); cudaFree(m->t_noised);
     delete m;
     e->mcts = nullptr;
@@ -1714,6 +2008,10 @@ int tafl_mcts_configure(tafl_engine* e, const tafl_mcts_config* cfg) {
     if (c.vl_width > 16) { e->err = "tafl_mcts_configure: vl_width is at most 16"; return TAFL_ERR_INVALID_ARG; }
     if (e->mcts && e->mcts->cfg.num_sims == c.num_sims && e->mcts->cfg.edge_capacity == c.edge_capacity &&
         e->mcts->cfg.node_capacity == c.node_capacity && e->mcts->cfg.flags == c.flags) {
+        if (hook_width(c) != e->mcts->l_width && e->mcts->v.e_prior) {   // the leaf batch is sized by vl_width
+            TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+            eval_free(e->mcts);
+        }
         e->mcts->cfg = c;   // same pools, possibly new cpuct / draw value
         return TAFL_OK;
     }
@@ -1983,24 +2281,32 @@ int tafl_mcts_overflow(tafl_engine* e, uint32_t* h_flags) {
 static int eval_alloc(tafl_engine* e) {
     MctsPools* m = e->mcts;
     if (m->v.e_prior) return TAFL_OK;
-    const size_t n = e->n_games, cells = (size_t)e->N * e->N;
+    const size_t games = e->n_games, cells = (size_t)e->N * e->N;
+    m->l_width = hook_width(m->cfg);
+    const size_t n = games * m->l_width;   // rows of the leaf batch
 #define EVAL_ALLOC(ptr, bytes)                                                                   \
     do {                                                                                         \
         cudaError_t _ce = cudaMalloc((void**)&(ptr), (bytes));                                   \
         if (_ce != cudaSuccess) return set_cuda_error(e, _ce, "cudaMalloc(" #ptr ")");           \
     } while (0)
-    EVAL_ALLOC(m->v.t_pending, n * sizeof(uint32_t));
+    EVAL_ALLOC(m->v.t_pending, games * sizeof(uint32_t));
+    EVAL_ALLOC(m->b_leaf, games * 16 * sizeof(uint32_t));
+    EVAL_ALLOC(m->b_kind, games * 16);
+    EVAL_ALLOC(m->b_w, games * sizeof(uint32_t));
+    EVAL_ALLOC(m->b_done, games * sizeof(uint32_t));
     EVAL_ALLOC(m->l_state, n * sizeof(tafl_state));
     EVAL_ALLOC(m->l_planes, n * cells);
     EVAL_ALLOC(m->l_moves, n * TAFL_MAX_MOVES * sizeof(tafl_move));
     EVAL_ALLOC(m->l_counts, n * sizeof(uint32_t));
     EVAL_ALLOC(m->l_priors, n * TAFL_MAX_MOVES * sizeof(float));
     EVAL_ALLOC(m->l_values, n * sizeof(float));
-    EVAL_ALLOC(m->v.e_prior, n * (size_t)m->v.edge_cap * sizeof(double));   // last: marks the set complete
+    EVAL_ALLOC(m->v.e_prior, games * (size_t)m->v.edge_cap * sizeof(double));   // last: marks the set complete
 #undef EVAL_ALLOC
     TAFL_CUDA_TRY(e, cudaMemsetAsync(m->l_priors, 0, n * TAFL_MAX_MOVES * sizeof(float), e->stream));
     TAFL_CUDA_TRY(e, cudaMemsetAsync(m->l_values, 0, n * sizeof(float), e->stream));
     TAFL_CUDA_TRY(e, cudaMemsetAsync(m->l_moves, 0, n * TAFL_MAX_MOVES * sizeof(tafl_move), e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->l_counts, 0, n * sizeof(uint32_t), e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->b_w, 0, games * sizeof(uint32_t), e->stream));
     return TAFL_OK;
 }
 
@@ -2008,7 +2314,7 @@ static void fill_batch(tafl_engine* e, tafl_leaf_batch* b) {
     MctsPools* m = e->mcts;
     b->d_states = m->l_state; b->d_planes = m->l_planes; b->d_moves = m->l_moves; b->d_counts = m->l_counts;
     b->d_priors = m->l_priors; b->d_values = m->l_values;
-    b->n_games = e->n_games; b->side_len = (uint32_t)e->N;
+    b->n_games = e->n_games * m->l_width; b->side_len = (uint32_t)e->N;   // rows: game * W + simulation
     b->stream = (void*)e->stream;
 }
 
@@ -2016,6 +2322,14 @@ static void fill_batch(tafl_engine* e, tafl_leaf_batch* b) {
 static int hook_round_launch(tafl_engine* e, int do_expand, int do_select) {
     MctsPools* m = e->mcts;
     const uint32_t n = e->n_games;
+    if (m->l_width > 1) {   // W leaves per tree: k_mcts_hook_vl, 16 lanes per tree
+        const VlBatch vb{m->b_leaf, m->b_kind, m->b_w, m->b_done};
+        TAFL_SPEC_DISPATCH(e, (k_mcts_hook_vl<BB, SP><<<grid_for(n, MCTS_WARPS * 2), MCTS_WARPS * 32, 0, e->stream>>>(
+                                  cx, m->v, n, m->cfg.num_sims, m->l_width, m->cfg.cpuct, m->cfg.draw_value, m->l_state, m->l_planes,
+                                  m->l_moves, m->l_counts, m->l_priors, m->l_values, vb, m->d_any_overflow, do_expand, do_select)));
+        MCTS_LAUNCHED(e);
+        return TAFL_OK;
+    }
     const int G = (e->mcts_group == 32 || e->mcts_group == 8) ? e->mcts_group : 16;
 #define TAFL_HOOK_LAUNCH(GG)                                                                                                        \
     TAFL_SPEC_DISPATCH(e, (k_mcts_hook_round<BB, SP, GG><<<grid_for(n, MCTS_WARPS * (32 / GG)), MCTS_WARPS * 32, 0, e->stream>>>(     \
@@ -2040,6 +2354,8 @@ int tafl_mcts_begin(tafl_engine* e) {
     MctsPools* m = e->mcts;
     launch_tree_init(e, 0);
     MCTS_LAUNCHED(e);
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->b_done, 0, (size_t)e->n_games * sizeof(uint32_t), e->stream));
+    TAFL_CUDA_TRY(e, cudaMemsetAsync(m->b_w, 0, (size_t)e->n_games * sizeof(uint32_t), e->stream));
     if (m->noise_eps != 0.0) {   // carried (already expanded) roots take the noise now, fresh ones after round 1
         TAFL_CUDA_TRY(e, cudaMemsetAsync(m->t_noised, 0, e->n_games, e->stream));
         k_mcts_root_noise<<<grid_for(e->n_games, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(m->v, e->n_games, m->d_noise, m->noise_eps, m->t_noised);
@@ -2075,10 +2391,10 @@ int tafl_mcts_select_leaves(tafl_engine* e, tafl_leaf_batch* out) {
     if (rc) return rc;
     MctsPools* m = e->mcts;
     if (m->phase != 1) { e->err = "tafl_mcts_select_leaves: call tafl_mcts_begin / tafl_mcts_expand_backup first"; return TAFL_ERR_INVALID_ARG; }
-    if (m->rounds >= m->cfg.num_sims) { e->err = "tafl_mcts_select_leaves: num_sims rounds already run (node pool is sized for num_sims)"; return TAFL_ERR_CAPACITY; }
+    if (m->rounds >= hook_rounds(m->cfg)) { e->err = "tafl_mcts_select_leaves: num_sims simulations already run (node pool is sized for num_sims)"; return TAFL_ERR_CAPACITY; }
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    if (e->hook_gen >= 2) {
+    if (e->hook_gen >= 2 || m->l_width > 1) {
         rc = hook_round_launch(e, 0, 1);
         if (rc) return rc;
     } else {   // first generation: one warp per tree (TAFL_HOOK_GEN=1; kept as the comparison point)
@@ -2099,7 +2415,7 @@ int tafl_mcts_expand_backup(tafl_engine* e) {
     if (m->phase != 2) { e->err = "tafl_mcts_expand_backup: no leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
     cudaSetDevice(e->device);
     const uint32_t n = e->n_games;
-    if (e->hook_gen >= 2) {
+    if (e->hook_gen >= 2 || m->l_width > 1) {
         rc = hook_round_launch(e, 1, 0);
         if (rc) return rc;
     } else {
@@ -2140,7 +2456,7 @@ int tafl_eval_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
     if (evaluator != TAFL_EVAL_STUB && evaluator != TAFL_EVAL_HASH) return TAFL_ERR_INVALID_ARG;
     if (!m->l_state) { e->err = "tafl_eval_builtin: no leaf batch (tafl_mcts_begin has not been called)"; return TAFL_ERR_INVALID_ARG; }
     cudaSetDevice(e->device);
-    const uint32_t n = e->n_games;
+    const uint32_t n = e->n_games * m->l_width;
     k_eval_builtin<<<grid_for(n, MCTS_WARPS), MCTS_WARPS * 32, 0, e->stream>>>(evaluator, seed, m->l_state, m->l_counts, n, m->l_priors,
                                                                               m->l_values);
     MCTS_LAUNCHED(e);
@@ -2154,7 +2470,7 @@ int tafl_leaf_batch_host(tafl_engine* e, tafl_state* h_states, uint8_t* h_planes
     MctsPools* m = e->mcts;
     if (m->phase != 2) { e->err = "tafl_leaf_batch_host: no leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
     cudaSetDevice(e->device);
-    const size_t n = e->n_games, cells = (size_t)e->N * e->N;
+    const size_t n = (size_t)e->n_games * m->l_width, cells = (size_t)e->N * e->N;
     if (h_states) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_states, m->l_state, n * sizeof(tafl_state), cudaMemcpyDeviceToHost, e->stream));
     if (h_planes) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_planes, m->l_planes, n * cells, cudaMemcpyDeviceToHost, e->stream));
     if (h_moves) TAFL_CUDA_TRY(e, cudaMemcpyAsync(h_moves, m->l_moves, n * TAFL_MAX_MOVES * sizeof(tafl_move), cudaMemcpyDeviceToHost, e->stream));
@@ -2168,7 +2484,7 @@ int tafl_leaf_eval_host(tafl_engine* e, const float* h_priors, const float* h_va
     MctsPools* m = e->mcts;
     if (m->phase != 2 || !h_priors || !h_values) { e->err = "tafl_leaf_eval_host: no leaf batch is pending"; return TAFL_ERR_INVALID_ARG; }
     cudaSetDevice(e->device);
-    const size_t n = e->n_games;
+    const size_t n = (size_t)e->n_games * m->l_width;
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(m->l_priors, h_priors, n * TAFL_MAX_MOVES * sizeof(float), cudaMemcpyHostToDevice, e->stream));
     TAFL_CUDA_TRY(e, cudaMemcpyAsync(m->l_values, h_values, n * sizeof(float), cudaMemcpyHostToDevice, e->stream));
     TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -2180,7 +2496,7 @@ int tafl_mcts_search_with(tafl_engine* e, tafl_evaluator_fn fn, void* user) {
     int rc = tafl_mcts_begin(e);
     if (rc) return rc;
     tafl_leaf_batch b;
-    for (uint32_t i = 0; i < e->mcts->cfg.num_sims; ++i) {
+    for (uint32_t i = 0, rounds = hook_rounds(e->mcts->cfg); i < rounds; ++i) {
         rc = tafl_mcts_select_leaves(e, &b);
         if (rc) return rc;
         rc = fn(user, &b);
@@ -2205,14 +2521,14 @@ int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
     // captured once per (evaluator, seed, config), replaces 3 x num_sims launches.
     if (!m->round_graph || m->rg_kind != evaluator || m->rg_seed != seed || m->rg_sims != m->cfg.num_sims ||
         m->rg_cpuct != m->cfg.cpuct || m->rg_draw != m->cfg.draw_value || m->rg_spec != e->spec || m->rg_eps != m->noise_eps ||
-        m->rg_gen != e->hook_gen * 2 + e->hook_fuse) {
+        m->rg_gen != (int)(e->hook_gen * 2 + e->hook_fuse + 8 * m->l_width)) {
         if (m->round_graph) { cudaGraphExecDestroy(m->round_graph); m->round_graph = nullptr; }
         TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         const uint64_t before = e->launches;
         cudaGraph_t graph = nullptr;
         TAFL_CUDA_TRY(e, cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
-        const bool fuse = e->hook_gen >= 2 && e->hook_fuse;
-        for (uint32_t i = 0; i < m->cfg.num_sims && rc == TAFL_OK; ++i) {
+        const bool fuse = (e->hook_gen >= 2 || m->l_width > 1) && e->hook_fuse;
+        for (uint32_t i = 0, rounds = hook_rounds(m->cfg); i < rounds && rc == TAFL_OK; ++i) {
             // round i: descent -> evaluator -> expand + backup.  Second generation: the expand + backup of round
             // i is fused into the launch that runs the descent of round i + 1 (two launches per simulation);
             // the root-noise kernel has to sit between the two after round 0, so that pair stays split.
@@ -2240,11 +2556,11 @@ int tafl_mcts_search_builtin(tafl_engine* e, int evaluator, uint64_t seed) {
         cudaGraphDestroy(graph);
         TAFL_CUDA_TRY(e, ce);
         m->rg_kind = evaluator; m->rg_seed = seed; m->rg_sims = m->cfg.num_sims; m->rg_cpuct = m->cfg.cpuct;
-        m->rg_draw = m->cfg.draw_value; m->rg_spec = e->spec; m->rg_eps = m->noise_eps; m->rg_gen = e->hook_gen * 2 + e->hook_fuse;
+        m->rg_draw = m->cfg.draw_value; m->rg_spec = e->spec; m->rg_eps = m->noise_eps; m->rg_gen = (int)(e->hook_gen * 2 + e->hook_fuse + 8 * m->l_width);
     }
     TAFL_CUDA_TRY(e, cudaGraphLaunch(m->round_graph, e->stream));
     e->launches += m->rg_launches;
-    m->rounds = m->cfg.num_sims;
+    m->rounds = hook_rounds(m->cfg);
     return tafl_mcts_finish(e);
 }
 

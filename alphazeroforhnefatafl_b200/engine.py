@@ -338,7 +338,9 @@ class LockstepGames:
 
     # -- MCTS (src/mcts.py) -----------------------------------------------------------------------
     def mcts_configure(self, num_sims, cpuct=1.0, draw_value=1e-4, edge_capacity=0, tree_reuse=False, node_capacity=0, vl_width=0):
-        """vl_width > 1: virtual loss, that many simulations in flight per tree (fused stub search only)"""
+        """vl_width > 1: virtual loss, that many simulations in flight per tree — in the fused stub search and through the
+        evaluator hook, where the leaf batch then has n_games * vl_width rows (row = game * vl_width + simulation)"""
+        self._hook_width = vl_width if vl_width > 1 else 1
         cfg = A.MctsConfig(num_sims=num_sims, cpuct=cpuct, draw_value=draw_value, edge_capacity=edge_capacity,
                            flags=A.MCTS_TREE_REUSE if tree_reuse else 0, node_capacity=node_capacity, vl_width=vl_width)
         self._ck(lib().tafl_mcts_configure(self._h, C.byref(cfg)))
@@ -426,7 +428,8 @@ class LockstepGames:
         self._ck(lib().tafl_mcts_search_builtin(self._h, evaluator, seed))
 
     def mcts_search_with(self, fn):
-        """fn(batch: LeafBatch) enqueues the evaluator on batch.stream; called num_sims times."""
+        """fn(batch: LeafBatch) enqueues the evaluator on batch.stream; called once per round (num_sims times, or
+        1 + ceil((num_sims - 1) / vl_width) with virtual loss)."""
         err = []
 
         def tramp(_user, bp):
@@ -442,8 +445,13 @@ class LockstepGames:
             raise err[0]
         self._ck(rc)
 
+    @property
+    def leaf_rows(self):
+        """rows of the evaluator hook's leaf batch"""
+        return self.n_games * getattr(self, "_hook_width", 1)
+
     def leaf_batch_host(self):
-        n, cells = self.n_games, self.side_len * self.side_len
+        n, cells = self.leaf_rows, self.side_len * self.side_len
         st = np.zeros(n, A.STATE_DTYPE)
         planes = np.zeros((n, cells), np.uint8)
         moves = np.zeros((n, A.MAX_MOVES), np.uint16)
@@ -454,7 +462,7 @@ class LockstepGames:
     def leaf_eval_host(self, priors, values):
         priors = np.ascontiguousarray(priors, np.float32)
         values = np.ascontiguousarray(values, np.float32)
-        assert priors.shape == (self.n_games, A.MAX_MOVES) and values.shape == (self.n_games,)
+        assert priors.shape == (self.leaf_rows, A.MAX_MOVES) and values.shape == (self.leaf_rows,)
         self._ck(lib().tafl_leaf_eval_host(self._h, A.ptr(priors), A.ptr(values)))
 
     def pack_records(self, d_out):

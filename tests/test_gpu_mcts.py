@@ -380,3 +380,79 @@ def test_gpu_virtual_loss_matches_oracle(orc, built_lib, name, preset, width, si
     with E.LockstepGames(rules, fen, 4, 0, width) as g:
         with pytest.raises(TaflError):
             g.mcts_configure(sims, 1.0, 1e-4, vl_width=17)
+
+
+@pytest.mark.parametrize("name,preset,width,sims", [("copenhagen", A.PRESET_COPENHAGEN, 128, 110), ("brandubh", A.PRESET_BRANDUBH, 64, 260),
+                                                    ("tablut", A.PRESET_TABLUT, 128, 150)])
+def test_gpu_virtual_loss_through_the_evaluator_hook(orc, built_lib, monkeypatch, name, preset, width, sims):
+    """k_mcts_hook_vl — W leaves per tree and round, the evaluator sees n_trees x W rows — against the oracle's
+    run_from_root_vl with the hash evaluator at W = 2, 4, 8, 16: visits, Q, statistics, games played over several moves
+    with tree reuse and root noise, fused and split launches; with the stub evaluator it equals the fused virtual-loss
+    kernel k_mcts_sims_vl bit for bit; the split C-ABI calls with host copies of the leaf batch drive the same kernel."""
+    rules, fen = orc.preset_rules(preset), board_for(orc, preset)
+    roots = sample_positions(orc, rules, fen, width, 203, seed=43, max_steps=260)
+    n, n_moves = len(roots), 3
+    rng = np.random.default_rng(5)
+    noise = rng.dirichlet(np.full(A.MAX_MOVES, 0.3), size=(n, n_moves))
+    for W, fuse, eps in ((2, "1", 0.0), (4, "1", 0.25), (8, "0", 0.0), (16, "1", 0.0)):
+        monkeypatch.setenv("TAFL_HOOK_FUSE", fuse)
+        exp = orc.mcts_episode_vl_eval(rules, width, roots, sims, n_moves, True, W, eval_seed=31, cpuct=1.3, draw_value=0.2,
+                                       n_threads=8, noise=noise if eps else None, eps=eps)
+        with E.LockstepGames(rules, fen, n, 0, width) as g:
+            g.set_states(roots)
+            g.mcts_configure(sims, 1.3, 0.2, tree_reuse=True, vl_width=W)
+            for j in range(n_moves):
+                if eps:
+                    g.mcts_root_noise(noise[:, j], eps)
+                g.mcts_search_builtin(A.EVAL_HASH, 31)
+                r = g.mcts_results()
+                assert np.array_equal(r["counts"], exp["counts"][:, j]), (W, j)
+                assert np.array_equal(r["visits"], exp["visits"][:, j]), (W, j)
+                assert r["q"].tobytes() == exp["q"][:, j].tobytes(), (W, j)
+                g.mcts_advance()
+            assert g.get_states().tobytes() == exp["final"].tobytes(), W
+            st = g.mcts_stats().as_dict()
+            for k in ("sims", "nodes", "edges", "terminal_hits", "depth_sum"):
+                assert st[k] == getattr(exp["stats"], k), (W, k)
+    monkeypatch.delenv("TAFL_HOOK_FUSE", raising=False)
+    # the stub evaluator through the hook == the fused virtual-loss kernel
+    for W in (4, 16):
+        res = {}
+        for mode in ("fused", "hook"):
+            with E.LockstepGames(rules, fen, n, 0, width) as g:
+                g.set_states(roots)
+                g.mcts_configure(sims, 1.0, 1e-4, vl_width=W)
+                if mode == "fused":
+                    g.mcts_search()
+                else:
+                    g.mcts_search_builtin(A.EVAL_STUB)
+                r = g.mcts_results()
+                res[mode] = (r["counts"].tobytes(), r["visits"].tobytes(), r["q"].tobytes(),
+                             {k: v for k, v in g.mcts_stats().as_dict().items() if k in ("sims", "nodes", "edges", "terminal_hits", "depth_sum")})
+        assert res["fused"] == res["hook"], W
+    # split calls, evaluator on the host: the batch has n * W rows, row = game * W + simulation
+    W = 4
+    exp = orc.mcts_episode_vl_eval(rules, width, roots[:40], 30, 1, False, W, eval_seed=None, n_threads=8)
+    with E.LockstepGames(rules, fen, 40, 0, width) as g:
+        g.set_states(roots[:40])
+        g.mcts_configure(30, 1.0, 1e-4, vl_width=W, edge_capacity=31 * 320)   # endgame roots: more than 160 plays per node
+        assert g.leaf_rows == 40 * W
+        g.mcts_begin()
+        rounds = 0
+        while True:
+            try:
+                g.mcts_select_leaves()
+            except TaflError:
+                break
+            b = g.leaf_batch_host()
+            assert b["counts"].shape == (40 * W,)
+            live = b["counts"].reshape(40, W) > 0
+            assert not live[:, 1:].any() if rounds == 0 else True        # the first batch of a fresh tree is its root alone
+            pri = np.full((40 * W, A.MAX_MOVES), 1.0 / A.MAX_MOVES, np.float32)
+            g.leaf_eval_host(pri, np.zeros(40 * W, np.float32))
+            g.mcts_expand_backup()
+            rounds += 1
+        assert rounds == 1 + (30 - 1 + W - 1) // W
+        g.mcts_finish()
+        r = g.mcts_results()
+        assert np.array_equal(r["visits"], exp["visits"][:, 0]) and r["q"].tobytes() == exp["q"][:, 0].tobytes()
