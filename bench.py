@@ -770,6 +770,27 @@ def _mcts_virtual_loss(cx, fresh):
             out["by_width"][str(W)] = (g.mcts_stats().as_dict()["sims"] - s0) / (a.elapsed_time(b) * 1e-3)
         finally:
             g.close()
+    # the same through the evaluator hook (stub evaluator on the device): W leaves per tree and round, the evaluator
+    # sees trees x W rows per call (k_mcts_hook_vl; W = 1 is k_mcts_hook_round)
+    from alphazeroforhnefatafl_b200 import _abi as A
+    out["hook_by_width"] = {}
+    for W in (1, 4, 8, 16):
+        g = fresh()
+        try:
+            g.mcts_configure(cx.args.mcts_sims, 1.0, 1e-4, vl_width=W)
+            st = torch.cuda.ExternalStream(g.stream, device=cx.local)
+            g.mcts_search_builtin(A.EVAL_STUB)          # captures the graph of rounds
+            s0 = g.mcts_stats().as_dict()["sims"]
+            with torch.cuda.stream(st):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(st)
+                for _ in range(3):
+                    g.mcts_search_builtin(A.EVAL_STUB)
+                b.record(st)
+                torch.cuda.synchronize()
+            out["hook_by_width"][str(W)] = (g.mcts_stats().as_dict()["sims"] - s0) / (a.elapsed_time(b) * 1e-3)
+        finally:
+            g.close()
     return out
 
 

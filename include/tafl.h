@@ -468,11 +468,15 @@ typedef struct {
     uint32_t flags;             /* TAFL_MCTS_*                                            */
     uint32_t node_capacity;     /* per-tree node pool, 0 = default num_sims+1 (x4 with
                                    tree reuse; a tree that outgrows it -> TAFL_ERR_CAPACITY) */
-    uint32_t vl_width;          /* virtual loss: simulations in flight per tree in tafl_mcts_search (0 / 1 = mcts.py's
-                                   sequential search; up to 16).  Build-defined semantics, restated in
+    uint32_t vl_width;          /* virtual loss: simulations in flight per tree (0 / 1 = mcts.py's sequential search;
+                                   up to 16).  Build-defined semantics, restated in
                                    oracle/mcts_oracle.hpp::run_from_root_vl: a batch of vl_width descents each sees
                                    the earlier ones as losses (n = N + vl, q = (N Q - vl) / n), then the new leaves
-                                   are expanded together and the batch is backed up in order.  Stub evaluator only. */
+                                   are expanded together and the batch is backed up in order.  Applies to
+                                   tafl_mcts_search (stub evaluator fused) and to the evaluator hook below, where
+                                   one round then carries vl_width leaves per tree: the leaf batch has
+                                   n_games * vl_width rows, row = game * vl_width + simulation, and a search takes
+                                   1 + ceil((num_sims - 1) / vl_width) rounds (a fresh root is a batch of one). */
 } tafl_mcts_config;
 
 /* allocate node/edge pools for every resident game (idempotent for an equal config) */
@@ -553,7 +557,7 @@ typedef struct {
     const uint32_t*   d_counts;   /* [n_games] legal moves; 0 = no evaluation wanted this round  */
     float*            d_priors;   /* [n_games][TAFL_MAX_MOVES] OUT                               */
     float*            d_values;   /* [n_games] OUT, from the point of view of the side to move   */
-    uint32_t          n_games, side_len;
+    uint32_t          n_games, side_len;   /* n_games = ROWS of the batch: resident games x max(1, vl_width) */
     void*             stream;     /* cudaStream_t the evaluator must enqueue its work on         */
 } tafl_leaf_batch;
 typedef int (*tafl_evaluator_fn)(void* user, const tafl_leaf_batch* batch);   /* 0 = ok */
