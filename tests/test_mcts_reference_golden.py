@@ -105,3 +105,30 @@ def test_oracle_virtual_loss_width_1_is_the_sequential_search(orc):
                 assert c["stats"].sims == a["stats"].sims
                 live = roots["status"] == 0
                 assert (c["visits"][:, 0].sum(1)[live] == sims - 1).all()      # the first simulation expands the root
+
+
+def test_oracle_virtual_loss_with_an_evaluator(orc):
+    """run_from_root_vl with the hash evaluator and root noise (what the evaluator hook runs with vl_width > 1): one
+    simulation in flight is the sequential evaluator search bit for bit; the stub through this entry point is the stub
+    virtual-loss search; wider batches keep the simulation count, differ in where the visits go, and a collision
+    (two simulations of one batch on the same fresh edge) takes the opener's leaf value instead of evaluating twice."""
+    import numpy as np
+    from alphazeroforhnefatafl_b200 import _abi as A
+    from parity_cases import sample_positions
+    for preset, width, sims in ((A.PRESET_BRANDUBH, 64, 150), (A.PRESET_COPENHAGEN, 128, 80)):
+        rules, fen = orc.preset_rules(preset), orc.preset_board(preset)
+        roots = sample_positions(orc, rules, fen, width, 16, seed=5, max_steps=200)
+        noise = np.random.default_rng(2).dirichlet(np.full(A.MAX_MOVES, 0.3), size=(len(roots), 2))
+        for reuse in (False, True):
+            for nz, eps in ((None, 0.0), (noise, 0.25)):
+                a = orc.mcts_episode(rules, width, roots, sims, 2, reuse, eval_seed=9, n_threads=4, noise=nz, eps=eps)
+                b = orc.mcts_episode_vl_eval(rules, width, roots, sims, 2, reuse, 1, eval_seed=9, n_threads=4, noise=nz, eps=eps)
+                assert np.array_equal(a["visits"], b["visits"]) and a["q"].tobytes() == b["q"].tobytes()
+                assert a["final"].tobytes() == b["final"].tobytes() and a["stats"].as_dict() == b["stats"].as_dict()
+            for W in (2, 16):
+                c = orc.mcts_episode_vl_eval(rules, width, roots, sims, 2, reuse, W, eval_seed=9, n_threads=4)
+                assert c["stats"].sims == a["stats"].sims
+                assert c["stats"].nodes <= a["stats"].nodes          # collisions open no node
+                s = orc.mcts_episode_vl(rules, width, roots, sims, 2, reuse, W, n_threads=4)
+                t = orc.mcts_episode_vl_eval(rules, width, roots, sims, 2, reuse, W, eval_seed=None, n_threads=4)
+                assert np.array_equal(s["visits"], t["visits"]) and s["q"].tobytes() == t["q"].tobytes()
