@@ -255,8 +255,13 @@ constexpr uint32_t CHAIN_SPIN_LIMIT = 1u << 22;       // ~ 0.3 s of polling: a l
 // states come from the staged copy of the caller's array (`src`); a row whose side_len is not the
 // engine's is rejected here (flag raised, the game keeps its resident state) instead of by a host
 // loop over 4 MiB of input before anything is enqueued.
+#if defined(TAFL_STEP_MAXNREG)   // A/B builds: an explicit register cap instead of the minimum-blocks hint
+#define TAFL_STEP_BOUNDS(MINB) __maxnreg__(TAFL_STEP_MAXNREG)
+#else
+#define TAFL_STEP_BOUNDS(MINB) __launch_bounds__(STEP_BLOCK, step_minb(MINB))
+#endif
 template <class BB, int SP, int MINB, bool BYVAL = false, bool SINGLE = false>
-__global__ void __launch_bounds__(STEP_BLOCK, step_minb(MINB))
+__global__ void TAFL_STEP_BOUNDS(MINB)
 k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
               uint32_t steps, int auto_reset, DevStats* __restrict__ stats, uint32_t* __restrict__ actions,
