@@ -1526,6 +1526,10 @@ k_mcts_hook_round(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t 
             if (!hdr_expanded(h.w)) { mode = M_LEAF; break; }   // the root of a fresh tree
             const uint32_t L = hdr_n_edges(h.w);
             if (L == 0) { v = 0.0; mode = M_BACKUP; break; }
+            if (gl < 3) {   // the node's state and piece table, wanted if the descent ends here with a new child (as k_mcts_sims_g)
+                const void* pf = gl == 0 ? (const void*)(n_state + node) : (const void*)(n_ptab + (size_t)node * MCTS_PT_MAX + (gl - 1) * 32);
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+            }
             uint32_t a, bN, bchild;
             grp_puct_select_priors<G>(edges + h.x, prior + h.x, L, h.y, cpuct, gmask, gl, a, bN, bchild);
             if (bN == 0) { mode = M_CREATE; sel_a = a; sel_base = h.x; break; }
@@ -1783,6 +1787,10 @@ k_mcts_hook_vl(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_t
                 if (!hdr_expanded(h.w)) { kind = VK_ROOT; leaf = node; break; }
                 const uint32_t L = hdr_n_edges(h.w);
                 if (L == 0) { kind = VK_EMPTY; leaf = node; break; }
+                if (gl < 3) {   // the node's state and piece table, wanted if the descent ends here with a new child
+                    const void* pf = gl == 0 ? (const void*)(n_state + node) : (const void*)(n_ptab + (size_t)node * MCTS_PT_MAX + (gl - 1) * 32);
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+                }
                 uint32_t a, bNraw, bchild;
                 grp_puct_select_priors_vl<G>(edges + h.x, prior + h.x, L, h.y, cpuct, gmask, gl, a, bNraw, bchild);
                 depth += 1;
