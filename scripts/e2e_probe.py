@@ -16,6 +16,36 @@ from alphazeroforhnefatafl_b200 import engine as E  # noqa: E402
 from alphazeroforhnefatafl_b200._lib import lib  # noqa: E402
 
 rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def physical_cores():
+    """logical CPUs grouped by physical core (thread_siblings_list), within what this process may use"""
+    allowed, cores, seen = os.sched_getaffinity(0), [], set()
+    for c in sorted(allowed):
+        if c in seen:
+            continue
+        try:
+            with open("/sys/devices/system/cpu/cpu%d/topology/thread_siblings_list" % c) as f:
+                sib = set()
+                for part in f.read().strip().split(","):
+                    lo, _, hi = part.partition("-")
+                    sib.update(range(int(lo), int(hi or lo) + 1))
+        except OSError:
+            sib = {c}
+        sib &= allowed
+        seen |= sib
+        cores.append(sorted(sib))
+    return cores
+
+
+if os.environ.get("PIN", "0") == "1" and world > 1:   # whole physical cores per rank: no two ranks share a core's hyperthreads
+    cores = physical_cores()
+    per = max(1, len(cores) // world)
+    mine = [c for core in cores[local * per:(local + 1) * per] for c in core]
+    if mine:
+        os.sched_setaffinity(0, mine)
+    if rank == 0:
+        print("pinning: %d physical cores, %d per rank, rank 0 on CPUs %s" % (len(cores), per, mine), flush=True)
 torch.cuda.set_device(local)
 if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
