@@ -298,6 +298,7 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
                     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(got) : "l"(chain + blockIdx.x) : "memory");
                     if (got == want) break;
                     if (++spins > CHAIN_SPIN_LIMIT) { atomicOr(chain + gridDim.x, 1u); break; }   // reported by the host, never a hang
+                    if ((spins & 4095u) == 0u && *(volatile uint32_t*)(chain + gridDim.x) != 0u) break;   // a token was already lost: do not wait again
                     if (TAFL_CHAIN_SLEEP) __nanosleep(TAFL_CHAIN_SLEEP);
                 }
             }
@@ -344,7 +345,8 @@ k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ s
     if (chained) {
         __syncthreads();                               // every state of this CTA is stored
         if (threadIdx.x == 0) {
-            const uint32_t token = chain_seq | (chain_pos + 1u);   // release: ordered after the barrier, hence after every thread's stores
+            uint32_t token = chain_seq | (chain_pos + 1u);   // release: ordered after the barrier, hence after every thread's stores
+            if (blockIdx.x == 0 && chain[gridDim.x + 1] == chain_pos + 1u) token = ~token;   // test hook (TAFL_STEP_CHAIN_LOSE): this token is lost
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(chain + blockIdx.x), "r"(token) : "memory");
         }
         // completion order of the nodes stays the launch order: this grid does not end before its predecessor has
@@ -1015,8 +1017,13 @@ static int step_graph_launch(tafl_engine* e, uint64_t seed, uint32_t n_steps, in
         if (chain && (!e->d_chain || e->chain_ctas != ctas)) {
             if (e->d_chain) cudaFree(e->d_chain);
             e->d_chain = nullptr;
-            TAFL_CUDA_TRY(e, cudaMalloc(&e->d_chain, ((size_t)ctas + 1) * sizeof(uint32_t)));
-            TAFL_CUDA_TRY(e, cudaMemsetAsync(e->d_chain, 0, ((size_t)ctas + 1) * sizeof(uint32_t), e->stream));
+            TAFL_CUDA_TRY(e, cudaMalloc(&e->d_chain, ((size_t)ctas + 2) * sizeof(uint32_t)));   // tokens, time-out word, test hook
+            TAFL_CUDA_TRY(e, cudaMemsetAsync(e->d_chain, 0, ((size_t)ctas + 2) * sizeof(uint32_t), e->stream));
+            if (const char* v = std::getenv("TAFL_STEP_CHAIN_LOSE")) {   // tests: node v (1-based) of every graph launch loses CTA 0's token
+                const uint32_t lose = (uint32_t)std::atoi(v);
+                TAFL_CUDA_TRY(e, cudaMemcpyAsync(e->d_chain + ctas + 1, &lose, sizeof(lose), cudaMemcpyHostToDevice, e->stream));
+                TAFL_CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+            }
             e->chain_ctas = ctas;
         }
         const uint64_t before = e->launches;

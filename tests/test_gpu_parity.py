@@ -375,6 +375,24 @@ def test_gpu_chained_step_graph_equals_whole_grid_dependencies(orc, built_lib, m
     assert got.tobytes() == exp.tobytes()
 
 
+def test_gpu_chained_step_graph_reports_a_lost_token(built_lib, monkeypatch):
+    """A CTA that never sees its predecessor's token must not hang the GPU: the poll gives up, the other CTAs stop
+    waiting, and the host call that synchronises next returns an error (the test hook makes CTA 0 of node 3 publish
+    a wrong token); the engine works again afterwards."""
+    import time
+    rules, fen = E.preset.rules.COPENHAGEN, E.preset.boards.COPENHAGEN
+    monkeypatch.setenv("TAFL_STEP_CHAIN", "2")
+    monkeypatch.setenv("TAFL_STEP_CHAIN_LOSE", "3")
+    with E.LockstepGames(rules, fen, 4096, 0, 128) as g:
+        t0 = time.perf_counter()
+        with pytest.raises(TaflError) as ei:
+            g.step_random(1, 16, steps_per_launch=1)
+        assert "token" in str(ei.value) and time.perf_counter() - t0 < 60.0
+        g.reset()
+        g.step_random(1, 3, steps_per_launch=1)          # fewer than four plies: plain launches, no chain
+        assert g.stats().as_dict()["steps"] > 0
+
+
 @pytest.mark.parametrize("name,preset,width", PRESET_CONFIGS[:3])
 def test_gpu_legal_move_kernels_agree(orc, built_lib, monkeypatch, name, preset, width):
     """get_all_possible_moves three ways — thread per game (TAFL_LM_G=1) and the warp-cooperative kernel with 8 and 16
