@@ -243,7 +243,11 @@ k_step_moves(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ st
 // Chaining pays once a grid has more than four 64-thread CTAs per SM (measured: 40 960 games 10.0 -> 7.6 us per ply, 65 536
 // 10.3 -> 8.95, 196 608 24.4 -> 22.7; below that the token hand-off costs more than the tail it hides: 32 768 games 6.8 -> 7.4)
 // and stops paying when the grid is many waves deep (524 288 games: 59.3 -> 60.1)
-constexpr uint32_t CHAIN_MIN_CTAS_PER_SM = 4, CHAIN_MAX_CTAS_PER_SM = 28;
+constexpr uint32_t CHAIN_MIN_CTAS_PER_SM = 4, CHAIN_MAX_CTAS_PER_SM = 28;   // in 64-game units per SM
+#if !defined(TAFL_CHAIN_BLOCK)
+#define TAFL_CHAIN_BLOCK 256
+#endif
+constexpr int CHAIN_BLOCK = TAFL_CHAIN_BLOCK;
 #if !defined(TAFL_CHAIN_SLEEP)
 #define TAFL_CHAIN_SLEEP 40
 #endif
@@ -258,9 +262,11 @@ constexpr uint32_t CHAIN_SPIN_LIMIT = 1u << 22;       // ~ 0.3 s of polling: a l
 #if defined(TAFL_STEP_MAXNREG)   // A/B builds: an explicit register cap instead of the minimum-blocks hint
 #define TAFL_STEP_BOUNDS(MINB) __maxnreg__(TAFL_STEP_MAXNREG)
 #else
-#define TAFL_STEP_BOUNDS(MINB) __launch_bounds__(STEP_BLOCK, step_minb(MINB))
+#define TAFL_STEP_BOUNDS(MINB) __launch_bounds__(BLOCK, (MINB) * 64 / BLOCK > 0 ? (MINB) * 64 / BLOCK : 1)
 #endif
-template <class BB, int SP, int MINB, bool BYVAL = false, bool SINGLE = false>
+// BLOCK: threads per CTA.  The nodes of a chained graph run CHAIN_BLOCK-thread CTAs (one token per 256 games instead
+// of per 64: 7.7 us per 65 536-game ply against 9.0 with 64, 8.55 with 128 and 9.2 with 512), everything else STEP_BLOCK.
+template <class BB, int SP, int MINB, bool BYVAL = false, bool SINGLE = false, int BLOCK = STEP_BLOCK>
 __global__ void TAFL_STEP_BOUNDS(MINB)
 k_step_random(const __grid_constant__ Ctx<BB, SP> cx, tafl_state* __restrict__ states, uint32_t n,
               const __grid_constant__ StateWords start_w, uint64_t seed, uint64_t gid_base, uint64_t ply0,
@@ -966,8 +972,10 @@ static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t firs
                               uint32_t steps, int auto_reset, const unsigned long long* d_ply_base = nullptr, bool pdl = false,
                               uint32_t* d_chain = nullptr) {
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid_for(n, STEP_BLOCK));
-    cfg.blockDim = dim3(STEP_BLOCK);
+    const bool chained = d_chain != nullptr && steps == 1 && e->step_single && e->step_minb == 8;
+    const unsigned block = chained ? CHAIN_BLOCK : STEP_BLOCK;
+    cfg.gridDim = dim3(grid_for(n, block));
+    cfg.blockDim = dim3(block);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -983,7 +991,12 @@ static int launch_step_random(tafl_engine* e, cudaStream_t stream, uint32_t firs
                                                      (const tafl_state*)nullptr, (uint32_t*)nullptr, d_chain)))
 #define TAFL_STEP_LAUNCH(MINB)                                     \
     do {                                                           \
-        if (steps == 1 && e->step_single && MINB == 8) TAFL_STEP_LAUNCH_(8, true); \
+        if (chained)                                               \
+            TAFL_SPEC_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, k_step_random<BB, SP, 8, false, true, CHAIN_BLOCK>, cx, e->d_states + first, n, \
+                                                             state_words(e->start), seed, e->game_id_base + first, ply0, steps, \
+                                                             auto_reset, e->d_stats, e->d_actions + first, d_ply_base,         \
+                                                             (const tafl_state*)nullptr, (uint32_t*)nullptr, d_chain)));      \
+        else if (steps == 1 && e->step_single && MINB == 8) TAFL_STEP_LAUNCH_(8, true); \
         else TAFL_STEP_LAUNCH_(MINB, false);                       \
     } while (0)
     switch (e->step_minb) {   // resident CTAs per SM the kernel is compiled for (register cap), see DESIGN.md
@@ -1006,14 +1019,14 @@ static int step_graph_launch(tafl_engine* e, uint64_t seed, uint32_t n_steps, in
     auto& k = e->step_graph_key;
     // CTA chaining needs the single-ply kernel, programmatic edges and a node index that fits the token
     // ... and pays when the grid is about one wave of CTAs (TAFL_STEP_CHAIN: 0 off, 1 by batch size, 2 always)
-    const uint32_t n_ctas = grid_for(e->n_games, STEP_BLOCK);
+    const uint32_t n_ctas = grid_for(e->n_games, 64);
     const bool chain_fits = e->step_chain_on == 2 || (n_ctas > CHAIN_MIN_CTAS_PER_SM * (uint32_t)e->sm_count && n_ctas <= CHAIN_MAX_CTAS_PER_SM * (uint32_t)e->sm_count);
     const int chain = e->step_chain_on && chain_fits && e->step_pdl_on && e->step_single && e->step_minb == 8 && n_steps < (1u << CHAIN_POS_BITS);
     if (!e->step_graph || k.seed != seed || k.steps != n_steps || k.auto_reset != auto_reset || k.minb != e->step_minb ||
         k.spec != e->spec || k.gid_base != e->game_id_base || k.chain != chain) {
         if (e->step_graph) { cudaGraphExecDestroy(e->step_graph); e->step_graph = nullptr; }
         if (!e->d_ply) TAFL_CUDA_TRY(e, cudaMalloc(&e->d_ply, 2 * sizeof(unsigned long long)));
-        const uint32_t ctas = grid_for(e->n_games, STEP_BLOCK);
+        const uint32_t ctas = grid_for(e->n_games, CHAIN_BLOCK);
         if (chain && (!e->d_chain || e->chain_ctas != ctas)) {
             if (e->d_chain) cudaFree(e->d_chain);
             e->d_chain = nullptr;
