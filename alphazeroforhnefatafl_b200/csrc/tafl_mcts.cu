@@ -339,15 +339,19 @@ __device__ __forceinline__ void grp_backup(uint4* __restrict__ n_hdr, MctsEdge* 
     }
 }
 
+#if !defined(TAFL_SIMS_WARPS)
+#define TAFL_SIMS_WARPS 4
+#endif
+constexpr int SIMS_WARPS = TAFL_SIMS_WARPS;   // warps per CTA of k_mcts_sims_g (they enter the create step together): 4 -> 4.09, 2 -> 3.92, 8 -> 3.84 x 10^8 sims/s
 template <class BB, int SP, int G, int MINB>
-__global__ void __launch_bounds__(MCTS_WARPS * 32, MINB)
+__global__ void __launch_bounds__(SIMS_WARPS * 32, (MINB * 4 / SIMS_WARPS > 0 ? MINB * 4 / SIMS_WARPS : 1))
 k_mcts_sims_g(const __grid_constant__ Ctx<BB, SP> cx, MctsView mv, uint32_t n_trees, uint32_t sims, double cpuct, double draw_value,
               uint32_t* __restrict__ any_overflow) {
     constexpr int TPW = 32 / G;
     enum { M_NONE = 0, M_BACKUP, M_CREATE, M_EXPAND };
     const int lane = threadIdx.x & 31, gl = lane % G, gshift = (lane / G) * G;
     const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << (G & 31)) - 1u) << gshift);
-    const uint32_t tree_raw = (blockIdx.x * MCTS_WARPS + (threadIdx.x >> 5)) * TPW + (uint32_t)(lane / G);
+    const uint32_t tree_raw = (blockIdx.x * SIMS_WARPS + (threadIdx.x >> 5)) * TPW + (uint32_t)(lane / G);
     const bool live = tree_raw < n_trees;
     const uint32_t tree = live ? tree_raw : 0u;
     tafl_state* const n_state = mv.n_state + (size_t)tree * mv.node_cap;
@@ -2091,7 +2095,7 @@ int tafl_mcts_search_async(tafl_engine* e) {
                                                                                            m->cfg.cpuct, m->cfg.draw_value, \
                                                                                            m->d_any_overflow)))
 #define TAFL_MCTS_LAUNCH_G(G, MINB)                                                                                         \
-    TAFL_SPEC_DISPATCH(e, (k_mcts_sims_g<BB, SP, G, MINB><<<grid_for(n, MCTS_WARPS * (32 / G)), MCTS_WARPS * 32, 0, e->stream>>>( \
+    TAFL_SPEC_DISPATCH(e, (k_mcts_sims_g<BB, SP, G, MINB><<<grid_for(n, SIMS_WARPS * (32 / G)), SIMS_WARPS * 32, 0, e->stream>>>( \
                               cx, m->v, n, m->cfg.num_sims, m->cfg.cpuct, m->cfg.draw_value, m->d_any_overflow)))
     if (m->cfg.vl_width > 1) {        // virtual loss: vl_width (<= 16) simulations in flight per tree, 16 lanes per tree
         TAFL_SPEC_DISPATCH(e, (k_mcts_sims_vl<BB, SP, 16><<<grid_for(n, MCTS_WARPS * 2), MCTS_WARPS * 32, 0, e->stream>>>(
